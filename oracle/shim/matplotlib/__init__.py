@@ -1,0 +1,35 @@
+"""No-op matplotlib so reference modules that style plots at import time load (cmb/Nkk.py:11)."""
+import types, sys
+
+
+class _Any:
+    def __getattr__(self, name):
+        return _Any()
+
+    def __call__(self, *a, **k):
+        return _Any()
+
+    def __getitem__(self, k):
+        return _Any()
+
+    def __setitem__(self, k, v):
+        pass
+
+    def __iter__(self):
+        return iter(())
+
+
+rcParams = _Any()
+style = _Any()
+
+
+def use(*a, **k):
+    pass
+
+
+pyplot = types.ModuleType('matplotlib.pyplot')
+pyplot.__getattr__ = lambda name: _Any()
+sys.modules['matplotlib.pyplot'] = pyplot
+pylab = types.ModuleType('pylab')
+pylab.__getattr__ = lambda name: _Any()
+sys.modules['pylab'] = pylab
