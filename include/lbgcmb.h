@@ -1,0 +1,80 @@
+/* lbgcmb.h -- C ABI of liblbgcmb.so, the B200 (sm_100a) implementation of the LBGCMB forecast hot path.
+ *
+ * The reference (michaelJwilson/LBGCMB) has no FFI: its boundary is a set of plain Python functions
+ * (SURVEY.md 8(b)).  Each entry point below names the reference function whose arithmetic it replaces;
+ * the Python mirrors in lbgcmb_b200/ (same names / argument meaning as the reference) are thin ctypes
+ * callers of these.  All pointers are HOST pointers to C-contiguous arrays owned by the caller; the
+ * library copies host<->device itself.  Every function returns 0 on success or a negative LBG_E* code;
+ * lbg_last_error() gives the message of the last failure on the calling thread.
+ * There is no CPU fallback: without a CUDA device lbg_ctx_create() fails.
+ */
+#ifndef LBGCMB_H
+#define LBGCMB_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LBG_OK          0
+#define LBG_EINVAL     -1   /* bad argument                     */
+#define LBG_ECUDA      -2   /* CUDA runtime error               */
+#define LBG_ESTATE     -3   /* required table not uploaded yet  */
+#define LBG_ENOMEM     -4
+
+/* estimator bits for `terms_mask` (cmb/Nkk.py:31 `terms`) */
+#define LBG_TT  1u
+#define LBG_TE  2u
+#define LBG_EE  4u
+#define LBG_EB  8u
+#define LBG_BB 16u
+
+typedef struct lbg_ctx lbg_ctx;   /* opaque: device, stream, uploaded tables, workspaces */
+
+/* ---- context ------------------------------------------------------------------------------------------- */
+int         lbg_ctx_create(int device, lbg_ctx** out);
+int         lbg_ctx_destroy(lbg_ctx* ctx);
+const char* lbg_last_error(void);
+const char* lbg_version(void);
+/* Device time (ms, CUDA events on the context's stream) spent in the kernels of the last compute call,
+ * and the number of kernel launches that call made. */
+int         lbg_last_kernel_ms(lbg_ctx* ctx, double* ms, int* launches);
+/* Dependent-DFMA micro-benchmark: measured FP64 FMA throughput of this GPU in TFLOP/s (FMA = 2 flop).
+ * This is the denominator of the N0 roofline. */
+int         lbg_fp64_peak(lbg_ctx* ctx, double* tflops);
+
+/* ---- CMB spectra tables: replaces the dict of cubic interp1d objects built by prep_camb.py:86-89 ------- */
+/* C_l on integer knots l = 0..n_ell-1, raw and dimensionless, order TT,EE,BB,TE (prep_camb.py:84).
+ * The library builds the not-a-knot cubic spline of scipy `interp1d(kind='cubic')` itself (value 0 outside
+ * the table, bounds_error=False / fill_value=0.0). */
+int lbg_upload_cl_tables(lbg_ctx* ctx, int n_ell, const double* lensed /*[4][n_ell]*/,
+                         const double* unlensed /*[4][n_ell]*/);
+/* Evaluate the uploaded splines (prep_camb.py:88-89 callables): which = 0 lensed / 1 unlensed, spec = 0..3. */
+int lbg_eval_cl(lbg_ctx* ctx, int which, int spec, int n, const double* x, double* out);
+
+/* One-shot scipy `interp1d(arange(n_knots), y, kind='cubic', bounds_error=False, fill_value=0.0)(x)`. */
+int lbg_eval_spline(lbg_ctx* ctx, int n_knots, const double* y, int n, const double* x, double* out);
+/* Host-only (no GPU): the n_knots+2 uniform cubic B-spline coefficients c[-1..n_knots] of that spline. */
+int lbg_cubic_spline_coeffs(int n_knots, const double* y, double* coef_out /*[n_knots+2]*/);
+
+/* ---- N0, root flavour: replaces cmb/Nkk.py:54-172 (Nkk), :13-26 (prep_lmaxmask), prep_camb.py:128-137
+ *      (Clxy) and cmb/DetectorNoise.py:8-32 ------------------------------------------------------------------
+ * Quadrature nodes/weights are explicit ("kernels take weights, never a rule"):
+ *   l1[n_l1], w_l1[n_l1]         the |u| grid (reference: arange(1, 5000.5, 0.5)) and its Simpson weights
+ *   cos_phi/sin_phi/w_phi[n_phi]  the phi grid (reference: arange(0, 2pi+dphi, dphi)) and its weights
+ * integral(L) = sum_ij w_phi[j] w_l1[i] l1[i] * sum_terms f F mask ;  N0 = (L(L+1)/2)^2 (2pi)^2 / integral.
+ * lmax_T / lmax_P / lmin_v: the 3000 / 5000 / 2 cuts of prep_lmaxmask.  `fold_phi` != 0 lets the library
+ * evaluate only one node of each mirror pair (phi, 2pi-phi); the number of integrand nodes
+ * actually executed is returned in *nodes_executed (may be NULL).
+ * out_terms (may be NULL) receives the per-estimator integrals, [5][n_L] in bit order TT,TE,EE,EB,BB. */
+int lbg_n0_ho02(lbg_ctx* ctx, int n_L, const double* L, unsigned terms_mask,
+                double thetab_arcmin, double deltaT_uK_arcmin, double Tcmb_K, int iterative,
+                int n_l1, const double* l1, const double* w_l1,
+                int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
+                double lmax_T, double lmax_P, double lmin_v, int fold_phi,
+                double* out_nkk /*[n_L]*/, double* out_terms /*[5][n_L] or NULL*/,
+                long long* nodes_executed /*or NULL*/);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LBGCMB_H */

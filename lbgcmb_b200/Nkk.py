@@ -1,0 +1,118 @@
+"""Hu-Okamoto N0 lensing-reconstruction noise; mirrors reference cmb/Nkk.py:31-184 (`Nkk`).
+
+Same signature, argument meaning, defaults and return type (float64[len(Ls)]).  The (phi, l1, L) cube of the
+reference (cmb/Nkk.py:54-167) is never materialised: the quadrature nodes/weights are built here exactly as
+the reference builds them and the integrand is evaluated by the sm_100a kernel in csrc/n0.cu through
+lbg_n0_ho02.  There is no CPU path.
+"""
+import os
+from pickle import load, dump
+
+import numpy as np
+
+from lbgcmb_b200 import _ffi
+from lbgcmb_b200.params import get_params
+from lbgcmb_b200.prep_camb import table_of
+
+TERM_BITS = {'TT': 1, 'TE': 2, 'EE': 4, 'EB': 8, 'BB': 16}
+_ORDER = ('TT', 'EE', 'BB', 'TE')
+
+# set by every Nkk()/n0_terms() call: integrand nodes executed, kernel ms, launches
+last_stats = {}
+
+
+def _simpson_weights(n, dx):
+    """Composite Simpson weights for an odd number of uniform samples (scipy simps, cmb/Nkk.py:166-167)."""
+    if n % 2 == 0:
+        raise ValueError('the reference N0 grids are odd-length (SURVEY.md N5)')
+    w = np.zeros(n)
+    w[0:n - 2:2] += dx / 3.0
+    w[1:n - 1:2] += 4.0 * dx / 3.0
+    w[2:n:2] += dx / 3.0
+    return w
+
+
+def root_grids(lmax=5000., Nphi=200, Nell=10000):
+    """Nodes and weights of cmb/Nkk.py:54-62,166-167: ell (9999), phi (201); note the swapped dx labels (N5)."""
+    dphi = 2. * np.pi / Nphi
+    dell = lmax / Nell
+    ell = np.arange(1.0, lmax + dell, dell)
+    pphi = np.arange(0.0, 2. * np.pi + dphi, dphi)
+    w_phi = _simpson_weights(pphi.size, dell)     # first simps pass runs over phi with dx=dell
+    w_ell = _simpson_weights(ell.size, dphi)      # second over l1 with dx=dphi
+    return ell, w_ell, pphi, w_phi
+
+
+def upload_cls(ctx, lensCl_interps, nolensCl_interps):
+    lens = [table_of(lensCl_interps[x]) for x in _ORDER]
+    n = min(t.size for t in lens)
+    nolens = []
+    for x in _ORDER:
+        nolens.append(table_of(nolensCl_interps[x], n_default=n))
+    n = min(n, min(t.size for t in nolens))
+    lt = _ffi.f64(np.stack([t[:n] for t in lens]))
+    ut = _ffi.f64(np.stack([t[:n] for t in nolens]))
+    _ffi.check(_ffi.lib().lbg_upload_cl_tables(ctx.handle, n, _ffi._dp(lt), _ffi._dp(ut)))
+    return n
+
+
+def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'), thetab=1., DeltaT=1.,
+             iterative=False, fold_phi=True, device=None, Tcmb=None, grids=None,
+             lmax_T=3000., lmax_P=5000., lmin_v=2., cos_sin=None):
+    """(N0[len(Ls)], {term: integral[len(Ls)]}) -- the combined noise plus the per-estimator integrals."""
+    for t in terms:
+        if t == 'TB':
+            raise KeyError('TB')   # the reference indexes nolensCl_interps['TB'], which get_Cls never builds
+        if t not in TERM_BITS:
+            raise ValueError('unknown estimator %s' % t)
+    mask = 0
+    for t in terms:
+        mask |= TERM_BITS[t]
+    ctx = _ffi.context(device)
+    upload_cls(ctx, lensCl_interps, nolensCl_interps)
+    ell, w_ell, pphi, w_phi = grids if grids is not None else root_grids()
+    Ld = _ffi.f64(Ls)
+    if cos_sin is None:
+        cos_sin = (np.cos(pphi), np.sin(pphi))
+    cphi, sphi = _ffi.f64(cos_sin[0]), _ffi.f64(cos_sin[1])
+    ell, w_ell, w_phi = _ffi.f64(ell), _ffi.f64(w_ell), _ffi.f64(w_phi)
+    out = np.empty(Ld.size)
+    out_terms = np.empty((5, Ld.size))
+    import ctypes as C
+    nodes = C.c_longlong(0)
+    if Tcmb is None:
+        Tcmb = get_params()['Tcmb']
+    _ffi.check(_ffi.lib().lbg_n0_ho02(ctx.handle, Ld.size, _ffi._dp(Ld), mask, float(thetab), float(DeltaT),
+                                      float(Tcmb), int(bool(iterative)), ell.size, _ffi._dp(ell), _ffi._dp(w_ell),
+                                      pphi.size, _ffi._dp(cphi), _ffi._dp(sphi), _ffi._dp(w_phi),
+                                      float(lmax_T), float(lmax_P), float(lmin_v), int(bool(fold_phi)),
+                                      _ffi._dp(out), _ffi._dp(out_terms), C.byref(nodes)))
+    ms, launches = ctx.last_kernel_ms()
+    last_stats.update(nodes=nodes.value, kernel_ms=ms, launches=launches, n_L=Ld.size)
+    return out, {t: out_terms[i] for i, t in enumerate(('TT', 'TE', 'EE', 'EB', 'BB'))}
+
+
+def _cache_path(Ls, terms, thetab, DeltaT, iterative):
+    root = os.environ['LBGCMB']
+    fpath = root + '/pickle/Nkk_thetab_%.2lf_DeltaT_%.2lf_' % (thetab, DeltaT) + 'Nlls_%d_Lmin_%d_Lmax_%d_' % (len(Ls), Ls[0], Ls[-1])
+    fpath += '_'.join(terms) + '_iterative_%d.p' % int(iterative == True)  # noqa: E712 (reference spelling)
+    return fpath
+
+
+def Nkk(lensCl_interps, nolensCl_interps, Ls, terms=['TT', 'TE', 'EE', 'EB'], thetab=1., DeltaT=1., iterative=False,
+        pickleit=True):
+    """Ckk noise curve for the flat-sky limit (Hu & Okamoto 2002); drop-in for cmb/Nkk.py:31.
+
+    The pickle cache of cmb/Nkk.py:36-46,174-182 is honoured only when $LBGCMB is set."""
+    have_root = 'LBGCMB' in os.environ
+    if have_root:
+        try:
+            return load(open(_cache_path(Ls, terms, thetab, DeltaT, iterative), 'rb'))
+        except Exception:
+            pass
+    result, _ = n0_terms(lensCl_interps, nolensCl_interps, Ls, terms, thetab, DeltaT, iterative)
+    if pickleit and have_root:
+        fpath = _cache_path(Ls, terms, thetab, DeltaT, iterative)
+        os.makedirs(os.path.dirname(fpath), exist_ok=True)
+        dump(result, open(fpath, 'wb'))
+    return result

@@ -1,0 +1,126 @@
+"""ctypes binding of liblbgcmb.so (include/lbgcmb.h).  No CPU fallback: a missing library or GPU raises."""
+import ctypes as C
+import os
+import threading
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'liblbgcmb.so')
+
+_lib = None
+_lock = threading.Lock()
+_ctxs = {}
+
+c_double_p = C.POINTER(C.c_double)
+c_ll_p = C.POINTER(C.c_longlong)
+c_int_p = C.POINTER(C.c_int)
+
+
+class LbgError(RuntimeError):
+    pass
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_double_p) if a is not None else None
+
+
+def f64(a):
+    """C-contiguous float64 copy/view of `a` (what every entry point expects)."""
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def lib():
+    """Load liblbgcmb.so (built by lbgcmb_b200/csrc/build.sh or __graft_entry__.build())."""
+    global _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.isfile(LIB_PATH):
+                raise LbgError('%s not found: run lbgcmb_b200/csrc/build.sh (there is no CPU fallback)' % LIB_PATH)
+            L = C.CDLL(LIB_PATH)
+            L.lbg_last_error.restype = C.c_char_p
+            L.lbg_version.restype = C.c_char_p
+            _declare(L)
+            _lib = L
+    return _lib
+
+
+def _declare(L):
+    vp, i, d, u = C.c_void_p, C.c_int, C.c_double, C.c_uint
+    sig = {
+        'lbg_ctx_create': [i, C.POINTER(vp)],
+        'lbg_ctx_destroy': [vp],
+        'lbg_last_kernel_ms': [vp, c_double_p, c_int_p],
+        'lbg_fp64_peak': [vp, c_double_p],
+        'lbg_upload_cl_tables': [vp, i, c_double_p, c_double_p],
+        'lbg_eval_cl': [vp, i, i, i, c_double_p, c_double_p],
+        'lbg_eval_spline': [vp, i, c_double_p, i, c_double_p, c_double_p],
+        'lbg_cubic_spline_coeffs': [i, c_double_p, c_double_p],
+        'lbg_n0_ho02': [vp, i, c_double_p, u, d, d, d, i, i, c_double_p, c_double_p, i, c_double_p, c_double_p,
+                        c_double_p, d, d, d, i, c_double_p, c_double_p, c_ll_p],
+    }
+    for name, args in sig.items():
+        fn = getattr(L, name)
+        fn.argtypes = args
+        fn.restype = C.c_int
+
+
+def check(rc):
+    if rc != 0:
+        msg = lib().lbg_last_error().decode('utf-8', 'replace')
+        if rc == -1:
+            raise ValueError(msg)
+        raise LbgError('liblbgcmb error %d: %s' % (rc, msg))
+
+
+class Context:
+    """One per GPU: owns the stream, the uploaded tables and the workspaces (lbg_ctx)."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        self.device = device
+        check(lib().lbg_ctx_create(int(device), C.byref(self._h)))
+        self._cl_key = None
+
+    def close(self):
+        if self._h:
+            lib().lbg_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    def last_kernel_ms(self):
+        ms, n = C.c_double(), C.c_int()
+        check(lib().lbg_last_kernel_ms(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def fp64_peak_tflops(self):
+        v = C.c_double()
+        check(lib().lbg_fp64_peak(self._h, C.byref(v)))
+        return v.value
+
+
+def default_device():
+    """LOCAL_RANK under torchrun (one process per GPU), else LBGCMB_DEVICE, else 0."""
+    return int(os.environ.get('LBGCMB_DEVICE', os.environ.get('LOCAL_RANK', '0')))
+
+
+def context(device=None):
+    """Process-wide context cache keyed by device index."""
+    if device is None:
+        device = default_device()
+    with _lock:
+        ctx = _ctxs.get(device)
+    if ctx is None:
+        ctx = Context(device)
+        with _lock:
+            _ctxs[device] = ctx
+    return ctx

@@ -1,0 +1,95 @@
+// common.cuh -- context object, error plumbing and small device helpers shared by all kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <mutex>
+#include "../../include/lbgcmb.h"
+
+namespace lbg {
+
+void set_error(const char* fmt, ...);
+
+#define LBG_CUDA(call)                                                                     \
+    do {                                                                                   \
+        cudaError_t e__ = (call);                                                          \
+        if (e__ != cudaSuccess) {                                                          \
+            lbg::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            return LBG_ECUDA;                                                              \
+        }                                                                                  \
+    } while (0)
+
+#define LBG_REQUIRE(cond, ...)            \
+    do {                                  \
+        if (!(cond)) {                    \
+            lbg::set_error(__VA_ARGS__);  \
+            return LBG_EINVAL;            \
+        }                                 \
+    } while (0)
+
+// Grow-only device buffer.
+struct DevBuf {
+    void*  p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes) {
+        if (bytes <= cap) return LBG_OK;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) { set_error("cudaMalloc(%zu) -> %s", bytes, cudaGetErrorString(e)); return LBG_ENOMEM; }
+        cap = bytes;
+        return LBG_OK;
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+// One row of the CMB spline table per integer knot: uniform cubic B-spline coefficients of the eight
+// spectra, 64 bytes, so that one knot = two 32-byte sectors.
+struct __align__(64) ClRow {
+    double uTT, uTE, uEE, uBB;   // unlensed (gradient) spectra, enter f_alpha
+    double lTT, lTE, lEE, lBB;   // lensed spectra, enter the filters (noise added analytically)
+};
+
+}  // namespace lbg
+
+struct lbg_ctx {
+    int          device = 0;
+    int          sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
+    double       last_ms = 0.0;
+    int          last_launches = 0;
+    std::mutex   mu;
+    // CMB tables
+    int          n_ell = 0;          // knots 0..n_ell-1
+    lbg::DevBuf  cl_rows;            // ClRow[n_ell + 2], row r holds coefficient index r-1
+    // N0 workspaces
+    lbg::DevBuf  n0_L, n0_utab, n0_phi, n0_partial, n0_out, n0_rowflag;
+    // generic scratch
+    lbg::DevBuf  s0, s1, s2, s3, s4, s5;
+    // P(k) / Limber state (see limber.cu)
+    int          n_k = 0;
+    lbg::DevBuf  pk_lnk, pk_plin;
+    int          pnl_nz = 0;
+    lbg::DevBuf  pk_pnl;
+};
+
+namespace lbg {
+struct KernelTimer {   // records ev0/ev1 on the context stream around the kernels of one API call
+    lbg_ctx* c;
+    explicit KernelTimer(lbg_ctx* ctx) : c(ctx) { c->last_launches = 0; cudaEventRecord(c->ev0, c->stream); }
+    void launched(int n = 1) { c->last_launches += n; }
+    int finish() {
+        cudaError_t e = cudaEventRecord(c->ev1, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e == cudaSuccess) { float ms = 0.f; e = cudaEventElapsedTime(&ms, c->ev0, c->ev1); c->last_ms = ms; }
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("kernel execution failed: %s", cudaGetErrorString(e)); return LBG_ECUDA; }
+        return LBG_OK;
+    }
+};
+}  // namespace lbg

@@ -1,0 +1,113 @@
+"""GPU parity: lbg_n0_ho02 (csrc/n0.cu) through the Python mirror of cmb/Nkk.py:31 vs
+  (a) golden vectors produced by the UNMODIFIED reference (tests/golden/n0_root_*.npz, oracle/make_golden.py),
+  (b) the numpy oracle (oracle/n0.py) on the same seeded inputs,
+  (c) size-independent properties at BASELINE grid sizes.
+Tolerance: relative 1e-10 (BASELINE.json north_star), FP64."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-10
+
+
+def _interps(ell, lens, nolens):
+    from lbgcmb_b200.prep_camb import cl_interps_from_tables
+    return cl_interps_from_tables(ell, lens, nolens)
+
+
+def test_spline_eval_matches_interp1d(ctx, cl_tables):
+    from scipy.interpolate import interp1d
+    from lbgcmb_b200.prep_camb import ClInterp
+    ell, lens, _ = cl_tables
+    x = np.random.default_rng(5).uniform(2, ell[-1], 20000)
+    for k in range(3):
+        got = ClInterp(ell, lens[k])(x)
+        ref = interp1d(ell, lens[k], kind='cubic', bounds_error=False, fill_value=0.0)(x)
+        assert np.max(np.abs(got / ref - 1)) < 1e-13
+    f = ClInterp(ell, lens[0])
+    assert f(np.array([-1.0, ell[-1] + 0.5])).tolist() == [0.0, 0.0]     # fill_value=0.0 outside the table
+    assert isinstance(f(10.0), float)
+
+
+@pytest.mark.parametrize('fold', [False, True])
+def test_golden_reference_vectors(ctx, golden_dir, fold):
+    from lbgcmb_b200 import Nkk
+    files = sorted(glob.glob(os.path.join(golden_dir, 'n0_root_*.npz')))
+    assert files, 'golden fixtures missing'
+    for f in files:
+        g = np.load(f)
+        li, ni = _interps(g['ell'], g['lensed'], g['unlensed'])
+        out, _ = Nkk.n0_terms(li, ni, g['Ls'], [str(t) for t in g['terms']], float(g['thetab']), float(g['DeltaT']),
+                              bool(g['iterative']), fold_phi=fold, Tcmb=float(g['Tcmb']),
+                              cos_sin=(g['cos_phi'], g['sin_phi']))
+        rel = np.max(np.abs(out / g['nkk_reference'] - 1))
+        assert rel < RTOL, '%s fold=%s rel=%.3e' % (os.path.basename(f), fold, rel)
+
+
+def test_against_live_oracle(ctx, cl_tables):
+    from oracle import n0 as on0
+    from lbgcmb_b200 import Nkk
+    ell, lens, nolens = cl_tables
+    Ls = np.array([50, 517, 5000])
+    ref = on0.nkk_root(on0.cl_interps(ell, lens), on0.cl_interps(ell, nolens), Ls, ('TT', 'TE', 'EE', 'EB'),
+                       1.4, 1.0, True)
+    li, ni = _interps(ell, lens, nolens)
+    for fold in (False, True):
+        got = Nkk.Nkk(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, iterative=True, pickleit=False) if fold else \
+            Nkk.n0_terms(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True, fold_phi=False)[0]
+        assert np.max(np.abs(got / ref - 1)) < RTOL
+
+
+def test_single_estimators_and_bb_against_oracle(ctx, cl_tables):
+    from oracle import n0 as on0
+    from lbgcmb_b200 import Nkk
+    ell, lens, nolens = cl_tables
+    nolens = nolens.copy()
+    nolens[2] = 0.5 * lens[2]          # non-zero unlensed BB so the BB estimator is exercised
+    Ls = np.array([333])
+    oi = (on0.cl_interps(ell, lens), on0.cl_interps(ell, nolens))
+    li, ni = _interps(ell, lens, nolens)
+    for terms in (['TT'], ['TE'], ['EE'], ['EB'], ['BB']):
+        ref = on0.nkk_root(oi[0], oi[1], Ls, tuple(terms), 3.0, 5.0, False)
+        got = Nkk.n0_terms(li, ni, Ls, terms, 3.0, 5.0, False)[0]
+        assert np.max(np.abs(got / ref - 1)) < RTOL, terms
+
+
+def test_grid_A_properties(ctx, cl_tables):
+    """Full reference grid (60 L, 50..5000): fold == unfold, min-variance sum of the per-estimator integrals."""
+    from lbgcmb_b200 import Nkk
+    from lbgcmb_b200.prep_Llls import prep_Llls
+    ell, lens, nolens = cl_tables
+    li, ni = _interps(ell, lens, nolens)
+    _, Llls, _ = prep_Llls(60, 50, 5000, log10=True)
+    a, ta = Nkk.n0_terms(li, ni, Llls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True, fold_phi=True)
+    b, tb = Nkk.n0_terms(li, ni, Llls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True, fold_phi=False)
+    assert np.all(np.isfinite(a)) and np.all(a > 0)
+    assert np.max(np.abs(a / b - 1)) < 1e-11
+    tot = ta['TT'] + ta['TE'] + ta['EE'] + 2.5 * ta['EB']
+    pre = (Llls * (Llls + 1.) / 2.) ** 2.
+    assert np.max(np.abs(pre * (2 * np.pi) ** 2 / tot / a - 1)) < 1e-13
+    # each estimator alone is noisier than the combination
+    for t in ('TT', 'TE', 'EE', 'EB'):
+        assert np.all(pre * (2 * np.pi) ** 2 / ta[t] > a)
+    # deterministic: bitwise identical on a second run
+    a2, _ = Nkk.n0_terms(li, ni, Llls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True, fold_phi=True)
+    assert np.array_equal(a, a2)
+    assert Nkk.last_stats['nodes'] == 60 * 101 * 9999
+
+
+def test_edge_cases(ctx, cl_tables):
+    from lbgcmb_b200 import Nkk
+    ell, lens, nolens = cl_tables
+    li, ni = _interps(ell, lens, nolens)
+    assert Nkk.Nkk(li, ni, np.array([], dtype=int), pickleit=False).shape == (0,)
+    with pytest.raises(KeyError):
+        Nkk.Nkk(li, ni, np.array([100]), terms=['TB'], pickleit=False)
+    with pytest.raises(ValueError):
+        Nkk.Nkk(li, ni, np.array([100]), terms=['XY'], pickleit=False)
+    one = Nkk.Nkk(li, ni, np.array([100]), pickleit=False)
+    many = Nkk.Nkk(li, ni, np.array([100, 100, 4000, 100]), pickleit=False)
+    assert many[0] == one[0] == many[1] == many[3]
