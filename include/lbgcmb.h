@@ -65,12 +65,18 @@ int lbg_cubic_spline_coeffs(int n_knots, const double* y, double* coef_out /*[n_
  * lmax_T / lmax_P / lmin_v: the 3000 / 5000 / 2 cuts of prep_lmaxmask.  `fold_phi` != 0 lets the library
  * evaluate only one node of each mirror pair (phi, 2pi-phi); the number of integrand nodes
  * actually executed is returned in *nodes_executed (may be NULL).
+ * exact_rows[n_exact] / exact_u[n_exact][n_phi][8] (optional, n_exact may be 0): rows of the l1 grid for which the caller
+ * supplies its own u-side spline values at |u|_j = sqrt((l cos_j)^2 + (l sin_j)^2), order unlensed TT,TE,EE,BB then lensed
+ * TT,TE,EE,BB.  Needed for bit-faithful parity with the reference on rows below the first non-zero C_l (l1 < 2 for CAMB
+ * tables, where C_0 = C_1 = 0): there 1/C^tot is pure detector noise and the reference's value inherits the last-bit
+ * rounding of scipy's spline evaluation (DESIGN.md "parity notes").  Rows on the lmax cuts are always treated exactly.
  * out_terms (may be NULL) receives the per-estimator integrals, [5][n_L] in bit order TT,TE,EE,EB,BB. */
 int lbg_n0_ho02(lbg_ctx* ctx, int n_L, const double* L, unsigned terms_mask,
                 double thetab_arcmin, double deltaT_uK_arcmin, double Tcmb_K, int iterative,
                 int n_l1, const double* l1, const double* w_l1,
                 int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
                 double lmax_T, double lmax_P, double lmin_v, int fold_phi,
+                int n_exact, const int* exact_rows, const double* exact_u,
                 double* out_nkk /*[n_L]*/, double* out_terms /*[5][n_L] or NULL*/,
                 long long* nodes_executed /*or NULL*/);
 

@@ -56,9 +56,37 @@ def upload_cls(ctx, lensCl_interps, nolensCl_interps):
     return n
 
 
+def _exact_u_rows(lensCl_interps, nolensCl_interps, ell, cphi, sphi, below):
+    """u-side spline values at |u|_j for the l1 rows below the first non-zero C_l (l1 < 2: CAMB tables have C_0 = C_1 = 0).
+
+    There C^tot(|u|) is pure detector noise (~1e-20) while the spline crosses zero between knots of size 1e-10, so the
+    reference's 1/C^tot carries the last-bit rounding of scipy's `interp1d` evaluation at relative 1e-6 -- and these rows
+    carry up to 20 % of the TT integral at low L.  For bit-faithful parity the few affected values (2 rows x 201 nodes x 8
+    spectra) are evaluated with the very routine the reference uses (prep_camb.py:88-89) and handed to the kernel
+    (lbg_n0_ho02 `exact_u`); every other node is evaluated on the device."""
+    from scipy.interpolate import interp1d
+    rows = np.nonzero(ell < below)[0].astype(np.int32)
+    if rows.size == 0:
+        return rows, np.zeros(0)
+    ux = ell[rows][:, None] * cphi[None, :]
+    uy = ell[rows][:, None] * sphi[None, :]
+    nu = (ux ** 2. + uy ** 2.) ** 0.5                          # cmb/Nkk.py:79
+    vals = np.empty((rows.size, cphi.size, 8))
+    k = 0
+    for interps in (nolensCl_interps, lensCl_interps):
+        for name in ('TT', 'TE', 'EE', 'BB'):
+            f = interps[name]
+            if not isinstance(f, interp1d):
+                f = interp1d(np.arange(table_of(f).size, dtype=np.float64), table_of(f), kind='cubic',
+                             bounds_error=False, fill_value=0.0)
+            vals[:, :, k] = f(nu)
+            k += 1
+    return np.ascontiguousarray(rows), np.ascontiguousarray(vals)
+
+
 def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'), thetab=1., DeltaT=1.,
              iterative=False, fold_phi=True, device=None, Tcmb=None, grids=None,
-             lmax_T=3000., lmax_P=5000., lmin_v=2., cos_sin=None):
+             lmax_T=3000., lmax_P=5000., lmin_v=2., cos_sin=None, exact_u_below=2.0):
     """(N0[len(Ls)], {term: integral[len(Ls)]}) -- the combined noise plus the per-estimator integrals."""
     for t in terms:
         if t == 'TB':
@@ -79,6 +107,7 @@ def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'
     out = np.empty(Ld.size)
     out_terms = np.empty((5, Ld.size))
     import ctypes as C
+    exact_rows, exact_u = _exact_u_rows(lensCl_interps, nolensCl_interps, ell, cphi, sphi, exact_u_below)
     nodes = C.c_longlong(0)
     if Tcmb is None:
         Tcmb = get_params()['Tcmb']
@@ -86,6 +115,7 @@ def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'
                                       float(Tcmb), int(bool(iterative)), ell.size, _ffi._dp(ell), _ffi._dp(w_ell),
                                       pphi.size, _ffi._dp(cphi), _ffi._dp(sphi), _ffi._dp(w_phi),
                                       float(lmax_T), float(lmax_P), float(lmin_v), int(bool(fold_phi)),
+                                      exact_rows.size, exact_rows.ctypes.data_as(_ffi.c_int_p), _ffi._dp(exact_u),
                                       _ffi._dp(out), _ffi._dp(out_terms), C.byref(nodes)))
     ms, launches = ctx.last_kernel_ms()
     last_stats.update(nodes=nodes.value, kernel_ms=ms, launches=launches, n_L=Ld.size)

@@ -57,7 +57,7 @@ def _declare(L):
         'lbg_eval_spline': [vp, i, c_double_p, i, c_double_p, c_double_p],
         'lbg_cubic_spline_coeffs': [i, c_double_p, c_double_p],
         'lbg_n0_ho02': [vp, i, c_double_p, u, d, d, d, i, i, c_double_p, c_double_p, i, c_double_p, c_double_p,
-                        c_double_p, d, d, d, i, c_double_p, c_double_p, c_ll_p],
+                        c_double_p, d, d, d, i, i, c_int_p, c_double_p, c_double_p, c_double_p, c_ll_p],
     }
     for name, args in sig.items():
         fn = getattr(L, name)

@@ -17,7 +17,7 @@ struct __align__(128) URow {
     double uT, uX, uE, uB;        // unlensed TT, TE, EE, BB at l
     double T1, E1, X1;            // lensed + noise TT, EE ; lensed TE  (prep_camb.py:128-137)
     double rT1h, rE1h, rE1, rB1h; // 0.5/T1, 0.5/E1, 1/E1, 0.5/B1
-    double flags;                 // bit0 T-terms active, bit1 T boundary row, bit2 P active, bit3 P boundary row
+    double flags;                 // bit0 T-terms active, bit2 P-terms active, bit4 row handled by n0_special_kernel
     double pad0, pad1;
 };
 
@@ -27,6 +27,8 @@ struct N0Params {
     double nT, nP, a;             // N_TT(l) = nT exp(a l (l+1)), N_EE = N_BB = nP exp(.)  (cmb/DetectorNoise.py:22-26)
     double lmax_T, lmax_P, lmin_v;
     double ebfac;
+    int fold;                     // phi nodes are mirror pairs: phi[] holds [6][n_phi] cos,sin,w,cos_m,sin_m,frac_j
+    unsigned near_lo[3], near_span[3];   // hi-word windows of |v|^2 around lmin_v^2, lmax_T^2, lmax_P^2
 };
 
 __device__ __forceinline__ void bspline_weights(double t, double& w0, double& w1, double& w2, double& w3) {
@@ -72,8 +74,111 @@ __global__ void n0_uside_kernel(N0Params P, const double* __restrict__ l1, const
     utab[r] = u;
 }
 
+struct UVals { double uT, uX, uE, uB, T1, E1, X1, rT1h, rE1h, rE1, rB1h; };
+
+// One integrand node (cmb/Nkk.py:66-162) for |u| = l at angle (c, s) = (cos phi, sin phi) and lensing multipole L.
+// actT / actP: the |u| side of prep_lmaxmask (cmb/Nkk.py:17,20) for the 3000 / 5000 families; wl = weight * l.
+__device__ __forceinline__ void n0_node(const N0Params& P, const ClRow* __restrict__ rows, double L, double l, double c, double s,
+                                        const UVals& u, bool actT, bool actP, double wl, bool mirror, double cm, double sm_, double fj,
+                                        double& aTT, double& aTE, double& aEE, double& aEB, double& aBB) {
+    // geometry exactly as cmb/Nkk.py:66-72,80 (no FMA contraction: |v| decides the masks)
+    const double ux = __dmul_rn(l, c), uy = __dmul_rn(l, s);
+    const double vx = __dsub_rn(L, ux);
+    const double nv2 = __dadd_rn(__dmul_rn(vx, vx), __dmul_rn(uy, uy));
+    const double nv = __dsqrt_rn(nv2);
+    const bool vok = !(nv < P.lmin_v);
+    bool okT = actT && vok && !(nv > P.lmax_T);
+    bool okP = actP && vok && !(nv > P.lmax_P);
+    double wT = wl, wP = wl;
+    if (mirror) {
+        // Folded phi grid: this node stands for (phi_j, 2pi - phi_j).  The two differ only by the rounding of cos/sin, which
+        // matters when |v| sits on a cut (e.g. the 3000-4000-5000 triangle at phi = pi/2).  Integer test on the high word of
+        // |v|^2 (ALU pipe, not FP64); inside the window both masks are evaluated exactly as the reference does.
+        const unsigned hi = (unsigned)__double2hiint(nv2);
+        if ((hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2]) {
+            const double fm = 1.0 - fj;
+            const double uxm = __dmul_rn(l, cm), uym = __dmul_rn(l, sm_);
+            const double vxm = __dsub_rn(L, uxm);
+            const double nvm = __dsqrt_rn(__dadd_rn(__dmul_rn(vxm, vxm), __dmul_rn(uym, uym)));
+            const bool vokm = !(nvm < P.lmin_v);
+            const bool okTm = actT && vokm && !(nvm > P.lmax_T);
+            const bool okPm = actP && vokm && !(nvm > P.lmax_P);
+            wT = wl * ((okT ? fj : 0.0) + (okTm ? fm : 0.0));
+            wP = wl * ((okP ? fj : 0.0) + (okPm ? fm : 0.0));
+            okT = okT || okTm;
+            okP = okP || okPm;
+        }
+    }
+    if (!(okT || okP)) return;
+
+    const double Lx = ux + vx;                     // cmb/Nkk.py:82
+    const double dLu = ux * Lx, dLv = vx * Lx;     // :84-85
+    // cos 2phi_uv and sin^2 2phi_uv from dot / cross products instead of two atan2 (:74-78,106,130,138)
+    const double dot = ux * vx - uy * uy, crs = uy * Lx;
+    const double d2 = dot * dot, x2 = crs * crs;
+    const double rden = 1.0 / (d2 + x2);
+    const double c2 = (d2 - x2) * rden;
+    const double s2sq = 4.0 * d2 * x2 * rden * rden;
+
+    // eight cubic splines at |v| (prep_camb.py:88-89), zero outside the table
+    int i = (int)nv;
+    if (i > P.n_ell - 2) i = P.n_ell - 2;
+    double w0, w1, w2, w3;
+    bspline_weights(nv - (double)i, w0, w1, w2, w3);
+    if (nv > (double)(P.n_ell - 1)) { w0 = w1 = w2 = w3 = 0.0; }
+    const double4* rp = reinterpret_cast<const double4*>(rows + i);
+    double4 A = ld4(rp), B = ld4(rp + 1);
+    double vT = w0 * A.x, vX = w0 * A.y, vE = w0 * A.z, vB = w0 * A.w;
+    double T2 = w0 * B.x, X2 = w0 * B.y, E2 = w0 * B.z, B2 = w0 * B.w;
+    A = ld4(rp + 2); B = ld4(rp + 3);
+    vT = fma(w1, A.x, vT); vX = fma(w1, A.y, vX); vE = fma(w1, A.z, vE); vB = fma(w1, A.w, vB);
+    T2 = fma(w1, B.x, T2); X2 = fma(w1, B.y, X2); E2 = fma(w1, B.z, E2); B2 = fma(w1, B.w, B2);
+    A = ld4(rp + 4); B = ld4(rp + 5);
+    vT = fma(w2, A.x, vT); vX = fma(w2, A.y, vX); vE = fma(w2, A.z, vE); vB = fma(w2, A.w, vB);
+    T2 = fma(w2, B.x, T2); X2 = fma(w2, B.y, X2); E2 = fma(w2, B.z, E2); B2 = fma(w2, B.w, B2);
+    A = ld4(rp + 6); B = ld4(rp + 7);
+    vT = fma(w3, A.x, vT); vX = fma(w3, A.y, vX); vE = fma(w3, A.z, vE); vB = fma(w3, A.w, vB);
+    T2 = fma(w3, B.x, T2); X2 = fma(w3, B.y, X2); E2 = fma(w3, B.z, E2); B2 = fma(w3, B.w, B2);
+    // detector noise at |v| (cmb/DetectorNoise.py:22-26)
+    const double en = exp(nv * (nv + 1.0) * P.a);
+    T2 = fma(P.nT, en, T2);
+    E2 = fma(P.nP, en, E2);
+    B2 = fma(P.nP, en, B2);
+
+    const unsigned terms = P.terms;
+    if (okT) {
+        if (terms & LBG_TT) {                      // cmb/Nkk.py:93-99
+            const double fa = u.uT * dLu + vT * dLv;
+            aTT = fma(wT, fa * fa * u.rT1h / T2, aTT);
+        }
+        if (terms & LBG_TE) {                      // cmb/Nkk.py:101-125
+            const double fa_uv = u.uX * c2 * dLu + vX * dLv;
+            const double fa_vu = u.uX * dLu + vX * c2 * dLv;
+            const double xx = u.X1 * X2;
+            const double num = u.E1 * T2 * fa_uv - xx * fa_vu;
+            const double den = u.T1 * E2 * u.E1 * T2 - xx * xx;
+            aTE = fma(wT, fa_uv * num / den, aTE);
+        }
+    }
+    if (okP) {
+        if (terms & LBG_EE) {                      // cmb/Nkk.py:127-133
+            const double fa = (u.uE * dLu + vE * dLv) * c2;
+            aEE = fma(wP, fa * fa * u.rE1h / E2, aEE);
+        }
+        if (terms & LBG_EB) {                      // cmb/Nkk.py:135-146
+            const double fa = u.uE * dLu - vB * dLv;
+            aEB = fma(wP, fa * fa * s2sq * u.rE1 / B2, aEB);
+        }
+        if (terms & LBG_BB) {                      // cmb/Nkk.py:148-154
+            const double fa = (u.uB * dLu + vB * dLv) * c2;
+            aBB = fma(wP, fa * fa * u.rB1h / B2, aBB);
+        }
+    }
+}
+
+// Main kernel: regular rows (flag bit4 clear), phi nodes possibly folded onto mirror pairs.
 __global__ void __launch_bounds__(128)
-n0_kernel(N0Params P, const double* __restrict__ Ls, const double* __restrict__ phi /*[5][n_phi]: cos,sin,w,ratioT,ratioP*/,
+n0_kernel(N0Params P, const double* __restrict__ Ls, const double* __restrict__ phi /*[6][n_phi]: cos,sin,w,cos_m,sin_m,frac_j*/,
           const URow* __restrict__ utab, const ClRow* __restrict__ rows, double* __restrict__ partial) {
     const int npairs = P.n_L * P.n_phi;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -83,98 +188,22 @@ n0_kernel(N0Params P, const double* __restrict__ Ls, const double* __restrict__ 
     const double L = Ls[iL], c = phi[j], s = phi[P.n_phi + j];
     const int r0 = blockIdx.y * P.rows_per_chunk;
     const int r1 = min(P.n_l1, r0 + P.rows_per_chunk);
-    const double xmax = (double)(P.n_ell - 1);
-    const unsigned terms = P.terms;
+    const bool fold = P.fold != 0;
+    const double cm = phi[3 * P.n_phi + j], sm_ = phi[4 * P.n_phi + j], fj = phi[5 * P.n_phi + j];
     double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
 
     for (int r = r0; r < r1; ++r) {
         const double4* up = reinterpret_cast<const double4*>(utab + r);
-        const double4 q3 = ld4(up + 3);              // rB1h, flags, pad, pad
+        const double4 q3 = ld4(up + 3);                // rB1h, flags, nT(l), nP(l)
         const int fl = (int)q3.y;
-        if (!(fl & 5)) continue;                       // block-uniform: row masked for every estimator
-        const double4 q0 = ld4(up);                  // l, wl, uT, uX
-        const double l = q0.x;
-        // geometry exactly as cmb/Nkk.py:66-72,80 (no FMA contraction: |v| decides the masks)
-        const double ux = __dmul_rn(l, c), uy = __dmul_rn(l, s);
-        const double vx = __dsub_rn(L, ux);
-        const double nv2 = __dadd_rn(__dmul_rn(vx, vx), __dmul_rn(uy, uy));
-        const double nv = __dsqrt_rn(nv2);
-        const bool vok = !(nv < P.lmin_v);
-        const bool okT = (fl & 1) && vok && !(nv > P.lmax_T);
-        const bool okP = (fl & 4) && vok && !(nv > P.lmax_P);
-        if (!(okT || okP)) continue;
-        double mT = okT ? 1.0 : 0.0, mP = okP ? 1.0 : 0.0;
-        if (fl & 2) mT *= phi[3 * P.n_phi + j];        // boundary row: |u| > lmax_T decided per phi node
-        if (fl & 8) mP *= phi[4 * P.n_phi + j];
-        const double4 q1 = ld4(up + 1);              // uE, uB, T1, E1
-        const double4 q2 = ld4(up + 2);              // X1, rT1h, rE1h, rE1
-        const double wl = q0.y, uT = q0.z, uX = q0.w, uE = q1.x, uB = q1.y, T1 = q1.z, E1 = q1.w;
-        const double X1 = q2.x, rT1h = q2.y, rE1h = q2.z, rE1 = q2.w, rB1h = q3.x;
-
-        const double Lx = ux + vx;                     // cmb/Nkk.py:82
-        const double dLu = ux * Lx, dLv = vx * Lx;     // :84-85
-        // cos 2phi_uv and sin^2 2phi_uv from dot / cross products instead of two atan2 (:74-78,106,130,138)
-        const double dot = ux * vx - uy * uy, crs = uy * Lx;
-        const double d2 = dot * dot, x2 = crs * crs;
-        const double rden = 1.0 / (d2 + x2);
-        const double c2 = (d2 - x2) * rden;
-        const double s2sq = 4.0 * d2 * x2 * rden * rden;
-
-        // eight cubic splines at |v| (prep_camb.py:88-89), zero outside the table
-        int i = (int)nv;
-        if (i > P.n_ell - 2) i = P.n_ell - 2;
-        double w0, w1, w2, w3;
-        bspline_weights(nv - (double)i, w0, w1, w2, w3);
-        if (nv > xmax) { w0 = w1 = w2 = w3 = 0.0; }
-        const double4* rp = reinterpret_cast<const double4*>(rows + i);
-        double4 A = ld4(rp), B = ld4(rp + 1);
-        double vT = w0 * A.x, vX = w0 * A.y, vE = w0 * A.z, vB = w0 * A.w;
-        double T2 = w0 * B.x, X2 = w0 * B.y, E2 = w0 * B.z, B2 = w0 * B.w;
-        A = ld4(rp + 2); B = ld4(rp + 3);
-        vT = fma(w1, A.x, vT); vX = fma(w1, A.y, vX); vE = fma(w1, A.z, vE); vB = fma(w1, A.w, vB);
-        T2 = fma(w1, B.x, T2); X2 = fma(w1, B.y, X2); E2 = fma(w1, B.z, E2); B2 = fma(w1, B.w, B2);
-        A = ld4(rp + 4); B = ld4(rp + 5);
-        vT = fma(w2, A.x, vT); vX = fma(w2, A.y, vX); vE = fma(w2, A.z, vE); vB = fma(w2, A.w, vB);
-        T2 = fma(w2, B.x, T2); X2 = fma(w2, B.y, X2); E2 = fma(w2, B.z, E2); B2 = fma(w2, B.w, B2);
-        A = ld4(rp + 6); B = ld4(rp + 7);
-        vT = fma(w3, A.x, vT); vX = fma(w3, A.y, vX); vE = fma(w3, A.z, vE); vB = fma(w3, A.w, vB);
-        T2 = fma(w3, B.x, T2); X2 = fma(w3, B.y, X2); E2 = fma(w3, B.z, E2); B2 = fma(w3, B.w, B2);
-        // detector noise at |v| (cmb/DetectorNoise.py:22-26)
-        const double en = exp(nv * (nv + 1.0) * P.a);
-        T2 = fma(P.nT, en, T2);
-        E2 = fma(P.nP, en, E2);
-        B2 = fma(P.nP, en, B2);
-
-        if (okT) {
-            const double wT = wl * mT;
-            if (terms & LBG_TT) {                      // cmb/Nkk.py:93-99
-                const double fa = uT * dLu + vT * dLv;
-                aTT = fma(wT, fa * fa * rT1h / T2, aTT);
-            }
-            if (terms & LBG_TE) {                      // cmb/Nkk.py:101-125
-                const double fa_uv = uX * c2 * dLu + vX * dLv;
-                const double fa_vu = uX * dLu + vX * c2 * dLv;
-                const double xx = X1 * X2;
-                const double num = E1 * T2 * fa_uv - xx * fa_vu;
-                const double den = T1 * E2 * E1 * T2 - xx * xx;
-                aTE = fma(wT, fa_uv * num / den, aTE);
-            }
-        }
-        if (okP) {
-            const double wP = wl * mP;
-            if (terms & LBG_EE) {                      // cmb/Nkk.py:127-133
-                const double fa = (uE * dLu + vE * dLv) * c2;
-                aEE = fma(wP, fa * fa * rE1h / E2, aEE);
-            }
-            if (terms & LBG_EB) {                      // cmb/Nkk.py:135-146
-                const double fa = uE * dLu - vB * dLv;
-                aEB = fma(wP, fa * fa * s2sq * rE1 / B2, aEB);
-            }
-            if (terms & LBG_BB) {                      // cmb/Nkk.py:148-154
-                const double fa = (uB * dLu + vB * dLv) * c2;
-                aBB = fma(wP, fa * fa * rB1h / B2, aBB);
-            }
-        }
+        if (!(fl & 5) || (fl & 16)) continue;          // block-uniform: masked row, or handled by n0_special_kernel
+        const double4 q0 = ld4(up);                    // l, wl, uT, uX
+        const double4 q1 = ld4(up + 1);                // uE, uB, T1, E1
+        const double4 q2 = ld4(up + 2);                // X1, rT1h, rE1h, rE1
+        UVals u;
+        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
+        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
+        n0_node(P, rows, L, q0.x, c, s, u, fl & 1, fl & 4, q0.y, fold, cm, sm_, fj, aTT, aTE, aEE, aEB, aBB);
     }
     if (valid) {
         const double wphi = phi[2 * P.n_phi + j];
@@ -188,9 +217,68 @@ n0_kernel(N0Params P, const double* __restrict__ Ls, const double* __restrict__ 
     }
 }
 
+// Special rows, always on the full (unfolded) phi grid:
+//  * rows sitting on the lmax_T / lmax_P cuts, where the reference's mask `|u| > lmax` (cmb/Nkk.py:17,20) depends on the
+//    rounding of |u| = sqrt((l cos)^2 + (l sin)^2) at each phi node;
+//  * rows the caller wants evaluated with its own u-side spline values at |u|_j (rows below the first non-zero C_l,
+//    where the reference's filter 1/C^tot is pure noise and its result inherits the rounding of scipy's spline).
+// su: [n_special][n_phi][8] splines at |u|_j (uTT,uTE,uEE,uBB,lTT,lTE,lEE,lBB); sm: [n_special][n_phi] |u|_j.
+__global__ void __launch_bounds__(128)
+n0_special_kernel(N0Params P, int n_special, int n_phi_full, const int* __restrict__ srow, const double* __restrict__ Ls,
+                  const double* __restrict__ phi /*[3][n_phi_full]*/, const URow* __restrict__ utab,
+                  const double* __restrict__ su, const double* __restrict__ snu, const ClRow* __restrict__ rows,
+                  double* __restrict__ partial /*[5][n_L*n_phi_full]*/) {
+    const int npairs = P.n_L * n_phi_full;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npairs) return;
+    const int iL = p / n_phi_full, j = p - iL * n_phi_full;
+    const double L = Ls[iL], c = phi[j], s = phi[n_phi_full + j];
+    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
+    for (int k = 0; k < n_special; ++k) {
+        const URow& ur = utab[srow[k]];
+        const double* v = su + ((size_t)k * n_phi_full + j) * 8;
+        const double nu = snu[(size_t)k * n_phi_full + j];
+        const double en = exp(nu * (nu + 1.0) * P.a);
+        UVals u;
+        u.uT = v[0]; u.uX = v[1]; u.uE = v[2]; u.uB = v[3];
+        u.T1 = v[4] + P.nT * en; u.X1 = v[5]; u.E1 = v[6] + P.nP * en;
+        const double B1 = v[7] + P.nP * en;
+        u.rT1h = 0.5 / u.T1; u.rE1h = 0.5 / u.E1; u.rE1 = 1.0 / u.E1; u.rB1h = 0.5 / B1;
+        n0_node(P, rows, L, ur.l, c, s, u, !(nu > P.lmax_T), !(nu > P.lmax_P), ur.wl, false, 0.0, 0.0, 1.0, aTT, aTE, aEE, aEB, aBB);
+    }
+    const double wphi = phi[2 * n_phi_full + j];
+    const size_t stride = (size_t)npairs;
+    partial[p] = aTT * wphi;
+    partial[stride + p] = aTE * wphi;
+    partial[2 * stride + p] = aEE * wphi;
+    partial[3 * stride + p] = aEB * wphi;
+    partial[4 * stride + p] = aBB * wphi;
+}
+
+// Library-side u values for special rows without caller-supplied ones: the eight splines at |u|_j.
+__global__ void n0_special_u_kernel(int n_ell, int n, const double* __restrict__ nu, const ClRow* __restrict__ rows,
+                                    double* __restrict__ out /*[n][8]*/) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    double x = nu[t];
+    double v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (x >= 0.0 && x <= (double)(n_ell - 1)) {
+        int i = (int)x;
+        if (i > n_ell - 2) i = n_ell - 2;
+        double w0, w1, w2, w3;
+        bspline_weights(x - (double)i, w0, w1, w2, w3);
+        const double* p = reinterpret_cast<const double*>(rows + i);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = w0 * p[k] + w1 * p[8 + k] + w2 * p[16 + k] + w3 * p[24 + k];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) out[(size_t)t * 8 + k] = v[k];
+}
+
 // One block per L: fixed-order reduction of the partial sums, then cmb/Nkk.py:169-172.
 __global__ void __launch_bounds__(128)
 n0_reduce_kernel(N0Params P, const double* __restrict__ Ls, const double* __restrict__ partial,
+                 const double* __restrict__ spartial, int n_phi_full,
                  double* __restrict__ out /*[6][n_L]: N0, TT, TE, EE, EB, BB integrals*/) {
     __shared__ double sm[5][128];
     const int iL = blockIdx.x, npairs = P.n_L * P.n_phi;
@@ -202,6 +290,13 @@ n0_reduce_kernel(N0Params P, const double* __restrict__ Ls, const double* __rest
         size_t o = (size_t)ch * npairs + (size_t)iL * P.n_phi + j;
 #pragma unroll
         for (int t = 0; t < 5; ++t) acc[t] += partial[t * stride + o];
+    }
+    if (spartial) {
+        const size_t sstride = (size_t)P.n_L * n_phi_full;
+        for (int j = threadIdx.x; j < n_phi_full; j += 128) {
+#pragma unroll
+            for (int t = 0; t < 5; ++t) acc[t] += spartial[t * sstride + (size_t)iL * n_phi_full + j];
+        }
     }
 #pragma unroll
     for (int t = 0; t < 5; ++t) sm[t][threadIdx.x] = acc[t];
@@ -233,66 +328,79 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
                            int n_l1, const double* l1, const double* w_l1,
                            int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
                            double lmax_T, double lmax_P, double lmin_v, int fold_phi,
+                           int n_exact, const int* exact_rows, const double* exact_u,
                            double* out_nkk, double* out_terms, long long* nodes_executed) {
     LBG_REQUIRE(c && L && l1 && w_l1 && cos_phi && sin_phi && w_phi && out_nkk, "lbg_n0_ho02: NULL argument");
-    LBG_REQUIRE(c->n_ell > 0, "lbg_n0_ho02: call lbg_upload_cl_tables first");
-    if (c->n_ell <= 0) return LBG_ESTATE;
+    if (c->n_ell <= 0) { set_error("lbg_n0_ho02: call lbg_upload_cl_tables first"); return LBG_ESTATE; }
     LBG_REQUIRE(n_L >= 0 && n_l1 > 0 && n_phi > 0, "lbg_n0_ho02: bad sizes n_L=%d n_l1=%d n_phi=%d", n_L, n_l1, n_phi);
     LBG_REQUIRE((terms_mask & ~(LBG_TT | LBG_TE | LBG_EE | LBG_EB | LBG_BB)) == 0 && terms_mask != 0,
                 "lbg_n0_ho02: unsupported terms mask 0x%x", terms_mask);
     LBG_REQUIRE(Tcmb_K > 0 && lmax_T <= lmax_P, "lbg_n0_ho02: need Tcmb > 0 and lmax_T <= lmax_P");
+    LBG_REQUIRE(n_exact >= 0 && (n_exact == 0 || (exact_rows && exact_u)), "lbg_n0_ho02: exact rows given without values");
     if (n_L == 0) { if (nodes_executed) *nodes_executed = 0; return LBG_OK; }
     std::lock_guard<std::mutex> g(c->mu);
     LBG_CUDA(cudaSetDevice(c->device));
 
-    // ---- phi nodes (optionally folded onto one node per mirror pair) -------------------------------------
-    std::vector<int> rep, mir;                       // representative node, its mirror (== rep if self-mirrored / unfolded)
+    // ---- phi nodes of the main kernel (optionally folded onto one node per mirror pair) -------------------
+    std::vector<double> ph;   // [6][n_phe]: cos, sin, w (pair sum), mirror cos, mirror sin, w_j / (w_j + w_m)
+    int n_phe = 0;
     if (fold_phi) {
+        n_phe = (n_phi + 1) / 2;
+        ph.assign(6 * (size_t)n_phe, 0.0);
         for (int j = 0, m = n_phi - 1; j <= m; ++j, --m) {
             bool ok = fabs(cos_phi[j] - cos_phi[m]) < 1e-9 && fabs(sin_phi[j] + sin_phi[m]) < 1e-9;
             LBG_REQUIRE(ok, "lbg_n0_ho02: fold_phi requested but nodes %d and %d are not mirror images", j, m);
-            rep.push_back(j); mir.push_back(m);
+            const double w = (m != j) ? w_phi[j] + w_phi[m] : w_phi[j];
+            ph[j] = cos_phi[j]; ph[n_phe + j] = sin_phi[j]; ph[2 * (size_t)n_phe + j] = w;
+            ph[3 * (size_t)n_phe + j] = cos_phi[m]; ph[4 * (size_t)n_phe + j] = sin_phi[m];
+            ph[5 * (size_t)n_phe + j] = (m != j && w != 0.0) ? w_phi[j] / w : 1.0;
         }
     } else {
-        for (int j = 0; j < n_phi; ++j) { rep.push_back(j); mir.push_back(j); }
+        n_phe = n_phi;
+        ph.assign(6 * (size_t)n_phe, 0.0);
+        memcpy(&ph[0], cos_phi, (size_t)n_phi * 8);
+        memcpy(&ph[n_phe], sin_phi, (size_t)n_phi * 8);
+        memcpy(&ph[2 * (size_t)n_phe], w_phi, (size_t)n_phi * 8);
     }
-    const int n_phe = (int)rep.size();
+    std::vector<double> phf(3 * (size_t)n_phi);  // full grid for the special rows
+    memcpy(&phf[0], cos_phi, (size_t)n_phi * 8);
+    memcpy(&phf[n_phi], sin_phi, (size_t)n_phi * 8);
+    memcpy(&phf[2 * (size_t)n_phi], w_phi, (size_t)n_phi * 8);
 
-    // ---- row flags; |u| masks of prep_lmaxmask (cmb/Nkk.py:17,20) on rows that sit on a cut ---------------
+    // ---- row flags; special rows = rows on a cut of prep_lmaxmask + rows the caller supplies exact u values for
     std::vector<int> rowflag(n_l1, 0);
-    int bT = -1, bP = -1;
+    std::vector<int> srow;                       // special rows, caller's first (same order as exact_u)
+    for (int k = 0; k < n_exact; ++k) {
+        LBG_REQUIRE(exact_rows[k] >= 0 && exact_rows[k] < n_l1, "lbg_n0_ho02: exact row %d out of range", exact_rows[k]);
+        srow.push_back(exact_rows[k]);
+    }
     long long active_rows = 0;
     for (int r = 0; r < n_l1; ++r) {
         double l = l1[r];
         LBG_REQUIRE(l > 0.0, "lbg_n0_ho02: l1 nodes must be positive");
         int f = 0;
-        if (l < lmax_T * (1.0 - 1e-12)) f |= 1; else if (l <= lmax_T * (1.0 + 1e-12)) { f |= 3; LBG_REQUIRE(bT < 0, "two l1 nodes on lmax_T"); bT = r; }
-        if (l < lmax_P * (1.0 - 1e-12)) f |= 4; else if (l <= lmax_P * (1.0 + 1e-12)) { f |= 12; LBG_REQUIRE(bP < 0, "two l1 nodes on lmax_P"); bP = r; }
+        bool onT = fabs(l - lmax_T) <= 1e-12 * lmax_T, onP = fabs(l - lmax_P) <= 1e-12 * lmax_P;
+        if (l < lmax_T || onT) f |= 1;
+        if (l < lmax_P || onP) f |= 4;
+        if (onT || onP) {
+            bool have = false;
+            for (int q : srow) have = have || q == r;
+            if (!have) srow.push_back(r);
+        }
         rowflag[r] = f;
         if (f) ++active_rows;
     }
-    std::vector<double> ph(5 * (size_t)n_phe, 1.0);
-    auto umask = [&](int row, int node, double thr) -> double {   // 1 if the reference keeps |u| at this node
-        volatile double ux = l1[row] * cos_phi[node], uy = l1[row] * sin_phi[node];
-        volatile double a2 = ux * ux, b2 = uy * uy;
-        volatile double s2 = a2 + b2;
-        double nu = sqrt(s2);                                     // cmb/Nkk.py:79
-        return nu > thr ? 0.0 : 1.0;
-    };
-    for (int e = 0; e < n_phe; ++e) {
-        int j = rep[e], m = mir[e];
-        double w = (m != j) ? w_phi[j] + w_phi[m] : w_phi[j];
-        ph[e] = cos_phi[j]; ph[n_phe + e] = sin_phi[j]; ph[2 * (size_t)n_phe + e] = w;
-        for (int k = 0; k < 2; ++k) {
-            int row = k ? bP : bT; double thr = k ? lmax_P : lmax_T;
-            double ratio = 1.0;
-            if (row >= 0) {
-                double kept = w_phi[j] * umask(row, j, thr) + (m != j ? w_phi[m] * umask(row, m, thr) : 0.0);
-                ratio = (w != 0.0) ? kept / w : 0.0;
-            }
-            ph[(3 + k) * (size_t)n_phe + e] = ratio;
+    for (int q : srow) rowflag[q] |= 16;
+    const int n_special = (int)srow.size();
+    // |u|_j exactly as cmb/Nkk.py:66-67,79 for every (special row, phi node)
+    std::vector<double> snu((size_t)n_special * n_phi);
+    for (int k = 0; k < n_special; ++k)
+        for (int j = 0; j < n_phi; ++j) {
+            volatile double ux = l1[srow[k]] * cos_phi[j], uy = l1[srow[k]] * sin_phi[j];
+            volatile double a2 = ux * ux, b2 = uy * uy;
+            volatile double s2 = a2 + b2;
+            snu[(size_t)k * n_phi + j] = sqrt(s2);
         }
-    }
 
     // ---- noise constants, cmb/DetectorNoise.py:13-26 ------------------------------------------------------
     const double arcmin2rad = M_PI / (60. * 180.);
@@ -308,8 +416,19 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     P.a = tb * tb / (8. * log(2.));
     P.lmax_T = lmax_T; P.lmax_P = lmax_P; P.lmin_v = lmin_v;
     P.ebfac = iterative ? 2.5 : 1.0;                              // cmb/Nkk.py:141-143
-    const long long npairs = (long long)n_L * n_phe;
-    LBG_REQUIRE(npairs < (1LL << 30), "lbg_n0_ho02: n_L * n_phi too large");
+    P.fold = fold_phi ? 1 : 0;
+    {
+        const double thr[3] = {lmin_v, lmax_T, lmax_P};
+        for (int k = 0; k < 3; ++k) {
+            double lo = thr[k] * thr[k] * (1.0 - 4e-6), hi = thr[k] * thr[k] * (1.0 + 4e-6);
+            unsigned long long blo, bhi;
+            memcpy(&blo, &lo, 8); memcpy(&bhi, &hi, 8);
+            P.near_lo[k] = (unsigned)(blo >> 32);
+            P.near_span[k] = (unsigned)(bhi >> 32) - P.near_lo[k];
+        }
+    }
+    const long long npairs = (long long)n_L * n_phe, npairs_full = (long long)n_L * n_phi;
+    LBG_REQUIRE(npairs_full < (1LL << 30), "lbg_n0_ho02: n_L * n_phi too large");
     const int bx = (int)((npairs + 127) / 128);
     int n_chunk = (c->sm_count * 32 + bx - 1) / bx;
     n_chunk = std::max(1, std::min(n_chunk, std::max(1, n_l1 / 128)));
@@ -317,31 +436,58 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     n_chunk = (n_l1 + P.rows_per_chunk - 1) / P.rows_per_chunk;
     P.n_chunk = n_chunk;
 
+    const size_t su_bytes = (size_t)n_special * n_phi * 8 * 8, snu_bytes = (size_t)n_special * n_phi * 8;
     if (c->n0_L.reserve((size_t)n_L * 8) || c->s0.reserve((size_t)n_l1 * 8) || c->s1.reserve((size_t)n_l1 * 8) ||
-        c->n0_rowflag.reserve((size_t)n_l1 * 4) || c->n0_phi.reserve(ph.size() * 8) ||
+        c->n0_rowflag.reserve((size_t)n_l1 * 4) || c->n0_phi.reserve((ph.size() + phf.size()) * 8) ||
         c->n0_utab.reserve((size_t)n_l1 * sizeof(URow)) ||
-        c->n0_partial.reserve((size_t)5 * n_chunk * npairs * 8) || c->n0_out.reserve((size_t)6 * n_L * 8))
+        c->n0_partial.reserve((size_t)5 * (n_chunk * npairs + npairs_full) * 8) || c->n0_out.reserve((size_t)6 * n_L * 8) ||
+        c->s2.reserve(su_bytes + 64) || c->s3.reserve(snu_bytes + 64) || c->s4.reserve((size_t)n_special * 4 + 64))
         return LBG_ENOMEM;
     cudaStream_t st = c->stream;
+    double* d_ph = c->n0_phi.as<double>();
+    double* d_phf = d_ph + ph.size();
+    double* d_part = c->n0_partial.as<double>();
+    double* d_spart = d_part + (size_t)5 * n_chunk * npairs;
     LBG_CUDA(cudaMemcpyAsync(c->n0_L.p, L, (size_t)n_L * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s0.p, l1, (size_t)n_l1 * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s1.p, w_l1, (size_t)n_l1 * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->n0_rowflag.p, rowflag.data(), (size_t)n_l1 * 4, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(c->n0_phi.p, ph.data(), ph.size() * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d_ph, ph.data(), ph.size() * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d_phf, phf.data(), phf.size() * 8, cudaMemcpyHostToDevice, st));
+    if (n_special) {
+        LBG_CUDA(cudaMemcpyAsync(c->s3.p, snu.data(), snu_bytes, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaMemcpyAsync(c->s4.p, srow.data(), (size_t)n_special * 4, cudaMemcpyHostToDevice, st));
+        if (n_exact)
+            LBG_CUDA(cudaMemcpyAsync(c->s2.p, exact_u, (size_t)n_exact * n_phi * 64, cudaMemcpyHostToDevice, st));
+    }
 
     KernelTimer t(c);
     n0_uside_kernel<<<(n_l1 + 127) / 128, 128, 0, st>>>(P, c->s0.as<double>(), c->s1.as<double>(), c->n0_rowflag.as<int>(),
                                                          c->cl_rows.as<ClRow>(), c->n0_utab.as<URow>());
-    n0_kernel<<<dim3(bx, n_chunk), 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_phi.as<double>(), c->n0_utab.as<URow>(),
-                                                 c->cl_rows.as<ClRow>(), c->n0_partial.as<double>());
-    n0_reduce_kernel<<<n_L, 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_partial.as<double>(), c->n0_out.as<double>());
-    t.launched(3);
+    t.launched();
+    if (n_special > n_exact) {   // library-evaluated splines at |u|_j for the rows the caller gave no values for
+        int cnt = (n_special - n_exact) * n_phi;
+        n0_special_u_kernel<<<(cnt + 127) / 128, 128, 0, st>>>(c->n_ell, cnt, c->s3.as<double>() + (size_t)n_exact * n_phi,
+                                                               c->cl_rows.as<ClRow>(), c->s2.as<double>() + (size_t)n_exact * n_phi * 8);
+        t.launched();
+    }
+    n0_kernel<<<dim3(bx, n_chunk), 128, 0, st>>>(P, c->n0_L.as<double>(), d_ph, c->n0_utab.as<URow>(),
+                                                 c->cl_rows.as<ClRow>(), d_part);
+    t.launched();
+    if (n_special) {
+        n0_special_kernel<<<(int)((npairs_full + 127) / 128), 128, 0, st>>>(P, n_special, n_phi, c->s4.as<int>(), c->n0_L.as<double>(), d_phf,
+                                                                            c->n0_utab.as<URow>(), c->s2.as<double>(), c->s3.as<double>(),
+                                                                            c->cl_rows.as<ClRow>(), d_spart);
+        t.launched();
+    }
+    n0_reduce_kernel<<<n_L, 128, 0, st>>>(P, c->n0_L.as<double>(), d_part, n_special ? d_spart : nullptr, n_phi, c->n0_out.as<double>());
+    t.launched();
     std::vector<double> host((size_t)6 * n_L);
     LBG_CUDA(cudaMemcpyAsync(host.data(), c->n0_out.p, host.size() * 8, cudaMemcpyDeviceToHost, st));
     int rc = t.finish();
     if (rc) return rc;
     memcpy(out_nkk, host.data(), (size_t)n_L * 8);
     if (out_terms) memcpy(out_terms, host.data() + n_L, (size_t)5 * n_L * 8);
-    if (nodes_executed) *nodes_executed = npairs * active_rows;
+    if (nodes_executed) *nodes_executed = npairs * (active_rows - n_special) + npairs_full * n_special;
     return LBG_OK;
 }

@@ -96,7 +96,8 @@ def test_grid_A_properties(ctx, cl_tables):
     # deterministic: bitwise identical on a second run
     a2, _ = Nkk.n0_terms(li, ni, Llls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True, fold_phi=True)
     assert np.array_equal(a, a2)
-    assert Nkk.last_stats['nodes'] == 60 * 101 * 9999
+    # 4 special rows (l1 = 1, 1.5 exact-u rows; 3000, 5000 cut rows) run on all 201 phi nodes, the rest on 101 mirror pairs
+    assert Nkk.last_stats['nodes'] == 60 * (101 * (9999 - 4) + 201 * 4)
 
 
 def test_edge_cases(ctx, cl_tables):
