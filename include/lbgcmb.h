@@ -80,6 +80,25 @@ int lbg_n0_ho02(lbg_ctx* ctx, int n_L, const double* L, unsigned terms_mask,
                 double* out_nkk /*[n_L]*/, double* out_terms /*[5][n_L] or NULL*/,
                 long long* nodes_executed /*or NULL*/);
 
+/* ---- matter power: linear table x growth^2 -> HALOFIT; replaces modi/cosmology.py:158-182 (pkalin/pkanlin) and the
+ *      array work of modi/halofit.py (sigma^2(R) integrals :36-44, Takahashi/Smith formula :139-212) ----------------- */
+/* k [h/Mpc] increasing, P_lin(k, z=0) [(Mpc/h)^3], w_lnk = scipy-1.2.1 simps weights of the ln k grid (halofit.py:42). */
+int lbg_upload_pk_linear(lbg_ctx* ctx, int n_k, const double* k, const double* plin_z0, const double* w_lnk);
+/* sigma_0^2(R) = simps(Delta_0^2(k) exp(-(kR)^2), ln k) at z = 0 (multiply by D(z)^2 for other redshifts). */
+int lbg_halofit_sigma2(lbg_ctx* ctx, int n_R, const double* R, double* out_sigma2);
+/* Build the device-resident P(k, z_r) table, one row per entry of halo_z[n_rows][8] =
+ * {D^2, k_nl, n_eff, curvature, Omega_m(z), Omega_L(z), use_halofit (0 -> linear row, modi/cosmology.py:171), unused}. */
+int lbg_pk_build_table(lbg_ctx* ctx, int n_rows, const double* halo_z, double fnu, double om0, double w, int takahashi,
+                       double* out_pnl /*[n_rows][n_k] or NULL: table stays on the device*/);
+/* np.interp(x, k, P_row) : oob = 0 -> 0 outside the k range (left=right=0, modi/lensing.py:175), 1 -> clamp (:161). */
+int lbg_pk_eval(lbg_ctx* ctx, int row, int n, const double* x, int oob, double* out);
+
+/* ---- Limber: C_l[b][l] = sum_z weight[b][z] * P_{prow[z]}(k = (l + 1/2)/chi[z]); replaces the z loops + quadrature of
+ *      Cgg.py:53-68, Ckg.py:42-59, cmb/lensing.py:27-43 (Simpson in z) and modi/lensing.py:127-179 (trapezoid in chi).
+ *      weight = kernel product x bias x unit factors x quadrature weight, so one kernel serves every flavour. */
+int lbg_limber(lbg_ctx* ctx, int n_batch, int n_ell, const double* ell, int n_z, const double* chi,
+               const double* weight /*[n_batch][n_z]*/, const int* prow /*[n_z]*/, int oob, double* out_cl /*[n_batch][n_ell]*/);
+
 #ifdef __cplusplus
 }
 #endif

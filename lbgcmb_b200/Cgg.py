@@ -1,0 +1,63 @@
+"""Limber C_gg, shot noise and variance; mirrors reference Cgg.py:17-95 (`Cgg`, `var_Cgg`, `Ngg`).
+
+Host (numpy, <= 1000 doubles, as in the reference): the z grid, p(z) normalisation, chi(z), H(z), `sliced_pz`, b(z).
+Device (csrc/limber.cu): P_nl(k, z) on every z node (growth + HALOFIT) and the sum over z for every l."""
+import numpy as np
+
+from lbgcmb_b200.cosmo import cosmo, C_KMS
+from lbgcmb_b200.params import get_params
+from lbgcmb_b200.pmh import engine_of
+from lbgcmb_b200.pz2nbar import pz_slice, nbar_convert
+from lbgcmb_b200.quadrature import simps_weights
+from lbgcmb_b200.sliced_pz import sliced_pz
+from lbgcmb_b200.utils import comoving_distance
+
+params = get_params()
+
+
+def _each(f, zs):
+    """b(z) sampled one node at a time, the way the reference calls it inside its z loop (Cgg.py:58)."""
+    return np.array([float(f(z)) for z in zs])
+
+
+def Cgg(Pk_interps, Llls, zmin, zmax, survey_pz, bz, survey_pz2=None, bz2=None, zeff=True):
+    dz = 0.01
+    zs = np.arange(zmin, zmax + dz, dz)
+    ps = survey_pz(zs)
+    norm = np.sum(ps) * dz
+    ps = ps / norm
+    chis = comoving_distance(zs)
+    if bz2 is None:
+        bz2 = bz
+    if survey_pz2 is None:
+        survey_pz2 = survey_pz
+    engine, nonlinear = engine_of(Pk_interps, 'nlinear')
+    prefactor = (cosmo.H(zs).value / C_KMS) * sliced_pz(zs, zmin, zmax, survey_pz) \
+        * sliced_pz(zs, zmin, zmax, survey_pz2) / chis ** 2.
+    w = simps_weights(zs.size, dz)                                      # Cgg.py:68
+    Ld = np.asarray(Llls, dtype=np.float64)
+    if zeff:
+        zz = dz * np.sum(ps * zs) / (np.sum(ps) * dz)                   # Cgg.py:46
+        amp = float(bz(zz)) * float(bz2(zz)) * np.sum(w * prefactor) / params['h_100']
+        return engine.limber(Ld, [zz], [comoving_distance(zz)], [[amp]], nonlinear=nonlinear)[0]
+    weights = w * prefactor * _each(bz, zs) * _each(bz2, zs) / params['h_100']
+    return engine.limber(Ld, zs, chis, weights[None, :], nonlinear=nonlinear)[0]
+
+
+def Ngg(Llls, zmin, zmax, survey_pz, nbar):
+    """Poisson noise 1 / (angular number density); Cgg.py:85-95."""
+    spz = pz_slice(zmin, zmax, survey_pz)
+    nbar = nbar_convert(nbar, unit='str')
+    return np.ones_like(Llls) / (nbar * spz)
+
+
+def var_Cgg(Llls, zmin, zmax, survey_pz, bz, nbar, fsky, cgg=None, Pk_interps=None, samplevar_lim=False):
+    if cgg is None:
+        cgg = Cgg(Pk_interps, Llls, zmin, zmax, survey_pz, bz, zeff=True)
+    if samplevar_lim:
+        num = cgg
+    else:
+        num = cgg + Ngg(Llls, zmin, zmax, survey_pz, nbar)
+    num = 2. * num ** 2.
+    den = (2. * Llls + 1.) * fsky
+    return num / den

@@ -11,6 +11,8 @@ LIB_PATH = os.path.join(_HERE, 'liblbgcmb.so')
 _lib = None
 _lock = threading.Lock()
 _ctxs = {}
+# device index -> id() of the python object whose linear P(k) table currently sits on that context (None: nobody's)
+table_owner = {}
 
 c_double_p = C.POINTER(C.c_double)
 c_ll_p = C.POINTER(C.c_longlong)
@@ -56,6 +58,11 @@ def _declare(L):
         'lbg_eval_cl': [vp, i, i, i, c_double_p, c_double_p],
         'lbg_eval_spline': [vp, i, c_double_p, i, c_double_p, c_double_p],
         'lbg_cubic_spline_coeffs': [i, c_double_p, c_double_p],
+        'lbg_upload_pk_linear': [vp, i, c_double_p, c_double_p, c_double_p],
+        'lbg_halofit_sigma2': [vp, i, c_double_p, c_double_p],
+        'lbg_pk_build_table': [vp, i, c_double_p, d, d, d, i, c_double_p],
+        'lbg_pk_eval': [vp, i, i, c_double_p, i, c_double_p],
+        'lbg_limber': [vp, i, i, c_double_p, i, c_double_p, c_double_p, c_int_p, i, c_double_p],
         'lbg_n0_ho02': [vp, i, c_double_p, u, d, d, d, i, i, c_double_p, c_double_p, i, c_double_p, c_double_p,
                         c_double_p, d, d, d, i, i, c_int_p, c_double_p, c_double_p, c_double_p, c_ll_p],
     }

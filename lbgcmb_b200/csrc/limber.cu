@@ -1,0 +1,249 @@
+// limber.cu -- matter power spectrum table (linear table x growth -> HALOFIT) and Limber projections.
+//
+// Replaces: modi/halofit.py:36-44 (sigma^2(R) Simpson integrals), :139-212 (Takahashi/Smith formula),
+//           modi/cosmology.py:158-182 (pkalin / pkanlin), and the Limber sums of Cgg.py:53-68, Ckg.py:42-59,
+//           cmb/lensing.py:27-43, modi/lensing.py:127-179 (all "sum_z weight_z * P(k=(l+1/2)/chi_z, z)").
+// The quintic-spline glue of modi/halofit.py:70-98 (k_nl, n_eff, curvature from 500 ln sigma samples) stays on the
+// host with the same scipy routine the reference calls (SURVEY.md "hard parts"); everything per (z,k) or (l,z) is here.
+#include "common.cuh"
+#include <cmath>
+
+namespace lbg {
+
+// sigma0^2(R) = sum_i w_i Delta0^2(k_i) exp(-(k_i R)^2): one block per R.  w = scipy-1.2.1 simps weights in ln k.
+__global__ void __launch_bounds__(256)
+sigma2_kernel(int n_k, const double* __restrict__ k, const double* __restrict__ d2w /*Delta0^2 * w*/,
+              const double* __restrict__ R, double* __restrict__ out) {
+    __shared__ double sm[256];
+    const double r = R[blockIdx.x];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n_k; i += 256) {
+        const double kr = k[i] * r;
+        acc += d2w[i] * exp(-(kr * kr));
+    }
+    sm[threadIdx.x] = acc;
+    __syncthreads();
+    for (int h = 128; h > 0; h >>= 1) {
+        if (threadIdx.x < h) sm[threadIdx.x] += sm[threadIdx.x + h];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[blockIdx.x] = sm[0];
+}
+
+struct HaloZ {           // per-redshift HALOFIT inputs (modi/halofit.py:139-199)
+    double D2;           // growth^2 applied to the z=0 table (modi/cosmology.py:160,175)
+    double rknl, neff, ncur, omz, ovz;
+    double use_halofit;  // 0 -> linear row (z > 4, modi/cosmology.py:171-172)
+    double pad;
+};
+
+struct HaloConst { double fnu, om0, w; int takahashi; };
+
+// One thread per (z, k) table node: P_nl(k, z) [(Mpc/h)^3] from Delta_lin^2 = P0 k^3 D^2 / (2 pi^2).
+__global__ void pnl_kernel(int n_z, int n_k, const double* __restrict__ k, const double* __restrict__ p0,
+                           const HaloZ* __restrict__ hz, HaloConst hc, double* __restrict__ out) {
+    const int ik = blockIdx.x * blockDim.x + threadIdx.x;
+    const int iz = blockIdx.y;
+    if (ik >= n_k) return;
+    const HaloZ h = hz[iz];
+    const double kk = k[ik];
+    const double twopi2 = 2.0 * 3.14159265358979323846 * 3.14159265358979323846;
+    const double plin_dim = p0[ik] * (kk * kk * kk) / twopi2 * h.D2;     // modi/cosmology.py:174-175
+    double res = plin_dim;
+    if (h.use_halofit != 0.0 && kk > 0.005) {                             // modi/halofit.py:139
+        const double neff = h.neff, rncur = h.ncur, w = hc.w, fnu = hc.fnu;
+        const double n2 = neff * neff, n3 = n2 * neff, n4 = n2 * n2;
+        double a, b, c, gam, alpha, beta, xmu, xnu;
+        if (hc.takahashi) {                                               // modi/halofit.py:152-166
+            a = pow(10.0, 1.5222 + 2.8553 * neff + 2.3706 * n2 + 0.9903 * n3 + 0.2250 * n4 - 0.6038 * rncur + 0.1749 * h.ovz * (1 + w));
+            b = pow(10.0, -0.5642 + 0.5864 * neff + 0.5716 * n2 - 1.5474 * rncur + 0.2279 * h.ovz * (1 + w));
+            c = pow(10.0, 0.3698 + 2.0404 * neff + 0.8161 * n2 + 0.5869 * rncur);
+            gam = 0.1971 - 0.0843 * neff + 0.8460 * rncur;
+            alpha = fabs(6.0835 + 1.3373 * neff - 0.1959 * n2 - 5.5274 * rncur);
+            beta = 2.0379 - 0.7354 * neff + 0.3157 * n2 + 1.2490 * n3 + 0.3980 * n4 - 0.1682 * rncur + fnu * (1.081 + 0.395 * n2);
+            xmu = 0.0;
+            xnu = pow(10.0, 5.2105 + 3.6902 * neff);
+        } else {                                                          // modi/halofit.py:168-180 (Smith+03)
+            a = pow(10.0, 1.4861 + 1.8369 * neff + 1.6762 * n2 + 0.7940 * n3 + 0.1670 * n4 - 0.6206 * rncur);
+            b = pow(10.0, 0.9463 + 0.9466 * neff + 0.3084 * n2 - 0.94 * rncur);
+            c = pow(10.0, -0.2807 + 0.6669 * neff + 0.3214 * n2 - 0.0793 * rncur);
+            gam = 0.8649 + 0.2989 * neff + 0.1631 * rncur;
+            alpha = fabs(1.3884 + 0.3700 * neff - 0.1452 * n2);
+            beta = 0.8291 + 0.9854 * neff + 0.3401 * n2;
+            xmu = pow(10.0, -3.5442 + 0.1908 * neff);
+            xnu = pow(10.0, 0.9589 + 1.2857 * neff);
+        }
+        double f1 = 1.0, f2 = 1.0, f3 = 1.0;
+        if (fabs(1 - h.omz) > 0.01) {                                     // modi/halofit.py:183-199
+            const double f1a = pow(h.omz, -0.0732), f2a = pow(h.omz, -0.1423), f3a = pow(h.omz, 0.0725);
+            const double f1b = pow(h.omz, -0.0307), f2b = pow(h.omz, -0.0585), f3b = pow(h.omz, 0.0743);
+            const double frac = h.ovz / (1 - h.omz);
+            if (hc.takahashi) { f1 = f1b; f2 = f2b; f3 = f3b; }
+            else { f1 = frac * f1b + (1 - frac) * f1a; f2 = frac * f2b + (1 - frac) * f2a; f3 = frac * f3b + (1 - frac) * f3a; }
+        }
+        const double y = kk / h.rknl;                                     // modi/halofit.py:201-212
+        double ph = a * pow(y, f1 * 3) / (1 + b * pow(y, f2) + pow(f3 * c * y, 3 - gam));
+        ph = ph / (1 + xmu / y + xnu / (y * y)) * (1 + fnu * (0.977 - 18.015 * (hc.om0 - 0.3)));
+        const double plinaa = plin_dim * (1 + fnu * 47.48 * kk * kk / (1 + 1.5 * kk * kk));
+        const double pq = plin_dim * pow(1 + plinaa, beta) / (1 + plinaa * alpha) * exp(-y / 4.0 - y * y / 8.0);
+        res = pq + ph;
+    }
+    out[(size_t)iz * n_k + ik] = res * twopi2 / (kk * kk * kk);           // modi/cosmology.py:179
+}
+
+// np.interp(x, k, P) with numpy's operation order; oob: 0 -> 0 outside [k0, k_{n-1}] (left=right=0), 1 -> clamp.
+__device__ __forceinline__ double interp_k(const double* __restrict__ ks, const double* __restrict__ P, int n_k, double x, int oob) {
+    if (x < ks[0]) return oob ? P[0] : 0.0;
+    if (x > ks[n_k - 1]) return oob ? P[n_k - 1] : 0.0;
+    if (x == ks[n_k - 1]) return P[n_k - 1];
+    int lo = 0, hi = n_k - 1;                    // ks[lo] <= x < ks[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (ks[mid] <= x) lo = mid; else hi = mid;
+    }
+    const double slope = __ddiv_rn(__dsub_rn(P[lo + 1], P[lo]), __dsub_rn(ks[lo + 1], ks[lo]));
+    return __dadd_rn(__dmul_rn(slope, __dsub_rn(x, ks[lo])), P[lo]);
+}
+
+#define LIMBER_BT 8
+// C_l[b][l] = sum_z weight[b][z] * P_z(k = (l + 1/2) / chi_z).  Block = 128 consecutive l for one batch entry; the k grid
+// sits in shared memory (binary search), the P(k,z) table rows stream from L2/HBM.
+__global__ void __launch_bounds__(128)
+limber_kernel(int n_batch, int n_ell, int n_z, int n_k, const double* __restrict__ ell, const double* __restrict__ chi,
+              const double* __restrict__ weight /*[n_batch][n_z]*/, const int* __restrict__ prow /*[n_z] table row per z node*/,
+              const double* __restrict__ ks, const double* __restrict__ ptab, int oob, double* __restrict__ out) {
+    extern __shared__ double sk[];
+    for (int i = threadIdx.x; i < n_k; i += blockDim.x) sk[i] = ks[i];
+    __syncthreads();
+    const int il = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b0 = blockIdx.y * LIMBER_BT;                  // tile of up to LIMBER_BT batch entries shares each P lookup
+    const int nb = min(LIMBER_BT, n_batch - b0);
+    if (il >= n_ell) return;
+    const double lp = ell[il] + 0.5;
+    double acc[LIMBER_BT];
+#pragma unroll
+    for (int q = 0; q < LIMBER_BT; ++q) acc[q] = 0.0;
+    for (int iz = 0; iz < n_z; ++iz) {
+        bool any = false;
+        for (int q = 0; q < nb; ++q) any = any || (weight[(size_t)(b0 + q) * n_z + iz] != 0.0);
+        if (!any) continue;                                  // block-uniform
+        const double x = __ddiv_rn(lp, chi[iz]);            // Cgg.py:57, Ckg.py:51, cmb/lensing.py:34, modi/cosmology.py:156
+        const double pv = interp_k(sk, ptab + (size_t)prow[iz] * n_k, n_k, x, oob);
+#pragma unroll
+        for (int q = 0; q < LIMBER_BT; ++q)
+            if (q < nb) acc[q] += weight[(size_t)(b0 + q) * n_z + iz] * pv;
+    }
+#pragma unroll
+    for (int q = 0; q < LIMBER_BT; ++q)
+        if (q < nb) out[(size_t)(b0 + q) * n_ell + il] = acc[q];
+}
+
+__global__ void pk_eval_kernel(int n, int n_k, const double* __restrict__ ks, const double* __restrict__ prow_ptr,
+                               const double* __restrict__ x, int oob, double* __restrict__ out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) out[t] = interp_k(ks, prow_ptr, n_k, x[t], oob);
+}
+}  // namespace lbg
+
+using namespace lbg;
+
+extern "C" int lbg_upload_pk_linear(lbg_ctx* c, int n_k, const double* k, const double* plin_z0, const double* w_lnk) {
+    LBG_REQUIRE(c && k && plin_z0 && w_lnk, "lbg_upload_pk_linear: NULL argument");
+    LBG_REQUIRE(n_k >= 4 && n_k <= 6000, "lbg_upload_pk_linear: n_k=%d outside [4, 6000] (k grid is staged in shared memory)", n_k);
+    for (int i = 1; i < n_k; ++i) LBG_REQUIRE(k[i] > k[i - 1] && k[0] > 0, "lbg_upload_pk_linear: k must be positive and increasing");
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    std::vector<double> buf(3 * (size_t)n_k);
+    const double twopi2 = 2.0 * M_PI * M_PI;
+    for (int i = 0; i < n_k; ++i) {
+        buf[i] = k[i];
+        buf[n_k + i] = plin_z0[i];
+        buf[2 * (size_t)n_k + i] = plin_z0[i] * (k[i] * k[i] * k[i]) / twopi2 * w_lnk[i];   // Delta0^2 * simps weight
+    }
+    if (c->pk_lnk.reserve(buf.size() * 8)) return LBG_ENOMEM;
+    LBG_CUDA(cudaMemcpyAsync(c->pk_lnk.p, buf.data(), buf.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    LBG_CUDA(cudaStreamSynchronize(c->stream));
+    c->n_k = n_k;
+    c->pnl_nz = 0;
+    return LBG_OK;
+}
+
+extern "C" int lbg_halofit_sigma2(lbg_ctx* c, int n_R, const double* R, double* out_sigma2) {
+    LBG_REQUIRE(c && R && out_sigma2 && n_R > 0, "lbg_halofit_sigma2: bad argument");
+    if (c->n_k <= 0) { set_error("lbg_halofit_sigma2: call lbg_upload_pk_linear first"); return LBG_ESTATE; }
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    if (c->s0.reserve((size_t)n_R * 8) || c->s1.reserve((size_t)n_R * 8)) return LBG_ENOMEM;
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, R, (size_t)n_R * 8, cudaMemcpyHostToDevice, c->stream));
+    const double* kd = c->pk_lnk.as<double>();
+    KernelTimer t(c);
+    sigma2_kernel<<<n_R, 256, 0, c->stream>>>(c->n_k, kd, kd + 2 * (size_t)c->n_k, c->s0.as<double>(), c->s1.as<double>());
+    t.launched();
+    LBG_CUDA(cudaMemcpyAsync(out_sigma2, c->s1.p, (size_t)n_R * 8, cudaMemcpyDeviceToHost, c->stream));
+    return t.finish();
+}
+
+extern "C" int lbg_pk_build_table(lbg_ctx* c, int n_rows, const double* halo_z /*[n_rows][8]*/, double fnu, double om0,
+                                  double w, int takahashi, double* out_pnl /*[n_rows][n_k] or NULL*/) {
+    LBG_REQUIRE(c && halo_z && n_rows > 0, "lbg_pk_build_table: bad argument");
+    if (c->n_k <= 0) { set_error("lbg_pk_build_table: call lbg_upload_pk_linear first"); return LBG_ESTATE; }
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    const int n_k = c->n_k;
+    if (c->s5.reserve((size_t)n_rows * sizeof(HaloZ)) || c->pk_pnl.reserve((size_t)n_rows * n_k * 8)) return LBG_ENOMEM;
+    LBG_CUDA(cudaMemcpyAsync(c->s5.p, halo_z, (size_t)n_rows * sizeof(HaloZ), cudaMemcpyHostToDevice, c->stream));
+    HaloConst hc{fnu, om0, w, takahashi};
+    const double* kd = c->pk_lnk.as<double>();
+    KernelTimer t(c);
+    pnl_kernel<<<dim3((n_k + 127) / 128, n_rows), 128, 0, c->stream>>>(n_rows, n_k, kd, kd + n_k, c->s5.as<HaloZ>(), hc, c->pk_pnl.as<double>());
+    t.launched();
+    if (out_pnl) LBG_CUDA(cudaMemcpyAsync(out_pnl, c->pk_pnl.p, (size_t)n_rows * n_k * 8, cudaMemcpyDeviceToHost, c->stream));
+    int rc = t.finish();
+    if (rc == LBG_OK) c->pnl_nz = n_rows;
+    return rc;
+}
+
+extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell, int n_z, const double* chi,
+                          const double* weight /*[n_batch][n_z]*/, const int* prow /*[n_z]*/, int oob,
+                          double* out_cl /*[n_batch][n_ell]*/) {
+    LBG_REQUIRE(c && ell && chi && weight && prow && out_cl, "lbg_limber: NULL argument");
+    LBG_REQUIRE(n_batch > 0 && n_ell >= 0 && n_z > 0, "lbg_limber: bad sizes");
+    if (c->pnl_nz <= 0) { set_error("lbg_limber: call lbg_pk_build_table first"); return LBG_ESTATE; }
+    for (int i = 0; i < n_z; ++i) LBG_REQUIRE(prow[i] >= 0 && prow[i] < c->pnl_nz, "lbg_limber: prow[%d]=%d outside the %d-row table", i, prow[i], c->pnl_nz);
+    if (n_ell == 0) return LBG_OK;
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    const size_t bw = (size_t)n_batch * n_z * 8, bo = (size_t)n_batch * n_ell * 8;
+    if (c->s0.reserve((size_t)n_ell * 8) || c->s1.reserve((size_t)n_z * 8) || c->s2.reserve(bw) || c->s3.reserve((size_t)n_z * 4) || c->s4.reserve(bo)) return LBG_ENOMEM;
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, ell, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s1.p, chi, (size_t)n_z * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s2.p, weight, bw, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s3.p, prow, (size_t)n_z * 4, cudaMemcpyHostToDevice, st));
+    const size_t smem = (size_t)c->n_k * 8;
+    if (smem > 48 * 1024) LBG_CUDA(cudaFuncSetAttribute(limber_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KernelTimer t(c);
+    limber_kernel<<<dim3((n_ell + 127) / 128, (n_batch + LIMBER_BT - 1) / LIMBER_BT), 128, smem, st>>>(n_batch, n_ell, n_z, c->n_k, c->s0.as<double>(), c->s1.as<double>(),
+                                                                        c->s2.as<double>(), c->s3.as<int>(), c->pk_lnk.as<double>(),
+                                                                        c->pk_pnl.as<double>(), oob, c->s4.as<double>());
+    t.launched();
+    LBG_CUDA(cudaMemcpyAsync(out_cl, c->s4.p, bo, cudaMemcpyDeviceToHost, st));
+    return t.finish();
+}
+
+extern "C" int lbg_pk_eval(lbg_ctx* c, int row, int n, const double* x, int oob, double* out) {
+    LBG_REQUIRE(c && x && out, "lbg_pk_eval: NULL argument");
+    if (c->pnl_nz <= 0) { set_error("lbg_pk_eval: call lbg_pk_build_table first"); return LBG_ESTATE; }
+    LBG_REQUIRE(row >= 0 && row < c->pnl_nz, "lbg_pk_eval: row %d outside the %d-row table", row, c->pnl_nz);
+    if (n <= 0) return LBG_OK;
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    if (c->s0.reserve((size_t)n * 8) || c->s1.reserve((size_t)n * 8)) return LBG_ENOMEM;
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, x, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+    KernelTimer t(c);
+    pk_eval_kernel<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->n_k, c->pk_lnk.as<double>(), c->pk_pnl.as<double>() + (size_t)row * c->n_k,
+                                                          c->s0.as<double>(), oob, c->s1.as<double>());
+    t.launched();
+    LBG_CUDA(cudaMemcpyAsync(out, c->s1.p, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+    return t.finish();
+}

@@ -1,0 +1,191 @@
+"""Background + P(k,z); mirrors reference modi/cosmology.py:17-194 (`Cosmology`).
+
+Host side (as in the reference): E(a), chi(a) by `quad` (:134-150), un-normalised D+ on 1000 ln a nodes + cubic spline
+(:92-117; the reference integrates with scipy's since-removed `romberg`, tol 1.48e-8 -- `quad` is used here, so D+ agrees
+with the reference to its own Romberg tolerance, not to 1e-10; D+ is an *input* to both the CUDA path and the oracle).
+Device side (csrc/limber.cu): pkalin / pkanlin rows for any number of redshifts at once (`pk_rows`), HALOFIT included.
+"""
+import numpy as np
+from scipy.integrate import quad
+from scipy.interpolate import InterpolatedUnivariateSpline as interpolate
+
+from lbgcmb_b200 import _ffi
+from lbgcmb_b200.cosmo import FlatLambdaCDM
+from lbgcmb_b200.modi import halofit as _hf
+from lbgcmb_b200.quadrature import simps_weights_x
+
+_owner = _ffi.table_owner
+
+
+class Cosmology(object):
+    def __init__(self, M=0.292, L=None, H0=100., B=None, sig8=0.819, klin=None, plin=None, pfile=None, device=None):
+        self.M = M
+        if L is None:
+            L = 1 - M
+        self.L = L
+        self.B = B
+        self.H0 = H0
+        self.sig8 = sig8
+        self.cin = 1000. / (299792458.)
+        self.cosmo = FlatLambdaCDM(H0=H0, Om0=M, Ob0=B, name="cosmo")
+        self.pfile = pfile
+        if pfile is not None:
+            self.klin, self.plin = np.loadtxt(pfile, unpack=True)
+        else:
+            self.klin, self.plin = klin, plin
+        self.Dplus = self._eval_Dplus()
+        self.device = device
+        self._sig0 = None
+        self._spec_cache = {}
+        self._rows_key = None
+
+    # ---- background (host) ------------------------------------------------------------------------------------
+    def _za(self, z, a):
+        if a is None:
+            if z is None:
+                print("At least one of scale factor or redshift is needed.")
+                return None
+            return z, self.ztoa(z)
+        return self.atoz(a), a
+
+    def atoz(self, a):
+        return 1. / a - 1.
+
+    def ztoa(self, z):
+        return 1. / (1. + z)
+
+    def OmegaMa(self, z=None, a=None):
+        z, a = self._za(z, a)
+        return self.M / a ** 3. / (self.M / a ** 3. + self.L)
+
+    def Ea(self, z=None, a=None):
+        z, a = self._za(z, a)
+        M, L = self.M, self.L
+        return a ** -1.5 * (M + (1. - M - L) * a + L * a ** 3.) ** 0.5
+
+    def Ha(self, z=None, a=None):
+        z, a = self._za(z, a)
+        return self.H0 * self.Ea(a=a)
+
+    def _eval_Dplus(self):
+        logx = np.linspace(-20., 0, 1000)
+        x = np.exp(logx)
+
+        def kernel(loga):
+            a = np.exp(loga)
+            return (a * self.Ea(a=a)) ** -3. * a
+        # cumulative integral node to node (each piece is smooth; quad reaches ~1e-14)
+        pieces = np.array([quad(kernel, logx[i], logx[i + 1], epsabs=0, epsrel=1e-13)[0] for i in range(logx.size - 1)])
+        cum = np.concatenate([[0.0], np.cumsum(pieces)])
+        y = self.Ea(a=x) * cum
+        return interpolate(x, y)
+
+    def Dgrow(self, z=None, a=None):
+        z, a = self._za(z, a)
+        return self.Dplus(a) / self.Dplus(1.)
+
+    def chia(self, z=None, a=None):
+        """comoving distance to scale factor a in Mpc/h (modi/cosmology.py:134-150)"""
+        fac = 100. * self.cin
+        f = lambda x: (self.Ea(a=x) * x ** 2) ** -1.
+        z, a = self._za(z, a)
+        if type(a) == np.ndarray:
+            y = np.zeros_like(a)
+            for foo in range(len(a)):
+                y[foo] = quad(f, a[foo], 1)[0]
+            return y / fac
+        return quad(f, a, 1)[0] / fac
+
+    def k_chil(self, l, z=None, a=None):
+        z, a = self._za(z, a)
+        return (l + 0.5) / self.chia(a=a)
+
+    # ---- P(k, z) (device) ---------------------------------------------------------------------------------------
+    def _ctx(self):
+        ctx = _ffi.context(self.device)
+        if _owner.get(ctx.device) != id(self):
+            k, p = _ffi.f64(self.klin), _ffi.f64(self.plin)
+            w = _ffi.f64(simps_weights_x(np.log(k)))
+            _ffi.check(_ffi.lib().lbg_upload_pk_linear(ctx.handle, k.size, _ffi._dp(k), _ffi._dp(p), _ffi._dp(w)))
+            _owner[ctx.device] = id(self)
+            self._rows_key = None
+        return ctx
+
+    def _sigma2_z0(self, R):
+        ctx = self._ctx()
+        R = _ffi.f64(np.atleast_1d(R))
+        out = np.empty(R.size)
+        _ffi.check(_ffi.lib().lbg_halofit_sigma2(ctx.handle, R.size, _ffi._dp(R), _ffi._dp(out)))
+        return out
+
+    def halofit_spec(self, z, sig8=None):
+        """(k_nl, n_eff, curvature) at redshift z: modi/halofit.py:7-100 applied to Delta^2_lin(k) D(z)^2."""
+        sig8 = self.sig8 if sig8 is None else sig8
+        key = (float(z), float(sig8))
+        if key not in self._spec_cache:
+            D2 = float(self.Dgrow(z=z)) ** 2.
+            if sig8 < 1.0 and sig8 > 0.6 and self._sig0 is None:
+                lnr = np.linspace(np.log(0.1), np.log(10.0), 500)
+                self._sig0 = (lnr, self._sigma2_z0(np.exp(lnr)))
+            if sig8 < 1.0 and sig8 > 0.6:
+                lnr, s0 = self._sig0
+                spec = _hf.spec_from_lnsig(lnr, np.log(D2 * s0), lambda R: D2 * self._sigma2_z0(R))
+            else:
+                spec = _hf._get_spec_from(lambda R: D2 * self._sigma2_z0(R), sig8)
+            self._spec_cache[key] = spec
+        return self._spec_cache[key]
+
+    def build_rows(self, zs, nonlinear=True, sig8=None, zmax_halofit=4.0, want_host=False):
+        """Device-resident table with row r = P(k, zs[r]): pkanlin (HALOFIT for z <= 4, else linear) or pkalin."""
+        zs = np.atleast_1d(np.asarray(zs, dtype=np.float64))
+        key = (zs.tobytes(), bool(nonlinear), sig8, zmax_halofit)
+        ctx = self._ctx()
+        if self._rows_key == key and not want_host:
+            return None
+        rows = np.zeros((zs.size, 8))
+        for r, z in enumerate(zs):
+            rows[r, 0] = float(self.Dgrow(z=z)) ** 2.
+            rows[r, 1] = 1.0
+            if nonlinear and not (z > zmax_halofit):               # modi/cosmology.py:171
+                rows[r, 1:4] = self.halofit_spec(z, sig8)
+                rows[r, 4] = float(self.cosmo.Om(self.atoz(self.ztoa(z))))
+                rows[r, 5] = float(self.cosmo.Ode(self.atoz(self.ztoa(z))))
+                rows[r, 6] = 1.0
+        out = np.empty((zs.size, len(self.klin))) if want_host else None
+        fnu = self.cosmo.Onu0 / self.cosmo.Om0
+        _ffi.check(_ffi.lib().lbg_pk_build_table(ctx.handle, zs.size, _ffi._dp(_ffi.f64(rows)), float(fnu), float(self.cosmo.Om0),
+                                                 -1.0, 1, _ffi._dp(out) if want_host else None))
+        self._rows_key = key
+        return out
+
+    def pkalin(self, z=None, a=None):
+        z, a = self._za(z, a)
+        return self.klin, self.build_rows([z], nonlinear=False, want_host=True)[0]
+
+    def pkanlin(self, z=None, a=None, sig8=None):
+        z, a = self._za(z, a)
+        return self.klin, self.build_rows([z], nonlinear=True, sig8=sig8, want_host=True)[0]
+
+    def limber(self, ells, zs, chis, weights, nonlinear=True, oob=0, sig8=None):
+        """C_l[b] = sum_z weights[b, z] P(k=(l+1/2)/chi_z, z) on the device (csrc/limber.cu limber_kernel)."""
+        zs = np.atleast_1d(np.asarray(zs, dtype=np.float64))
+        self.build_rows(zs, nonlinear=nonlinear, sig8=sig8)
+        ctx = self._ctx()
+        ells, chis = _ffi.f64(np.atleast_1d(ells)), _ffi.f64(np.atleast_1d(chis))
+        w = _ffi.f64(np.atleast_2d(weights))
+        prow = np.arange(zs.size, dtype=np.int32)
+        if chis.size != zs.size or w.shape[1] != zs.size:
+            raise ValueError('zs, chis and weights disagree in length')
+        out = np.empty((w.shape[0], ells.size))
+        _ffi.check(_ffi.lib().lbg_limber(ctx.handle, w.shape[0], ells.size, _ffi._dp(ells), zs.size, _ffi._dp(chis), _ffi._dp(w),
+                                         prow.ctypes.data_as(_ffi.c_int_p), int(oob), _ffi._dp(out)))
+        return out
+
+    def pk_eval(self, z, k, nonlinear=True, oob=0):
+        """np.interp(k, klin, P(z)) on the device: the `Pk_interps[...] (z, k)` callable of pmh.py:18-37."""
+        self.build_rows([z], nonlinear=nonlinear)
+        ctx = self._ctx()
+        ka = _ffi.f64(np.atleast_1d(k))
+        out = np.empty(ka.size)
+        _ffi.check(_ffi.lib().lbg_pk_eval(ctx.handle, 0, ka.size, _ffi._dp(ka.ravel()), int(oob), _ffi._dp(out)))
+        return out.reshape(ka.shape)

@@ -1,0 +1,116 @@
+"""GPU parity: HALOFIT table + Limber kernels (csrc/limber.cu) through the mirrors of modi/halofit.py, Cgg.py, Ckg.py,
+cmb/lensing.py vs the reference's golden vectors (tests/golden/halofit.npz, limber_root.npz) and the numpy oracle.
+Tolerance: relative 1e-10 (FP64)."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-10
+
+
+def _g(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def test_halofit_golden(ctx, golden_dir):
+    from lbgcmb_b200.cosmo import FlatLambdaCDM
+    from lbgcmb_b200.modi import halofit as hf
+    g = _g(golden_dir, 'halofit.npz')
+    cosmo = FlatLambdaCDM(H0=100., Om0=float(g['om_m']), Ob0=float(g['om_b']))
+    k, p = g['k'], g['plin']
+    for i, (z, d) in enumerate(zip(g['zs'], g['D'])):
+        delta = p * k ** 3 / (2. * np.pi ** 2) * d ** 2.
+        spec = hf._get_spec(k, delta, float(g['sig8']))
+        assert np.allclose(spec, g['spec'][i], rtol=1e-10), (z, spec, g['spec'][i])
+        got = hf.halofit(k, delta, float(g['sig8']), z, cosmo, takahashi=True)
+        assert np.max(np.abs(got / g['delta_nl'][i] - 1)) < RTOL, z
+        got = hf.halofit(k, delta, float(g['sig8']), z, cosmo, takahashi=False)
+        assert np.max(np.abs(got / g['delta_nl_smith'][i] - 1)) < RTOL, z
+
+
+def test_sigma2_power_law_closed_form(ctx):
+    """sigma^2(R) for Delta^2 = k^n on a wide grid: 0.5 Gamma(n/2) R^-n (SURVEY.md 8(c) closed forms)."""
+    from math import gamma
+    from lbgcmb_b200.modi.halofit import _DeviceTable
+    k = np.exp(np.linspace(np.log(1e-6), np.log(1e4), 4001))
+    for n in (2.0, 3.5):      # n >= 2 keeps the k < 1e-6 truncation below 1e-12
+        tab = _DeviceTable(k, k ** n)
+        R = np.array([0.1, 1.0, 7.0])
+        assert np.allclose(tab.sigma2(R), 0.5 * gamma(n / 2) * R ** -n, rtol=1e-9)
+
+
+def _setup(g):
+    from lbgcmb_b200 import pmh
+    from lbgcmb_b200.Gaussian_pz import Gaussian_pz
+    T = pmh.PkTable(g['k'], g['plin'])
+    Pk = pmh.get_PkInterps(T)
+    assert np.allclose([float(T.engine.Dgrow(z=z)) for z in g['zchk']], g['Dchk'], rtol=1e-13)
+    pz_u = lambda z: Gaussian_pz(z, 2.96, 0.24)
+    pz_g = lambda z: Gaussian_pz(z, 3.8, 0.3)
+    return Pk, pz_u, pz_g, (lambda z: 1. + z)
+
+
+def test_limber_root_golden(ctx, golden_dir):
+    from lbgcmb_b200 import Cgg, Ckg, lensing
+    g = _g(golden_dir, 'limber_root.npz')
+    Pk, pz_u, pz_g, bz = _setup(g)
+    L, zmin, zmax = g['Llls'], float(g['zmin']), float(g['zmax'])
+    got = {
+        'cgg_zeff': Cgg.Cgg(Pk, L, zmin, zmax, pz_u, bz, zeff=True),
+        'cgg_full': Cgg.Cgg(Pk, L, zmin, zmax, pz_u, bz, zeff=False),
+        'cgg_ug_full': Cgg.Cgg(Pk, L, 1.8, 5.8, pz_u, bz, survey_pz2=pz_g, bz2=bz, zeff=False),
+        'ckg_zeff': Ckg.Ckg(Pk, L, zmin, zmax, pz_u, bz, zeff=True),
+        'ckg_full': Ckg.Ckg(Pk, L, zmin, zmax, pz_u, bz, zeff=False),
+        'ckk': lensing.Ckk(Pk, L),
+        'ngg': Cgg.Ngg(L, zmin, zmax, pz_u, 2181.0),
+        'lensing_kernel': lensing.lensing_kernel(np.array([0.5, 1.0, 3.0, 10.0])),
+    }
+    for name, v in got.items():
+        rel = np.max(np.abs(v / g[name] - 1))
+        assert rel < RTOL, '%s rel=%.3e' % (name, rel)
+
+
+def test_pk_callable_matches_oracle_and_rejects_foreign(ctx, golden_dir):
+    from lbgcmb_b200 import Cgg, pmh
+    from lbgcmb_b200.cosmo import FlatLambdaCDM
+    from lbgcmb_b200.synthetic import PARAMS
+    from oracle import halofit as ohf
+    g = _g(golden_dir, 'limber_root.npz')
+    Pk, pz_u, _, bz = _setup(g)
+    eng = Pk['camb_nlin'].engine
+    cosmo = FlatLambdaCDM(H0=100., Om0=PARAMS['om_m'], Ob0=PARAMS['om_b'])
+    ora = ohf.ModiPk(g['k'], g['plin'], lambda z: float(eng.Dgrow(z=z)), cosmo, PARAMS['sig_8']).interps()
+    ks = np.concatenate([[1e-6, 1e3], np.exp(np.linspace(np.log(2e-5), np.log(90.), 500))])
+    for z in (0.3, 2.96, 7.0):
+        for name in ('camb_lin', 'camb_nlin'):
+            a, b = Pk[name](z, ks), ora[name](z, ks)
+            assert a[0] == 0.0 and a[1] == 0.0                         # zero outside the table (left = right = 0)
+            assert np.max(np.abs(a[2:] / b[2:] - 1)) < RTOL, (z, name)
+    assert isinstance(Pk['camb_nlin'](1.0, 0.1), float)
+    with pytest.raises(ValueError):
+        pmh.Pmm(Pk, ks, 1.0, type='weird')
+    with pytest.raises(TypeError):
+        Cgg.Cgg({'camb_nlin': lambda z, k: k, 'camb_lin': lambda z, k: k}, g['Llls'], 0.96, 4.96, pz_u, bz)
+
+
+def test_limber_full_grid_properties(ctx, golden_dir):
+    """4951 multipoles: agrees with the 60-l grid where they coincide; linear in the bias; batching is consistent."""
+    from lbgcmb_b200 import Ckg
+    g = _g(golden_dir, 'limber_root.npz')
+    Pk, pz_u, _, bz = _setup(g)
+    Lfull = np.arange(50, 5001)
+    full = Ckg.Ckg(Pk, Lfull, 0.96, 4.96, pz_u, bz, zeff=False)
+    sub = Ckg.Ckg(Pk, g['Llls'], 0.96, 4.96, pz_u, bz, zeff=False)
+    assert np.array_equal(full[g['Llls'] - 50], sub)
+    twice = Ckg.Ckg(Pk, g['Llls'], 0.96, 4.96, pz_u, lambda z: 2. * (1. + z), zeff=False)
+    assert np.max(np.abs(twice / (2. * sub) - 1)) < 1e-14
+    eng = Pk['camb_nlin'].engine
+    zs = np.array([1.0, 2.0, 3.0])
+    chis = np.array([eng.chia(z=z) for z in zs])
+    w = np.random.default_rng(0).random((19, 3))
+    batched = eng.limber(Lfull[:300], zs, chis, w)
+    for b in (0, 7, 8, 18):
+        assert np.array_equal(batched[b], eng.limber(Lfull[:300], zs, chis, w[b:b + 1])[0])
+    assert eng.limber(np.array([]), zs, chis, w).shape == (19, 0)

@@ -1,0 +1,68 @@
+"""CPU: the oracle restatements reproduce the golden vectors written by the UNMODIFIED reference
+(oracle/make_golden.py, run in the build container).  This is what pins the oracle."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import halofit as ohf, limber as olim, n0 as on0
+from oracle.shim.astropy.cosmology import FlatLambdaCDM
+
+
+def _g(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def test_n0_root_against_reference_vector(golden_dir):
+    g = _g(golden_dir, 'n0_root_so_ttee.npz')     # 1 L: ~4 s on one core
+    li, ni = on0.cl_interps(g['ell'], g['lensed']), on0.cl_interps(g['ell'], g['unlensed'])
+    got = on0.nkk_root(li, ni, g['Ls'], tuple(str(t) for t in g['terms']), float(g['thetab']), float(g['DeltaT']),
+                       bool(g['iterative']), Tcmb=float(g['Tcmb']), cos_phi=g['cos_phi'], sin_phi=g['sin_phi'])
+    assert np.max(np.abs(got / g['nkk_reference'] - 1)) < 1e-13
+
+
+def test_halofit_against_reference_vectors(golden_dir):
+    g = _g(golden_dir, 'halofit.npz')
+    cosmo = FlatLambdaCDM(H0=100., Om0=float(g['om_m']), Ob0=float(g['om_b']))
+    k, p = g['k'], g['plin']
+    for i in (0, 3):
+        z, d = g['zs'][i], g['D'][i]
+        delta = p * k ** 3 / (2. * np.pi ** 2) * d ** 2.
+        assert np.allclose(ohf.get_spec(k, delta, float(g['sig8'])), g['spec'][i], rtol=1e-12)
+        assert np.max(np.abs(ohf.halofit(k, delta, float(g['sig8']), z, cosmo, True) / g['delta_nl'][i] - 1)) < 1e-13
+        assert np.max(np.abs(ohf.halofit(k, delta, float(g['sig8']), z, cosmo, False) / g['delta_nl_smith'][i] - 1)) < 1e-13
+
+
+def test_limber_cheap_cases_against_reference_vectors(golden_dir):
+    """zeff (thin-slice) spectra, shot noise and the lensing kernel: one halofit call each."""
+    from lbgcmb_b200.modi.cosmology import Cosmology
+    from lbgcmb_b200.synthetic import PARAMS
+    g = _g(golden_dir, 'limber_root.npz')
+    eng = Cosmology(M=PARAMS['om_m'], H0=100., B=PARAMS['om_b'], sig8=PARAMS['sig_8'], klin=g['k'], plin=g['plin'])
+    Dg = lambda z: float(eng.Dgrow(z=z))
+    assert np.allclose([Dg(z) for z in g['zchk']], g['Dchk'], rtol=1e-13)      # the growth input did not drift
+    cosmo = FlatLambdaCDM(H0=100., Om0=PARAMS['om_m'], Ob0=PARAMS['om_b'])
+    pk = ohf.ModiPk(g['k'], g['plin'], Dg, cosmo, PARAMS['sig_8']).interps()
+    bg = olim.Background(PARAMS)
+    assert np.allclose(bg.chi(g['zchk']), g['chichk'], rtol=1e-14)
+    from oracle.simps121 import simps
+
+    def pz(z, z0=2.96, s=0.24):     # Gaussian_pz.py:11-29
+        zs = np.arange(0., 10., 0.01)
+        return np.exp(-(z - z0) ** 2. / (2. * s ** 2.)) / simps(np.exp(-(zs - z0) ** 2. / (2. * s ** 2.)), dx=0.01)
+    bz = lambda z: 1. + z
+    L = g['Llls']
+    zmin, zmax = float(g['zmin']), float(g['zmax'])
+    assert np.max(np.abs(olim.Cgg(bg, pk, L, zmin, zmax, pz, bz, zeff=True) / g['cgg_zeff'] - 1)) < 1e-12
+    assert np.max(np.abs(olim.Ckg(bg, pk, L, zmin, zmax, pz, bz, zeff=True) / g['ckg_zeff'] - 1)) < 1e-12
+    assert np.max(np.abs(olim.Ngg(L, zmin, zmax, pz, 2181.0) / g['ngg'] - 1)) < 1e-13
+    assert np.allclose(bg.lensing_kernel(np.array([0.5, 1.0, 3.0, 10.0])), g['lensing_kernel'], rtol=1e-14)
+
+
+@pytest.mark.reference
+def test_reference_modules_import_under_shim():
+    from oracle import refload
+    if not refload.available():
+        pytest.skip('/root/reference not present (GPU box)')
+    for m in ('Nkk', 'Cgg', 'Ckg', 'lensing', 'halofit', 'nkk', 'snr', 'prep_Llls'):
+        assert refload.load(m).__file__.startswith(refload.REF)
