@@ -80,6 +80,20 @@ int lbg_n0_ho02(lbg_ctx* ctx, int n_L, const double* L, unsigned terms_mask,
                 double* out_nkk /*[n_L]*/, double* out_terms /*[5][n_L] or NULL*/,
                 long long* nodes_executed /*or NULL*/);
 
+/* ---- N0, modi flavour: replaces modi/nkk.py:35-92 (N_fisher: mode = LBG_TT, LBG_EE, LBG_EB) and :94-146 (N_fisherTE:
+ *      mode = LBG_TE).  out_int[n_L] is the double integral `int2` those functions return;
+ *      int2(L) = sum_i w_l[i] l[i] sum_j w_phi[j] frac(L, l_i, phi_j), frac = 0 where |l - L| lies outside [min l, max l].
+ * Four spline tables on unit-spaced knots x0[t] + 0..tab_n[t]-1, values concatenated in tab_y; they are the
+ * InterpolatedUnivariateSpline(k=3) arguments of the reference, in its argument order:
+ *   TT/EE/EB: icl1, icl2 (unlensed), icln1, icln2 (lensed + detector noise);  TE: iclte, iclnt, iclne, iclnte.
+ * The splines extrapolate beyond their knots (FITPACK ext=0), as the reference's do. */
+int lbg_n0_modi(lbg_ctx* ctx, int mode, int n_L, const double* L, int n_l, const double* l, const double* w_l,
+                int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
+                const int* tab_n /*[4]*/, const double* tab_x0 /*[4]*/, const double* tab_y /*concatenated*/,
+                double* out_int /*[n_L]*/);
+/* scipy InterpolatedUnivariateSpline(x0 + arange(n_knots), y, k=3)(x) (modi/nkk.py:205-213 callables). */
+int lbg_eval_spline_ext(lbg_ctx* ctx, int n_knots, double x0, const double* y, int n, const double* x, double* out);
+
 /* ---- matter power: linear table x growth^2 -> HALOFIT; replaces modi/cosmology.py:158-182 (pkalin/pkanlin) and the
  *      array work of modi/halofit.py (sigma^2(R) integrals :36-44, Takahashi/Smith formula :139-212) ----------------- */
 /* k [h/Mpc] increasing, P_lin(k, z=0) [(Mpc/h)^3], w_lnk = scipy-1.2.1 simps weights of the ln k grid (halofit.py:42). */
@@ -98,6 +112,32 @@ int lbg_pk_eval(lbg_ctx* ctx, int row, int n, const double* x, int oob, double* 
  *      weight = kernel product x bias x unit factors x quadrature weight, so one kernel serves every flavour. */
 int lbg_limber(lbg_ctx* ctx, int n_batch, int n_ell, const double* ell, int n_z, const double* chi,
                const double* weight /*[n_batch][n_z]*/, const int* prow /*[n_z]*/, int oob, double* out_cl /*[n_batch][n_ell]*/);
+
+/* ---- S/N, covariance and Fisher accumulation over multipoles ---------------------------------------------------- */
+/* snr.py:21-25 `snr`: sqrt( sum_{l <= lmax} nmodes (C_l / sqrt(Var_l))^2 ). */
+int lbg_snr(lbg_ctx* ctx, int n_ell, const double* ell, const double* cl, const double* var, const double* nmodes,
+            double lmax, double* out_snr);
+/* interloper.py:42-63 `get_ClsCov` for any set of fields: tot[l][a][b] = (C + N)^{ab}(l) (n_f x n_f, symmetric);
+ * spectrum i is the field pair (spec_a[i], spec_b[i]);
+ * cov[l][i][j] = (T^{ac} T^{bd} + T^{ad} T^{bc}) / (2 l + 1) / fsky  with (a,b) = pair i and (c,d) = pair j. */
+int lbg_gaussian_cov(lbg_ctx* ctx, int n_ell, const double* ell, int n_f, const double* tot /*[n_ell][n_f][n_f]*/,
+                     int n_spec, const int* spec_a, const int* spec_b, double fsky, double* out_cov /*[n_ell][n_spec][n_spec]*/);
+/* interloper.py:223-253 (Fisher matrix and bias vector) and yu.py:99-106 (rho_L^2 = r^T rho^-1 r, n_par = 1):
+ * per multipole Q_l[p][q] = dD_p^T Cov_l^-1 dD_q and b_l[p] = dD_p^T Cov_l^-1 dDelta_l (LU with partial pivoting on the
+ * diagonally equilibrated matrix); out_F = sum_l mode_weight[l] Q_l, out_b = sum_l mode_weight[l] b_l (fixed-order sums).
+ * n_spec <= 32, n_par <= 8.  dDelta / out_b / out_per_ell ([n_ell][n_par][n_par], the Q_l themselves) may be NULL.
+ * A multi-GPU caller shards l, calls this per rank and all-reduces out_F / out_b (lbgcmb_b200/dist.py, NCCL). */
+int lbg_fisher_accum(lbg_ctx* ctx, int n_ell, int n_spec, int n_par, const double* cov /*[n_ell][n_spec][n_spec]*/,
+                     const double* dD /*[n_ell][n_par][n_spec]*/, const double* dDelta /*[n_ell][n_spec] or NULL*/,
+                     const double* mode_weight /*[n_ell]*/, double* out_F /*[n_par][n_par]*/, double* out_b /*[n_par] or NULL*/,
+                     double* out_per_ell /*or NULL*/);
+/* mqw/py/mqw.py:63-104 `Fisher` (clustering-redshift N_p(z_i) Fisher): bins[n_bin][8] = {bp, bs, Np, Ns, wp, ws, wps, -}
+ * per redshift shell (mqw.py:24-41); cgg[n_ell] shared by all shells (cgg_per_bin = 0, as mqw.py:48) or
+ * cgg[n_bin][n_ell] (cgg_per_bin = 1, as cadence/cadence.py:97); mode_weight[l] = 2l+1 (0 beyond an l cut).
+ * out_F[n_bin][n_bin]: mqw.py:97-104; out_Fsl[n_bin]: the Schur-Limber diagonal F_ii of mqw.py:83; out_S[n_ell]: S(l). */
+int lbg_mqw_fisher(lbg_ctx* ctx, int n_ell, int n_bin, const double* cgg, int cgg_per_bin, const double* bins /*[n_bin][8]*/,
+                   const double* mode_weight /*[n_ell]*/, double fsky, double* out_F, double* out_Fsl /*or NULL*/,
+                   double* out_S /*or NULL*/);
 
 #ifdef __cplusplus
 }

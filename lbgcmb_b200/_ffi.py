@@ -63,6 +63,13 @@ def _declare(L):
         'lbg_pk_build_table': [vp, i, c_double_p, d, d, d, i, c_double_p],
         'lbg_pk_eval': [vp, i, i, c_double_p, i, c_double_p],
         'lbg_limber': [vp, i, i, c_double_p, i, c_double_p, c_double_p, c_int_p, i, c_double_p],
+        'lbg_n0_modi': [vp, i, i, c_double_p, i, c_double_p, c_double_p, i, c_double_p, c_double_p, c_double_p,
+                        c_int_p, c_double_p, c_double_p, c_double_p],
+        'lbg_eval_spline_ext': [vp, i, d, c_double_p, i, c_double_p, c_double_p],
+        'lbg_snr': [vp, i, c_double_p, c_double_p, c_double_p, c_double_p, d, c_double_p],
+        'lbg_gaussian_cov': [vp, i, c_double_p, i, c_double_p, i, c_int_p, c_int_p, d, c_double_p],
+        'lbg_fisher_accum': [vp, i, i, i, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p],
+        'lbg_mqw_fisher': [vp, i, i, c_double_p, i, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_n0_ho02': [vp, i, c_double_p, u, d, d, d, i, i, c_double_p, c_double_p, i, c_double_p, c_double_p,
                         c_double_p, d, d, d, i, i, c_int_p, c_double_p, c_double_p, c_double_p, c_ll_p],
     }

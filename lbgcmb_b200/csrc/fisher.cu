@@ -1,0 +1,331 @@
+// fisher.cu -- per-multipole covariance / S-N / Fisher accumulation (the "L4" stage of the forecast path).
+//
+// Replaces: snr.py:21-25 (snr), interloper.py:42-63 (get_ClsCov), interloper.py:223-253 (per-L inverse covariance,
+//           Fisher and bias-vector sums), yu.py:76-108 (per-L tracer correlation matrix, rho_L^2 = r^T rho^-1 r),
+//           mqw/py/mqw.py:91-104 and cadence/cadence.py:156-166 (N_p(z_i) Fisher outwith the Schur limit).
+// Every sum over multipoles is a fixed-order tree (block partials -> one final block): deterministic, no atomics.
+// The work is tiny at reference sizes (<= 4951 multipoles, matrices <= 20 x 20): these kernels are latency bound and
+// no roofline fraction is claimed for them.
+#include "common.cuh"
+#include <cmath>
+
+namespace lbg {
+
+constexpr int RED_T = 256;
+
+// Block-wide sum of `nv` values per thread (nv <= 32 per pass); result valid in thread 0.
+template <int NV>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double* sm /*[NV][RED_T]*/) {
+#pragma unroll
+    for (int q = 0; q < NV; ++q) sm[q * RED_T + threadIdx.x] = v[q];
+    __syncthreads();
+    for (int h = RED_T / 2; h > 0; h >>= 1) {
+        if (threadIdx.x < h) {
+#pragma unroll
+            for (int q = 0; q < NV; ++q) sm[q * RED_T + threadIdx.x] += sm[q * RED_T + threadIdx.x + h];
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int q = 0; q < NV; ++q) v[q] = sm[q * RED_T];
+    __syncthreads();
+}
+
+// snr.py:21-25: sum over l <= lmax of nmodes (C / sqrt(Var))^2 ; one block, fixed order.
+__global__ void __launch_bounds__(RED_T)
+snr_kernel(int n, const double* __restrict__ ell, const double* __restrict__ cl, const double* __restrict__ var,
+           const double* __restrict__ nmodes, double lmax, double* __restrict__ out) {
+    __shared__ double sm[RED_T];
+    double acc[1] = {0.0};
+    for (int i = threadIdx.x; i < n; i += RED_T) {
+        if (ell[i] <= lmax) {
+            const double r = cl[i] / sqrt(var[i]);
+            acc[0] += nmodes[i] * (r * r);
+        }
+    }
+    block_sum<1>(acc, sm);
+    if (threadIdx.x == 0) out[0] = sqrt(acc[0]);
+}
+
+// interloper.py:42-63 for any set of fields: tot[l][a][b] = (C + N)^{ab}(l); spectrum i is the field pair (sa[i], sb[i]).
+// cov[l][i][j] = (T^{a c} T^{b d} + T^{a d} T^{b c}) / (2 l + 1) / fsky  with (a,b) = pair i, (c,d) = pair j.
+__global__ void gaussian_cov_kernel(int n_ell, int n_f, int n_spec, const double* __restrict__ ell, const double* __restrict__ tot,
+                                    const int* __restrict__ sa, const int* __restrict__ sb, double fsky, double* __restrict__ cov) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long n = (long long)n_ell * n_spec * n_spec;
+    if (t >= n) return;
+    const int j = (int)(t % n_spec), i = (int)((t / n_spec) % n_spec), l = (int)(t / ((long long)n_spec * n_spec));
+    const double* T = tot + (size_t)l * n_f * n_f;
+    const int a = sa[i], b = sb[i], c = sa[j], d = sb[j];
+    double r = __dmul_rn(T[a * n_f + c], T[b * n_f + d]);
+    r = __dadd_rn(r, __dmul_rn(T[a * n_f + d], T[b * n_f + c]));
+    r = __ddiv_rn(r, __dadd_rn(__dmul_rn(2.0, ell[l]), 1.0));
+    cov[t] = __ddiv_rn(r, fsky);
+}
+
+// In-thread solve of the symmetric system C X = B by LU with partial pivoting after symmetric diagonal equilibration
+// (C_ij / sqrt(C_ii C_jj)): band-power covariances span many decades between kk and gg, the correlation matrix does not.
+template <int MS, int MR>
+__device__ void solve_spd(int ns, int nr, double* A /*[ns][ns], destroyed*/, double* B /*[nr][ns] in, solution out*/) {
+    double sc[MS];
+    for (int i = 0; i < ns; ++i) sc[i] = 1.0 / sqrt(fabs(A[i * ns + i]));
+    for (int i = 0; i < ns; ++i)
+        for (int j = 0; j < ns; ++j) A[i * ns + j] *= sc[i] * sc[j];
+    for (int r = 0; r < nr; ++r)
+        for (int i = 0; i < ns; ++i) B[r * ns + i] *= sc[i];
+    for (int k = 0; k < ns; ++k) {
+        int p = k;
+        double best = fabs(A[k * ns + k]);
+        for (int i = k + 1; i < ns; ++i) {
+            const double v = fabs(A[i * ns + k]);
+            if (v > best) { best = v; p = i; }
+        }
+        if (p != k) {
+            for (int j = 0; j < ns; ++j) { const double t = A[k * ns + j]; A[k * ns + j] = A[p * ns + j]; A[p * ns + j] = t; }
+            for (int r = 0; r < nr; ++r) { const double t = B[r * ns + k]; B[r * ns + k] = B[r * ns + p]; B[r * ns + p] = t; }
+        }
+        const double piv = 1.0 / A[k * ns + k];
+        for (int i = k + 1; i < ns; ++i) {
+            const double f = A[i * ns + k] * piv;
+            if (f != 0.0) {
+                for (int j = k + 1; j < ns; ++j) A[i * ns + j] -= f * A[k * ns + j];
+                for (int r = 0; r < nr; ++r) B[r * ns + i] -= f * B[r * ns + k];
+            }
+        }
+    }
+    for (int r = 0; r < nr; ++r)
+        for (int i = ns - 1; i >= 0; --i) {
+            double s = B[r * ns + i];
+            for (int j = i + 1; j < ns; ++j) s -= A[i * ns + j] * B[r * ns + j];
+            B[r * ns + i] = s / A[i * ns + i];
+        }
+    for (int r = 0; r < nr; ++r)
+        for (int i = 0; i < ns; ++i) B[r * ns + i] *= sc[i];
+}
+
+constexpr int MAX_PAR = 8;
+
+// One thread per multipole: X = C^-1 [dD_0 .. dD_{np-1}, dDelta], then q[l] = {dD_p . X_q (np x np), dD_p . X_delta (np)}.
+// interloper.py:223-253 (np = 2, ns = 3), yu.py:99-106 (np = 1, ns = number of tracers).
+template <int MS>
+__global__ void __launch_bounds__(64)
+quadform_kernel(int n_ell, int ns, int np, const double* __restrict__ cov, const double* __restrict__ dD,
+                const double* __restrict__ dDelta, double* __restrict__ q /*[n_ell][np*np + np]*/) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= n_ell) return;
+    double A[MS * MS], B[(MAX_PAR + 1) * MS], D[MAX_PAR * MS];
+    for (int e = 0; e < ns * ns; ++e) A[e] = cov[(size_t)l * ns * ns + e];
+    for (int e = 0; e < np * ns; ++e) { D[e] = dD[(size_t)l * np * ns + e]; B[e] = D[e]; }
+    const int nr = np + (dDelta ? 1 : 0);
+    if (dDelta) for (int i = 0; i < ns; ++i) B[np * ns + i] = dDelta[(size_t)l * ns + i];
+    solve_spd<MS, MAX_PAR + 1>(ns, nr, A, B);
+    const int nq = np * np + np;
+    double* o = q + (size_t)l * nq;
+    for (int p = 0; p < np; ++p) {
+        for (int r = 0; r < np; ++r) {
+            double s = 0.0;
+            for (int i = 0; i < ns; ++i) s += D[p * ns + i] * B[r * ns + i];
+            o[p * np + r] = s;
+        }
+        double s = 0.0;
+        if (dDelta) for (int i = 0; i < ns; ++i) s += D[p * ns + i] * B[np * ns + i];
+        o[np * np + p] = s;
+    }
+}
+
+// out[e] = sum_l w[l] q[l][e]; one block per entry e, fixed order.
+__global__ void __launch_bounds__(RED_T)
+weighted_sum_kernel(int n_ell, int nq, const double* __restrict__ w, const double* __restrict__ q, double* __restrict__ out) {
+    __shared__ double sm[RED_T];
+    const int e = blockIdx.x;
+    double acc[1] = {0.0};
+    for (int l = threadIdx.x; l < n_ell; l += RED_T) acc[0] += w[l] * q[(size_t)l * nq + e];
+    block_sum<1>(acc, sm);
+    if (threadIdx.x == 0) out[e] = acc[0];
+}
+
+struct MqwBin { double bp, bs, Np, Ns, wp, ws, wps, pad; };   // per redshift shell, mqw/py/mqw.py:24-41
+
+// mqw.py:63-94: A00(l) = sum_i [cgg (bp Np)^2 + wp], sshift(l) = sum_i A0i^2 / Aii, S = A00 / (A00 - sshift).
+__global__ void mqw_schur_kernel(int n_ell, int n_bin, size_t cgg_stride, const double* __restrict__ cgg,
+                                 const MqwBin* __restrict__ bins, double* __restrict__ A00, double* __restrict__ S) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= n_ell) return;
+    double a00 = 0.0, ss = 0.0;
+    for (int i = 0; i < n_bin; ++i) {
+        const MqwBin b = bins[i];
+        const double c = cgg[(size_t)i * cgg_stride + l];
+        const double bpNp = b.bp * b.Np, bsNs = b.bs * b.Ns;
+        a00 += c * (bpNp * bpNp) + b.wp;
+        const double A0i = bpNp * bsNs * c + b.wps;
+        const double Aii = bsNs * bsNs * c + b.ws;
+        ss += A0i * A0i / Aii;
+    }
+    A00[l] = a00;
+    S[l] = a00 / (a00 - ss);
+}
+
+// mqw.py:97-104: block (i, j) sums over l; block (i, n_bin) does the Schur-Limber diagonal of mqw.py:83-87.
+__global__ void __launch_bounds__(RED_T)
+mqw_fisher_kernel(int n_ell, int n_bin, size_t cgg_stride, const double* __restrict__ cgg, const MqwBin* __restrict__ bins,
+                  const double* __restrict__ w /*(2l+1) or 0 beyond an l cut*/, double fsky, const double* __restrict__ A00,
+                  const double* __restrict__ S, double* __restrict__ F /*[n_bin][n_bin]*/, double* __restrict__ Fsl /*[n_bin]*/) {
+    __shared__ double sm[RED_T];
+    const int i = blockIdx.y, j = blockIdx.x;
+    const MqwBin bi = bins[i];
+    double acc[1] = {0.0};
+    if (j == n_bin) {
+        for (int l = threadIdx.x; l < n_ell; l += RED_T) {
+            const double c = cgg[(size_t)i * cgg_stride + l];
+            const double num = bi.bp * bi.bs * c;
+            acc[0] += w[l] * (num * num / A00[l]);
+        }
+        block_sum<1>(acc, sm);
+        if (threadIdx.x == 0) Fsl[i] = bi.Ns * fsky * acc[0];
+        return;
+    }
+    const MqwBin bj = bins[j];
+    for (int l = threadIdx.x; l < n_ell; l += RED_T) {
+        const double ci = cgg[(size_t)i * cgg_stride + l], cj = cgg[(size_t)j * cgg_stride + l];
+        const double a00 = A00[l], s = S[l];
+        const double bsNs_i = bi.bs * bi.Ns, bsNs_j = bj.bs * bj.Ns;
+        const double Aii = bsNs_i * bsNs_i * ci + bi.ws, Ajj = bsNs_j * bsNs_j * cj + bj.ws;
+        const double A0i = bi.bp * bi.Np * bsNs_i * ci + bi.wps, A0j = bj.bp * bj.Np * bsNs_j * cj + bj.wps;
+        const double A0i_j = bi.bp * bsNs_i * ci, A0j_j = bj.bp * bsNs_j * cj;
+        const double ri = A0i / sqrt(a00 * Aii), rj = A0j / sqrt(a00 * Ajj);
+        double t = 2.0 * s * s * ri * rj * sqrt(1.0 / Aii / Ajj) * A0i_j * A0j_j / a00;
+        if (i == j) t += s * A0i_j * A0i_j / Aii / a00;
+        acc[0] += w[l] * t;
+    }
+    block_sum<1>(acc, sm);
+    if (threadIdx.x == 0) F[i * n_bin + j] = fsky * acc[0];
+}
+}  // namespace lbg
+
+using namespace lbg;
+
+extern "C" int lbg_snr(lbg_ctx* c, int n_ell, const double* ell, const double* cl, const double* var, const double* nmodes,
+                       double lmax, double* out_snr) {
+    LBG_REQUIRE(c && out_snr && n_ell >= 0, "lbg_snr: bad argument");
+    LBG_REQUIRE(n_ell == 0 || (ell && cl && var && nmodes), "lbg_snr: NULL array");
+    if (n_ell == 0) { *out_snr = 0.0; return LBG_OK; }
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    const size_t nb = (size_t)n_ell * 8;
+    if (c->s0.reserve(4 * nb + 8)) return LBG_ENOMEM;
+    double* d = c->s0.as<double>();
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaMemcpyAsync(d, ell, nb, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d + n_ell, cl, nb, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d + 2 * (size_t)n_ell, var, nb, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d + 3 * (size_t)n_ell, nmodes, nb, cudaMemcpyHostToDevice, st));
+    KernelTimer t(c);
+    snr_kernel<<<1, RED_T, 0, st>>>(n_ell, d, d + n_ell, d + 2 * (size_t)n_ell, d + 3 * (size_t)n_ell, lmax, d + 4 * (size_t)n_ell);
+    t.launched();
+    LBG_CUDA(cudaMemcpyAsync(out_snr, d + 4 * (size_t)n_ell, 8, cudaMemcpyDeviceToHost, st));
+    return t.finish();
+}
+
+extern "C" int lbg_gaussian_cov(lbg_ctx* c, int n_ell, const double* ell, int n_f, const double* tot, int n_spec,
+                                const int* spec_a, const int* spec_b, double fsky, double* out_cov) {
+    LBG_REQUIRE(c && ell && tot && spec_a && spec_b && out_cov, "lbg_gaussian_cov: NULL argument");
+    LBG_REQUIRE(n_ell >= 0 && n_f > 0 && n_spec > 0 && fsky > 0, "lbg_gaussian_cov: bad sizes");
+    for (int i = 0; i < n_spec; ++i)
+        LBG_REQUIRE(spec_a[i] >= 0 && spec_a[i] < n_f && spec_b[i] >= 0 && spec_b[i] < n_f, "lbg_gaussian_cov: spectrum %d names a field outside 0..%d", i, n_f - 1);
+    if (n_ell == 0) return LBG_OK;
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    const size_t nt = (size_t)n_ell * n_f * n_f, nc = (size_t)n_ell * n_spec * n_spec;
+    if (c->s0.reserve((size_t)n_ell * 8) || c->s1.reserve(nt * 8) || c->s2.reserve((size_t)2 * n_spec * 4) || c->s3.reserve(nc * 8)) return LBG_ENOMEM;
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, ell, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s1.p, tot, nt * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s2.p, spec_a, (size_t)n_spec * 4, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s2.as<int>() + n_spec, spec_b, (size_t)n_spec * 4, cudaMemcpyHostToDevice, st));
+    KernelTimer t(c);
+    gaussian_cov_kernel<<<(unsigned)((nc + 127) / 128), 128, 0, st>>>(n_ell, n_f, n_spec, c->s0.as<double>(), c->s1.as<double>(),
+                                                                     c->s2.as<int>(), c->s2.as<int>() + n_spec, fsky, c->s3.as<double>());
+    t.launched();
+    LBG_CUDA(cudaMemcpyAsync(out_cov, c->s3.p, nc * 8, cudaMemcpyDeviceToHost, st));
+    return t.finish();
+}
+
+extern "C" int lbg_fisher_accum(lbg_ctx* c, int n_ell, int n_spec, int n_par, const double* cov, const double* dD,
+                                const double* dDelta, const double* mode_weight, double* out_F, double* out_b,
+                                double* out_per_ell) {
+    LBG_REQUIRE(c && out_F, "lbg_fisher_accum: NULL argument");
+    LBG_REQUIRE(n_ell >= 0 && n_spec >= 1 && n_spec <= 32, "lbg_fisher_accum: n_spec=%d outside [1, 32]", n_spec);
+    LBG_REQUIRE(n_par >= 1 && n_par <= MAX_PAR, "lbg_fisher_accum: n_par=%d outside [1, %d]", n_par, MAX_PAR);
+    LBG_REQUIRE(n_ell == 0 || (cov && dD && mode_weight), "lbg_fisher_accum: NULL array");
+    LBG_REQUIRE(!out_b || dDelta, "lbg_fisher_accum: out_b requested without dDelta");
+    const int nq = n_par * n_par + n_par;
+    if (n_ell == 0) {
+        for (int e = 0; e < n_par * n_par; ++e) out_F[e] = 0.0;
+        if (out_b) for (int e = 0; e < n_par; ++e) out_b[e] = 0.0;
+        return LBG_OK;
+    }
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    const size_t ncov = (size_t)n_ell * n_spec * n_spec, nd = (size_t)n_ell * n_par * n_spec, ndl = (size_t)n_ell * n_spec;
+    if (c->s0.reserve(ncov * 8) || c->s1.reserve(nd * 8) || c->s2.reserve(ndl * 8) || c->s3.reserve((size_t)n_ell * 8) ||
+        c->s4.reserve((size_t)n_ell * nq * 8) || c->s5.reserve((size_t)nq * 8)) return LBG_ENOMEM;
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, cov, ncov * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s1.p, dD, nd * 8, cudaMemcpyHostToDevice, st));
+    if (dDelta) LBG_CUDA(cudaMemcpyAsync(c->s2.p, dDelta, ndl * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s3.p, mode_weight, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
+    const double* dd = dDelta ? c->s2.as<double>() : nullptr;
+    const int gx = (n_ell + 63) / 64;
+    KernelTimer t(c);
+    if (n_spec <= 4)       quadform_kernel<4><<<gx, 64, 0, st>>>(n_ell, n_spec, n_par, c->s0.as<double>(), c->s1.as<double>(), dd, c->s4.as<double>());
+    else if (n_spec <= 8)  quadform_kernel<8><<<gx, 64, 0, st>>>(n_ell, n_spec, n_par, c->s0.as<double>(), c->s1.as<double>(), dd, c->s4.as<double>());
+    else if (n_spec <= 16) quadform_kernel<16><<<gx, 64, 0, st>>>(n_ell, n_spec, n_par, c->s0.as<double>(), c->s1.as<double>(), dd, c->s4.as<double>());
+    else                   quadform_kernel<32><<<gx, 64, 0, st>>>(n_ell, n_spec, n_par, c->s0.as<double>(), c->s1.as<double>(), dd, c->s4.as<double>());
+    t.launched();
+    weighted_sum_kernel<<<nq, RED_T, 0, st>>>(n_ell, nq, c->s3.as<double>(), c->s4.as<double>(), c->s5.as<double>());
+    t.launched();
+    std::vector<double> host(nq);
+    LBG_CUDA(cudaMemcpyAsync(host.data(), c->s5.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, st));
+    std::vector<double> per;
+    if (out_per_ell) {
+        per.resize((size_t)n_ell * nq);
+        LBG_CUDA(cudaMemcpyAsync(per.data(), c->s4.p, per.size() * 8, cudaMemcpyDeviceToHost, st));
+    }
+    int rc = t.finish();
+    if (rc) return rc;
+    memcpy(out_F, host.data(), (size_t)n_par * n_par * 8);
+    if (out_b) memcpy(out_b, host.data() + n_par * n_par, (size_t)n_par * 8);
+    if (out_per_ell)
+        for (int l = 0; l < n_ell; ++l) memcpy(out_per_ell + (size_t)l * n_par * n_par, per.data() + (size_t)l * nq, (size_t)n_par * n_par * 8);
+    return LBG_OK;
+}
+
+extern "C" int lbg_mqw_fisher(lbg_ctx* c, int n_ell, int n_bin, const double* cgg, int cgg_per_bin, const double* bins,
+                              const double* mode_weight, double fsky, double* out_F, double* out_Fsl, double* out_S) {
+    LBG_REQUIRE(c && cgg && bins && mode_weight && out_F, "lbg_mqw_fisher: NULL argument");
+    LBG_REQUIRE(n_ell > 0 && n_bin > 0 && n_bin <= 1024, "lbg_mqw_fisher: bad sizes n_ell=%d n_bin=%d", n_ell, n_bin);
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    const size_t ncg = (size_t)(cgg_per_bin ? n_bin : 1) * n_ell;
+    if (c->s0.reserve(ncg * 8) || c->s1.reserve((size_t)n_bin * sizeof(MqwBin)) || c->s2.reserve((size_t)n_ell * 8) ||
+        c->s3.reserve((size_t)2 * n_ell * 8) || c->s4.reserve((size_t)(n_bin + 1) * n_bin * 8)) return LBG_ENOMEM;
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, cgg, ncg * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s1.p, bins, (size_t)n_bin * sizeof(MqwBin), cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s2.p, mode_weight, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
+    double* A00 = c->s3.as<double>();
+    double* S = A00 + n_ell;
+    double* F = c->s4.as<double>();
+    double* Fsl = F + (size_t)n_bin * n_bin;
+    const size_t stride = cgg_per_bin ? (size_t)n_ell : 0;
+    KernelTimer t(c);
+    mqw_schur_kernel<<<(n_ell + 127) / 128, 128, 0, st>>>(n_ell, n_bin, stride, c->s0.as<double>(), c->s1.as<MqwBin>(), A00, S);
+    t.launched();
+    mqw_fisher_kernel<<<dim3(n_bin + 1, n_bin), RED_T, 0, st>>>(n_ell, n_bin, stride, c->s0.as<double>(), c->s1.as<MqwBin>(),
+                                                               c->s2.as<double>(), fsky, A00, S, F, Fsl);
+    t.launched();
+    LBG_CUDA(cudaMemcpyAsync(out_F, F, (size_t)n_bin * n_bin * 8, cudaMemcpyDeviceToHost, st));
+    if (out_Fsl) LBG_CUDA(cudaMemcpyAsync(out_Fsl, Fsl, (size_t)n_bin * 8, cudaMemcpyDeviceToHost, st));
+    if (out_S) LBG_CUDA(cudaMemcpyAsync(out_S, S, (size_t)n_ell * 8, cudaMemcpyDeviceToHost, st));
+    return t.finish();
+}

@@ -1,0 +1,59 @@
+"""Device-side covariance / Fisher primitives shared by the mirrors of interloper.py, mqw.py and yu.py
+(csrc/fisher.cu through lbg_gaussian_cov, lbg_fisher_accum, lbg_mqw_fisher).  No CPU path."""
+import numpy as np
+
+from lbgcmb_b200 import _ffi
+
+
+def gaussian_cov(Llls, tot, spectra, fsky, device=None):
+    """cov[l, i, j] of interloper.py:42-63 for field pairs `spectra` = [(a, b), ...] and tot[l, a, b] = (C + N)^{ab}."""
+    ctx = _ffi.context(device)
+    L = _ffi.f64(Llls)
+    tot = _ffi.f64(tot)
+    if tot.ndim != 3 or tot.shape[0] != L.size or tot.shape[1] != tot.shape[2]:
+        raise ValueError('tot must be [n_ell, n_f, n_f]')
+    sa = np.ascontiguousarray([s[0] for s in spectra], dtype=np.int32)
+    sb = np.ascontiguousarray([s[1] for s in spectra], dtype=np.int32)
+    out = np.empty((L.size, sa.size, sa.size))
+    _ffi.check(_ffi.lib().lbg_gaussian_cov(ctx.handle, L.size, _ffi._dp(L), tot.shape[1], _ffi._dp(tot), sa.size,
+                                           sa.ctypes.data_as(_ffi.c_int_p), sb.ctypes.data_as(_ffi.c_int_p), float(fsky), _ffi._dp(out)))
+    return out
+
+
+def fisher_accum(cov, dD, mode_weight, dDelta=None, per_ell=False, device=None):
+    """F = sum_l w_l dD_l Cov_l^-1 dD_l^T  (and b = sum_l w_l dD_l Cov_l^-1 dDelta_l); interloper.py:223-253.
+
+    cov [n_ell, n_spec, n_spec]; dD [n_ell, n_par, n_spec]; dDelta [n_ell, n_spec] or None.
+    Returns F, b (None without dDelta) and, with per_ell, the per-multipole Q_l [n_ell, n_par, n_par]."""
+    ctx = _ffi.context(device)
+    cov, dD, w = _ffi.f64(cov), _ffi.f64(dD), _ffi.f64(mode_weight)
+    n_ell, n_par, n_spec = dD.shape
+    if cov.shape != (n_ell, n_spec, n_spec) or w.shape != (n_ell,):
+        raise ValueError('cov / dD / mode_weight shapes disagree')
+    dl = None
+    if dDelta is not None:
+        dl = _ffi.f64(dDelta)
+        if dl.shape != (n_ell, n_spec):
+            raise ValueError('dDelta must be [n_ell, n_spec]')
+    F = np.empty((n_par, n_par))
+    b = np.empty(n_par) if dl is not None else None
+    Q = np.empty((n_ell, n_par, n_par)) if per_ell else None
+    _ffi.check(_ffi.lib().lbg_fisher_accum(ctx.handle, n_ell, n_spec, n_par, _ffi._dp(cov), _ffi._dp(dD), _ffi._dp(dl), _ffi._dp(w),
+                                           _ffi._dp(F), _ffi._dp(b), _ffi._dp(Q)))
+    return (F, b, Q) if per_ell else (F, b)
+
+
+def mqw_fisher(cgg, bins, mode_weight, fsky, device=None):
+    """(F [n_bin, n_bin], F_ii Schur-Limber [n_bin], S(l)) of mqw/py/mqw.py:63-104; bins[n_bin, 7] = bp,bs,Np,Ns,wp,ws,wps."""
+    ctx = _ffi.context(device)
+    cgg, w = _ffi.f64(cgg), _ffi.f64(mode_weight)
+    b = np.zeros((len(bins), 8))
+    b[:, :7] = np.asarray(bins, dtype=np.float64)
+    n_bin, n_ell = b.shape[0], w.size
+    per_bin = cgg.ndim == 2
+    if cgg.shape != ((n_bin, n_ell) if per_bin else (n_ell,)):
+        raise ValueError('cgg must be [n_ell] or [n_bin, n_ell]')
+    F, Fsl, S = np.empty((n_bin, n_bin)), np.empty(n_bin), np.empty(n_ell)
+    _ffi.check(_ffi.lib().lbg_mqw_fisher(ctx.handle, n_ell, n_bin, _ffi._dp(cgg), int(per_bin), _ffi._dp(b), _ffi._dp(w), float(fsky),
+                                         _ffi._dp(F), _ffi._dp(Fsl), _ffi._dp(S)))
+    return F, Fsl, S

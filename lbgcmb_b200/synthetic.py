@@ -64,3 +64,15 @@ def linz_bz(z):
 
 DROPOUTS = {  # (z0, sigma, nbar [deg^-2]) -- SURVEY.md 8(d)
     'u': (2.96, 0.24, 2181.0), 'g': (3.8, 0.3, 5409.0), 'r': (4.9, 0.3, 1332.0), 'i': (5.9, 0.3, 300.0)}
+
+
+def write_class_files(clfile, clsfile, n_unlensed=5799, n_lensed=5299):
+    """CLASS-format text files as modi/nkk.py:168-192 reads them: columns l, TT, EE, TE, BB, phiphi, TPhi, Ephi for
+    l = 2.., spectra multiplied by l(l+1)/2pi; the unlensed file runs 500 multipoles further (modi/nkk.py:186)."""
+    ell, lens, nolens = cmb_cl_tables(n_unlensed + 2)
+    for path, tab, n in ((clfile, nolens, n_unlensed), (clsfile, lens, n_lensed)):
+        l = ell[2:n + 2]
+        f = l * (l + 1.) / (2. * np.pi)
+        pp = 1.0e-7 / (l * (l + 1.)) ** 2 * np.exp(-l / 800.)
+        cols = [l, tab[0, 2:n + 2] * f, tab[1, 2:n + 2] * f, tab[3, 2:n + 2] * f, tab[2, 2:n + 2] * f, pp * f, 0. * l, 0. * l]
+        np.savetxt(path, np.array(cols).T, fmt='%.17e')

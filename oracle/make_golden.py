@@ -107,7 +107,142 @@ def make_limber():
                         zchk=zchk, Dchk=np.array([Dg(z) for z in zchk]), chichk=bg.chi(zchk), **res)
 
 
-MAKERS = {'n0': make_n0, 'halofit': make_halofit, 'limber': make_limber}
+def fisher_tracers():
+    """Analytic stand-ins for the survey inputs of interloper.py / mqw.py / yu.py (shared by the GPU tests)."""
+    g = lambda z0, s: (lambda z: np.exp(-(np.asarray(z, dtype=np.float64) - z0) ** 2 / (2. * s * s)) / (np.sqrt(2. * np.pi) * s))
+    return {
+        'pz_u': g(2.96, 0.24), 'bz': (lambda z: 1. + z),
+        'pz_int': (lambda z: 0.94 * g(2.96, 0.24)(z) + 0.06 * g(1.5, 0.2)(z)), 'bz_int': (lambda z: 0.97 * (1. + z)),
+        'yu': [((lambda z: 1.3 + 0. * z), g(0.4, 0.15), 900.), ((lambda z: 1.7 + 0. * z), g(0.8, 0.2), 300.),
+               ((lambda z: 1.2 + 0.5 * z), g(1.4, 0.3), 150.)],
+        'mqw_ps': g(3.0, 0.4), 'mqw_pp': g(3.1, 0.45), 'mqw_bs': (lambda z: 2.0 + 0.3 * z), 'mqw_bp': (lambda z: 1. + z),
+    }
+
+
+def make_fisher():
+    import os as _os
+    from . import halofit as ohf, fisher as ofi
+    hf = refload.load('halofit')
+    Cgg, Ckg, lensing = refload.load('Cgg'), refload.load('Ckg'), refload.load('lensing')
+    snr = refload.load('snr')
+    prep = refload.load('prep_Llls')
+    sys.path[:0] = [_os.path.join(refload.REF, x) for x in ('dropouts', 'mqw/py', 'dropouts/bz/py', 'dropouts/schechter')]
+    cwd = _os.getcwd()
+    _os.chdir(refload.REF)                         # schmittfull_nz.py reads dat/ss17_tracers.dat relative to the cwd
+    interloper, mqw = refload.load('interloper'), refload.load('mqw')
+    _os.chdir(cwd)
+    k, p, eng, cosmo, P = _pk_setup()
+    Dg = lambda z: float(eng.Dgrow(z=z))
+    ref_pk = ohf.ModiPk(k, p, Dg, cosmo, P['sig_8'], halofit_fn=hf.halofit).interps()
+    T = fisher_tracers()
+    _, Llls, nmodes = prep.prep_Llls(60, 50, 5000, log10=True)
+    zmin, zmax, fsky = 0.96, 4.96, 0.4
+    out = {'k': k, 'plin': p, 'Llls': Llls, 'nmodes': nmodes, 'zmin': zmin, 'zmax': zmax, 'fsky': fsky}
+    t = time.time()
+    # ---- interloper.py: fiducial and contaminated spectra with the reference's own Limber code --------------------------
+    nkk = 2.0e-8 * (1. + (Llls / 1500.) ** 2.)
+    Ld = Llls.astype(np.float64)
+    def allcls(pz, bz, nbar):
+        cgg = Cgg.Cgg(ref_pk, Llls, zmin, zmax, pz, bz, zeff=False, bz2=bz, survey_pz2=pz)
+        ngg = Cgg.Ngg(Ld, zmin, zmax, pz, nbar)
+        ckg = Ckg.Ckg(ref_pk, Llls, zmin, zmax, pz, bz, zeff=False)
+        ckk = lensing.Ckk(ref_pk, Llls)
+        return ({'gg': cgg, 'kg': ckg, 'gk': ckg, 'kk': ckk},
+                {'gg': ngg, 'kg': np.zeros_like(ckg), 'gk': np.zeros_like(ckg), 'kk': nkk})
+    Cls, Nls = allcls(T['pz_u'], T['bz'], 2181.0)
+    xCls, xNls = allcls(T['pz_int'], T['bz_int'], 2181.0 / 0.94)
+    print('interloper spectra: %.1f s' % (time.time() - t))
+    covs = interloper.get_ClsCov(Llls, Cls, Nls, fsky)
+    fid_sig8, fid_b1, LllMax = 0.819 * Dg(2.96), 3.96, 1752.6
+    fb = ofi.fisher_bias(Llls, nmodes, Cls, Nls, xCls, xNls, fsky, fid_sig8, fid_b1, LllMax,
+                         get_ClsCov=interloper.get_ClsCov, dp_DL=interloper.dp_DL)      # script body over the reference functions
+    mine = ofi.fisher_bias(Llls, nmodes, Cls, Nls, xCls, xNls, fsky, fid_sig8, fid_b1, LllMax)
+    print('fisher_bias oracle rel diff', np.max(np.abs(mine['Fisher'] / fb['Fisher'] - 1)), np.max(np.abs(mine['dtheta'] / fb['dtheta'] - 1)))
+    for name, d in (('C', Cls), ('N', Nls), ('xC', xCls), ('xN', xNls)):
+        for key in ('gg', 'kg', 'kk'):
+            out['%s_%s' % (name, key)] = d[key]
+    keys = list(Cls)
+    out['cov_keys'] = np.array([a + b for a in keys for b in keys])
+    out['cov'] = np.array([covs[a + b] for a in keys for b in keys])
+    out.update(fid_sig8=fid_sig8, fid_b1=fid_b1, LllMax=LllMax, Fisher=fb['Fisher'], iFisher=fb['iFisher'], interim=fb['interim'],
+               dtheta=fb['dtheta'])
+    # ---- snr.py ---------------------------------------------------------------------------------------------------------
+    vkg = ((Cls['kk'] + nkk) * (Cls['gg'] + Nls['gg']) + Cls['kg'] ** 2.) / ((2. * Llls + 1.) * fsky)
+    out['vkg'] = vkg
+    out['snr_all'] = snr.snr(Llls, Cls['kg'], vkg, nmodes)
+    out['snr_cut'] = snr.snr(Llls, Cls['kg'], vkg, nmodes, lmax=LllMax)
+    # ---- mqw.py: 20 shells, every integer l in [60, 5000] -----------------------------------------------------------------
+    _, Lm, _nm = prep.prep_Llls(60, 60, 5000, log10=False)
+    t = time.time()
+    zs = np.arange(2.0 + 0.05, 4.0 + 0.05, 0.1)
+    res = mqw.Fisher(ref_pk, Lm, 50., 2000., T['mqw_ps'], T['mqw_bs'], T['mqw_pp'], T['mqw_bp'], dz=0.1, fsky=0.35, zmin=2.0, zmax=4.0,
+                     fover=0.1, percentiles=list(zs))
+    print('mqw.Fisher reference: %.1f s' % (time.time() - t))
+    out['mqw_L'] = Lm
+    out['mqw_out'] = np.array([float(np.ravel(x)[0]) for x in res])
+    ub = lambda z: 1.0
+    out['mqw_cgg'] = Cgg.Cgg(ref_pk, Lm, 2.0, 4.0, T['mqw_pp'], ub, survey_pz2=T['mqw_ps'], bz2=ub, zeff=True)
+    # ---- yu.py: 3 tracers, 4 multipoles, z grid 0.01..10 --------------------------------------------------------------------
+    t = time.time()
+    Ly = Llls[::18]
+    ckk_y = lensing.Ckk(ref_pk, Ly)
+    rho, kgs, ggs, ngs = [], [], [], []
+    for ii, L in enumerate(Ly):
+        L1 = np.array([L])
+        kg = [Ckg.Ckg(ref_pk, L1, 0.01, 10.0, pz, bz, zeff=False)[0] for (bz, pz, n) in T['yu']]
+        gg = [[Cgg.Cgg(ref_pk, L1, 0.01, 10.0, pz, bz, bz2=b2, survey_pz2=p2, zeff=False)[0] for (bz, pz, n) in T['yu']] for (b2, p2, n2) in T['yu']]
+        ng = [Cgg.Ngg(L1.astype(np.float64), 0.01, 10.0, pz, n)[0] for (bz, pz, n) in T['yu']]
+        rho.append(ofi.rho_from_spectra(ckk_y[ii], kg, gg, ng))
+        kgs.append(kg); ggs.append(gg); ngs.append(ng)
+    print('yu: %.1f s' % (time.time() - t), rho)
+    out.update(yu_L=Ly, yu_ckk=ckk_y, yu_kg=np.array(kgs), yu_gg=np.array(ggs), yu_ngg=np.array(ngs), yu_rho=np.array(rho))
+    np.savez_compressed(os.path.join(GOLD, 'fisher.npz'), **out)
+
+
+def make_modi():
+    """modi/nkk.py run unmodified: N_fisher / N_fisherTE on in-memory splines, and the CMB class on CLASS-format files."""
+    import tempfile
+    from scipy.interpolate import InterpolatedUnivariateSpline as IUS
+    from lbgcmb_b200.synthetic import cmb_cl_tables, write_class_files
+    nkk = refload.load('nkk')                      # /root/reference/modi/nkk.py
+    ell, lens, nolens = cmb_cl_tables(5801)
+    eu, el = ell[2:5801], ell[2:5301]
+    u = {'TT': nolens[0, 2:5801], 'EE': nolens[1, 2:5801], 'BB': nolens[2, 2:5801], 'TE': nolens[3, 2:5801]}
+    le = {'TT': lens[0, 2:5301], 'EE': lens[1, 2:5301], 'BB': lens[2, 2:5301], 'TE': lens[3, 2:5301]}
+    thetab, delT = 1.4, 7.0
+    Ls = np.array([100., 1000., 10. ** 3.5])
+    out = {'Ls': Ls, 'thetab': thetab, 'delT': delT}
+    t = time.time()
+    for mode in ('TT', 'EE', 'EB'):
+        a1, a2 = mode[0] * 2, mode[1] * 2
+        lint = np.linspace(1., 5000. if mode in ('EB', 'EE') else 3000., 10000)
+        n1, n2 = on0.detector_noise(el, thetab, delT, a1, 2.786), on0.detector_noise(el, thetab, delT, a2, 2.786)
+        args = (IUS(eu, u[a1]), IUS(eu, u[a2]), IUS(el, le[a1] + n1), IUS(el, le[a2] + n2))
+        out['int_' + mode] = np.array([nkk.N_fisher(L, lint, *args, mode) for L in Ls])
+        mine = np.array([on0.modi_N_fisher(L, lint, *args, mode) for L in Ls])
+        print(mode, out['int_' + mode], 'oracle rel diff %.2e' % np.max(np.abs(mine / out['int_' + mode] - 1)))
+    lint = np.linspace(1., 3000., 10000)
+    n1, n2 = on0.detector_noise(el, thetab, delT, 'TT', 2.786), on0.detector_noise(el, thetab, delT, 'EE', 2.786)
+    args = (IUS(eu, u['TE']), IUS(el, le['TT'] + n1), IUS(el, le['EE'] + n2), IUS(el, le['TE']))
+    out['int_TE'] = np.array([nkk.N_fisherTE(L, lint, *args) for L in Ls])
+    mine = np.array([on0.modi_N_fisherTE(L, lint, *args) for L in Ls])
+    print('TE', out['int_TE'], 'oracle rel diff %.2e' % np.max(np.abs(mine / out['int_TE'] - 1)))
+    print('N_fisher cases: %.1f s' % (time.time() - t))
+    # the CMB container on files (modi/nkk.py:148-261), default 15-L grid
+    t = time.time()
+    d = tempfile.mkdtemp(prefix='lbgcmb_class_')
+    clf, clsf = os.path.join(d, 'cl.dat'), os.path.join(d, 'cl_lensed.dat')
+    write_class_files(clf, clsf)
+    cmb = nkk.CMB(clfile=clf, clsfile=clsf)
+    out['lat'] = cmb.lat
+    out['cmb_TT'] = cmb.do_noise('T', 'T', thetab, delT)[2]
+    out['cmb_EB'] = cmb.do_noise('E', 'B', thetab, delT)[2]
+    out['cmb_TE'] = cmb.do_noiseTE(thetab, delT)[2]
+    print('CMB class: %.1f s' % (time.time() - t), out['cmb_TT'][:3], out['cmb_EB'][:3], out['cmb_TE'][:3])
+    np.savez_compressed(os.path.join(GOLD, 'n0_modi.npz'), **out)
+
+
+MAKERS = {'n0': make_n0, 'halofit': make_halofit, 'limber': make_limber, 'fisher': make_fisher, 'modi': make_modi}
 
 if __name__ == '__main__':
     os.makedirs(GOLD, exist_ok=True)

@@ -30,6 +30,7 @@ def setup():
     from . import simps121
     here = os.path.dirname(os.path.abspath(__file__))
     sys.path[:0] = [os.path.join(here, 'shim'), REF, os.path.join(REF, 'cmb'), os.path.join(REF, 'modi')]
+    import matplotlib  # noqa: F401  (the shim registers matplotlib.pyplot and pylab)
     # python-2 / old-numpy isms used by the reference
     for name, typ in (('int', int), ('float', float)):
         if not hasattr(np, name):

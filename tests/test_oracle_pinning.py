@@ -66,3 +66,54 @@ def test_reference_modules_import_under_shim():
         pytest.skip('/root/reference not present (GPU box)')
     for m in ('Nkk', 'Cgg', 'Ckg', 'lensing', 'halofit', 'nkk', 'snr', 'prep_Llls'):
         assert refload.load(m).__file__.startswith(refload.REF)
+
+
+def test_fisher_oracle_against_reference_vectors(golden_dir):
+    """snr / get_ClsCov / Fisher + bias loop / mqw.Fisher / rho_L restatements vs what the unmodified reference produced."""
+    from oracle import fisher as ofi
+    from oracle.make_golden import fisher_tracers
+    g = _g(golden_dir, 'fisher.npz')
+    z = np.zeros_like(g['C_kg'])
+    Cls = {'gg': g['C_gg'], 'kg': g['C_kg'], 'gk': g['C_kg'], 'kk': g['C_kk']}
+    Nls = {'gg': g['N_gg'], 'kg': z, 'gk': z, 'kk': g['N_kk']}
+    xCls = {'gg': g['xC_gg'], 'kg': g['xC_kg'], 'gk': g['xC_kg'], 'kk': g['xC_kk']}
+    xNls = {'gg': g['xN_gg'], 'kg': z, 'gk': z, 'kk': g['xN_kk']}
+    L, nm, fsky = g['Llls'], g['nmodes'], float(g['fsky'])
+    assert ofi.snr(L, g['C_kg'], g['vkg'], nm) == g['snr_all']
+    assert ofi.snr(L, g['C_kg'], g['vkg'], nm, lmax=float(g['LllMax'])) == g['snr_cut']
+    cov = ofi.get_ClsCov(L, Cls, Nls, fsky)
+    for k, ref in zip(g['cov_keys'], g['cov']):
+        assert np.array_equal(cov[str(k)], ref), k
+    fb = ofi.fisher_bias(L, nm, Cls, Nls, xCls, xNls, fsky, float(g['fid_sig8']), float(g['fid_b1']), float(g['LllMax']))
+    for key in ('Fisher', 'iFisher', 'interim', 'dtheta'):
+        assert np.array_equal(fb[key], g[key]), key
+    for i in range(g['yu_L'].size):
+        assert ofi.rho_from_spectra(g['yu_ckk'][i], g['yu_kg'][i], g['yu_gg'][i], g['yu_ngg'][i]) == g['yu_rho'][i]
+    # mqw.Fisher: per-shell scalars as mqw.py:24-41, then the oracle's matrix -> the reference's percent errors
+    T = fisher_tracers()
+    zs = np.arange(2.0 + 0.05, 4.0 + 0.05, 0.1)
+    conv = lambda n: n / (np.pi / 180.) ** 2.
+    bins = []
+    for zee in zs:
+        Ns, Np = conv(50.) * T['mqw_ps'](zee) * 0.1, conv(2000.) * T['mqw_pp'](zee) * 0.1
+        bins.append([T['mqw_bp'](zee), T['mqw_bs'](zee), Np, Ns, Np, Ns, 0.1 * min(Np, Ns)])
+    bins = np.array(bins, dtype=np.float64)
+    F, Fii, S = ofi.mqw_fisher(g['mqw_cgg'], g['mqw_L'].astype(float), bins, 0.35)
+    out = np.empty(40)
+    out[0::2] = 100. * np.sqrt(1. / Fii) / bins[:, 2]
+    out[1::2] = 100. * np.sqrt(np.diag(np.linalg.inv(F))) / bins[:, 2]
+    assert np.max(np.abs(out / g['mqw_out'] - 1)) < 1e-12
+
+
+def test_modi_n0_oracle_against_reference_vector(golden_dir):
+    from scipy.interpolate import InterpolatedUnivariateSpline as IUS
+    from lbgcmb_b200.synthetic import cmb_cl_tables
+    g = _g(golden_dir, 'n0_modi.npz')
+    ell, lens, nolens = cmb_cl_tables(5801)
+    eu, el = ell[2:5801], ell[2:5301]
+    thetab, delT = float(g['thetab']), float(g['delT'])
+    n1 = on0.detector_noise(el, thetab, delT, 'TT', 2.786)
+    lint = np.linspace(1., 3000., 10000)
+    args = (IUS(eu, nolens[0, 2:5801]), IUS(eu, nolens[0, 2:5801]), IUS(el, lens[0, 2:5301] + n1), IUS(el, lens[0, 2:5301] + n1))
+    got = on0.modi_N_fisher(g['Ls'][1], lint, *args, 'TT')          # ~2 s
+    assert abs(got / g['int_TT'][1] - 1) < 1e-13
