@@ -104,6 +104,9 @@ int lbg_halofit_sigma2(lbg_ctx* ctx, int n_R, const double* R, double* out_sigma
  * {D^2, k_nl, n_eff, curvature, Omega_m(z), Omega_L(z), use_halofit (0 -> linear row, modi/cosmology.py:171), unused}. */
 int lbg_pk_build_table(lbg_ctx* ctx, int n_rows, const double* halo_z, double fnu, double om0, double w, int takahashi,
                        double* out_pnl /*[n_rows][n_k] or NULL: table stays on the device*/);
+/* Caller-supplied rows P_r(k) on their own k grid (the `kp = (k, P)` tables modi/lensing.py:127-150 interpolates): replaces
+ * the device table built by lbg_pk_build_table (call lbg_upload_pk_linear again before rebuilding one). */
+int lbg_pk_upload_rows(lbg_ctx* ctx, int n_k, const double* k, int n_rows, const double* rows /*[n_rows][n_k]*/);
 /* np.interp(x, k, P_row) : oob = 0 -> 0 outside the k range (left=right=0, modi/lensing.py:175), 1 -> clamp (:161). */
 int lbg_pk_eval(lbg_ctx* ctx, int row, int n, const double* x, int oob, double* out);
 

@@ -61,6 +61,7 @@ def _declare(L):
         'lbg_upload_pk_linear': [vp, i, c_double_p, c_double_p, c_double_p],
         'lbg_halofit_sigma2': [vp, i, c_double_p, c_double_p],
         'lbg_pk_build_table': [vp, i, c_double_p, d, d, d, i, c_double_p],
+        'lbg_pk_upload_rows': [vp, i, c_double_p, i, c_double_p],
         'lbg_pk_eval': [vp, i, i, c_double_p, i, c_double_p],
         'lbg_limber': [vp, i, i, c_double_p, i, c_double_p, c_double_p, c_int_p, i, c_double_p],
         'lbg_n0_modi': [vp, i, i, c_double_p, i, c_double_p, c_double_p, i, c_double_p, c_double_p, c_double_p,

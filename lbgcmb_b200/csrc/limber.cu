@@ -247,3 +247,22 @@ extern "C" int lbg_pk_eval(lbg_ctx* c, int row, int n, const double* x, int oob,
     LBG_CUDA(cudaMemcpyAsync(out, c->s1.p, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
     return t.finish();
 }
+
+// Caller-supplied P(k) rows on their own k grid (the `kp = (k, P)` tables of modi/lensing.py:127-167): replaces the
+// device table; a later lbg_pk_build_table needs lbg_upload_pk_linear again.
+extern "C" int lbg_pk_upload_rows(lbg_ctx* c, int n_k, const double* k, int n_rows, const double* rows) {
+    LBG_REQUIRE(c && k && rows, "lbg_pk_upload_rows: NULL argument");
+    LBG_REQUIRE(n_k >= 2 && n_k <= 6000 && n_rows > 0, "lbg_pk_upload_rows: bad sizes n_k=%d n_rows=%d (n_k <= 6000: the k grid is staged in shared memory)", n_k, n_rows);
+    for (int i = 1; i < n_k; ++i) LBG_REQUIRE(k[i] > k[i - 1], "lbg_pk_upload_rows: k must be increasing");
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    std::vector<double> buf(3 * (size_t)n_k, 0.0);
+    memcpy(buf.data(), k, (size_t)n_k * 8);
+    if (c->pk_lnk.reserve(buf.size() * 8) || c->pk_pnl.reserve((size_t)n_rows * n_k * 8)) return LBG_ENOMEM;
+    LBG_CUDA(cudaMemcpyAsync(c->pk_lnk.p, buf.data(), buf.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    LBG_CUDA(cudaMemcpyAsync(c->pk_pnl.p, rows, (size_t)n_rows * n_k * 8, cudaMemcpyHostToDevice, c->stream));
+    LBG_CUDA(cudaStreamSynchronize(c->stream));
+    c->n_k = n_k;
+    c->pnl_nz = n_rows;
+    return LBG_OK;
+}

@@ -1,0 +1,70 @@
+"""Multi-GPU plumbing: one process per GPU (torchrun), multipole / configuration sharding, and the only exchange step of
+the path -- the sum of the per-shard Fisher matrix and bias vector.
+
+`torch.distributed` is used for the rendezvous and the collective (NCCL over NVLink on GPUs; gloo in the CPU tests);
+the per-shard arithmetic is lbg_fisher_accum on each rank's own GPU.  Units (N0 per L, Limber per (pair, l)) are
+independent, so nothing else communicates."""
+import numpy as np
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist if (dist.is_available() and dist.is_initialized()) else None
+
+
+def rank_world():
+    d = _dist()
+    return (d.get_rank(), d.get_world_size()) if d else (0, 1)
+
+
+def shard_slice(n, rank=None, world=None):
+    """Contiguous block [lo, hi) of n units for this rank (sizes differ by at most one; cost per L is uniform)."""
+    if rank is None or world is None:
+        rank, world = rank_world()
+    base, extra = divmod(n, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def allreduce_sum(*arrays):
+    """Sum float64 numpy arrays over all ranks in one collective (packed); identity without a process group."""
+    d = _dist()
+    if d is None or d.get_world_size() == 1:
+        return [np.array(a, dtype=np.float64) for a in arrays]
+    import torch
+    flat = np.concatenate([np.asarray(a, dtype=np.float64).ravel() for a in arrays])
+    dev = torch.device('cuda', torch.cuda.current_device()) if d.get_backend() == 'nccl' else torch.device('cpu')
+    t = torch.from_numpy(flat).to(dev)
+    d.all_reduce(t, op=d.ReduceOp.SUM)
+    flat = t.cpu().numpy()
+    out, o = [], 0
+    for a in arrays:
+        a = np.asarray(a)
+        out.append(flat[o:o + a.size].reshape(a.shape).copy())
+        o += a.size
+    return out
+
+
+def allgather_concat(local):
+    """Concatenate each rank's 1-d float64 slice in rank order (per-L N0 / C_l curves when every rank needs the whole)."""
+    d = _dist()
+    local = np.ascontiguousarray(local, dtype=np.float64)
+    if d is None or d.get_world_size() == 1:
+        return local.copy()
+    parts = [None] * d.get_world_size()
+    d.all_gather_object(parts, local)
+    return np.concatenate(parts)
+
+
+def fisher_accum_sharded(cov, dD, mode_weight, dDelta=None, accum=None):
+    """interloper.py:223-253 with the multipoles sharded over ranks: every rank passes the FULL arrays, evaluates its own
+    block on its GPU and receives the all-reduced (F, b).  `accum` replaces the device call in the CPU (gloo) tests."""
+    if accum is None:
+        from lbgcmb_b200.fisher import fisher_accum as accum
+    lo, hi = shard_slice(len(mode_weight))
+    F, b = accum(np.asarray(cov)[lo:hi], np.asarray(dD)[lo:hi], np.asarray(mode_weight)[lo:hi],
+                 dDelta=None if dDelta is None else np.asarray(dDelta)[lo:hi])
+    if b is None:
+        return allreduce_sum(F)[0], None
+    F, b = allreduce_sum(F, b)
+    return F, b

@@ -1,8 +1,8 @@
 """Background + P(k,z); mirrors reference modi/cosmology.py:17-194 (`Cosmology`).
 
 Host side (as in the reference): E(a), chi(a) by `quad` (:134-150), un-normalised D+ on 1000 ln a nodes + cubic spline
-(:92-117; the reference integrates with scipy's since-removed `romberg`, tol 1.48e-8 -- `quad` is used here, so D+ agrees
-with the reference to its own Romberg tolerance, not to 1e-10; D+ is an *input* to both the CUDA path and the oracle).
+(:92-117; the reference integrates with scipy-1.2.1 `romberg`, since removed from scipy and restated in
+lbgcmb_b200/quadrature.py, so D+ matches the reference's own value rather than the exact integral).
 Device side (csrc/limber.cu): pkalin / pkanlin rows for any number of redshifts at once (`pk_rows`), HALOFIT included.
 """
 import numpy as np
@@ -12,7 +12,7 @@ from scipy.interpolate import InterpolatedUnivariateSpline as interpolate
 from lbgcmb_b200 import _ffi
 from lbgcmb_b200.cosmo import FlatLambdaCDM
 from lbgcmb_b200.modi import halofit as _hf
-from lbgcmb_b200.quadrature import simps_weights_x
+from lbgcmb_b200.quadrature import simps_weights_x, romberg
 
 _owner = _ffi.table_owner
 
@@ -68,16 +68,14 @@ class Cosmology(object):
         return self.H0 * self.Ea(a=a)
 
     def _eval_Dplus(self):
+        """Un-normalised D(a) on 1000 ln a nodes: Romberg from ln a = -20 to each node (modi/cosmology.py:92-111)."""
         logx = np.linspace(-20., 0, 1000)
         x = np.exp(logx)
 
         def kernel(loga):
             a = np.exp(loga)
             return (a * self.Ea(a=a)) ** -3. * a
-        # cumulative integral node to node (each piece is smooth; quad reaches ~1e-14)
-        pieces = np.array([quad(kernel, logx[i], logx[i + 1], epsabs=0, epsrel=1e-13)[0] for i in range(logx.size - 1)])
-        cum = np.concatenate([[0.0], np.cumsum(pieces)])
-        y = self.Ea(a=x) * cum
+        y = self.Ea(a=x) * np.array([romberg(kernel, logx.min(), loga) for loga in logx])
         return interpolate(x, y)
 
     def Dgrow(self, z=None, a=None):
@@ -178,6 +176,24 @@ class Cosmology(object):
             raise ValueError('zs, chis and weights disagree in length')
         out = np.empty((w.shape[0], ells.size))
         _ffi.check(_ffi.lib().lbg_limber(ctx.handle, w.shape[0], ells.size, _ffi._dp(ells), zs.size, _ffi._dp(chis), _ffi._dp(w),
+                                         prow.ctypes.data_as(_ffi.c_int_p), int(oob), _ffi._dp(out)))
+        return out
+
+    def limber_rows(self, ells, chis, weights, k, rows, prow, oob=1):
+        """Limber sum over caller-supplied rows P_r(k) (modi/lensing.py `kp` tables); replaces the device table."""
+        ctx = _ffi.context(self.device)
+        k, rows = _ffi.f64(k), _ffi.f64(np.atleast_2d(rows))
+        if rows.shape[1] != k.size:
+            raise ValueError('k and P disagree in length')
+        _ffi.check(_ffi.lib().lbg_pk_upload_rows(ctx.handle, k.size, _ffi._dp(k), rows.shape[0], _ffi._dp(rows)))
+        _owner[ctx.device] = None                              # the linear table must be uploaded again before HALOFIT rows
+        self._rows_key = None
+        ells, chis, w = _ffi.f64(np.atleast_1d(ells)), _ffi.f64(np.atleast_1d(chis)), _ffi.f64(np.atleast_2d(weights))
+        prow = np.ascontiguousarray(prow, dtype=np.int32)
+        if w.shape[1] != chis.size or prow.size != chis.size:
+            raise ValueError('chis, weights and prow disagree in length')
+        out = np.empty((w.shape[0], ells.size))
+        _ffi.check(_ffi.lib().lbg_limber(ctx.handle, w.shape[0], ells.size, _ffi._dp(ells), chis.size, _ffi._dp(chis), _ffi._dp(w),
                                          prow.ctypes.data_as(_ffi.c_int_p), int(oob), _ffi._dp(out)))
         return out
 

@@ -65,3 +65,28 @@ def trapz_weights_x(x):
     w[:-1] += 0.5 * h
     w[1:] += 0.5 * h
     return w
+
+
+def romberg(f, a, b, tol=1.48e-8, rtol=1.48e-8, divmax=10):
+    """scipy-1.2.1 `romberg(f, a, b, vec_func=True)` for a vectorised integrand: the rule the reference's growth factor is
+    built with (modi/cosmology.py:107; removed from scipy >= 1.15).  Host-side helper, <= 1025 ordinates per call."""
+    span = b - a
+    acc = 0.5 * (f(a) + f(b))
+    prev = [span * acc]
+    out = prev[0]
+    panels = 1
+    for level in range(1, divmax + 1):
+        panels *= 2
+        half = panels / 2
+        h = float(b - a) / half
+        acc = acc + np.sum(f((a + 0.5 * h) + h * np.arange(half)), axis=0)
+        cur = [span * acc / panels]
+        for k in range(level):
+            p4 = 4.0 ** (k + 1)
+            cur.append((p4 * cur[k] - prev[k]) / (p4 - 1.0))
+        out = cur[level]
+        err = abs(out - prev[level - 1])
+        if err < tol or err < rtol * abs(out):
+            break
+        prev = cur
+    return out

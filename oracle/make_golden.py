@@ -242,7 +242,44 @@ def make_modi():
     np.savez_compressed(os.path.join(GOLD, 'n0_modi.npz'), **out)
 
 
-MAKERS = {'n0': make_n0, 'halofit': make_halofit, 'limber': make_limber, 'fisher': make_fisher, 'modi': make_modi}
+def make_modi_lensing():
+    """modi/cosmology.py + modi/lensing.py run unmodified (refload.load_modi): LensingX at z = 1 with an LSST-like dN/dz."""
+    from . import modi_lensing as oml
+    from lbgcmb_b200.synthetic import eh_like_plin, PARAMS
+    cos, lens = refload.load_modi()
+    k, p = eh_like_plin()
+    c = cos.Cosmology(M=PARAMS['om_m'], B=PARAMS['om_b'], sig8=PARAMS['sig_8'], klin=k, plin=p)
+    oc = oml.ModiCosmology(M=PARAMS['om_m'], B=PARAMS['om_b'], sig8=PARAMS['sig_8'], klin=k, plin=p)
+    dndz = lambda z: z ** 2. * np.exp(-(z / 0.5) ** 1.0)
+    dndz2 = lambda z: z ** 1.5 * np.exp(-(z / 0.4) ** 1.2)
+    bz = lambda z: 1.438 + 0. * z                              # tools.BiasZ(cosmo).const(b = 1.438), modi/lensing.py:212
+    ell = np.logspace(1, 3.47, 120)
+    out = {'k': k, 'plin': p, 'l': ell, 'z': 1.0}
+    res = {}
+    for name, C, LX in (('ref', c, lens.LensingX), ('ora', oc, oml.LensingX)):
+        t = time.time()
+        mmz = lambda z: [k, C.pkanlin(z=z)[1]]
+        hmz = lambda z: [k, C.pkanlin(z=z)[1] * bz(z)]
+        hhz = lambda z: [k, C.pkanlin(z=z)[1] * bz(z) ** 2.]
+        lx = LX(z=1.0, dndz=dndz, cosmo=C, l=ell)
+        r = {'clkkz': lx.cl_kkz(mmz), 'clggz': lx.clz(hhz, auto=True), 'clkgz': lx.clz(hmz, auto=False),
+             'clggzeff': lx.cl_zeff(hhz(1.0), auto=True), 'clkgzeff': lx.cl_zeff(hmz(1.0), auto=False),
+             'clbitracer': lx.cl_zeff_bitracer(hhz(1.0), dndz2),
+             'kerg': lx.kerg, 'kercmb': lx.kercmb, 'dggwtsdN': lx.dggwtsdN, 'dkgwtsdN': lx.dkgwtsdN, 'kkwts': lx.kkwts,
+             'chis': lx.chis, 'norm': lx.norm}
+        res[name] = r
+        print(name, 'LensingX: %.1f s' % (time.time() - t))
+    for key in res['ref']:
+        print(key, 'oracle rel diff %.2e' % np.max(np.abs(np.asarray(res['ora'][key]) / np.asarray(res['ref'][key]) - 1)))
+    zchk = np.array([0.0, 0.5, 1.0, 2.0, 4.0, 10.0, 1100.0])
+    out.update(res['ref'])
+    out.update(zchk=zchk, Dchk=np.array([c.Dgrow(z=z) for z in zchk]), chichk=np.array([c.chia(z=z) for z in zchk]),
+               pknl_z1=c.pkanlin(z=1.0)[1], pklin_z5=c.pkanlin(z=5.0)[1])
+    np.savez_compressed(os.path.join(GOLD, 'modi_lensing.npz'), **out)
+
+
+MAKERS = {'n0': make_n0, 'halofit': make_halofit, 'limber': make_limber, 'fisher': make_fisher, 'modi': make_modi,
+          'modi_lensing': make_modi_lensing}
 
 if __name__ == '__main__':
     os.makedirs(GOLD, exist_ok=True)

@@ -27,7 +27,7 @@ def setup():
         raise RuntimeError('reference tree not present at %s' % REF)
     import numpy as np
     import scipy.integrate
-    from . import simps121
+    from . import simps121, romberg121
     here = os.path.dirname(os.path.abspath(__file__))
     sys.path[:0] = [os.path.join(here, 'shim'), REF, os.path.join(REF, 'cmb'), os.path.join(REF, 'modi')]
     import matplotlib  # noqa: F401  (the shim registers matplotlib.pyplot and pylab)
@@ -40,6 +40,8 @@ def setup():
     builtins.reduce = functools.reduce
     # scipy 1.2.1 simps -- NOT scipy.integrate.simpson
     scipy.integrate.simps = simps121.simps
+    # scipy 1.2.1 romberg (modi/cosmology.py:6,107); removed from scipy >= 1.15
+    scipy.integrate.romberg = romberg121.romberg
     os.environ.setdefault('LBGCMB', tempfile.mkdtemp(prefix='lbgcmb_scratch_'))
     _done = True
 
@@ -49,3 +51,32 @@ def load(name):
     setup()
     import importlib
     return importlib.import_module(name)
+
+
+def load_modi():
+    """(cosmology, lensing): the reference's modi/cosmology.py and modi/lensing.py, loaded from where they lie.
+
+    They import their siblings under `modi_*` names that exist nowhere in the tree (modi/cosmology.py:10-11,
+    modi/lensing.py:6-9) and modi/lensing.py carries two python-2 print statements (:83, :294): the aliases are registered
+    here and the two statements are parenthesised IN MEMORY before compiling -- nothing is copied or written."""
+    setup()
+    import re
+    import types
+    if 'modi_lensing_ref' in sys.modules:
+        return sys.modules['modi_cosmology'], sys.modules['modi_lensing_ref']
+    sys.modules['modi_halofit'] = load('halofit')
+    for stub in ('modi_tools', 'modi_pk_pregen'):            # circular helper imports; unused by Cosmology / LensingX
+        sys.modules.setdefault(stub, types.ModuleType(stub))
+    def exec_file(modname, path, fix=None):
+        src = open(path).read()
+        if fix:
+            src = fix(src)
+        mod = types.ModuleType(modname)
+        mod.__file__ = path
+        sys.modules[modname] = mod
+        exec(compile(src, path, 'exec'), mod.__dict__)
+        return mod
+    cosmology = exec_file('modi_cosmology', os.path.join(REF, 'modi', 'cosmology.py'))
+    py3 = lambda src: re.sub(r'^(\s*)print (.+)$', lambda m: '%sprint(%s)' % (m.group(1), m.group(2)), src, flags=re.M)
+    lensing = exec_file('modi_lensing_ref', os.path.join(REF, 'modi', 'lensing.py'), fix=py3)
+    return cosmology, lensing

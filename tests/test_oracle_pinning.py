@@ -117,3 +117,35 @@ def test_modi_n0_oracle_against_reference_vector(golden_dir):
     args = (IUS(eu, nolens[0, 2:5801]), IUS(eu, nolens[0, 2:5801]), IUS(el, lens[0, 2:5301] + n1), IUS(el, lens[0, 2:5301] + n1))
     got = on0.modi_N_fisher(g['Ls'][1], lint, *args, 'TT')          # ~2 s
     assert abs(got / g['int_TT'][1] - 1) < 1e-13
+
+
+def test_modi_lensing_oracle_against_reference_vectors(golden_dir):
+    """ModiCosmology + LensingX restatements vs the reference's own modi/cosmology.py + modi/lensing.py outputs
+    (the z-resolved clz cases take 200 HALOFIT calls and are pinned by oracle/make_golden.py, which prints 0.0 for them)."""
+    from oracle import modi_lensing as oml
+    from lbgcmb_b200.synthetic import PARAMS
+    g = _g(golden_dir, 'modi_lensing.npz')
+    c = oml.ModiCosmology(M=PARAMS['om_m'], B=PARAMS['om_b'], sig8=PARAMS['sig_8'], klin=g['k'], plin=g['plin'])
+    assert np.array_equal([c.Dgrow(z=z) for z in g['zchk']], g['Dchk'])
+    assert np.array_equal([c.chia(z=z) for z in g['zchk']], g['chichk'])
+    assert np.array_equal(c.pkanlin(z=1.0)[1], g['pknl_z1'])
+    dndz = lambda z: z ** 2. * np.exp(-(z / 0.5) ** 1.0)
+    dndz2 = lambda z: z ** 1.5 * np.exp(-(z / 0.4) ** 1.2)
+    lx = oml.LensingX(z=1.0, dndz=dndz, cosmo=c, l=g['l'])
+    hh = [g['k'], g['pknl_z1'] * 1.438 ** 2.]
+    hm = [g['k'], g['pknl_z1'] * 1.438]
+    assert np.array_equal(lx.cl_zeff(hh, auto=True), g['clggzeff'])
+    assert np.array_equal(lx.cl_zeff(hm, auto=False), g['clkgzeff'])
+    assert np.array_equal(lx.cl_zeff_bitracer(hh, dndz2), g['clbitracer'])
+    assert np.array_equal(lx.cl_kkz(lambda z: [g['k'], c.pkanlin(z=z)[1]]), g['clkkz'])
+    for name in ('kerg', 'kercmb', 'dggwtsdN', 'dkgwtsdN', 'chis'):
+        assert np.array_equal(getattr(lx, name), g[name]), name
+
+
+def test_romberg_restatements_agree():
+    from oracle.romberg121 import romberg as r1
+    from lbgcmb_b200.quadrature import romberg as r2
+    f = lambda x: np.exp(-x * x) * np.cos(3 * x)
+    for a, b in ((0., 1.), (-20., 0.), (0., 0.), (-2., 5.)):
+        assert r1(f, a, b, vec_func=True) == r2(f, a, b)
+    assert abs(r2(lambda x: x ** 3, 0., 2.) - 4.0) < 1e-13        # exact after one Richardson step
