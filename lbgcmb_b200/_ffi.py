@@ -6,7 +6,7 @@ import threading
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'liblbgcmb.so')
+LIB_PATH = os.environ.get('LBGCMB_LIB') or os.path.join(_HERE, 'liblbgcmb.so')   # override: kernel experiments only
 
 _lib = None
 _lock = threading.Lock()

@@ -67,8 +67,10 @@ struct lbg_ctx {
     // CMB tables
     int          n_ell = 0;          // knots 0..n_ell-1
     lbg::DevBuf  cl_rows;            // ClRow[n_ell + 2], row r holds coefficient index r-1
+    lbg::DevBuf  cl_soa;             // the same coefficients spectrum-major: double[8][cl_soa_stride]
+    int          cl_soa_stride = 0;
     // N0 workspaces
-    lbg::DevBuf  n0_L, n0_utab, n0_phi, n0_partial, n0_out, n0_rowflag;
+    lbg::DevBuf  n0_L, n0_utab, n0_phi, n0_partial, n0_out, n0_rowflag, n0_G;
     // generic scratch
     lbg::DevBuf  s0, s1, s2, s3, s4, s5;
     // P(k) / Limber state (see limber.cu)

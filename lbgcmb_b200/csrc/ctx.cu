@@ -109,7 +109,7 @@ extern "C" int lbg_ctx_destroy(lbg_ctx* c) {
     if (!c) return LBG_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (DevBuf* b : {&c->cl_rows, &c->n0_L, &c->n0_utab, &c->n0_phi, &c->n0_partial, &c->n0_out, &c->n0_rowflag,
+    for (DevBuf* b : {&c->cl_rows, &c->cl_soa, &c->n0_L, &c->n0_utab, &c->n0_phi, &c->n0_partial, &c->n0_out, &c->n0_rowflag, &c->n0_G,
                       &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->pk_lnk, &c->pk_plin, &c->pk_pnl})
         b->release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
@@ -162,8 +162,15 @@ extern "C" int lbg_upload_cl_tables(lbg_ctx* c, int n_ell, const double* lensed,
             for (int r = 0; r < n_ell + 2; ++r) reinterpret_cast<double*>(&rows[r])[which * 4 + col] = coef[r];
         }
     }
-    if (c->cl_rows.reserve(rows.size() * sizeof(ClRow))) return LBG_ENOMEM;
+    // spectrum-major copy for the N0 main kernel: neighbouring lanes (neighbouring |v|) then read neighbouring doubles
+    const int stride = (n_ell + 2 + 15) & ~15;
+    std::vector<double> soa((size_t)8 * stride, 0.0);
+    for (int r = 0; r < n_ell + 2; ++r)
+        for (int k = 0; k < 8; ++k) soa[(size_t)k * stride + r] = reinterpret_cast<const double*>(&rows[r])[k];
+    if (c->cl_rows.reserve(rows.size() * sizeof(ClRow)) || c->cl_soa.reserve(soa.size() * 8)) return LBG_ENOMEM;
     LBG_CUDA(cudaMemcpyAsync(c->cl_rows.p, rows.data(), rows.size() * sizeof(ClRow), cudaMemcpyHostToDevice, c->stream));
+    LBG_CUDA(cudaMemcpyAsync(c->cl_soa.p, soa.data(), soa.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    c->cl_soa_stride = stride;
     LBG_CUDA(cudaStreamSynchronize(c->stream));
     c->n_ell = n_ell;
     return LBG_OK;

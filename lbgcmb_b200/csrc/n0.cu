@@ -23,6 +23,7 @@ struct __align__(128) URow {
 
 struct N0Params {
     int n_L, n_phi, n_l1, n_chunk, rows_per_chunk, n_ell;
+    int soa_stride;               // > 0: `rows` of n0_node is the spectrum-major table double[8][soa_stride]
     unsigned terms;
     double nT, nP, a;             // N_TT(l) = nT exp(a l (l+1)), N_EE = N_BB = nP exp(.)  (cmb/DetectorNoise.py:22-26)
     double lmax_T, lmax_P, lmin_v;
@@ -78,6 +79,7 @@ struct UVals { double uT, uX, uE, uB, T1, E1, X1, rT1h, rE1h, rE1, rB1h; };
 
 // One integrand node (cmb/Nkk.py:66-162) for |u| = l at angle (c, s) = (cos phi, sin phi) and lensing multipole L.
 // actT / actP: the |u| side of prep_lmaxmask (cmb/Nkk.py:17,20) for the 3000 / 5000 families; wl = weight * l.
+template <bool SOA = false>
 __device__ __forceinline__ void n0_node(const N0Params& P, const ClRow* __restrict__ rows, double L, double l, double c, double s,
                                         const UVals& u, bool actT, bool actP, double wl, bool mirror, double cm, double sm_, double fj,
                                         double& aTT, double& aTE, double& aEE, double& aEB, double& aBB) {
@@ -126,19 +128,29 @@ __device__ __forceinline__ void n0_node(const N0Params& P, const ClRow* __restri
     double w0, w1, w2, w3;
     bspline_weights(nv - (double)i, w0, w1, w2, w3);
     if (nv > (double)(P.n_ell - 1)) { w0 = w1 = w2 = w3 = 0.0; }
-    const double4* rp = reinterpret_cast<const double4*>(rows + i);
-    double4 A = ld4(rp), B = ld4(rp + 1);
-    double vT = w0 * A.x, vX = w0 * A.y, vE = w0 * A.z, vB = w0 * A.w;
-    double T2 = w0 * B.x, X2 = w0 * B.y, E2 = w0 * B.z, B2 = w0 * B.w;
-    A = ld4(rp + 2); B = ld4(rp + 3);
-    vT = fma(w1, A.x, vT); vX = fma(w1, A.y, vX); vE = fma(w1, A.z, vE); vB = fma(w1, A.w, vB);
-    T2 = fma(w1, B.x, T2); X2 = fma(w1, B.y, X2); E2 = fma(w1, B.z, E2); B2 = fma(w1, B.w, B2);
-    A = ld4(rp + 4); B = ld4(rp + 5);
-    vT = fma(w2, A.x, vT); vX = fma(w2, A.y, vX); vE = fma(w2, A.z, vE); vB = fma(w2, A.w, vB);
-    T2 = fma(w2, B.x, T2); X2 = fma(w2, B.y, X2); E2 = fma(w2, B.z, E2); B2 = fma(w2, B.w, B2);
-    A = ld4(rp + 6); B = ld4(rp + 7);
-    vT = fma(w3, A.x, vT); vX = fma(w3, A.y, vX); vE = fma(w3, A.z, vE); vB = fma(w3, A.w, vB);
-    T2 = fma(w3, B.x, T2); X2 = fma(w3, B.y, X2); E2 = fma(w3, B.z, E2); B2 = fma(w3, B.w, B2);
+    double vT, vX, vE, vB, T2, X2, E2, B2;
+    if (SOA) {
+        const double* q = reinterpret_cast<const double*>(rows) + i;
+        const size_t st = (size_t)P.soa_stride;
+#define LBG_SPL(k) fma(w3, __ldg(q + (k) * st + 3), fma(w2, __ldg(q + (k) * st + 2), fma(w1, __ldg(q + (k) * st + 1), w0 * __ldg(q + (k) * st))))
+        vT = LBG_SPL(0); vX = LBG_SPL(1); vE = LBG_SPL(2); vB = LBG_SPL(3);
+        T2 = LBG_SPL(4); X2 = LBG_SPL(5); E2 = LBG_SPL(6); B2 = LBG_SPL(7);
+#undef LBG_SPL
+    } else {
+        const double4* rp = reinterpret_cast<const double4*>(rows + i);
+        double4 A = ld4(rp), B = ld4(rp + 1);
+        vT = w0 * A.x; vX = w0 * A.y; vE = w0 * A.z; vB = w0 * A.w;
+        T2 = w0 * B.x; X2 = w0 * B.y; E2 = w0 * B.z; B2 = w0 * B.w;
+        A = ld4(rp + 2); B = ld4(rp + 3);
+        vT = fma(w1, A.x, vT); vX = fma(w1, A.y, vX); vE = fma(w1, A.z, vE); vB = fma(w1, A.w, vB);
+        T2 = fma(w1, B.x, T2); X2 = fma(w1, B.y, X2); E2 = fma(w1, B.z, E2); B2 = fma(w1, B.w, B2);
+        A = ld4(rp + 4); B = ld4(rp + 5);
+        vT = fma(w2, A.x, vT); vX = fma(w2, A.y, vX); vE = fma(w2, A.z, vE); vB = fma(w2, A.w, vB);
+        T2 = fma(w2, B.x, T2); X2 = fma(w2, B.y, X2); E2 = fma(w2, B.z, E2); B2 = fma(w2, B.w, B2);
+        A = ld4(rp + 6); B = ld4(rp + 7);
+        vT = fma(w3, A.x, vT); vX = fma(w3, A.y, vX); vE = fma(w3, A.z, vE); vB = fma(w3, A.w, vB);
+        T2 = fma(w3, B.x, T2); X2 = fma(w3, B.y, X2); E2 = fma(w3, B.z, E2); B2 = fma(w3, B.w, B2);
+    }
     // detector noise at |v| (cmb/DetectorNoise.py:22-26)
     const double en = exp(nv * (nv + 1.0) * P.a);
     T2 = fma(P.nT, en, T2);
@@ -214,6 +226,299 @@ n0_kernel(N0Params P, const double* __restrict__ Ls, const double* __restrict__ 
         partial[2 * stride + o] = aEE * wphi;
         partial[3 * stride + o] = aEB * wphi;
         partial[4 * stride + o] = aBB * wphi;
+    }
+}
+
+// ---- "rows" variant: thread <-> one l1 row (consecutive lanes = consecutive |u|), loop over the phi nodes ------------
+// The u-side values live in registers for the whole phi loop (no u-row traffic), cos/sin/weights of the phi nodes come
+// from constant memory through the uniform datapath, and the four B-spline rows a warp gathers at |v| lie within a few
+// cache lines because |v| moves by at most 0.5 between neighbouring lanes.
+#define LBG_MAX_PHI_CONST 1024
+__constant__ double c_phi[6 * LBG_MAX_PHI_CONST];   // [6][n_phi]: cos, sin, w, cos_m, sin_m, frac_j
+
+#ifndef LBG_ROWS_MINB
+#define LBG_ROWS_MINB 4
+#endif
+__global__ void __launch_bounds__(128, LBG_ROWS_MINB)
+n0_rows_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const ClRow* __restrict__ rows,
+               double* __restrict__ partial /*[5][n_L][n_rb]*/) {
+    __shared__ double red[5][4];
+    const int r = blockIdx.x * 128 + threadIdx.x;
+    const int iL = blockIdx.y, n_rb = gridDim.x;
+    const double L = Ls[iL];
+    const bool fold = P.fold != 0;
+    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
+    int fl = 0;
+    double l = 1.0, wl = 0.0;
+    UVals u = {};
+    if (r < P.n_l1) {
+        const double4* up = reinterpret_cast<const double4*>(utab + r);
+        const double4 q0 = ld4(up), q1 = ld4(up + 1), q2 = ld4(up + 2), q3 = ld4(up + 3);
+        fl = (int)q3.y;
+        l = q0.x; wl = q0.y;
+        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
+        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
+    }
+    if ((fl & 5) && !(fl & 16)) {
+        const bool actT = fl & 1, actP = fl & 4;
+        for (int j = 0; j < P.n_phi; ++j) {
+            const double c = c_phi[j], s = c_phi[P.n_phi + j], wj = c_phi[2 * P.n_phi + j];
+            const double cm = c_phi[3 * P.n_phi + j], sm_ = c_phi[4 * P.n_phi + j], fj = c_phi[5 * P.n_phi + j];
+            n0_node<true>(P, rows, L, l, c, s, u, actT, actP, wj, fold, cm, sm_, fj, aTT, aTE, aEE, aEB, aBB);
+        }
+    }
+    double acc[5] = {aTT * wl, aTE * wl, aEE * wl, aEB * wl, aBB * wl};
+#pragma unroll
+    for (int t = 0; t < 5; ++t) {
+        double v = acc[t];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) red[t][threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 5) {
+        const int t = threadIdx.x;
+        const double v = (red[t][0] + red[t][1]) + (red[t][2] + red[t][3]);
+        partial[((size_t)t * P.n_L + iL) * n_rb + blockIdx.x] = v;
+    }
+}
+
+// One block per L: fixed-order sum of the row-block partials (+ the special rows), then cmb/Nkk.py:169-172.
+__global__ void __launch_bounds__(128)
+n0_rows_reduce_kernel(N0Params P, int n_rb, const double* __restrict__ Ls, const double* __restrict__ partial,
+                      const double* __restrict__ spartial, int n_phi_full, double* __restrict__ out) {
+    __shared__ double sm[5][128];
+    const int iL = blockIdx.x;
+    double acc[5] = {0, 0, 0, 0, 0};
+    for (int b = threadIdx.x; b < n_rb; b += 128) {
+#pragma unroll
+        for (int t = 0; t < 5; ++t) acc[t] += partial[((size_t)t * P.n_L + iL) * n_rb + b];
+    }
+    if (spartial) {
+        const size_t sstride = (size_t)P.n_L * n_phi_full;
+        for (int j = threadIdx.x; j < n_phi_full; j += 128) {
+#pragma unroll
+            for (int t = 0; t < 5; ++t) acc[t] += spartial[t * sstride + (size_t)iL * n_phi_full + j];
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < 5; ++t) sm[t][threadIdx.x] = acc[t];
+    __syncthreads();
+    for (int h = 64; h > 0; h >>= 1) {
+        if (threadIdx.x < h) {
+#pragma unroll
+            for (int t = 0; t < 5; ++t) sm[t][threadIdx.x] += sm[t][threadIdx.x + h];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double L = Ls[iL];
+        double tot = (((sm[0][0] + sm[1][0]) + sm[2][0]) + P.ebfac * sm[3][0]) + sm[4][0];
+        const double twopi = 2.0 * 3.14159265358979323846;
+        double r = tot / (twopi * twopi);
+        r = 1.0 / r;
+        const double pre = L * (L + 1.0) / 2.0;
+        out[iL] = r * (pre * pre);
+        for (int t = 0; t < 5; ++t) out[(size_t)(t + 1) * P.n_L + iL] = sm[t][0];
+    }
+}
+
+// ---- "rows2" variant: the rows decomposition with a restructured node ----------------------------------------------
+// Same integrand, arranged for the FP64 pipe (the limiter once the table gathers are coalesced):
+//  * |v|^2 = l (l - 2 L cos) + L^2 by two FMAs; one rsqrt yields both |v| and 1/|v|^2 (the cos 2phi_uv / sin^2 2phi_uv
+//    denominators are |u|^2 |v|^2);  L.u, L.v, u.v, u x v come from per-(L, phi) products staged in shared memory;
+//  * the four filter denominators (C^TT_tot(v), TE determinant, C^EE_tot(v), C^BB_tot(v)) share ONE reciprocal;
+//  * detector noise at |v| = G[i] exp(a t (2 i + 1 + t)) with G[i] = exp(a i (i + 1)) tabulated per knot and a degree-7
+//    Taylor polynomial in the small remainder (|x| < 0.03, checked on the host; otherwise exp() is called);
+//  * masks are integer tests on the high word of |v|^2.  A node whose |v|^2 lies within 4e-6 of a cut is left to a second
+//    pass that evaluates it with the bit-faithful n0_node (the reference decides those masks on its own rounding).
+// Blocks whose rows all lie above lmax_T skip the temperature estimators and their four splines (DO_T = false).
+struct PhiNode { double A, B, C, w; };     // 2 L cos phi, L cos phi, L sin phi, quadrature weight
+
+__device__ __forceinline__ double rsqrt_fast(double x) {       // MUFU.RSQ64H seed + one third-order step: ~1 ulp, x normal > 0
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double e = fma(-(x * y), y, 1.0);
+    const double p = fma(0.375, e, 0.5) * e;
+    return fma(y, p, y);
+}
+
+__device__ __forceinline__ double rcp_fast(double x) {         // MUFU.RCP64H seed + one third-order step, x normal
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double e = fma(-x, y, 1.0);
+    const double q = fma(e, e, e);
+    return fma(y, q, y);
+}
+
+template <bool DO_T, bool EXPN>
+__device__ __forceinline__ void n0_fast_node(const N0Params& P, const double* __restrict__ tab, const double* __restrict__ G,
+                                             double L2, double l, double l2, double rl2, const UVals& u, bool actT, bool actP,
+                                             const PhiNode ph, double& aTT, double& aTE, double& aEE, double& aEB) {
+    const double nv2 = fma(l, l - ph.A, L2);
+    const unsigned hi = (unsigned)__double2hiint(nv2);
+    const bool rare = (hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2];
+    const bool vok = !rare && hi > P.near_lo[0];
+    const bool okT = DO_T && actT && vok && hi < P.near_lo[1];
+    const bool okP = actP && vok && hi < P.near_lo[2];
+    if (!__any_sync(0xffffffffu, okT || okP)) return;
+
+    const double y = rsqrt_fast(fmax(nv2, 1e-300));
+    const double nv = nv2 * y;
+    const double dLu = l * ph.B, dLv = L2 - dLu;           // L.u, L.v
+    const double dot = dLu - l2, crs = l * ph.C;           // u.v, |u x v|
+    const double d2 = dot * dot, x2 = crs * crs;
+    const double rden = rl2 * (y * y);                     // 1 / (|u|^2 |v|^2)
+    const double c2 = (d2 - x2) * rden;
+    const double s2sq = fma(-c2, c2, 1.0);
+
+    int i = min((int)nv, P.n_ell - 2);
+    const double fi = (double)i;
+    const double t = nv - fi, um = 1.0 - t;
+    const double t2 = t * t, u2 = um * um;
+    const double w0 = (u2 * (1.0 / 6.0)) * um, w3 = (t2 * (1.0 / 6.0)) * t;
+    const double w1 = fma(t2, fma(0.5, t, -1.0), 2.0 / 3.0), w2 = fma(u2, fma(0.5, um, -1.0), 2.0 / 3.0);
+    const double* q = tab + i;
+    const size_t st = (size_t)P.soa_stride;
+#define LBG_SPL(k) fma(w3, __ldg(q + (k) * st + 3), fma(w2, __ldg(q + (k) * st + 2), fma(w1, __ldg(q + (k) * st + 1), w0 * __ldg(q + (k) * st))))
+    double vT = 0.0, vX = 0.0, T2 = 1.0, X2 = 0.0;
+    if (DO_T) { vT = LBG_SPL(0); vX = LBG_SPL(1); T2 = LBG_SPL(4); X2 = LBG_SPL(5); }
+    const double vE = LBG_SPL(2), vB = LBG_SPL(3);
+    double E2 = LBG_SPL(6), B2 = LBG_SPL(7);
+#undef LBG_SPL
+    double en;
+    if (EXPN) {
+        en = exp((nv2 + nv) * P.a);
+    } else {
+        const double x = (P.a * t) * fma(2.0, fi, 1.0 + t);
+        double pl = fma(x, 1.0 / 5040.0, 1.0 / 720.0);
+        pl = fma(pl, x, 1.0 / 120.0); pl = fma(pl, x, 1.0 / 24.0); pl = fma(pl, x, 1.0 / 6.0);
+        pl = fma(pl, x, 0.5); pl = fma(pl, x, 1.0); pl = fma(pl, x, 1.0);
+        en = __ldg(G + i) * pl;
+    }
+    if (DO_T) T2 = fma(P.nT, en, T2);
+    E2 = fma(P.nP, en, E2);
+    B2 = fma(P.nP, en, B2);
+
+    // one reciprocal for the four filter denominators
+    double E1T2 = 1.0, xx = 0.0, den = 1.0;
+    if (DO_T) {
+        E1T2 = u.E1 * T2; xx = u.X1 * X2;
+        den = fma(u.T1 * E2, E1T2, -(xx * xx));
+        if (!(P.terms & LBG_TE)) den = 1.0;
+        if (!(P.terms & LBG_TT)) T2 = 1.0;
+    }
+    if (!(P.terms & LBG_EB)) B2 = 1.0;
+    const double p1 = DO_T ? T2 * den : 1.0, p2 = E2 * B2;
+    const double r = rcp_fast(DO_T ? p1 * p2 : p2);
+    const double r34 = DO_T ? r * p1 : r;                  // 1 / (E2 B2)
+    const double rE2 = r34 * B2, rB2 = r34 * E2;
+    const double uEd = u.uE * dLu;
+    if (DO_T) {
+        const double r12 = r * p2;                         // 1 / (T2 den)
+        const double rT2 = r12 * den, rdn = r12 * T2;
+        const double fa = fma(vT, dLv, u.uT * dLu);
+        const double tt = (fa * fa) * (u.rT1h * rT2);
+        const double uXd = u.uX * dLu, vXd = vX * dLv;
+        const double fa_uv = fma(uXd, c2, vXd), fa_vu = fma(vXd, c2, uXd);
+        const double num = fma(E1T2, fa_uv, -(xx * fa_vu));
+        const double te = (fa_uv * num) * rdn;
+        aTT = fma(ph.w, okT ? tt : 0.0, aTT);
+        aTE = fma(ph.w, okT ? te : 0.0, aTE);
+    }
+    const double fe = fma(vE, dLv, uEd) * c2;
+    const double ee = (fe * fe) * (u.rE1h * rE2);
+    const double fb = fma(-vB, dLv, uEd);
+    const double eb = ((fb * fb) * s2sq) * (u.rE1 * rB2);
+    aEE = fma(ph.w, okP ? ee : 0.0, aEE);
+    aEB = fma(ph.w, okP ? eb : 0.0, aEB);
+}
+
+// G[i] = exp(a i (i + 1)) on the integer knots (cmb/DetectorNoise.py:22 without the amplitude).
+__global__ void n0_noise_knots_kernel(int n, double a, double* __restrict__ G) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) G[i] = exp(((double)i * ((double)i + 1.0)) * a);
+}
+
+template <bool DO_T, bool EXPN>
+__device__ __forceinline__ void n0_rows2_loop(const N0Params& P, const double* __restrict__ tab, const double* __restrict__ G,
+                                              const PhiNode* __restrict__ sph, double L2, double l, const UVals& u, bool actT, bool actP,
+                                              double& aTT, double& aTE, double& aEE, double& aEB) {
+    const double l2 = l * l, rl2 = 1.0 / l2;
+    int j = 0;
+    for (; j + 1 < P.n_phi; j += 2) {      // two independent nodes per trip: ILP for the FP64 pipe
+        n0_fast_node<DO_T, EXPN>(P, tab, G, L2, l, l2, rl2, u, actT, actP, sph[j], aTT, aTE, aEE, aEB);
+        n0_fast_node<DO_T, EXPN>(P, tab, G, L2, l, l2, rl2, u, actT, actP, sph[j + 1], aTT, aTE, aEE, aEB);
+    }
+    if (j < P.n_phi) n0_fast_node<DO_T, EXPN>(P, tab, G, L2, l, l2, rl2, u, actT, actP, sph[j], aTT, aTE, aEE, aEB);
+}
+
+template <bool EXPN>
+__global__ void __launch_bounds__(128)
+n0_rows2_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const double* __restrict__ tab,
+                const double* __restrict__ G, double* __restrict__ partial /*[5][n_L][n_rb]*/) {
+    extern __shared__ double shm[];
+    PhiNode* sph = reinterpret_cast<PhiNode*>(shm);                 // [n_phi]
+    double (*red)[4] = reinterpret_cast<double (*)[4]>(shm + 4 * P.n_phi);
+    __shared__ int s_anyT;
+    const int r = blockIdx.x * 128 + threadIdx.x;
+    const int iL = blockIdx.y, n_rb = gridDim.x;
+    const double L = Ls[iL];
+    const double L2 = L * L;
+    if (threadIdx.x == 0) s_anyT = 0;
+    for (int j = threadIdx.x; j < P.n_phi; j += 128) {
+        const double c = c_phi[j], s = c_phi[P.n_phi + j];
+        PhiNode n;
+        n.B = L * c; n.A = 2.0 * n.B; n.C = L * s; n.w = c_phi[2 * P.n_phi + j];
+        sph[j] = n;
+    }
+    int fl = 0;
+    double l = 1.0, wl = 0.0;
+    UVals u = {};
+    if (r < P.n_l1) {
+        const double4* up = reinterpret_cast<const double4*>(utab + r);
+        const double4 q0 = ld4(up), q1 = ld4(up + 1), q2 = ld4(up + 2), q3 = ld4(up + 3);
+        fl = (int)q3.y;
+        l = q0.x; wl = q0.y;
+        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
+        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
+    }
+    const bool act = (fl & 5) && !(fl & 16);
+    const bool actT = act && (fl & 1), actP = act && (fl & 4);
+    __syncthreads();
+    if (actT) s_anyT = 1;                                           // benign race: every writer stores 1
+    __syncthreads();
+    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
+    if (s_anyT) n0_rows2_loop<true, EXPN>(P, tab, G, sph, L2, l, u, actT, actP, aTT, aTE, aEE, aEB);
+    else        n0_rows2_loop<false, EXPN>(P, tab, G, sph, L2, l, u, actT, actP, aTT, aTE, aEE, aEB);
+    // second pass: nodes within 4e-6 of a cut in |v|^2, evaluated exactly as the reference rounds them
+    if (act) {
+        const bool fold = P.fold != 0;
+        for (int j = 0; j < P.n_phi; ++j) {
+            const double nv2 = fma(l, l - sph[j].A, L2);
+            const unsigned hi = (unsigned)__double2hiint(nv2);
+            if ((hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2])
+                n0_node<true>(P, reinterpret_cast<const ClRow*>(tab), L, l, c_phi[j], c_phi[P.n_phi + j], u, fl & 1, fl & 4, sph[j].w, fold,
+                              c_phi[3 * P.n_phi + j], c_phi[4 * P.n_phi + j], c_phi[5 * P.n_phi + j], aTT, aTE, aEE, aEB, aBB);
+        }
+    }
+    if (!(P.terms & LBG_TT)) aTT = 0.0;
+    if (!(P.terms & LBG_TE)) aTE = 0.0;
+    if (!(P.terms & LBG_EE)) aEE = 0.0;
+    if (!(P.terms & LBG_EB)) aEB = 0.0;
+    double acc[5] = {aTT * wl, aTE * wl, aEE * wl, aEB * wl, aBB * wl};
+#pragma unroll
+    for (int t = 0; t < 5; ++t) {
+        double v = acc[t];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) red[t][threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 5) {
+        const int t = threadIdx.x;
+        const double v = (red[t][0] + red[t][1]) + (red[t][2] + red[t][3]);
+        partial[((size_t)t * P.n_L + iL) * n_rb + blockIdx.x] = v;
     }
 }
 
@@ -410,6 +715,7 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     const double dP = sqrt(2.) * dT;
 
     N0Params P;
+    P.soa_stride = c->cl_soa_stride;
     P.n_L = n_L; P.n_phi = n_phe; P.n_l1 = n_l1; P.n_ell = c->n_ell; P.terms = terms_mask;
     P.nT = (dT / Tcmb_K) * (dT / Tcmb_K);
     P.nP = (dP / Tcmb_K) * (dP / Tcmb_K);
@@ -436,18 +742,25 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     n_chunk = (n_l1 + P.rows_per_chunk - 1) / P.rows_per_chunk;
     P.n_chunk = n_chunk;
 
+    // kernel variant: 0 = thread per (L, phi) marching over |u| rows, 1 = thread per |u| row looping over phi ("rows")
+    int variant = 2;
+    if (const char* e = getenv("LBG_N0_VARIANT")) variant = atoi(e);
+    if (n_phe > LBG_MAX_PHI_CONST || n_L > 65535) variant = 0;
+    // rows2 needs: only TT/TE/EE/EB requested, every |v| up to lmax_P inside the table, cuts ordered lmin_v < lmax_T <= lmax_P
+    if (variant == 2 && ((terms_mask & LBG_BB) || lmax_P > (double)(c->n_ell - 2) || !(lmin_v > 0.0 && lmin_v < lmax_T))) variant = 1;
+    const int n_rb = (n_l1 + 127) / 128;
     const size_t su_bytes = (size_t)n_special * n_phi * 8 * 8, snu_bytes = (size_t)n_special * n_phi * 8;
     if (c->n0_L.reserve((size_t)n_L * 8) || c->s0.reserve((size_t)n_l1 * 8) || c->s1.reserve((size_t)n_l1 * 8) ||
-        c->n0_rowflag.reserve((size_t)n_l1 * 4) || c->n0_phi.reserve((ph.size() + phf.size()) * 8) ||
+        c->n0_rowflag.reserve((size_t)n_l1 * 4) || c->n0_G.reserve((size_t)c->n_ell * 8 + 64) || c->n0_phi.reserve((ph.size() + phf.size()) * 8) ||
         c->n0_utab.reserve((size_t)n_l1 * sizeof(URow)) ||
-        c->n0_partial.reserve((size_t)5 * (n_chunk * npairs + npairs_full) * 8) || c->n0_out.reserve((size_t)6 * n_L * 8) ||
+        c->n0_partial.reserve((size_t)5 * (std::max((long long)n_chunk * npairs, (long long)n_L * n_rb) + npairs_full) * 8) || c->n0_out.reserve((size_t)6 * n_L * 8) ||
         c->s2.reserve(su_bytes + 64) || c->s3.reserve(snu_bytes + 64) || c->s4.reserve((size_t)n_special * 4 + 64))
         return LBG_ENOMEM;
     cudaStream_t st = c->stream;
     double* d_ph = c->n0_phi.as<double>();
     double* d_phf = d_ph + ph.size();
     double* d_part = c->n0_partial.as<double>();
-    double* d_spart = d_part + (size_t)5 * n_chunk * npairs;
+    double* d_spart = d_part + (size_t)5 * std::max((long long)n_chunk * npairs, (long long)n_L * n_rb);
     LBG_CUDA(cudaMemcpyAsync(c->n0_L.p, L, (size_t)n_L * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s0.p, l1, (size_t)n_l1 * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s1.p, w_l1, (size_t)n_l1 * 8, cudaMemcpyHostToDevice, st));
@@ -461,6 +774,7 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
             LBG_CUDA(cudaMemcpyAsync(c->s2.p, exact_u, (size_t)n_exact * n_phi * 64, cudaMemcpyHostToDevice, st));
     }
 
+    if (variant >= 1) LBG_CUDA(cudaMemcpyToSymbolAsync(c_phi, ph.data(), ph.size() * 8, 0, cudaMemcpyHostToDevice, st));
     KernelTimer t(c);
     n0_uside_kernel<<<(n_l1 + 127) / 128, 128, 0, st>>>(P, c->s0.as<double>(), c->s1.as<double>(), c->n0_rowflag.as<int>(),
                                                          c->cl_rows.as<ClRow>(), c->n0_utab.as<URow>());
@@ -471,8 +785,21 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
                                                                c->cl_rows.as<ClRow>(), c->s2.as<double>() + (size_t)n_exact * n_phi * 8);
         t.launched();
     }
-    n0_kernel<<<dim3(bx, n_chunk), 128, 0, st>>>(P, c->n0_L.as<double>(), d_ph, c->n0_utab.as<URow>(),
-                                                 c->cl_rows.as<ClRow>(), d_part);
+    if (variant == 2) {
+        const double xmax = P.a * 2.0 * (double)c->n_ell;                 // largest Taylor argument of the noise factor
+        const size_t smem = ((size_t)4 * n_phe + 5 * 4) * 8;
+        n0_noise_knots_kernel<<<(c->n_ell + 255) / 256, 256, 0, st>>>(c->n_ell, P.a, c->n0_G.as<double>());
+        t.launched();
+        if (xmax < 0.03)
+            n0_rows2_kernel<false><<<dim3(n_rb, n_L), 128, smem, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_soa.as<double>(), c->n0_G.as<double>(), d_part);
+        else
+            n0_rows2_kernel<true><<<dim3(n_rb, n_L), 128, smem, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_soa.as<double>(), c->n0_G.as<double>(), d_part);
+    } else if (variant == 1) {
+        n0_rows_kernel<<<dim3(n_rb, n_L), 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_soa.as<ClRow>(), d_part);
+    } else {
+        n0_kernel<<<dim3(bx, n_chunk), 128, 0, st>>>(P, c->n0_L.as<double>(), d_ph, c->n0_utab.as<URow>(),
+                                                     c->cl_rows.as<ClRow>(), d_part);
+    }
     t.launched();
     if (n_special) {
         n0_special_kernel<<<(int)((npairs_full + 127) / 128), 128, 0, st>>>(P, n_special, n_phi, c->s4.as<int>(), c->n0_L.as<double>(), d_phf,
@@ -480,7 +807,10 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
                                                                             c->cl_rows.as<ClRow>(), d_spart);
         t.launched();
     }
-    n0_reduce_kernel<<<n_L, 128, 0, st>>>(P, c->n0_L.as<double>(), d_part, n_special ? d_spart : nullptr, n_phi, c->n0_out.as<double>());
+    if (variant >= 1)
+        n0_rows_reduce_kernel<<<n_L, 128, 0, st>>>(P, n_rb, c->n0_L.as<double>(), d_part, n_special ? d_spart : nullptr, n_phi, c->n0_out.as<double>());
+    else
+        n0_reduce_kernel<<<n_L, 128, 0, st>>>(P, c->n0_L.as<double>(), d_part, n_special ? d_spart : nullptr, n_phi, c->n0_out.as<double>());
     t.launched();
     std::vector<double> host((size_t)6 * n_L);
     LBG_CUDA(cudaMemcpyAsync(host.data(), c->n0_out.p, host.size() * 8, cudaMemcpyDeviceToHost, st));

@@ -1,0 +1,17 @@
+"""Small N0 case for ncu (every 10th L of the bench grid): python scripts/n0_profile_case.py [variant]"""
+import os
+import sys
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+if len(sys.argv) > 1:
+    os.environ['LBG_N0_VARIANT'] = sys.argv[1]
+from lbgcmb_b200 import Nkk
+from lbgcmb_b200.prep_camb import cl_interps_from_tables
+from lbgcmb_b200.synthetic import cmb_cl_tables
+
+ell, lens, nolens = cmb_cl_tables()
+li, ni = cl_interps_from_tables(ell, lens, nolens)
+Ls = np.arange(50, 5001, 10)
+for rep in range(2):
+    out, _ = Nkk.n0_terms(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True)
+print('kernel_ms %.3f' % Nkk.last_stats['kernel_ms'], 'nodes', Nkk.last_stats['nodes'], out[:2])
