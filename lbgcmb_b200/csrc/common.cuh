@@ -9,6 +9,8 @@
 #include <mutex>
 #include "../../include/lbgcmb.h"
 
+#define LBG_PAIR_STRIDE 16384      /* compile-time spectrum stride of cl_pairs: the 32 gathers of a node share one base register */
+
 namespace lbg {
 
 void set_error(const char* fmt, ...);
@@ -69,6 +71,7 @@ struct lbg_ctx {
     lbg::DevBuf  cl_rows;            // ClRow[n_ell + 2], row r holds coefficient index r-1
     lbg::DevBuf  cl_soa;             // the same coefficients spectrum-major: double[8][cl_soa_stride]
     int          cl_soa_stride = 0;
+    lbg::DevBuf  cl_pairs;           // overlapping pairs (c_r, c_{r+1}) per spectrum: double2[8][LBG_PAIR_STRIDE] (n0 rows2 kernel)
     // N0 workspaces
     lbg::DevBuf  n0_L, n0_utab, n0_phi, n0_partial, n0_out, n0_rowflag, n0_G;
     // generic scratch

@@ -378,14 +378,16 @@ __device__ __forceinline__ void n0_fast_node(const N0Params& P, const double* __
     const double t2 = t * t, u2 = um * um;
     const double w0 = (u2 * (1.0 / 6.0)) * um, w3 = (t2 * (1.0 / 6.0)) * t;
     const double w1 = fma(t2, fma(0.5, t, -1.0), 2.0 / 3.0), w2 = fma(u2, fma(0.5, um, -1.0), 2.0 / 3.0);
-    const double* q = tab + i;
-    const size_t st = (size_t)P.soa_stride;
-#define LBG_SPL(k) fma(w3, __ldg(q + (k) * st + 3), fma(w2, __ldg(q + (k) * st + 2), fma(w1, __ldg(q + (k) * st + 1), w0 * __ldg(q + (k) * st))))
-    double vT = 0.0, vX = 0.0, T2 = 1.0, X2 = 0.0;
-    if (DO_T) { vT = LBG_SPL(0); vX = LBG_SPL(1); T2 = LBG_SPL(4); X2 = LBG_SPL(5); }
-    const double vE = LBG_SPL(2), vB = LBG_SPL(3);
-    double E2 = LBG_SPL(6), B2 = LBG_SPL(7);
+    const double2* q = reinterpret_cast<const double2*>(tab) + i;   // (c_i, c_{i+1}) pairs, compile-time spectrum stride
+    double vT = 0.0, vX = 0.0, T2 = 1.0, X2 = 0.0, vE, vB, E2, B2;
+    {
+        double2 a, b;
+#define LBG_SPL(k, out) a = __ldg(q + (k) * LBG_PAIR_STRIDE); b = __ldg(q + (k) * LBG_PAIR_STRIDE + 2); \
+                        out = fma(w3, b.y, fma(w2, b.x, fma(w1, a.y, w0 * a.x)))
+        if (DO_T) { LBG_SPL(0, vT); LBG_SPL(1, vX); LBG_SPL(4, T2); LBG_SPL(5, X2); }
+        LBG_SPL(2, vE); LBG_SPL(3, vB); LBG_SPL(6, E2); LBG_SPL(7, B2);
 #undef LBG_SPL
+    }
     double en;
     if (EXPN) {
         en = exp((nv2 + nv) * P.a);
@@ -455,8 +457,8 @@ __device__ __forceinline__ void n0_rows2_loop(const N0Params& P, const double* _
 
 template <bool EXPN>
 __global__ void __launch_bounds__(128)
-n0_rows2_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const double* __restrict__ tab,
-                const double* __restrict__ G, double* __restrict__ partial /*[5][n_L][n_rb]*/) {
+n0_rows2_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const double* __restrict__ tab /*pairs*/,
+                const double* __restrict__ soa, const double* __restrict__ G, double* __restrict__ partial /*[5][n_L][n_rb]*/) {
     extern __shared__ double shm[];
     PhiNode* sph = reinterpret_cast<PhiNode*>(shm);                 // [n_phi]
     double (*red)[4] = reinterpret_cast<double (*)[4]>(shm + 4 * P.n_phi);
@@ -498,7 +500,7 @@ n0_rows2_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
             const double nv2 = fma(l, l - sph[j].A, L2);
             const unsigned hi = (unsigned)__double2hiint(nv2);
             if ((hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2])
-                n0_node<true>(P, reinterpret_cast<const ClRow*>(tab), L, l, c_phi[j], c_phi[P.n_phi + j], u, fl & 1, fl & 4, sph[j].w, fold,
+                n0_node<true>(P, reinterpret_cast<const ClRow*>(soa), L, l, c_phi[j], c_phi[P.n_phi + j], u, fl & 1, fl & 4, sph[j].w, fold,
                               c_phi[3 * P.n_phi + j], c_phi[4 * P.n_phi + j], c_phi[5 * P.n_phi + j], aTT, aTE, aEE, aEB, aBB);
         }
     }
@@ -747,7 +749,7 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     if (const char* e = getenv("LBG_N0_VARIANT")) variant = atoi(e);
     if (n_phe > LBG_MAX_PHI_CONST || n_L > 65535) variant = 0;
     // rows2 needs: only TT/TE/EE/EB requested, every |v| up to lmax_P inside the table, cuts ordered lmin_v < lmax_T <= lmax_P
-    if (variant == 2 && ((terms_mask & LBG_BB) || lmax_P > (double)(c->n_ell - 2) || !(lmin_v > 0.0 && lmin_v < lmax_T))) variant = 1;
+    if (variant == 2 && ((terms_mask & LBG_BB) || lmax_P > (double)(c->n_ell - 2) || c->n_ell + 2 > LBG_PAIR_STRIDE || !(lmin_v > 0.0 && lmin_v < lmax_T))) variant = 1;
     const int n_rb = (n_l1 + 127) / 128;
     const size_t su_bytes = (size_t)n_special * n_phi * 8 * 8, snu_bytes = (size_t)n_special * n_phi * 8;
     if (c->n0_L.reserve((size_t)n_L * 8) || c->s0.reserve((size_t)n_l1 * 8) || c->s1.reserve((size_t)n_l1 * 8) ||
@@ -791,9 +793,9 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
         n0_noise_knots_kernel<<<(c->n_ell + 255) / 256, 256, 0, st>>>(c->n_ell, P.a, c->n0_G.as<double>());
         t.launched();
         if (xmax < 0.03)
-            n0_rows2_kernel<false><<<dim3(n_rb, n_L), 128, smem, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_soa.as<double>(), c->n0_G.as<double>(), d_part);
+            n0_rows2_kernel<false><<<dim3(n_rb, n_L), 128, smem, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_pairs.as<double>(), c->cl_soa.as<double>(), c->n0_G.as<double>(), d_part);
         else
-            n0_rows2_kernel<true><<<dim3(n_rb, n_L), 128, smem, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_soa.as<double>(), c->n0_G.as<double>(), d_part);
+            n0_rows2_kernel<true><<<dim3(n_rb, n_L), 128, smem, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_pairs.as<double>(), c->cl_soa.as<double>(), c->n0_G.as<double>(), d_part);
     } else if (variant == 1) {
         n0_rows_kernel<<<dim3(n_rb, n_L), 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_soa.as<ClRow>(), d_part);
     } else {
