@@ -72,6 +72,8 @@ struct lbg_ctx {
     lbg::DevBuf  cl_soa;             // the same coefficients spectrum-major: double[8][cl_soa_stride]
     int          cl_soa_stride = 0;
     lbg::DevBuf  cl_pairs;           // overlapping pairs (c_r, c_{r+1}) per spectrum: double2[8][LBG_PAIR_STRIDE] (n0 rows2 kernel)
+    lbg::DevBuf  cl_poly;            // per-call: double4[n_ell-1][8] monomial coefficients per knot interval, noise folded in (n0 rows3 kernel)
+    bool         ub_zero = false;    // unlensed BB identically zero (its slot is then never read)
     // N0 workspaces
     lbg::DevBuf  n0_L, n0_utab, n0_phi, n0_partial, n0_out, n0_rowflag, n0_G;
     // generic scratch

@@ -109,7 +109,7 @@ extern "C" int lbg_ctx_destroy(lbg_ctx* c) {
     if (!c) return LBG_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (DevBuf* b : {&c->cl_rows, &c->cl_soa, &c->cl_pairs, &c->n0_L, &c->n0_utab, &c->n0_phi, &c->n0_partial, &c->n0_out, &c->n0_rowflag, &c->n0_G,
+    for (DevBuf* b : {&c->cl_rows, &c->cl_soa, &c->cl_pairs, &c->cl_poly, &c->n0_L, &c->n0_utab, &c->n0_phi, &c->n0_partial, &c->n0_out, &c->n0_rowflag, &c->n0_G,
                       &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->pk_lnk, &c->pk_plin, &c->pk_pnl})
         b->release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
@@ -183,6 +183,8 @@ extern "C" int lbg_upload_cl_tables(lbg_ctx* c, int n_ell, const double* lensed,
     }
     LBG_CUDA(cudaStreamSynchronize(c->stream));
     c->n_ell = n_ell;
+    c->ub_zero = true;
+    for (int r = 0; r < n_ell; ++r) c->ub_zero = c->ub_zero && unlensed[(size_t)2 * n_ell + r] == 0.0;
     return LBG_OK;
 }
 

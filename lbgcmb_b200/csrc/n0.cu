@@ -524,6 +524,206 @@ n0_rows2_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
     }
 }
 
+// ---- "rows3" variant: rows decomposition, per-interval polynomial tables with the detector noise folded in ----------
+// What bounds rows2 is not one pipe but three at once (ncu r1b: FP64 56 %, L1 data pipe 63 %, issue 56 %): every coefficient
+// a lane loads costs register-fill bandwidth (128 B/clk/SM, no dedupe between lanes), and the B-spline form spends 12 FP64
+// instructions on the basis weights plus 4 per spectrum.  rows3 therefore
+//  * evaluates each spectrum from the monomial coefficients of its knot interval (Horner, 3 DFMA, one 32-byte row slot),
+//    slot-major with a compile-time slot stride: the L1 data stage spends one wavefront per 128-byte line a load touches, so
+//    neighbouring lanes (neighbouring |v|) must find their coefficients of one slot in neighbouring bytes;
+//  * folds the detector noise into the C^tot slots when the table is built for the call: on [i, i+1] the factor
+//    exp(a t (2i+1+t)) - 1 is replaced by its cubic interpolant at the four Chebyshev nodes (relative error bounded by
+//    (beta^4 + 12 a beta^2 + 12 a^2) / 3072, beta = a (2 lmax + 1); the host falls back to rows2 when the bound exceeds 2e-12);
+//  * drops the unlensed-BB slot when that spectrum is identically zero (CAMB scalar runs: prep_camb.py:84-85);
+//  * takes cos phi_j / w_j from constant memory (uniform datapath) and needs only cos: cos 2phi_uv = 2 (u.v)^2/(|u|^2|v|^2) - 1;
+//  * skips the temperature estimators (four slots, ~40 FP64 instructions) for warps whose |v| all exceed lmax_T.
+// Nodes within 4e-6 of a cut in |v|^2 are still left to the bit-faithful second pass (n0_node).
+__constant__ double2 c_cw[LBG_MAX_PHI_CONST];        // (cos phi_j, w_j) of the (folded) phi grid
+
+struct ChebFit { double m[4][4]; double t[4]; };     // monomial coefficients = m . samples at t[]
+
+// slots per interval: 0 C^EE_tot, 1 C^BB_tot, 2 unlensed EE, 3 unlensed BB | 4 C^TT_tot, 5 lensed TE, 6 unlensed TT, 7 unlensed TE
+__global__ void n0_poly_table_kernel(N0Params P, ChebFit F, int n_int, const double* __restrict__ soa, double4* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_int) return;
+    const size_t st = (size_t)P.soa_stride;
+    double4 a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const double c0 = soa[k * st + i], c1 = soa[k * st + i + 1], c2 = soa[k * st + i + 2], c3 = soa[k * st + i + 3];
+        a[k].x = (c0 + 4.0 * c1 + c2) * (1.0 / 6.0);
+        a[k].y = (c2 - c0) * 0.5;
+        a[k].z = (c0 - 2.0 * c1 + c2) * 0.5;
+        a[k].w = ((c3 - c0) + 3.0 * (c1 - c2)) * (1.0 / 6.0);
+    }
+    const double fi = (double)i;
+    double g[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) g[q] = expm1((P.a * F.t[q]) * fma(2.0, fi, 1.0 + F.t[q]));
+    const double G = exp((fi * (fi + 1.0)) * P.a);
+    double n[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) n[q] = G * (F.m[q][0] * g[0] + F.m[q][1] * g[1] + F.m[q][2] * g[2] + F.m[q][3] * g[3]);
+    n[0] += G;
+    // layout double2[slot][half][LBG_PAIR_STRIDE]: (a0,a1) and (a2,a3) of one slot in separate arrays, so the 16-17 intervals a warp
+    // gathers per load span ~272 bytes (3 lines) and the load costs its register-fill minimum of 4 wavefronts
+    double2* o = reinterpret_cast<double2*>(out) + i;
+#define LBG_PUT(slot, v) o[(2 * (slot)) * LBG_PAIR_STRIDE] = make_double2((v).x, (v).y); o[(2 * (slot) + 1) * LBG_PAIR_STRIDE] = make_double2((v).z, (v).w)
+    const double4 e2 = make_double4(fma(P.nP, n[0], a[6].x), fma(P.nP, n[1], a[6].y), fma(P.nP, n[2], a[6].z), fma(P.nP, n[3], a[6].w));
+    const double4 b2 = make_double4(fma(P.nP, n[0], a[7].x), fma(P.nP, n[1], a[7].y), fma(P.nP, n[2], a[7].z), fma(P.nP, n[3], a[7].w));
+    const double4 t2 = make_double4(fma(P.nT, n[0], a[4].x), fma(P.nT, n[1], a[4].y), fma(P.nT, n[2], a[4].z), fma(P.nT, n[3], a[4].w));
+    LBG_PUT(0, e2); LBG_PUT(1, b2); LBG_PUT(2, a[2]); LBG_PUT(3, a[3]);
+    LBG_PUT(4, t2); LBG_PUT(5, a[5]); LBG_PUT(6, a[0]); LBG_PUT(7, a[1]);
+#undef LBG_PUT
+}
+
+template <int SLOT>
+__device__ __forceinline__ double horner3(const double2* __restrict__ p, double t) {    // p = table + interval index
+    const double2 lo = __ldg(p + (2 * SLOT) * LBG_PAIR_STRIDE), hi = __ldg(p + (2 * SLOT + 1) * LBG_PAIR_STRIDE);
+    return fma(fma(fma(hi.y, t, hi.x), t, lo.y), t, lo.x);
+}
+
+struct RowGeom { double L2, l2, rl2x2, lL, m2lL, l2pL2; };   // per-thread constants of one (L, |u|) row
+
+template <bool DO_T, bool HAS_UB, bool FULL>
+__device__ __forceinline__ void n0_poly_node(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
+                                             bool actT, bool actP, const double2 cw,
+                                             double& aTT, double& aTE, double& aEE, double& aEB) {
+    const double nv2 = fma(g.m2lL, cw.x, g.l2pL2);               // |v|^2 = l^2 + L^2 - 2 l L cos phi
+    const unsigned hi = (unsigned)__double2hiint(nv2);
+    const bool rare = (hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2];
+    const bool vok = !rare && hi > P.near_lo[0];
+    const bool okT = DO_T && actT && vok && hi < P.near_lo[1];
+    const bool okP = actP && vok && hi < P.near_lo[2];
+    if (!__any_sync(0xffffffffu, okT || okP)) return;
+    const bool doT = DO_T && __any_sync(0xffffffffu, okT);       // warp-uniform
+
+    const double y = rsqrt_fast(nv2);                            // lanes with a bad |v|^2 carry NaN; their terms are selected away
+    const double nv = nv2 * y;
+    const double dLu = g.lL * cw.x, dLv = g.L2 - dLu;            // L.u, L.v
+    const double dot = dLu - g.l2;                               // u.v
+    const double c2 = fma((dot * dot) * (y * y), g.rl2x2, -1.0); // cos 2phi_uv
+    const double s2sq = fma(-c2, c2, 1.0);                       // sin^2 2phi_uv
+
+    const int i = max(min((int)nv, P.n_ell - 2), 0);
+    const double t = nv - (double)i;
+    const double2* row = reinterpret_cast<const double2*>(ptab) + i;
+    const double E2 = horner3<0>(row, t), vE = horner3<2>(row, t);
+    double B2 = horner3<1>(row, t);
+    const double vB = HAS_UB ? horner3<3>(row, t) : 0.0;
+    if (!FULL) { if (!(P.terms & LBG_EB)) B2 = 1.0; }
+    const double uEd = u.uE * dLu;
+    const double p2 = E2 * B2;
+    double rE2, rB2;
+    if (doT) {
+        double T2 = horner3<4>(row, t);
+        const double X2 = horner3<5>(row, t), vT = horner3<6>(row, t), vX = horner3<7>(row, t);
+        const double E1T2 = u.E1 * T2, xx = u.X1 * X2;
+        double den = fma(u.T1 * E2, E1T2, -(xx * xx));
+        if (!FULL) { if (!(P.terms & LBG_TE)) den = 1.0;  if (!(P.terms & LBG_TT)) T2 = 1.0; }
+        const double p1 = T2 * den;
+        const double r = rcp_fast(p1 * p2);                      // one reciprocal for the four filter denominators
+        const double r34 = r * p1, r12 = r * p2;
+        rE2 = r34 * B2; rB2 = r34 * E2;
+        const double rT2 = r12 * den, rdn = r12 * T2;
+        const double fa = fma(vT, dLv, u.uT * dLu);
+        const double tt = (fa * fa) * (u.rT1h * rT2);
+        const double uXd = u.uX * dLu, vXd = vX * dLv;
+        const double fa_uv = fma(uXd, c2, vXd), fa_vu = fma(vXd, c2, uXd);
+        const double num = fma(E1T2, fa_uv, -(xx * fa_vu));
+        const double te = (fa_uv * num) * rdn;
+        aTT = fma(cw.y, okT ? tt : 0.0, aTT);
+        aTE = fma(cw.y, okT ? te : 0.0, aTE);
+    } else {
+        const double r = rcp_fast(p2);
+        rE2 = r * B2; rB2 = r * E2;
+    }
+    const double fe = fma(vE, dLv, uEd) * c2;
+    const double ee = (fe * fe) * (u.rE1h * rE2);
+    const double fb = HAS_UB ? fma(-vB, dLv, uEd) : uEd;
+    const double eb = ((fb * fb) * s2sq) * (u.rE1 * rB2);
+    aEE = fma(cw.y, okP ? ee : 0.0, aEE);
+    aEB = fma(cw.y, okP ? eb : 0.0, aEB);
+}
+
+template <bool DO_T, bool HAS_UB, bool FULL>
+__device__ __forceinline__ void n0_rows3_loop(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
+                                              bool actT, bool actP, double& aTT, double& aTE, double& aEE, double& aEB) {
+    int j = 0;
+    for (; j + 1 < P.n_phi; j += 2) {      // two independent nodes per trip: ILP for the FP64 pipe
+        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], aTT, aTE, aEE, aEB);
+        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j + 1], aTT, aTE, aEE, aEB);
+    }
+    if (j < P.n_phi) n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], aTT, aTE, aEE, aEB);
+}
+
+#ifndef LBG_ROWS3_MINB
+#define LBG_ROWS3_MINB 4
+#endif
+template <bool HAS_UB, bool FULL>
+__global__ void __launch_bounds__(128, LBG_ROWS3_MINB)
+n0_rows3_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const double4* __restrict__ ptab,
+                const double* __restrict__ soa, double* __restrict__ partial /*[5][n_L][n_rb]*/) {
+    __shared__ double red[5][4];
+    __shared__ int s_anyT;
+    const int r = blockIdx.x * 128 + threadIdx.x;
+    const int iL = blockIdx.y, n_rb = gridDim.x;
+    const double L = Ls[iL];
+    if (threadIdx.x == 0) s_anyT = 0;
+    int fl = 0;
+    double l = 1.0, wl = 0.0;
+    UVals u = {};
+    if (r < P.n_l1) {
+        const double4* up = reinterpret_cast<const double4*>(utab + r);
+        const double4 q0 = ld4(up), q1 = ld4(up + 1), q2 = ld4(up + 2), q3 = ld4(up + 3);
+        fl = (int)q3.y;
+        l = q0.x; wl = q0.y;
+        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
+        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
+    }
+    const bool act = (fl & 5) && !(fl & 16);
+    const bool actT = act && (fl & 1), actP = act && (fl & 4);
+    __syncthreads();
+    if (actT) s_anyT = 1;                                           // benign race: every writer stores 1
+    __syncthreads();
+    RowGeom g;
+    g.L2 = L * L; g.l2 = l * l; g.rl2x2 = 2.0 / g.l2; g.lL = l * L; g.m2lL = -2.0 * g.lL; g.l2pL2 = g.l2 + g.L2;
+    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
+    if (s_anyT) n0_rows3_loop<true, HAS_UB, FULL>(P, ptab, g, u, actT, actP, aTT, aTE, aEE, aEB);
+    else        n0_rows3_loop<false, HAS_UB, FULL>(P, ptab, g, u, actT, actP, aTT, aTE, aEE, aEB);
+    // second pass: nodes within 4e-6 of a cut in |v|^2, evaluated exactly as the reference rounds them
+    if (act) {
+        const bool fold = P.fold != 0;
+        for (int j = 0; j < P.n_phi; ++j) {
+            const double nv2 = fma(g.m2lL, c_cw[j].x, g.l2pL2);
+            const unsigned hi = (unsigned)__double2hiint(nv2);
+            if ((hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2])
+                n0_node<true>(P, reinterpret_cast<const ClRow*>(soa), L, l, c_phi[j], c_phi[P.n_phi + j], u, fl & 1, fl & 4, c_cw[j].y, fold,
+                              c_phi[3 * P.n_phi + j], c_phi[4 * P.n_phi + j], c_phi[5 * P.n_phi + j], aTT, aTE, aEE, aEB, aBB);
+        }
+    }
+    if (!FULL) {
+        if (!(P.terms & LBG_TT)) aTT = 0.0;
+        if (!(P.terms & LBG_TE)) aTE = 0.0;
+        if (!(P.terms & LBG_EE)) aEE = 0.0;
+        if (!(P.terms & LBG_EB)) aEB = 0.0;
+    }
+    double acc[5] = {aTT * wl, aTE * wl, aEE * wl, aEB * wl, aBB * wl};
+#pragma unroll
+    for (int t = 0; t < 5; ++t) {
+        double v = acc[t];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) red[t][threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 5) {
+        const int t = threadIdx.x;
+        const double v = (red[t][0] + red[t][1]) + (red[t][2] + red[t][3]);
+        partial[((size_t)t * P.n_L + iL) * n_rb + blockIdx.x] = v;
+    }
+}
+
 // Special rows, always on the full (unfolded) phi grid:
 //  * rows sitting on the lmax_T / lmax_P cuts, where the reference's mask `|u| > lmax` (cmb/Nkk.py:17,20) depends on the
 //    rounding of |u| = sqrt((l cos)^2 + (l sin)^2) at each phi node;
@@ -745,18 +945,44 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     P.n_chunk = n_chunk;
 
     // kernel variant: 0 = thread per (L, phi) marching over |u| rows, 1 = thread per |u| row looping over phi ("rows")
-    int variant = 2;
+    int variant = 3;
     if (const char* e = getenv("LBG_N0_VARIANT")) variant = atoi(e);
     if (n_phe > LBG_MAX_PHI_CONST || n_L > 65535) variant = 0;
     // rows2 needs: only TT/TE/EE/EB requested, every |v| up to lmax_P inside the table, cuts ordered lmin_v < lmax_T <= lmax_P
-    if (variant == 2 && ((terms_mask & LBG_BB) || lmax_P > (double)(c->n_ell - 2) || c->n_ell + 2 > LBG_PAIR_STRIDE || !(lmin_v > 0.0 && lmin_v < lmax_T))) variant = 1;
+    if (variant >= 2 && ((terms_mask & LBG_BB) || lmax_P > (double)(c->n_ell - 2) || c->n_ell + 2 > LBG_PAIR_STRIDE || !(lmin_v > 0.0 && lmin_v < lmax_T))) variant = 1;
+    ChebFit fit;
+    if (variant == 3) {
+        // rows3 folds the noise into the table: relative error bound of the per-interval Chebyshev cubic (see the kernel's header)
+        const double beta = P.a * (2.0 * lmax_P + 1.0);
+        const double bound = (beta * beta * beta * beta + 12.0 * P.a * beta * beta + 12.0 * P.a * P.a) / 3072.0;
+        if (bound > 2e-12) variant = 2;
+        // monomial <- samples matrix of the four Chebyshev nodes on [0, 1] (Gauss-Jordan in long double)
+        long double V[4][8];
+        for (int q = 0; q < 4; ++q) {
+            const long double tq = 0.5L + 0.5L * cosl((2 * q + 1) * M_PIl / 8.0L);
+            fit.t[q] = (double)tq;
+        }
+        for (int q = 0; q < 4; ++q) {
+            long double pw = 1.0L;
+            for (int k = 0; k < 4; ++k) { V[q][k] = pw; pw *= (long double)fit.t[q]; V[q][4 + k] = (q == k) ? 1.0L : 0.0L; }
+        }
+        for (int col = 0; col < 4; ++col) {
+            int piv = col;
+            for (int q = col + 1; q < 4; ++q) if (fabsl(V[q][col]) > fabsl(V[piv][col])) piv = q;
+            for (int k = 0; k < 8; ++k) std::swap(V[col][k], V[piv][k]);
+            const long double d = V[col][col];
+            for (int k = 0; k < 8; ++k) V[col][k] /= d;
+            for (int q = 0; q < 4; ++q) if (q != col) { const long double f = V[q][col]; for (int k = 0; k < 8; ++k) V[q][k] -= f * V[col][k]; }
+        }
+        for (int q = 0; q < 4; ++q) for (int k = 0; k < 4; ++k) fit.m[q][k] = (double)V[q][4 + k];
+    }
     const int n_rb = (n_l1 + 127) / 128;
     const size_t su_bytes = (size_t)n_special * n_phi * 8 * 8, snu_bytes = (size_t)n_special * n_phi * 8;
     if (c->n0_L.reserve((size_t)n_L * 8) || c->s0.reserve((size_t)n_l1 * 8) || c->s1.reserve((size_t)n_l1 * 8) ||
         c->n0_rowflag.reserve((size_t)n_l1 * 4) || c->n0_G.reserve((size_t)c->n_ell * 8 + 64) || c->n0_phi.reserve((ph.size() + phf.size()) * 8) ||
         c->n0_utab.reserve((size_t)n_l1 * sizeof(URow)) ||
         c->n0_partial.reserve((size_t)5 * (std::max((long long)n_chunk * npairs, (long long)n_L * n_rb) + npairs_full) * 8) || c->n0_out.reserve((size_t)6 * n_L * 8) ||
-        c->s2.reserve(su_bytes + 64) || c->s3.reserve(snu_bytes + 64) || c->s4.reserve((size_t)n_special * 4 + 64))
+        (variant == 3 && c->cl_poly.reserve((size_t)LBG_PAIR_STRIDE * 8 * 32)) || c->s2.reserve(su_bytes + 64) || c->s3.reserve(snu_bytes + 64) || c->s4.reserve((size_t)n_special * 4 + 64))
         return LBG_ENOMEM;
     cudaStream_t st = c->stream;
     double* d_ph = c->n0_phi.as<double>();
@@ -787,7 +1013,22 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
                                                                c->cl_rows.as<ClRow>(), c->s2.as<double>() + (size_t)n_exact * n_phi * 8);
         t.launched();
     }
-    if (variant == 2) {
+    if (variant == 3) {
+        std::vector<double> cw(2 * (size_t)n_phe);
+        for (int j = 0; j < n_phe; ++j) { cw[2 * j] = ph[j]; cw[2 * j + 1] = ph[2 * (size_t)n_phe + j]; }
+        LBG_CUDA(cudaMemcpyToSymbolAsync(c_cw, cw.data(), cw.size() * 8, 0, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaStreamSynchronize(st));      // cw is a local
+        const int n_int = c->n_ell - 1;
+        n0_poly_table_kernel<<<(n_int + 127) / 128, 128, 0, st>>>(P, fit, n_int, c->cl_soa.as<double>(), c->cl_poly.as<double4>());
+        t.launched();
+        const bool full = terms_mask == (LBG_TT | LBG_TE | LBG_EE | LBG_EB);
+        const dim3 grid(n_rb, n_L);
+#define LBG_R3(UB, FULL) n0_rows3_kernel<UB, FULL><<<grid, 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), \
+                             c->cl_poly.as<double4>(), c->cl_soa.as<double>(), d_part)
+        if (c->ub_zero) { if (full) LBG_R3(false, true); else LBG_R3(false, false); }
+        else            { if (full) LBG_R3(true, true);  else LBG_R3(true, false); }
+#undef LBG_R3
+    } else if (variant == 2) {
         const double xmax = P.a * 2.0 * (double)c->n_ell;                 // largest Taylor argument of the noise factor
         const size_t smem = ((size_t)4 * n_phe + 5 * 4) * 8;
         n0_noise_knots_kernel<<<(c->n_ell + 255) / 256, 256, 0, st>>>(c->n_ell, P.a, c->n0_G.as<double>());
