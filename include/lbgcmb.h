@@ -38,6 +38,11 @@ const char* lbg_version(void);
 /* Device time (ms, CUDA events on the context's stream) spent in the kernels of the last compute call,
  * and the number of kernel launches that call made. */
 int         lbg_last_kernel_ms(lbg_ctx* ctx, double* ms, int* launches);
+/* Device time (ms) of the dominant kernel alone in the last lbg_n0_ho02 call (the integrand kernel, n0_rows3_kernel by
+ * default): CUDA events on the context's stream right around that one launch.  Numerator of bench.py's roofline. */
+int         lbg_last_main_kernel_ms(lbg_ctx* ctx, double* ms);
+/* Device time (CUDA events on the context stream) and kernel launches summed over every call since the last reset. */
+int         lbg_kernel_totals(lbg_ctx* ctx, double* ms, long long* launches, int reset);
 /* Dependent-DFMA micro-benchmark: measured FP64 FMA throughput of this GPU in TFLOP/s (FMA = 2 flop).
  * This is the denominator of the N0 roofline. */
 int         lbg_fp64_peak(lbg_ctx* ctx, double* tflops);

@@ -16,7 +16,15 @@ params = get_params()
 
 
 def _each(f, zs):
-    """b(z) sampled one node at a time, the way the reference calls it inside its z loop (Cgg.py:58)."""
+    """b(z) on every node of the z grid.  The reference calls it one node at a time inside its z loop (Cgg.py:58); an
+    array-capable callable gives the same numbers in one call, anything else (scalar-only branches such as
+    interloper.py:156, np.vectorize'd tables that return the wrong shape) is sampled node by node as the reference does."""
+    try:
+        v = np.asarray(f(zs), dtype=np.float64)
+        if v.shape == zs.shape:
+            return v
+    except Exception:
+        pass
     return np.array([float(f(z)) for z in zs])
 
 

@@ -77,8 +77,15 @@ def _exact_u_rows(lensCl_interps, nolensCl_interps, ell, cphi, sphi, below):
         for name in ('TT', 'TE', 'EE', 'BB'):
             f = interps[name]
             if not isinstance(f, interp1d):
-                f = interp1d(np.arange(table_of(f).size, dtype=np.float64), table_of(f), kind='cubic',
-                             bounds_error=False, fill_value=0.0)
+                g = getattr(f, '_scipy_interp1d', None)                # built once per table-backed callable
+                if g is None:
+                    g = interp1d(np.arange(table_of(f).size, dtype=np.float64), table_of(f), kind='cubic',
+                                 bounds_error=False, fill_value=0.0)
+                    try:
+                        f._scipy_interp1d = g
+                    except AttributeError:
+                        pass
+                f = g
             vals[:, :, k] = f(nu)
             k += 1
     return np.ascontiguousarray(rows), np.ascontiguousarray(vals)
@@ -118,7 +125,7 @@ def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'
                                       exact_rows.size, exact_rows.ctypes.data_as(_ffi.c_int_p), _ffi._dp(exact_u),
                                       _ffi._dp(out), _ffi._dp(out_terms), C.byref(nodes)))
     ms, launches = ctx.last_kernel_ms()
-    last_stats.update(nodes=nodes.value, kernel_ms=ms, launches=launches, n_L=Ld.size)
+    last_stats.update(nodes=nodes.value, kernel_ms=ms, launches=launches, n_L=Ld.size, main_kernel_ms=ctx.last_main_kernel_ms())
     return out, {t: out_terms[i] for i, t in enumerate(('TT', 'TE', 'EE', 'EB', 'BB'))}
 
 

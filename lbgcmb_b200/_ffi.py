@@ -53,6 +53,8 @@ def _declare(L):
         'lbg_ctx_create': [i, C.POINTER(vp)],
         'lbg_ctx_destroy': [vp],
         'lbg_last_kernel_ms': [vp, c_double_p, c_int_p],
+        'lbg_last_main_kernel_ms': [vp, c_double_p],
+        'lbg_kernel_totals': [vp, c_double_p, c_ll_p, i],
         'lbg_fp64_peak': [vp, c_double_p],
         'lbg_upload_cl_tables': [vp, i, c_double_p, c_double_p],
         'lbg_eval_cl': [vp, i, i, i, c_double_p, c_double_p],
@@ -115,6 +117,17 @@ class Context:
     def last_kernel_ms(self):
         ms, n = C.c_double(), C.c_int()
         check(lib().lbg_last_kernel_ms(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def last_main_kernel_ms(self):
+        v = C.c_double()
+        check(lib().lbg_last_main_kernel_ms(self._h, C.byref(v)))
+        return v.value
+
+    def kernel_totals(self, reset=False):
+        """(device ms, kernel launches) summed over every library call on this context since the last reset."""
+        ms, n = C.c_double(), C.c_longlong()
+        check(lib().lbg_kernel_totals(self._h, C.byref(ms), C.byref(n), int(bool(reset))))
         return ms.value, n.value
 
     def fp64_peak_tflops(self):

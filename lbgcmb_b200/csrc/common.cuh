@@ -63,8 +63,12 @@ struct lbg_ctx {
     int          sm_count = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t  ev2 = nullptr, ev3 = nullptr;   // around the dominant kernel of the last call (roofline timing)
+    double       last_main_ms = 0.0;
     double       last_ms = 0.0;
     int          last_launches = 0;
+    double       total_ms = 0.0;     // since the last lbg_kernel_totals(reset)
+    long long    total_launches = 0;
     std::mutex   mu;
     // CMB tables
     int          n_ell = 0;          // knots 0..n_ell-1
@@ -93,7 +97,7 @@ struct KernelTimer {   // records ev0/ev1 on the context stream around the kerne
     int finish() {
         cudaError_t e = cudaEventRecord(c->ev1, c->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-        if (e == cudaSuccess) { float ms = 0.f; e = cudaEventElapsedTime(&ms, c->ev0, c->ev1); c->last_ms = ms; }
+        if (e == cudaSuccess) { float ms = 0.f; e = cudaEventElapsedTime(&ms, c->ev0, c->ev1); c->last_ms = ms; c->total_ms += ms; c->total_launches += c->last_launches; }
         if (e == cudaSuccess) e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("kernel execution failed: %s", cudaGetErrorString(e)); return LBG_ECUDA; }
         return LBG_OK;

@@ -101,6 +101,8 @@ extern "C" int lbg_ctx_create(int device, lbg_ctx** out) {
     LBG_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     LBG_CUDA(cudaEventCreate(&c->ev0));
     LBG_CUDA(cudaEventCreate(&c->ev1));
+    LBG_CUDA(cudaEventCreate(&c->ev2));
+    LBG_CUDA(cudaEventCreate(&c->ev3));
     *out = c;
     return LBG_OK;
 }
@@ -112,7 +114,7 @@ extern "C" int lbg_ctx_destroy(lbg_ctx* c) {
     for (DevBuf* b : {&c->cl_rows, &c->cl_soa, &c->cl_pairs, &c->cl_poly, &c->n0_L, &c->n0_utab, &c->n0_phi, &c->n0_partial, &c->n0_out, &c->n0_rowflag, &c->n0_G,
                       &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->pk_lnk, &c->pk_plin, &c->pk_pnl})
         b->release();
-    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->stream);
     delete c;
     return LBG_OK;
@@ -122,6 +124,21 @@ extern "C" int lbg_last_kernel_ms(lbg_ctx* c, double* ms, int* launches) {
     LBG_REQUIRE(c, "lbg_last_kernel_ms: ctx is NULL");
     if (ms) *ms = c->last_ms;
     if (launches) *launches = c->last_launches;
+    return LBG_OK;
+}
+
+extern "C" int lbg_last_main_kernel_ms(lbg_ctx* c, double* ms) {
+    LBG_REQUIRE(c && ms, "lbg_last_main_kernel_ms: NULL argument");
+    *ms = c->last_main_ms;
+    return LBG_OK;
+}
+
+extern "C" int lbg_kernel_totals(lbg_ctx* c, double* ms, long long* launches, int reset) {
+    LBG_REQUIRE(c, "lbg_kernel_totals: ctx is NULL");
+    std::lock_guard<std::mutex> g(c->mu);
+    if (ms) *ms = c->total_ms;
+    if (launches) *launches = c->total_launches;
+    if (reset) { c->total_ms = 0.0; c->total_launches = 0; }
     return LBG_OK;
 }
 

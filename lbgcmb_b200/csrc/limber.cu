@@ -7,6 +7,7 @@
 // host with the same scipy routine the reference calls (SURVEY.md "hard parts"); everything per (z,k) or (l,z) is here.
 #include "common.cuh"
 #include <cmath>
+#include <algorithm>
 
 namespace lbg {
 
@@ -106,24 +107,33 @@ __device__ __forceinline__ double interp_k(const double* __restrict__ ks, const 
 }
 
 #define LIMBER_BT 8
-// C_l[b][l] = sum_z weight[b][z] * P_z(k = (l + 1/2) / chi_z).  Block = 128 consecutive l for one batch entry; the k grid
-// sits in shared memory (binary search), the P(k,z) table rows stream from L2/HBM.
+#define LIMBER_ZMIN 64     /* at least this many z nodes per split */
+#define LIMBER_SMAX 32
+// Number of z splits: a function of n_z ONLY, so that a multipole's value does not depend on which other multipoles or
+// batch entries travel in the same call (tests/test_limber_gpu.py::test_limber_full_grid_properties).
+static inline int limber_splits(int n_z) { return std::max(1, std::min(LIMBER_SMAX, n_z / LIMBER_ZMIN)); }
+
+// partial[s][b][l] = sum_{z in split s} weight[b][z] * P_z(k = (l + 1/2) / chi_z).
+// Block = 128 consecutive l x up to LIMBER_BT batch entries (they share each P lookup) x one z split; the k grid sits in
+// shared memory (binary search), the P(k,z) table rows stream from L2.  148 SMs want >= ~600 blocks: Ckk on 4951 l is
+// 39 l-blocks x 31 splits.  Sums run in z order inside a split and in split order in limber_reduce_kernel (deterministic).
 __global__ void __launch_bounds__(128)
-limber_kernel(int n_batch, int n_ell, int n_z, int n_k, const double* __restrict__ ell, const double* __restrict__ chi,
+limber_kernel(int n_batch, int n_ell, int n_z, int n_k, int z_per_split, const double* __restrict__ ell, const double* __restrict__ chi,
               const double* __restrict__ weight /*[n_batch][n_z]*/, const int* __restrict__ prow /*[n_z] table row per z node*/,
-              const double* __restrict__ ks, const double* __restrict__ ptab, int oob, double* __restrict__ out) {
+              const double* __restrict__ ks, const double* __restrict__ ptab, int oob, double* __restrict__ partial) {
     extern __shared__ double sk[];
     for (int i = threadIdx.x; i < n_k; i += blockDim.x) sk[i] = ks[i];
     __syncthreads();
     const int il = blockIdx.x * blockDim.x + threadIdx.x;
-    const int b0 = blockIdx.y * LIMBER_BT;                  // tile of up to LIMBER_BT batch entries shares each P lookup
+    const int b0 = blockIdx.y * LIMBER_BT;
     const int nb = min(LIMBER_BT, n_batch - b0);
+    const int z0 = blockIdx.z * z_per_split, z1 = min(n_z, z0 + z_per_split);
     if (il >= n_ell) return;
     const double lp = ell[il] + 0.5;
     double acc[LIMBER_BT];
 #pragma unroll
     for (int q = 0; q < LIMBER_BT; ++q) acc[q] = 0.0;
-    for (int iz = 0; iz < n_z; ++iz) {
+    for (int iz = z0; iz < z1; ++iz) {
         bool any = false;
         for (int q = 0; q < nb; ++q) any = any || (weight[(size_t)(b0 + q) * n_z + iz] != 0.0);
         if (!any) continue;                                  // block-uniform
@@ -135,7 +145,15 @@ limber_kernel(int n_batch, int n_ell, int n_z, int n_k, const double* __restrict
     }
 #pragma unroll
     for (int q = 0; q < LIMBER_BT; ++q)
-        if (q < nb) out[(size_t)(b0 + q) * n_ell + il] = acc[q];
+        if (q < nb) partial[((size_t)blockIdx.z * n_batch + b0 + q) * n_ell + il] = acc[q];
+}
+
+__global__ void limber_reduce_kernel(size_t n, int n_split, const double* __restrict__ partial, double* __restrict__ out) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    double v = partial[t];
+    for (int s = 1; s < n_split; ++s) v += partial[(size_t)s * n + t];
+    out[t] = v;
 }
 
 __global__ void pk_eval_kernel(int n, int n_k, const double* __restrict__ ks, const double* __restrict__ prow_ptr,
@@ -215,6 +233,8 @@ extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell,
     LBG_CUDA(cudaSetDevice(c->device));
     const size_t bw = (size_t)n_batch * n_z * 8, bo = (size_t)n_batch * n_ell * 8;
     if (c->s0.reserve((size_t)n_ell * 8) || c->s1.reserve((size_t)n_z * 8) || c->s2.reserve(bw) || c->s3.reserve((size_t)n_z * 4) || c->s4.reserve(bo)) return LBG_ENOMEM;
+    const int n_split = limber_splits(n_z), z_per_split = (n_z + n_split - 1) / n_split;
+    if (n_split > 1 && c->s5.reserve(bo * n_split)) return LBG_ENOMEM;
     cudaStream_t st = c->stream;
     LBG_CUDA(cudaMemcpyAsync(c->s0.p, ell, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s1.p, chi, (size_t)n_z * 8, cudaMemcpyHostToDevice, st));
@@ -223,10 +243,16 @@ extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell,
     const size_t smem = (size_t)c->n_k * 8;
     if (smem > 48 * 1024) LBG_CUDA(cudaFuncSetAttribute(limber_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     KernelTimer t(c);
-    limber_kernel<<<dim3((n_ell + 127) / 128, (n_batch + LIMBER_BT - 1) / LIMBER_BT), 128, smem, st>>>(n_batch, n_ell, n_z, c->n_k, c->s0.as<double>(), c->s1.as<double>(),
-                                                                        c->s2.as<double>(), c->s3.as<int>(), c->pk_lnk.as<double>(),
-                                                                        c->pk_pnl.as<double>(), oob, c->s4.as<double>());
+    double* part = n_split > 1 ? c->s5.as<double>() : c->s4.as<double>();
+    limber_kernel<<<dim3((n_ell + 127) / 128, (n_batch + LIMBER_BT - 1) / LIMBER_BT, n_split), 128, smem, st>>>(
+        n_batch, n_ell, n_z, c->n_k, z_per_split, c->s0.as<double>(), c->s1.as<double>(), c->s2.as<double>(), c->s3.as<int>(),
+        c->pk_lnk.as<double>(), c->pk_pnl.as<double>(), oob, part);
     t.launched();
+    if (n_split > 1) {
+        const size_t n = (size_t)n_batch * n_ell;
+        limber_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, n_split, part, c->s4.as<double>());
+        t.launched();
+    }
     LBG_CUDA(cudaMemcpyAsync(out_cl, c->s4.p, bo, cudaMemcpyDeviceToHost, st));
     return t.finish();
 }

@@ -1021,6 +1021,7 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
         const int n_int = c->n_ell - 1;
         n0_poly_table_kernel<<<(n_int + 127) / 128, 128, 0, st>>>(P, fit, n_int, c->cl_soa.as<double>(), c->cl_poly.as<double4>());
         t.launched();
+        cudaEventRecord(c->ev2, st);
         const bool full = terms_mask == (LBG_TT | LBG_TE | LBG_EE | LBG_EB);
         const dim3 grid(n_rb, n_L);
 #define LBG_R3(UB, FULL) n0_rows3_kernel<UB, FULL><<<grid, 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), \
@@ -1044,6 +1045,7 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
                                                      c->cl_rows.as<ClRow>(), d_part);
     }
     t.launched();
+    cudaEventRecord(c->ev3, st);
     if (n_special) {
         n0_special_kernel<<<(int)((npairs_full + 127) / 128), 128, 0, st>>>(P, n_special, n_phi, c->s4.as<int>(), c->n0_L.as<double>(), d_phf,
                                                                             c->n0_utab.as<URow>(), c->s2.as<double>(), c->s3.as<double>(),
@@ -1059,6 +1061,7 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     LBG_CUDA(cudaMemcpyAsync(host.data(), c->n0_out.p, host.size() * 8, cudaMemcpyDeviceToHost, st));
     int rc = t.finish();
     if (rc) return rc;
+    { float ms = 0.f; c->last_main_ms = (variant == 3 && cudaEventElapsedTime(&ms, c->ev2, c->ev3) == cudaSuccess) ? ms : c->last_ms; }
     memcpy(out_nkk, host.data(), (size_t)n_L * 8);
     if (out_terms) memcpy(out_terms, host.data() + n_L, (size_t)5 * n_L * 8);
     if (nodes_executed) *nodes_executed = npairs * (active_rows - n_special) + npairs_full * n_special;

