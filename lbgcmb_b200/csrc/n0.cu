@@ -587,11 +587,12 @@ struct RowGeom { double L2, l2, rl2x2, lL, m2lL, l2pL2; };   // per-thread const
 
 template <bool DO_T, bool HAS_UB, bool FULL>
 __device__ __forceinline__ void n0_poly_node(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
-                                             bool actT, bool actP, const double2 cw,
+                                             bool actT, bool actP, const double2 cw, bool& any_rare,
                                              double& aTT, double& aTE, double& aEE, double& aEB) {
     const double nv2 = fma(g.m2lL, cw.x, g.l2pL2);               // |v|^2 = l^2 + L^2 - 2 l L cos phi
     const unsigned hi = (unsigned)__double2hiint(nv2);
     const bool rare = (hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2];
+    any_rare = any_rare || rare;                                 // the bit-faithful second pass only runs for rows that saw one
     const bool vok = !rare && hi > P.near_lo[0];
     const bool okT = DO_T && actT && vok && hi < P.near_lo[1];
     const bool okP = actP && vok && hi < P.near_lo[2];
@@ -646,19 +647,24 @@ __device__ __forceinline__ void n0_poly_node(const N0Params& P, const double4* _
     aEB = fma(cw.y, okP ? eb : 0.0, aEB);
 }
 
+#ifndef LBG_ROWS3_UNROLL
+#define LBG_ROWS3_UNROLL 2
+#endif
 template <bool DO_T, bool HAS_UB, bool FULL>
 __device__ __forceinline__ void n0_rows3_loop(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
-                                              bool actT, bool actP, double& aTT, double& aTE, double& aEE, double& aEB) {
+                                              bool actT, bool actP, bool& any_rare, double& aTT, double& aTE, double& aEE, double& aEB) {
     int j = 0;
+#if LBG_ROWS3_UNROLL >= 2
     for (; j + 1 < P.n_phi; j += 2) {      // two independent nodes per trip: ILP for the FP64 pipe
-        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], aTT, aTE, aEE, aEB);
-        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j + 1], aTT, aTE, aEE, aEB);
+        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], any_rare, aTT, aTE, aEE, aEB);
+        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j + 1], any_rare, aTT, aTE, aEE, aEB);
     }
-    if (j < P.n_phi) n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], aTT, aTE, aEE, aEB);
+#endif
+    for (; j < P.n_phi; ++j) n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], any_rare, aTT, aTE, aEE, aEB);
 }
 
 #ifndef LBG_ROWS3_MINB
-#define LBG_ROWS3_MINB 4
+#define LBG_ROWS3_MINB 5
 #endif
 template <bool HAS_UB, bool FULL>
 __global__ void __launch_bounds__(128, LBG_ROWS3_MINB)
@@ -689,10 +695,11 @@ n0_rows3_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
     RowGeom g;
     g.L2 = L * L; g.l2 = l * l; g.rl2x2 = 2.0 / g.l2; g.lL = l * L; g.m2lL = -2.0 * g.lL; g.l2pL2 = g.l2 + g.L2;
     double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
-    if (s_anyT) n0_rows3_loop<true, HAS_UB, FULL>(P, ptab, g, u, actT, actP, aTT, aTE, aEE, aEB);
-    else        n0_rows3_loop<false, HAS_UB, FULL>(P, ptab, g, u, actT, actP, aTT, aTE, aEE, aEB);
+    bool any_rare = false;
+    if (s_anyT) n0_rows3_loop<true, HAS_UB, FULL>(P, ptab, g, u, actT, actP, any_rare, aTT, aTE, aEE, aEB);
+    else        n0_rows3_loop<false, HAS_UB, FULL>(P, ptab, g, u, actT, actP, any_rare, aTT, aTE, aEE, aEB);
     // second pass: nodes within 4e-6 of a cut in |v|^2, evaluated exactly as the reference rounds them
-    if (act) {
+    if (act && any_rare) {
         const bool fold = P.fold != 0;
         for (int j = 0; j < P.n_phi; ++j) {
             const double nv2 = fma(g.m2lL, c_cw[j].x, g.l2pL2);
