@@ -147,6 +147,18 @@ int lbg_mqw_fisher(lbg_ctx* ctx, int n_ell, int n_bin, const double* cgg, int cg
                    const double* mode_weight /*[n_ell]*/, double fsky, double* out_F, double* out_Fsl /*or NULL*/,
                    double* out_S /*or NULL*/);
 
+/* ---- survey-design grid (BASELINE configs[4]): for every (noise level n, galaxy configuration g) the cumulative S/N of
+ *      C_kg (snr.py:118-124 with the Ckg.py:83-87 variance) and the (sigma8, b1) Fisher matrix + interloper bias vector of
+ *      D = (C_kk, C_kg, C_gg) (interloper.py:200-253) -- the same per-multipole arithmetic as lbg_gaussian_cov +
+ *      lbg_fisher_accum + lbg_snr, one CTA per design.
+ *      cgg/ckg[n_cfg][n_ell]; xcgg/xckg: interloper-contaminated spectra (both NULL: no bias vector);
+ *      cfg[n_cfg][8] = {N_gg, contaminated N_gg, fiducial b1, L cut of the Fisher sums (L < cut), L cut of the S/N (L <= cut), -,-,-};
+ *      nkk[n_noise][n_ell] = N0 per noise level;  out[n_noise][n_cfg][8] = {S/N, F00, F01, F10, F11, b0, b1, 0}
+ *      (S/N is not divided by sqrt(fsky); parameters in the order sigma8, b1). */
+int lbg_forecast_grid(lbg_ctx* ctx, int n_ell, const double* ell, const double* nmodes, const double* ckk,
+                      int n_cfg, const double* cgg, const double* ckg, const double* xcgg, const double* xckg,
+                      const double* cfg, int n_noise, const double* nkk, double fsky, double fid_sig8, double* out);
+
 #ifdef __cplusplus
 }
 #endif

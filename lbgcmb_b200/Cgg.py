@@ -28,27 +28,43 @@ def _each(f, zs):
     return np.array([float(f(z)) for z in zs])
 
 
-def Cgg(Pk_interps, Llls, zmin, zmax, survey_pz, bz, survey_pz2=None, bz2=None, zeff=True):
+def cgg_nodes(zmin, zmax):
+    """z nodes, chi(z) and scipy-1.2.1 Simpson weights of Cgg.py:18-19,68."""
     dz = 0.01
     zs = np.arange(zmin, zmax + dz, dz)
-    ps = survey_pz(zs)
-    norm = np.sum(ps) * dz
-    ps = ps / norm
-    chis = comoving_distance(zs)
+    return zs, comoving_distance(zs), simps_weights(zs.size, dz)
+
+
+def cgg_weights(zs, chis, w, zmin, zmax, survey_pz, bz, survey_pz2=None, bz2=None):
+    """Per-node Limber weights of the full z integral (Cgg.py:53-68): quadrature weight x (H/c) p1 p2 / chi^2 x b1 b2 / h."""
     if bz2 is None:
         bz2 = bz
     if survey_pz2 is None:
         survey_pz2 = survey_pz
-    engine, nonlinear = engine_of(Pk_interps, 'nlinear')
     prefactor = (cosmo.H(zs).value / C_KMS) * sliced_pz(zs, zmin, zmax, survey_pz) \
         * sliced_pz(zs, zmin, zmax, survey_pz2) / chis ** 2.
-    w = simps_weights(zs.size, dz)                                      # Cgg.py:68
+    return w * prefactor * _each(bz, zs) * _each(bz2, zs) / params['h_100']
+
+
+def Cgg(Pk_interps, Llls, zmin, zmax, survey_pz, bz, survey_pz2=None, bz2=None, zeff=True):
+    dz = 0.01
+    zs, chis, w = cgg_nodes(zmin, zmax)
+    engine, nonlinear = engine_of(Pk_interps, 'nlinear')
     Ld = np.asarray(Llls, dtype=np.float64)
     if zeff:
+        if bz2 is None:
+            bz2 = bz
+        if survey_pz2 is None:
+            survey_pz2 = survey_pz
+        ps = survey_pz(zs)
+        norm = np.sum(ps) * dz
+        ps = ps / norm
+        prefactor = (cosmo.H(zs).value / C_KMS) * sliced_pz(zs, zmin, zmax, survey_pz) \
+            * sliced_pz(zs, zmin, zmax, survey_pz2) / chis ** 2.
         zz = dz * np.sum(ps * zs) / (np.sum(ps) * dz)                   # Cgg.py:46
         amp = float(bz(zz)) * float(bz2(zz)) * np.sum(w * prefactor) / params['h_100']
         return engine.limber(Ld, [zz], [comoving_distance(zz)], [[amp]], nonlinear=nonlinear)[0]
-    weights = w * prefactor * _each(bz, zs) * _each(bz2, zs) / params['h_100']
+    weights = cgg_weights(zs, chis, w, zmin, zmax, survey_pz, bz, survey_pz2, bz2)
     return engine.limber(Ld, zs, chis, weights[None, :], nonlinear=nonlinear)[0]
 
 

@@ -13,22 +13,34 @@ from lbgcmb_b200.utils import comoving_distance
 params = get_params()
 
 
-def Ckg(Pk_interps, Llls, zmin, zmax, survey_pz, bz, zeff=True):
+def ckg_nodes(zmin, zmax):
+    """z nodes (no end point, Ckg.py:19-20), chi(z) and Simpson weights (even length -> scipy-1.2.1 'avg' rule)."""
     dz = 0.01
     zs = np.arange(zmin, zmax, dz)
-    ps = survey_pz(zs)
-    norm = np.sum(ps) * dz
-    ps = ps / norm
+    return zs, comoving_distance(zs), simps_weights(zs.size, zs[1] - zs[0])
+
+
+def ckg_weights(zs, chis, w, zmin, zmax, survey_pz, bz):
+    """Per-node Limber weights of the full z integral (Ckg.py:42-57): quadrature x W_kappa p / chi^2 x b / h^2."""
+    prefactor = lensing_kernel(zs) * sliced_pz(zs, zmin, zmax, survey_pz) / chis ** 2.
+    return w * prefactor * _each(bz, zs) / params['h_100'] ** 2.
+
+
+def Ckg(Pk_interps, Llls, zmin, zmax, survey_pz, bz, zeff=True):
+    dz = 0.01
     engine, nonlinear = engine_of(Pk_interps, 'nlinear')
     Ld = np.asarray(Llls, dtype=np.float64)
     if zeff:
+        zs = np.arange(zmin, zmax, dz)
+        ps = survey_pz(zs)
+        norm = np.sum(ps) * dz
+        ps = ps / norm
         zg = np.sum(ps * zs) * dz / np.sum(dz * ps)                     # Ckg.py:29
         chi_g = comoving_distance(zg)
         amp = float(bz(zg)) * lensing_kernel(zg) / chi_g ** 2. / params['h_100'] ** 2.
         return engine.limber(Ld, [zg], [chi_g], [[amp]], nonlinear=nonlinear)[0]
-    chis = comoving_distance(zs)
-    prefactor = lensing_kernel(zs) * sliced_pz(zs, zmin, zmax, survey_pz) / chis ** 2.
-    weights = simps_weights(zs.size, zs[1] - zs[0]) * prefactor * _each(bz, zs) / params['h_100'] ** 2.
+    zs, chis, w = ckg_nodes(zmin, zmax)
+    weights = ckg_weights(zs, chis, w, zmin, zmax, survey_pz, bz)
     return engine.limber(Ld, zs, chis, weights[None, :], nonlinear=nonlinear)[0]
 
 

@@ -7,29 +7,10 @@
 // The work is tiny at reference sizes (<= 4951 multipoles, matrices <= 20 x 20): these kernels are latency bound and
 // no roofline fraction is claimed for them.
 #include "common.cuh"
+#include "fisher_dev.cuh"
 #include <cmath>
 
 namespace lbg {
-
-constexpr int RED_T = 256;
-
-// Block-wide sum of `nv` values per thread (nv <= 32 per pass); result valid in thread 0.
-template <int NV>
-__device__ __forceinline__ void block_sum(double (&v)[NV], double* sm /*[NV][RED_T]*/) {
-#pragma unroll
-    for (int q = 0; q < NV; ++q) sm[q * RED_T + threadIdx.x] = v[q];
-    __syncthreads();
-    for (int h = RED_T / 2; h > 0; h >>= 1) {
-        if (threadIdx.x < h) {
-#pragma unroll
-            for (int q = 0; q < NV; ++q) sm[q * RED_T + threadIdx.x] += sm[q * RED_T + threadIdx.x + h];
-        }
-        __syncthreads();
-    }
-#pragma unroll
-    for (int q = 0; q < NV; ++q) v[q] = sm[q * RED_T];
-    __syncthreads();
-}
 
 // snr.py:21-25: sum over l <= lmax of nmodes (C / sqrt(Var))^2 ; one block, fixed order.
 __global__ void __launch_bounds__(RED_T)
@@ -57,50 +38,7 @@ __global__ void gaussian_cov_kernel(int n_ell, int n_f, int n_spec, const double
     const int j = (int)(t % n_spec), i = (int)((t / n_spec) % n_spec), l = (int)(t / ((long long)n_spec * n_spec));
     const double* T = tot + (size_t)l * n_f * n_f;
     const int a = sa[i], b = sb[i], c = sa[j], d = sb[j];
-    double r = __dmul_rn(T[a * n_f + c], T[b * n_f + d]);
-    r = __dadd_rn(r, __dmul_rn(T[a * n_f + d], T[b * n_f + c]));
-    r = __ddiv_rn(r, __dadd_rn(__dmul_rn(2.0, ell[l]), 1.0));
-    cov[t] = __ddiv_rn(r, fsky);
-}
-
-// In-thread solve of the symmetric system C X = B by LU with partial pivoting after symmetric diagonal equilibration
-// (C_ij / sqrt(C_ii C_jj)): band-power covariances span many decades between kk and gg, the correlation matrix does not.
-template <int MS, int MR>
-__device__ void solve_spd(int ns, int nr, double* A /*[ns][ns], destroyed*/, double* B /*[nr][ns] in, solution out*/) {
-    double sc[MS];
-    for (int i = 0; i < ns; ++i) sc[i] = 1.0 / sqrt(fabs(A[i * ns + i]));
-    for (int i = 0; i < ns; ++i)
-        for (int j = 0; j < ns; ++j) A[i * ns + j] *= sc[i] * sc[j];
-    for (int r = 0; r < nr; ++r)
-        for (int i = 0; i < ns; ++i) B[r * ns + i] *= sc[i];
-    for (int k = 0; k < ns; ++k) {
-        int p = k;
-        double best = fabs(A[k * ns + k]);
-        for (int i = k + 1; i < ns; ++i) {
-            const double v = fabs(A[i * ns + k]);
-            if (v > best) { best = v; p = i; }
-        }
-        if (p != k) {
-            for (int j = 0; j < ns; ++j) { const double t = A[k * ns + j]; A[k * ns + j] = A[p * ns + j]; A[p * ns + j] = t; }
-            for (int r = 0; r < nr; ++r) { const double t = B[r * ns + k]; B[r * ns + k] = B[r * ns + p]; B[r * ns + p] = t; }
-        }
-        const double piv = 1.0 / A[k * ns + k];
-        for (int i = k + 1; i < ns; ++i) {
-            const double f = A[i * ns + k] * piv;
-            if (f != 0.0) {
-                for (int j = k + 1; j < ns; ++j) A[i * ns + j] -= f * A[k * ns + j];
-                for (int r = 0; r < nr; ++r) B[r * ns + i] -= f * B[r * ns + k];
-            }
-        }
-    }
-    for (int r = 0; r < nr; ++r)
-        for (int i = ns - 1; i >= 0; --i) {
-            double s = B[r * ns + i];
-            for (int j = i + 1; j < ns; ++j) s -= A[i * ns + j] * B[r * ns + j];
-            B[r * ns + i] = s / A[i * ns + i];
-        }
-    for (int r = 0; r < nr; ++r)
-        for (int i = 0; i < ns; ++i) B[r * ns + i] *= sc[i];
+    cov[t] = gaussian_cov_entry(T, n_f, a, b, c, d, ell[l], fsky);
 }
 
 constexpr int MAX_PAR = 8;

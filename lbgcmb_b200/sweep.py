@@ -1,0 +1,103 @@
+"""Survey-design sweep (BASELINE.json configs[4]): N0 + S/N + (sigma8, b1) Fisher over beam x noise x n(z) configurations,
+sharded over the GPUs of one box.
+
+The reference has no such driver: it loops `Nkk` over experiments (snr.py:108-116, bolometers.py) and re-runs its scripts
+per dropout band.  Here the same per-design arithmetic -- Nkk.Nkk per (thetab, DeltaT, iterative); Cgg.Cgg / Ckg.Ckg
+(zeff=False) / lensing.Ckk per n(z); snr.snr on the Ckg.var_Ckg variance; interloper.get_ClsCov + the Fisher / bias sums of
+interloper.py:200-260 -- runs as
+  * one N0 launch per noise level (csrc/n0.cu; the dominant cost, independent per level -> the unit that is sharded),
+  * ONE batched Limber launch per spectrum type for all n(z) configurations (csrc/limber.cu, batch axis),
+  * ONE launch for the whole noise x n(z) grid of S/N + Fisher problems (csrc/sweep.cu, lbg_forecast_grid).
+Multi-GPU: rank r takes a contiguous block of noise levels (dist.shard_slice); no data-path collective;
+the [n_noise, n_cfg, 8] result blocks are concatenated in rank order at the end (dist.allgather_concat)."""
+import numpy as np
+
+from lbgcmb_b200 import _ffi
+from lbgcmb_b200 import dist as _dist
+from lbgcmb_b200.Cgg import Ngg, cgg_nodes, cgg_weights
+from lbgcmb_b200.Ckg import ckg_nodes, ckg_weights
+from lbgcmb_b200.pmh import engine_of
+
+OUT_FIELDS = ('snr', 'F_s8s8', 'F_s8b1', 'F_b1s8', 'F_b1b1', 'bias_s8', 'bias_b1')
+
+
+def limber_grid(Pk_interps, Llls, samples, zmin=0.01, zmax=10.0):
+    """C_gg[n, n_l], C_kg[n, n_l], N_gg[n] for samples = [{'pz', 'bz', 'nbar'}, ...] on a common z range: what
+    Cgg.Cgg(..., zeff=False), Ckg.Ckg(..., zeff=False) and Cgg.Ngg return per sample, from two batched launches."""
+    engine, nonlinear = engine_of(Pk_interps, 'nlinear')
+    Ld = np.asarray(Llls, dtype=np.float64)
+    zs, chis, w = cgg_nodes(zmin, zmax)
+    wg = np.stack([cgg_weights(zs, chis, w, zmin, zmax, s['pz'], s['bz']) for s in samples])
+    cgg = engine.limber(Ld, zs, chis, wg, nonlinear=nonlinear)
+    zs, chis, w = ckg_nodes(zmin, zmax)
+    wk = np.stack([ckg_weights(zs, chis, w, zmin, zmax, s['pz'], s['bz']) for s in samples])
+    ckg = engine.limber(Ld, zs, chis, wk, nonlinear=nonlinear)
+    ngg = np.array([Ngg(Ld[:1], zmin, zmax, s['pz'], s['nbar'])[0] for s in samples])
+    return cgg, ckg, ngg
+
+
+def forecast_grid(Llls, nmodes, ckk, cgg, ckg, ngg, nkk, fsky, fid_sig8, fid_b1, LllMax, snr_lmax=None,
+                  xcgg=None, xckg=None, xngg=None, device=None):
+    """out[n_noise, n_cfg, 8] = (S/N, F_s8s8, F_s8b1, F_b1s8, F_b1b1, bias_s8, bias_b1, 0) for every (N0 curve, n(z) config).
+
+    Per design this equals snr.snr(Llls, ckg, var_Ckg, nmodes, lmax=snr_lmax) and interloper.fisher_bias(...)['Fisher'],
+    ['interim']; the contaminated spectra are optional (no bias vector without them)."""
+    ctx = _ffi.context(device)
+    L, nm, ckk = _ffi.f64(Llls), _ffi.f64(nmodes), _ffi.f64(ckk)
+    cgg, ckg, nkk = _ffi.f64(np.atleast_2d(cgg)), _ffi.f64(np.atleast_2d(ckg)), _ffi.f64(np.atleast_2d(nkk))
+    n_cfg, n_ell = cgg.shape
+    if ckg.shape != cgg.shape or nkk.shape[1] != n_ell or L.shape != (n_ell,) or nm.shape != (n_ell,) or ckk.shape != (n_ell,):
+        raise ValueError('spectra / multipole arrays disagree in shape')
+    cfg = np.zeros((n_cfg, 8))
+    cfg[:, 0] = ngg
+    cfg[:, 1] = ngg if xngg is None else xngg
+    cfg[:, 2] = fid_b1
+    cfg[:, 3] = LllMax
+    cfg[:, 4] = LllMax if snr_lmax is None else snr_lmax
+    bias = xcgg is not None
+    if bias:
+        xcgg, xckg = _ffi.f64(np.atleast_2d(xcgg)), _ffi.f64(np.atleast_2d(xckg))
+        if xcgg.shape != cgg.shape or xckg.shape != cgg.shape:
+            raise ValueError('contaminated spectra disagree in shape')
+    out = np.empty((nkk.shape[0], n_cfg, 8))
+    _ffi.check(_ffi.lib().lbg_forecast_grid(ctx.handle, n_ell, _ffi._dp(L), _ffi._dp(nm), _ffi._dp(ckk), n_cfg, _ffi._dp(cgg),
+                                            _ffi._dp(ckg), _ffi._dp(xcgg) if bias else None, _ffi._dp(xckg) if bias else None,
+                                            _ffi._dp(_ffi.f64(cfg)), nkk.shape[0], _ffi._dp(nkk), float(fsky), float(fid_sig8),
+                                            _ffi._dp(out)))
+    return out
+
+
+def survey_sweep(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noise_configs, samples, fsky,
+                 fid_sig8=0.819, xsamples=None, zmin=0.01, zmax=10.0, terms=('TT', 'TE', 'EE', 'EB'),
+                 n0_fn=None, spectra_fn=None, grid_fn=None):
+    """Full grid: noise_configs = [(thetab, DeltaT, iterative), ...] x samples = [{'pz','bz','nbar','fid_b1','LllMax'}, ...]
+    (xsamples: the interloper-contaminated twins, same length, for the bias vector).
+
+    Returns {'out': [n_noise, n_cfg, 8] (OUT_FIELDS), 'nkk': [n_noise, n_l], 'ckk', 'cgg', 'ckg', 'ngg'} on every rank.
+    Under torch.distributed each rank evaluates its own block of noise levels.  `n0_fn`, `spectra_fn`, `grid_fn` replace the
+    device calls in the CPU (gloo) tests of the sharding logic."""
+    Ld = np.asarray(Llls, dtype=np.float64)
+    if n0_fn is None:
+        from lbgcmb_b200.Nkk import n0_terms
+
+        def n0_fn(cfg):
+            return n0_terms(lensCl_interps, nolensCl_interps, Llls, terms, cfg[0], cfg[1], cfg[2])[0]
+    if spectra_fn is None:
+        from lbgcmb_b200.lensing import Ckk
+
+        def spectra_fn(smp):
+            return (Ckk(Pk_interps, Ld),) + limber_grid(Pk_interps, Ld, smp, zmin, zmax)
+    if grid_fn is None:
+        grid_fn = forecast_grid
+    ckk, cgg, ckg, ngg = spectra_fn(samples)
+    xc = spectra_fn(xsamples)[1:] if xsamples is not None else (None, None, None)
+    lo, hi = _dist.shard_slice(len(noise_configs))
+    nkk = np.array([n0_fn(cfg) for cfg in noise_configs[lo:hi]]).reshape(hi - lo, Ld.size)
+    if hi > lo:
+        out = grid_fn(Ld, nmodes, ckk, cgg, ckg, ngg, nkk, fsky, fid_sig8, [s['fid_b1'] for s in samples],
+                      [s['LllMax'] for s in samples], xcgg=xc[0], xckg=xc[1], xngg=xc[2])
+    else:
+        out = np.zeros((0, len(samples), 8))
+    out = _dist.allgather_concat(out.ravel()).reshape(len(noise_configs), len(samples), 8)
+    nkk = _dist.allgather_concat(nkk.ravel()).reshape(len(noise_configs), Ld.size)
+    return {'out': out, 'nkk': nkk, 'ckk': ckk, 'cgg': cgg, 'ckg': ckg, 'ngg': ngg}
