@@ -323,7 +323,7 @@ def main():
     e2e = units / e2e_s
     if rank == 0:
         nodes = stage['nodes']
-        main_ms = Nkk.last_stats['main_kernel_ms']               # n0_rows3_kernel alone, last step (CUDA events around the launch)
+        main_ms = Nkk.last_stats['main_kernel_ms']               # n0_rows5_kernel alone, last step (CUDA events around the launch)
         ach = nodes * OPS_PER_NODE / (main_ms * 1e-3) * 1e-12
         n_band = len(bands)
         fc_ms = (acc['all_ms'] - acc['n0_ms']) / a.steps
@@ -350,10 +350,10 @@ def main():
                     'd2h_bytes_per_step': 8 * 6 * Ls.size + d2h_fc, 'ms_per_step': e2e_s / a.steps * 1e3},
             'gpu_launches': acc['launches'],
             'roofline': {'bound': 'fp64', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak if peak else None,
-                         'traffic': N0_DRAM_BYTES_PER_LAUNCH, 'traffic_source': 'ncu --set full, profiles/ (dram__bytes_read+write of one n0_rows3 launch)',
+                         'traffic': N0_DRAM_BYTES_PER_LAUNCH, 'traffic_source': 'ncu --set full, profiles/ (dram__bytes_read+write of one n0_rows5 launch)',
                          'peak_source': 'measured DFMA micro-benchmark in this run (lbg_fp64_peak); nominal %.1f; MEASURED_PEAKS.json has no FP64 entry '
                                         '(hbm_gbs=%s is not the bound: arithmetic intensity > 1e4 flop/B)' % (FP64_NOMINAL_TFLOPS, mp.get('hbm_gbs')),
-                         'ops_per_node': OPS_PER_NODE, 'kernel': 'n0_rows3_kernel', 'kernel_ms': main_ms,
+                         'ops_per_node': OPS_PER_NODE, 'kernel': 'n0_rows5_kernel', 'kernel_ms': main_ms,
                          'kernel_share_of_step': main_ms * a.steps / all_ms},
             'clocks': clocks, 'wall_s_timed_region': t_region,
         }

@@ -577,10 +577,17 @@ __global__ void n0_poly_table_kernel(N0Params P, ChebFit F, int n_int, const dou
 #undef LBG_PUT
 }
 
+#ifndef LBG_ESTRIN
+#define LBG_ESTRIN 0
+#endif
 template <int SLOT>
-__device__ __forceinline__ double horner3(const double2* __restrict__ p, double t) {    // p = table + interval index
+__device__ __forceinline__ double horner3(const double2* __restrict__ p, double t, double t2) {    // p = table + interval index
     const double2 lo = __ldg(p + (2 * SLOT) * LBG_PAIR_STRIDE), hi = __ldg(p + (2 * SLOT + 1) * LBG_PAIR_STRIDE);
+#if LBG_ESTRIN
+    return fma(fma(hi.y, t, hi.x), t2, fma(lo.y, t, lo.x));      // two independent FMAs, then one: dependent depth 2 instead of 3
+#else
     return fma(fma(fma(hi.y, t, hi.x), t, lo.y), t, lo.x);
+#endif
 }
 
 struct RowGeom { double L2, l2, rl2x2, lL, m2lL, l2pL2; };   // per-thread constants of one (L, |u|) row
@@ -608,17 +615,18 @@ __device__ __forceinline__ void n0_poly_node(const N0Params& P, const double4* _
 
     const int i = max(min((int)nv, P.n_ell - 2), 0);
     const double t = nv - (double)i;
+    const double t2 = t * t;
     const double2* row = reinterpret_cast<const double2*>(ptab) + i;
-    const double E2 = horner3<0>(row, t), vE = horner3<2>(row, t);
-    double B2 = horner3<1>(row, t);
-    const double vB = HAS_UB ? horner3<3>(row, t) : 0.0;
+    const double E2 = horner3<0>(row, t, t2), vE = horner3<2>(row, t, t2);
+    double B2 = horner3<1>(row, t, t2);
+    const double vB = HAS_UB ? horner3<3>(row, t, t2) : 0.0;
     if (!FULL) { if (!(P.terms & LBG_EB)) B2 = 1.0; }
     const double uEd = u.uE * dLu;
     const double p2 = E2 * B2;
     double rE2, rB2;
     if (doT) {
-        double T2 = horner3<4>(row, t);
-        const double X2 = horner3<5>(row, t), vT = horner3<6>(row, t), vX = horner3<7>(row, t);
+        double T2 = horner3<4>(row, t, t2);
+        const double X2 = horner3<5>(row, t, t2), vT = horner3<6>(row, t, t2), vX = horner3<7>(row, t, t2);
         const double E1T2 = u.E1 * T2, xx = u.X1 * X2;
         double den = fma(u.T1 * E2, E1T2, -(xx * xx));
         if (!FULL) { if (!(P.terms & LBG_TE)) den = 1.0;  if (!(P.terms & LBG_TT)) T2 = 1.0; }
@@ -654,6 +662,13 @@ template <bool DO_T, bool HAS_UB, bool FULL>
 __device__ __forceinline__ void n0_rows3_loop(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
                                               bool actT, bool actP, bool& any_rare, double& aTT, double& aTE, double& aEE, double& aEB) {
     int j = 0;
+#if LBG_ROWS3_UNROLL >= 3
+    for (; j + 2 < P.n_phi; j += 3) {
+        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], any_rare, aTT, aTE, aEE, aEB);
+        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j + 1], any_rare, aTT, aTE, aEE, aEB);
+        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j + 2], any_rare, aTT, aTE, aEE, aEB);
+    }
+#endif
 #if LBG_ROWS3_UNROLL >= 2
     for (; j + 1 < P.n_phi; j += 2) {      // two independent nodes per trip: ILP for the FP64 pipe
         n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], any_rare, aTT, aTE, aEE, aEB);
@@ -707,6 +722,179 @@ n0_rows3_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
             if ((hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2])
                 n0_node<true>(P, reinterpret_cast<const ClRow*>(soa), L, l, c_phi[j], c_phi[P.n_phi + j], u, fl & 1, fl & 4, c_cw[j].y, fold,
                               c_phi[3 * P.n_phi + j], c_phi[4 * P.n_phi + j], c_phi[5 * P.n_phi + j], aTT, aTE, aEE, aEB, aBB);
+        }
+    }
+    if (!FULL) {
+        if (!(P.terms & LBG_TT)) aTT = 0.0;
+        if (!(P.terms & LBG_TE)) aTE = 0.0;
+        if (!(P.terms & LBG_EE)) aEE = 0.0;
+        if (!(P.terms & LBG_EB)) aEB = 0.0;
+    }
+    double acc[5] = {aTT * wl, aTE * wl, aEE * wl, aEB * wl, aBB * wl};
+#pragma unroll
+    for (int t = 0; t < 5; ++t) {
+        double v = acc[t];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) red[t][threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 5) {
+        const int t = threadIdx.x;
+        const double v = (red[t][0] + red[t][1]) + (red[t][2] + red[t][3]);
+        partial[((size_t)t * P.n_L + iL) * n_rb + blockIdx.x] = v;
+    }
+}
+
+// ---- "rows5": rows3 tables and arithmetic, masks turned into phi-index ranges -------------------------------------------
+// On the folded grid cos phi_j decreases with j, so |v|^2 = l^2 + L^2 - 2 l L cos phi_j (and its high word `hi`, the value
+// every mask test of rows3 looks at) is non-decreasing in j: each mask is a RANGE of j.  A thread finds its range ends once
+// per row by bisection on `hi` (six searches of ~7 steps, 2 instructions per node amortised):
+//     [j0s, j0e)  nodes inside the |v| = lmin window      -> second pass;   fast path needs j >= j0e
+//     [jT , jTe)  nodes inside the |v| = lmax_T window    -> second pass;   T estimators need j < jT
+//     [jP , jPe)  nodes inside the |v| = lmax_P window    -> second pass;   P estimators need j < jP
+// and the warp walks j over [min j0e, max jT) with the 7-slot body, then up to max jP with the 3-slot body.  Gains over
+// rows3 (ncu r1b: the kernel is issue-bound -- FP64 instructions hold the dispatch port for two cycles -- so every
+// non-FP64 instruction removed counts): no per-node window arithmetic / votes / branches (about 25 of 99 instructions
+// per warp-node), fully masked nodes are never visited, and the branch-free bodies let the scheduler overlap the table
+// loads of two nodes.  The selected values are bit-identical to rows3 for every node it evaluates.
+__device__ __forceinline__ int first_j_hi_ge(const RowGeom& g, int n_phi, unsigned x) {   // first j with hi(j) >= x (n_phi if none)
+    int lo = 0, hi = n_phi;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const unsigned h = (unsigned)__double2hiint(fma(g.m2lL, c_cw[mid].x, g.l2pL2));
+        if (h >= x) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
+template <bool DO_T, bool HAS_UB, bool FULL>
+__device__ __forceinline__ void n0_node5(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
+                                         bool okT, bool okP, const double2 cw,
+                                         double& aTT, double& aTE, double& aEE, double& aEB) {
+    const double nv2 = fma(g.m2lL, cw.x, g.l2pL2);               // |v|^2; lanes outside their own range may carry junk: selected away
+    const double y = rsqrt_fast(nv2);
+    const double nv = nv2 * y;
+    const double dLu = g.lL * cw.x, dLv = g.L2 - dLu;            // L.u, L.v
+    const double dot = dLu - g.l2;                               // u.v
+    const double c2 = fma((dot * dot) * (y * y), g.rl2x2, -1.0); // cos 2phi_uv = 2 (u.v)^2 / (|u|^2 |v|^2) - 1
+    const double s2sq = fma(-c2, c2, 1.0);                       // sin^2 2phi_uv
+    const int i = max(min((int)nv, P.n_ell - 2), 0);
+    const double t = nv - (double)i;
+    const double2* row = reinterpret_cast<const double2*>(ptab) + i;
+    const double E2 = horner3<0>(row, t, 0.0), vE = horner3<2>(row, t, 0.0);
+    double B2 = horner3<1>(row, t, 0.0);
+    const double vB = HAS_UB ? horner3<3>(row, t, 0.0) : 0.0;
+    if (!FULL) { if (!(P.terms & LBG_EB)) B2 = 1.0; }
+    const double uEd = u.uE * dLu;
+    const double p2 = E2 * B2;
+    double rE2, rB2;
+    if (DO_T) {
+        double T2 = horner3<4>(row, t, 0.0);
+        const double X2 = horner3<5>(row, t, 0.0), vT = horner3<6>(row, t, 0.0), vX = horner3<7>(row, t, 0.0);
+        const double E1T2 = u.E1 * T2, xx = u.X1 * X2;
+        double den = fma(u.T1 * E2, E1T2, -(xx * xx));
+        if (!FULL) { if (!(P.terms & LBG_TE)) den = 1.0;  if (!(P.terms & LBG_TT)) T2 = 1.0; }
+        const double p1 = T2 * den;
+        const double r = rcp_fast(p1 * p2);                      // one reciprocal for the four filter denominators
+        const double r34 = r * p1, r12 = r * p2;
+        rE2 = r34 * B2; rB2 = r34 * E2;
+        const double rT2 = r12 * den, rdn = r12 * T2;
+        const double fa = fma(vT, dLv, u.uT * dLu);
+        const double tt = (fa * fa) * (u.rT1h * rT2);
+        const double uXd = u.uX * dLu, vXd = vX * dLv;
+        const double fa_uv = fma(uXd, c2, vXd), fa_vu = fma(vXd, c2, uXd);
+        const double num = fma(E1T2, fa_uv, -(xx * fa_vu));
+        const double te = (fa_uv * num) * rdn;
+        aTT = fma(cw.y, okT ? tt : 0.0, aTT);
+        aTE = fma(cw.y, okT ? te : 0.0, aTE);
+    } else {
+        const double r = rcp_fast(p2);
+        rE2 = r * B2; rB2 = r * E2;
+    }
+    const double fe = fma(vE, dLv, uEd) * c2;
+    const double ee = (fe * fe) * (u.rE1h * rE2);
+    const double fb = HAS_UB ? fma(-vB, dLv, uEd) : uEd;
+    const double eb = ((fb * fb) * s2sq) * (u.rE1 * rB2);
+    aEE = fma(cw.y, okP ? ee : 0.0, aEE);
+    aEB = fma(cw.y, okP ? eb : 0.0, aEB);
+}
+
+#ifndef LBG_ROWS5_MINB
+#define LBG_ROWS5_MINB 4
+#endif
+#ifndef LBG_ROWS5_UNROLL
+#define LBG_ROWS5_UNROLL 2
+#endif
+template <bool HAS_UB, bool FULL>
+__global__ void __launch_bounds__(128, LBG_ROWS5_MINB)
+n0_rows5_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const double4* __restrict__ ptab,
+                const double* __restrict__ soa, double* __restrict__ partial /*[5][n_L][n_rb]*/) {
+    __shared__ double red[5][4];
+    const int r = blockIdx.x * 128 + threadIdx.x;
+    const int iL = blockIdx.y, n_rb = gridDim.x;
+    const double L = Ls[iL];
+    int fl = 0;
+    double l = 1.0, wl = 0.0;
+    UVals u = {};
+    if (r < P.n_l1) {
+        const double4* up = reinterpret_cast<const double4*>(utab + r);
+        const double4 q0 = ld4(up), q1 = ld4(up + 1), q2 = ld4(up + 2), q3 = ld4(up + 3);
+        fl = (int)q3.y;
+        l = q0.x; wl = q0.y;
+        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
+        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
+    }
+    const bool act = (fl & 5) && !(fl & 16);
+    const bool actT = act && (fl & 1), actP = act && (fl & 4);
+    RowGeom g;
+    g.L2 = L * L; g.l2 = l * l; g.rl2x2 = 2.0 / g.l2; g.lL = l * L; g.m2lL = -2.0 * g.lL; g.l2pL2 = g.l2 + g.L2;
+    const int n = P.n_phi;
+    // range ends of this row (see the header); inactive lanes get empty ranges that do not widen the warp's walk
+    int j0s = n, j0e = n, jT = 0, jTe = 0, jP = 0, jPe = 0;
+    if (act) {
+        j0s = first_j_hi_ge(g, n, P.near_lo[0]);
+        j0e = first_j_hi_ge(g, n, P.near_lo[0] + P.near_span[0] + 1u);
+        jT = first_j_hi_ge(g, n, P.near_lo[1]);
+        jTe = first_j_hi_ge(g, n, P.near_lo[1] + P.near_span[1] + 1u);
+        jP = first_j_hi_ge(g, n, P.near_lo[2]);
+        jPe = first_j_hi_ge(g, n, P.near_lo[2] + P.near_span[2] + 1u);
+    }
+    const bool any_rare = act && (j0e > j0s || jTe > jT || jPe > jP);
+    const int endT = actT ? jT : 0, endP = actP ? jP : 0;       // first j at which the T / P estimators stop (|v| side)
+    const int w0 = __reduce_min_sync(0xffffffffu, j0e);
+    const int wT = __reduce_max_sync(0xffffffffu, endT), wP = __reduce_max_sync(0xffffffffu, endP);
+    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
+#define LBG_OKT(j) ((j) >= j0e && (j) < endT)
+#define LBG_OKP(j) ((j) >= j0e && (j) < endP && !((j) >= jT && (j) < jTe))
+    int j = w0;
+#if LBG_ROWS5_UNROLL >= 2
+    for (; j + 1 < wT; j += 2) {                                 // temperature + polarisation, two independent nodes per trip
+        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j), LBG_OKP(j), c_cw[j], aTT, aTE, aEE, aEB);
+        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j + 1), LBG_OKP(j + 1), c_cw[j + 1], aTT, aTE, aEE, aEB);
+    }
+#endif
+    for (; j < wT; ++j) n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j), LBG_OKP(j), c_cw[j], aTT, aTE, aEE, aEB);
+#if LBG_ROWS5_UNROLL >= 2
+    for (; j + 1 < wP; j += 2) {                                 // polarisation only
+        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j), c_cw[j], aTT, aTE, aEE, aEB);
+        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j + 1), c_cw[j + 1], aTT, aTE, aEE, aEB);
+    }
+#endif
+    for (; j < wP; ++j) n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j), c_cw[j], aTT, aTE, aEE, aEB);
+#undef LBG_OKT
+#undef LBG_OKP
+    if (any_rare) {                                              // bit-faithful second pass over the window nodes only
+        const bool fold = P.fold != 0;
+        for (int k = 0; k < 3; ++k) {
+            const int a = k == 0 ? j0s : (k == 1 ? jT : jP), b = k == 0 ? j0e : (k == 1 ? jTe : jPe);
+            for (int jj = a; jj < b; ++jj) {
+                if (k == 2 && jj >= jT && jj < jTe) continue;    // lmax_T == lmax_P: the windows coincide, visit once
+                if (k == 1 && jj >= j0s && jj < j0e) continue;
+                if (k == 2 && jj >= j0s && jj < j0e) continue;
+                n0_node<true>(P, reinterpret_cast<const ClRow*>(soa), L, l, c_phi[jj], c_phi[n + jj], u, fl & 1, fl & 4, c_cw[jj].y, fold,
+                              c_phi[3 * n + jj], c_phi[4 * n + jj], c_phi[5 * n + jj], aTT, aTE, aEE, aEB, aBB);
+            }
         }
     }
     if (!FULL) {
@@ -952,11 +1140,18 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     P.n_chunk = n_chunk;
 
     // kernel variant: 0 = thread per (L, phi) marching over |u| rows, 1 = thread per |u| row looping over phi ("rows")
-    int variant = 3;
+    int variant = 5;
     if (const char* e = getenv("LBG_N0_VARIANT")) variant = atoi(e);
     if (n_phe > LBG_MAX_PHI_CONST || n_L > 65535) variant = 0;
     // rows2 needs: only TT/TE/EE/EB requested, every |v| up to lmax_P inside the table, cuts ordered lmin_v < lmax_T <= lmax_P
     if (variant >= 2 && ((terms_mask & LBG_BB) || lmax_P > (double)(c->n_ell - 2) || c->n_ell + 2 > LBG_PAIR_STRIDE || !(lmin_v > 0.0 && lmin_v < lmax_T))) variant = 1;
+    // rows5 walks index ranges: needs cos phi_j strictly decreasing (the folded grid) and disjoint, ordered cut windows
+    bool rows5 = variant == 5;
+    if (rows5) {
+        variant = 3;
+        for (int j = 1; j < n_phe; ++j) rows5 = rows5 && ph[j] < ph[j - 1];
+        rows5 = rows5 && fold_phi && P.near_lo[0] + P.near_span[0] < P.near_lo[1] && P.near_lo[1] <= P.near_lo[2];
+    }
     ChebFit fit;
     if (variant == 3) {
         // rows3 folds the noise into the table: relative error bound of the per-interval Chebyshev cubic (see the kernel's header)
@@ -1033,8 +1228,16 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
         const dim3 grid(n_rb, n_L);
 #define LBG_R3(UB, FULL) n0_rows3_kernel<UB, FULL><<<grid, 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), \
                              c->cl_poly.as<double4>(), c->cl_soa.as<double>(), d_part)
-        if (c->ub_zero) { if (full) LBG_R3(false, true); else LBG_R3(false, false); }
-        else            { if (full) LBG_R3(true, true);  else LBG_R3(true, false); }
+#define LBG_R5(UB, FULL) n0_rows5_kernel<UB, FULL><<<grid, 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), \
+                             c->cl_poly.as<double4>(), c->cl_soa.as<double>(), d_part)
+        if (rows5) {
+            if (c->ub_zero) { if (full) LBG_R5(false, true); else LBG_R5(false, false); }
+            else            { if (full) LBG_R5(true, true);  else LBG_R5(true, false); }
+        } else {
+            if (c->ub_zero) { if (full) LBG_R3(false, true); else LBG_R3(false, false); }
+            else            { if (full) LBG_R3(true, true);  else LBG_R3(true, false); }
+        }
+#undef LBG_R5
 #undef LBG_R3
     } else if (variant == 2) {
         const double xmax = P.a * 2.0 * (double)c->n_ell;                 // largest Taylor argument of the noise factor
