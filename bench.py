@@ -29,7 +29,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 OPS_PER_NODE = 145          # frozen convention, SURVEY.md 8(d) / BASELINE.md section 4
-N0_DRAM_BYTES_PER_LAUNCH = None   # filled from the ncu capture once measured at the bench size
+N0_DRAM_BYTES_PER_LAUNCH = 2193152   # ncu --set full, profiles/r1c_n0_rows5_ncu_full_summary.txt: dram read+write of the 496-L profile launch (the tables; partial sums stay in L2)
 FP64_NOMINAL_TFLOPS = 37.2  # 148 SM x 64 DFMA/clk x 2 x 1.965 GHz
 
 # (thetab [arcmin], DeltaT [uK-arcmin], iterative): rank r of a multi-GPU run takes SWEEP[r % len]
@@ -350,7 +350,7 @@ def main():
                     'd2h_bytes_per_step': 8 * 6 * Ls.size + d2h_fc, 'ms_per_step': e2e_s / a.steps * 1e3},
             'gpu_launches': acc['launches'],
             'roofline': {'bound': 'fp64', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak if peak else None,
-                         'traffic': N0_DRAM_BYTES_PER_LAUNCH, 'traffic_source': 'ncu --set full, profiles/ (dram__bytes_read+write of one n0_rows5 launch)',
+                         'traffic': N0_DRAM_BYTES_PER_LAUNCH, 'traffic_source': 'ncu --set full of scripts/n0_profile_case.py (every 10th L), profiles/r1c_n0_rows5_ncu_full_summary.txt: the spline tables once; algorithmic bytes per launch = 8 B x n_L output',
                          'peak_source': 'measured DFMA micro-benchmark in this run (lbg_fp64_peak); nominal %.1f; MEASURED_PEAKS.json has no FP64 entry '
                                         '(hbm_gbs=%s is not the bound: arithmetic intensity > 1e4 flop/B)' % (FP64_NOMINAL_TFLOPS, mp.get('hbm_gbs')),
                          'ops_per_node': OPS_PER_NODE, 'kernel': 'n0_rows5_kernel', 'kernel_ms': main_ms,

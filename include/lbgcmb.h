@@ -147,6 +147,14 @@ int lbg_mqw_fisher(lbg_ctx* ctx, int n_ell, int n_bin, const double* cgg, int cg
                    const double* mode_weight /*[n_ell]*/, double fsky, double* out_F, double* out_Fsl /*or NULL*/,
                    double* out_S /*or NULL*/);
 
+/* cadence/cadence.py:64-191 `Fisher` (the LSST-lens flavour of the same forecast): per-shell cgg[n_bin][n_ell], the same bins
+ * layout, mode_weight[l] = 2l+1 inside the reference's LCUT (cadence.py:73-74: the cut of the LAST shell) and 0 beyond.
+ * out_F reproduces cadence.py:155-165 as written, including its running `Interim` sum:
+ *   F_ij = [i == j] fsky B_i + B_i + sum_{j' <= j} T_ij',  B_i = sum_l w S A0i_j^2 / Aii / A00,  T_ij = the cross term of mqw.py:100. */
+int lbg_cadence_fisher(lbg_ctx* ctx, int n_ell, int n_bin, const double* cgg /*[n_bin][n_ell]*/, const double* bins /*[n_bin][8]*/,
+                       const double* mode_weight /*[n_ell]*/, double fsky, double* out_F, double* out_Fsl /*or NULL*/,
+                       double* out_S /*or NULL*/);
+
 /* ---- survey-design grid (BASELINE configs[4]): for every (noise level n, galaxy configuration g) the cumulative S/N of
  *      C_kg (snr.py:118-124 with the Ckg.py:83-87 variance) and the (sigma8, b1) Fisher matrix + interloper bias vector of
  *      D = (C_kk, C_kg, C_gg) (interloper.py:200-253) -- the same per-multipole arithmetic as lbg_gaussian_cov +

@@ -73,6 +73,7 @@ def _declare(L):
         'lbg_gaussian_cov': [vp, i, c_double_p, i, c_double_p, i, c_int_p, c_int_p, d, c_double_p],
         'lbg_fisher_accum': [vp, i, i, i, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p],
         'lbg_mqw_fisher': [vp, i, i, c_double_p, i, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
+        'lbg_cadence_fisher': [vp, i, i, c_double_p, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_forecast_grid': [vp, i, c_double_p, c_double_p, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p,
                               c_double_p, i, c_double_p, d, d, c_double_p],
         'lbg_n0_ho02': [vp, i, c_double_p, u, d, d, d, i, i, c_double_p, c_double_p, i, c_double_p, c_double_p,

@@ -107,7 +107,8 @@ __global__ void mqw_schur_kernel(int n_ell, int n_bin, size_t cgg_stride, const 
 __global__ void __launch_bounds__(RED_T)
 mqw_fisher_kernel(int n_ell, int n_bin, size_t cgg_stride, const double* __restrict__ cgg, const MqwBin* __restrict__ bins,
                   const double* __restrict__ w /*(2l+1) or 0 beyond an l cut*/, double fsky, const double* __restrict__ A00,
-                  const double* __restrict__ S, double* __restrict__ F /*[n_bin][n_bin]*/, double* __restrict__ Fsl /*[n_bin]*/) {
+                  const double* __restrict__ S, double* __restrict__ F /*[n_bin][n_bin]*/, double* __restrict__ Fsl /*[n_bin]*/,
+                  double* __restrict__ Bd /*NULL, or [n_bin]: cadence flavour -- the diagonal base sum is returned apart*/) {
     __shared__ double sm[RED_T];
     const int i = blockIdx.y, j = blockIdx.x;
     const MqwBin bi = bins[i];
@@ -122,6 +123,17 @@ mqw_fisher_kernel(int n_ell, int n_bin, size_t cgg_stride, const double* __restr
         if (threadIdx.x == 0) Fsl[i] = bi.Ns * fsky * acc[0];
         return;
     }
+    if (j == n_bin + 1) {          // cadence/cadence.py:156: B_i = sum_l (2l+1) S A0i_j^2 / Aii / A00 (no fsky)
+        for (int l = threadIdx.x; l < n_ell; l += RED_T) {
+            const double ci = cgg[(size_t)i * cgg_stride + l];
+            const double bsNs_i = bi.bs * bi.Ns;
+            const double Aii = bsNs_i * bsNs_i * ci + bi.ws, A0i_j = bi.bp * bsNs_i * ci;
+            acc[0] += w[l] * (S[l] * A0i_j * A0i_j / Aii / A00[l]);
+        }
+        block_sum<1>(acc, sm);
+        if (threadIdx.x == 0) Bd[i] = acc[0];
+        return;
+    }
     const MqwBin bj = bins[j];
     for (int l = threadIdx.x; l < n_ell; l += RED_T) {
         const double ci = cgg[(size_t)i * cgg_stride + l], cj = cgg[(size_t)j * cgg_stride + l];
@@ -132,7 +144,7 @@ mqw_fisher_kernel(int n_ell, int n_bin, size_t cgg_stride, const double* __restr
         const double A0i_j = bi.bp * bsNs_i * ci, A0j_j = bj.bp * bsNs_j * cj;
         const double ri = A0i / sqrt(a00 * Aii), rj = A0j / sqrt(a00 * Ajj);
         double t = 2.0 * s * s * ri * rj * sqrt(1.0 / Aii / Ajj) * A0i_j * A0j_j / a00;
-        if (i == j) t += s * A0i_j * A0i_j / Aii / a00;
+        if (i == j && !Bd) t += s * A0i_j * A0i_j / Aii / a00;
         acc[0] += w[l] * t;
     }
     block_sum<1>(acc, sm);
@@ -238,15 +250,15 @@ extern "C" int lbg_fisher_accum(lbg_ctx* c, int n_ell, int n_spec, int n_par, co
     return LBG_OK;
 }
 
-extern "C" int lbg_mqw_fisher(lbg_ctx* c, int n_ell, int n_bin, const double* cgg, int cgg_per_bin, const double* bins,
-                              const double* mode_weight, double fsky, double* out_F, double* out_Fsl, double* out_S) {
-    LBG_REQUIRE(c && cgg && bins && mode_weight && out_F, "lbg_mqw_fisher: NULL argument");
+static int mqw_fisher_impl(lbg_ctx* c, int n_ell, int n_bin, const double* cgg, int cgg_per_bin, const double* bins,
+                           const double* mode_weight, double fsky, double* out_F, double* out_Fsl, double* out_S, bool cadence) {
+    LBG_REQUIRE(c && cgg && bins && mode_weight && out_F, "lbg_mqw_fisher / lbg_cadence_fisher: NULL argument");
     LBG_REQUIRE(n_ell > 0 && n_bin > 0 && n_bin <= 1024, "lbg_mqw_fisher: bad sizes n_ell=%d n_bin=%d", n_ell, n_bin);
     std::lock_guard<std::mutex> g(c->mu);
     LBG_CUDA(cudaSetDevice(c->device));
     const size_t ncg = (size_t)(cgg_per_bin ? n_bin : 1) * n_ell;
     if (c->s0.reserve(ncg * 8) || c->s1.reserve((size_t)n_bin * sizeof(MqwBin)) || c->s2.reserve((size_t)n_ell * 8) ||
-        c->s3.reserve((size_t)2 * n_ell * 8) || c->s4.reserve((size_t)(n_bin + 1) * n_bin * 8)) return LBG_ENOMEM;
+        c->s3.reserve((size_t)2 * n_ell * 8) || c->s4.reserve((size_t)(n_bin + 2) * n_bin * 8)) return LBG_ENOMEM;
     cudaStream_t st = c->stream;
     LBG_CUDA(cudaMemcpyAsync(c->s0.p, cgg, ncg * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s1.p, bins, (size_t)n_bin * sizeof(MqwBin), cudaMemcpyHostToDevice, st));
@@ -255,15 +267,39 @@ extern "C" int lbg_mqw_fisher(lbg_ctx* c, int n_ell, int n_bin, const double* cg
     double* S = A00 + n_ell;
     double* F = c->s4.as<double>();
     double* Fsl = F + (size_t)n_bin * n_bin;
+    double* Bd = cadence ? Fsl + n_bin : nullptr;
     const size_t stride = cgg_per_bin ? (size_t)n_ell : 0;
     KernelTimer t(c);
     mqw_schur_kernel<<<(n_ell + 127) / 128, 128, 0, st>>>(n_ell, n_bin, stride, c->s0.as<double>(), c->s1.as<MqwBin>(), A00, S);
     t.launched();
-    mqw_fisher_kernel<<<dim3(n_bin + 1, n_bin), RED_T, 0, st>>>(n_ell, n_bin, stride, c->s0.as<double>(), c->s1.as<MqwBin>(),
-                                                               c->s2.as<double>(), fsky, A00, S, F, Fsl);
+    mqw_fisher_kernel<<<dim3(n_bin + (cadence ? 2 : 1), n_bin), RED_T, 0, st>>>(n_ell, n_bin, stride, c->s0.as<double>(), c->s1.as<MqwBin>(),
+                                                               c->s2.as<double>(), fsky, A00, S, F, Fsl, Bd);
     t.launched();
     LBG_CUDA(cudaMemcpyAsync(out_F, F, (size_t)n_bin * n_bin * 8, cudaMemcpyDeviceToHost, st));
     if (out_Fsl) LBG_CUDA(cudaMemcpyAsync(out_Fsl, Fsl, (size_t)n_bin * 8, cudaMemcpyDeviceToHost, st));
     if (out_S) LBG_CUDA(cudaMemcpyAsync(out_S, S, (size_t)n_ell * 8, cudaMemcpyDeviceToHost, st));
-    return t.finish();
+    std::vector<double> B(cadence ? n_bin : 0);
+    if (cadence) LBG_CUDA(cudaMemcpyAsync(B.data(), Bd, (size_t)n_bin * 8, cudaMemcpyDeviceToHost, st));
+    int rc = t.finish();
+    if (rc || !cadence) return rc;
+    // cadence/cadence.py:155-165 as written: `Interim` starts at the base term WITHOUT fsky and keeps accumulating the j terms,
+    // and each Fisher[i, j] receives its running sum:  F_ij = [i == j] fsky B_i + B_i + sum_{j' <= j} T_ij'  (out_F holds T)
+    for (int i = 0; i < n_bin; ++i) {
+        double run = B[i];
+        for (int j = 0; j < n_bin; ++j) {
+            run += out_F[(size_t)i * n_bin + j];
+            out_F[(size_t)i * n_bin + j] = (i == j ? fsky * B[i] : 0.0) + run;
+        }
+    }
+    return LBG_OK;
+}
+
+extern "C" int lbg_mqw_fisher(lbg_ctx* c, int n_ell, int n_bin, const double* cgg, int cgg_per_bin, const double* bins,
+                              const double* mode_weight, double fsky, double* out_F, double* out_Fsl, double* out_S) {
+    return mqw_fisher_impl(c, n_ell, n_bin, cgg, cgg_per_bin, bins, mode_weight, fsky, out_F, out_Fsl, out_S, false);
+}
+
+extern "C" int lbg_cadence_fisher(lbg_ctx* c, int n_ell, int n_bin, const double* cgg, const double* bins,
+                                  const double* mode_weight, double fsky, double* out_F, double* out_Fsl, double* out_S) {
+    return mqw_fisher_impl(c, n_ell, n_bin, cgg, 1, bins, mode_weight, fsky, out_F, out_Fsl, out_S, true);
 }
