@@ -278,8 +278,66 @@ def make_modi_lensing():
     np.savez_compressed(os.path.join(GOLD, 'modi_lensing.npz'), **out)
 
 
+def load_cadence():
+    """The reference's cadence/cadence.py (functions only) loaded from where it lies: its two python-2 print statements (:174,
+    :189) are parenthesised IN MEMORY and the __main__ block is not compiled; `np.array` on the ragged output rows (:186-187
+    mix floats with 1-element arrays, an error on numpy >= 1.24) is given dtype=object through a proxy of the numpy module."""
+    import re
+    import types
+    refload.setup()
+    path = os.path.join(refload.REF, 'cadence', 'cadence.py')
+    src = open(path).read().split("if __name__ == '__main__':")[0]
+    src = re.sub(r'^(\s*)print  (.+)$', lambda m: '%sprint(%s)' % (m.group(1), m.group(2)), src, flags=re.M)
+    mod = types.ModuleType('cadence_ref')
+    mod.__file__ = path
+    exec(compile(src, path, 'exec'), mod.__dict__)
+
+    class _NP(object):
+        def __getattr__(self, name):
+            return getattr(np, name)
+
+        @staticmethod
+        def array(x, *a, **k):
+            try:
+                return np.array(x, *a, **k)
+            except ValueError:
+                return np.array([[float(np.ravel(e)[0]) for e in row] for row in x])
+    mod.np = _NP()
+    return mod
+
+
+def make_cadence():
+    """cadence.Fisher (unmodified reference function) on analytic spectroscopic inputs; 6 shells, every integer l in [60, 1500]."""
+    from . import halofit as ohf
+    hf = refload.load('halofit')
+    prep = refload.load('prep_Llls')
+    cad = load_cadence()
+    k, p, eng, cosmo, P = _pk_setup()
+    Dg = lambda z: float(eng.Dgrow(z=z))
+    ref_pk = ohf.ModiPk(k, p, Dg, cosmo, P['sig_8'], halofit_fn=hf.halofit).interps()
+    _, Lm, _nm = prep.prep_Llls(60, 60, 1500, log10=False)
+    T = cadence_inputs()
+    out = {'k': k, 'plin': p, 'L': Lm, 'zs': T['zs'], 'tNs': T['tNs'], 'tNp': T['tNp'], 'fsky': T['fsky'], 'fover': T['fover']}
+    cad.dz = 0.1
+    t = time.time()
+    for name, sources in (('lenses', False), ('sources', True)):
+        res = cad.Fisher(ref_pk, Lm, T['zs'], T['tNs'], T['tNp'], T['pz'], T['bz'], fsky=T['fsky'], fover=T['fover'], sources=sources, printit=False)
+        out['out_' + name] = np.asarray(res, dtype=np.float64)
+    out['lenses_bz'] = np.array([float(cad.lenses_bz(z)) for z in T['zs']])
+    out['Cij'] = cad.Cij(ref_pk, Lm[:50].astype(np.float64), 0.45, 0.55)
+    print('cadence.Fisher reference: %.1f s' % (time.time() - t), out['out_lenses'][:2])
+    np.savez_compressed(os.path.join(GOLD, 'cadence.npz'), **out)
+
+
+def cadence_inputs():
+    """Analytic stand-ins for get_desiCz() / desi_eff (cadence.py:25-41, schmittfull_bz.py): shared with the GPU test."""
+    g = lambda z0, s: (lambda z: np.exp(-(np.asarray(z, dtype=np.float64) - z0) ** 2 / (2. * s * s)) / (np.sqrt(2. * np.pi) * s))
+    return {'zs': np.arange(0.3, 0.85, 0.1), 'tNs': 1500., 'tNp': 1.2e5, 'pz': g(0.6, 0.3), 'bz': (lambda z: 1.2 + 0.6 * z),
+            'fsky': 5060. / 41253., 'fover': 0.05}
+
+
 MAKERS = {'n0': make_n0, 'halofit': make_halofit, 'limber': make_limber, 'fisher': make_fisher, 'modi': make_modi,
-          'modi_lensing': make_modi_lensing}
+          'modi_lensing': make_modi_lensing, 'cadence': make_cadence}
 
 if __name__ == '__main__':
     os.makedirs(GOLD, exist_ok=True)

@@ -10,6 +10,18 @@ class _Q:
     def __init__(self, v):
         self.value = v
 
+    # growth_rate.py:17 forms (H(0) / H(z)) ** 2 * a ** -3 on Quantities before taking .value
+    def __truediv__(self, o):
+        return _Q(self.value / (o.value if isinstance(o, _Q) else o))
+
+    def __mul__(self, o):
+        return _Q(self.value * (o.value if isinstance(o, _Q) else o))
+
+    __rmul__ = __mul__
+
+    def __pow__(self, e):
+        return _Q(self.value ** e)
+
 
 class FlatLambdaCDM:
     """Flat LCDM with Tcmb0 = 0 (matter + Lambda only), as astropy builds it for cosmo.py:6."""

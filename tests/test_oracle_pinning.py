@@ -59,6 +59,25 @@ def test_limber_cheap_cases_against_reference_vectors(golden_dir):
     assert np.allclose(bg.lensing_kernel(np.array([0.5, 1.0, 3.0, 10.0])), g['lensing_kernel'], rtol=1e-14)
 
 
+def test_cadence_fisher_against_reference_vector(golden_dir):
+    """oracle/cadence.py vs the unmodified cadence.Fisher (print statements parenthesised in memory): both flavours."""
+    from lbgcmb_b200.modi.cosmology import Cosmology
+    from lbgcmb_b200.synthetic import PARAMS
+    from oracle import cadence as ocad
+    from oracle.make_golden import cadence_inputs
+    g = _g(golden_dir, 'cadence.npz')
+    eng = Cosmology(M=PARAMS['om_m'], H0=100., B=PARAMS['om_b'], sig8=PARAMS['sig_8'], klin=g['k'], plin=g['plin'])
+    cosmo = FlatLambdaCDM(H0=100., Om0=PARAMS['om_m'], Ob0=PARAMS['om_b'])
+    pk = ohf.ModiPk(g['k'], g['plin'], lambda z: float(eng.Dgrow(z=z)), cosmo, PARAMS['sig_8']).interps()
+    bg = olim.Background(PARAMS)
+    T = cadence_inputs()
+    assert np.allclose([ocad.lenses_bz(bg, z) for z in g['zs']], g['lenses_bz'], rtol=1e-13)
+    for name, sources in (('lenses', False), ('sources', True)):
+        got = ocad.Fisher(bg, pk, g['L'].astype(np.float64), g['zs'], float(g['tNs']), float(g['tNp']), T['pz'], T['bz'],
+                          fsky=float(g['fsky']), fover=float(g['fover']), sources=sources)
+        assert np.max(np.abs(got / g['out_' + name] - 1)) < 1e-10, name
+
+
 @pytest.mark.reference
 def test_reference_modules_import_under_shim():
     from oracle import refload
