@@ -1,15 +1,16 @@
 #!/usr/bin/env python
-"""bench.py -- headline benchmark of the LBGCMB forecast hot path on B200 (see DESIGN.md "Measurement").
+"""bench.py -- headline benchmark of the LBGCMB forecast hot path on B200.
 
 One step = the Hu-Okamoto N0 (TT+TE+EE+EB, iterative EB; BASELINE.json configs[1]: thetab=1.4', DeltaT=1 uK',
-every integer L in [50, 5000] -> 4951 L-modes) followed by the Limber C_kk/C_kg/C_gg + SNR/Fisher stage on the
-same multipoles when that stage is built (--no-limber to leave it out).  metric = L-modes per second.
+every integer L in [50, 5000] -> 4951 L-modes) followed by the Limber C_kk/C_kg/C_gg + covariance + S/N + (sigma8, b1)
+Fisher / interloper-bias stage for the u, g, r, i dropout samples on the same multipoles (configs[0], [2]; --no-limber
+leaves it out).  metric = L-modes per second.
 
-  value      whole-job L-modes/s, device time of the kernels (CUDA events on the library's stream), tables resident
-  e2e        the same metric through the reference-facing Python call (Nkk.Nkk(...)) with HOST inputs: spline build,
-             table upload, H2D, kernels, D2H all inside the timed region
-  roofline   dominant kernel (n0_kernel): FP64-pipe bound, achieved = executed integrand nodes x 145 op / time
-  cpu_baseline  the numpy port of the reference (oracle/n0.py) on this box's host cores, bounded sample
+  value      whole-job L-modes/s over the device time of every kernel of the step (CUDA events on the library's stream)
+  e2e        the same metric through the reference-facing Python calls (Nkk.n0_terms, interloper.get_allCls, snr.snr, ...)
+             with HOST inputs: spline/table builds, H2D, kernels, D2H all inside the timed region
+  roofline   dominant kernel (n0_rows5_kernel): FP64-pipe bound; achieved = executed FP64 flop (ncu count per node) / time
+  cpu_baseline  the numpy port of the reference (oracle/) on this box's host cores, bounded sample
 
 N>1 (torchrun, one rank per GPU): weak scaling -- rank r runs the full L grid for sweep configuration r of
 BASELINE.json configs[4] (beam/noise sweep); no data-path collective; max-over-ranks timing.
@@ -30,6 +31,11 @@ sys.path.insert(0, ROOT)
 
 OPS_PER_NODE = 145          # frozen convention, SURVEY.md 8(d) / BASELINE.md section 4
 N0_DRAM_BYTES_PER_LAUNCH = 2193152   # ncu --set full, profiles/r1c_n0_rows5_ncu_full_summary.txt: dram read+write of the 496-L profile launch (the tables; partial sums stay in L2)
+# FP64 flop the rows5 kernel EXECUTES per folded quadrature node (2 DFMA + DMUL + DADD thread instructions of the ncu capture
+# profiles/r1c_n0_rows5_ncu_full_summary.txt / r1c raw page: 6998.8 flop/clk x 4 957 967 clk / 5.002e8 nodes); masked nodes are not visited
+EXEC_FLOP_PER_NODE = 69.4
+NCU_PIPES = {'fp64_pipe_active': 0.498, 'lsu_data_pipe_wavefronts': 0.723, 'issue_active': 0.428,
+             'source': 'profiles/r1c_n0_rows5_ncu_full_summary.txt (ncu --set full, every 10th L of the bench grid)'}
 FP64_NOMINAL_TFLOPS = 37.2  # 148 SM x 64 DFMA/clk x 2 x 1.965 GHz
 
 # (thetab [arcmin], DeltaT [uK-arcmin], iterative): rank r of a multi-GPU run takes SWEEP[r % len]
@@ -324,7 +330,8 @@ def main():
     if rank == 0:
         nodes = stage['nodes']
         main_ms = Nkk.last_stats['main_kernel_ms']               # n0_rows5_kernel alone, last step (CUDA events around the launch)
-        ach = nodes * OPS_PER_NODE / (main_ms * 1e-3) * 1e-12
+        ach = nodes * EXEC_FLOP_PER_NODE / (main_ms * 1e-3) * 1e-12       # executed FP64 flop/s (hardware count from ncu x nodes / live time)
+        conv = nodes * OPS_PER_NODE / (main_ms * 1e-3) * 1e-12           # SURVEY.md 8(d) frozen convention: 145 op per folded node
         n_band = len(bands)
         fc_ms = (acc['all_ms'] - acc['n0_ms']) / a.steps
         # bytes counted from the arrays handed to / returned by the C ABI per step
@@ -350,11 +357,17 @@ def main():
                     'd2h_bytes_per_step': 8 * 6 * Ls.size + d2h_fc, 'ms_per_step': e2e_s / a.steps * 1e3},
             'gpu_launches': acc['launches'],
             'roofline': {'bound': 'fp64', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak if peak else None,
-                         'traffic': N0_DRAM_BYTES_PER_LAUNCH, 'traffic_source': 'ncu --set full of scripts/n0_profile_case.py (every 10th L), profiles/r1c_n0_rows5_ncu_full_summary.txt: the spline tables once; algorithmic bytes per launch = 8 B x n_L output',
+                         'traffic': N0_DRAM_BYTES_PER_LAUNCH, 'traffic_source': 'ncu --set full of scripts/n0_profile_case.py (every 10th L): the spline tables once; '
+                                                                                'algorithmic bytes per launch = 8 B x n_L output',
+                         'achieved_definition': 'FP64 flop the kernel executes (%.1f per folded node, DFMA = 2: ncu instruction counts) x nodes / kernel time '
+                                                'measured live with CUDA events; fully masked nodes (22%% of the grid) are skipped, DMUL/DADD fill a pipe slot '
+                                                'with 1 flop, so the pipe is busier than frac says: see pipes' % EXEC_FLOP_PER_NODE,
+                         'pipes_ncu': NCU_PIPES,
+                         'convention_145op': {'achieved': conv, 'frac': conv / peak if peak else None,
+                                              'note': 'SURVEY.md 8(d) op count of the reference integrand (145 per node) x folded nodes / time: algorithmic, not executed'},
                          'peak_source': 'measured DFMA micro-benchmark in this run (lbg_fp64_peak); nominal %.1f; MEASURED_PEAKS.json has no FP64 entry '
                                         '(hbm_gbs=%s is not the bound: arithmetic intensity > 1e4 flop/B)' % (FP64_NOMINAL_TFLOPS, mp.get('hbm_gbs')),
-                         'ops_per_node': OPS_PER_NODE, 'kernel': 'n0_rows5_kernel', 'kernel_ms': main_ms,
-                         'kernel_share_of_step': main_ms * a.steps / all_ms},
+                         'kernel': 'n0_rows5_kernel', 'kernel_ms': main_ms, 'kernel_share_of_step': main_ms * a.steps / all_ms},
             'clocks': clocks, 'wall_s_timed_region': t_region,
         }
         if not a.no_cpu_baseline:
