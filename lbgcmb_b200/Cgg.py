@@ -2,6 +2,8 @@
 
 Host (numpy, <= 1000 doubles, as in the reference): the z grid, p(z) normalisation, chi(z), H(z), `sliced_pz`, b(z).
 Device (csrc/limber.cu): P_nl(k, z) on every z node (growth + HALOFIT) and the sum over z for every l."""
+from functools import lru_cache
+
 import numpy as np
 
 from lbgcmb_b200.cosmo import cosmo, C_KMS
@@ -28,11 +30,20 @@ def _each(f, zs):
     return np.array([float(f(z)) for z in zs])
 
 
-def cgg_nodes(zmin, zmax):
-    """z nodes, chi(z) and scipy-1.2.1 Simpson weights of Cgg.py:18-19,68."""
+@lru_cache(maxsize=64)
+def _cgg_nodes(zmin, zmax):
     dz = 0.01
     zs = np.arange(zmin, zmax + dz, dz)
-    return zs, comoving_distance(zs), simps_weights(zs.size, dz)
+    out = (zs, comoving_distance(zs), simps_weights(zs.size, dz), cosmo.H(zs).value / C_KMS)
+    for a in out:
+        a.setflags(write=False)
+    return out
+
+
+def cgg_nodes(zmin, zmax):
+    """z nodes, chi(z) and scipy-1.2.1 Simpson weights of Cgg.py:18-19,68 (grid constants of the fixed cosmology: kept per
+    (zmin, zmax))."""
+    return _cgg_nodes(float(zmin), float(zmax))[:3]
 
 
 def cgg_weights(zs, chis, w, zmin, zmax, survey_pz, bz, survey_pz2=None, bz2=None):
@@ -41,9 +52,12 @@ def cgg_weights(zs, chis, w, zmin, zmax, survey_pz, bz, survey_pz2=None, bz2=Non
         bz2 = bz
     if survey_pz2 is None:
         survey_pz2 = survey_pz
-    prefactor = (cosmo.H(zs).value / C_KMS) * sliced_pz(zs, zmin, zmax, survey_pz) \
-        * sliced_pz(zs, zmin, zmax, survey_pz2) / chis ** 2.
-    return w * prefactor * _each(bz, zs) * _each(bz2, zs) / params['h_100']
+    p1 = sliced_pz(zs, zmin, zmax, survey_pz)
+    p2 = p1 if survey_pz2 is survey_pz else sliced_pz(zs, zmin, zmax, survey_pz2)
+    b1 = _each(bz, zs)
+    b2 = b1 if bz2 is bz else _each(bz2, zs)
+    prefactor = (cosmo.H(zs).value / C_KMS) * p1 * p2 / chis ** 2.
+    return w * prefactor * b1 * b2 / params['h_100']
 
 
 def Cgg(Pk_interps, Llls, zmin, zmax, survey_pz, bz, survey_pz2=None, bz2=None, zeff=True):

@@ -1,4 +1,6 @@
 """Limber C_kg and its variance; mirrors reference Ckg.py:18-87 (`Ckg`, `var_Ckg`)."""
+from functools import lru_cache
+
 import numpy as np
 
 from lbgcmb_b200.Cgg import Cgg, Ngg, _each
@@ -13,16 +15,27 @@ from lbgcmb_b200.utils import comoving_distance
 params = get_params()
 
 
-def ckg_nodes(zmin, zmax):
-    """z nodes (no end point, Ckg.py:19-20), chi(z) and Simpson weights (even length -> scipy-1.2.1 'avg' rule)."""
+@lru_cache(maxsize=64)
+def _ckg_nodes(zmin, zmax):
     dz = 0.01
     zs = np.arange(zmin, zmax, dz)
-    return zs, comoving_distance(zs), simps_weights(zs.size, zs[1] - zs[0])
+    out = (zs, comoving_distance(zs), simps_weights(zs.size, zs[1] - zs[0]), lensing_kernel(zs))
+    for a in out:
+        a.setflags(write=False)
+    return out
+
+
+def ckg_nodes(zmin, zmax):
+    """z nodes (no end point, Ckg.py:19-20), chi(z) and Simpson weights (even length -> scipy-1.2.1 'avg' rule); grid
+    constants of the fixed cosmology, kept per (zmin, zmax)."""
+    return _ckg_nodes(float(zmin), float(zmax))[:3]
 
 
 def ckg_weights(zs, chis, w, zmin, zmax, survey_pz, bz):
     """Per-node Limber weights of the full z integral (Ckg.py:42-57): quadrature x W_kappa p / chi^2 x b / h^2."""
-    prefactor = lensing_kernel(zs) * sliced_pz(zs, zmin, zmax, survey_pz) / chis ** 2.
+    cached = _ckg_nodes(float(zmin), float(zmax))
+    wk = cached[3] if zs is cached[0] else lensing_kernel(zs)
+    prefactor = wk * sliced_pz(zs, zmin, zmax, survey_pz) / chis ** 2.
     return w * prefactor * _each(bz, zs) / params['h_100'] ** 2.
 
 

@@ -38,6 +38,7 @@ class Cosmology(object):
         self._sig0 = None
         self._spec_cache = {}
         self._spl0 = None
+        self._rows_cache = {}
         self._rows_key = None
 
     # ---- background (host) ------------------------------------------------------------------------------------
@@ -115,6 +116,7 @@ class Cosmology(object):
         if _owner.get(_ffi.context(self.device).device) == id(self):
             _owner[_ffi.context(self.device).device] = None
         self._rows_key = None
+        self._rows_cache = {}
 
     def _sigma2_z0(self, R):
         ctx = self._ctx()
@@ -183,18 +185,23 @@ class Cosmology(object):
         ctx = self._ctx()
         if self._rows_key == key and not want_host:
             return None
-        rows = np.zeros((zs.size, 8))
-        aa = self.ztoa(zs)
-        rows[:, 0] = (self.Dplus(aa) / self.Dplus(1.)) ** 2.                 # Dgrow(z)^2, modi/cosmology.py:113-117
-        rows[:, 1] = 1.0
-        if nonlinear:
-            hf = ~(zs > zmax_halofit)                                         # modi/cosmology.py:171
-            if np.any(hf):
-                zz = self.atoz(aa[hf])
-                rows[hf, 1:4] = self.halofit_specs(zs[hf], rows[hf, 0], sig8)
-                rows[hf, 4] = self.cosmo.Om(zz)
-                rows[hf, 5] = self.cosmo.Ode(zz)
-                rows[hf, 6] = 1.0
+        rows = self._rows_cache.get(key)        # per z grid: D^2, k_nl, n_eff, C, Omega_m(z), Omega_L(z) (dropped by invalidate_device)
+        if rows is None:
+            rows = np.zeros((zs.size, 8))
+            aa = self.ztoa(zs)
+            rows[:, 0] = (self.Dplus(aa) / self.Dplus(1.)) ** 2.                 # Dgrow(z)^2, modi/cosmology.py:113-117
+            rows[:, 1] = 1.0
+            if nonlinear:
+                hf = ~(zs > zmax_halofit)                                         # modi/cosmology.py:171
+                if np.any(hf):
+                    zz = self.atoz(aa[hf])
+                    rows[hf, 1:4] = self.halofit_specs(zs[hf], rows[hf, 0], sig8)
+                    rows[hf, 4] = self.cosmo.Om(zz)
+                    rows[hf, 5] = self.cosmo.Ode(zz)
+                    rows[hf, 6] = 1.0
+            if len(self._rows_cache) >= 16:
+                self._rows_cache.clear()
+            self._rows_cache[key] = rows
         out = np.empty((zs.size, len(self.klin))) if want_host else None
         fnu = self.cosmo.Onu0 / self.cosmo.Om0
         _ffi.check(_ffi.lib().lbg_pk_build_table(ctx.handle, zs.size, _ffi._dp(_ffi.f64(rows)), float(fnu), float(self.cosmo.Om0),

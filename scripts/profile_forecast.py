@@ -29,7 +29,7 @@ ctx = _ffi.context()
 ctx.kernel_totals(reset=True)
 pr = cProfile.Profile(); pr.enable(); run(); pr.disable()
 print('kernel totals', ctx.kernel_totals())
-pstats.Stats(pr).sort_stats('cumulative').print_stats(35)
+pstats.Stats(pr).sort_stats('tottime').print_stats(28)
 
 # host side of N0
 from lbgcmb_b200 import Nkk
