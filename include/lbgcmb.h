@@ -115,6 +115,21 @@ int lbg_pk_upload_rows(lbg_ctx* ctx, int n_k, const double* k, int n_rows, const
 /* np.interp(x, k, P_row) : oob = 0 -> 0 outside the k range (left=right=0, modi/lensing.py:175), 1 -> clamp (:161). */
 int lbg_pk_eval(lbg_ctx* ctx, int row, int n, const double* x, int oob, double* out);
 
+/* ---- Eisenstein & Hu (1999) MDM transfer function; replaces EisensteinHu/EisensteinAndHu.c:101-217 (TFmdm_set_cosm, arguments in
+ *      its order: omega_matter, omega_baryon, omega_hdm, degen_hdm, omega_lambda, hubble [100 km/s/Mpc], redshift), :221-264
+ *      (TFmdm_onek_mpc) and :268-280 (TFmdm_onek_hmpc: k in h/Mpc).  float64 and stateless where the reference is float32 with
+ *      globals; same clamps (omega_baryon / omega_hdm <= 0 -> 1e-5, degen_hdm < 1 -> 1), theta_cmb = 2.7255 / 2.7 (:122).
+ *      out_tf_cb = T_cb(k) (the reference's return value), out_tf_cbnu = its global tf_cbnu (may be NULL),
+ *      out_growth_to_z0 = its global growth_to_z0 (may be NULL).  Illegal hubble / redshift (the reference exit(1)s) -> LBG_EINVAL. */
+int lbg_eh_transfer(lbg_ctx* ctx, double omega_matter, double omega_baryon, double omega_hdm, int degen_hdm, double omega_lambda,
+                    double hubble, double redshift, int n_k, const double* k_hmpc, double* out_tf_cb, double* out_tf_cbnu,
+                    double* out_growth_to_z0);
+/* Linear table P(k, z=0) = A k^ns T_cb(k)^2 with A fixed by sigma8 (top-hat R = 8 Mpc/h, trapezoid in ln k over the grid), built on
+ * the device and left on the context exactly as lbg_upload_pk_linear leaves a host table (cosmology sweeps
+ * need no host table).  w_lnk as in lbg_upload_pk_linear; out_plin (may be NULL) receives the table. */
+int lbg_eh_linear_table(lbg_ctx* ctx, double omega_matter, double omega_baryon, double omega_hdm, int degen_hdm, double omega_lambda,
+                        double hubble, double ns, double sigma8, int n_k, const double* k, const double* w_lnk, double* out_plin);
+
 /* ---- Limber: C_l[b][l] = sum_z weight[b][z] * P_{prow[z]}(k = (l + 1/2)/chi[z]); replaces the z loops + quadrature of
  *      Cgg.py:53-68, Ckg.py:42-59, cmb/lensing.py:27-43 (Simpson in z) and modi/lensing.py:127-179 (trapezoid in chi).
  *      weight = kernel product x bias x unit factors x quadrature weight, so one kernel serves every flavour. */

@@ -65,6 +65,8 @@ def _declare(L):
         'lbg_pk_build_table': [vp, i, c_double_p, d, d, d, i, c_double_p],
         'lbg_pk_upload_rows': [vp, i, c_double_p, i, c_double_p],
         'lbg_pk_eval': [vp, i, i, c_double_p, i, c_double_p],
+        'lbg_eh_transfer': [vp, d, d, d, i, d, d, d, i, c_double_p, c_double_p, c_double_p, c_double_p],
+        'lbg_eh_linear_table': [vp, d, d, d, i, d, d, d, d, i, c_double_p, c_double_p, c_double_p],
         'lbg_limber': [vp, i, i, c_double_p, i, c_double_p, c_double_p, c_int_p, i, c_double_p],
         'lbg_n0_modi': [vp, i, i, c_double_p, i, c_double_p, c_double_p, i, c_double_p, c_double_p, c_double_p,
                         c_int_p, c_double_p, c_double_p, c_double_p],

@@ -336,8 +336,26 @@ def cadence_inputs():
             'fsky': 5060. / 41253., 'fover': 0.05}
 
 
+EH_CASES = [(0.292, 0.0468, 0.0, 1, 0.708, 0.69, 0.0), (0.3106, 0.04898, 0.0, 3, 0.6894, 0.677, 3.0),
+            (0.31, 0.049, 0.0045, 3, 0.69, 0.68, 1.0), (0.25, 0.04, 0.02, 1, 0.70, 0.72, 0.5)]
+
+
+def make_eh():
+    """T_cb(k), T_cbnu(k) from the compiled reference (oracle/_ref/libeh_ref.so <- EisensteinHu/EisensteinAndHu.c, float32)."""
+    from . import eh
+    if not eh.ref_available():
+        raise RuntimeError('run `make -C oracle` first')
+    k = np.exp(np.linspace(np.log(1e-4), np.log(50.), 400))
+    out = {'k': k, 'cases': np.array(EH_CASES)}
+    for i, args in enumerate(EH_CASES):
+        cb, cbnu = eh.ref_transfer(args, k)
+        out['tf_cb_%d' % i], out['tf_cbnu_%d' % i] = cb, cbnu
+    np.savez_compressed(os.path.join(GOLD, 'eh.npz'), **out)
+    print('eh golden:', [float(out['tf_cb_%d' % i][200]) for i in range(len(EH_CASES))])
+
+
 MAKERS = {'n0': make_n0, 'halofit': make_halofit, 'limber': make_limber, 'fisher': make_fisher, 'modi': make_modi,
-          'modi_lensing': make_modi_lensing, 'cadence': make_cadence}
+          'modi_lensing': make_modi_lensing, 'cadence': make_cadence, 'eh': make_eh}
 
 if __name__ == '__main__':
     os.makedirs(GOLD, exist_ok=True)

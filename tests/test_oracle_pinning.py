@@ -78,6 +78,23 @@ def test_cadence_fisher_against_reference_vector(golden_dir):
         assert np.max(np.abs(got / g['out_' + name] - 1)) < 1e-10, name
 
 
+def test_eh_oracle_against_compiled_reference(golden_dir):
+    """oracle/eh.py (float64) vs the reference's own EisensteinAndHu.c (float32): golden vectors everywhere, and the compiled
+    library itself (oracle/_ref/libeh_ref.so, built by oracle/Makefile) wherever it is present."""
+    from oracle import eh
+    g = _g(golden_dir, 'eh.npz')
+    for i, case in enumerate(g['cases']):
+        args = tuple(case[:3]) + (int(case[3]),) + tuple(case[4:])
+        cb, cbnu = eh.onek_hmpc(eh.set_cosm(*args), g['k'])
+        assert np.max(np.abs(cb / g['tf_cb_%d' % i] - 1)) < 2e-6
+        assert np.max(np.abs(cbnu / g['tf_cbnu_%d' % i] - 1)) < 2e-6
+        if eh.ref_available():
+            live = eh.ref_transfer(args, g['k'][::40])
+            assert np.array_equal(live[0], g['tf_cb_%d' % i][::40])
+    # SURVEY.md probe: T(k = 0.1 h/Mpc) = 0.1273156 for the RunPB cosmology at z = 0
+    assert abs(eh.onek_hmpc(eh.set_cosm(0.292, 0.0468, 0.0, 1, 0.708, 0.69, 0.0), np.array([0.1]))[0][0] - 0.1273156) < 2e-7
+
+
 @pytest.mark.reference
 def test_reference_modules_import_under_shim():
     from oracle import refload
