@@ -565,10 +565,12 @@ __global__ void n0_poly_table_kernel(N0Params P, ChebFit F, int n_int, const dou
 #pragma unroll
     for (int q = 0; q < 4; ++q) n[q] = G * (F.m[q][0] * g[0] + F.m[q][1] * g[1] + F.m[q][2] * g[2] + F.m[q][3] * g[3]);
     n[0] += G;
-    // layout double2[slot][half][LBG_PAIR_STRIDE]: (a0,a1) and (a2,a3) of one slot in separate arrays, so the 16-17 intervals a warp
-    // gathers per load span ~272 bytes (3 lines) and the load costs its register-fill minimum of 4 wavefronts
-    double2* o = reinterpret_cast<double2*>(out) + i;
-#define LBG_PUT(slot, v) o[(2 * (slot)) * LBG_PAIR_STRIDE] = make_double2((v).x, (v).y); o[(2 * (slot) + 1) * LBG_PAIR_STRIDE] = make_double2((v).z, (v).w)
+    // layout double[slot][coefficient][LBG_PAIR_STRIDE]: four 8-byte loads per slot.  scripts/micro/ldg_pattern.cu (B200): a warp
+    // LDG.E.64 whose lane pairs share an element costs 2.6 SM-clk on the L1-hit path, an LDG.E.128 of the same shape 6.9 -- two 64-bit
+    // loads move the same bytes 24 % cheaper, and the 16-17 intervals a warp touches are 136 contiguous bytes of one array
+    double* o = reinterpret_cast<double*>(out) + i;
+#define LBG_PUT(slot, v) o[(4 * (slot)) * LBG_PAIR_STRIDE] = (v).x; o[(4 * (slot) + 1) * LBG_PAIR_STRIDE] = (v).y; \
+                         o[(4 * (slot) + 2) * LBG_PAIR_STRIDE] = (v).z; o[(4 * (slot) + 3) * LBG_PAIR_STRIDE] = (v).w
     const double4 e2 = make_double4(fma(P.nP, n[0], a[6].x), fma(P.nP, n[1], a[6].y), fma(P.nP, n[2], a[6].z), fma(P.nP, n[3], a[6].w));
     const double4 b2 = make_double4(fma(P.nP, n[0], a[7].x), fma(P.nP, n[1], a[7].y), fma(P.nP, n[2], a[7].z), fma(P.nP, n[3], a[7].w));
     const double4 t2 = make_double4(fma(P.nT, n[0], a[4].x), fma(P.nT, n[1], a[4].y), fma(P.nT, n[2], a[4].z), fma(P.nT, n[3], a[4].w));
@@ -581,12 +583,13 @@ __global__ void n0_poly_table_kernel(N0Params P, ChebFit F, int n_int, const dou
 #define LBG_ESTRIN 0
 #endif
 template <int SLOT>
-__device__ __forceinline__ double horner3(const double2* __restrict__ p, double t, double t2) {    // p = table + interval index
-    const double2 lo = __ldg(p + (2 * SLOT) * LBG_PAIR_STRIDE), hi = __ldg(p + (2 * SLOT + 1) * LBG_PAIR_STRIDE);
+__device__ __forceinline__ double horner3(const double* __restrict__ p, double t, double t2) {    // p = table + interval index
+    const double a0 = __ldg(p + (4 * SLOT) * LBG_PAIR_STRIDE), a1 = __ldg(p + (4 * SLOT + 1) * LBG_PAIR_STRIDE);
+    const double a2 = __ldg(p + (4 * SLOT + 2) * LBG_PAIR_STRIDE), a3 = __ldg(p + (4 * SLOT + 3) * LBG_PAIR_STRIDE);
 #if LBG_ESTRIN
-    return fma(fma(hi.y, t, hi.x), t2, fma(lo.y, t, lo.x));      // two independent FMAs, then one: dependent depth 2 instead of 3
+    return fma(fma(a3, t, a2), t2, fma(a1, t, a0));               // two independent FMAs, then one: dependent depth 2 instead of 3
 #else
-    return fma(fma(fma(hi.y, t, hi.x), t, lo.y), t, lo.x);
+    return fma(fma(fma(a3, t, a2), t, a1), t, a0);
 #endif
 }
 
@@ -616,7 +619,7 @@ __device__ __forceinline__ void n0_poly_node(const N0Params& P, const double4* _
     const int i = max(min((int)nv, P.n_ell - 2), 0);
     const double t = nv - (double)i;
     const double t2 = t * t;
-    const double2* row = reinterpret_cast<const double2*>(ptab) + i;
+    const double* row = reinterpret_cast<const double*>(ptab) + i;
     const double E2 = horner3<0>(row, t, t2), vE = horner3<2>(row, t, t2);
     double B2 = horner3<1>(row, t, t2);
     const double vB = HAS_UB ? horner3<3>(row, t, t2) : 0.0;
@@ -768,20 +771,29 @@ __device__ __forceinline__ int first_j_hi_ge(const RowGeom& g, int n_phi, unsign
     return lo;
 }
 
+// First half of a node: everything the table loads depend on.  Computed one trip AHEAD of its use (software pipelining): the
+// loads of a trip then issue at the top of the loop body and the next trip's rsqrt / index chain fills their latency.
+struct NodePre { double y, t; int i; };
+__device__ __forceinline__ NodePre n0_prep5(const N0Params& P, const RowGeom& g, double c) {
+    NodePre q;
+    const double nv2 = fma(g.m2lL, c, g.l2pL2);                  // |v|^2; lanes outside their own range may carry junk: selected away
+    q.y = rsqrt_fast(nv2);
+    const double nv = nv2 * q.y;
+    q.i = max(min((int)nv, P.n_ell - 2), 0);
+    q.t = nv - (double)q.i;
+    return q;
+}
+
 template <bool DO_T, bool HAS_UB, bool FULL>
 __device__ __forceinline__ void n0_node5(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
-                                         bool okT, bool okP, const double2 cw,
+                                         bool okT, bool okP, const double2 cw, const NodePre pre,
                                          double& aTT, double& aTE, double& aEE, double& aEB) {
-    const double nv2 = fma(g.m2lL, cw.x, g.l2pL2);               // |v|^2; lanes outside their own range may carry junk: selected away
-    const double y = rsqrt_fast(nv2);
-    const double nv = nv2 * y;
+    const double y = pre.y, t = pre.t;
+    const double* row = reinterpret_cast<const double*>(ptab) + pre.i;
     const double dLu = g.lL * cw.x, dLv = g.L2 - dLu;            // L.u, L.v
     const double dot = dLu - g.l2;                               // u.v
     const double c2 = fma((dot * dot) * (y * y), g.rl2x2, -1.0); // cos 2phi_uv = 2 (u.v)^2 / (|u|^2 |v|^2) - 1
     const double s2sq = fma(-c2, c2, 1.0);                       // sin^2 2phi_uv
-    const int i = max(min((int)nv, P.n_ell - 2), 0);
-    const double t = nv - (double)i;
-    const double2* row = reinterpret_cast<const double2*>(ptab) + i;
     const double E2 = horner3<0>(row, t, 0.0), vE = horner3<2>(row, t, 0.0);
     double B2 = horner3<1>(row, t, 0.0);
     const double vB = HAS_UB ? horner3<3>(row, t, 0.0) : 0.0;
@@ -867,21 +879,22 @@ n0_rows5_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
     double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
 #define LBG_OKT(j) ((j) >= j0e && (j) < endT)
 #define LBG_OKP(j) ((j) >= j0e && (j) < endP && !((j) >= jT && (j) < jTe))
+    // pairs (j, j+1) from w0 on: 7-slot body while j < wT, then 3-slot body while j < wP.  A pair's second node may lie past a
+    // range end (or past n_phi): its predicates are false there, and c_cw holds LBG_MAX_PHI_CONST finite entries.
     int j = w0;
-#if LBG_ROWS5_UNROLL >= 2
-    for (; j + 1 < wT; j += 2) {                                 // temperature + polarisation, two independent nodes per trip
-        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j), LBG_OKP(j), c_cw[j], aTT, aTE, aEE, aEB);
-        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j + 1), LBG_OKP(j + 1), c_cw[j + 1], aTT, aTE, aEE, aEB);
+    NodePre p0 = n0_prep5(P, g, c_cw[j].x), p1 = n0_prep5(P, g, c_cw[j + 1].x);
+    for (; j < wT; j += 2) {
+        const NodePre n0 = n0_prep5(P, g, c_cw[j + 2].x), n1 = n0_prep5(P, g, c_cw[j + 3].x);
+        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j), LBG_OKP(j), c_cw[j], p0, aTT, aTE, aEE, aEB);
+        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j + 1), LBG_OKP(j + 1), c_cw[j + 1], p1, aTT, aTE, aEE, aEB);
+        p0 = n0; p1 = n1;
     }
-#endif
-    for (; j < wT; ++j) n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j), LBG_OKP(j), c_cw[j], aTT, aTE, aEE, aEB);
-#if LBG_ROWS5_UNROLL >= 2
-    for (; j + 1 < wP; j += 2) {                                 // polarisation only
-        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j), c_cw[j], aTT, aTE, aEE, aEB);
-        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j + 1), c_cw[j + 1], aTT, aTE, aEE, aEB);
+    for (; j < wP; j += 2) {
+        const NodePre n0 = n0_prep5(P, g, c_cw[j + 2].x), n1 = n0_prep5(P, g, c_cw[j + 3].x);
+        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j), c_cw[j], p0, aTT, aTE, aEE, aEB);
+        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j + 1), c_cw[j + 1], p1, aTT, aTE, aEE, aEB);
+        p0 = n0; p1 = n1;
     }
-#endif
-    for (; j < wP; ++j) n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j), c_cw[j], aTT, aTE, aEE, aEB);
 #undef LBG_OKT
 #undef LBG_OKP
     if (any_rare) {                                              // bit-faithful second pass over the window nodes only
@@ -1150,7 +1163,7 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     if (rows5) {
         variant = 3;
         for (int j = 1; j < n_phe; ++j) rows5 = rows5 && ph[j] < ph[j - 1];
-        rows5 = rows5 && fold_phi && P.near_lo[0] + P.near_span[0] < P.near_lo[1] && P.near_lo[1] <= P.near_lo[2];
+        rows5 = rows5 && n_phe + 4 <= LBG_MAX_PHI_CONST && fold_phi && P.near_lo[0] + P.near_span[0] < P.near_lo[1] && P.near_lo[1] <= P.near_lo[2];
     }
     ChebFit fit;
     if (variant == 3) {
