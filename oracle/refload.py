@@ -37,6 +37,8 @@ def setup():
             setattr(np, name, typ)
     if not hasattr(np, 'trapz'):
         np.trapz = np.trapezoid
+    if not hasattr(np, 'NaN'):
+        np.NaN = np.nan                      # dropouts/bz/py/get_bz.py:43-44
     builtins.reduce = functools.reduce
     # scipy 1.2.1 simps -- NOT scipy.integrate.simpson
     scipy.integrate.simps = simps121.simps
