@@ -111,3 +111,13 @@ def fisher_bias(Llls, nmodes, Cls, Nls, xCls, xNls, fsky, fid_sig8, fid_b1, LllM
             dtheta[i] += iFisher[i, j] * interim[j]
     return {'Fisher': Fisher, 'iFisher': iFisher, 'interim': interim, 'dtheta': dtheta,
             'biased_sig8': fid_sig8 + dtheta[0], 'biased_b1': fid_b1 + dtheta[1]}
+
+
+def save_result(path, peakz, band, int_frac, res):
+    """The dat/result4interloper_*.json layout of interloper.py:271-275 (`res` = the dict fisher_bias returns plus fid_sig8, fid_b1)."""
+    import json
+    output = {'peakz': peakz, 'fid_sig8': float(res['fid_sig8']), 'fid_b1': float(res['fid_b1']), 'biased_sig8': float(res['biased_sig8']),
+              'biased_b1': float(res['biased_b1']), 'iFisher': np.asarray(res['iFisher']).tolist(), 'intfrac': int_frac}
+    with open(path, 'w') as fp:
+        json.dump(output, fp, sort_keys=True, indent=4)
+    return output
