@@ -112,3 +112,33 @@ def test_edge_cases(ctx, cl_tables):
     one = Nkk.Nkk(li, ni, np.array([100]), pickleit=False)
     many = Nkk.Nkk(li, ni, np.array([100, 100, 4000, 100]), pickleit=False)
     assert many[0] == one[0] == many[1] == many[3]
+
+
+def test_full_grid_B_properties(ctx, cl_tables, monkeypatch):
+    """BASELINE.json configs[1] at full size (every integer L in [50, 5000]): size-independent properties.
+    * every L of the run equals the same L evaluated in a small call (the value of an L never depends on its neighbours);
+    * the range-walking kernel (rows5, default) and the per-node-mask kernel (rows3) agree to the last bits on all 4951 L;
+    * N0 is smooth in L: no isolated outliers (a dropped or doubled node shows up as a spike at the 1e-3 level);
+    * three spot values against the live numpy oracle."""
+    from lbgcmb_b200 import Nkk
+    from oracle import n0 as on0
+    ell, lens, nolens = cl_tables
+    li, ni = _interps(ell, lens, nolens)
+    Ls = np.arange(50, 5001)
+    full, tf = Nkk.n0_terms(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True)
+    assert full.shape == (4951,) and np.all(np.isfinite(full)) and np.all(full > 0)
+    pick = np.array([50, 51, 999, 1000, 2999, 3000, 3001, 4999, 5000])
+    small, _ = Nkk.n0_terms(li, ni, pick, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True)
+    assert np.array_equal(full[pick - 50], small)
+    monkeypatch.setenv('LBG_N0_VARIANT', '3')
+    v3, t3 = Nkk.n0_terms(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True)
+    monkeypatch.delenv('LBG_N0_VARIANT')
+    assert np.max(np.abs(full / v3 - 1)) < 5e-15
+    for t in ('TT', 'TE', 'EE', 'EB'):
+        assert np.max(np.abs(tf[t] / t3[t] - 1)) < 5e-15
+    lf = np.log(full)
+    second = lf[2:] - 2. * lf[1:-1] + lf[:-2]
+    assert np.max(np.abs(second)) < 1e-3
+    spot = np.array([137, 2222, 4321])
+    ref = on0.nkk_root(on0.cl_interps(ell, lens), on0.cl_interps(ell, nolens), spot, ('TT', 'TE', 'EE', 'EB'), 1.4, 1.0, True)
+    assert np.max(np.abs(full[spot - 50] / ref - 1)) < 1e-10
