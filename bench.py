@@ -30,12 +30,12 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 OPS_PER_NODE = 145          # frozen convention, SURVEY.md 8(d) / BASELINE.md section 4
-N0_DRAM_BYTES_PER_LAUNCH = 2193152   # ncu --set full, profiles/r1c_n0_rows5_ncu_full_summary.txt: dram read+write of the 496-L profile launch (the tables; partial sums stay in L2)
+N0_DRAM_BYTES_PER_LAUNCH = 2212352   # ncu --set full, profiles/r1d_n0_rows5_ncu_full_summary.txt: dram read+write of the 496-L profile launch (the tables; partial sums stay in L2)
 # FP64 flop the rows5 kernel EXECUTES per folded quadrature node (2 DFMA + DMUL + DADD thread instructions of the ncu capture
-# profiles/r1c_n0_rows5_ncu_full_summary.txt / r1c raw page: 6998.8 flop/clk x 4 957 967 clk / 5.002e8 nodes); masked nodes are not visited
-EXEC_FLOP_PER_NODE = 69.4
-NCU_PIPES = {'fp64_pipe_active': 0.498, 'lsu_data_pipe_wavefronts': 0.723, 'issue_active': 0.428,
-             'source': 'profiles/r1c_n0_rows5_ncu_full_summary.txt (ncu --set full, every 10th L of the bench grid)'}
+# profiles/r1d_n0_rows5_ncu_full_summary.txt: 7357.9 flop/clk x 4 778 091 clk / 5.011e8 nodes); masked nodes are not visited
+EXEC_FLOP_PER_NODE = 70.2
+NCU_PIPES = {'fp64_pipe_active': 0.483, 'lsu_data_pipe_wavefronts': 0.769, 'issue_active': 0.498,
+             'source': 'profiles/r1d_n0_rows5_ncu_full_summary.txt (ncu --set full, every 10th L of the bench grid)'}
 FP64_NOMINAL_TFLOPS = 37.2  # 148 SM x 64 DFMA/clk x 2 x 1.965 GHz
 
 # (thetab [arcmin], DeltaT [uK-arcmin], iterative): rank r of a multi-GPU run takes SWEEP[r % len]
