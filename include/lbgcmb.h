@@ -32,6 +32,10 @@ typedef struct lbg_ctx lbg_ctx;   /* opaque: device, stream, uploaded tables, wo
 
 /* ---- context ------------------------------------------------------------------------------------------- */
 int         lbg_ctx_create(int device, lbg_ctx** out);
+/* A further context on the same GPU (own stream, scratch and mutex) whose calls may overlap those of lane 0: lane 0 streams have
+ * the device's highest priority, lanes >= 1 the lowest, so a long N0 launch on lane 1 yields SM slots to the short Limber /
+ * covariance kernels of lane 0 (lbgcmb_b200/Nkk.py n0_terms_async).  lbg_ctx_create(d, out) == lbg_ctx_create_lane(d, 0, out). */
+int         lbg_ctx_create_lane(int device, int lane, lbg_ctx** out);
 int         lbg_ctx_destroy(lbg_ctx* ctx);
 const char* lbg_last_error(void);
 const char* lbg_version(void);

@@ -93,7 +93,7 @@ def _exact_u_rows(lensCl_interps, nolensCl_interps, ell, cphi, sphi, below):
 
 def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'), thetab=1., DeltaT=1.,
              iterative=False, fold_phi=True, device=None, Tcmb=None, grids=None,
-             lmax_T=3000., lmax_P=5000., lmin_v=2., cos_sin=None, exact_u_below=2.0):
+             lmax_T=3000., lmax_P=5000., lmin_v=2., cos_sin=None, exact_u_below=2.0, lane=0):
     """(N0[len(Ls)], {term: integral[len(Ls)]}) -- the combined noise plus the per-estimator integrals."""
     for t in terms:
         if t == 'TB':
@@ -103,7 +103,7 @@ def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'
     mask = 0
     for t in terms:
         mask |= TERM_BITS[t]
-    ctx = _ffi.context(device)
+    ctx = _ffi.context(device, lane)
     upload_cls(ctx, lensCl_interps, nolensCl_interps)
     ell, w_ell, pphi, w_phi = grids if grids is not None else root_grids()
     Ld = _ffi.f64(Ls)
@@ -127,6 +127,33 @@ def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'
     ms, launches = ctx.last_kernel_ms()
     last_stats.update(nodes=nodes.value, kernel_ms=ms, launches=launches, n_L=Ld.size, main_kernel_ms=ctx.last_main_kernel_ms())
     return out, {t: out_terms[i] for i, t in enumerate(('TT', 'TE', 'EE', 'EB', 'BB'))}
+
+
+_pool = None
+
+
+def _submit(fn):
+    global _pool
+    if _pool is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix='lbg-n0')
+    return _pool.submit(fn)
+
+
+def n0_terms_async(*args, **kw):
+    """`n0_terms` submitted to a worker thread on a second context of the same GPU (lane 1: own stream and scratch);
+    returns a concurrent.futures.Future whose result() is what n0_terms returns.
+
+    The N0 curve is the long pole of a forecast (25 ms for 4951 L) and nothing in the Limber stage depends on it until
+    the variances are formed (Ckg.py:83-87), so a driver can start it first and build its spectra meanwhile: the library
+    call releases the GIL and the two contexts' kernels share the GPU."""
+    kw.setdefault('lane', 1)
+    return _submit(lambda: n0_terms(*args, **kw))
+
+
+def Nkk_async(lensCl_interps, nolensCl_interps, Ls, terms=['TT', 'TE', 'EE', 'EB'], thetab=1., DeltaT=1., iterative=False):
+    """Future of Nkk(...) (no pickle cache): see n0_terms_async."""
+    return _submit(lambda: n0_terms(lensCl_interps, nolensCl_interps, Ls, terms, thetab, DeltaT, iterative, lane=1)[0])
 
 
 def _cache_path(Ls, terms, thetab, DeltaT, iterative):

@@ -51,6 +51,7 @@ def _declare(L):
     vp, i, d, u = C.c_void_p, C.c_int, C.c_double, C.c_uint
     sig = {
         'lbg_ctx_create': [i, C.POINTER(vp)],
+        'lbg_ctx_create_lane': [i, i, C.POINTER(vp)],
         'lbg_ctx_destroy': [vp],
         'lbg_last_kernel_ms': [vp, c_double_p, c_int_p],
         'lbg_last_main_kernel_ms': [vp, c_double_p],
@@ -98,10 +99,11 @@ def check(rc):
 class Context:
     """One per GPU: owns the stream, the uploaded tables and the workspaces (lbg_ctx)."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, lane=0):
         self._h = C.c_void_p()
         self.device = device
-        check(lib().lbg_ctx_create(int(device), C.byref(self._h)))
+        self.lane = lane
+        check(lib().lbg_ctx_create_lane(int(device), int(lane), C.byref(self._h)))
         self._cl_key = None
 
     def close(self):
@@ -146,14 +148,17 @@ def default_device():
     return int(os.environ.get('LBGCMB_DEVICE', os.environ.get('LOCAL_RANK', '0')))
 
 
-def context(device=None):
-    """Process-wide context cache keyed by device index."""
+def context(device=None, lane=0):
+    """Process-wide context cache keyed by (device index, lane).  Lane 0 is the default context; another lane is a second
+    context (own stream, own scratch, own mutex) on the same GPU, for calls that should overlap lane-0 work
+    (Nkk.n0_terms_async runs on lane 1)."""
     if device is None:
         device = default_device()
+    key = device if lane == 0 else (device, lane)
     with _lock:
-        ctx = _ctxs.get(device)
+        ctx = _ctxs.get(key)
     if ctx is None:
-        ctx = Context(device)
+        ctx = Context(device, lane)
         with _lock:
-            _ctxs[device] = ctx
+            ctx = _ctxs.setdefault(key, ctx)
     return ctx

@@ -83,8 +83,11 @@ using namespace lbg;
 extern "C" const char* lbg_last_error(void) { return g_err.c_str(); }
 extern "C" const char* lbg_version(void) { return "lbgcmb-b200 0.1.0 (sm_100a)"; }
 
-extern "C" int lbg_ctx_create(int device, lbg_ctx** out) {
+extern "C" int lbg_ctx_create(int device, lbg_ctx** out) { return lbg_ctx_create_lane(device, 0, out); }
+
+extern "C" int lbg_ctx_create_lane(int device, int lane, lbg_ctx** out) {
     LBG_REQUIRE(out != nullptr, "lbg_ctx_create: out is NULL");
+    LBG_REQUIRE(lane >= 0, "lbg_ctx_create_lane: lane %d is negative", lane);
     *out = nullptr;
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
@@ -98,7 +101,11 @@ extern "C" int lbg_ctx_create(int device, lbg_ctx** out) {
     lbg_ctx* c = new lbg_ctx();
     c->device = device;
     LBG_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
-    LBG_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    // lane 0 gets the device's highest stream priority, any other lane the lowest: when both lanes have CTAs pending, the short
+    // lane-0 kernels (Limber, covariance) are dispatched first as SM slots free up instead of waiting for the whole N0 grid
+    int prio_least = 0, prio_greatest = 0;
+    LBG_CUDA(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+    LBG_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, lane == 0 ? prio_greatest : prio_least));
     LBG_CUDA(cudaEventCreate(&c->ev0));
     LBG_CUDA(cudaEventCreate(&c->ev1));
     LBG_CUDA(cudaEventCreate(&c->ev2));

@@ -1281,6 +1281,10 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
         n0_reduce_kernel<<<n_L, 128, 0, st>>>(P, c->n0_L.as<double>(), d_part, n_special ? d_spart : nullptr, n_phi, c->n0_out.as<double>());
     t.launched();
     std::vector<double> host((size_t)6 * n_L);
+    // Wait for the kernels here, not inside the copy: a device-to-host copy into pageable memory issued while the stream is busy
+    // blocks in the driver for the whole kernel time and (measured, scripts/overlap_timeline.py) stalls the pageable copies of
+    // every other context of the process with it, which would serialise lane-0 calls behind this 25 ms launch.
+    LBG_CUDA(cudaStreamSynchronize(st));
     LBG_CUDA(cudaMemcpyAsync(host.data(), c->n0_out.p, host.size() * 8, cudaMemcpyDeviceToHost, st));
     int rc = t.finish();
     if (rc) return rc;

@@ -142,3 +142,27 @@ def test_full_grid_B_properties(ctx, cl_tables, monkeypatch):
     spot = np.array([137, 2222, 4321])
     ref = on0.nkk_root(on0.cl_interps(ell, lens), on0.cl_interps(ell, nolens), spot, ('TT', 'TE', 'EE', 'EB'), 1.4, 1.0, True)
     assert np.max(np.abs(full[spot - 50] / ref - 1)) < 1e-10
+
+
+def test_async_lane_matches_sync_and_overlaps_limber(ctx, cl_tables):
+    """Nkk.n0_terms_async / Nkk_async (second context of the same GPU): bit-identical to the blocking call, also when Limber
+    launches run on the default context while it is in flight."""
+    from lbgcmb_b200 import Nkk, pmh
+    from lbgcmb_b200.lensing import Ckk
+    from lbgcmb_b200.synthetic import eh_like_plin
+    ell, lens, nolens = cl_tables
+    li, ni = _interps(ell, lens, nolens)
+    Ls = np.arange(50, 450)
+    want, want_terms = Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False)
+    k, p = eh_like_plin()
+    Pk = pmh.get_PkInterps(pmh.PkTable(k, p))
+    ckk0 = Ckk(Pk, Ls.astype(np.float64))
+    fut = Nkk.n0_terms_async(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False)
+    ckk1 = [Ckk(Pk, Ls.astype(np.float64)) for _ in range(3)]          # default context, while N0 runs on lane 1
+    got, got_terms = fut.result()
+    assert np.array_equal(got, want)
+    for t in want_terms:
+        assert np.array_equal(got_terms[t], want_terms[t])
+    for c in ckk1:
+        assert np.array_equal(c, ckk0)
+    assert np.array_equal(Nkk.Nkk_async(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 7.0, False).result(), want)
