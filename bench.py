@@ -245,11 +245,30 @@ def run_reference(a, rank, world):
         'e2e': {'value': rate, 'unit': 'L-modes/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_JSON_FD = None
+
+
+def _stdout_for_json_only():
+    """Everything libraries write to fd 1 (NCCL prints its version banner there) goes to stderr; the JSON line alone is
+    written to the original stdout by emit()."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, (json.dumps(line) + '\n').encode())
 
 
 def main():
     a = parse()
+    _stdout_for_json_only()
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local = int(os.environ.get('LOCAL_RANK', '0'))
@@ -411,7 +430,7 @@ def main():
             line['cpu_baseline'] = {'value': r, 'unit': 'L-modes/s', 'cores': 1, 'kind': 'port',
                                     'sample': 'L=%s of the %d-L grid, numpy port (oracle/n0.py %.1f s; oracle/limber.py + fisher.py %.1f s '
                                               'incl. first-use HALOFIT rows), 1 process' % (sample.tolist(), Ls.size, s_n0, s_fc)}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
