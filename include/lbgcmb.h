@@ -113,6 +113,12 @@ int lbg_halofit_sigma2(lbg_ctx* ctx, int n_R, const double* R, double* out_sigma
  * {D^2, k_nl, n_eff, curvature, Omega_m(z), Omega_L(z), use_halofit (0 -> linear row, modi/cosmology.py:171), unused}. */
 int lbg_pk_build_table(lbg_ctx* ctx, int n_rows, const double* halo_z, double fnu, double om0, double w, int takahashi,
                        double* out_pnl /*[n_rows][n_k] or NULL: table stays on the device*/);
+/* The context holds up to 4 P(k,z) tables; one is current (the one lbg_pk_build_table fills and lbg_limber / lbg_pk_eval read).
+ * Makes table `slot` (0..3) current and returns its row count in *out_rows (0: nothing built in it yet).  Pointer swaps only.
+ * Every table is dropped when a new linear table or k grid is installed (lbg_upload_pk_linear, lbg_eh_linear_table,
+ * lbg_pk_upload_rows).  The reference has no counterpart: its camb interpolator answers any z (prep_camb.py:55-68); here a
+ * forecast that alternates between the C_gg, C_kg and C_kk z grids keeps one table per grid instead of rebuilding. */
+int lbg_pk_select_slot(lbg_ctx* ctx, int slot, int* out_rows);
 /* Caller-supplied rows P_r(k) on their own k grid (the `kp = (k, P)` tables modi/lensing.py:127-150 interpolates): replaces
  * the device table built by lbg_pk_build_table (call lbg_upload_pk_linear again before rebuilding one). */
 int lbg_pk_upload_rows(lbg_ctx* ctx, int n_k, const double* k, int n_rows, const double* rows /*[n_rows][n_k]*/);

@@ -84,12 +84,20 @@ struct lbg_ctx {
     lbg::DevBuf  s0, s1, s2, s3, s4, s5;
     // P(k) / Limber state (see limber.cu)
     int          n_k = 0;
-    lbg::DevBuf  pk_lnk, pk_plin;
-    int          pnl_nz = 0;
+    lbg::DevBuf  pk_lnk, pk_plin, pk_rdk;
+    int          pnl_nz = 0;         // rows of the CURRENT P(k,z) table (pk_pnl); 0 = none built
     lbg::DevBuf  pk_pnl;
+    // parked P(k,z) tables (lbg_pk_select_slot): a forecast alternates between a few z grids (C_gg, C_kg, C_kk nodes) and
+    // would otherwise rebuild the same rows for every spectrum; all are dropped when a new linear table / k grid is installed
+    static const int PK_SLOTS = 4;
+    int          pk_cur = 0;
+    int          store_nz[PK_SLOTS] = {0, 0, 0, 0};
+    lbg::DevBuf  pk_store[PK_SLOTS];
+    void drop_pk_tables() { pnl_nz = 0; for (int i = 0; i < PK_SLOTS; ++i) store_nz[i] = 0; }
 };
 
 namespace lbg {
+int upload_rdk(lbg_ctx* c, int n_k, const double* k);   // limber.cu: reciprocal k-cell widths for the installed k grid
 struct KernelTimer {   // records ev0/ev1 on the context stream around the kernels of one API call
     lbg_ctx* c;
     explicit KernelTimer(lbg_ctx* ctx) : c(ctx) { c->last_launches = 0; cudaEventRecord(c->ev0, c->stream); }

@@ -119,8 +119,9 @@ extern "C" int lbg_ctx_destroy(lbg_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : {&c->cl_rows, &c->cl_soa, &c->cl_pairs, &c->cl_poly, &c->n0_L, &c->n0_utab, &c->n0_phi, &c->n0_partial, &c->n0_out, &c->n0_rowflag, &c->n0_G,
-                      &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->pk_lnk, &c->pk_plin, &c->pk_pnl})
+                      &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->pk_lnk, &c->pk_plin, &c->pk_pnl, &c->pk_rdk})
         b->release();
+    for (DevBuf& b : c->pk_store) b.release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->stream);
     delete c;

@@ -175,7 +175,8 @@ extern "C" int lbg_eh_linear_table(lbg_ctx* c, double omega_matter, double omega
     if (out_plin) LBG_CUDA(cudaMemcpyAsync(out_plin, tab + n_k, nb, cudaMemcpyDeviceToHost, c->stream));
     int rc = t.finish();
     if (rc) return rc;
+    if ((rc = upload_rdk(c, n_k, k))) return rc;
     c->n_k = n_k;
-    c->pnl_nz = 0;
+    c->drop_pk_tables();
     return LBG_OK;
 }

@@ -108,44 +108,117 @@ __device__ __forceinline__ double interp_k(const double* __restrict__ ks, const 
 
 #define LIMBER_BT 8
 #define LIMBER_ZMIN 64     /* at least this many z nodes per split */
-#define LIMBER_SMAX 32
+#define LIMBER_SMAX 30     /* 39 l-blocks (4951 multipoles) x 30 splits = 1170 CTAs: one wave of 148 SMs x 8 CTAs */
+#ifndef LIMBER_U
+#define LIMBER_U 4         /* z nodes in flight per thread: their table loads (L2 latency) overlap */
+#endif
+#define LIMBER_WALK 6      /* cells the bracket may move from the previous z node before the search falls back to bisection */
 // Number of z splits: a function of n_z ONLY, so that a multipole's value does not depend on which other multipoles or
 // batch entries travel in the same call (tests/test_limber_gpu.py::test_limber_full_grid_properties).
 static inline int limber_splits(int n_z) { return std::max(1, std::min(LIMBER_SMAX, n_z / LIMBER_ZMIN)); }
 
+// RN(a / b) from rb = RN(1 / b) (a true IEEE reciprocal, computed once per z node / per k cell on the host) in five FMA-pipe
+// instructions instead of the ~45 of the division routine: q0 = RN(a rb) is within 1.5 ulp, the first residual step makes it
+// faithful, and for a faithful q and a correctly rounded reciprocal the second step returns the correctly rounded quotient
+// (Markstein 1990).  Outside the range where no intermediate can underflow / overflow it falls back to the division itself.
+// Checked bit for bit against a / b on 4e9 random pairs and on the bench grid by scripts/micro/div_markstein.cu.
+__device__ __forceinline__ double div_rn(double a, double b, double rb) {
+    double q = a * rb;
+    if (!(fabs(q) > 1e-250 && fabs(q) < 1e250)) return __ddiv_rn(a, b);
+    double r = fma(-q, b, a);
+    q = fma(r, rb, q);
+    r = fma(-q, b, a);
+    return fma(r, rb, q);
+}
+
+// The cell of np.interp: the unique lo with ks[lo] <= x < ks[lo + 1] (caller guarantees ks[0] <= x < ks[n_k - 1]).  x = (l + 1/2) / chi
+// moves by a fraction of a cell between neighbouring z nodes, so the search starts from the previous node's cell and walks; same
+// cell as the bisection of interp_k, hence the same value bit for bit.
+__device__ __forceinline__ int hunt_cell(const double* __restrict__ ks, int n_k, double x, int lo) {
+    int moved = 0;
+    while (x < __ldg(ks + lo)) { --lo; if (++moved > LIMBER_WALK) break; }
+    while (moved <= LIMBER_WALK && x >= __ldg(ks + lo + 1)) { ++lo; ++moved; }
+    if (moved > LIMBER_WALK) {
+        int hi = n_k - 1;
+        lo = 0;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (__ldg(ks + mid) <= x) lo = mid; else hi = mid;
+        }
+    }
+    return lo;
+}
+
 // partial[s][b][l] = sum_{z in split s} weight[b][z] * P_z(k = (l + 1/2) / chi_z).
-// Block = 128 consecutive l x up to LIMBER_BT batch entries (they share each P lookup) x one z split; the k grid sits in
-// shared memory (binary search), the P(k,z) table rows stream from L2.  148 SMs want >= ~600 blocks: Ckk on 4951 l is
-// 39 l-blocks x 31 splits.  Sums run in z order inside a split and in split order in limber_reduce_kernel (deterministic).
-__global__ void __launch_bounds__(128)
-limber_kernel(int n_batch, int n_ell, int n_z, int n_k, int z_per_split, const double* __restrict__ ell, const double* __restrict__ chi,
-              const double* __restrict__ weight /*[n_batch][n_z]*/, const int* __restrict__ prow /*[n_z] table row per z node*/,
-              const double* __restrict__ ks, const double* __restrict__ ptab, int oob, double* __restrict__ partial) {
-    extern __shared__ double sk[];
-    for (int i = threadIdx.x; i < n_k; i += blockDim.x) sk[i] = ks[i];
-    __syncthreads();
+// Block = 128 consecutive l x NB batch entries (they share each P lookup) x one z split.  The k grid and the reciprocal cell
+// widths (32 KB together) are read through L1; the P(k,z) table rows stream from L2.  No shared memory, so the CTAs co-reside
+// with whatever the other lane has on the SMs.
+// Each trip handles LIMBER_U z nodes: cells first (short walks), then all table loads, then the interpolations and the sums
+// IN z ORDER inside a split; split order in limber_reduce_kernel (deterministic, and the same additions in the same order as
+// one node per trip).  NB is the number of batch entries of this launch's blocks (1 for the reference-style single calls, else
+// LIMBER_BT with the last block's missing entries pointed at entry 0 and not stored).
+template <int NB>
+__global__ void __launch_bounds__(128, 8)
+limber_kernel(int n_batch, int n_ell, int n_z, int n_k, int z_per_split, const double* __restrict__ ell, const double* __restrict__ zc /*chi | RN(1/chi)*/,
+              const double* __restrict__ weight /*[n_batch][n_z]*/, const unsigned char* __restrict__ live_z /*[batch block][n_z]*/,
+              const int* __restrict__ prow /*[n_z] table row per z node*/, const double* __restrict__ ks,
+              const double* __restrict__ rdk /*[n_k - 1] RN(1 / (ks[i+1] - ks[i]))*/, const double* __restrict__ ptab, int oob,
+              double* __restrict__ partial) {
     const int il = blockIdx.x * blockDim.x + threadIdx.x;
-    const int b0 = blockIdx.y * LIMBER_BT;
-    const int nb = min(LIMBER_BT, n_batch - b0);
-    const int z0 = blockIdx.z * z_per_split, z1 = min(n_z, z0 + z_per_split);
     if (il >= n_ell) return;
+    const int b0 = blockIdx.y * NB;
+    const int z0 = blockIdx.z * z_per_split, z1 = min(n_z, z0 + z_per_split);
+    const double* __restrict__ chi = zc;
+    const double* __restrict__ rchi = zc + n_z;
+    const unsigned char* __restrict__ lv = live_z + (size_t)blockIdx.y * n_z;
+    const double* wq[NB];
+#pragma unroll
+    for (int q = 0; q < NB; ++q) wq[q] = weight + (size_t)(b0 + q < n_batch ? b0 + q : 0) * n_z;
     const double lp = ell[il] + 0.5;
-    double acc[LIMBER_BT];
+    const double k_first = __ldg(ks), k_last = __ldg(ks + n_k - 1);
+    double acc[NB];
 #pragma unroll
-    for (int q = 0; q < LIMBER_BT; ++q) acc[q] = 0.0;
-    for (int iz = z0; iz < z1; ++iz) {
-        bool any = false;
-        for (int q = 0; q < nb; ++q) any = any || (weight[(size_t)(b0 + q) * n_z + iz] != 0.0);
-        if (!any) continue;                                  // block-uniform
-        const double x = __ddiv_rn(lp, chi[iz]);            // Cgg.py:57, Ckg.py:51, cmb/lensing.py:34, modi/cosmology.py:156
-        const double pv = interp_k(sk, ptab + (size_t)prow[iz] * n_k, n_k, x, oob);
+    for (int q = 0; q < NB; ++q) acc[q] = 0.0;
+    int cell = (n_k - 1) >> 1;
+    for (int iz = z0; iz < z1; iz += LIMBER_U) {
+        bool live[LIMBER_U], inside[LIMBER_U];
+        int lo[LIMBER_U];
+        double x[LIMBER_U];
 #pragma unroll
-        for (int q = 0; q < LIMBER_BT; ++q)
-            if (q < nb) acc[q] += weight[(size_t)(b0 + q) * n_z + iz] * pv;
+        for (int u = 0; u < LIMBER_U; ++u) {
+            const int z = min(iz + u, z1 - 1);
+            live[u] = (iz + u < z1) && lv[z];        // block-uniform
+            x[u] = div_rn(lp, __ldg(chi + z), __ldg(rchi + z));   // Cgg.py:57, Ckg.py:51, cmb/lensing.py:34, modi/cosmology.py:156
+            inside[u] = x[u] >= k_first && x[u] < k_last;
+            lo[u] = x[u] < k_first ? 0 : n_k - 2;    // outside the grid, or exactly on the last knot: P[0] / P[n_k - 1] below
+            if (live[u] && inside[u]) { cell = hunt_cell(ks, n_k, x[u], cell); lo[u] = cell; }
+        }
+        double p0[LIMBER_U], p1[LIMBER_U];
+#pragma unroll
+        for (int u = 0; u < LIMBER_U; ++u) {
+            const double* row = ptab + (size_t)__ldg(prow + min(iz + u, z1 - 1)) * n_k + lo[u];
+            p0[u] = live[u] ? __ldg(row) : 0.0;
+            p1[u] = live[u] ? __ldg(row + 1) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < LIMBER_U; ++u) {
+            if (!live[u]) continue;
+            double pv;
+            if (inside[u]) {                         // np.interp with numpy's operation order
+                const double k0 = __ldg(ks + lo[u]), k1 = __ldg(ks + lo[u] + 1);
+                const double slope = div_rn(__dsub_rn(p1[u], p0[u]), __dsub_rn(k1, k0), __ldg(rdk + lo[u]));
+                pv = __dadd_rn(__dmul_rn(slope, __dsub_rn(x[u], k0)), p0[u]);
+            } else if (x[u] < k_first) pv = oob ? p0[u] : 0.0;
+            else if (x[u] > k_last) pv = oob ? p1[u] : 0.0;
+            else pv = p1[u];                         // x == k_last (NaN ends here too and stays NaN through p1 only if the table has one)
+            const int z = iz + u;
+#pragma unroll
+            for (int q = 0; q < NB; ++q) acc[q] += __ldg(wq[q] + z) * pv;
+        }
     }
 #pragma unroll
-    for (int q = 0; q < LIMBER_BT; ++q)
-        if (q < nb) partial[((size_t)blockIdx.z * n_batch + b0 + q) * n_ell + il] = acc[q];
+    for (int q = 0; q < NB; ++q)
+        if (b0 + q < n_batch) partial[((size_t)blockIdx.z * n_batch + b0 + q) * n_ell + il] = acc[q];
 }
 
 __global__ void limber_reduce_kernel(size_t n, int n_split, const double* __restrict__ partial, double* __restrict__ out) {
@@ -165,6 +238,16 @@ __global__ void pk_eval_kernel(int n, int n_k, const double* __restrict__ ks, co
 
 using namespace lbg;
 
+// RN(1 / (k[i+1] - k[i])) for the Limber kernel's np.interp slope (div_rn); called by everything that installs a k grid.
+int lbg::upload_rdk(lbg_ctx* c, int n_k, const double* k) {
+    std::vector<double> r((size_t)n_k, 0.0);
+    for (int i = 0; i + 1 < n_k; ++i) r[i] = 1.0 / (k[i + 1] - k[i]);
+    if (c->pk_rdk.reserve(r.size() * 8)) return LBG_ENOMEM;
+    LBG_CUDA(cudaMemcpyAsync(c->pk_rdk.p, r.data(), r.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    LBG_CUDA(cudaStreamSynchronize(c->stream));
+    return LBG_OK;
+}
+
 extern "C" int lbg_upload_pk_linear(lbg_ctx* c, int n_k, const double* k, const double* plin_z0, const double* w_lnk) {
     LBG_REQUIRE(c && k && plin_z0 && w_lnk, "lbg_upload_pk_linear: NULL argument");
     LBG_REQUIRE(n_k >= 4 && n_k <= 6000, "lbg_upload_pk_linear: n_k=%d outside [4, 6000] (k grid is staged in shared memory)", n_k);
@@ -181,8 +264,9 @@ extern "C" int lbg_upload_pk_linear(lbg_ctx* c, int n_k, const double* k, const 
     if (c->pk_lnk.reserve(buf.size() * 8)) return LBG_ENOMEM;
     LBG_CUDA(cudaMemcpyAsync(c->pk_lnk.p, buf.data(), buf.size() * 8, cudaMemcpyHostToDevice, c->stream));
     LBG_CUDA(cudaStreamSynchronize(c->stream));
+    if (int rc = upload_rdk(c, n_k, k)) return rc;
     c->n_k = n_k;
-    c->pnl_nz = 0;
+    c->drop_pk_tables();
     return LBG_OK;
 }
 
@@ -221,6 +305,21 @@ extern "C" int lbg_pk_build_table(lbg_ctx* c, int n_rows, const double* halo_z /
     return rc;
 }
 
+extern "C" int lbg_pk_select_slot(lbg_ctx* c, int slot, int* out_rows) {
+    LBG_REQUIRE(c, "lbg_pk_select_slot: ctx is NULL");
+    LBG_REQUIRE(slot >= 0 && slot < lbg_ctx::PK_SLOTS, "lbg_pk_select_slot: slot %d outside [0, %d)", slot, lbg_ctx::PK_SLOTS);
+    std::lock_guard<std::mutex> g(c->mu);
+    if (slot != c->pk_cur) {                       // park the current table, bring the requested one in (pointer swaps, no GPU work)
+        std::swap(c->pk_pnl, c->pk_store[c->pk_cur]);
+        std::swap(c->pnl_nz, c->store_nz[c->pk_cur]);
+        std::swap(c->pk_pnl, c->pk_store[slot]);
+        std::swap(c->pnl_nz, c->store_nz[slot]);
+        c->pk_cur = slot;
+    }
+    if (out_rows) *out_rows = c->pnl_nz;
+    return LBG_OK;
+}
+
 extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell, int n_z, const double* chi,
                           const double* weight /*[n_batch][n_z]*/, const int* prow /*[n_z]*/, int oob,
                           double* out_cl /*[n_batch][n_ell]*/) {
@@ -232,21 +331,35 @@ extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell,
     std::lock_guard<std::mutex> g(c->mu);
     LBG_CUDA(cudaSetDevice(c->device));
     const size_t bw = (size_t)n_batch * n_z * 8, bo = (size_t)n_batch * n_ell * 8;
-    if (c->s0.reserve((size_t)n_ell * 8) || c->s1.reserve((size_t)n_z * 8) || c->s2.reserve(bw) || c->s3.reserve((size_t)n_z * 4) || c->s4.reserve(bo)) return LBG_ENOMEM;
+    if (c->s0.reserve((size_t)n_ell * 8) || c->s1.reserve((size_t)n_z * 16) || c->s2.reserve(bw) ||
+        c->s3.reserve((size_t)n_z * 4 + (size_t)((n_batch + LIMBER_BT - 1) / LIMBER_BT + 1) * n_z) || c->s4.reserve(bo)) return LBG_ENOMEM;
     const int n_split = limber_splits(n_z), z_per_split = (n_z + n_split - 1) / n_split;
     if (n_split > 1 && c->s5.reserve(bo * n_split)) return LBG_ENOMEM;
     cudaStream_t st = c->stream;
     LBG_CUDA(cudaMemcpyAsync(c->s0.p, ell, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(c->s1.p, chi, (size_t)n_z * 8, cudaMemcpyHostToDevice, st));
+    std::vector<double> zc(2 * (size_t)n_z);                  // chi | RN(1 / chi) for div_rn
+    for (int i = 0; i < n_z; ++i) { zc[i] = chi[i]; zc[(size_t)n_z + i] = 1.0 / chi[i]; }
+    LBG_CUDA(cudaMemcpyAsync(c->s1.p, zc.data(), zc.size() * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s2.p, weight, bw, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(c->s3.p, prow, (size_t)n_z * 4, cudaMemcpyHostToDevice, st));
-    const size_t smem = (size_t)c->n_k * 8;
-    if (smem > 48 * 1024) LBG_CUDA(cudaFuncSetAttribute(limber_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int nbk = n_batch == 1 ? 1 : LIMBER_BT, n_bb = (n_batch + nbk - 1) / nbk;
+    // s3: prow[n_z] (int) then live[n_bb][n_z] (bytes): a z node none of a block's batch entries weights is skipped by that block
+    std::vector<unsigned char> meta((size_t)n_z * 4 + (size_t)n_bb * n_z);
+    memcpy(meta.data(), prow, (size_t)n_z * 4);
+    for (int bb = 0; bb < n_bb; ++bb)
+        for (int i = 0; i < n_z; ++i) {
+            bool any = false;
+            for (int q = bb * nbk; q < std::min(n_batch, (bb + 1) * nbk); ++q) any = any || (weight[(size_t)q * n_z + i] != 0.0);
+            meta[(size_t)n_z * 4 + (size_t)bb * n_z + i] = any;
+        }
+    LBG_CUDA(cudaMemcpyAsync(c->s3.p, meta.data(), meta.size(), cudaMemcpyHostToDevice, st));
     KernelTimer t(c);
     double* part = n_split > 1 ? c->s5.as<double>() : c->s4.as<double>();
-    limber_kernel<<<dim3((n_ell + 127) / 128, (n_batch + LIMBER_BT - 1) / LIMBER_BT, n_split), 128, smem, st>>>(
-        n_batch, n_ell, n_z, c->n_k, z_per_split, c->s0.as<double>(), c->s1.as<double>(), c->s2.as<double>(), c->s3.as<int>(),
-        c->pk_lnk.as<double>(), c->pk_pnl.as<double>(), oob, part);
+    const dim3 grid((n_ell + 127) / 128, n_bb, n_split);
+    const unsigned char* live = (const unsigned char*)c->s3.p + (size_t)n_z * 4;
+#define LBG_LIMBER(NB) limber_kernel<NB><<<grid, 128, 0, st>>>(n_batch, n_ell, n_z, c->n_k, z_per_split, c->s0.as<double>(), c->s1.as<double>(), \
+        c->s2.as<double>(), live, c->s3.as<int>(), c->pk_lnk.as<double>(), c->pk_rdk.as<double>(), c->pk_pnl.as<double>(), oob, part)
+    if (nbk == 1) LBG_LIMBER(1); else LBG_LIMBER(LIMBER_BT);
+#undef LBG_LIMBER
     t.launched();
     if (n_split > 1) {
         const size_t n = (size_t)n_batch * n_ell;
@@ -288,7 +401,9 @@ extern "C" int lbg_pk_upload_rows(lbg_ctx* c, int n_k, const double* k, int n_ro
     LBG_CUDA(cudaMemcpyAsync(c->pk_lnk.p, buf.data(), buf.size() * 8, cudaMemcpyHostToDevice, c->stream));
     LBG_CUDA(cudaMemcpyAsync(c->pk_pnl.p, rows, (size_t)n_rows * n_k * 8, cudaMemcpyHostToDevice, c->stream));
     LBG_CUDA(cudaStreamSynchronize(c->stream));
+    if (int rc = upload_rdk(c, n_k, k)) return rc;
     c->n_k = n_k;
+    c->drop_pk_tables();
     c->pnl_nz = n_rows;
     return LBG_OK;
 }

@@ -15,6 +15,7 @@ from lbgcmb_b200.modi import halofit as _hf
 from lbgcmb_b200.quadrature import simps_weights_x, romberg
 
 _owner = _ffi.table_owner
+_PK_SLOTS = 4                            # lbg_ctx::PK_SLOTS
 
 
 class Cosmology(object):
@@ -40,6 +41,8 @@ class Cosmology(object):
         self._spl0 = None
         self._rows_cache = {}
         self._rows_key = None
+        self._slots = {}                 # z-grid key -> device table slot (lbg_pk_select_slot); insertion order = LRU order
+        self._cur_slot = 0
 
     # ---- background (host) ------------------------------------------------------------------------------------
     def _za(self, z, a):
@@ -109,6 +112,7 @@ class Cosmology(object):
             _ffi.check(_ffi.lib().lbg_upload_pk_linear(ctx.handle, k.size, _ffi._dp(k), _ffi._dp(p), _ffi._dp(w)))
             _owner[ctx.device] = id(self)
             self._rows_key = None
+            self._slots = {}             # the upload dropped every P(k,z) table of the context
         return ctx
 
     def invalidate_device(self):
@@ -117,6 +121,7 @@ class Cosmology(object):
             _owner[_ffi.context(self.device).device] = None
         self._rows_key = None
         self._rows_cache = {}
+        self._slots = {}
 
     def _sigma2_z0(self, R):
         ctx = self._ctx()
@@ -185,6 +190,24 @@ class Cosmology(object):
         ctx = self._ctx()
         if self._rows_key == key and not want_host:
             return None
+        slot = self._slots.pop(key, None)
+        if slot is not None and not want_host:                  # built earlier for this z grid and still parked on the device
+            self._slots[key] = slot
+            self._select_slot(ctx, slot)
+            self._rows_key = key
+            return None
+        if slot is None:
+            # single-row tables (pk_eval, pkalin / pkanlin) share the last slot so that they do not evict the z-grid tables
+            small = zs.size == 1
+            pool = (_PK_SLOTS - 1,) if small else range(_PK_SLOTS - 1)
+            used = set(self._slots.values())
+            free = [i for i in pool if i not in used]
+            if free:
+                slot = free[0]
+            else:
+                old = next(k for k, v in self._slots.items() if v in pool)   # least recently used
+                slot = self._slots.pop(old)
+        self._select_slot(ctx, slot)
         rows = self._rows_cache.get(key)        # per z grid: D^2, k_nl, n_eff, C, Omega_m(z), Omega_L(z) (dropped by invalidate_device)
         if rows is None:
             rows = np.zeros((zs.size, 8))
@@ -207,7 +230,14 @@ class Cosmology(object):
         _ffi.check(_ffi.lib().lbg_pk_build_table(ctx.handle, zs.size, _ffi._dp(_ffi.f64(rows)), float(fnu), float(self.cosmo.Om0),
                                                  -1.0, 1, _ffi._dp(out) if want_host else None))
         self._rows_key = key
+        self._slots[key] = slot
         return out
+
+    def _select_slot(self, ctx, slot):
+        import ctypes as C
+        n = C.c_int(0)
+        _ffi.check(_ffi.lib().lbg_pk_select_slot(ctx.handle, int(slot), C.byref(n)))
+        self._cur_slot = slot
 
     def pkalin(self, z=None, a=None):
         z, a = self._za(z, a)
@@ -241,6 +271,7 @@ class Cosmology(object):
         _ffi.check(_ffi.lib().lbg_pk_upload_rows(ctx.handle, k.size, _ffi._dp(k), rows.shape[0], _ffi._dp(rows)))
         _owner[ctx.device] = None                              # the linear table must be uploaded again before HALOFIT rows
         self._rows_key = None
+        self._slots = {}
         ells, chis, w = _ffi.f64(np.atleast_1d(ells)), _ffi.f64(np.atleast_1d(chis)), _ffi.f64(np.atleast_2d(weights))
         prow = np.ascontiguousarray(prow, dtype=np.int32)
         if w.shape[1] != chis.size or prow.size != chis.size:
