@@ -79,10 +79,15 @@ def dp_DL(p, fid_sig8, fid_b1, DL):
         raise ValueError('\n\nDerivative with respect to given parameter is not available.\n\n')
 
 
-def fisher_bias(Llls, nmodes, Cls, Nls, xCls, xNls, fsky, fid_sig8, fid_b1, LllMax, device=None):
+def fisher_bias(Llls, nmodes, Cls, Nls, xCls, xNls, fsky, fid_sig8, fid_b1, LllMax, device=None, fused=True):
     """interloper.py:200-260: Fisher matrix of (sigma8, b1) from D = (Ckk, Ckg, Cgg) for L < LllMax and the parameter shift
-    caused by the contaminated spectra xCls / xNls.  Returns dict(Fisher, iFisher, interim, dtheta, biased_sig8, biased_b1)."""
+    caused by the contaminated spectra xCls / xNls.  Returns dict(Fisher, iFisher, interim, dtheta, biased_sig8, biased_b1).
+    `fused=False` forces the general route (get_ClsCov + fisher_accum) for inputs the one-launch route would also accept."""
     Llls = np.asarray(Llls)
+    one = _fused_fisher_bias(Llls, nmodes, Cls, Nls, xCls, xNls, fsky, fid_sig8, fid_b1, LllMax, device) if fused else None
+    if one is not None:
+        Fisher, interim = one
+        return _finish_bias(Fisher, interim, fid_sig8, fid_b1)
     covs = get_ClsCov(Llls, Cls, Nls, fsky)
     keep = Llls < LllMax                                                 # :221
     n = int(np.count_nonzero(keep))
@@ -104,13 +109,38 @@ def fisher_bias(Llls, nmodes, Cls, Nls, xCls, xNls, fsky, fid_sig8, fid_b1, LllM
     DDL = np.stack([np.zeros(n), dckg, dcgg], axis=1)                    # :250
     w = np.asarray(nmodes, dtype=np.float64)[:n]
     Fisher, interim = _fisher.fisher_accum(cov, dD, w, dDelta=DDL, device=device)
+    return _finish_bias(Fisher, interim, fid_sig8, fid_b1)
+
+
+def _finish_bias(Fisher, interim, fid_sig8, fid_b1):
     iFisher = inv(Fisher)
     dtheta = np.zeros(2)
     for i in range(2):
         for j in range(2):
-            dtheta[i] += iFisher[i, j] * interim[j]
+            dtheta[i] += iFisher[i, j] * interim[j]                      # interloper.py:255-258
     return {'Fisher': Fisher, 'iFisher': iFisher, 'interim': interim, 'dtheta': dtheta,
             'biased_sig8': fid_sig8 + dtheta[0], 'biased_b1': fid_b1 + dtheta[1]}
+
+
+def _fused_fisher_bias(Llls, nmodes, Cls, Nls, xCls, xNls, fsky, fid_sig8, fid_b1, LllMax, device):
+    """One launch (csrc/sweep.cu, a 1 x 1 design grid) when the inputs have the shape get_allCls gives them -- constant N_gg,
+    N_kg = 0, C_gk = C_kg, increasing L: the per-multipole covariance, its solve and the Fisher / bias sums never leave the
+    device.  Any other input takes the general get_ClsCov + fisher_accum route; the two agree to 1e-12
+    (tests/test_sweep_gpu.py, tests/test_forecast_stage_gpu.py)."""
+    from lbgcmb_b200.sweep import forecast_grid
+    try:
+        ngg, xngg = np.asarray(Nls['gg'], dtype=np.float64), np.asarray(xNls['gg'], dtype=np.float64)
+        ok = (ngg.size > 0 and np.all(ngg == ngg.flat[0]) and np.all(xngg == xngg.flat[0])
+              and not np.any(Nls['kg']) and not np.any(Nls['gk']) and not np.any(xNls['kg'])
+              and (Cls['gk'] is Cls['kg'] or np.array_equal(Cls['gk'], Cls['kg']))
+              and np.all(np.diff(Llls) > 0))
+    except (KeyError, TypeError, ValueError):
+        return None
+    if not ok:
+        return None
+    out = forecast_grid(Llls, nmodes, Cls['kk'], Cls['gg'], Cls['kg'], ngg.flat[0], Nls['kk'], fsky, fid_sig8, fid_b1, LllMax,
+                        xcgg=xCls['gg'], xckg=xCls['kg'], xngg=xngg.flat[0], device=device)
+    return out[0, 0, 1:5].reshape(2, 2).copy(), out[0, 0, 5:7].copy()
 
 
 def save_result(path, peakz, band, int_frac, res):

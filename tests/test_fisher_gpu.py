@@ -52,9 +52,15 @@ def test_fisher_bias_golden(ctx, g):
     from oracle import fisher as ofi
     Cls, Nls, xCls, xNls = _dicts(g)
     args = (g['Llls'], g['nmodes'], Cls, Nls, xCls, xNls, float(g['fsky']), float(g['fid_sig8']), float(g['fid_b1']), float(g['LllMax']))
-    got = fisher_bias(*args)
+    got = fisher_bias(*args)                       # one launch (csrc/sweep.cu) when the inputs have get_allCls's shape
+    gen = fisher_bias(*args, fused=False)          # get_ClsCov + fisher_accum
     for key in ('Fisher', 'iFisher', 'interim', 'dtheta'):
         assert np.max(np.abs(got[key] / g[key] - 1)) < RTOL, key
+        assert np.max(np.abs(gen[key] / g[key] - 1)) < RTOL, key
+        assert np.max(np.abs(got[key] / gen[key] - 1)) < 1e-11, key
+    Nls2 = dict(Nls, gg=Nls['gg'] * np.linspace(1., 1.1, len(g['Llls'])))     # non-constant N_gg: general route only
+    a, b = fisher_bias(args[0], args[1], Cls, Nls2, *args[4:]), fisher_bias(args[0], args[1], Cls, Nls2, *args[4:], fused=False)
+    assert np.array_equal(a['Fisher'], b['Fisher'])
     ora = ofi.fisher_bias(*args)
     assert np.max(np.abs(got['Fisher'] / ora['Fisher'] - 1)) < RTOL
     assert np.allclose(got['iFisher'], got['iFisher'].T, rtol=1e-12)

@@ -50,7 +50,7 @@ def test_forecast_grid_matches_mirrors(ctx, setup):
             xNls = {'gg': xngg[g] * np.ones_like(Ls), 'kg': z, 'gk': z, 'kk': nkk[n]}
             vkg = ((ckk + nkk[n]) * (cgg[g] + ngg[g]) + ckg[g] ** 2.) / ((2. * Ls + 1.) * bench.FSKY)
             sn = snr.snr(Ls, ckg[g], vkg, nmodes, lmax=s['LllMax'])
-            fb = interloper.fisher_bias(Ls, nmodes, Cls, Nls, xCls, xNls, bench.FSKY, 0.819, s['fid_b1'], s['LllMax'])
+            fb = interloper.fisher_bias(Ls, nmodes, Cls, Nls, xCls, xNls, bench.FSKY, 0.819, s['fid_b1'], s['LllMax'], fused=False)
             ref = np.concatenate([[sn], fb['Fisher'].ravel(), fb['interim']])
             assert np.max(np.abs(out[n, g, :7] / ref - 1)) < 1e-12, (n, g, out[n, g], ref)
     nob = sweep.forecast_grid(Ls, nmodes, ckk, cgg, ckg, ngg, nkk, bench.FSKY, 0.819, [s['fid_b1'] for s in samples],
