@@ -196,16 +196,6 @@ extern "C" int lbg_upload_cl_tables(lbg_ctx* c, int n_ell, const double* lensed,
     LBG_CUDA(cudaMemcpyAsync(c->cl_rows.p, rows.data(), rows.size() * sizeof(ClRow), cudaMemcpyHostToDevice, c->stream));
     LBG_CUDA(cudaMemcpyAsync(c->cl_soa.p, soa.data(), soa.size() * 8, cudaMemcpyHostToDevice, c->stream));
     c->cl_soa_stride = stride;
-    if (n_ell + 2 <= LBG_PAIR_STRIDE) {
-        std::vector<double> pr((size_t)8 * LBG_PAIR_STRIDE * 2, 0.0);
-        for (int k = 0; k < 8; ++k)
-            for (int r = 0; r < n_ell + 2; ++r) {
-                pr[((size_t)k * LBG_PAIR_STRIDE + r) * 2] = soa[(size_t)k * stride + r];
-                pr[((size_t)k * LBG_PAIR_STRIDE + r) * 2 + 1] = r + 1 < n_ell + 2 ? soa[(size_t)k * stride + r + 1] : 0.0;
-            }
-        if (c->cl_pairs.reserve(pr.size() * 8)) return LBG_ENOMEM;
-        LBG_CUDA(cudaMemcpyAsync(c->cl_pairs.p, pr.data(), pr.size() * 8, cudaMemcpyHostToDevice, c->stream));
-    }
     LBG_CUDA(cudaStreamSynchronize(c->stream));
     c->n_ell = n_ell;
     c->ub_zero = true;

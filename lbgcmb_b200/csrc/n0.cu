@@ -437,6 +437,14 @@ __device__ __forceinline__ void n0_fast_node(const N0Params& P, const double* __
 }
 
 // G[i] = exp(a i (i + 1)) on the integer knots (cmb/DetectorNoise.py:22 without the amplitude).
+// pairs[k][r] = (c_k[r], c_k[r + 1]) for the eight spectra (rows2 kernel): double2[8][LBG_PAIR_STRIDE], zero beyond the table.
+__global__ void n0_pairs_kernel(int n, int stride, const double* __restrict__ soa, double* __restrict__ pairs) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
+    if (r >= n || r >= LBG_PAIR_STRIDE) return;
+    pairs[((size_t)k * LBG_PAIR_STRIDE + r) * 2] = soa[(size_t)k * stride + r];
+    pairs[((size_t)k * LBG_PAIR_STRIDE + r) * 2 + 1] = r + 1 < n ? soa[(size_t)k * stride + r + 1] : 0.0;
+}
+
 __global__ void n0_noise_knots_kernel(int n, double a, double* __restrict__ G) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) G[i] = exp(((double)i * ((double)i + 1.0)) * a);
@@ -1253,6 +1261,11 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
 #undef LBG_R5
 #undef LBG_R3
     } else if (variant == 2) {
+        // overlapping-pair copy of the spline coefficients, built from the spectrum-major table (only this variant reads it)
+        if (c->cl_pairs.reserve((size_t)8 * LBG_PAIR_STRIDE * 16)) return LBG_ENOMEM;
+        LBG_CUDA(cudaMemsetAsync(c->cl_pairs.p, 0, (size_t)8 * LBG_PAIR_STRIDE * 16, st));
+        n0_pairs_kernel<<<dim3((c->n_ell + 2 + 255) / 256, 8), 256, 0, st>>>(c->n_ell + 2, c->cl_soa_stride, c->cl_soa.as<double>(), c->cl_pairs.as<double>());
+        t.launched();
         const double xmax = P.a * 2.0 * (double)c->n_ell;                 // largest Taylor argument of the noise factor
         const size_t smem = ((size_t)4 * n_phe + 5 * 4) * 8;
         n0_noise_knots_kernel<<<(c->n_ell + 255) / 256, 256, 0, st>>>(c->n_ell, P.a, c->n0_G.as<double>());

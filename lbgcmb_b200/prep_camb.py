@@ -54,6 +54,8 @@ def table_of(interp, n_default=None):
     x = getattr(interp, 'x', None)
     y = getattr(interp, 'y', None)
     if x is not None and y is not None:
+        if isinstance(interp, ClInterp):                       # integer knots 0..n-1 checked at construction
+            return interp.y
         x = np.asarray(x, dtype=np.float64)
         if x.ndim == 1 and np.array_equal(x, np.arange(x.size)):
             return _ffi.f64(y)

@@ -166,3 +166,18 @@ def test_async_lane_matches_sync_and_overlaps_limber(ctx, cl_tables):
     for c in ckk1:
         assert np.array_equal(c, ckk0)
     assert np.array_equal(Nkk.Nkk_async(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 7.0, False).result(), want)
+
+
+def test_kernel_variants_agree(ctx, cl_tables, monkeypatch):
+    """The earlier integrand kernels stay selectable (LBG_N0_VARIANT: 0 node-per-thread, 1 rows, 2 rows + pair table built on the
+    device, 3 rows3) and agree with the default rows5 kernel to 1e-12."""
+    from lbgcmb_b200 import Nkk
+    ell, lens, nolens = cl_tables
+    li, ni = _interps(ell, lens, nolens)
+    Ls = np.array([50, 333, 2999, 3001, 5000])
+    want = Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False)[0]
+    for v in ('0', '1', '2', '3'):
+        monkeypatch.setenv('LBG_N0_VARIANT', v)
+        got = Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False)[0]
+        assert np.max(np.abs(got / want - 1)) < 1e-12, v
+    monkeypatch.delenv('LBG_N0_VARIANT')
