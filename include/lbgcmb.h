@@ -140,6 +140,14 @@ int lbg_eh_transfer(lbg_ctx* ctx, double omega_matter, double omega_baryon, doub
 int lbg_eh_linear_table(lbg_ctx* ctx, double omega_matter, double omega_baryon, double omega_hdm, int degen_hdm, double omega_lambda,
                         double hubble, double ns, double sigma8, int n_k, const double* k, const double* w_lnk, double* out_plin);
 
+/* ---- linear growth tables; replaces the 1000 `romberg` calls of modi/cosmology.py:92-111 (_eval_Dplus) for n_cosmo cosmologies in
+ *      one launch: out_y[c][i] = E(a_i) * romberg(kernel, loga[0], loga[i]) with kernel(ln a) = (a E(a))^-3 a and
+ *      E(a) = a^-1.5 sqrt(M + (1 - M - L) a + L a^3) (modi/cosmology.py:119-125); the scipy-1.2.1 rule (tol = rtol = 1.48e-8,
+ *      at most 2^10 panels).  D(a) / D(1) is then the reference's cubic spline through (a_i, y_i) (:111-117), left to the host.
+ *      out_levels (may be NULL) receives the refinement level at which each node stopped. */
+int lbg_growth_table(lbg_ctx* ctx, int n_cosmo, const double* omega_m, const double* omega_l, int n, const double* loga,
+                     double* out_y, int* out_levels);
+
 /* ---- Limber: C_l[b][l] = sum_z weight[b][z] * P_{prow[z]}(k = (l + 1/2)/chi[z]); replaces the z loops + quadrature of
  *      Cgg.py:53-68, Ckg.py:42-59, cmb/lensing.py:27-43 (Simpson in z) and modi/lensing.py:127-179 (trapezoid in chi).
  *      weight = kernel product x bias x unit factors x quadrature weight, so one kernel serves every flavour. */

@@ -53,6 +53,7 @@ def _declare(L):
         'lbg_ctx_create': [i, C.POINTER(vp)],
         'lbg_ctx_create_lane': [i, i, C.POINTER(vp)],
         'lbg_pk_select_slot': [vp, i, C.POINTER(C.c_int)],
+        'lbg_growth_table': [vp, i, c_double_p, c_double_p, i, c_double_p, c_double_p, C.POINTER(C.c_int)],
         'lbg_ctx_destroy': [vp],
         'lbg_last_kernel_ms': [vp, c_double_p, c_int_p],
         'lbg_last_main_kernel_ms': [vp, c_double_p],

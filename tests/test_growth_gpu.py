@@ -1,0 +1,31 @@
+"""Linear-growth tables on the device (csrc/growth.cu) against the host restatement of the reference's
+`_eval_Dplus` (modi/cosmology.py:92-111, scipy-1.2.1 romberg; itself pinned to the reference in tests/test_oracle_pinning.py)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_growth_tables_match_host_romberg(ctx):
+    from lbgcmb_b200.modi.cosmology import Cosmology, growth_tables, LOGA_NODES
+    from lbgcmb_b200.synthetic import eh_like_plin
+    k, p = eh_like_plin()
+    cosmos = [(0.292, 0.708), (0.25, 0.70), (1.0, 0.0), (0.35, 0.65)]
+    tabs, lev = growth_tables([c[0] for c in cosmos], [c[1] for c in cosmos], want_levels=True)
+    assert tabs.shape == (4, 1000) and np.all(tabs[:, 0] == 0.0) and np.all(tabs[:, 1:] > 0)
+    assert lev.min() >= 1 and lev.max() <= 10
+    zs = np.concatenate([[0.0], np.linspace(0.01, 10., 400), [50., 1100.]])
+    for (M, L), y in zip(cosmos, tabs):
+        host = Cosmology(M=M, L=L, B=0.0468, klin=k, plin=p)                    # 1000 Romberg integrals on the host
+        want = host.Dplus(np.exp(LOGA_NODES))
+        assert np.max(np.abs(y[1:] / want[1:] - 1)) < 1e-12
+        dev = Cosmology(M=M, L=L, B=0.0468, klin=k, plin=p, Dplus_table=y)
+        assert np.max(np.abs(dev.Dgrow(z=zs) / host.Dgrow(z=zs) - 1)) < 1e-12
+    one = Cosmology(M=0.292, B=0.0468, klin=k, plin=p, Dplus_table='device')
+    assert np.max(np.abs(one.Dplus(np.exp(LOGA_NODES[1:])) / tabs[0, 1:] - 1)) < 1e-15
+    # matter-dominated: D+ ~ a to the accuracy of the rule (its own tolerance, 1.48e-8)
+    a = np.exp(LOGA_NODES[500:])
+    eds = tabs[2, 500:] / tabs[2, -1]
+    assert np.max(np.abs(eds / a - 1)) < 1e-6
+    with pytest.raises(Exception):
+        growth_tables([-0.3])
