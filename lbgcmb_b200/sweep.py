@@ -101,3 +101,54 @@ def survey_sweep(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noi
     out = _dist.allgather_concat(out.ravel()).reshape(len(noise_configs), len(samples), 8)
     nkk = _dist.allgather_concat(nkk.ravel()).reshape(len(noise_configs), Ld.size)
     return {'out': out, 'nkk': nkk, 'ckk': ckk, 'cgg': cgg, 'ckg': ckg, 'ngg': ngg}
+
+
+def sharded_forecast(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noise_config, sample, fsky, fid_sig8=0.819,
+                     xsample=None, zmin=0.01, zmax=10.0, terms=('TT', 'TE', 'EE', 'EB'), n0_fn=None, spectra_fn=None, grid_fn=None):
+    """ONE forecast (one experiment, one galaxy sample) with the multipole grid sharded over the ranks -- the layout north_star
+    names: every rank evaluates N0, C_kk, C_gg, C_kg and the per-multipole covariance / Fisher terms on its own contiguous block
+    of L (dist.shard_slice; N0 per L and Limber per l are independent), and the only exchange inside the path is ONE all-reduce
+    of the partial sums (S/N^2, the 2 x 2 Fisher matrix of (sigma8, b1), the bias vector): 7 doubles over NCCL.  The curves are
+    then gathered so that every rank returns the full arrays, as snr.py / interloper.py produce them.
+
+    noise_config = (thetab, DeltaT, iterative); sample = {'pz', 'bz', 'nbar', 'fid_b1', 'LllMax'}; xsample: the interloper-
+    contaminated twin (bias vector).  Returns {'snr', 'Fisher', 'interim', 'dtheta', 'nkk', 'ckk', 'cgg', 'ckg', 'ngg'}.
+    `n0_fn`, `spectra_fn`, `grid_fn` replace the device calls in the CPU (gloo) test of the sharding logic."""
+    Ld = np.asarray(Llls, dtype=np.float64)
+    nm = np.asarray(nmodes, dtype=np.float64)
+    lo, hi = _dist.shard_slice(Ld.size)
+    Lr = Ld[lo:hi]
+    if n0_fn is None:
+        from lbgcmb_b200.Nkk import n0_terms
+
+        def n0_fn(Ls):
+            return n0_terms(lensCl_interps, nolensCl_interps, Ls, terms, noise_config[0], noise_config[1], noise_config[2])[0]
+    if spectra_fn is None:
+        from lbgcmb_b200.lensing import Ckk
+
+        def spectra_fn(Ls, smp):
+            return (Ckk(Pk_interps, Ls),) + limber_grid(Pk_interps, Ls, smp, zmin, zmax)
+    if grid_fn is None:
+        grid_fn = forecast_grid
+    smp = [sample] if xsample is None else [sample, xsample]
+    if hi > lo:
+        nkk = np.asarray(n0_fn(np.asarray(Llls)[lo:hi]), dtype=np.float64)
+        ckk, cgg, ckg, ngg = spectra_fn(Lr, smp)
+        x = {} if xsample is None else {'xcgg': cgg[1:2], 'xckg': ckg[1:2], 'xngg': ngg[1:2]}
+        part = grid_fn(Lr, nm[lo:hi], ckk, cgg[:1], ckg[:1], ngg[:1], nkk[None, :], fsky, fid_sig8, [sample['fid_b1']],
+                       [sample['LllMax']], **x)[0, 0]
+        sums = np.concatenate([[part[0] ** 2.], part[1:7]])           # S/N adds in quadrature over the shards
+    else:                                                             # more ranks than multipoles
+        nkk, ckk, cgg, ckg = np.zeros(0), np.zeros(0), np.zeros((len(smp), 0)), np.zeros((len(smp), 0))
+        ngg = np.zeros(len(smp))
+        sums = np.zeros(7)
+    sums, ngg_sum = _dist.allreduce_sum(sums, np.where(hi > lo, ngg, 0.0))       # THE exchange step of the path
+    n_have = _dist.allreduce_sum(np.array([1.0 if hi > lo else 0.0]))[0][0]
+    F = sums[1:5].reshape(2, 2)
+    interim = sums[5:7]
+    out = {'snr': float(np.sqrt(sums[0])), 'Fisher': F, 'interim': interim,
+           'dtheta': np.linalg.solve(F, interim) if xsample is not None and np.linalg.det(F) != 0 else np.zeros(2),
+           'ngg': ngg_sum / n_have}
+    for name, arr in (('nkk', nkk), ('ckk', ckk), ('cgg', cgg[0] if hi > lo else np.zeros(0)), ('ckg', ckg[0] if hi > lo else np.zeros(0))):
+        out[name] = _dist.allgather_concat(arr)
+    return out

@@ -84,3 +84,31 @@ def test_survey_sweep_end_to_end_vs_oracle(ctx, setup):
             fb = of.fisher_bias(L4, nm4, Cls, Nls, xCls, xNls, bench.FSKY, 0.819, s['fid_b1'], s['LllMax'])
             ref = np.concatenate([[sn], fb['Fisher'].ravel()])
             assert np.max(np.abs(res['out'][n, g, :5] / ref - 1)) < 1e-9, (n, g)
+
+
+def test_sharded_forecast_single_rank_matches_mirrors(ctx):
+    """sweep.sharded_forecast on one rank (the whole L grid is its shard) = snr.snr + interloper.fisher_bias on the same inputs."""
+    import bench
+    from lbgcmb_b200 import Nkk, interloper, pmh, snr as snr_mod, sweep
+    from lbgcmb_b200.prep_camb import cl_interps_from_tables
+    li, ni = cl_interps_from_tables(*bench.make_inputs())
+    kk, pp, bands = bench.forecast_inputs()
+    Pk = pmh.get_PkInterps(pmh.PkTable(kk, pp))
+    Ls = np.arange(50, 2400, 7)
+    Lf = Ls.astype(np.float64)
+    nm = np.full(Lf.size, 7.0)
+    b = bands[1]
+    smp = {'pz': b['pz'], 'bz': b['bz'], 'nbar': b['nbar'], 'fid_b1': b['fid_b1'], 'LllMax': b['LllMax']}
+    xsmp = {'pz': b['pzz'], 'bz': b['bz'], 'nbar': b['nbar_wint']}
+    got = sweep.sharded_forecast(li, ni, Pk, Ls, nm, (1.4, 7.0, False), smp, bench.FSKY, xsample=xsmp)
+    nkk = Nkk.Nkk(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 7.0, iterative=False, pickleit=False)
+    Cls, Nls = interloper.get_allCls(Pk, Lf, b['nbar'], bench.FSKY, 0.01, 10.0, b['pz'], b['bz'], zeff=False, nkk=nkk)
+    xCls, xNls = interloper.get_allCls(Pk, Lf, b['nbar_wint'], bench.FSKY, 0.01, 10.0, b['pzz'], b['bz'], zeff=False, nkk=nkk)
+    vkg = ((Cls['kk'] + nkk) * (Cls['gg'] + Nls['gg']) + Cls['kg'] ** 2.) / ((2. * Lf + 1.) * bench.FSKY)
+    sn = snr_mod.snr(Lf, Cls['kg'], vkg, nm, lmax=b['LllMax'])
+    fb = interloper.fisher_bias(Lf, nm, Cls, Nls, xCls, xNls, bench.FSKY, 0.819, b['fid_b1'], b['LllMax'], fused=False)
+    assert np.array_equal(got['nkk'], nkk)
+    assert np.max(np.abs(got['cgg'] / Cls['gg'] - 1)) < 1e-13 and np.max(np.abs(got['ckg'] / Cls['kg'] - 1)) < 1e-13
+    assert abs(got['snr'] / sn - 1) < 1e-12
+    assert np.max(np.abs(got['Fisher'] / fb['Fisher'] - 1)) < 1e-11
+    assert np.max(np.abs(got['dtheta'] / fb['dtheta'] - 1)) < 1e-9
