@@ -26,6 +26,38 @@ def shard_slice(n, rank=None, world=None):
     return lo, lo + base + (1 if rank < extra else 0)
 
 
+def shard_indices(n, rank=None, world=None):
+    """Cyclic shard: units rank, rank + world, ... of n.  For N0 the cost per L falls with L (more of the (l1, phi) grid is masked
+    by the lmax cuts and skipped), so contiguous blocks would leave the low-L rank with the longest job."""
+    if rank is None or world is None:
+        rank, world = rank_world()
+    return np.arange(rank, n, world)
+
+
+def allgather_cyclic(local, n):
+    """Inverse of shard_indices for any number of equally sharded float64 curves: `local` is [n_curves, n_mine] on this rank;
+    returns [n_curves, n] on every rank, one collective (NCCL all_gather of a padded block; gloo on CPU)."""
+    d = _dist()
+    local = np.atleast_2d(np.ascontiguousarray(local, dtype=np.float64))
+    if d is None or d.get_world_size() == 1:
+        return local.copy()
+    import torch
+    world = d.get_world_size()
+    width = (n + world - 1) // world
+    pad = np.zeros((local.shape[0], width))
+    pad[:, :local.shape[1]] = local
+    dev = torch.device('cuda', torch.cuda.current_device()) if d.get_backend() == 'nccl' else torch.device('cpu')
+    mine = torch.from_numpy(pad).to(dev)
+    parts = torch.empty((world * pad.shape[0], width), dtype=torch.float64, device=dev)      # ranks concatenated along dim 0
+    d.all_gather_into_tensor(parts, mine)
+    parts = parts.cpu().numpy().reshape(world, pad.shape[0], width)
+    out = np.empty((local.shape[0], n))
+    for r in range(world):
+        m = len(range(r, n, world))
+        out[:, r::world] = parts[r, :, :m]
+    return out
+
+
 def allreduce_sum(*arrays):
     """Sum float64 numpy arrays over all ranks in one collective (packed); identity without a process group."""
     d = _dist()

@@ -104,25 +104,27 @@ def survey_sweep(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noi
 
 
 def sharded_forecast(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noise_config, sample, fsky, fid_sig8=0.819,
-                     xsample=None, zmin=0.01, zmax=10.0, terms=('TT', 'TE', 'EE', 'EB'), n0_fn=None, spectra_fn=None, grid_fn=None):
+                     xsample=None, zmin=0.01, zmax=10.0, terms=('TT', 'TE', 'EE', 'EB'), n0_fn=None, spectra_fn=None, grid_fn=None,
+                     timing=None):
     """ONE forecast (one experiment, one galaxy sample) with the multipole grid sharded over the ranks -- the layout north_star
-    names: every rank evaluates N0, C_kk, C_gg, C_kg and the per-multipole covariance / Fisher terms on its own contiguous block
-    of L (dist.shard_slice; N0 per L and Limber per l are independent), and the only exchange inside the path is ONE all-reduce
-    of the partial sums (S/N^2, the 2 x 2 Fisher matrix of (sigma8, b1), the bias vector): 7 doubles over NCCL.  The curves are
-    then gathered so that every rank returns the full arrays, as snr.py / interloper.py produce them.
+    names: every rank evaluates N0, C_kk, C_gg, C_kg and the per-multipole covariance / Fisher terms on its own multipoles
+    (dist.shard_indices: L[rank::world], because the N0 cost per L falls with L; N0 per L and Limber per l are independent), and
+    the only exchange inside the path is ONE all-reduce of the partial sums (S/N^2, the 2 x 2 Fisher matrix of (sigma8, b1), the
+    bias vector, N_gg): 10 doubles over NCCL.  The curves are then gathered (one all_gather) so that every rank returns the full
+    arrays, as snr.py / interloper.py produce them.  On a GPU the N0 curve runs on the library's second context
+    (Nkk.n0_terms_async) while the spectra are built.
 
     noise_config = (thetab, DeltaT, iterative); sample = {'pz', 'bz', 'nbar', 'fid_b1', 'LllMax'}; xsample: the interloper-
     contaminated twin (bias vector).  Returns {'snr', 'Fisher', 'interim', 'dtheta', 'nkk', 'ckk', 'cgg', 'ckg', 'ngg'}.
-    `n0_fn`, `spectra_fn`, `grid_fn` replace the device calls in the CPU (gloo) test of the sharding logic."""
+    `n0_fn`, `spectra_fn`, `grid_fn` replace the device calls in the CPU (gloo) test of the sharding logic; `timing`, a dict,
+    receives this rank's wall seconds per phase."""
+    import time
+    t0 = time.perf_counter()
     Ld = np.asarray(Llls, dtype=np.float64)
     nm = np.asarray(nmodes, dtype=np.float64)
-    lo, hi = _dist.shard_slice(Ld.size)
-    Lr = Ld[lo:hi]
-    if n0_fn is None:
-        from lbgcmb_b200.Nkk import n0_terms
-
-        def n0_fn(Ls):
-            return n0_terms(lensCl_interps, nolensCl_interps, Ls, terms, noise_config[0], noise_config[1], noise_config[2])[0]
+    mine = _dist.shard_indices(Ld.size)
+    Lr = Ld[mine]
+    have = mine.size > 0
     if spectra_fn is None:
         from lbgcmb_b200.lensing import Ckk
 
@@ -131,24 +133,36 @@ def sharded_forecast(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes,
     if grid_fn is None:
         grid_fn = forecast_grid
     smp = [sample] if xsample is None else [sample, xsample]
-    if hi > lo:
-        nkk = np.asarray(n0_fn(np.asarray(Llls)[lo:hi]), dtype=np.float64)
-        ckk, cgg, ckg, ngg = spectra_fn(Lr, smp)
+    if have:
+        if n0_fn is None:
+            from lbgcmb_b200.Nkk import n0_terms_async
+            fut = n0_terms_async(lensCl_interps, nolensCl_interps, np.asarray(Llls)[mine], terms, noise_config[0], noise_config[1],
+                                 noise_config[2])
+            ckk, cgg, ckg, ngg = spectra_fn(Lr, smp)
+            t1 = time.perf_counter()
+            nkk = fut.result()[0]
+        else:
+            nkk = np.asarray(n0_fn(np.asarray(Llls)[mine]), dtype=np.float64)
+            ckk, cgg, ckg, ngg = spectra_fn(Lr, smp)
+            t1 = time.perf_counter()
+        t2 = time.perf_counter()
         x = {} if xsample is None else {'xcgg': cgg[1:2], 'xckg': ckg[1:2], 'xngg': ngg[1:2]}
-        part = grid_fn(Lr, nm[lo:hi], ckk, cgg[:1], ckg[:1], ngg[:1], nkk[None, :], fsky, fid_sig8, [sample['fid_b1']],
+        part = grid_fn(Lr, nm[mine], ckk, cgg[:1], ckg[:1], ngg[:1], nkk[None, :], fsky, fid_sig8, [sample['fid_b1']],
                        [sample['LllMax']], **x)[0, 0]
-        sums = np.concatenate([[part[0] ** 2.], part[1:7]])           # S/N adds in quadrature over the shards
+        sums = np.concatenate([[part[0] ** 2.], part[1:7], ngg[:1], [1.0]])     # S/N adds in quadrature over the shards
+        curves = np.stack([nkk, ckk, cgg[0], ckg[0]])
     else:                                                             # more ranks than multipoles
-        nkk, ckk, cgg, ckg = np.zeros(0), np.zeros(0), np.zeros((len(smp), 0)), np.zeros((len(smp), 0))
-        ngg = np.zeros(len(smp))
-        sums = np.zeros(7)
-    sums, ngg_sum = _dist.allreduce_sum(sums, np.where(hi > lo, ngg, 0.0))       # THE exchange step of the path
-    n_have = _dist.allreduce_sum(np.array([1.0 if hi > lo else 0.0]))[0][0]
+        t1 = t2 = time.perf_counter()
+        sums = np.zeros(9)
+        curves = np.zeros((4, 0))
+    t3 = time.perf_counter()
+    sums = _dist.allreduce_sum(sums)[0]                               # THE exchange step of the path
+    curves = _dist.allgather_cyclic(curves, Ld.size)
+    t4 = time.perf_counter()
     F = sums[1:5].reshape(2, 2)
     interim = sums[5:7]
-    out = {'snr': float(np.sqrt(sums[0])), 'Fisher': F, 'interim': interim,
-           'dtheta': np.linalg.solve(F, interim) if xsample is not None and np.linalg.det(F) != 0 else np.zeros(2),
-           'ngg': ngg_sum / n_have}
-    for name, arr in (('nkk', nkk), ('ckk', ckk), ('cgg', cgg[0] if hi > lo else np.zeros(0)), ('ckg', ckg[0] if hi > lo else np.zeros(0))):
-        out[name] = _dist.allgather_concat(arr)
-    return out
+    if timing is not None:
+        timing.update(spectra_s=t1 - t0, n0_wait_s=t2 - t1, grid_s=t3 - t2, collectives_s=t4 - t3, n_L_mine=int(mine.size))
+    return {'snr': float(np.sqrt(sums[0])), 'Fisher': F, 'interim': interim,
+            'dtheta': np.linalg.solve(F, interim) if xsample is not None and np.linalg.det(F) != 0 else np.zeros(2),
+            'ngg': sums[7] / sums[8], 'nkk': curves[0], 'ckk': curves[1], 'cgg': curves[2], 'ckg': curves[3]}

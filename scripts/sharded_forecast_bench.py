@@ -17,13 +17,13 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 def main():
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (('RANK', '0'), ('WORLD_SIZE', '1'), ('LOCAL_RANK', '0')))
+    import bench
+    bench._stdout_for_json_only()                       # before NCCL initialises: its version banner goes to fd 1
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
-    import bench
-    bench._stdout_for_json_only()
     from lbgcmb_b200 import pmh, sweep
     from lbgcmb_b200.prep_camb import cl_interps_from_tables
     li, ni = cl_interps_from_tables(*bench.make_inputs())
@@ -35,8 +35,10 @@ def main():
     smp = {'pz': b['pz'], 'bz': b['bz'], 'nbar': b['nbar'], 'fid_b1': b['fid_b1'], 'LllMax': b['LllMax']}
     xsmp = {'pz': b['pzz'], 'bz': b['bz'], 'nbar': b['nbar_wint']}
 
+    timing = {}
+
     def run():
-        return sweep.sharded_forecast(li, ni, Pk, Ls, nm, (1.4, 1.0, True), smp, bench.FSKY, xsample=xsmp)
+        return sweep.sharded_forecast(li, ni, Pk, Ls, nm, (1.4, 1.0, True), smp, bench.FSKY, xsample=xsmp, timing=timing)
 
     def barrier():
         torch.cuda.synchronize()
@@ -54,6 +56,7 @@ def main():
     dt = torch.tensor([(time.perf_counter() - t0) / reps], dtype=torch.float64, device='cuda')
     if world > 1:
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    phases = dict(timing)
     if rank == 0:
         dev = None
         if world > 1:                                    # the whole grid on this rank alone, outside any process group
@@ -69,7 +72,7 @@ def main():
                                 '+ S/N + (sigma8,b1) Fisher / bias; one NCCL all-reduce of 7 partial sums + curve gathers',
                     'n_gpus': world, 'ms_per_forecast': float(dt[0]) * 1e3, 'L_modes_per_s': Ls.size / float(dt[0]), 'scaling': 'strong',
                     'snr': res['snr'], 'Fisher': res['Fisher'].tolist(), 'dtheta': res['dtheta'].tolist(),
-                    'max_rel_dev_vs_one_rank': dev})
+                    'max_rel_dev_vs_one_rank': dev, 'rank0_phase_ms': {k: (v * 1e3 if k.endswith('_s') else v) for k, v in phases.items()}})
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
