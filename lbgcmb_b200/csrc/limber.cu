@@ -210,7 +210,7 @@ limber_kernel(int n_batch, int n_ell, int n_z, int n_k, int z_per_split, const d
                 pv = __dadd_rn(__dmul_rn(slope, __dsub_rn(x[u], k0)), p0[u]);
             } else if (x[u] < k_first) pv = oob ? p0[u] : 0.0;
             else if (x[u] > k_last) pv = oob ? p1[u] : 0.0;
-            else pv = p1[u];                         // x == k_last (NaN ends here too and stays NaN through p1 only if the table has one)
+            else pv = x[u] == k_last ? p1[u] : x[u] + p1[u];   // exactly the last knot; a NaN node (chi = NaN) stays NaN as in np.interp
             const int z = iz + u;
 #pragma unroll
             for (int q = 0; q < NB; ++q) acc[q] += __ldg(wq[q] + z) * pv;
