@@ -77,11 +77,7 @@ def survey_sweep(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noi
     Under torch.distributed each rank evaluates its own block of noise levels.  `n0_fn`, `spectra_fn`, `grid_fn` replace the
     device calls in the CPU (gloo) tests of the sharding logic."""
     Ld = np.asarray(Llls, dtype=np.float64)
-    if n0_fn is None:
-        from lbgcmb_b200.Nkk import n0_terms
-
-        def n0_fn(cfg):
-            return n0_terms(lensCl_interps, nolensCl_interps, Llls, terms, cfg[0], cfg[1], cfg[2])[0]
+    n0_async = n0_fn is None
     if spectra_fn is None:
         from lbgcmb_b200.lensing import Ckk
 
@@ -89,10 +85,17 @@ def survey_sweep(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noi
             return (Ckk(Pk_interps, Ld),) + limber_grid(Pk_interps, Ld, smp, zmin, zmax)
     if grid_fn is None:
         grid_fn = forecast_grid
+    lo, hi = _dist.shard_slice(len(noise_configs))
+    futs = None
+    if n0_async:                                 # this rank's N0 curves run on the second context while the spectra are built
+        from lbgcmb_b200.Nkk import n0_terms_async
+        futs = [n0_terms_async(lensCl_interps, nolensCl_interps, Llls, terms, cfg[0], cfg[1], cfg[2]) for cfg in noise_configs[lo:hi]]
     ckk, cgg, ckg, ngg = spectra_fn(samples)
     xc = spectra_fn(xsamples)[1:] if xsamples is not None else (None, None, None)
-    lo, hi = _dist.shard_slice(len(noise_configs))
-    nkk = np.array([n0_fn(cfg) for cfg in noise_configs[lo:hi]]).reshape(hi - lo, Ld.size)
+    if futs is not None:
+        nkk = np.array([f.result()[0] for f in futs]).reshape(hi - lo, Ld.size)
+    else:
+        nkk = np.array([n0_fn(cfg) for cfg in noise_configs[lo:hi]]).reshape(hi - lo, Ld.size)
     if hi > lo:
         out = grid_fn(Ld, nmodes, ckk, cgg, ckg, ngg, nkk, fsky, fid_sig8, [s['fid_b1'] for s in samples],
                       [s['LllMax'] for s in samples], xcgg=xc[0], xckg=xc[1], xngg=xc[2])
