@@ -89,7 +89,8 @@ def survey_sweep(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noi
     futs = None
     if n0_async:                                 # this rank's N0 curves run on the second context while the spectra are built
         from lbgcmb_b200.Nkk import n0_terms_async
-        futs = [n0_terms_async(lensCl_interps, nolensCl_interps, Llls, terms, cfg[0], cfg[1], cfg[2]) for cfg in noise_configs[lo:hi]]
+        futs = [n0_terms_async(lensCl_interps, nolensCl_interps, Llls, terms, cfg[0], cfg[1], cfg[2], reuse_tables=True)
+                for cfg in noise_configs[lo:hi]]
     ckk, cgg, ckg, ngg = spectra_fn(samples)
     xc = spectra_fn(xsamples)[1:] if xsamples is not None else (None, None, None)
     if futs is not None:
