@@ -55,7 +55,10 @@ def upload_cls(ctx, lensCl_interps, nolensCl_interps, reuse=False):
     lt = _ffi.f64(np.stack([t[:n] for t in lens]))
     ut = _ffi.f64(np.stack([t[:n] for t in nolens]))
     last = getattr(ctx, '_cl_last', None)
-    if reuse and last is not None and last[0].shape == lt.shape and np.array_equal(last[0], lt) and np.array_equal(last[1], ut):
+    same = last is not None and last[0].shape == lt.shape and np.array_equal(last[0], lt) and np.array_equal(last[1], ut)
+    if not same:
+        ctx._exact_cache = None              # host-side values derived from the tables (_exact_u_rows)
+    if same and reuse:
         return n
     _ffi.check(_ffi.lib().lbg_upload_cl_tables(ctx.handle, n, _ffi._dp(lt), _ffi._dp(ut)))
     ctx._cl_last = (lt, ut)
@@ -120,7 +123,14 @@ def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'
     out = np.empty(Ld.size)
     out_terms = np.empty((5, Ld.size))
     import ctypes as C
-    exact_rows, exact_u = _exact_u_rows(lensCl_interps, nolensCl_interps, ell, cphi, sphi, exact_u_below)
+    # the scipy-evaluated u-side rows depend on the tables and the grids only: kept while the context's tables are value-equal
+    ekey = (ell.size, float(exact_u_below), cphi.tobytes(), sphi.tobytes(), ell.tobytes())
+    cached = getattr(ctx, '_exact_cache', None)
+    if cached is not None and cached[0] == ekey:
+        exact_rows, exact_u = cached[1], cached[2]
+    else:
+        exact_rows, exact_u = _exact_u_rows(lensCl_interps, nolensCl_interps, ell, cphi, sphi, exact_u_below)
+        ctx._exact_cache = (ekey, exact_rows, exact_u)
     nodes = C.c_longlong(0)
     if Tcmb is None:
         Tcmb = get_params()['Tcmb']
