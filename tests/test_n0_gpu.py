@@ -181,3 +181,29 @@ def test_kernel_variants_agree(ctx, cl_tables, monkeypatch):
         got = Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False)[0]
         assert np.max(np.abs(got / want - 1)) < 1e-12, v
     monkeypatch.delenv('LBG_N0_VARIANT')
+
+
+def test_flat_spectrum_tt_closed_form(ctx):
+    """SURVEY.md 8(c) closed form: constant C_l (lensed = unlensed = c0), white noise without a beam and no |v| cuts.  Then
+    f_TT = c0 (L.u + L.v) = c0 L^2 for every node, F = f / (2 T^2) with T = c0 + N, the integrand is constant and the reference's
+    Simpson rule over l1 in [1, 5000] x phi in [0, 2 pi] is exact for it:
+        integral = c0^2 L^4 / (2 T^2) * pi (5000^2 - 1),   N0 = (L (L + 1) / 2)^2 (2 pi)^2 / integral.
+    Non-grid L so that v = L - u never vanishes.  Independent of the oracle."""
+    from lbgcmb_b200 import Nkk
+    from lbgcmb_b200.DetectorNoise import DetectorNoise
+    c0 = 3.0e-10
+    n = 10151
+    ell = np.arange(n, dtype=np.float64)
+    tab = np.zeros((4, n))
+    tab[0] = c0                                   # TT flat; EE, BB, TE zero
+    li, ni = _interps(ell, tab, tab.copy())
+    Ls = np.array([50.25, 777.3, 2999.9, 4999.7])
+    DeltaT = 5.0
+    noise = float(DetectorNoise(np.array([100.]), 0.0, DeltaT, 'TT')[0])       # thetab = 0: white
+    T = c0 + noise
+    want = (Ls * (Ls + 1.) / 2.) ** 2. * (2. * np.pi) ** 2. / (c0 ** 2. * Ls ** 4. / (2. * T ** 2.) * np.pi * (5000. ** 2. - 1.))
+    got = Nkk.n0_terms(li, ni, Ls, ['TT'], 0.0, DeltaT, False, lmax_T=1e9, lmax_P=1e9, lmin_v=1e-9, exact_u_below=0.0)[0]
+    assert np.max(np.abs(got / want - 1)) < 1e-12
+    nofold = Nkk.n0_terms(li, ni, Ls, ['TT'], 0.0, DeltaT, False, lmax_T=1e9, lmax_P=1e9, lmin_v=1e-9, exact_u_below=0.0,
+                          fold_phi=False)[0]
+    assert np.max(np.abs(nofold / want - 1)) < 1e-12
