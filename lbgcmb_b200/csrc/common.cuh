@@ -49,6 +49,24 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+// Grow-only pinned host staging buffer (true asynchronous DMA; pageable copies are staged by the driver piece by piece).
+struct PinBuf {
+    void*  p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes) {
+        if (bytes <= cap) return LBG_OK;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        bytes = (bytes + (1u << 16)) & ~(size_t)((1u << 16) - 1);
+        cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+        if (e != cudaSuccess) { set_error("cudaHostAlloc(%zu) -> %s", bytes, cudaGetErrorString(e)); return LBG_ENOMEM; }
+        cap = bytes;
+        return LBG_OK;
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
 // One row of the CMB spline table per integer knot: uniform cubic B-spline coefficients of the eight
 // spectra, 64 bytes, so that one knot = two 32-byte sectors.
 struct __align__(64) ClRow {
@@ -82,6 +100,7 @@ struct lbg_ctx {
     lbg::DevBuf  n0_L, n0_utab, n0_phi, n0_partial, n0_out, n0_rowflag, n0_G;
     // generic scratch
     lbg::DevBuf  s0, s1, s2, s3, s4, s5;
+    lbg::PinBuf  pin_in, pin_out;    // pinned staging for the short, copy-dominated calls (lbg_limber)
     // P(k) / Limber state (see limber.cu)
     int          n_k = 0;
     lbg::DevBuf  pk_lnk, pk_plin, pk_rdk;

@@ -331,33 +331,41 @@ extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell,
     std::lock_guard<std::mutex> g(c->mu);
     LBG_CUDA(cudaSetDevice(c->device));
     const size_t bw = (size_t)n_batch * n_z * 8, bo = (size_t)n_batch * n_ell * 8;
-    if (c->s0.reserve((size_t)n_ell * 8) || c->s1.reserve((size_t)n_z * 16) || c->s2.reserve(bw) ||
-        c->s3.reserve((size_t)n_z * 4 + (size_t)((n_batch + LIMBER_BT - 1) / LIMBER_BT + 1) * n_z) || c->s4.reserve(bo)) return LBG_ENOMEM;
+    const int nbk = n_batch == 1 ? 1 : LIMBER_BT, n_bb = (n_batch + nbk - 1) / nbk;
+    // every input of the call is packed into ONE pinned staging block and crosses PCIe in one copy (five pageable copies cost more
+    // than the kernel): [ell | chi | RN(1/chi) | weight | prow (int) | live (bytes)], each piece 256-byte aligned
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t o_ell = 0, o_zc = up((size_t)n_ell * 8), o_w = o_zc + up((size_t)n_z * 16), o_prow = o_w + up(bw),
+                 o_live = o_prow + up((size_t)n_z * 4), total = o_live + up((size_t)n_bb * n_z);
+    if (c->s0.reserve(total) || c->s4.reserve(bo) || c->pin_in.reserve(total) || c->pin_out.reserve(bo)) return LBG_ENOMEM;
     const int n_split = limber_splits(n_z), z_per_split = (n_z + n_split - 1) / n_split;
     if (n_split > 1 && c->s5.reserve(bo * n_split)) return LBG_ENOMEM;
     cudaStream_t st = c->stream;
-    LBG_CUDA(cudaMemcpyAsync(c->s0.p, ell, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
-    std::vector<double> zc(2 * (size_t)n_z);                  // chi | RN(1 / chi) for div_rn
+    unsigned char* hin = c->pin_in.as<unsigned char>();
+    memcpy(hin + o_ell, ell, (size_t)n_ell * 8);
+    double* zc = reinterpret_cast<double*>(hin + o_zc);       // chi | RN(1 / chi) for div_rn
     for (int i = 0; i < n_z; ++i) { zc[i] = chi[i]; zc[(size_t)n_z + i] = 1.0 / chi[i]; }
-    LBG_CUDA(cudaMemcpyAsync(c->s1.p, zc.data(), zc.size() * 8, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(c->s2.p, weight, bw, cudaMemcpyHostToDevice, st));
-    const int nbk = n_batch == 1 ? 1 : LIMBER_BT, n_bb = (n_batch + nbk - 1) / nbk;
-    // s3: prow[n_z] (int) then live[n_bb][n_z] (bytes): a z node none of a block's batch entries weights is skipped by that block
-    std::vector<unsigned char> meta((size_t)n_z * 4 + (size_t)n_bb * n_z);
-    memcpy(meta.data(), prow, (size_t)n_z * 4);
+    memcpy(hin + o_w, weight, bw);
+    memcpy(hin + o_prow, prow, (size_t)n_z * 4);
+    unsigned char* lv = hin + o_live;                         // a z node none of a block's batch entries weights is skipped by that block
     for (int bb = 0; bb < n_bb; ++bb)
         for (int i = 0; i < n_z; ++i) {
             bool any = false;
             for (int q = bb * nbk; q < std::min(n_batch, (bb + 1) * nbk); ++q) any = any || (weight[(size_t)q * n_z + i] != 0.0);
-            meta[(size_t)n_z * 4 + (size_t)bb * n_z + i] = any;
+            lv[(size_t)bb * n_z + i] = any;
         }
-    LBG_CUDA(cudaMemcpyAsync(c->s3.p, meta.data(), meta.size(), cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, hin, total, cudaMemcpyHostToDevice, st));
+    const unsigned char* din = c->s0.as<unsigned char>();
+    const double* d_ell = reinterpret_cast<const double*>(din + o_ell);
+    const double* d_zc = reinterpret_cast<const double*>(din + o_zc);
+    const double* d_w = reinterpret_cast<const double*>(din + o_w);
+    const int* d_prow = reinterpret_cast<const int*>(din + o_prow);
+    const unsigned char* live = din + o_live;
     KernelTimer t(c);
     double* part = n_split > 1 ? c->s5.as<double>() : c->s4.as<double>();
     const dim3 grid((n_ell + 127) / 128, n_bb, n_split);
-    const unsigned char* live = (const unsigned char*)c->s3.p + (size_t)n_z * 4;
-#define LBG_LIMBER(NB) limber_kernel<NB><<<grid, 128, 0, st>>>(n_batch, n_ell, n_z, c->n_k, z_per_split, c->s0.as<double>(), c->s1.as<double>(), \
-        c->s2.as<double>(), live, c->s3.as<int>(), c->pk_lnk.as<double>(), c->pk_rdk.as<double>(), c->pk_pnl.as<double>(), oob, part)
+#define LBG_LIMBER(NB) limber_kernel<NB><<<grid, 128, 0, st>>>(n_batch, n_ell, n_z, c->n_k, z_per_split, d_ell, d_zc, d_w, live, d_prow, \
+        c->pk_lnk.as<double>(), c->pk_rdk.as<double>(), c->pk_pnl.as<double>(), oob, part)
     if (nbk == 1) LBG_LIMBER(1); else LBG_LIMBER(LIMBER_BT);
 #undef LBG_LIMBER
     t.launched();
@@ -366,8 +374,10 @@ extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell,
         limber_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, n_split, part, c->s4.as<double>());
         t.launched();
     }
-    LBG_CUDA(cudaMemcpyAsync(out_cl, c->s4.p, bo, cudaMemcpyDeviceToHost, st));
-    return t.finish();
+    LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, c->s4.p, bo, cudaMemcpyDeviceToHost, st));
+    const int rc = t.finish();
+    if (rc == LBG_OK) memcpy(out_cl, c->pin_out.p, bo);
+    return rc;
 }
 
 extern "C" int lbg_pk_eval(lbg_ctx* c, int row, int n, const double* x, int oob, double* out) {
