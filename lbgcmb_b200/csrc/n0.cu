@@ -1105,7 +1105,12 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
         bool onT = fabs(l - lmax_T) <= 1e-12 * lmax_T, onP = fabs(l - lmax_P) <= 1e-12 * lmax_P;
         if (l < lmax_T || onT) f |= 1;
         if (l < lmax_P || onP) f |= 4;
-        if (onT || onP) {
+        // a row sitting on the LAST KNOT of a table that ends inside the integration range: the reference's interp1d returns the
+        // knot value or its fill value 0 per phi node, depending on whether |u|_j = sqrt((l cos)^2 + (l sin)^2) rounds to the knot
+        // or one ulp above it (prep_camb.py:88-89) -- the same per-node rounding as the lmax cuts, so the same treatment
+        const double l_end = (double)(c->n_ell - 1);
+        const bool onEnd = f != 0 && fabs(l - l_end) <= 1e-12 * l_end;
+        if (onT || onP || onEnd) {
             bool have = false;
             for (int q : srow) have = have || q == r;
             if (!have) srow.push_back(r);

@@ -207,3 +207,27 @@ def test_flat_spectrum_tt_closed_form(ctx):
     nofold = Nkk.n0_terms(li, ni, Ls, ['TT'], 0.0, DeltaT, False, lmax_T=1e9, lmax_P=1e9, lmin_v=1e-9, exact_u_below=0.0,
                           fold_phi=False)[0]
     assert np.max(np.abs(nofold / want - 1)) < 1e-12
+
+
+def test_short_and_long_tables(ctx, cl_tables):
+    """Tables that end inside the integration range (the reference's interp1d returns 0 beyond its last knot, so C^tot is pure
+    noise there: prep_camb.py:88-89) and tables longer than the fast kernels' compile-time stride (fall-back kernel)."""
+    from oracle import n0 as on0
+    from lbgcmb_b200 import Nkk
+    from lbgcmb_b200.synthetic import cmb_cl_tables
+    ell, lens, nolens = cl_tables
+    n = 4001                                                   # knots 0..4000 < lmax_P = 5000
+    Ls = np.array([60, 3500])
+    ref = on0.nkk_root(on0.cl_interps(ell[:n], lens[:, :n]), on0.cl_interps(ell[:n], nolens[:, :n]), Ls, ('TT', 'TE', 'EE', 'EB'),
+                       1.4, 7.0, False)
+    li, ni = _interps(ell[:n], lens[:, :n], nolens[:, :n])
+    got = Nkk.Nkk(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 7.0, iterative=False, pickleit=False)
+    assert np.max(np.abs(got / ref - 1)) < RTOL
+    ell2, lens2, nolens2 = cmb_cl_tables(n_ell=17001)          # > 16382 knots
+    assert np.array_equal(lens2[:, :ell.size], lens)           # same spectra, longer tables
+    li2, ni2 = _interps(ell2, lens2, nolens2)
+    li0, ni0 = _interps(ell, lens, nolens)
+    Ls = np.array([50, 2000, 5000])
+    a = Nkk.Nkk(li2, ni2, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, iterative=True, pickleit=False)
+    b = Nkk.Nkk(li0, ni0, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, iterative=True, pickleit=False)
+    assert np.max(np.abs(a / b - 1)) < RTOL                    # the far end of a not-a-knot spline does not reach l <= 10000
