@@ -231,3 +231,20 @@ def test_short_and_long_tables(ctx, cl_tables):
     a = Nkk.Nkk(li2, ni2, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, iterative=True, pickleit=False)
     b = Nkk.Nkk(li0, ni0, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, iterative=True, pickleit=False)
     assert np.max(np.abs(a / b - 1)) < RTOL                    # the far end of a not-a-knot spline does not reach l <= 10000
+
+
+def test_unusual_L_and_wide_beam_against_oracle(ctx, cl_tables):
+    """L outside the usual grid (below the first l1 node, non-integer, beyond lmax_P where only part of the |v| annulus survives)
+    and the widest beam / highest noise of the BASELINE sweep (the noise factor reaches e^19 at l = 5000)."""
+    from oracle import n0 as on0
+    from lbgcmb_b200 import Nkk
+    ell, lens, nolens = cl_tables
+    li, ni = _interps(ell, lens, nolens)
+    ol, on = on0.cl_interps(ell, lens), on0.cl_interps(ell, nolens)
+    terms = ('TT', 'TE', 'EE', 'EB')
+    for Ls, thetab, DeltaT, it in ((np.array([2, 7.5, 6000, 9990]), 1.4, 7.0, False), (np.array([50, 1234, 5000]), 7.0, 30.0, False),
+                                   (np.array([3000, 3001]), 1.0, 1.0, True)):
+        ref = on0.nkk_root(ol, on, Ls, terms, thetab, DeltaT, it)
+        got = Nkk.n0_terms(li, ni, Ls, terms, thetab, DeltaT, it)[0]
+        assert np.all(np.isfinite(got)) and np.all(got > 0)
+        assert np.max(np.abs(got / ref - 1)) < RTOL, (Ls, thetab, np.abs(got / ref - 1))
