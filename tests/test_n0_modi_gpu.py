@@ -90,3 +90,30 @@ def test_cmb_class_on_class_files(ctx, g, tmp_path):
     assert np.max(np.abs(cmb.do_noiseTE(thetab, delT)[2] / g['cmb_TE'] - 1)) < RTOL
     assert cmb.do_noise('T', 'E', thetab, delT) is None                 # "Wrong function", modi/nkk.py:200-203
     assert np.allclose(Nl2, nkk.N_inst(thetab, delT, cmb.ells, 'T'), rtol=1e-12)
+
+
+def test_n_fisher_extreme_L_against_oracle(ctx):
+    """modi flavour at the ends: L below the first l node, L next to / beyond the last one (part or all of the l2 = |L - l| range
+    falls outside [min l, max l] and `frac` is zeroed there, modi/nkk.py:84-85; beyond 2 max l the integral is exactly 0)."""
+    from scipy.interpolate import InterpolatedUnivariateSpline as IUS
+    from lbgcmb_b200.modi import nkk
+    from oracle import n0 as on0
+    eu, el, u, le = _tables()
+    lint = np.linspace(1., 3000., 1500)
+    nT = on0.detector_noise(el, 1.4, 7.0, 'TT', 2.786)
+    nE = on0.detector_noise(el, 1.4, 7.0, 'EE', 2.786)
+    Ls = np.array([1.5, 2.0, 2999.5, 3000.0, 3500.0, 5999.0, 7000.0])
+    cases = {'TT': (IUS(eu, u['TT']), IUS(eu, u['TT']), IUS(el, le['TT'] + nT), IUS(el, le['TT'] + nT)),
+             'EE': (IUS(eu, u['EE']), IUS(eu, u['EE']), IUS(el, le['EE'] + nE), IUS(el, le['EE'] + nE)),
+             'EB': (IUS(eu, u['EE']), IUS(eu, u['BB']), IUS(el, le['EE'] + nE), IUS(el, le['BB'] + nE))}
+    for mode, args in cases.items():
+        got = nkk.N_fisher(Ls, lint, *args, mode)
+        ref = np.array([on0.modi_N_fisher(float(L), lint, *args, mode) for L in Ls])
+        assert got[-1] == 0.0 and ref[-1] == 0.0
+        ok = ref != 0
+        assert np.max(np.abs(got[ok] / ref[ok] - 1)) < RTOL, (mode, got / ref - 1)
+    args = (IUS(eu, u['TE']), IUS(el, le['TT'] + nT), IUS(el, le['EE'] + nE), IUS(el, le['TE']))
+    got = nkk.N_fisherTE(Ls, lint, *args)
+    ref = np.array([on0.modi_N_fisherTE(float(L), lint, *args) for L in Ls])
+    ok = ref != 0
+    assert np.array_equal(got == 0, ref == 0) and np.max(np.abs(got[ok] / ref[ok] - 1)) < RTOL, got / ref - 1
