@@ -172,6 +172,15 @@ int lbg_fisher_accum(lbg_ctx* ctx, int n_ell, int n_spec, int n_par, const doubl
                      const double* dD /*[n_ell][n_par][n_spec]*/, const double* dDelta /*[n_ell][n_spec] or NULL*/,
                      const double* mode_weight /*[n_ell]*/, double* out_F /*[n_par][n_par]*/, double* out_b /*[n_par] or NULL*/,
                      double* out_per_ell /*or NULL*/);
+/* The same Fisher sum for n_f correlated fields at once, in field form (no n_spec x n_spec covariance is formed):
+ *   out_F[p][q] = sum_l mode_weight[l] * 1/2 Tr[ C_l^-1 d_pC_l  C_l^-1 d_qC_l ],  C_l[a][b] = (C + N)^{ab}(l) symmetric, n_f x n_f,
+ * which equals interloper.py:223-253 (`dD^T Cov^-1 dD` with the interloper.py:42-63 covariance) when the data vector holds every auto
+ * and cross spectrum of the fields and mode_weight[l] = nmodes[l] (2 l + 1) fsky.  Spectrum s is the field pair (spec_a[s], spec_b[s]);
+ * pairs that are not listed are zero in C_l and in its derivatives (disjoint redshift bins); every field needs its auto spectrum.
+ * tot[n_spec][n_ell] = C + N, dC[n_par][n_spec][n_ell] = parameter derivatives.  n_f <= 160, n_par <= 8 (BASELINE configs[3]:
+ * kappa + 6 tracers x 20 bins = 121 fields, 241 spectra).  out_per_ell ([n_ell][n_par][n_par], unweighted) may be NULL. */
+int lbg_field_fisher(lbg_ctx* ctx, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
+                     int n_par, const double* dC, const double* mode_weight, double* out_F, double* out_per_ell /*or NULL*/);
 /* mqw/py/mqw.py:63-104 `Fisher` (clustering-redshift N_p(z_i) Fisher): bins[n_bin][8] = {bp, bs, Np, Ns, wp, ws, wps, -}
  * per redshift shell (mqw.py:24-41); cgg[n_ell] shared by all shells (cgg_per_bin = 0, as mqw.py:48) or
  * cgg[n_bin][n_ell] (cgg_per_bin = 1, as cadence/cadence.py:97); mode_weight[l] = 2l+1 (0 beyond an l cut).

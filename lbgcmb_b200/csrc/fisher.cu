@@ -250,6 +250,158 @@ extern "C" int lbg_fisher_accum(lbg_ctx* c, int n_ell, int n_spec, int n_par, co
     return LBG_OK;
 }
 
+// Field-level Fisher matrix for n_f correlated Gaussian fields (kappa and every tomographic galaxy bin at once):
+//   Q_l[p][q] = 1/2 Tr[ C_l^-1 d_p C_l  C_l^-1 d_q C_l ],   C_l[a][b] = (C + N)^{ab}(l),
+// algebraically the interloper.py:223-253 sum dD^T Cov^-1 dD with the Gaussian covariance of interloper.py:42-63 taken over ALL
+// auto and cross spectra of the fields (the (2l+1) fsky factor is part of the caller's mode weight), but without ever forming the
+// n_spec x n_spec covariance: 121 fields (6 tracers x 20 bins + kappa, BASELINE configs[3]) would need a 7381 x 7381 inverse per l.
+// One CTA per multipole (persistent, strided): C_l scattered from the spectra list into shared memory, inverted in place
+// (Gauss-Jordan, no pivoting: C_l is symmetric positive definite), M_p = C^-1 d_pC built from the CSC pattern of the spectra list
+// into the CTA's scratch rows (L2 resident), then the traces sum_ij M_p[i][j] M_q[j][i] by a fixed-order block reduction.
+constexpr int FF_T = 256;
+
+__global__ void __launch_bounds__(FF_T)
+field_fisher_kernel(int n_ell, int nf, int n_spec, int np, const int* __restrict__ sa, const int* __restrict__ sb,
+                    const int* __restrict__ colptr, const int* __restrict__ rowidx, const int* __restrict__ specidx,
+                    const double* __restrict__ tot /*[n_spec][n_ell]*/, const double* __restrict__ dC /*[np][n_spec][n_ell]*/,
+                    double* __restrict__ scratch /*[gridDim.x][np][nf*nf]*/, double* __restrict__ q /*[n_ell][np*np]*/) {
+    extern __shared__ double ff_sm[];
+    double* W = ff_sm;                       // [nf][nf]
+    double* col = W + (size_t)nf * nf;       // [nf]
+    double* red = col + nf;                  // [FF_T / 32][36]
+    const int n2 = nf * nf, tid = threadIdx.x;
+    double* M = scratch + (size_t)blockIdx.x * np * n2;
+    for (int l = blockIdx.x; l < n_ell; l += gridDim.x) {
+        for (int e = tid; e < n2; e += FF_T) W[e] = 0.0;
+        __syncthreads();
+        for (int s = tid; s < n_spec; s += FF_T) {
+            const double v = tot[(size_t)s * n_ell + l];
+            W[sa[s] * nf + sb[s]] = v;
+            W[sb[s] * nf + sa[s]] = v;
+        }
+        __syncthreads();
+        for (int k = 0; k < nf; ++k) {
+            for (int i = tid; i < nf; i += FF_T) col[i] = W[i * nf + k];
+            __syncthreads();
+            const double d = 1.0 / col[k];
+            for (int j = tid; j < nf; j += FF_T) W[k * nf + j] = (j == k ? 1.0 : W[k * nf + j]) * d;
+            __syncthreads();
+            for (int e = tid; e < n2; e += FF_T) {
+                const int i = e / nf, j = e - i * nf;
+                if (i != k) W[e] = (j == k ? 0.0 : W[e]) - col[i] * W[k * nf + j];
+            }
+            __syncthreads();
+        }
+        for (int p = 0; p < np; ++p) {
+            const double* dp = dC + (size_t)p * n_spec * n_ell + l;
+            for (int e = tid; e < n2; e += FF_T) {
+                const int i = e / nf, j = e - i * nf;
+                double acc = 0.0;
+                for (int t = colptr[j]; t < colptr[j + 1]; ++t) acc += W[i * nf + rowidx[t]] * dp[(size_t)specidx[t] * n_ell];
+                M[(size_t)p * n2 + e] = acc;
+            }
+        }
+        __syncthreads();                     // M is read back by other threads of this CTA (global memory, same block)
+        double acc[36];
+#pragma unroll
+        for (int e = 0; e < 36; ++e) acc[e] = 0.0;
+        for (int e = tid; e < n2; e += FF_T) {
+            const int i = e / nf, j = e - i * nf;
+            double a[MAX_PAR], b[MAX_PAR];
+#pragma unroll
+            for (int p = 0; p < MAX_PAR; ++p) {
+                a[p] = p < np ? M[(size_t)p * n2 + e] : 0.0;
+                b[p] = p < np ? M[(size_t)p * n2 + j * nf + i] : 0.0;
+            }
+            int t = 0;
+#pragma unroll
+            for (int p = 0; p < MAX_PAR; ++p)
+#pragma unroll
+                for (int r = p; r < MAX_PAR; ++r, ++t) acc[t] += a[p] * b[r];
+        }
+#pragma unroll
+        for (int e = 0; e < 36; ++e) {
+            double v = acc[e];
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((tid & 31) == 0) red[(tid >> 5) * 36 + e] = v;
+        }
+        __syncthreads();
+        if (tid < np * np) {
+            const int p = tid / np, r = tid - p * np, lo = p < r ? p : r, hi = p < r ? r : p;
+            const int t = lo * MAX_PAR - lo * (lo - 1) / 2 + (hi - lo);
+            double v = 0.0;
+            for (int w = 0; w < FF_T / 32; ++w) v += red[w * 36 + t];
+            q[(size_t)l * np * np + tid] = 0.5 * v;
+        }
+        __syncthreads();
+    }
+}
+
+extern "C" int lbg_field_fisher(lbg_ctx* c, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
+                                int n_par, const double* dC, const double* mode_weight, double* out_F, double* out_per_ell) {
+    LBG_REQUIRE(c && out_F, "lbg_field_fisher: NULL argument");
+    LBG_REQUIRE(n_ell >= 0 && n_f >= 1 && n_f <= 160, "lbg_field_fisher: n_f=%d outside [1, 160]", n_f);
+    LBG_REQUIRE(n_spec >= 1 && n_spec <= n_f * (n_f + 1) / 2, "lbg_field_fisher: n_spec=%d outside [1, n_f (n_f + 1) / 2]", n_spec);
+    LBG_REQUIRE(n_par >= 1 && n_par <= MAX_PAR, "lbg_field_fisher: n_par=%d outside [1, %d]", n_par, MAX_PAR);
+    LBG_REQUIRE(spec_a && spec_b, "lbg_field_fisher: NULL spectrum list");
+    LBG_REQUIRE(n_ell == 0 || (tot && dC && mode_weight), "lbg_field_fisher: NULL array");
+    // CSC pattern of the symmetric matrices the spectra list fills; every field needs its auto spectrum (else C_l is singular)
+    std::vector<int> cnt(n_f + 1, 0), seen((size_t)n_f * n_f, 0);
+    for (int s = 0; s < n_spec; ++s) {
+        const int a = spec_a[s], b = spec_b[s];
+        LBG_REQUIRE(a >= 0 && a < n_f && b >= 0 && b < n_f, "lbg_field_fisher: spectrum %d names field pair (%d, %d) outside [0, %d)", s, a, b, n_f);
+        LBG_REQUIRE(!seen[(size_t)a * n_f + b], "lbg_field_fisher: field pair (%d, %d) listed twice", a, b);
+        seen[(size_t)a * n_f + b] = seen[(size_t)b * n_f + a] = 1;
+        cnt[b + 1]++;
+        if (a != b) cnt[a + 1]++;
+    }
+    for (int f = 0; f < n_f; ++f) LBG_REQUIRE(seen[(size_t)f * n_f + f], "lbg_field_fisher: field %d has no auto spectrum", f);
+    for (int e = 0; e < n_par * n_par; ++e) out_F[e] = 0.0;
+    if (n_ell == 0) return LBG_OK;
+    for (int f = 0; f < n_f; ++f) cnt[f + 1] += cnt[f];
+    const int nnz = cnt[n_f];
+    std::vector<int> pat((size_t)2 * n_spec + n_f + 1 + 2 * (size_t)nnz), fill(cnt.begin(), cnt.end() - 1);
+    int* h_sa = pat.data(); int* h_sb = h_sa + n_spec; int* h_cp = h_sb + n_spec; int* h_ri = h_cp + n_f + 1; int* h_si = h_ri + nnz;
+    for (int s = 0; s < n_spec; ++s) {
+        const int a = spec_a[s], b = spec_b[s];
+        h_sa[s] = a; h_sb[s] = b;
+        h_ri[fill[b]] = a; h_si[fill[b]++] = s;
+        if (a != b) { h_ri[fill[a]] = b; h_si[fill[a]++] = s; }
+    }
+    for (int f = 0; f <= n_f; ++f) h_cp[f] = cnt[f];
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    const size_t n2 = (size_t)n_f * n_f, smem = (n2 + n_f + (FF_T / 32) * 36) * 8;
+    int sms = 148;
+    LBG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    int per_sm = (int)((220u * 1024u) / smem);
+    per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
+    const int gx = n_ell < sms * per_sm ? n_ell : sms * per_sm;
+    const int nq = n_par * n_par;
+    const size_t nt = (size_t)n_spec * n_ell, nd = nt * n_par, nscr = (size_t)gx * n_par * n2;
+    if (c->s0.reserve(nt * 8) || c->s1.reserve(nd * 8) || c->s2.reserve(pat.size() * 4 + nscr * 8 + 8) || c->s3.reserve((size_t)n_ell * 8) ||
+        c->s4.reserve((size_t)n_ell * nq * 8) || c->s5.reserve((size_t)nq * 8)) return LBG_ENOMEM;
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaFuncSetAttribute(field_fisher_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, tot, nt * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s1.p, dC, nd * 8, cudaMemcpyHostToDevice, st));
+    const size_t scr_off = (pat.size() * 4 + 7) & ~(size_t)7;
+    LBG_CUDA(cudaMemcpyAsync(c->s2.p, pat.data(), pat.size() * 4, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(c->s3.p, mode_weight, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
+    const int* d_pat = c->s2.as<int>();
+    double* scr = reinterpret_cast<double*>(c->s2.as<char>() + scr_off);
+    KernelTimer t(c);
+    field_fisher_kernel<<<gx, FF_T, smem, st>>>(n_ell, n_f, n_spec, n_par, d_pat, d_pat + n_spec, d_pat + 2 * n_spec,
+                                                d_pat + 2 * n_spec + n_f + 1, d_pat + 2 * n_spec + n_f + 1 + nnz,
+                                                c->s0.as<double>(), c->s1.as<double>(), scr, c->s4.as<double>());
+    t.launched();
+    weighted_sum_kernel<<<nq, RED_T, 0, st>>>(n_ell, nq, c->s3.as<double>(), c->s4.as<double>(), c->s5.as<double>());
+    t.launched();
+    LBG_CUDA(cudaMemcpyAsync(out_F, c->s5.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, st));
+    if (out_per_ell) LBG_CUDA(cudaMemcpyAsync(out_per_ell, c->s4.p, (size_t)n_ell * nq * 8, cudaMemcpyDeviceToHost, st));
+    return t.finish();
+}
+
 static int mqw_fisher_impl(lbg_ctx* c, int n_ell, int n_bin, const double* cgg, int cgg_per_bin, const double* bins,
                            const double* mode_weight, double fsky, double* out_F, double* out_Fsl, double* out_S, bool cadence) {
     LBG_REQUIRE(c && cgg && bins && mode_weight && out_F, "lbg_mqw_fisher / lbg_cadence_fisher: NULL argument");

@@ -43,6 +43,27 @@ def fisher_accum(cov, dD, mode_weight, dDelta=None, per_ell=False, device=None):
     return (F, b, Q) if per_ell else (F, b)
 
 
+def field_fisher(n_f, spectra, tot, dC, mode_weight, per_ell=False, device=None):
+    """F[p, q] = sum_l w_l 1/2 Tr[C_l^-1 d_pC_l C_l^-1 d_qC_l] for n_f correlated fields (lbg_field_fisher): the interloper.py:223-253
+    Fisher sum over ALL auto and cross spectra of the fields (w_l = nmodes (2l+1) fsky), without the n_spec x n_spec covariance.
+
+    spectra = [(a, b), ...] field pairs (unlisted pairs are zero); tot [n_spec, n_ell] = C + N; dC [n_par, n_spec, n_ell]."""
+    ctx = _ffi.context(device)
+    tot, dC, w = _ffi.f64(tot), _ffi.f64(dC), _ffi.f64(mode_weight)
+    n_spec, n_ell = tot.shape
+    if dC.ndim != 3 or dC.shape[1:] != (n_spec, n_ell) or w.shape != (n_ell,) or len(spectra) != n_spec:
+        raise ValueError('spectra / tot / dC / mode_weight shapes disagree')
+    n_par = dC.shape[0]
+    sa = np.ascontiguousarray([s[0] for s in spectra], dtype=np.int32)
+    sb = np.ascontiguousarray([s[1] for s in spectra], dtype=np.int32)
+    F = np.empty((n_par, n_par))
+    Q = np.empty((n_ell, n_par, n_par)) if per_ell else None
+    _ffi.check(_ffi.lib().lbg_field_fisher(ctx.handle, n_ell, int(n_f), n_spec, sa.ctypes.data_as(_ffi.c_int_p),
+                                           sb.ctypes.data_as(_ffi.c_int_p), _ffi._dp(tot), n_par, _ffi._dp(dC), _ffi._dp(w), _ffi._dp(F),
+                                           _ffi._dp(Q) if per_ell else None))
+    return (F, Q) if per_ell else F
+
+
 def mqw_fisher(cgg, bins, mode_weight, fsky, device=None):
     """(F [n_bin, n_bin], F_ii Schur-Limber [n_bin], S(l)) of mqw/py/mqw.py:63-104; bins[n_bin, 7] = bp,bs,Np,Ns,wp,ws,wps."""
     ctx = _ffi.context(device)

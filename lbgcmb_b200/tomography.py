@@ -1,0 +1,121 @@
+"""Tomographic CMB-lensing x galaxy Fisher forecast over cosmological and bias parameters (BASELINE configs[3]: kappa + 6 tracers x 20
+redshift bins, parameters sigma8 / sum m_nu / Omega_m and one bias amplitude per tracer).
+
+The reference has no single driver for it: tracers as in yu.py:44-48, bins of mqw/py/mqw.py:20, Limber projections in
+the modi flavour (modi/lensing.py:69-179: W_g = H dN/dz normalised by its trapezoid over chi, trapezoid over chi of W W / chi^2 P), the
+Fisher sum of interloper.py:200-253 taken over all fields at once (fisher.field_fisher), and its only cosmological derivative is the
+analytic sigma8 one of interloper.py:65-74.  Here every cosmology of the finite-difference stencil is built on the device: linear table
+from the Eisenstein-Hu fit with massive neutrinos (lbg_eh_linear_table, EisensteinAndHu.c:102-264), growth tables for the whole stencil
+in one launch (lbg_growth_table), HALOFIT rows and the Limber sums (csrc/limber.cu), then one lbg_field_fisher launch.  With the
+multipoles sharded over ranks the partial matrices meet in one all-reduce (dist.allreduce_sum)."""
+import numpy as np
+
+from lbgcmb_b200 import dist, eisenstein_hu, fisher
+from lbgcmb_b200.modi.cosmology import Cosmology, growth_tables
+from lbgcmb_b200.modi.lensing import LensingX, PkZ
+from lbgcmb_b200.quadrature import trapz_weights_x
+
+FIDUCIAL = {'sig8': 0.819, 'M': 0.292, 'B': 0.0468, 'h': 0.69, 'ns': 0.965, 'mnu': 0.06}       # M, h: modi/lensing.py:24-28
+STEPS = {'sig8': 0.01, 'M': 0.005, 'B': 0.001, 'h': 0.01, 'ns': 0.01, 'mnu': 0.02}                 # absolute, central differences
+K_GRID = np.logspace(-4., 2., 1200)
+
+
+def omega_hdm(mnu, h):
+    """Density parameter of sum m_nu [eV] in massive neutrinos: m / (93.14 h^2 eV)."""
+    return mnu / (93.14 * h * h)
+
+
+def make_cosmology(theta, Dplus_table='device', k=None, device=None):
+    """modi Cosmology for the parameter dict `theta` (keys of FIDUCIAL) with its linear table built on the device by the E-H fit,
+    sigma8-normalised (so sigma8 is a parameter in its own right and the other ones move the shape at fixed sigma8)."""
+    k = K_GRID if k is None else np.asarray(k, dtype=np.float64)
+    M, h = theta['M'], theta['h']
+    plin = eisenstein_hu.linear_power(k, M, theta['B'], 1. - M, h, theta['ns'], theta['sig8'], omega_hdm=omega_hdm(theta['mnu'], h),
+                                      degen_hdm=1, device=device)
+    return Cosmology(M=M, B=theta['B'], sig8=theta['sig8'], klin=k, plin=plin, device=device, Dplus_table=Dplus_table)
+
+
+def field_spectra(cosmo, ell, tracers, nodes_per_bin=10, nonlinear=True, kk=True):
+    """C_kk [n_ell] (None without `kk`), C_kg [n_field, n_ell], C_gg [n_field, n_ell] for every redshift bin of every tracer; one batched
+    Limber launch per tracer (2 n_bin entries sharing each P(k, z) lookup).  tracers: dicts with 'edges' [n_bin + 1] (contiguous bins),
+    'dndz' and 'bz' callables.  Bin i integrates over its own `nodes_per_bin` + 1 nodes of the tracer's z grid (edge nodes belong to both
+    neighbours), normalised over the bin as modi/lensing.py:78-87."""
+    ell = np.asarray(ell, dtype=np.float64)
+    lx = LensingX(z=1.0, dndz=None, cosmo=cosmo, l=ell)
+    ckk = lx.cl_kkz(PkZ(cosmo, nonlinear=nonlinear)) if kk else None
+    m = int(nodes_per_bin)
+    kg, gg = [], []
+    for t in tracers:
+        edges = np.asarray(t['edges'], dtype=np.float64)
+        nb = edges.size - 1
+        zs = np.concatenate([np.linspace(edges[i], edges[i + 1], m + 1)[:-1] for i in range(nb)] + [edges[-1:]])
+        chis = cosmo.chia(z=zs)
+        ker = cosmo.Ha(z=zs) * t['dndz'](zs)                                  # modi/lensing.py:109-112
+        kcmb = lx.kernel_cmb(z=zs)
+        b = np.array([float(t['bz'](z)) for z in zs])
+        w = np.zeros((2 * nb, zs.size))
+        for i in range(nb):
+            s = slice(i * m, (i + 1) * m + 1)
+            tw = trapz_weights_x(chis[s])
+            kg_i = ker[s] / np.dot(tw, ker[s])                                # normalised over the bin, :78-87
+            w[i, s] = kcmb[s] * kg_i / chis[s] ** 2. * b[s] * tw              # kgwts, :90
+            w[nb + i, s] = kg_i ** 2. / chis[s] ** 2. * b[s] ** 2. * tw       # ggwts, :89
+        out = cosmo.limber(ell, zs, chis, w, nonlinear=nonlinear, oob=1)
+        kg.append(out[:nb])
+        gg.append(out[nb:])
+    return ckk, np.concatenate(kg), np.concatenate(gg)
+
+
+def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=('sig8', 'mnu'), steps=None, nodes_per_bin=10,
+                       nonlinear=True, k=None, device=None, sharded=False):
+    """Fisher matrix over `cosmo_params` + one bias amplitude per tracer (b(z) -> A_t b(z), fiducial A_t = 1) from kappa and every
+    galaxy bin: fields (kappa, g_1 .. g_n), spectra kk, kappa g_i, g_i g_i (bins of one tracer are disjoint; cross-tracer overlaps
+    are neglected), noise N_kk = `nkk` [n_ell] and 1 / nbar_i on the galaxy autos (tracers[t]['nbar']: per bin, sr^-1).
+
+    Cosmological derivatives are central differences over cosmologies built on the device; bias derivatives are analytic
+    (C_kg / A, 2 C_gg / A).  n_par <= 8.  sharded=True: this rank takes ell[rank::world] and the matrices are all-reduced.
+    Returns dict: params, F, cov (= F^-1), sigma (marginalised 1-sigma), spectra (fiducial kk, kg, gg on this rank's multipoles)."""
+    fid = dict(FIDUCIAL, **(fid or {}))
+    steps = dict(STEPS, **(steps or {}))
+    ell, nmodes, nkk = (np.asarray(a, dtype=np.float64) for a in (ell, nmodes, nkk))
+    if sharded:
+        idx = dist.shard_indices(ell.size)
+        ell, nmodes, nkk = ell[idx], nmodes[idx], nkk[idx]
+    names = list(cosmo_params) + ['b_%s' % t.get('name', i) for i, t in enumerate(tracers)]
+    if len(names) > 8:
+        raise ValueError('at most 8 parameters (lbg_field_fisher): %d cosmological + %d tracers' % (len(cosmo_params), len(tracers)))
+    for p in cosmo_params:
+        if p not in FIDUCIAL:
+            raise ValueError('unknown cosmological parameter %r (one of %s)' % (p, sorted(FIDUCIAL)))
+    thetas = [fid]
+    for p in cosmo_params:
+        thetas += [dict(fid, **{p: fid[p] + steps[p]}), dict(fid, **{p: fid[p] - steps[p]})]
+    growth = growth_tables([t['M'] for t in thetas], device=device)           # the whole stencil in one launch
+    spec = []
+    for i, (theta, y) in enumerate(zip(thetas, growth)):
+        c = make_cosmology(theta, Dplus_table=y, k=k, device=device)
+        spec.append(field_spectra(c, ell, tracers, nodes_per_bin, nonlinear))
+        c.invalidate_device() if hasattr(c, 'invalidate_device') else None
+    ckk, ckg, cgg = spec[0]
+    nb = [len(t['edges']) - 1 for t in tracers]
+    nf = 1 + sum(nb)
+    ngg = np.concatenate([np.broadcast_to(1. / np.asarray(t['nbar'], dtype=np.float64), (n,)) for t, n in zip(tracers, nb)])
+    spectra = [(0, 0)] + [(0, i) for i in range(1, nf)] + [(i, i) for i in range(1, nf)]
+    tot = np.concatenate([(ckk + nkk)[None], ckg, cgg + ngg[:, None]])
+    dC = np.zeros((len(names), len(spectra), ell.size))
+    for j, p in enumerate(cosmo_params):
+        up, dn = spec[1 + 2 * j], spec[2 + 2 * j]
+        dC[j] = np.concatenate([(up[0] - dn[0])[None], up[1] - dn[1], up[2] - dn[2]]) / (2. * steps[p])
+    o = 0
+    for t, n in enumerate(nb):
+        j = len(cosmo_params) + t
+        dC[j, 1 + o:1 + o + n] = ckg[o:o + n]
+        dC[j, nf + o:nf + o + n] = 2. * cgg[o:o + n]
+        o += n
+    w = nmodes * (2. * ell + 1.) * fsky
+    F = fisher.field_fisher(nf, spectra, tot, dC, w, device=device)
+    if sharded:
+        F, = dist.allreduce_sum(F)
+    cov = np.linalg.inv(F)
+    return {'params': names, 'F': F, 'cov': cov, 'sigma': np.sqrt(np.diag(cov)), 'fiducial': fid,
+            'spectra': {'kk': ckk, 'kg': ckg, 'gg': cgg, 'ngg': ngg}, 'fields': nf, 'n_cosmologies': len(thetas)}

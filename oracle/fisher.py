@@ -115,3 +115,24 @@ def rho_from_spectra(kk, kg, gg, ngg):
         for j in np.arange(len(kg)):
             interim += kg[i] * irho[i, j] * kg[j]
     return np.sqrt(interim)
+
+
+def field_fisher(n_f, spectra, tot, dC, mode_weight):
+    """Field form of the interloper.py:223-253 Fisher sum for n_f correlated Gaussian fields (no reference counterpart beyond n_f = 2):
+    F[p, q] = sum_l w_l 1/2 Tr[C_l^-1 d_pC_l C_l^-1 d_qC_l], dense numpy.  With fields (kappa, g), spectra (kk, kg, gg) and
+    w_l = nmodes (2l+1) fsky it equals fisher_bias()'s `dD^T Cov^-1 dD` sum (checked in tests/test_field_fisher_gpu.py)."""
+    tot, dC = np.asarray(tot, dtype=np.float64), np.asarray(dC, dtype=np.float64)
+    n_par, n_spec, n_ell = dC.shape
+    F = np.zeros((n_par, n_par))
+    Q = np.zeros((n_ell, n_par, n_par))
+    for l in range(n_ell):
+        C = np.zeros((n_f, n_f))
+        D = np.zeros((n_par, n_f, n_f))
+        for s, (a, b) in enumerate(spectra):
+            C[a, b] = C[b, a] = tot[s, l]
+            D[:, a, b] = dC[:, s, l]
+            D[:, b, a] = dC[:, s, l]
+        M = np.linalg.solve(C, D)                       # [n_par, n_f, n_f] = C^-1 d_pC
+        Q[l] = 0.5 * np.einsum('pij,qji->pq', M, M)
+        F += mode_weight[l] * Q[l]
+    return F, Q
