@@ -92,10 +92,9 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
         thetas += [dict(fid, **{p: fid[p] + steps[p]}), dict(fid, **{p: fid[p] - steps[p]})]
     growth = growth_tables([t['M'] for t in thetas], device=device)           # the whole stencil in one launch
     spec = []
-    for i, (theta, y) in enumerate(zip(thetas, growth)):
+    for theta, y in zip(thetas, growth):
         c = make_cosmology(theta, Dplus_table=y, k=k, device=device)
         spec.append(field_spectra(c, ell, tracers, nodes_per_bin, nonlinear))
-        c.invalidate_device() if hasattr(c, 'invalidate_device') else None
     ckk, ckg, cgg = spec[0]
     nb = [len(t['edges']) - 1 for t in tracers]
     nf = 1 + sum(nb)

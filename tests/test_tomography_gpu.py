@@ -1,0 +1,72 @@
+"""GPU tests of the tomographic cosmology-parameter Fisher driver (lbgcmb_b200/tomography.py; BASELINE configs[3]).
+The reference has no such driver, so it is pinned piecewise: the per-bin Limber sums against the reference-pinned
+LensingX mirror (modi/lensing.py:69-179), the finite-difference sigma8 derivative against the exact 2 C / sigma8 of linear theory
+(interloper.py:65-74), the Fisher sum against the dense numpy restatement."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+dndz = lambda z: z ** 2. * np.exp(-(z / 0.5) ** 1.0)
+bz = lambda z: 1.1 + 0.4 * z
+ELL = np.unique(np.round(np.logspace(np.log10(50.), np.log10(3000.), 40)))
+
+
+def test_one_bin_equals_lensingx(ctx):
+    from lbgcmb_b200 import tomography as tm
+    from lbgcmb_b200.modi.lensing import LensingX, PkZ
+    c = tm.make_cosmology(tm.FIDUCIAL)
+    ckk, kg, gg = tm.field_spectra(c, ELL, [{'edges': [0.75, 1.25], 'dndz': dndz, 'bz': bz}], nodes_per_bin=99)
+    lx = LensingX(z=1.0, dndz=dndz, cosmo=c, l=ELL, dz=0.5, nz=100)
+    assert np.max(np.abs(kg[0] / lx.clz(PkZ(c, bias=bz, power=1), auto=False) - 1)) < 1e-12
+    assert np.max(np.abs(gg[0] / lx.clz(PkZ(c, bias=bz, power=2), auto=True) - 1)) < 1e-12
+    assert np.array_equal(ckk, lx.cl_kkz(PkZ(c)))
+    assert np.all(ckk > 0) and np.all(kg > 0) and np.all(gg > 0)
+
+
+def _tracers():
+    return [{'name': 'lo', 'edges': np.linspace(0.4, 1.0, 4), 'dndz': dndz, 'bz': bz, 'nbar': 3e6},
+            {'name': 'hi', 'edges': np.linspace(1.0, 2.0, 3), 'dndz': lambda z: np.exp(-0.5 * ((z - 1.5) / 0.4) ** 2.),
+             'bz': lambda z: 2.0 + 0. * z, 'nbar': [4e6, 2e6]}]
+
+
+def test_sigma8_derivative_and_fisher_sum(ctx):
+    from lbgcmb_b200 import tomography as tm
+    from oracle.fisher import field_fisher as dense
+    nm = np.ones_like(ELL)
+    nkk = 2e-8 * np.ones_like(ELL)
+    r = tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, cosmo_params=('sig8',), nonlinear=False)
+    assert r['params'] == ['sig8', 'b_lo', 'b_hi'] and r['fields'] == 6 and r['n_cosmologies'] == 3
+    s = r['spectra']
+    nf = 6
+    spectra = [(0, 0)] + [(0, i) for i in range(1, nf)] + [(i, i) for i in range(1, nf)]
+    tot = np.concatenate([(s['kk'] + nkk)[None], s['kg'], s['gg'] + s['ngg'][:, None]])
+    C = np.concatenate([s['kk'][None], s['kg'], s['gg']])
+    dC = np.zeros((3, len(spectra), ELL.size))
+    dC[0] = 2. * C / tm.FIDUCIAL['sig8']                          # linear theory: every spectrum scales as sigma8^2
+    dC[1, 1:4], dC[1, 6:9] = s['kg'][:3], 2. * s['gg'][:3]
+    dC[2, 4:6], dC[2, 9:11] = s['kg'][3:], 2. * s['gg'][3:]
+    F0, _ = dense(nf, spectra, tot, dC, nm * (2. * ELL + 1.) * 0.4)
+    assert np.max(np.abs(r['F'] - F0) / np.sqrt(np.outer(np.diag(F0), np.diag(F0)))) < 1e-9
+    assert np.all(np.linalg.eigvalsh(r['F']) > 0) and np.allclose(r['cov'] @ r['F'], np.eye(3), atol=1e-8)
+    assert np.array_equal(s['ngg'], 1. / np.array([3e6, 3e6, 3e6, 4e6, 2e6]))
+
+
+def test_neutrino_mass_forecast(ctx):
+    from lbgcmb_b200 import tomography as tm
+    nm = np.ones_like(ELL)
+    nkk = 2e-8 * np.ones_like(ELL)
+    r = tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, cosmo_params=('sig8', 'mnu', 'M'))
+    assert r['params'] == ['sig8', 'mnu', 'M', 'b_lo', 'b_hi'] and r['n_cosmologies'] == 7
+    F = r['F']
+    assert np.all(np.isfinite(F)) and np.array_equal(F, F.T) and np.all(np.linalg.eigvalsh(F) > 0)
+    assert np.all(r['sigma'] > 0) and np.all(r['sigma'] >= 1. / np.sqrt(np.diag(F)) * (1 - 1e-12))     # marginalised >= conditional
+    # the same call with the multipoles "sharded" over one rank, and halved noise -> more information on every parameter
+    r1 = tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, cosmo_params=('sig8', 'mnu', 'M'), sharded=True)
+    assert np.array_equal(r1['F'], F)
+    r2 = tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, 0.5 * nkk, cosmo_params=('sig8', 'mnu', 'M'))
+    assert np.all(np.diag(r2['F']) > np.diag(F))
+    with pytest.raises(ValueError):
+        tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, cosmo_params=('w0',))
+    with pytest.raises(ValueError):
+        tm.tomographic_fisher(_tracers() * 4, ELL, nm, 0.4, nkk, cosmo_params=('sig8',))
