@@ -255,75 +255,127 @@ extern "C" int lbg_fisher_accum(lbg_ctx* c, int n_ell, int n_spec, int n_par, co
 // algebraically the interloper.py:223-253 sum dD^T Cov^-1 dD with the Gaussian covariance of interloper.py:42-63 taken over ALL
 // auto and cross spectra of the fields (the (2l+1) fsky factor is part of the caller's mode weight), but without ever forming the
 // n_spec x n_spec covariance: 121 fields (6 tracers x 20 bins + kappa, BASELINE configs[3]) would need a 7381 x 7381 inverse per l.
-// One CTA per multipole (persistent, strided): C_l scattered from the spectra list into shared memory, inverted in place
-// (Gauss-Jordan, no pivoting: C_l is symmetric positive definite), M_p = C^-1 d_pC built from the CSC pattern of the spectra list
-// into the CTA's scratch rows (L2 resident), then the traces sum_ij M_p[i][j] M_q[j][i] by a fixed-order block reduction.
-constexpr int FF_T = 256;
+// One CTA per multipole (persistent, strided), everything in shared memory:
+//   1. C_l scattered from the spectra list, inverted in place (Gauss-Jordan without pivoting: C_l is symmetric positive definite;
+//      warp <-> row, lane <-> column, two barriers per pivot);
+//   2. for every (i, j): a_p = (W d_pC)[i][j] from the CSC column j of the pattern and b_q = (d_qC W)[i][j] from column i
+//      (the pattern is symmetric), Q_pq += a_p b_q -- nothing is stored.  Columns much denser than the rest (the kappa column of
+//      the arrowhead pattern: n_f entries against 2) would serialise the warps that meet them, so up to FF_HEAVY such columns are
+//      evaluated once per multipole by all threads into shared memory (W d_pC)[.][h] and read from there;
+//   3. fixed-order block reduction of the n_par (n_par + 1) / 2 sums.
+constexpr int FF_T = 512;
+constexpr int FF_HEAVY = 2;
 
+template <bool DV_SM, int NCG /*32-column groups per row: row stride S = 32 NCG >= n_f, padding kept zero*/>
 __global__ void __launch_bounds__(FF_T)
-field_fisher_kernel(int n_ell, int nf, int n_spec, int np, const int* __restrict__ sa, const int* __restrict__ sb,
+field_fisher_kernel(int n_ell, int nf, int n_spec, int np, int n_heavy, const int* __restrict__ sa, const int* __restrict__ sb,
                     const int* __restrict__ colptr, const int* __restrict__ rowidx, const int* __restrict__ specidx,
+                    const int* __restrict__ heavy /*[nf]: slot of a heavy column or -1*/,
                     const double* __restrict__ tot /*[n_spec][n_ell]*/, const double* __restrict__ dC /*[np][n_spec][n_ell]*/,
-                    double* __restrict__ scratch /*[gridDim.x][np][nf*nf]*/, double* __restrict__ q /*[n_ell][np*np]*/) {
+                    double* __restrict__ q /*[n_ell][np*np]*/) {
     extern __shared__ double ff_sm[];
-    double* W = ff_sm;                       // [nf][nf]
-    double* col = W + (size_t)nf * nf;       // [nf]
-    double* red = col + nf;                  // [FF_T / 32][36]
-    const int n2 = nf * nf, tid = threadIdx.x;
-    double* M = scratch + (size_t)blockIdx.x * np * n2;
+    constexpr int S = 32 * NCG;
+    double* W = ff_sm;                                       // [nf][S]
+    double* red = W + (size_t)nf * S;                        // [FF_T / 32][36]
+    double* mh = red + (FF_T / 32) * 36;                     // [n_heavy][np][nf]
+    double* dval = mh + (size_t)n_heavy * np * nf;           // [np][n_spec] (DV_SM)
+    const int n2 = nf * S, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    __shared__ int hcol[FF_HEAVY];
+    for (int j = tid; j < nf; j += FF_T) if (heavy[j] >= 0) hcol[heavy[j]] = j;
     for (int l = blockIdx.x; l < n_ell; l += gridDim.x) {
         for (int e = tid; e < n2; e += FF_T) W[e] = 0.0;
+        if (DV_SM) for (int e = tid; e < np * n_spec; e += FF_T) dval[e] = dC[(size_t)e * n_ell + l];
         __syncthreads();
         for (int s = tid; s < n_spec; s += FF_T) {
             const double v = tot[(size_t)s * n_ell + l];
-            W[sa[s] * nf + sb[s]] = v;
-            W[sb[s] * nf + sa[s]] = v;
+            W[sa[s] * S + sb[s]] = v;
+            W[sb[s] * S + sa[s]] = v;
         }
         __syncthreads();
         for (int k = 0; k < nf; ++k) {
-            for (int i = tid; i < nf; i += FF_T) col[i] = W[i * nf + k];
+            // lane <-> columns lane, lane + 32, ..: the pivot row is read once per sweep; every other row costs one load, one FMA and
+            // one store per element (no predicates: the padding columns are zero and stay zero), then column k gets -f
+            const double d = 1.0 / W[k * S + k];
+            double y[NCG];
+#pragma unroll
+            for (int u = 0; u < NCG; ++u) y[u] = W[k * S + lane + 32 * u];
+#pragma unroll 2
+            for (int i = warp; i < nf; i += FF_T / 32) {
+                if (i == k) continue;
+                double* ri = W + i * S;
+                const double f = ri[k] * d;
+                double x[NCG];
+#pragma unroll
+                for (int u = 0; u < NCG; ++u) x[u] = ri[lane + 32 * u];
+                __syncwarp();
+#pragma unroll
+                for (int u = 0; u < NCG; ++u) ri[lane + 32 * u] = x[u] - f * y[u];
+                __syncwarp();
+                if (lane == 0) ri[k] = -f;
+            }
             __syncthreads();
-            const double d = 1.0 / col[k];
-            for (int j = tid; j < nf; j += FF_T) W[k * nf + j] = (j == k ? 1.0 : W[k * nf + j]) * d;
-            __syncthreads();
-            for (int e = tid; e < n2; e += FF_T) {
-                const int i = e / nf, j = e - i * nf;
-                if (i != k) W[e] = (j == k ? 0.0 : W[e]) - col[i] * W[k * nf + j];
+            if (warp == 0) {
+#pragma unroll
+                for (int u = 0; u < NCG; ++u) W[k * S + lane + 32 * u] = y[u] * d;
+                __syncwarp();
+                if (lane == 0) W[k * S + k] = d;
             }
             __syncthreads();
         }
-        for (int p = 0; p < np; ++p) {
-            const double* dp = dC + (size_t)p * n_spec * n_ell + l;
-            for (int e = tid; e < n2; e += FF_T) {
-                const int i = e / nf, j = e - i * nf;
-                double acc = 0.0;
-                for (int t = colptr[j]; t < colptr[j + 1]; ++t) acc += W[i * nf + rowidx[t]] * dp[(size_t)specidx[t] * n_ell];
-                M[(size_t)p * n2 + e] = acc;
-            }
+        // dv(p, s): derivative p of spectrum s at this multipole
+#define FF_DV(p, s) (DV_SM ? dval[(p) * n_spec + (s)] : dC[((size_t)(p) * n_spec + (s)) * n_ell + l])
+        for (int e = tid; e < n_heavy * np * nf; e += FF_T) {            // (W d_pC)[i][h] for the heavy columns h
+            const int i = e % nf, p = (e / nf) % np, h = e / (nf * np), col = hcol[h];
+            double acc = 0.0;
+            for (int t = colptr[col]; t < colptr[col + 1]; ++t) acc += W[rowidx[t] * S + i] * FF_DV(p, specidx[t]);   // W symmetric
+            mh[e] = acc;
         }
-        __syncthreads();                     // M is read back by other threads of this CTA (global memory, same block)
+        __syncthreads();
         double acc[36];
 #pragma unroll
         for (int e = 0; e < 36; ++e) acc[e] = 0.0;
-        for (int e = tid; e < n2; e += FF_T) {
-            const int i = e / nf, j = e - i * nf;
-            double a[MAX_PAR], b[MAX_PAR];
+        for (int i = warp; i < nf; i += FF_T / 32) {
+            const int hi = heavy[i], i0 = colptr[i], i1 = colptr[i + 1];
+            for (int j = lane; j < nf; j += 32) {
+                const int hj = heavy[j];
+                double a[MAX_PAR], b[MAX_PAR];
 #pragma unroll
-            for (int p = 0; p < MAX_PAR; ++p) {
-                a[p] = p < np ? M[(size_t)p * n2 + e] : 0.0;
-                b[p] = p < np ? M[(size_t)p * n2 + j * nf + i] : 0.0;
+                for (int p = 0; p < MAX_PAR; ++p) a[p] = b[p] = 0.0;
+                if (hj >= 0) {
+#pragma unroll
+                    for (int p = 0; p < MAX_PAR; ++p) if (p < np) a[p] = mh[(hj * np + p) * nf + i];
+                } else {
+                    for (int t = colptr[j]; t < colptr[j + 1]; ++t) {
+                        const double w = W[i * S + rowidx[t]];
+                        const int s = specidx[t];
+#pragma unroll
+                        for (int p = 0; p < MAX_PAR; ++p) if (p < np) a[p] += w * FF_DV(p, s);
+                    }
+                }
+                if (hi >= 0) {
+#pragma unroll
+                    for (int p = 0; p < MAX_PAR; ++p) if (p < np) b[p] = mh[(hi * np + p) * nf + j];
+                } else {
+                    for (int t = i0; t < i1; ++t) {
+                        const double w = W[rowidx[t] * S + j];
+                        const int s = specidx[t];
+#pragma unroll
+                        for (int p = 0; p < MAX_PAR; ++p) if (p < np) b[p] += w * FF_DV(p, s);
+                    }
+                }
+                int t = 0;
+#pragma unroll
+                for (int p = 0; p < MAX_PAR; ++p)
+#pragma unroll
+                    for (int r = p; r < MAX_PAR; ++r, ++t) acc[t] += a[p] * b[r];
             }
-            int t = 0;
-#pragma unroll
-            for (int p = 0; p < MAX_PAR; ++p)
-#pragma unroll
-                for (int r = p; r < MAX_PAR; ++r, ++t) acc[t] += a[p] * b[r];
         }
+#undef FF_DV
 #pragma unroll
         for (int e = 0; e < 36; ++e) {
             double v = acc[e];
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if ((tid & 31) == 0) red[(tid >> 5) * 36 + e] = v;
+            if (lane == 0) red[warp * 36 + e] = v;
         }
         __syncthreads();
         if (tid < np * np) {
@@ -358,10 +410,17 @@ extern "C" int lbg_field_fisher(lbg_ctx* c, int n_ell, int n_f, int n_spec, cons
     for (int f = 0; f < n_f; ++f) LBG_REQUIRE(seen[(size_t)f * n_f + f], "lbg_field_fisher: field %d has no auto spectrum", f);
     for (int e = 0; e < n_par * n_par; ++e) out_F[e] = 0.0;
     if (n_ell == 0) return LBG_OK;
+    // heavy columns: more than 8 entries and more than 4x the mean column; staged only when there are at most FF_HEAVY of them
+    const int nnz = 2 * n_spec - n_f;
+    std::vector<int> hv(n_f, -1);
+    int n_heavy = 0;
+    for (int f = 0; f < n_f; ++f)
+        if (cnt[f + 1] > 8 && (long long)cnt[f + 1] * n_f > 4LL * nnz) { if (n_heavy < FF_HEAVY) hv[f] = n_heavy; n_heavy++; }
+    if (n_heavy > FF_HEAVY) { n_heavy = 0; std::fill(hv.begin(), hv.end(), -1); }
     for (int f = 0; f < n_f; ++f) cnt[f + 1] += cnt[f];
-    const int nnz = cnt[n_f];
-    std::vector<int> pat((size_t)2 * n_spec + n_f + 1 + 2 * (size_t)nnz), fill(cnt.begin(), cnt.end() - 1);
-    int* h_sa = pat.data(); int* h_sb = h_sa + n_spec; int* h_cp = h_sb + n_spec; int* h_ri = h_cp + n_f + 1; int* h_si = h_ri + nnz;
+    std::vector<int> pat((size_t)2 * n_spec + 2 * n_f + 1 + 2 * (size_t)nnz), fill(cnt.begin(), cnt.end() - 1);
+    int* h_sa = pat.data(); int* h_sb = h_sa + n_spec; int* h_cp = h_sb + n_spec; int* h_hv = h_cp + n_f + 1; int* h_ri = h_hv + n_f;
+    int* h_si = h_ri + nnz;
     for (int s = 0; s < n_spec; ++s) {
         const int a = spec_a[s], b = spec_b[s];
         h_sa[s] = a; h_sb[s] = b;
@@ -369,31 +428,38 @@ extern "C" int lbg_field_fisher(lbg_ctx* c, int n_ell, int n_f, int n_spec, cons
         if (a != b) { h_ri[fill[a]] = b; h_si[fill[a]++] = s; }
     }
     for (int f = 0; f <= n_f; ++f) h_cp[f] = cnt[f];
+    for (int f = 0; f < n_f; ++f) h_hv[f] = hv[f];
     std::lock_guard<std::mutex> g(c->mu);
     LBG_CUDA(cudaSetDevice(c->device));
-    const size_t n2 = (size_t)n_f * n_f, smem = (n2 + n_f + (FF_T / 32) * 36) * 8;
+    const int ncg = (n_f + 31) / 32;
+    const size_t n2 = (size_t)n_f * 32 * ncg, base = (n2 + (FF_T / 32) * 36 + (size_t)n_heavy * n_par * n_f) * 8;
+    const size_t dvb = (size_t)n_par * n_spec * 8;
+    const bool dv_sm = base + dvb <= 220u * 1024u;
+    const size_t smem = base + (dv_sm ? dvb : 0);
     int sms = 148;
     LBG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
-    int per_sm = (int)((220u * 1024u) / smem);
-    per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
-    const int gx = n_ell < sms * per_sm ? n_ell : sms * per_sm;
+    const int gx = n_ell < sms ? n_ell : sms;     // one CTA per SM: 512 threads x 128 registers fill the register file
     const int nq = n_par * n_par;
-    const size_t nt = (size_t)n_spec * n_ell, nd = nt * n_par, nscr = (size_t)gx * n_par * n2;
-    if (c->s0.reserve(nt * 8) || c->s1.reserve(nd * 8) || c->s2.reserve(pat.size() * 4 + nscr * 8 + 8) || c->s3.reserve((size_t)n_ell * 8) ||
+    const size_t nt = (size_t)n_spec * n_ell, nd = nt * n_par;
+    if (c->s0.reserve(nt * 8) || c->s1.reserve(nd * 8) || c->s2.reserve(pat.size() * 4) || c->s3.reserve((size_t)n_ell * 8) ||
         c->s4.reserve((size_t)n_ell * nq * 8) || c->s5.reserve((size_t)nq * 8)) return LBG_ENOMEM;
     cudaStream_t st = c->stream;
-    LBG_CUDA(cudaFuncSetAttribute(field_fisher_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    typedef void (*ff_kernel_t)(int, int, int, int, int, const int*, const int*, const int*, const int*, const int*, const int*, const double*,
+                                const double*, double*);
+    static const ff_kernel_t kerns[2][5] = {
+        {field_fisher_kernel<false, 1>, field_fisher_kernel<false, 2>, field_fisher_kernel<false, 3>, field_fisher_kernel<false, 4>, field_fisher_kernel<false, 5>},
+        {field_fisher_kernel<true, 1>, field_fisher_kernel<true, 2>, field_fisher_kernel<true, 3>, field_fisher_kernel<true, 4>, field_fisher_kernel<true, 5>}};
+    const ff_kernel_t kern = kerns[dv_sm ? 1 : 0][ncg - 1];
+    LBG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     LBG_CUDA(cudaMemcpyAsync(c->s0.p, tot, nt * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s1.p, dC, nd * 8, cudaMemcpyHostToDevice, st));
-    const size_t scr_off = (pat.size() * 4 + 7) & ~(size_t)7;
     LBG_CUDA(cudaMemcpyAsync(c->s2.p, pat.data(), pat.size() * 4, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s3.p, mode_weight, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
     const int* d_pat = c->s2.as<int>();
-    double* scr = reinterpret_cast<double*>(c->s2.as<char>() + scr_off);
     KernelTimer t(c);
-    field_fisher_kernel<<<gx, FF_T, smem, st>>>(n_ell, n_f, n_spec, n_par, d_pat, d_pat + n_spec, d_pat + 2 * n_spec,
-                                                d_pat + 2 * n_spec + n_f + 1, d_pat + 2 * n_spec + n_f + 1 + nnz,
-                                                c->s0.as<double>(), c->s1.as<double>(), scr, c->s4.as<double>());
+    kern<<<gx, FF_T, smem, st>>>(n_ell, n_f, n_spec, n_par, n_heavy, d_pat, d_pat + n_spec, d_pat + 2 * n_spec,
+                                 d_pat + 2 * n_spec + 2 * n_f + 1, d_pat + 2 * n_spec + 2 * n_f + 1 + nnz, d_pat + 2 * n_spec + n_f + 1,
+                                 c->s0.as<double>(), c->s1.as<double>(), c->s4.as<double>());
     t.launched();
     weighted_sum_kernel<<<nq, RED_T, 0, st>>>(n_ell, nq, c->s3.as<double>(), c->s4.as<double>(), c->s5.as<double>());
     t.launched();

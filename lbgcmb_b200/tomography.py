@@ -35,31 +35,43 @@ def make_cosmology(theta, Dplus_table='device', k=None, device=None):
     return Cosmology(M=M, B=theta['B'], sig8=theta['sig8'], klin=k, plin=plin, device=device, Dplus_table=Dplus_table)
 
 
-def field_spectra(cosmo, ell, tracers, nodes_per_bin=10, nonlinear=True, kk=True):
+def field_spectra(cosmo, ell, tracers, nodes_per_bin=10, nonlinear=True, kk=True, geometry=None):
     """C_kk [n_ell] (None without `kk`), C_kg [n_field, n_ell], C_gg [n_field, n_ell] for every redshift bin of every tracer; one batched
     Limber launch per tracer (2 n_bin entries sharing each P(k, z) lookup).  tracers: dicts with 'edges' [n_bin + 1] (contiguous bins),
     'dndz' and 'bz' callables.  Bin i integrates over its own `nodes_per_bin` + 1 nodes of the tracer's z grid (edge nodes belong to both
-    neighbours), normalised over the bin as modi/lensing.py:78-87."""
+    neighbours), normalised over the bin as modi/lensing.py:78-87.  `geometry`: a dict the caller keeps between calls with the SAME
+    ell, tracers and nodes_per_bin; the distances and weight vectors (host `quad`s, modi/cosmology.py:134-150) depend on (M, L) only and
+    are then computed once per background instead of once per cosmology."""
     ell = np.asarray(ell, dtype=np.float64)
-    lx = LensingX(z=1.0, dndz=None, cosmo=cosmo, l=ell)
+    key = (cosmo.M, cosmo.L, cosmo.H0)
+    geo = None if geometry is None else geometry.get(key)
+    if geo is None:
+        lx = LensingX(z=1.0, dndz=None, cosmo=cosmo, l=ell)
+        m = int(nodes_per_bin)
+        per_tracer = []
+        for t in tracers:
+            edges = np.asarray(t['edges'], dtype=np.float64)
+            nb = edges.size - 1
+            zs = np.concatenate([np.linspace(edges[i], edges[i + 1], m + 1)[:-1] for i in range(nb)] + [edges[-1:]])
+            chis = cosmo.chia(z=zs)
+            ker = cosmo.Ha(z=zs) * t['dndz'](zs)                                  # modi/lensing.py:109-112
+            kcmb = lx.kernel_cmb(z=zs)
+            b = np.array([float(t['bz'](z)) for z in zs])
+            w = np.zeros((2 * nb, zs.size))
+            for i in range(nb):
+                s = slice(i * m, (i + 1) * m + 1)
+                tw = trapz_weights_x(chis[s])
+                kg_i = ker[s] / np.dot(tw, ker[s])                                # normalised over the bin, :78-87
+                w[i, s] = kcmb[s] * kg_i / chis[s] ** 2. * b[s] * tw              # kgwts, :90
+                w[nb + i, s] = kg_i ** 2. / chis[s] ** 2. * b[s] ** 2. * tw       # ggwts, :89
+            per_tracer.append((nb, zs, chis, w))
+        geo = (lx, per_tracer)
+        if geometry is not None:
+            geometry[key] = geo
+    lx, per_tracer = geo
     ckk = lx.cl_kkz(PkZ(cosmo, nonlinear=nonlinear)) if kk else None
-    m = int(nodes_per_bin)
     kg, gg = [], []
-    for t in tracers:
-        edges = np.asarray(t['edges'], dtype=np.float64)
-        nb = edges.size - 1
-        zs = np.concatenate([np.linspace(edges[i], edges[i + 1], m + 1)[:-1] for i in range(nb)] + [edges[-1:]])
-        chis = cosmo.chia(z=zs)
-        ker = cosmo.Ha(z=zs) * t['dndz'](zs)                                  # modi/lensing.py:109-112
-        kcmb = lx.kernel_cmb(z=zs)
-        b = np.array([float(t['bz'](z)) for z in zs])
-        w = np.zeros((2 * nb, zs.size))
-        for i in range(nb):
-            s = slice(i * m, (i + 1) * m + 1)
-            tw = trapz_weights_x(chis[s])
-            kg_i = ker[s] / np.dot(tw, ker[s])                                # normalised over the bin, :78-87
-            w[i, s] = kcmb[s] * kg_i / chis[s] ** 2. * b[s] * tw              # kgwts, :90
-            w[nb + i, s] = kg_i ** 2. / chis[s] ** 2. * b[s] ** 2. * tw       # ggwts, :89
+    for nb, zs, chis, w in per_tracer:
         out = cosmo.limber(ell, zs, chis, w, nonlinear=nonlinear, oob=1)
         kg.append(out[:nb])
         gg.append(out[nb:])
@@ -91,10 +103,10 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
     for p in cosmo_params:
         thetas += [dict(fid, **{p: fid[p] + steps[p]}), dict(fid, **{p: fid[p] - steps[p]})]
     growth = growth_tables([t['M'] for t in thetas], device=device)           # the whole stencil in one launch
-    spec = []
+    spec, geometry = [], {}
     for theta, y in zip(thetas, growth):
         c = make_cosmology(theta, Dplus_table=y, k=k, device=device)
-        spec.append(field_spectra(c, ell, tracers, nodes_per_bin, nonlinear))
+        spec.append(field_spectra(c, ell, tracers, nodes_per_bin, nonlinear, geometry=geometry))
     ckk, ckg, cgg = spec[0]
     nb = [len(t['edges']) - 1 for t in tracers]
     nf = 1 + sum(nb)
