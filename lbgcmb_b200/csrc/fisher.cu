@@ -274,10 +274,11 @@ field_fisher_kernel(int n_ell, int nf, int n_spec, int np, int n_heavy, const in
                     const double* __restrict__ tot /*[n_spec][n_ell]*/, const double* __restrict__ dC /*[np][n_spec][n_ell]*/,
                     double* __restrict__ q /*[n_ell][np*np]*/) {
     extern __shared__ double ff_sm[];
-    constexpr int S = 32 * NCG;
+    constexpr int S = 32 * NCG, RPW = 2 * NCG;               // rows per warp: 16 warps x RPW >= S >= n_f
     double* W = ff_sm;                                       // [nf][S]
     double* red = W + (size_t)nf * S;                        // [FF_T / 32][36]
-    double* mh = red + (FF_T / 32) * 36;                     // [n_heavy][np][nf]
+    double* pbuf = red + (FF_T / 32) * 36;                   // [2][S] pivot row, double-buffered
+    double* mh = pbuf + 2 * S;                     // [n_heavy][np][nf]
     double* dval = mh + (size_t)n_heavy * np * nf;           // [np][n_spec] (DV_SM)
     const int n2 = nf * S, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     __shared__ int hcol[FF_HEAVY];
@@ -292,36 +293,59 @@ field_fisher_kernel(int n_ell, int nf, int n_spec, int np, int n_heavy, const in
             W[sb[s] * S + sa[s]] = v;
         }
         __syncthreads();
-        for (int k = 0; k < nf; ++k) {
-            // lane <-> columns lane, lane + 32, ..: the pivot row is read once per sweep; every other row costs one load, one FMA and
-            // one store per element (no predicates: the padding columns are zero and stay zero), then column k gets -f
-            const double d = 1.0 / W[k * S + k];
-            double y[NCG];
+        // Gauss-Jordan with the matrix in REGISTERS: warp w holds rows w, w + 16, .. (slot r), lane <-> columns lane, lane + 32, ..
+        // (zero padding stays zero).  Per pivot: the owning warp publishes row k through a double-buffered shared row (one barrier per
+        // pivot), every row takes its multiplier from the lane that owns column k by shuffle, one FMA per element.  Shared memory
+        // carries 2 rows per pivot instead of the whole matrix twice (the shared-memory version sat at 79 % of the L1 data pipe).
+        double m[RPW][NCG];
 #pragma unroll
-            for (int u = 0; u < NCG; ++u) y[u] = W[k * S + lane + 32 * u];
-#pragma unroll 2
-            for (int i = warp; i < nf; i += FF_T / 32) {
-                if (i == k) continue;
-                double* ri = W + i * S;
-                const double f = ri[k] * d;
-                double x[NCG];
+        for (int r = 0; r < RPW; ++r) {
+            const int i = warp + (FF_T / 32) * r;
 #pragma unroll
-                for (int u = 0; u < NCG; ++u) x[u] = ri[lane + 32 * u];
-                __syncwarp();
-#pragma unroll
-                for (int u = 0; u < NCG; ++u) ri[lane + 32 * u] = x[u] - f * y[u];
-                __syncwarp();
-                if (lane == 0) ri[k] = -f;
-            }
-            __syncthreads();
-            if (warp == 0) {
-#pragma unroll
-                for (int u = 0; u < NCG; ++u) W[k * S + lane + 32 * u] = y[u] * d;
-                __syncwarp();
-                if (lane == 0) W[k * S + k] = d;
-            }
-            __syncthreads();
+            for (int u = 0; u < NCG; ++u) m[r][u] = i < nf ? W[i * S + lane + 32 * u] : 0.0;
         }
+        for (int k = 0; k < nf; ++k) {
+            double* prow = pbuf + (k & 1) * S;
+            const int kw = k & (FF_T / 32 - 1), kr = k / (FF_T / 32), ku = k >> 5, kl = k & 31;
+            if (warp == kw) {
+#pragma unroll
+                for (int r = 0; r < RPW; ++r)
+                    if (r == kr) {
+#pragma unroll
+                        for (int u = 0; u < NCG; ++u) prow[lane + 32 * u] = m[r][u];
+                    }
+            }
+            __syncthreads();
+            const double d = 1.0 / prow[k];
+            double y[NCG];
+            bool own[NCG];
+#pragma unroll
+            for (int u = 0; u < NCG; ++u) { y[u] = prow[lane + 32 * u]; own[u] = u == ku && lane == kl; }
+#pragma unroll
+            for (int r = 0; r < RPW; ++r) {
+                const int i = warp + (FF_T / 32) * r;
+                double xk = 0.0;
+#pragma unroll
+                for (int u = 0; u < NCG; ++u) if (u == ku) xk = m[r][u];
+                const double f = __shfl_sync(0xffffffffu, xk, kl) * d;
+                if (i == k) {
+#pragma unroll
+                    for (int u = 0; u < NCG; ++u) m[r][u] = own[u] ? d : y[u] * d;
+                } else {
+#pragma unroll
+                    for (int u = 0; u < NCG; ++u) m[r][u] = own[u] ? -f : m[r][u] - f * y[u];
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < RPW; ++r) {
+            const int i = warp + (FF_T / 32) * r;
+            if (i < nf) {
+#pragma unroll
+                for (int u = 0; u < NCG; ++u) W[i * S + lane + 32 * u] = m[r][u];
+            }
+        }
+        __syncthreads();
         // dv(p, s): derivative p of spectrum s at this multipole
 #define FF_DV(p, s) (DV_SM ? dval[(p) * n_spec + (s)] : dC[((size_t)(p) * n_spec + (s)) * n_ell + l])
         for (int e = tid; e < n_heavy * np * nf; e += FF_T) {            // (W d_pC)[i][h] for the heavy columns h
@@ -432,7 +456,13 @@ extern "C" int lbg_field_fisher(lbg_ctx* c, int n_ell, int n_f, int n_spec, cons
     std::lock_guard<std::mutex> g(c->mu);
     LBG_CUDA(cudaSetDevice(c->device));
     const int ncg = (n_f + 31) / 32;
-    const size_t n2 = (size_t)n_f * 32 * ncg, base = (n2 + (FF_T / 32) * 36 + (size_t)n_heavy * n_par * n_f) * 8;
+    const size_t n2 = (size_t)n_f * 32 * ncg;
+    size_t base = (n2 + (FF_T / 32) * 36 + 64 * ncg + (size_t)n_heavy * n_par * n_f) * 8;
+    if (base > 226u * 1024u) {                 // no room to stage the dense columns next to a 160 x 160 matrix: evaluate them in place
+        n_heavy = 0;
+        for (int f = 0; f < n_f; ++f) h_hv[f] = -1;
+        base = (n2 + (FF_T / 32) * 36 + 64 * ncg) * 8;
+    }
     const size_t dvb = (size_t)n_par * n_spec * 8;
     const bool dv_sm = base + dvb <= 220u * 1024u;
     const size_t smem = base + (dv_sm ? dvb : 0);

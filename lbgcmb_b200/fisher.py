@@ -61,6 +61,8 @@ def field_fisher(n_f, spectra, tot, dC, mode_weight, per_ell=False, device=None)
     _ffi.check(_ffi.lib().lbg_field_fisher(ctx.handle, n_ell, int(n_f), n_spec, sa.ctypes.data_as(_ffi.c_int_p),
                                            sb.ctypes.data_as(_ffi.c_int_p), _ffi._dp(tot), n_par, _ffi._dp(dC), _ffi._dp(w), _ffi._dp(F),
                                            _ffi._dp(Q) if per_ell else None))
+    if not np.all(np.isfinite(F)):                     # a zero pivot: the reference's np.linalg.inv raises on a singular covariance
+        raise np.linalg.LinAlgError('lbg_field_fisher: C_l is singular (zero pivot) or holds non-finite entries at some multipole')
     return (F, Q) if per_ell else F
 
 

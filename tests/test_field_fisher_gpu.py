@@ -14,7 +14,9 @@ RTOL = 1e-10
 
 def _random_case(rng, n_f, n_ell, n_par, arrow):
     """SPD field covariances per multipole with the given sparsity pattern and random symmetric derivatives on the same pattern."""
-    if arrow:                                           # kappa x every bin, bins mutually uncorrelated
+    if arrow == 2:                                      # two dense fields (CMB and galaxy lensing, say) x every bin
+        spectra = [(0, 0), (0, 1), (1, 1)] + [(h, i) for h in (0, 1) for i in range(2, n_f)] + [(i, i) for i in range(2, n_f)]
+    elif arrow:                                         # kappa x every bin, bins mutually uncorrelated
         spectra = [(0, 0)] + [(0, i) for i in range(1, n_f)] + [(i, i) for i in range(1, n_f)]
     else:
         spectra = [(a, b) for a in range(n_f) for b in range(a, n_f)]
@@ -26,7 +28,7 @@ def _random_case(rng, n_f, n_ell, n_par, arrow):
             if a == b:
                 tot[s, l] = d[a]
             else:
-                r = rng.uniform(-1, 1) * (0.6 / np.sqrt(n_f) if arrow else 0.5 / n_f)   # keeps C diagonally dominant after scaling
+                r = rng.uniform(-1, 1) * (0.4 / np.sqrt(n_f) if arrow else 0.5 / n_f)   # keeps C diagonally dominant after scaling
                 tot[s, l] = r * np.sqrt(d[a] * d[b])
     dC = tot[None] * rng.uniform(-2, 2, (n_par, n_spec, 1)) * rng.uniform(0.5, 1.5, (n_par, n_spec, n_ell))
     w = rng.uniform(1, 100, n_ell)
@@ -34,7 +36,8 @@ def _random_case(rng, n_f, n_ell, n_par, arrow):
 
 
 @pytest.mark.parametrize('n_f,n_ell,n_par,arrow', [(1, 5, 1, False), (2, 40, 2, False), (7, 33, 3, False), (21, 20, 8, True),
-                                                   (32, 9, 4, False), (121, 6, 4, True), (160, 2, 2, True)])
+                                                   (32, 9, 4, False), (121, 6, 4, True), (160, 2, 2, True),
+                                                   (160, 3, 8, True), (160, 2, 8, 2), (40, 11, 5, 2), (33, 300, 2, True)])
 def test_field_fisher_vs_dense_numpy(ctx, n_f, n_ell, n_par, arrow):
     from lbgcmb_b200.fisher import field_fisher
     from oracle.fisher import field_fisher as ref
@@ -78,4 +81,6 @@ def test_field_fisher_errors(ctx):
         field_fisher(1, [(0, 0)], one, np.ones((9, 1, 3)), np.ones(3))
     with pytest.raises(ValueError):
         field_fisher(1, [(0, 0)], one, np.ones((1, 2, 3)), np.ones(3))
+    with pytest.raises(np.linalg.LinAlgError):
+        field_fisher(2, [(0, 0), (0, 1), (1, 1)], np.array([[1., 1.], [1., 1.], [1., 1.]]), np.ones((1, 3, 2)), np.ones(2))   # singular C_l
     assert np.array_equal(field_fisher(1, [(0, 0)], np.ones((1, 0)), np.ones((2, 1, 0)), np.ones(0)), np.zeros((2, 2)))
