@@ -266,6 +266,20 @@ extern "C" int lbg_fisher_accum(lbg_ctx* c, int n_ell, int n_spec, int n_par, co
 constexpr int FF_T = 512;
 constexpr int FF_HEAVY = 2;
 
+// One Gauss-Jordan sweep over the rows a warp holds, pivot column in column group KU: multiplier from the owning lane, one FMA per element.
+// (The pivot row passes through here too and is overwritten by the caller.)
+template <int NCG, int RPW, int KU>
+__device__ __forceinline__ void ff_sweep(double (&m)[RPW][NCG], const double (&y)[NCG], double d, int kl, int lane) {
+    const bool own = lane == kl;
+#pragma unroll
+    for (int r = 0; r < RPW; ++r) {
+        const double f = __shfl_sync(0xffffffffu, m[r][KU], kl) * d;
+#pragma unroll
+        for (int u = 0; u < NCG; ++u) m[r][u] = m[r][u] - f * y[u];
+        if (own) m[r][KU] = -f;
+    }
+}
+
 template <bool DV_SM, int NCG /*32-column groups per row: row stride S = 32 NCG >= n_f, padding kept zero*/>
 __global__ void __launch_bounds__(FF_T)
 field_fisher_kernel(int n_ell, int nf, int n_spec, int np, int n_heavy, const int* __restrict__ sa, const int* __restrict__ sb,
@@ -318,23 +332,23 @@ field_fisher_kernel(int n_ell, int nf, int n_spec, int np, int n_heavy, const in
             __syncthreads();
             const double d = 1.0 / prow[k];
             double y[NCG];
-            bool own[NCG];
 #pragma unroll
-            for (int u = 0; u < NCG; ++u) { y[u] = prow[lane + 32 * u]; own[u] = u == ku && lane == kl; }
+            for (int u = 0; u < NCG; ++u) y[u] = prow[lane + 32 * u];
+            // the column group of k is warp-uniform: one specialised sweep per group keeps every register index static
+            switch (ku) {
+                case 0: ff_sweep<NCG, RPW, 0>(m, y, d, kl, lane); break;
+                case 1: if constexpr (NCG > 1) ff_sweep<NCG, RPW, 1>(m, y, d, kl, lane); break;
+                case 2: if constexpr (NCG > 2) ff_sweep<NCG, RPW, 2>(m, y, d, kl, lane); break;
+                case 3: if constexpr (NCG > 3) ff_sweep<NCG, RPW, 3>(m, y, d, kl, lane); break;
+                default: if constexpr (NCG > 4) ff_sweep<NCG, RPW, 4>(m, y, d, kl, lane); break;
+            }
+            if (warp == kw) {                                // the pivot row itself: scaled old row, pivot -> 1 / pivot
 #pragma unroll
-            for (int r = 0; r < RPW; ++r) {
-                const int i = warp + (FF_T / 32) * r;
-                double xk = 0.0;
+                for (int r = 0; r < RPW; ++r)
+                    if (r == kr) {
 #pragma unroll
-                for (int u = 0; u < NCG; ++u) if (u == ku) xk = m[r][u];
-                const double f = __shfl_sync(0xffffffffu, xk, kl) * d;
-                if (i == k) {
-#pragma unroll
-                    for (int u = 0; u < NCG; ++u) m[r][u] = own[u] ? d : y[u] * d;
-                } else {
-#pragma unroll
-                    for (int u = 0; u < NCG; ++u) m[r][u] = own[u] ? -f : m[r][u] - f * y[u];
-                }
+                        for (int u = 0; u < NCG; ++u) m[r][u] = (u == ku && lane == kl) ? d : y[u] * d;
+                    }
             }
         }
 #pragma unroll
