@@ -98,14 +98,16 @@ def field_spectra(cosmo, ell, tracers, nodes_per_bin=10, nonlinear=True, kk=True
 
 
 def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=('sig8', 'mnu'), steps=None, nodes_per_bin=10,
-                       nonlinear=True, k=None, device=None, sharded=False):
+                       nonlinear=True, k=None, device=None, sharded=False, spectra_fn=None, accum=None):
     """Fisher matrix over `cosmo_params` + one bias amplitude per tracer (b(z) -> A_t b(z), fiducial A_t = 1) from kappa and every
     galaxy bin: fields (kappa, g_1 .. g_n), spectra kk, kappa g_i, g_i g_i (bins of one tracer are disjoint; cross-tracer overlaps
     are neglected), noise N_kk = `nkk` [n_ell] and 1 / nbar_i on the galaxy autos (tracers[t]['nbar']: per bin, sr^-1).
 
     Cosmological derivatives are central differences over cosmologies built on the device; bias derivatives are analytic
     (C_kg / A, 2 C_gg / A).  n_par <= 8.  sharded=True: this rank takes ell[rank::world] and the matrices are all-reduced.
-    Returns dict: params, F, cov (= F^-1), sigma (marginalised 1-sigma), spectra (fiducial kk, kg, gg on this rank's multipoles)."""
+    Returns dict: params, F, cov (= F^-1), sigma (marginalised 1-sigma), spectra (fiducial kk, kg, gg on this rank's multipoles).
+    `spectra_fn(theta, ell) -> (ckk, ckg, cgg)` and `accum` (signature of fisher.field_fisher) replace the device calls in the CPU
+    (gloo) tests of the sharding logic; the product path leaves both None."""
     fid = dict(FIDUCIAL, **(fid or {}))
     steps = dict(STEPS, **(steps or {}))
     ell, nmodes, nkk = (np.asarray(a, dtype=np.float64) for a in (ell, nmodes, nkk))
@@ -121,11 +123,14 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
     thetas = [fid]
     for p in cosmo_params:
         thetas += [dict(fid, **{p: fid[p] + steps[p]}), dict(fid, **{p: fid[p] - steps[p]})]
-    growth = growth_tables([t['M'] for t in thetas], device=device)           # the whole stencil in one launch
-    spec, geometry = [], {}
-    for theta, y in zip(thetas, growth):
-        c = make_cosmology(theta, Dplus_table=y, k=k, device=device)
-        spec.append(field_spectra(c, ell, tracers, nodes_per_bin, nonlinear, geometry=geometry))
+    if spectra_fn is None:
+        growth = growth_tables([t['M'] for t in thetas], device=device)       # the whole stencil in one launch
+        spec, geometry = [], {}
+        for theta, y in zip(thetas, growth):
+            c = make_cosmology(theta, Dplus_table=y, k=k, device=device)
+            spec.append(field_spectra(c, ell, tracers, nodes_per_bin, nonlinear, geometry=geometry))
+    else:
+        spec = [spectra_fn(theta, ell) for theta in thetas]
     ckk, ckg, cgg = spec[0]
     nb = [len(t['edges']) - 1 for t in tracers]
     nf = 1 + sum(nb)
@@ -143,7 +148,10 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
         dC[j, nf + o:nf + o + n] = 2. * cgg[o:o + n]
         o += n
     w = nmodes * (2. * ell + 1.) * fsky
-    F = fisher.field_fisher(nf, spectra, tot, dC, w, device=device)
+    if accum is None:
+        F = fisher.field_fisher(nf, spectra, tot, dC, w, device=device)
+    else:
+        F = accum(nf, spectra, tot, dC, w)
     if sharded:
         F, = dist.allreduce_sum(F)
     cov = np.linalg.inv(F)
