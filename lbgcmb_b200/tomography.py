@@ -137,13 +137,16 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
     ngg = np.concatenate([np.broadcast_to(1. / np.asarray(t['nbar'], dtype=np.float64), (n,)) for t, n in zip(tracers, nb)])
     spectra = [(0, 0)] + [(0, i) for i in range(1, nf)] + [(i, i) for i in range(1, nf)]
     tot = np.concatenate([(ckk + nkk)[None], ckg, cgg + ngg[:, None]])
-    dC = np.zeros((len(names), len(spectra), ell.size))
+    dC = np.empty((len(names), len(spectra), ell.size))
     for j, p in enumerate(cosmo_params):
         up, dn = spec[1 + 2 * j], spec[2 + 2 * j]
-        dC[j] = np.concatenate([(up[0] - dn[0])[None], up[1] - dn[1], up[2] - dn[2]]) / (2. * steps[p])
+        for sl, x, y in ((slice(0, 1), up[0], dn[0]), (slice(1, nf), up[1], dn[1]), (slice(nf, 2 * nf - 1), up[2], dn[2])):
+            np.subtract(x, y, out=dC[j, sl].reshape(np.shape(x)))
+            dC[j, sl] /= 2. * steps[p]
     o = 0
     for t, n in enumerate(nb):
         j = len(cosmo_params) + t
+        dC[j] = 0.0
         dC[j, 1 + o:1 + o + n] = ckg[o:o + n]
         dC[j, nf + o:nf + o + n] = 2. * cgg[o:o + n]
         o += n
