@@ -39,6 +39,13 @@ def test_version_and_error_string():
     assert b'lbg_cubic_spline_coeffs' in lib.lbg_last_error()
 
 
+def test_field_fisher_rejects_null_context_before_any_device_work():
+    lib = _ffi.lib()
+    rc = lib.lbg_field_fisher(None, 1, 1, 1, None, None, None, 1, None, None, None, None)
+    assert rc == -1
+    assert b'lbg_field_fisher' in lib.lbg_last_error()
+
+
 def test_no_cpu_fallback_without_device():
     import torch
     if torch.cuda.is_available():
