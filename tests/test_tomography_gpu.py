@@ -70,3 +70,24 @@ def test_neutrino_mass_forecast(ctx):
         tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, cosmo_params=('w0',))
     with pytest.raises(ValueError):
         tm.tomographic_fisher(_tracers() * 4, ELL, nm, 0.4, nkk, cosmo_params=('sig8',))
+
+
+def test_geometry_cache_is_per_background(ctx):
+    """Distances / weight vectors are shared by cosmologies with the same (M, L, H0) and rebuilt for another background;
+    cached and uncached calls return identical spectra."""
+    from lbgcmb_b200 import tomography as tm
+    tr = _tracers()
+    fid = tm.FIDUCIAL
+    geo = {}
+    a = tm.field_spectra(tm.make_cosmology(fid), ELL, tr, geometry=geo)
+    assert len(geo) == 1
+    b = tm.field_spectra(tm.make_cosmology(dict(fid, sig8=0.83)), ELL, tr, geometry=geo)
+    assert len(geo) == 1 and np.all(b[1] > a[1])                                   # same background, more power
+    c = tm.field_spectra(tm.make_cosmology(dict(fid, M=0.30)), ELL, tr, geometry=geo)
+    assert len(geo) == 2 and not np.array_equal(c[1], a[1])
+    a2 = tm.field_spectra(tm.make_cosmology(fid), ELL, tr, geometry=geo)            # served from the cache
+    a3 = tm.field_spectra(tm.make_cosmology(fid), ELL, tr, kk=False)                # no cache, no C_kk
+    assert a3[0] is None
+    for x, y, z in zip(a[1:], a2[1:], a3[1:]):
+        assert np.array_equal(x, y) and np.array_equal(x, z)
+    assert np.array_equal(a[0], a2[0])
