@@ -21,6 +21,19 @@ _ORDER = ('TT', 'EE', 'BB', 'TE')
 last_stats = {}
 
 
+def prep_lmaxmask(nu, nv):
+    """The multipole cuts of cmb/Nkk.py:13-26 as 0/1 arrays per estimator: |u| and |v| at most 3000 for the temperature
+    estimators and 5000 for the polarisation ones, |v| at least 2.  Host helper with the reference's return type; the kernel
+    applies the same cuts as phi-index ranges (csrc/n0.cu) and never forms these arrays."""
+    nu, nv = np.asarray(nu), np.asarray(nv)
+    cut = {}
+    for lmax in (3000, 5000):
+        keep = np.ones_like(nu) if lmax == 3000 else np.ones_like(nv)
+        keep[(nu > lmax) | (nv > lmax) | (nv < 2)] = 0.0
+        cut[lmax] = keep
+    return {'TT': cut[3000], 'TE': cut[3000], 'EE': cut[5000], 'BB': cut[5000], 'TB': cut[5000], 'EB': cut[5000]}
+
+
 def _simpson_weights(n, dx):
     """Composite Simpson weights for an odd number of uniform samples (scipy simps, cmb/Nkk.py:166-167)."""
     if n % 2 == 0:

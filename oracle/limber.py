@@ -109,3 +109,20 @@ def Ngg(Llls, zmin, zmax, survey_pz, nbar):
     zz = np.arange(zmin, zmax, 0.001)
     spz = np.trapezoid(survey_pz(zz), zz, dx=0.001)
     return np.ones_like(Llls) / (nbar / (np.pi / 180.) ** 2. * spz)
+
+
+def var_auto(Llls, cl, nl, fsky):
+    """2 (C + N)^2 / ((2L + 1) fsky): Cgg.py:70-83 (var_Cgg) and cmb/lensing.py:54-66 (var_Ckk); nl = 0 for samplevar_lim."""
+    num = cl + nl
+    num = 2. * num ** 2.
+    den = (2. * Llls + 1.) * fsky
+    return num / den
+
+
+def var_cross(Llls, ckk, nkk, cgg, ngg, ckg, fsky, rho=None):
+    """((C_kk (1 - rho^2) + N_kk)(C_gg + N_gg) + C_kg^2) / ((2L + 1) fsky): Ckg.py:60-87 (var_Ckg)."""
+    if rho is not None:
+        ckk = (1. - rho ** 2.) * ckk
+    num = (ckk + nkk) * (cgg + ngg) + ckg ** 2.
+    den = (2. * Llls + 1.) * fsky
+    return num / den

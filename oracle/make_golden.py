@@ -336,6 +336,89 @@ def cadence_inputs():
             'fsky': 5060. / 41253., 'fover': 0.05}
 
 
+def variance_inputs():
+    """Analytic inputs of the variance / ellipse goldens, shared with tests/test_variances_gpu.py."""
+    g = lambda z0, s: (lambda z: np.exp(-(np.asarray(z, dtype=np.float64) - z0) ** 2 / (2. * s * s)) / (np.sqrt(2. * np.pi) * s))
+    return {'pz': g(2.96, 0.24), 'bz': (lambda z: 1. + z), 'bz2': (lambda z: 0.8 + 0.5 * z), 'nbar': 2181.0, 'fsky': 0.4,
+            'zmin': 0.96, 'zmax': 4.96, 'rho': (lambda L: 0.8 * np.exp(-np.asarray(L, dtype=np.float64) / 3000.)),
+            'nkk': (lambda L: 2.0e-8 * (1. + (np.asarray(L, dtype=np.float64) / 1500.) ** 2.)),
+            'covs': [np.array([[2.0e-4, 3.0e-4], [3.0e-4, 9.0e-3]]), np.array([[4.0, -1.5], [-1.5, 1.0]]),
+                     np.array([[1.0e-2, 0.0], [0.0, 1.0e-2]])]}
+
+
+def make_variances():
+    """The variance wrappers (Cgg.py:70-83, Ckg.py:60-87, cmb/lensing.py:54-66), prep_camb.Clxy (:128-137), pmh.Pmm/Pmh/Phh
+    (:26-47), Nkk.prep_lmaxmask (cmb/Nkk.py:13-26) and fisher_contour.plot_ellipse (:15-111), all run UNMODIFIED."""
+    from . import halofit as ohf
+    from lbgcmb_b200.synthetic import cmb_cl_tables
+    hf = refload.load('halofit')
+    Cgg, Ckg, lensing, Nkk = refload.load('Cgg'), refload.load('Ckg'), refload.load('lensing'), refload.load('Nkk')
+    prep_camb, pmh, fcont = refload.load('prep_camb'), refload.load('pmh'), refload.load('fisher_contour')
+    prep = refload.load('prep_Llls')
+    k, p, eng, cosmo, P = _pk_setup()
+    Dg = lambda z: float(eng.Dgrow(z=z))
+    ref_pk = ohf.ModiPk(k, p, Dg, cosmo, P['sig_8'], halofit_fn=hf.halofit).interps()
+    T = variance_inputs()
+    _, Llls, nmodes = prep.prep_Llls(60, 50, 5000, log10=True)
+    Ld = Llls.astype(np.float64)
+    zmin, zmax, fsky, nbar = T['zmin'], T['zmax'], T['fsky'], T['nbar']
+    nkk = T['nkk'](Ld)
+    out = {'k': k, 'plin': p, 'Llls': Llls, 'nkk': nkk}
+    t = time.time()
+    cgg_full = Cgg.Cgg(ref_pk, Ld, zmin, zmax, T['pz'], T['bz'], zeff=False)
+    out['cgg_full'] = cgg_full
+    out['var_cgg'] = Cgg.var_Cgg(Ld, zmin, zmax, T['pz'], T['bz'], nbar, fsky, Pk_interps=ref_pk)
+    out['var_cgg_sv'] = Cgg.var_Cgg(Ld, zmin, zmax, T['pz'], T['bz'], nbar, fsky, Pk_interps=ref_pk, samplevar_lim=True)
+    out['var_cgg_given'] = Cgg.var_Cgg(Ld, zmin, zmax, T['pz'], T['bz'], nbar, fsky, cgg=cgg_full)
+    li, ni = None, None
+    vk = lambda **kw: Ckg.var_Ckg(ref_pk, li, ni, Ld, zmin, zmax, T['pz'], T['bz'], nbar, fsky, nkk=nkk, **kw)
+    out['var_ckg'] = vk()
+    out['var_ckg_full'] = vk(zeff=False)
+    out['var_ckg_rho'] = vk(rho=T['rho'])
+    out['var_ckg_msl'] = vk(modesample_lim=True)
+    out['var_ckg_ngg'] = vk(ngg=3.0e-9 * np.ones_like(Ld))
+    out['var_ckk'] = lensing.var_Ckk(Ld, fsky, nkk, Pk_interps=ref_pk)
+    out['var_ckk_sv'] = lensing.var_Ckk(Ld, fsky, nkk, Pk_interps=ref_pk, samplevar_lim=True)
+    print('variance wrappers: %.1f s' % (time.time() - t))
+    # nkk=None: the wrapper runs Nkk itself (two multipoles; thetab / DeltaT / iterative forwarded)
+    t = time.time()
+    ell, lens, nolens = cmb_cl_tables(5300)
+    li, ni = on0.cl_interps(ell, lens), on0.cl_interps(ell, nolens)
+    L2 = np.array([100., 2000.])
+    out['L2'] = L2
+    out['var_ckg_nkknone'] = Ckg.var_Ckg(ref_pk, li, ni, L2, zmin, zmax, T['pz'], T['bz'], nbar, fsky, thetab=1.4, DeltaT=7.0,
+                                         iterative=True, pickleit=False)
+    print('var_Ckg(nkk=None): %.1f s' % (time.time() - t))
+    # Clxy on integer and fractional multipoles
+    x = np.array([2., 10.5, 100., 1000.25, 2999.5, 5000.])
+    out['clxy_x'] = x
+    for a in ('TT', 'EE', 'BB', 'TE'):
+        out['clxy_' + a] = prep_camb.Clxy(li, x.copy(), a, 1.4, 7.0)
+    # P(k,z) helpers
+    kk = np.array([1.0e-3, 0.02, 0.1, 0.5, 2.0, 30.0])
+    out['pk_k'], out['pk_z'] = kk, 1.3
+    out['pmm_lin'] = pmh.Pmm(ref_pk, kk, 1.3, type='linear')
+    out['pmm_nlin'] = pmh.Pmm(ref_pk, kk, 1.3)
+    out['pmh'] = pmh.Pmh(ref_pk, T['bz'], kk, 1.3)
+    out['phh'] = pmh.Phh(ref_pk, T['bz'], kk, 1.3)
+    out['phh2'] = pmh.Phh(ref_pk, T['bz'], kk, 1.3, bz2=T['bz2'])
+    # prep_lmaxmask on values either side of every cut
+    nu = np.array([1., 2., 2999.5, 3000., 3000.5, 4999., 5000., 5000.5, 10., 10.])
+    nv = np.array([10., 10., 10., 10., 10., 10., 10., 10., 1.5, 5001.])
+    m = Nkk.prep_lmaxmask(nu, nv)
+    out['mask_nu'], out['mask_nv'] = nu, nv
+    out['mask_keys'] = np.array(sorted(m))
+    out['masks'] = np.array([m[key] for key in sorted(m)])
+    # Fisher ellipses
+    for i, cov in enumerate(T['covs']):
+        for tag, ml in (('68', 0.68), ('95', 0.95), ('none', None)):
+            out['ell_%d_%s' % (i, tag)] = fcont.plot_ellipse(cov=cov.copy(), mass_level=ml, data_out=True, theta_num=1000,
+                                                              x_cent=0.8, y_cent=3.9)
+    out['ell_axes'] = fcont.plot_ellipse(semimaj=2.0, semimin=0.5, phi=0.3, theta_num=500, data_out=True)
+    np.savez_compressed(os.path.join(GOLD, 'variances.npz'), **out)
+    print('variances golden written:', sorted(out))
+
+
 EH_CASES = [(0.292, 0.0468, 0.0, 1, 0.708, 0.69, 0.0), (0.3106, 0.04898, 0.0, 3, 0.6894, 0.677, 3.0),
             (0.31, 0.049, 0.0045, 3, 0.69, 0.68, 1.0), (0.25, 0.04, 0.02, 1, 0.70, 0.72, 0.5)]
 
@@ -355,7 +438,7 @@ def make_eh():
 
 
 MAKERS = {'n0': make_n0, 'halofit': make_halofit, 'limber': make_limber, 'fisher': make_fisher, 'modi': make_modi,
-          'modi_lensing': make_modi_lensing, 'cadence': make_cadence, 'eh': make_eh}
+          'modi_lensing': make_modi_lensing, 'cadence': make_cadence, 'eh': make_eh, 'variances': make_variances}
 
 if __name__ == '__main__':
     os.makedirs(GOLD, exist_ok=True)
