@@ -71,14 +71,22 @@ int lbg_cubic_spline_coeffs(int n_knots, const double* y, double* coef_out /*[n_
  *   l1[n_l1], w_l1[n_l1]         the |u| grid (reference: arange(1, 5000.5, 0.5)) and its Simpson weights
  *   cos_phi/sin_phi/w_phi[n_phi]  the phi grid (reference: arange(0, 2pi+dphi, dphi)) and its weights
  * integral(L) = sum_ij w_phi[j] w_l1[i] l1[i] * sum_terms f F mask ;  N0 = (L(L+1)/2)^2 (2pi)^2 / integral.
- * lmax_T / lmax_P / lmin_v: the 3000 / 5000 / 2 cuts of prep_lmaxmask.  `fold_phi` != 0 lets the library
- * evaluate only one node of each mirror pair (phi, 2pi-phi); the number of integrand nodes
- * actually executed is returned in *nodes_executed (may be NULL).
- * exact_rows[n_exact] / exact_u[n_exact][n_phi][8] (optional, n_exact may be 0): rows of the l1 grid for which the caller
- * supplies its own u-side spline values at |u|_j = sqrt((l cos_j)^2 + (l sin_j)^2), order unlensed TT,TE,EE,BB then lensed
- * TT,TE,EE,BB.  Needed for bit-faithful parity with the reference on rows below the first non-zero C_l (l1 < 2 for CAMB
- * tables, where C_0 = C_1 = 0): there 1/C^tot is pure detector noise and the reference's value inherits the last-bit
- * rounding of scipy's spline evaluation (DESIGN.md "parity notes").  Rows on the lmax cuts are always treated exactly.
+ * lmax_T / lmax_P / lmin_v: the 3000 / 5000 / 2 cuts of prep_lmaxmask (0 < lmin_v < lmax_T <= lmax_P).
+ * fold_phi: 0 = evaluate every phi node; 1 = evaluate one node of each mirror pair (phi, 2pi-phi) (the grid must be
+ * symmetric) with the range-walking kernel; 2 = mirror pairs with the generic per-node-mask kernel (a second implementation of the
+ * same sums, for cross-checks).  lbg_n0_last_path() tells which integrand kernel the last call ran: 5 = range-walking
+ * (n0_rows5_kernel; needs fold_phi = 1, cos phi_j strictly decreasing over the first half of the grid, tables that cover every reachable
+ * |v| <= min(lmax_P, max L + max l1) and a beam narrow enough for the folded-noise fit, about 7.5 arcmin at lmax_P = 5000),
+ * 3 = generic (n0_rows3_kernel; anything else).  Inputs neither kernel can serve (more than 508 phi nodes after folding, |v| beyond
+ * 16380) return LBG_EINVAL with a message; there is no other kernel and no environment switch.
+ * *nodes_executed (may be NULL) receives the number of (phi, l1, L) nodes of the rows the main kernel was launched for.
+ * Rows below the first non-zero C_l (l1 < 2 for CAMB tables, where C_0 = C_1 = 0): there 1/C^tot is pure detector noise and the
+ * reference's value inherits the last-bit rounding of scipy's spline routines (DESIGN.md "parity notes").  The library evaluates the
+ * u-side splines of every row with l1 < lbg_n0_set_exact_below() (default 2.0) on the host with scipy's own operation order
+ * (make_interp_spline's LAPACK-order solve + de Boor evaluation, bit-identical: lbg_scipy_cubic_eval_host), so a C caller reaches the
+ * reference to 1e-10 without scipy.  exact_rows[n_exact] / exact_u[n_exact][n_phi][8] (optional, n_exact may be 0): rows for which
+ * the caller supplies its own values at |u|_j = sqrt((l cos_j)^2 + (l sin_j)^2) instead, order unlensed TT,TE,EE,BB then lensed
+ * TT,TE,EE,BB.  Rows on the lmax cuts are always treated exactly.
  * out_terms (may be NULL) receives the per-estimator integrals, [5][n_L] in bit order TT,TE,EE,EB,BB. */
 int lbg_n0_ho02(lbg_ctx* ctx, int n_L, const double* L, unsigned terms_mask,
                 double thetab_arcmin, double deltaT_uK_arcmin, double Tcmb_K, int iterative,
@@ -88,6 +96,24 @@ int lbg_n0_ho02(lbg_ctx* ctx, int n_L, const double* L, unsigned terms_mask,
                 int n_exact, const int* exact_rows, const double* exact_u,
                 double* out_nkk /*[n_L]*/, double* out_terms /*[5][n_L] or NULL*/,
                 long long* nodes_executed /*or NULL*/);
+/* The same call in two halves: _begin validates, stages the inputs in pinned memory and enqueues every kernel and the result copy on
+ * the context's stream, then returns; _end waits and hands the results over.  Between the two the host (and other contexts of the
+ * same GPU, lbg_ctx_create_lane) may do anything except call N0 / table uploads on THIS context (LBG_ESTATE).  A forecast starts
+ * its 25 ms N0 curve first and builds the Limber spectra meanwhile -- one thread, no polling.  *nodes_unmasked (may be NULL): the
+ * number of integrand nodes that passed a mask, counted by the kernels (the nodes the reference's masks leave non-zero). */
+int lbg_n0_ho02_begin(lbg_ctx* ctx, int n_L, const double* L, unsigned terms_mask,
+                      double thetab_arcmin, double deltaT_uK_arcmin, double Tcmb_K, int iterative,
+                      int n_l1, const double* l1, const double* w_l1,
+                      int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
+                      double lmax_T, double lmax_P, double lmin_v, int fold_phi,
+                      int n_exact, const int* exact_rows, const double* exact_u);
+int lbg_n0_ho02_end(lbg_ctx* ctx, int n_L, double* out_nkk /*[n_L]*/, double* out_terms /*[5][n_L] or NULL*/,
+                    long long* nodes_executed /*or NULL*/, long long* nodes_unmasked /*or NULL*/);
+int lbg_n0_set_exact_below(lbg_ctx* ctx, double l_below);   /* 0 disables the scipy-order rows */
+int lbg_n0_last_path(lbg_ctx* ctx, int* path);
+/* Host-only (no GPU): scipy `interp1d(arange(n_knots), y, kind='cubic', bounds_error=False, fill_value=0.0)(x)`, bit for bit
+ * (prep_camb.py:88-89 as scipy evaluates it: LAPACK-order not-a-knot solve, de Boor recurrence). */
+int lbg_scipy_cubic_eval_host(int n_knots, const double* y, int n, const double* x, double* out);
 
 /* ---- N0, modi flavour: replaces modi/nkk.py:35-92 (N_fisher: mode = LBG_TT, LBG_EE, LBG_EB) and :94-146 (N_fisherTE:
  *      mode = LBG_TE).  out_int[n_L] is the double integral `int2` those functions return;
@@ -153,6 +179,22 @@ int lbg_growth_table(lbg_ctx* ctx, int n_cosmo, const double* omega_m, const dou
  *      weight = kernel product x bias x unit factors x quadrature weight, so one kernel serves every flavour. */
 int lbg_limber(lbg_ctx* ctx, int n_batch, int n_ell, const double* ell, int n_z, const double* chi,
                const double* weight /*[n_batch][n_z]*/, const int* prow /*[n_z]*/, int oob, double* out_cl /*[n_batch][n_ell]*/);
+
+/* ---- the Limber stage of one forecast in one call: interloper.py:23-40 (`get_allCls`) without its N0 call, for n_s galaxy samples
+ *      on one set of multipoles: C_gg (Cgg.py:53-68, zeff=False, auto spectrum), C_kg (Ckg.py:42-59, zeff=False) per sample and
+ *      C_kk (cmb/lensing.py:21-52) once.  The host only evaluates the callables: pz_*[s][n] = p_s(z) and bz_*[s][n] = b_s(z) on the
+ *      C_gg nodes (Cgg.py:18-19) and on the C_kg nodes (Ckg.py:19-20), norm[s] = trapz(p_s) on the dz = 0.001 grid of sliced_pz.py:6-9.
+ *      On the device: the sliced_pz renormalisation (sliced_pz.py:10-26, dz_* = its 6-decimal rounded grid spacing), the prefactors
+ *      (H/c) p^ p^ / chi^2 b b / h and W_kappa p^ / chi^2 b / h^2 times the Simpson weights w_*, and the sums over z against the
+ *      P(k,z) tables parked in slot_gg / slot_kg / slot_kk (lbg_pk_select_slot + lbg_pk_build_table: one row per grid node, in order).
+ *      hc_gg = H(z)/c on the C_gg nodes, wk_kg = W_kappa(z) on the C_kg nodes (cmb/lensing.py:14-19), weight_kk = the complete
+ *      per-node weight of the C_kk sum (n_kk = 0: no C_kk).  One pinned staging block in, one out. */
+int lbg_forecast_spectra(lbg_ctx* ctx, int n_ell, const double* ell, double zmin, double zmax, double h100,
+                         int n_gg, const double* z_gg, const double* chi_gg, const double* hc_gg, const double* w_gg, double dz_gg, int slot_gg,
+                         int n_kg, const double* z_kg, const double* chi_kg, const double* wk_kg, const double* w_kg, double dz_kg, int slot_kg,
+                         int n_kk, const double* chi_kk, const double* weight_kk, int slot_kk,
+                         int n_s, const double* pz_gg, const double* bz_gg, const double* pz_kg, const double* bz_kg, const double* norm,
+                         double* out_cgg /*[n_s][n_ell]*/, double* out_ckg /*[n_s][n_ell]*/, double* out_ckk /*[n_ell] or NULL*/);
 
 /* ---- S/N, covariance and Fisher accumulation over multipoles ---------------------------------------------------- */
 /* snr.py:21-25 `snr`: sqrt( sum_{l <= lmax} nmodes (C_l / sqrt(Var_l))^2 ). */

@@ -56,9 +56,24 @@ def root_grids(lmax=5000., Nphi=200, Nell=10000):
     return ell, w_ell, pphi, w_phi
 
 
+_DEFAULT_GRIDS = None
+
+
+def _default_grids():
+    """root_grids() and cos / sin of its phi nodes, computed once (the reference rebuilds them per call, cmb/Nkk.py:54-62)."""
+    global _DEFAULT_GRIDS
+    if _DEFAULT_GRIDS is None:
+        ell, w_ell, pphi, w_phi = root_grids()
+        _DEFAULT_GRIDS = tuple(_ffi.f64(a) for a in (ell, w_ell, pphi, w_phi, np.cos(pphi), np.sin(pphi)))
+        for a in _DEFAULT_GRIDS:
+            a.setflags(write=False)
+    return _DEFAULT_GRIDS
+
+
 def upload_cls(ctx, lensCl_interps, nolensCl_interps, reuse=False):
-    """C_l tables -> the context (spline solve + H2D).  `reuse`: skip the upload when the tables equal, value for value, the ones
-    this context received last (a sweep over beam / noise calls N0 many times on the same spectra)."""
+    """C_l tables -> the context.  The library compares them, value for value, with the tables it already holds and keeps its
+    splines when nothing changed (a sweep over beam / noise calls N0 many times on the same spectra), so every call hands the
+    tables over; `reuse` is accepted for compatibility and changes nothing."""
     lens = [table_of(lensCl_interps[x]) for x in _ORDER]
     n = min(t.size for t in lens)
     nolens = []
@@ -67,56 +82,42 @@ def upload_cls(ctx, lensCl_interps, nolensCl_interps, reuse=False):
     n = min(n, min(t.size for t in nolens))
     lt = _ffi.f64(np.stack([t[:n] for t in lens]))
     ut = _ffi.f64(np.stack([t[:n] for t in nolens]))
-    last = getattr(ctx, '_cl_last', None)
-    same = last is not None and last[0].shape == lt.shape and np.array_equal(last[0], lt) and np.array_equal(last[1], ut)
-    if not same:
-        ctx._exact_cache = None              # host-side values derived from the tables (_exact_u_rows)
-    if same and reuse:
-        return n
     _ffi.check(_ffi.lib().lbg_upload_cl_tables(ctx.handle, n, _ffi._dp(lt), _ffi._dp(ut)))
-    ctx._cl_last = (lt, ut)
     return n
 
 
-def _exact_u_rows(lensCl_interps, nolensCl_interps, ell, cphi, sphi, below):
-    """u-side spline values at |u|_j for the l1 rows below the first non-zero C_l (l1 < 2: CAMB tables have C_0 = C_1 = 0).
+class N0Call(object):
+    """An N0 call in flight (lbg_n0_ho02_begin issued): `result()` waits for it and returns what n0_terms returns."""
 
-    There C^tot(|u|) is pure detector noise (~1e-20) while the spline crosses zero between knots of size 1e-10, so the
-    reference's 1/C^tot carries the last-bit rounding of scipy's `interp1d` evaluation at relative 1e-6 -- and these rows
-    carry up to 20 % of the TT integral at low L.  For bit-faithful parity the few affected values (2 rows x 201 nodes x 8
-    spectra) are evaluated with the very routine the reference uses (prep_camb.py:88-89) and handed to the kernel
-    (lbg_n0_ho02 `exact_u`); every other node is evaluated on the device."""
-    from scipy.interpolate import interp1d
-    rows = np.nonzero(ell < below)[0].astype(np.int32)
-    if rows.size == 0:
-        return rows, np.zeros(0)
-    ux = ell[rows][:, None] * cphi[None, :]
-    uy = ell[rows][:, None] * sphi[None, :]
-    nu = (ux ** 2. + uy ** 2.) ** 0.5                          # cmb/Nkk.py:79
-    vals = np.empty((rows.size, cphi.size, 8))
-    k = 0
-    for interps in (nolensCl_interps, lensCl_interps):
-        for name in ('TT', 'TE', 'EE', 'BB'):
-            f = interps[name]
-            if not isinstance(f, interp1d):
-                g = getattr(f, '_scipy_interp1d', None)                # built once per table-backed callable
-                if g is None:
-                    g = interp1d(np.arange(table_of(f).size, dtype=np.float64), table_of(f), kind='cubic',
-                                 bounds_error=False, fill_value=0.0)
-                    try:
-                        f._scipy_interp1d = g
-                    except AttributeError:
-                        pass
-                f = g
-            vals[:, :, k] = f(nu)
-            k += 1
-    return np.ascontiguousarray(rows), np.ascontiguousarray(vals)
+    def __init__(self, ctx, n_L, keep):
+        self.ctx, self.n_L, self._keep, self._res = ctx, n_L, keep, None
+
+    def result(self):
+        if self._res is None:
+            import ctypes as C
+            out = np.empty(self.n_L)
+            out_terms = np.empty((5, self.n_L))
+            nodes, unmasked, path = C.c_longlong(0), C.c_longlong(0), C.c_int(0)
+            _ffi.check(_ffi.lib().lbg_n0_ho02_end(self.ctx.handle, self.n_L, _ffi._dp(out), _ffi._dp(out_terms), C.byref(nodes),
+                                                  C.byref(unmasked)))
+            _ffi.check(_ffi.lib().lbg_n0_last_path(self.ctx.handle, C.byref(path)))
+            ms, launches = self.ctx.last_kernel_ms()
+            last_stats.update(nodes=nodes.value, nodes_unmasked=unmasked.value, kernel_ms=ms, launches=launches, n_L=self.n_L,
+                              main_kernel_ms=self.ctx.last_main_kernel_ms(), path=path.value)
+            self._keep = None
+            self._res = (out, {t: out_terms[i] for i, t in enumerate(('TT', 'TE', 'EE', 'EB', 'BB'))})
+        return self._res
 
 
-def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'), thetab=1., DeltaT=1.,
+def n0_begin(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'), thetab=1., DeltaT=1.,
              iterative=False, fold_phi=True, device=None, Tcmb=None, grids=None,
-             lmax_T=3000., lmax_P=5000., lmin_v=2., cos_sin=None, exact_u_below=2.0, lane=0, reuse_tables=False):
-    """(N0[len(Ls)], {term: integral[len(Ls)]}) -- the combined noise plus the per-estimator integrals."""
+             lmax_T=3000., lmax_P=5000., lmin_v=2., cos_sin=None, exact_u_below=2.0, lane=0, reuse_tables=False,
+             exact_rows=None, exact_u=None):
+    """Start an N0 evaluation (tables compared / uploaded, inputs staged, kernels enqueued) and return at once: N0Call.
+
+    fold_phi: True = one node per mirror pair (phi, 2 pi - phi), False = every node, 2 = mirror pairs through the generic
+    per-node-mask kernel (cross-check).  exact_u_below: l1 rows below it get their u-side spline values from the library's
+    scipy-order host routine (csrc/ctx.cu; DESIGN.md "parity notes"); exact_rows / exact_u let a caller supply its own."""
     for t in terms:
         if t == 'TB':
             raise KeyError('TB')   # the reference indexes nolensCl_interps['TB'], which get_Cls never builds
@@ -126,63 +127,59 @@ def n0_terms(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'
     for t in terms:
         mask |= TERM_BITS[t]
     ctx = _ffi.context(device, lane)
-    upload_cls(ctx, lensCl_interps, nolensCl_interps, reuse=reuse_tables)
-    ell, w_ell, pphi, w_phi = grids if grids is not None else root_grids()
-    Ld = _ffi.f64(Ls)
-    if cos_sin is None:
-        cos_sin = (np.cos(pphi), np.sin(pphi))
-    cphi, sphi = _ffi.f64(cos_sin[0]), _ffi.f64(cos_sin[1])
-    ell, w_ell, w_phi = _ffi.f64(ell), _ffi.f64(w_ell), _ffi.f64(w_phi)
-    out = np.empty(Ld.size)
-    out_terms = np.empty((5, Ld.size))
-    import ctypes as C
-    # the scipy-evaluated u-side rows depend on the tables and the grids only: kept while the context's tables are value-equal
-    ekey = (ell.size, float(exact_u_below), cphi.tobytes(), sphi.tobytes(), ell.tobytes())
-    cached = getattr(ctx, '_exact_cache', None)
-    if cached is not None and cached[0] == ekey:
-        exact_rows, exact_u = cached[1], cached[2]
+    upload_cls(ctx, lensCl_interps, nolensCl_interps)
+    if grids is None and cos_sin is None:
+        ell, w_ell, pphi, w_phi, cphi, sphi = _default_grids()
     else:
-        exact_rows, exact_u = _exact_u_rows(lensCl_interps, nolensCl_interps, ell, cphi, sphi, exact_u_below)
-        ctx._exact_cache = (ekey, exact_rows, exact_u)
-    nodes = C.c_longlong(0)
+        ell, w_ell, pphi, w_phi = grids if grids is not None else root_grids()
+        if cos_sin is None:
+            cos_sin = (np.cos(pphi), np.sin(pphi))
+        cphi, sphi = _ffi.f64(cos_sin[0]), _ffi.f64(cos_sin[1])
+        ell, w_ell, w_phi = _ffi.f64(ell), _ffi.f64(w_ell), _ffi.f64(w_phi)
+    Ld = _ffi.f64(Ls)
     if Tcmb is None:
         Tcmb = get_params()['Tcmb']
-    _ffi.check(_ffi.lib().lbg_n0_ho02(ctx.handle, Ld.size, _ffi._dp(Ld), mask, float(thetab), float(DeltaT),
-                                      float(Tcmb), int(bool(iterative)), ell.size, _ffi._dp(ell), _ffi._dp(w_ell),
-                                      pphi.size, _ffi._dp(cphi), _ffi._dp(sphi), _ffi._dp(w_phi),
-                                      float(lmax_T), float(lmax_P), float(lmin_v), int(bool(fold_phi)),
-                                      exact_rows.size, exact_rows.ctypes.data_as(_ffi.c_int_p), _ffi._dp(exact_u),
-                                      _ffi._dp(out), _ffi._dp(out_terms), C.byref(nodes)))
-    ms, launches = ctx.last_kernel_ms()
-    last_stats.update(nodes=nodes.value, kernel_ms=ms, launches=launches, n_L=Ld.size, main_kernel_ms=ctx.last_main_kernel_ms())
-    return out, {t: out_terms[i] for i, t in enumerate(('TT', 'TE', 'EE', 'EB', 'BB'))}
+    if exact_rows is None:
+        exact_rows, exact_u = np.zeros(0, dtype=np.int32), np.zeros(0)
+    exact_rows = np.ascontiguousarray(exact_rows, dtype=np.int32)
+    exact_u = _ffi.f64(exact_u)
+    fold = 2 if fold_phi == 2 and fold_phi is not True else int(bool(fold_phi))
+    _ffi.check(_ffi.lib().lbg_n0_set_exact_below(ctx.handle, float(exact_u_below)))
+    _ffi.check(_ffi.lib().lbg_n0_ho02_begin(ctx.handle, Ld.size, _ffi._dp(Ld), mask, float(thetab), float(DeltaT),
+                                            float(Tcmb), int(bool(iterative)), ell.size, _ffi._dp(ell), _ffi._dp(w_ell),
+                                            pphi.size, _ffi._dp(cphi), _ffi._dp(sphi), _ffi._dp(w_phi),
+                                            float(lmax_T), float(lmax_P), float(lmin_v), fold,
+                                            exact_rows.size, exact_rows.ctypes.data_as(_ffi.c_int_p), _ffi._dp(exact_u)))
+    return N0Call(ctx, Ld.size, (Ld, ell, w_ell, cphi, sphi, w_phi, exact_rows, exact_u))
 
 
-_pool = None
-
-
-def _submit(fn):
-    global _pool
-    if _pool is None:
-        from concurrent.futures import ThreadPoolExecutor
-        _pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix='lbg-n0')
-    return _pool.submit(fn)
+def n0_terms(*args, **kw):
+    """(N0[len(Ls)], {term: integral[len(Ls)]}) -- the combined noise plus the per-estimator integrals (arguments of n0_begin)."""
+    return n0_begin(*args, **kw).result()
 
 
 def n0_terms_async(*args, **kw):
-    """`n0_terms` submitted to a worker thread on a second context of the same GPU (lane 1: own stream and scratch);
-    returns a concurrent.futures.Future whose result() is what n0_terms returns.
+    """`n0_begin` on a second context of the same GPU (lane 1: own stream, scratch and phi-table block, lowest stream priority);
+    returns the N0Call, whose result() is what n0_terms returns.
 
-    The N0 curve is the long pole of a forecast (25 ms for 4951 L) and nothing in the Limber stage depends on it until
-    the variances are formed (Ckg.py:83-87), so a driver can start it first and build its spectra meanwhile: the library
-    call releases the GIL and the two contexts' kernels share the GPU."""
+    The N0 curve is the long pole of a forecast (25 ms for 4951 L) and nothing in the Limber stage depends on it until the
+    variances are formed (Ckg.py:83-87), so a driver starts it first and builds its spectra meanwhile: one host thread, the two
+    contexts' kernels share the GPU (the short lane-0 kernels take SM slots as N0 CTAs retire)."""
     kw.setdefault('lane', 1)
-    return _submit(lambda: n0_terms(*args, **kw))
+    return n0_begin(*args, **kw)
+
+
+class _Mapped(object):
+    def __init__(self, call, fn):
+        self._call, self._fn = call, fn
+
+    def result(self):
+        return self._fn(self._call.result())
 
 
 def Nkk_async(lensCl_interps, nolensCl_interps, Ls, terms=['TT', 'TE', 'EE', 'EB'], thetab=1., DeltaT=1., iterative=False):
-    """Future of Nkk(...) (no pickle cache): see n0_terms_async."""
-    return _submit(lambda: n0_terms(lensCl_interps, nolensCl_interps, Ls, terms, thetab, DeltaT, iterative, lane=1)[0])
+    """Nkk(...) in flight on lane 1 (no pickle cache): result() returns the curve.  See n0_terms_async."""
+    return _Mapped(n0_begin(lensCl_interps, nolensCl_interps, Ls, terms, thetab, DeltaT, iterative, lane=1), lambda r: r[0])
 
 
 def _cache_path(Ls, terms, thetab, DeltaT, iterative):

@@ -71,6 +71,12 @@ def _declare(L):
         'lbg_eh_transfer': [vp, d, d, d, i, d, d, d, i, c_double_p, c_double_p, c_double_p, c_double_p],
         'lbg_eh_linear_table': [vp, d, d, d, i, d, d, d, d, i, c_double_p, c_double_p, c_double_p],
         'lbg_limber': [vp, i, i, c_double_p, i, c_double_p, c_double_p, c_int_p, i, c_double_p],
+        'lbg_forecast_spectra': [vp, i, c_double_p, d, d, d,
+                                 i, c_double_p, c_double_p, c_double_p, c_double_p, d, i,
+                                 i, c_double_p, c_double_p, c_double_p, c_double_p, d, i,
+                                 i, c_double_p, c_double_p, i,
+                                 i, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p,
+                                 c_double_p, c_double_p, c_double_p],
         'lbg_n0_modi': [vp, i, i, c_double_p, i, c_double_p, c_double_p, i, c_double_p, c_double_p, c_double_p,
                         c_int_p, c_double_p, c_double_p, c_double_p],
         'lbg_eval_spline_ext': [vp, i, d, c_double_p, i, c_double_p, c_double_p],
@@ -84,6 +90,12 @@ def _declare(L):
                               c_double_p, i, c_double_p, d, d, c_double_p],
         'lbg_n0_ho02': [vp, i, c_double_p, u, d, d, d, i, i, c_double_p, c_double_p, i, c_double_p, c_double_p,
                         c_double_p, d, d, d, i, i, c_int_p, c_double_p, c_double_p, c_double_p, c_ll_p],
+        'lbg_n0_ho02_begin': [vp, i, c_double_p, u, d, d, d, i, i, c_double_p, c_double_p, i, c_double_p, c_double_p,
+                              c_double_p, d, d, d, i, i, c_int_p, c_double_p],
+        'lbg_n0_ho02_end': [vp, i, c_double_p, c_double_p, c_ll_p, c_ll_p],
+        'lbg_n0_set_exact_below': [vp, d],
+        'lbg_n0_last_path': [vp, c_int_p],
+        'lbg_scipy_cubic_eval_host': [i, c_double_p, i, c_double_p, c_double_p],
     }
     for name, args in sig.items():
         fn = getattr(L, name)

@@ -76,8 +76,11 @@ struct __align__(64) ClRow {
 
 }  // namespace lbg
 
+struct lbg_n0_plan;               // n0.cu: grid-dependent part of an N0 call, kept between calls
+
 struct lbg_ctx {
     int          device = 0;
+    int          lane = 0;
     int          sm_count = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
@@ -93,11 +96,24 @@ struct lbg_ctx {
     lbg::DevBuf  cl_rows;            // ClRow[n_ell + 2], row r holds coefficient index r-1
     lbg::DevBuf  cl_soa;             // the same coefficients spectrum-major: double[8][cl_soa_stride]
     int          cl_soa_stride = 0;
-    lbg::DevBuf  cl_pairs;           // overlapping pairs (c_r, c_{r+1}) per spectrum: double2[8][LBG_PAIR_STRIDE] (n0 rows2 kernel)
-    lbg::DevBuf  cl_poly;            // per-call: double4[n_ell-1][8] monomial coefficients per knot interval, noise folded in (n0 rows3 kernel)
+    lbg::DevBuf  cl_poly;            // per-call: double[8 slots][4][LBG_PAIR_STRIDE] monomial coefficients per knot interval, noise folded in
     bool         ub_zero = false;    // unlensed BB identically zero (its slot is then never read)
-    // N0 workspaces
-    lbg::DevBuf  n0_L, n0_utab, n0_phi, n0_partial, n0_out, n0_rowflag, n0_G;
+    std::vector<double> cl_host;     // the uploaded tables, [8][n_ell] in ClRow order: value comparison on re-upload, scipy-order splines
+    unsigned long long  cl_gen = 0;  // bumped by every upload that changed the tables
+    std::vector<double> cl_bspl_t, cl_bspl_c;   // scipy make_interp_spline(k=3) representation (knots; [8][n_ell] coefficients), built on demand
+    unsigned long long  cl_bspl_gen = ~0ull;
+    // N0 workspaces and state
+    lbg::DevBuf  n0_L, n0_utab, n0_partial, n0_out, n0_plan_dev;
+    lbg::PinBuf  pin_n0, pin_n0_out;
+    lbg_n0_plan* n0_plan = nullptr;
+    bool         n0_pending = false; // lbg_n0_ho02_begin issued, lbg_n0_ho02_end not yet
+    int          n0_n_L = 0;
+    int          n0_path = 0;        // integrand kernel of the last call: 5 = range-walking (rows5), 3 = generic per-node masks (rows3)
+    long long    n0_nodes_walked = 0;
+    double       n0_exact_below = 2.0;   // l1 rows below this get their u-side splines from the scipy-order host routine
+    std::vector<double> n0_exact_vals;
+    unsigned long long  n0_exact_gen = ~0ull;
+    bool         cw_lane_valid = false;
     // generic scratch
     lbg::DevBuf  s0, s1, s2, s3, s4, s5;
     lbg::PinBuf  pin_in, pin_out;    // pinned staging for the short, copy-dominated calls (lbg_limber)
@@ -117,6 +133,9 @@ struct lbg_ctx {
 
 namespace lbg {
 int upload_rdk(lbg_ctx* c, int n_k, const double* k);   // limber.cu: reciprocal k-cell widths for the installed k grid
+int ensure_scipy_bspline(lbg_ctx* c);                   // ctx.cu: fills cl_bspl_t / cl_bspl_c for the current tables
+// scipy.interpolate.make_interp_spline(arange(n), y, k=3) bit for bit (not-a-knot knots, LAPACK dgbsv order): ctx.cu
+void scipy_notaknot_cubic(int n, const double* y, double* t_out /*[n+4] or NULL*/, double* c_out /*[n]*/);
 struct KernelTimer {   // records ev0/ev1 on the context stream around the kernels of one API call
     lbg_ctx* c;
     explicit KernelTimer(lbg_ctx* ctx) : c(ctx) { c->last_launches = 0; cudaEventRecord(c->ev0, c->stream); }

@@ -1,6 +1,7 @@
 // ctx.cu -- context lifetime, error strings, CMB spline tables, FP64 peak micro-benchmark.
 #include "common.cuh"
 #include <future>
+#include <algorithm>
 #include <cstring>
 #include <cstdarg>
 #include <cmath>
@@ -48,6 +49,119 @@ void cardinal_bspline_coeffs(int n, const double* y, std::vector<double>& c /* n
         c[0] = 2.0 * c[1] - c[2] + M[0];
         c[n + 1] = 2.0 * c[n] - c[n - 1] + M[n - 1];
     }
+}
+
+// scipy's own representation of the same interpolant: make_interp_spline(arange(n), y, k=3) -> knots t = (0,0,0,0,2,3,..,n-3,
+// n-1 x 4) (`_not_a_knot`), coefficients from the collocation matrix (`_coloc`, de Boor) solved by LAPACK dgbsv with kl = ku = 3.
+// The sums below follow dgbtf2 + dgbtrs + dtbsv statement by statement, with the rank-1 / axpy updates fused (fma) and the
+// multipliers formed by the reciprocal of the pivot, which is how the OpenBLAS kernels scipy ships compute them on FMA-capable
+// x86-64: the coefficients come out bit-identical to scipy's (tests/test_scipy_spline_cpu.py).  Needed only where the reference's
+// result hangs on the rounding of this routine (n0.cu, rows below the first non-zero C_l).
+void scipy_notaknot_cubic(int n, const double* y, double* t_out, double* c_out) {
+    const int k = 3, kl = 3, ku = 3, kv = kl + ku, ldab = 2 * kl + ku + 1;
+    std::vector<double> t((size_t)n + k + 1);
+    for (int i = 0; i < 4; ++i) t[i] = 0.0;
+    for (int i = 2; i <= n - 3; ++i) t[4 + i - 2] = (double)i;
+    for (int i = 0; i < 4; ++i) t[n + i] = (double)(n - 1);
+    if (t_out) memcpy(t_out, t.data(), t.size() * 8);
+    std::vector<double> AB((size_t)ldab * n, 0.0);
+    auto ab = [&](int i, int j) -> double& { return AB[(size_t)j * ldab + i]; };
+    int left = k;
+    for (int j = 0; j < n; ++j) {                       // collocation rows: the four non-zero B-splines at x = j
+        const double xv = (double)j;
+        while (left < n - 1 && xv >= t[left + 1]) ++left;
+        double h[4], hh[4];
+        h[0] = 1.0;
+        for (int q = 1; q <= k; ++q) {
+            memcpy(hh, h, q * sizeof(double));
+            h[0] = 0.0;
+            for (int m = 1; m <= q; ++m) {
+                const int ind = left + m;
+                const double xb = t[ind], xa = t[ind - q];
+                if (xb == xa) { h[m] = 0.0; continue; }
+                const double w = hh[m - 1] / (xb - xa);
+                h[m - 1] += w * (xb - xv);
+                h[m] = w * (xv - xa);
+            }
+        }
+        for (int a = 0; a <= k; ++a) { const int clmn = left - k + a; ab(kl + ku + j - clmn, clmn) = h[a]; }
+    }
+    std::vector<double> b(y, y + n);
+    std::vector<int> ipiv(n);
+    int ju = 0;
+    for (int j = 0; j < n; ++j) {                       // dgbtf2
+        const int km = std::min(kl, n - 1 - j);
+        int jp = 0;
+        double mx = fabs(ab(kv, j));
+        for (int i = 1; i <= km; ++i) if (fabs(ab(kv + i, j)) > mx) { mx = fabs(ab(kv + i, j)); jp = i; }
+        ipiv[j] = jp + j;
+        if (ab(kv + jp, j) == 0.0) continue;            // singular column: cannot happen for distinct knots
+        ju = std::max(ju, std::min(j + ku + jp, n - 1));
+        if (jp != 0) for (int q = 0; q <= ju - j; ++q) std::swap(ab(kv + jp - q, j + q), ab(kv - q, j + q));
+        if (km > 0) {
+            const double r = 1.0 / ab(kv, j);
+            for (int i = 1; i <= km; ++i) ab(kv + i, j) *= r;
+            for (int q = 1; q <= ju - j; ++q) {
+                const double yj = ab(kv - q, j + q);
+                if (yj != 0.0) { const double temp = -yj; for (int i = 1; i <= km; ++i) ab(kv - q + i, j + q) = fma(ab(kv + i, j), temp, ab(kv - q + i, j + q)); }
+            }
+        }
+    }
+    for (int j = 0; j < n - 1; ++j) {                   // dgbtrs, L
+        const int lm = std::min(kl, n - 1 - j);
+        if (ipiv[j] != j) std::swap(b[ipiv[j]], b[j]);
+        const double temp = -b[j];
+        for (int i = 1; i <= lm; ++i) b[j + i] = fma(ab(kv + i, j), temp, b[j + i]);
+    }
+    for (int j = n - 1; j >= 0; --j) {                  // dtbsv, U
+        if (b[j] != 0.0) {
+            b[j] = b[j] / ab(kv, j);
+            const double temp = b[j];
+            for (int i = j - 1; i >= std::max(0, j - kv); --i) b[i] = fma(-temp, ab(kv + i - j, j), b[i]);
+        }
+    }
+    memcpy(c_out, b.data(), (size_t)n * 8);
+}
+
+// BSpline.__call__ of that representation at one point (`_bspl.evaluate_spline` -> `find_interval`, `_deBoor_D`, k = 3, nu = 0), in its
+// operation order; interp1d(bounds_error=False, fill_value=0.0) semantics outside [0, n-1] are the caller's.
+double scipy_bspline_eval(const double* t, const double* c, int n, double x) {
+    const int k = 3;
+    int ell = k;
+    while (x >= t[ell + 1] && ell + 1 != n) ++ell;
+    double hh[4], h[4];
+    h[0] = 1.0;
+    for (int j = 1; j <= k; ++j) {
+        memcpy(hh, h, j * sizeof(double));
+        h[0] = 0.0;
+        for (int q = 1; q <= j; ++q) {
+            const int ind = ell + q;
+            const double xb = t[ind], xa = t[ind - j];
+            if (xb == xa) { h[q] = 0.0; continue; }
+            const double w = hh[q - 1] / (xb - xa);
+            h[q - 1] += w * (xb - x);
+            h[q] = w * (x - xa);
+        }
+    }
+    double out = 0.0;
+    for (int a = 0; a <= k; ++a) out += c[ell + a - k] * h[a];
+    return out;
+}
+
+int ensure_scipy_bspline(lbg_ctx* c) {
+    if (c->cl_bspl_gen == c->cl_gen && !c->cl_bspl_t.empty()) return LBG_OK;
+    const int n = c->n_ell;
+    if (n < 6 || c->cl_host.size() != (size_t)8 * n) { set_error("scipy-order spline needs the host copy of at least 6 knots"); return LBG_ESTATE; }
+    c->cl_bspl_t.assign((size_t)n + 4, 0.0);
+    c->cl_bspl_c.assign((size_t)8 * n, 0.0);
+    std::vector<std::future<void>> jobs;
+    for (int s = 0; s < 8; ++s)
+        jobs.push_back(std::async(std::launch::async, [c, n, s] {
+            scipy_notaknot_cubic(n, c->cl_host.data() + (size_t)s * n, s == 0 ? c->cl_bspl_t.data() : nullptr, c->cl_bspl_c.data() + (size_t)s * n);
+        }));
+    for (auto& j : jobs) j.get();
+    c->cl_bspl_gen = c->cl_gen;
+    return LBG_OK;
 }
 
 __global__ void eval_cl_kernel(const ClRow* __restrict__ rows, int n_ell, int col, int n,
@@ -102,6 +216,7 @@ extern "C" int lbg_ctx_create_lane(int device, int lane, lbg_ctx** out) {
     LBG_CUDA(cudaSetDevice(device));
     lbg_ctx* c = new lbg_ctx();
     c->device = device;
+    c->lane = lane;
     LBG_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
     // lane 0 gets the device's highest stream priority, any other lane the lowest: when both lanes have CTAs pending, the short
     // lane-0 kernels (Limber, covariance) are dispatched first as SM slots free up instead of waiting for the whole N0 grid
@@ -116,15 +231,18 @@ extern "C" int lbg_ctx_create_lane(int device, int lane, lbg_ctx** out) {
     return LBG_OK;
 }
 
+void lbg_n0_release(lbg_ctx* c);   // n0.cu
+
 extern "C" int lbg_ctx_destroy(lbg_ctx* c) {
     if (!c) return LBG_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (DevBuf* b : {&c->cl_rows, &c->cl_soa, &c->cl_pairs, &c->cl_poly, &c->n0_L, &c->n0_utab, &c->n0_phi, &c->n0_partial, &c->n0_out, &c->n0_rowflag, &c->n0_G,
+    lbg_n0_release(c);
+    for (DevBuf* b : {&c->cl_rows, &c->cl_soa, &c->cl_poly, &c->n0_L, &c->n0_utab, &c->n0_partial, &c->n0_out, &c->n0_plan_dev,
                       &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->pk_lnk, &c->pk_plin, &c->pk_pnl, &c->pk_rdk})
         b->release();
     for (DevBuf& b : c->pk_store) b.release();
-    c->pin_in.release(); c->pin_out.release();
+    c->pin_in.release(); c->pin_out.release(); c->pin_n0.release(); c->pin_n0_out.release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -178,9 +296,20 @@ extern "C" int lbg_upload_cl_tables(lbg_ctx* c, int n_ell, const double* lensed,
     LBG_REQUIRE(c && lensed && unlensed, "lbg_upload_cl_tables: NULL argument");
     LBG_REQUIRE(n_ell >= 4, "lbg_upload_cl_tables: need at least 4 knots, got %d", n_ell);
     std::lock_guard<std::mutex> g(c->mu);
+    if (c->n0_pending) { set_error("lbg_upload_cl_tables: an N0 call is pending on this context"); return LBG_ESTATE; }
     LBG_CUDA(cudaSetDevice(c->device));
     // input order TT,EE,BB,TE (prep_camb.py:84) -> row order TT,TE,EE,BB
     const int src_of_col[4] = {0, 3, 1, 2};
+    // A forecast loop hands over the same tables call after call (only beam / noise / L change): compare with the resident copy,
+    // value for value, and keep the splines when nothing changed (the whole input is still read once per call).
+    if (c->n_ell == n_ell && c->cl_host.size() == (size_t)8 * n_ell) {
+        bool same = true;
+        for (int which = 0; which < 2 && same; ++which)
+            for (int col = 0; col < 4 && same; ++col)
+                same = !memcmp(c->cl_host.data() + (size_t)(which * 4 + col) * n_ell,
+                               (which ? lensed : unlensed) + (size_t)src_of_col[col] * n_ell, (size_t)n_ell * 8);
+        if (same) return LBG_OK;
+    }
     std::vector<ClRow> rows(n_ell + 2);
     // the eight spline solves are independent sequential recurrences (0.1 ms each at 10^4 knots): one host thread per spectrum,
     // each writing its coefficients straight into the spectrum-major table the N0 main kernel reads (neighbouring lanes =
@@ -208,6 +337,11 @@ extern "C" int lbg_upload_cl_tables(lbg_ctx* c, int n_ell, const double* lensed,
     c->n_ell = n_ell;
     c->ub_zero = true;
     for (int r = 0; r < n_ell; ++r) c->ub_zero = c->ub_zero && unlensed[(size_t)2 * n_ell + r] == 0.0;
+    c->cl_host.resize((size_t)8 * n_ell);
+    for (int which = 0; which < 2; ++which)
+        for (int col = 0; col < 4; ++col)
+            memcpy(c->cl_host.data() + (size_t)(which * 4 + col) * n_ell, (which ? lensed : unlensed) + (size_t)src_of_col[col] * n_ell, (size_t)n_ell * 8);
+    ++c->cl_gen;
     return LBG_OK;
 }
 
@@ -249,6 +383,18 @@ extern "C" int lbg_eval_spline(lbg_ctx* c, int n_knots, const double* y, int n, 
     t.launched();
     LBG_CUDA(cudaMemcpyAsync(out, c->s1.p, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
     return t.finish();
+}
+
+// Host-only (no GPU): scipy `interp1d(arange(n_knots), y, kind='cubic', bounds_error=False, fill_value=0.0)(x)` in scipy's own
+// operation order (LAPACK-order not-a-knot solve + de Boor evaluation): bit-identical values, for the places where the reference's
+// result hangs on them.
+extern "C" int lbg_scipy_cubic_eval_host(int n_knots, const double* y, int n, const double* x, double* out) {
+    LBG_REQUIRE(y && x && out && n_knots >= 6 && n >= 0, "lbg_scipy_cubic_eval_host: bad argument");
+    std::vector<double> t((size_t)n_knots + 4), cf((size_t)n_knots);
+    scipy_notaknot_cubic(n_knots, y, t.data(), cf.data());
+    const double xmax = (double)(n_knots - 1);
+    for (int i = 0; i < n; ++i) out[i] = (x[i] >= 0.0 && x[i] <= xmax) ? scipy_bspline_eval(t.data(), cf.data(), n_knots, x[i]) : 0.0;
+    return LBG_OK;
 }
 
 // Host-only helper (no GPU needed): the n_knots+2 cardinal B-spline coefficients c[-1..n_knots] the kernels use.

@@ -234,6 +234,62 @@ __global__ void pk_eval_kernel(int n, int n_k, const double* __restrict__ ks, co
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < n) out[t] = interp_k(ks, prow_ptr, n_k, x[t], oob);
 }
+
+// ---- fused forecast spectra (lbg_forecast_spectra) ---------------------------------------------------------------------------
+// Per-node Limber weights of one galaxy sample on one z grid, built on the device from the sampled p(z), b(z):
+//   sliced_pz.py:4-27   p^ = p / norm, zero outside [zmin, zmax], then divided by sum(p^) * dz
+//   kind 0 (C_gg)       Cgg.py:53-68   w = simps_w * (H/c) p^ p^ / chi^2 * b b / h
+//   kind 1 (C_kg)       Ckg.py:42-57   w = simps_w * W_kappa p^ / chi^2 * b / h^2
+// One block per (sample, kind); the sum over the grid is a fixed-order block reduction.
+struct WeightGrid { int n; const double *z, *chi, *fac, *w, *p, *b; double* out; double dz; };
+
+__global__ void __launch_bounds__(256)
+forecast_weights_kernel(WeightGrid gg, WeightGrid kg, const double* __restrict__ norm, double zmin, double zmax, double h100) {
+    __shared__ double sm[256];
+    const int s = blockIdx.x, kind = blockIdx.y;
+    const WeightGrid G = kind == 0 ? gg : kg;
+    const double* p = G.p + (size_t)s * G.n;
+    const double* b = G.b + (size_t)s * G.n;
+    const double nrm = norm[s];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < G.n; i += 256) {
+        const double z = G.z[i];
+        double v = p[i] / nrm;
+        if (z < zmin || z > zmax) v = 0.0;
+        acc += v;
+    }
+    sm[threadIdx.x] = acc;
+    __syncthreads();
+    for (int hh = 128; hh > 0; hh >>= 1) {
+        if (threadIdx.x < hh) sm[threadIdx.x] += sm[threadIdx.x + hh];
+        __syncthreads();
+    }
+    const double den = sm[0] * G.dz;
+    for (int i = threadIdx.x; i < G.n; i += 256) {
+        const double z = G.z[i], chi = G.chi[i];
+        double v = p[i] / nrm;
+        if (z < zmin || z > zmax) v = 0.0;
+        v = v / den;
+        double wv;
+        if (kind == 0) wv = (((G.w[i] * (((G.fac[i] * v) * v) / (chi * chi))) * b[i]) * b[i]) / h100;
+        else           wv = ((G.w[i] * ((G.fac[i] * v) / (chi * chi))) * b[i]) / (h100 * h100);
+        G.out[(size_t)s * G.n + i] = wv;
+    }
+}
+
+// live[bb][z] = some batch entry of batch block bb weights z node z (limber_kernel skips the others)
+__global__ void limber_live_kernel(int n_batch, int nbk, int n_z, const double* __restrict__ weight, unsigned char* __restrict__ live) {
+    const int z = blockIdx.x * blockDim.x + threadIdx.x, bb = blockIdx.y;
+    if (z >= n_z) return;
+    bool any = false;
+    for (int q = bb * nbk; q < min(n_batch, (bb + 1) * nbk); ++q) any = any || (weight[(size_t)q * n_z + z] != 0.0);
+    live[(size_t)bb * n_z + z] = any;
+}
+
+__global__ void iota_kernel(int n, int* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = i;
+}
 }  // namespace lbg
 
 using namespace lbg;
@@ -325,10 +381,10 @@ extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell,
                           double* out_cl /*[n_batch][n_ell]*/) {
     LBG_REQUIRE(c && ell && chi && weight && prow && out_cl, "lbg_limber: NULL argument");
     LBG_REQUIRE(n_batch > 0 && n_ell >= 0 && n_z > 0, "lbg_limber: bad sizes");
+    std::lock_guard<std::mutex> g(c->mu);     // the table state is read under the lock: another thread may be swapping slots
     if (c->pnl_nz <= 0) { set_error("lbg_limber: call lbg_pk_build_table first"); return LBG_ESTATE; }
     for (int i = 0; i < n_z; ++i) LBG_REQUIRE(prow[i] >= 0 && prow[i] < c->pnl_nz, "lbg_limber: prow[%d]=%d outside the %d-row table", i, prow[i], c->pnl_nz);
     if (n_ell == 0) return LBG_OK;
-    std::lock_guard<std::mutex> g(c->mu);
     LBG_CUDA(cudaSetDevice(c->device));
     const size_t bw = (size_t)n_batch * n_z * 8, bo = (size_t)n_batch * n_ell * 8;
     const int nbk = n_batch == 1 ? 1 : LIMBER_BT, n_bb = (n_batch + nbk - 1) / nbk;
@@ -347,7 +403,9 @@ extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell,
     for (int i = 0; i < n_z; ++i) { zc[i] = chi[i]; zc[(size_t)n_z + i] = 1.0 / chi[i]; }
     memcpy(hin + o_w, weight, bw);
     memcpy(hin + o_prow, prow, (size_t)n_z * 4);
-    unsigned char* lv = hin + o_live;                         // a z node none of a block's batch entries weights is skipped by that block
+    // a z node none of a block's batch entries weights is skipped by that block.  Deliberate deviation from the reference's
+    // simps(prefactor * result): a NaN / Inf P(k,z) row under an all-zero weight gives 0 here, NaN there
+    unsigned char* lv = hin + o_live;
     for (int bb = 0; bb < n_bb; ++bb)
         for (int i = 0; i < n_z; ++i) {
             bool any = false;
@@ -382,10 +440,10 @@ extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell,
 
 extern "C" int lbg_pk_eval(lbg_ctx* c, int row, int n, const double* x, int oob, double* out) {
     LBG_REQUIRE(c && x && out, "lbg_pk_eval: NULL argument");
+    std::lock_guard<std::mutex> g(c->mu);
     if (c->pnl_nz <= 0) { set_error("lbg_pk_eval: call lbg_pk_build_table first"); return LBG_ESTATE; }
     LBG_REQUIRE(row >= 0 && row < c->pnl_nz, "lbg_pk_eval: row %d outside the %d-row table", row, c->pnl_nz);
     if (n <= 0) return LBG_OK;
-    std::lock_guard<std::mutex> g(c->mu);
     LBG_CUDA(cudaSetDevice(c->device));
     if (c->s0.reserve((size_t)n * 8) || c->s1.reserve((size_t)n * 8)) return LBG_ENOMEM;
     LBG_CUDA(cudaMemcpyAsync(c->s0.p, x, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
@@ -415,5 +473,107 @@ extern "C" int lbg_pk_upload_rows(lbg_ctx* c, int n_k, const double* k, int n_ro
     c->n_k = n_k;
     c->drop_pk_tables();
     c->pnl_nz = n_rows;
+    return LBG_OK;
+}
+
+
+// One Limber sum on device-resident inputs (the body of lbg_limber without its copies); weights / live / partial are the caller's.
+static int limber_launch_dev(lbg_ctx* c, cudaStream_t st, int n_batch, int n_ell, const double* d_ell, int n_z, const double* d_zc,
+                             const double* d_w, unsigned char* d_live, const int* d_prow, const double* d_table, int oob,
+                             double* d_partial, double* d_out, int* launches) {
+    const int nbk = n_batch == 1 ? 1 : LIMBER_BT, n_bb = (n_batch + nbk - 1) / nbk;
+    const int n_split = limber_splits(n_z), z_per_split = (n_z + n_split - 1) / n_split;
+    limber_live_kernel<<<dim3((n_z + 127) / 128, n_bb), 128, 0, st>>>(n_batch, nbk, n_z, d_w, d_live);
+    double* part = n_split > 1 ? d_partial : d_out;
+    const dim3 grid((n_ell + 127) / 128, n_bb, n_split);
+#define LBG_LIMBER(NB) limber_kernel<NB><<<grid, 128, 0, st>>>(n_batch, n_ell, n_z, c->n_k, z_per_split, d_ell, d_zc, d_w, d_live, d_prow, \
+        c->pk_lnk.as<double>(), c->pk_rdk.as<double>(), d_table, oob, part)
+    if (nbk == 1) LBG_LIMBER(1); else LBG_LIMBER(LIMBER_BT);
+#undef LBG_LIMBER
+    *launches += 2;
+    if (n_split > 1) {
+        const size_t n = (size_t)n_batch * n_ell;
+        limber_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, n_split, part, d_out);
+        ++*launches;
+    }
+    return LBG_OK;
+}
+
+extern "C" int lbg_forecast_spectra(lbg_ctx* c, int n_ell, const double* ell, double zmin, double zmax, double h100,
+                                    int n_gg, const double* z_gg, const double* chi_gg, const double* hc_gg, const double* w_gg, double dz_gg, int slot_gg,
+                                    int n_kg, const double* z_kg, const double* chi_kg, const double* wk_kg, const double* w_kg, double dz_kg, int slot_kg,
+                                    int n_kk, const double* chi_kk, const double* weight_kk, int slot_kk,
+                                    int n_s, const double* pz_gg, const double* bz_gg, const double* pz_kg, const double* bz_kg, const double* norm,
+                                    double* out_cgg, double* out_ckg, double* out_ckk) {
+    LBG_REQUIRE(c && ell && z_gg && chi_gg && hc_gg && w_gg && z_kg && chi_kg && wk_kg && w_kg && pz_gg && bz_gg && pz_kg && bz_kg && norm &&
+                out_cgg && out_ckg, "lbg_forecast_spectra: NULL argument");
+    LBG_REQUIRE(n_ell >= 0 && n_gg > 0 && n_kg > 0 && n_s > 0 && n_kk >= 0, "lbg_forecast_spectra: bad sizes");
+    LBG_REQUIRE(n_kk == 0 || (chi_kk && weight_kk && out_ckk), "lbg_forecast_spectra: C_kk grid given without its arrays / output");
+    LBG_REQUIRE(h100 > 0 && dz_gg > 0 && dz_kg > 0, "lbg_forecast_spectra: h100 and the grid spacings must be positive");
+    if (n_ell == 0) return LBG_OK;
+    std::lock_guard<std::mutex> g(c->mu);
+    if (c->n_k <= 0) { set_error("lbg_forecast_spectra: call lbg_upload_pk_linear first"); return LBG_ESTATE; }
+    const int slots[3] = {slot_gg, slot_kg, slot_kk}, want[3] = {n_gg, n_kg, n_kk};
+    const double* table[3] = {nullptr, nullptr, nullptr};
+    for (int q = 0; q < 3; ++q) {
+        if (want[q] == 0) continue;
+        LBG_REQUIRE(slots[q] >= 0 && slots[q] < lbg_ctx::PK_SLOTS, "lbg_forecast_spectra: table slot %d outside [0, %d)", slots[q], lbg_ctx::PK_SLOTS);
+        const bool cur = slots[q] == c->pk_cur;
+        const int rows = cur ? c->pnl_nz : c->store_nz[slots[q]];
+        if (rows != want[q]) { set_error("lbg_forecast_spectra: table slot %d holds %d rows, the grid has %d nodes (build it with lbg_pk_build_table)", slots[q], rows, want[q]); return LBG_ESTATE; }
+        table[q] = cur ? c->pk_pnl.as<double>() : c->pk_store[slots[q]].as<double>();
+    }
+    LBG_CUDA(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    // ---- one pinned staging block in ------------------------------------------------------------------------------------------
+    const size_t n_in = (size_t)n_ell + 2 * ((size_t)n_gg + n_kg + n_kk) + 3 * (size_t)n_gg + 3 * (size_t)n_kg + n_kk +
+                        2 * (size_t)n_s * ((size_t)n_gg + n_kg) + n_s;
+    const int n_zmax = std::max(n_gg, std::max(n_kg, n_kk));
+    const int n_bb = (n_s + LIMBER_BT - 1) / LIMBER_BT;
+    const size_t n_out = (size_t)(2 * n_s + (n_kk ? 1 : 0)) * n_ell;
+    const size_t n_w = (size_t)n_s * ((size_t)n_gg + n_kg);
+    const size_t part_sz = (size_t)LIMBER_SMAX * std::max(n_s, 1) * n_ell;
+    if (c->s0.reserve(n_in * 8 + 64) || c->pin_in.reserve(n_in * 8 + 64) || c->s4.reserve(n_out * 8 + 64) || c->pin_out.reserve(n_out * 8 + 64) ||
+        c->s1.reserve(n_w * 8 + 64) || c->s2.reserve((size_t)n_bb * n_zmax + 64) || c->s3.reserve((size_t)n_zmax * 4 + 64) || c->s5.reserve(part_sz * 8))
+        return LBG_ENOMEM;
+    double* h = c->pin_in.as<double>();
+    size_t o = 0;
+    auto put = [&](const double* src, size_t n) { size_t at = o; if (n) memcpy(h + o, src, n * 8); o += n; return at; };
+    auto put_zc = [&](const double* chi, int n) { size_t at = o; for (int i = 0; i < n; ++i) { h[o + i] = chi[i]; h[o + n + i] = 1.0 / chi[i]; } o += 2 * (size_t)n; return at; };
+    const size_t o_ell = put(ell, n_ell);
+    const size_t o_zc_gg = put_zc(chi_gg, n_gg), o_zc_kg = put_zc(chi_kg, n_kg), o_zc_kk = put_zc(chi_kk, n_kk);
+    const size_t o_hc = put(hc_gg, n_gg), o_wgg = put(w_gg, n_gg), o_zgg = put(z_gg, n_gg);
+    const size_t o_wk = put(wk_kg, n_kg), o_wkg = put(w_kg, n_kg), o_zkg = put(z_kg, n_kg);
+    const size_t o_wkk = put(weight_kk, n_kk);
+    const size_t o_pgg = put(pz_gg, (size_t)n_s * n_gg), o_bgg = put(bz_gg, (size_t)n_s * n_gg);
+    const size_t o_pkg = put(pz_kg, (size_t)n_s * n_kg), o_bkg = put(bz_kg, (size_t)n_s * n_kg);
+    const size_t o_norm = put(norm, n_s);
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, h, o * 8, cudaMemcpyHostToDevice, st));
+    const double* d = c->s0.as<double>();
+    double* d_wgg = c->s1.as<double>();
+    double* d_wkg = d_wgg + (size_t)n_s * n_gg;
+    double* d_out = c->s4.as<double>();
+    KernelTimer t(c);
+    int launches = 0;
+    iota_kernel<<<(n_zmax + 255) / 256, 256, 0, st>>>(n_zmax, c->s3.as<int>());
+    WeightGrid G0{n_gg, d + o_zgg, d + o_zc_gg, d + o_hc, d + o_wgg, d + o_pgg, d + o_bgg, d_wgg, dz_gg};
+    WeightGrid G1{n_kg, d + o_zkg, d + o_zc_kg, d + o_wk, d + o_wkg, d + o_pkg, d + o_bkg, d_wkg, dz_kg};
+    forecast_weights_kernel<<<dim3(n_s, 2), 256, 0, st>>>(G0, G1, d + o_norm, zmin, zmax, h100);
+    launches += 2;
+    limber_launch_dev(c, st, n_s, n_ell, d + o_ell, n_gg, d + o_zc_gg, d_wgg, c->s2.as<unsigned char>(), c->s3.as<int>(), table[0], 0,
+                      c->s5.as<double>(), d_out, &launches);
+    limber_launch_dev(c, st, n_s, n_ell, d + o_ell, n_kg, d + o_zc_kg, d_wkg, c->s2.as<unsigned char>(), c->s3.as<int>(), table[1], 0,
+                      c->s5.as<double>(), d_out + (size_t)n_s * n_ell, &launches);
+    if (n_kk)
+        limber_launch_dev(c, st, 1, n_ell, d + o_ell, n_kk, d + o_zc_kk, d + o_wkk, c->s2.as<unsigned char>(), c->s3.as<int>(), table[2], 0,
+                          c->s5.as<double>(), d_out + (size_t)2 * n_s * n_ell, &launches);
+    t.launched(launches);
+    LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, d_out, n_out * 8, cudaMemcpyDeviceToHost, st));
+    const int rc = t.finish();
+    if (rc) return rc;
+    const double* r = c->pin_out.as<double>();
+    memcpy(out_cgg, r, (size_t)n_s * n_ell * 8);
+    memcpy(out_ckg, r + (size_t)n_s * n_ell, (size_t)n_s * n_ell * 8);
+    if (n_kk) memcpy(out_ckk, r + (size_t)2 * n_s * n_ell, (size_t)n_ell * 8);
     return LBG_OK;
 }

@@ -1,12 +1,20 @@
 // n0.cu -- Hu-Okamoto flat-sky N0 reconstruction noise, root flavour (replaces cmb/Nkk.py:54-172).
 //
-// Work decomposition (B200: 148 SMs, FP64-pipe bound, tables L2-resident):
-//   thread  <-> one (L, phi_j) pair; it marches over a chunk of the l1 = |u| grid.
-//   Every quantity that depends on l1 only (unlensed/total spectra at u, their reciprocals, weight*l1)
-//   is precomputed once per noise configuration into a 128-byte "u row" that the whole block reads
-//   at the same address (broadcast).  The v-side spectra are eight cubic splines evaluated from a
-//   knot-major table of uniform B-spline coefficients (64 B per knot, four consecutive knots per node).
-//   Partial sums go to a scratch buffer and are reduced in a fixed order (deterministic, no atomics).
+// Work decomposition (B200: 148 SMs, FP64 pipe + L1 data pipe bound, tables L2-resident):
+//   thread <-> one |u| = l1 row of one L; it loops over the phi nodes.  CTA = 128 consecutive rows, grid = n_L x 79 row blocks.
+//   Everything that depends on l1 only (spectra at u, totals, reciprocals, weight * l1) is computed once per call into a
+//   128-byte "u row" (n0_uside_kernel) and lives in registers for the whole phi loop.  The v-side spectra are cubic splines
+//   evaluated by Horner from a per-call table of per-interval monomial coefficients with the detector noise folded in
+//   (n0_poly_table_kernel).  Partial sums go to a scratch buffer and are reduced in a fixed order (deterministic, no atomics).
+//
+// Two integrand kernels, chosen by the inputs and reported by lbg_n0_last_path():
+//   n0_rows5_kernel (path 5)  phi grid folded onto mirror pairs: |v|^2 is monotone in the node index, so every cut of
+//                             prep_lmaxmask (cmb/Nkk.py:13-26) is an index RANGE found once per row; masked nodes are never visited.
+//   n0_rows3_kernel (path 3)  the generic kernel: per-node masks.  Taken for an unfolded phi grid, for tables that end inside the
+//                             reachable |v| range (the spline's fill value 0 takes over there, prep_camb.py:88-89), for beams so wide
+//                             that the folded-noise fit leaves its 2e-12 bound (then exp() per node), or on request (fold_phi = 2).
+// Both leave the nodes within 4e-6 of a cut in |v|^2 to a second pass that evaluates them with the reference's own operation order
+// (n0_node), and both hand the few rows whose u side needs per-node treatment to n0_special_kernel.
 #include "common.cuh"
 #include <cmath>
 
@@ -22,14 +30,16 @@ struct __align__(128) URow {
 };
 
 struct N0Params {
-    int n_L, n_phi, n_l1, n_chunk, rows_per_chunk, n_ell;
-    int soa_stride;               // > 0: `rows` of n0_node is the spectrum-major table double[8][soa_stride]
+    int n_L, n_phi, n_l1, n_ell, n_rb;
+    int n_int;                    // knot intervals of the per-call polynomial table (covers every reachable |v|)
+    int soa_stride;               // the spectrum-major B-spline table is double[8][soa_stride]
+    int lane;                     // which block of c_cw holds this call's (cos phi_j, w_j)
     unsigned terms;
     double nT, nP, a;             // N_TT(l) = nT exp(a l (l+1)), N_EE = N_BB = nP exp(.)  (cmb/DetectorNoise.py:22-26)
     double lmax_T, lmax_P, lmin_v;
     double ebfac;
     int fold;                     // phi nodes are mirror pairs: phi[] holds [6][n_phi] cos,sin,w,cos_m,sin_m,frac_j
-    unsigned near_lo[3], near_span[3];   // hi-word windows of |v|^2 around lmin_v^2, lmax_T^2, lmax_P^2
+    unsigned near_lo[4], near_span[4];   // hi-word windows of |v|^2 around lmin_v^2, lmax_T^2, lmax_P^2, (last knot)^2
 };
 
 __device__ __forceinline__ void bspline_weights(double t, double& w0, double& w1, double& w2, double& w3) {
@@ -77,10 +87,11 @@ __global__ void n0_uside_kernel(N0Params P, const double* __restrict__ l1, const
 
 struct UVals { double uT, uX, uE, uB, T1, E1, X1, rT1h, rE1h, rE1, rB1h; };
 
-// One integrand node (cmb/Nkk.py:66-162) for |u| = l at angle (c, s) = (cos phi, sin phi) and lensing multipole L.
-// actT / actP: the |u| side of prep_lmaxmask (cmb/Nkk.py:17,20) for the 3000 / 5000 families; wl = weight * l.
+// One integrand node (cmb/Nkk.py:66-162) for |u| = l at angle (c, s) = (cos phi, sin phi) and lensing multipole L, in the
+// reference's operation order.  actT / actP: the |u| side of prep_lmaxmask (cmb/Nkk.py:17,20) for the 3000 / 5000 families;
+// wl = weight * l.  Returns whether the node passed a mask (it then counts as an unmasked node).
 template <bool SOA = false>
-__device__ __forceinline__ void n0_node(const N0Params& P, const ClRow* __restrict__ rows, double L, double l, double c, double s,
+__device__ __forceinline__ bool n0_node(const N0Params& P, const ClRow* __restrict__ rows, double L, double l, double c, double s,
                                         const UVals& u, bool actT, bool actP, double wl, bool mirror, double cm, double sm_, double fj,
                                         double& aTT, double& aTE, double& aEE, double& aEB, double& aBB) {
     // geometry exactly as cmb/Nkk.py:66-72,80 (no FMA contraction: |v| decides the masks)
@@ -111,7 +122,7 @@ __device__ __forceinline__ void n0_node(const N0Params& P, const ClRow* __restri
             okP = okP || okPm;
         }
     }
-    if (!(okT || okP)) return;
+    if (!(okT || okP)) return false;
 
     const double Lx = ux + vx;                     // cmb/Nkk.py:82
     const double dLu = ux * Lx, dLv = vx * Lx;     // :84-85
@@ -186,154 +197,14 @@ __device__ __forceinline__ void n0_node(const N0Params& P, const ClRow* __restri
             aBB = fma(wP, fa * fa * u.rB1h / B2, aBB);
         }
     }
+    return true;
 }
 
-// Main kernel: regular rows (flag bit4 clear), phi nodes possibly folded onto mirror pairs.
-__global__ void __launch_bounds__(128)
-n0_kernel(N0Params P, const double* __restrict__ Ls, const double* __restrict__ phi /*[6][n_phi]: cos,sin,w,cos_m,sin_m,frac_j*/,
-          const URow* __restrict__ utab, const ClRow* __restrict__ rows, double* __restrict__ partial) {
-    const int npairs = P.n_L * P.n_phi;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool valid = p < npairs;
-    const int pp = valid ? p : npairs - 1;
-    const int iL = pp / P.n_phi, j = pp - iL * P.n_phi;
-    const double L = Ls[iL], c = phi[j], s = phi[P.n_phi + j];
-    const int r0 = blockIdx.y * P.rows_per_chunk;
-    const int r1 = min(P.n_l1, r0 + P.rows_per_chunk);
-    const bool fold = P.fold != 0;
-    const double cm = phi[3 * P.n_phi + j], sm_ = phi[4 * P.n_phi + j], fj = phi[5 * P.n_phi + j];
-    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
-
-    for (int r = r0; r < r1; ++r) {
-        const double4* up = reinterpret_cast<const double4*>(utab + r);
-        const double4 q3 = ld4(up + 3);                // rB1h, flags, nT(l), nP(l)
-        const int fl = (int)q3.y;
-        if (!(fl & 5) || (fl & 16)) continue;          // block-uniform: masked row, or handled by n0_special_kernel
-        const double4 q0 = ld4(up);                    // l, wl, uT, uX
-        const double4 q1 = ld4(up + 1);                // uE, uB, T1, E1
-        const double4 q2 = ld4(up + 2);                // X1, rT1h, rE1h, rE1
-        UVals u;
-        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
-        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
-        n0_node(P, rows, L, q0.x, c, s, u, fl & 1, fl & 4, q0.y, fold, cm, sm_, fj, aTT, aTE, aEE, aEB, aBB);
-    }
-    if (valid) {
-        const double wphi = phi[2 * P.n_phi + j];
-        const size_t stride = (size_t)P.n_chunk * npairs;
-        const size_t o = (size_t)blockIdx.y * npairs + p;
-        partial[o] = aTT * wphi;
-        partial[stride + o] = aTE * wphi;
-        partial[2 * stride + o] = aEE * wphi;
-        partial[3 * stride + o] = aEB * wphi;
-        partial[4 * stride + o] = aBB * wphi;
-    }
-}
-
-// ---- "rows" variant: thread <-> one l1 row (consecutive lanes = consecutive |u|), loop over the phi nodes ------------
-// The u-side values live in registers for the whole phi loop (no u-row traffic), cos/sin/weights of the phi nodes come
-// from constant memory through the uniform datapath, and the four B-spline rows a warp gathers at |v| lie within a few
-// cache lines because |v| moves by at most 0.5 between neighbouring lanes.
-#define LBG_MAX_PHI_CONST 1024
-__constant__ double c_phi[6 * LBG_MAX_PHI_CONST];   // [6][n_phi]: cos, sin, w, cos_m, sin_m, frac_j
-
-#ifndef LBG_ROWS_MINB
-#define LBG_ROWS_MINB 4
-#endif
-__global__ void __launch_bounds__(128, LBG_ROWS_MINB)
-n0_rows_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const ClRow* __restrict__ rows,
-               double* __restrict__ partial /*[5][n_L][n_rb]*/) {
-    __shared__ double red[5][4];
-    const int r = blockIdx.x * 128 + threadIdx.x;
-    const int iL = blockIdx.y, n_rb = gridDim.x;
-    const double L = Ls[iL];
-    const bool fold = P.fold != 0;
-    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
-    int fl = 0;
-    double l = 1.0, wl = 0.0;
-    UVals u = {};
-    if (r < P.n_l1) {
-        const double4* up = reinterpret_cast<const double4*>(utab + r);
-        const double4 q0 = ld4(up), q1 = ld4(up + 1), q2 = ld4(up + 2), q3 = ld4(up + 3);
-        fl = (int)q3.y;
-        l = q0.x; wl = q0.y;
-        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
-        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
-    }
-    if ((fl & 5) && !(fl & 16)) {
-        const bool actT = fl & 1, actP = fl & 4;
-        for (int j = 0; j < P.n_phi; ++j) {
-            const double c = c_phi[j], s = c_phi[P.n_phi + j], wj = c_phi[2 * P.n_phi + j];
-            const double cm = c_phi[3 * P.n_phi + j], sm_ = c_phi[4 * P.n_phi + j], fj = c_phi[5 * P.n_phi + j];
-            n0_node<true>(P, rows, L, l, c, s, u, actT, actP, wj, fold, cm, sm_, fj, aTT, aTE, aEE, aEB, aBB);
-        }
-    }
-    double acc[5] = {aTT * wl, aTE * wl, aEE * wl, aEB * wl, aBB * wl};
-#pragma unroll
-    for (int t = 0; t < 5; ++t) {
-        double v = acc[t];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) == 0) red[t][threadIdx.x >> 5] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < 5) {
-        const int t = threadIdx.x;
-        const double v = (red[t][0] + red[t][1]) + (red[t][2] + red[t][3]);
-        partial[((size_t)t * P.n_L + iL) * n_rb + blockIdx.x] = v;
-    }
-}
-
-// One block per L: fixed-order sum of the row-block partials (+ the special rows), then cmb/Nkk.py:169-172.
-__global__ void __launch_bounds__(128)
-n0_rows_reduce_kernel(N0Params P, int n_rb, const double* __restrict__ Ls, const double* __restrict__ partial,
-                      const double* __restrict__ spartial, int n_phi_full, double* __restrict__ out) {
-    __shared__ double sm[5][128];
-    const int iL = blockIdx.x;
-    double acc[5] = {0, 0, 0, 0, 0};
-    for (int b = threadIdx.x; b < n_rb; b += 128) {
-#pragma unroll
-        for (int t = 0; t < 5; ++t) acc[t] += partial[((size_t)t * P.n_L + iL) * n_rb + b];
-    }
-    if (spartial) {
-        const size_t sstride = (size_t)P.n_L * n_phi_full;
-        for (int j = threadIdx.x; j < n_phi_full; j += 128) {
-#pragma unroll
-            for (int t = 0; t < 5; ++t) acc[t] += spartial[t * sstride + (size_t)iL * n_phi_full + j];
-        }
-    }
-#pragma unroll
-    for (int t = 0; t < 5; ++t) sm[t][threadIdx.x] = acc[t];
-    __syncthreads();
-    for (int h = 64; h > 0; h >>= 1) {
-        if (threadIdx.x < h) {
-#pragma unroll
-            for (int t = 0; t < 5; ++t) sm[t][threadIdx.x] += sm[t][threadIdx.x + h];
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        const double L = Ls[iL];
-        double tot = (((sm[0][0] + sm[1][0]) + sm[2][0]) + P.ebfac * sm[3][0]) + sm[4][0];
-        const double twopi = 2.0 * 3.14159265358979323846;
-        double r = tot / (twopi * twopi);
-        r = 1.0 / r;
-        const double pre = L * (L + 1.0) / 2.0;
-        out[iL] = r * (pre * pre);
-        for (int t = 0; t < 5; ++t) out[(size_t)(t + 1) * P.n_L + iL] = sm[t][0];
-    }
-}
-
-// ---- "rows2" variant: the rows decomposition with a restructured node ----------------------------------------------
-// Same integrand, arranged for the FP64 pipe (the limiter once the table gathers are coalesced):
-//  * |v|^2 = l (l - 2 L cos) + L^2 by two FMAs; one rsqrt yields both |v| and 1/|v|^2 (the cos 2phi_uv / sin^2 2phi_uv
-//    denominators are |u|^2 |v|^2);  L.u, L.v, u.v, u x v come from per-(L, phi) products staged in shared memory;
-//  * the four filter denominators (C^TT_tot(v), TE determinant, C^EE_tot(v), C^BB_tot(v)) share ONE reciprocal;
-//  * detector noise at |v| = G[i] exp(a t (2 i + 1 + t)) with G[i] = exp(a i (i + 1)) tabulated per knot and a degree-7
-//    Taylor polynomial in the small remainder (|x| < 0.03, checked on the host; otherwise exp() is called);
-//  * masks are integer tests on the high word of |v|^2.  A node whose |v|^2 lies within 4e-6 of a cut is left to a second
-//    pass that evaluates it with the bit-faithful n0_node (the reference decides those masks on its own rounding).
-// Blocks whose rows all lie above lmax_T skip the temperature estimators and their four splines (DO_T = false).
-struct PhiNode { double A, B, C, w; };     // 2 L cos phi, L cos phi, L sin phi, quadrature weight
+// (cos phi_j, w_j) of the (folded) phi grid, one block per context lane so that the two lanes of a GPU (lbg_ctx_create_lane) may
+// run N0 calls with different grids at the same time.  Read through the uniform datapath: j is warp-uniform.
+#define LBG_MAX_LANES 4
+#define LBG_MAX_PHI 512
+__constant__ double2 c_cw[LBG_MAX_LANES][LBG_MAX_PHI];
 
 __device__ __forceinline__ double rsqrt_fast(double x) {       // MUFU.RSQ64H seed + one third-order step: ~1 ulp, x normal > 0
     double y;
@@ -351,228 +222,45 @@ __device__ __forceinline__ double rcp_fast(double x) {         // MUFU.RCP64H se
     return fma(y, q, y);
 }
 
-template <bool DO_T, bool EXPN>
-__device__ __forceinline__ void n0_fast_node(const N0Params& P, const double* __restrict__ tab, const double* __restrict__ G,
-                                             double L2, double l, double l2, double rl2, const UVals& u, bool actT, bool actP,
-                                             const PhiNode ph, double& aTT, double& aTE, double& aEE, double& aEB) {
-    const double nv2 = fma(l, l - ph.A, L2);
-    const unsigned hi = (unsigned)__double2hiint(nv2);
-    const bool rare = (hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2];
-    const bool vok = !rare && hi > P.near_lo[0];
-    const bool okT = DO_T && actT && vok && hi < P.near_lo[1];
-    const bool okP = actP && vok && hi < P.near_lo[2];
-    if (!__any_sync(0xffffffffu, okT || okP)) return;
-
-    const double y = rsqrt_fast(fmax(nv2, 1e-300));
-    const double nv = nv2 * y;
-    const double dLu = l * ph.B, dLv = L2 - dLu;           // L.u, L.v
-    const double dot = dLu - l2, crs = l * ph.C;           // u.v, |u x v|
-    const double d2 = dot * dot, x2 = crs * crs;
-    const double rden = rl2 * (y * y);                     // 1 / (|u|^2 |v|^2)
-    const double c2 = (d2 - x2) * rden;
-    const double s2sq = fma(-c2, c2, 1.0);
-
-    int i = min((int)nv, P.n_ell - 2);
-    const double fi = (double)i;
-    const double t = nv - fi, um = 1.0 - t;
-    const double t2 = t * t, u2 = um * um;
-    const double w0 = (u2 * (1.0 / 6.0)) * um, w3 = (t2 * (1.0 / 6.0)) * t;
-    const double w1 = fma(t2, fma(0.5, t, -1.0), 2.0 / 3.0), w2 = fma(u2, fma(0.5, um, -1.0), 2.0 / 3.0);
-    const double2* q = reinterpret_cast<const double2*>(tab) + i;   // (c_i, c_{i+1}) pairs, compile-time spectrum stride
-    double vT = 0.0, vX = 0.0, T2 = 1.0, X2 = 0.0, vE, vB, E2, B2;
-    {
-        double2 a, b;
-#define LBG_SPL(k, out) a = __ldg(q + (k) * LBG_PAIR_STRIDE); b = __ldg(q + (k) * LBG_PAIR_STRIDE + 2); \
-                        out = fma(w3, b.y, fma(w2, b.x, fma(w1, a.y, w0 * a.x)))
-        if (DO_T) { LBG_SPL(0, vT); LBG_SPL(1, vX); LBG_SPL(4, T2); LBG_SPL(5, X2); }
-        LBG_SPL(2, vE); LBG_SPL(3, vB); LBG_SPL(6, E2); LBG_SPL(7, B2);
-#undef LBG_SPL
-    }
-    double en;
-    if (EXPN) {
-        en = exp((nv2 + nv) * P.a);
-    } else {
-        const double x = (P.a * t) * fma(2.0, fi, 1.0 + t);
-        double pl = fma(x, 1.0 / 5040.0, 1.0 / 720.0);
-        pl = fma(pl, x, 1.0 / 120.0); pl = fma(pl, x, 1.0 / 24.0); pl = fma(pl, x, 1.0 / 6.0);
-        pl = fma(pl, x, 0.5); pl = fma(pl, x, 1.0); pl = fma(pl, x, 1.0);
-        en = __ldg(G + i) * pl;
-    }
-    if (DO_T) T2 = fma(P.nT, en, T2);
-    E2 = fma(P.nP, en, E2);
-    B2 = fma(P.nP, en, B2);
-
-    // one reciprocal for the four filter denominators
-    double E1T2 = 1.0, xx = 0.0, den = 1.0;
-    if (DO_T) {
-        E1T2 = u.E1 * T2; xx = u.X1 * X2;
-        den = fma(u.T1 * E2, E1T2, -(xx * xx));
-        if (!(P.terms & LBG_TE)) den = 1.0;
-        if (!(P.terms & LBG_TT)) T2 = 1.0;
-    }
-    if (!(P.terms & LBG_EB)) B2 = 1.0;
-    const double p1 = DO_T ? T2 * den : 1.0, p2 = E2 * B2;
-    const double r = rcp_fast(DO_T ? p1 * p2 : p2);
-    const double r34 = DO_T ? r * p1 : r;                  // 1 / (E2 B2)
-    const double rE2 = r34 * B2, rB2 = r34 * E2;
-    const double uEd = u.uE * dLu;
-    if (DO_T) {
-        const double r12 = r * p2;                         // 1 / (T2 den)
-        const double rT2 = r12 * den, rdn = r12 * T2;
-        const double fa = fma(vT, dLv, u.uT * dLu);
-        const double tt = (fa * fa) * (u.rT1h * rT2);
-        const double uXd = u.uX * dLu, vXd = vX * dLv;
-        const double fa_uv = fma(uXd, c2, vXd), fa_vu = fma(vXd, c2, uXd);
-        const double num = fma(E1T2, fa_uv, -(xx * fa_vu));
-        const double te = (fa_uv * num) * rdn;
-        aTT = fma(ph.w, okT ? tt : 0.0, aTT);
-        aTE = fma(ph.w, okT ? te : 0.0, aTE);
-    }
-    const double fe = fma(vE, dLv, uEd) * c2;
-    const double ee = (fe * fe) * (u.rE1h * rE2);
-    const double fb = fma(-vB, dLv, uEd);
-    const double eb = ((fb * fb) * s2sq) * (u.rE1 * rB2);
-    aEE = fma(ph.w, okP ? ee : 0.0, aEE);
-    aEB = fma(ph.w, okP ? eb : 0.0, aEB);
-}
-
-// G[i] = exp(a i (i + 1)) on the integer knots (cmb/DetectorNoise.py:22 without the amplitude).
-// pairs[k][r] = (c_k[r], c_k[r + 1]) for the eight spectra (rows2 kernel): double2[8][LBG_PAIR_STRIDE], zero beyond the table.
-__global__ void n0_pairs_kernel(int n, int stride, const double* __restrict__ soa, double* __restrict__ pairs) {
-    const int r = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
-    if (r >= n || r >= LBG_PAIR_STRIDE) return;
-    pairs[((size_t)k * LBG_PAIR_STRIDE + r) * 2] = soa[(size_t)k * stride + r];
-    pairs[((size_t)k * LBG_PAIR_STRIDE + r) * 2 + 1] = r + 1 < n ? soa[(size_t)k * stride + r + 1] : 0.0;
-}
-
-__global__ void n0_noise_knots_kernel(int n, double a, double* __restrict__ G) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) G[i] = exp(((double)i * ((double)i + 1.0)) * a);
-}
-
-template <bool DO_T, bool EXPN>
-__device__ __forceinline__ void n0_rows2_loop(const N0Params& P, const double* __restrict__ tab, const double* __restrict__ G,
-                                              const PhiNode* __restrict__ sph, double L2, double l, const UVals& u, bool actT, bool actP,
-                                              double& aTT, double& aTE, double& aEE, double& aEB) {
-    const double l2 = l * l, rl2 = 1.0 / l2;
-    int j = 0;
-    for (; j + 1 < P.n_phi; j += 2) {      // two independent nodes per trip: ILP for the FP64 pipe
-        n0_fast_node<DO_T, EXPN>(P, tab, G, L2, l, l2, rl2, u, actT, actP, sph[j], aTT, aTE, aEE, aEB);
-        n0_fast_node<DO_T, EXPN>(P, tab, G, L2, l, l2, rl2, u, actT, actP, sph[j + 1], aTT, aTE, aEE, aEB);
-    }
-    if (j < P.n_phi) n0_fast_node<DO_T, EXPN>(P, tab, G, L2, l, l2, rl2, u, actT, actP, sph[j], aTT, aTE, aEE, aEB);
-}
-
-template <bool EXPN>
-__global__ void __launch_bounds__(128)
-n0_rows2_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const double* __restrict__ tab /*pairs*/,
-                const double* __restrict__ soa, const double* __restrict__ G, double* __restrict__ partial /*[5][n_L][n_rb]*/) {
-    extern __shared__ double shm[];
-    PhiNode* sph = reinterpret_cast<PhiNode*>(shm);                 // [n_phi]
-    double (*red)[4] = reinterpret_cast<double (*)[4]>(shm + 4 * P.n_phi);
-    __shared__ int s_anyT;
-    const int r = blockIdx.x * 128 + threadIdx.x;
-    const int iL = blockIdx.y, n_rb = gridDim.x;
-    const double L = Ls[iL];
-    const double L2 = L * L;
-    if (threadIdx.x == 0) s_anyT = 0;
-    for (int j = threadIdx.x; j < P.n_phi; j += 128) {
-        const double c = c_phi[j], s = c_phi[P.n_phi + j];
-        PhiNode n;
-        n.B = L * c; n.A = 2.0 * n.B; n.C = L * s; n.w = c_phi[2 * P.n_phi + j];
-        sph[j] = n;
-    }
-    int fl = 0;
-    double l = 1.0, wl = 0.0;
-    UVals u = {};
-    if (r < P.n_l1) {
-        const double4* up = reinterpret_cast<const double4*>(utab + r);
-        const double4 q0 = ld4(up), q1 = ld4(up + 1), q2 = ld4(up + 2), q3 = ld4(up + 3);
-        fl = (int)q3.y;
-        l = q0.x; wl = q0.y;
-        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
-        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
-    }
-    const bool act = (fl & 5) && !(fl & 16);
-    const bool actT = act && (fl & 1), actP = act && (fl & 4);
-    __syncthreads();
-    if (actT) s_anyT = 1;                                           // benign race: every writer stores 1
-    __syncthreads();
-    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
-    if (s_anyT) n0_rows2_loop<true, EXPN>(P, tab, G, sph, L2, l, u, actT, actP, aTT, aTE, aEE, aEB);
-    else        n0_rows2_loop<false, EXPN>(P, tab, G, sph, L2, l, u, actT, actP, aTT, aTE, aEE, aEB);
-    // second pass: nodes within 4e-6 of a cut in |v|^2, evaluated exactly as the reference rounds them
-    if (act) {
-        const bool fold = P.fold != 0;
-        for (int j = 0; j < P.n_phi; ++j) {
-            const double nv2 = fma(l, l - sph[j].A, L2);
-            const unsigned hi = (unsigned)__double2hiint(nv2);
-            if ((hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2])
-                n0_node<true>(P, reinterpret_cast<const ClRow*>(soa), L, l, c_phi[j], c_phi[P.n_phi + j], u, fl & 1, fl & 4, sph[j].w, fold,
-                              c_phi[3 * P.n_phi + j], c_phi[4 * P.n_phi + j], c_phi[5 * P.n_phi + j], aTT, aTE, aEE, aEB, aBB);
-        }
-    }
-    if (!(P.terms & LBG_TT)) aTT = 0.0;
-    if (!(P.terms & LBG_TE)) aTE = 0.0;
-    if (!(P.terms & LBG_EE)) aEE = 0.0;
-    if (!(P.terms & LBG_EB)) aEB = 0.0;
-    double acc[5] = {aTT * wl, aTE * wl, aEE * wl, aEB * wl, aBB * wl};
-#pragma unroll
-    for (int t = 0; t < 5; ++t) {
-        double v = acc[t];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) == 0) red[t][threadIdx.x >> 5] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < 5) {
-        const int t = threadIdx.x;
-        const double v = (red[t][0] + red[t][1]) + (red[t][2] + red[t][3]);
-        partial[((size_t)t * P.n_L + iL) * n_rb + blockIdx.x] = v;
-    }
-}
-
-// ---- "rows3" variant: rows decomposition, per-interval polynomial tables with the detector noise folded in ----------
-// What bounds rows2 is not one pipe but three at once (ncu r1b: FP64 56 %, L1 data pipe 63 %, issue 56 %): every coefficient
-// a lane loads costs register-fill bandwidth (128 B/clk/SM, no dedupe between lanes), and the B-spline form spends 12 FP64
-// instructions on the basis weights plus 4 per spectrum.  rows3 therefore
-//  * evaluates each spectrum from the monomial coefficients of its knot interval (Horner, 3 DFMA, one 32-byte row slot),
-//    slot-major with a compile-time slot stride: the L1 data stage spends one wavefront per 128-byte line a load touches, so
-//    neighbouring lanes (neighbouring |v|) must find their coefficients of one slot in neighbouring bytes;
-//  * folds the detector noise into the C^tot slots when the table is built for the call: on [i, i+1] the factor
+// ---- per-call polynomial table ----------------------------------------------------------------------------------------------
+// What bounds the integrand kernels is not one pipe but three at once (ncu: FP64, L1 data pipe, issue): every coefficient a lane
+// loads costs register-fill bandwidth (128 B/clk/SM, no dedupe between lanes).  They therefore
+//  * evaluate each spectrum from the monomial coefficients of its knot interval (Horner, 3 DFMA, four 8-byte loads per slot),
+//    coefficient-major with a compile-time stride so that neighbouring lanes (neighbouring |v|) find a coefficient in neighbouring bytes;
+//  * fold the detector noise into the C^tot slots when the table is built for the call: on [i, i+1] the factor
 //    exp(a t (2i+1+t)) - 1 is replaced by its cubic interpolant at the four Chebyshev nodes (relative error bounded by
-//    (beta^4 + 12 a beta^2 + 12 a^2) / 3072, beta = a (2 lmax + 1); the host falls back to rows2 when the bound exceeds 2e-12);
-//  * drops the unlensed-BB slot when that spectrum is identically zero (CAMB scalar runs: prep_camb.py:84-85);
-//  * takes cos phi_j / w_j from constant memory (uniform datapath) and needs only cos: cos 2phi_uv = 2 (u.v)^2/(|u|^2|v|^2) - 1;
-//  * skips the temperature estimators (four slots, ~40 FP64 instructions) for warps whose |v| all exceed lmax_T.
-// Nodes within 4e-6 of a cut in |v|^2 are still left to the bit-faithful second pass (n0_node).
-__constant__ double2 c_cw[LBG_MAX_PHI_CONST];        // (cos phi_j, w_j) of the (folded) phi grid
-
+//    (beta^4 + 12 a beta^2 + 12 a^2) / 3072, beta = a (2 vmax + 1); beyond 2e-12 the generic kernel calls exp() per node instead);
+//  * never read the unlensed-BB slot when that spectrum is identically zero (CAMB scalar runs: prep_camb.py:84-85).
+// Intervals beyond the last knot of the table hold the spline's fill value 0 (+ the noise): prep_camb.py:88-89.
 struct ChebFit { double m[4][4]; double t[4]; };     // monomial coefficients = m . samples at t[]
 
 // slots per interval: 0 C^EE_tot, 1 C^BB_tot, 2 unlensed EE, 3 unlensed BB | 4 C^TT_tot, 5 lensed TE, 6 unlensed TT, 7 unlensed TE
-__global__ void n0_poly_table_kernel(N0Params P, ChebFit F, int n_int, const double* __restrict__ soa, double4* __restrict__ out) {
+__global__ void n0_poly_table_kernel(N0Params P, ChebFit F, int fold_noise, const double* __restrict__ soa, double4* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_int) return;
+    if (i >= P.n_int) return;
     const size_t st = (size_t)P.soa_stride;
     double4 a[8];
+    const bool in_table = i < P.n_ell - 1;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const double c0 = soa[k * st + i], c1 = soa[k * st + i + 1], c2 = soa[k * st + i + 2], c3 = soa[k * st + i + 3];
+        double c0 = 0.0, c1 = 0.0, c2 = 0.0, c3 = 0.0;
+        if (in_table) { c0 = soa[k * st + i]; c1 = soa[k * st + i + 1]; c2 = soa[k * st + i + 2]; c3 = soa[k * st + i + 3]; }
         a[k].x = (c0 + 4.0 * c1 + c2) * (1.0 / 6.0);
         a[k].y = (c2 - c0) * 0.5;
         a[k].z = (c0 - 2.0 * c1 + c2) * 0.5;
         a[k].w = ((c3 - c0) + 3.0 * (c1 - c2)) * (1.0 / 6.0);
     }
-    const double fi = (double)i;
-    double g[4];
+    double n[4] = {0.0, 0.0, 0.0, 0.0};
+    if (fold_noise) {
+        const double fi = (double)i;
+        double g[4];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) g[q] = expm1((P.a * F.t[q]) * fma(2.0, fi, 1.0 + F.t[q]));
-    const double G = exp((fi * (fi + 1.0)) * P.a);
-    double n[4];
+        for (int q = 0; q < 4; ++q) g[q] = expm1((P.a * F.t[q]) * fma(2.0, fi, 1.0 + F.t[q]));
+        const double G = exp((fi * (fi + 1.0)) * P.a);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) n[q] = G * (F.m[q][0] * g[0] + F.m[q][1] * g[1] + F.m[q][2] * g[2] + F.m[q][3] * g[3]);
-    n[0] += G;
+        for (int q = 0; q < 4; ++q) n[q] = G * (F.m[q][0] * g[0] + F.m[q][1] * g[1] + F.m[q][2] * g[2] + F.m[q][3] * g[3]);
+        n[0] += G;
+    }
     // layout double[slot][coefficient][LBG_PAIR_STRIDE]: four 8-byte loads per slot.  scripts/micro/ldg_pattern.cu (B200): a warp
     // LDG.E.64 whose lane pairs share an element costs 2.6 SM-clk on the L1-hit path, an LDG.E.128 of the same shape 6.9 -- two 64-bit
     // loads move the same bytes 24 % cheaper, and the 16-17 intervals a warp touches are 136 contiguous bytes of one array
@@ -587,35 +275,67 @@ __global__ void n0_poly_table_kernel(N0Params P, ChebFit F, int n_int, const dou
 #undef LBG_PUT
 }
 
-#ifndef LBG_ESTRIN
-#define LBG_ESTRIN 0
-#endif
 template <int SLOT>
-__device__ __forceinline__ double horner3(const double* __restrict__ p, double t, double t2) {    // p = table + interval index
+__device__ __forceinline__ double horner3(const double* __restrict__ p, double t) {    // p = table + interval index
     const double a0 = __ldg(p + (4 * SLOT) * LBG_PAIR_STRIDE), a1 = __ldg(p + (4 * SLOT + 1) * LBG_PAIR_STRIDE);
     const double a2 = __ldg(p + (4 * SLOT + 2) * LBG_PAIR_STRIDE), a3 = __ldg(p + (4 * SLOT + 3) * LBG_PAIR_STRIDE);
-#if LBG_ESTRIN
-    return fma(fma(a3, t, a2), t2, fma(a1, t, a0));               // two independent FMAs, then one: dependent depth 2 instead of 3
-#else
     return fma(fma(fma(a3, t, a2), t, a1), t, a0);
-#endif
 }
 
 struct RowGeom { double L2, l2, rl2x2, lL, m2lL, l2pL2; };   // per-thread constants of one (L, |u|) row
 
-template <bool DO_T, bool HAS_UB, bool FULL>
+// Row of this thread + the per-CTA epilogue shared by both integrand kernels.
+struct RowCtx { int fl; double l, wl; UVals u; };
+__device__ __forceinline__ RowCtx load_row(const N0Params& P, const URow* __restrict__ utab, int r) {
+    RowCtx c;
+    c.fl = 0; c.l = 1.0; c.wl = 0.0; c.u = UVals{};
+    if (r < P.n_l1) {
+        const double4* up = reinterpret_cast<const double4*>(utab + r);
+        const double4 q0 = ld4(up), q1 = ld4(up + 1), q2 = ld4(up + 2), q3 = ld4(up + 3);
+        c.fl = (int)q3.y;
+        c.l = q0.x; c.wl = q0.y;
+        c.u.uT = q0.z; c.u.uX = q0.w; c.u.uE = q1.x; c.u.uB = q1.y; c.u.T1 = q1.z; c.u.E1 = q1.w;
+        c.u.X1 = q2.x; c.u.rT1h = q2.y; c.u.rE1h = q2.z; c.u.rE1 = q2.w; c.u.rB1h = q3.x;
+    }
+    return c;
+}
+
+// partial[6][n_L][n_rb]: the five estimator sums of this CTA's 128 rows and, in slot 5, the number of unmasked nodes it evaluated.
+__device__ __forceinline__ void store_partials(const N0Params& P, double (*red)[4], int iL, int rb, double wl, double aTT, double aTE,
+                                               double aEE, double aEB, double aBB, double cnt, double* __restrict__ partial) {
+    double acc[6] = {aTT * wl, aTE * wl, aEE * wl, aEB * wl, aBB * wl, cnt};
+#pragma unroll
+    for (int t = 0; t < 6; ++t) {
+        double v = acc[t];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) red[t][threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        const int t = threadIdx.x;
+        const double v = (red[t][0] + red[t][1]) + (red[t][2] + red[t][3]);
+        partial[((size_t)t * P.n_L + iL) * P.n_rb + rb] = v;
+    }
+}
+
+// ---- generic integrand kernel: per-node masks (path 3) --------------------------------------------------------------------------
+// EXPN: the detector noise is NOT in the table; C^tot(v) = spline + N exp(a |v| (|v| + 1)) per node.
+template <bool DO_T, bool EXPN>
 __device__ __forceinline__ void n0_poly_node(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
-                                             bool actT, bool actP, const double2 cw, bool& any_rare,
-                                             double& aTT, double& aTE, double& aEE, double& aEB) {
+                                             bool actT, bool actP, const double2 cw, bool& any_rare, double& cnt,
+                                             double& aTT, double& aTE, double& aEE, double& aEB, double& aBB) {
     const double nv2 = fma(g.m2lL, cw.x, g.l2pL2);               // |v|^2 = l^2 + L^2 - 2 l L cos phi
     const unsigned hi = (unsigned)__double2hiint(nv2);
-    const bool rare = (hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2];
+    const bool rare = (hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] ||
+                      (hi - P.near_lo[2]) <= P.near_span[2] || (hi - P.near_lo[3]) <= P.near_span[3];
     any_rare = any_rare || rare;                                 // the bit-faithful second pass only runs for rows that saw one
     const bool vok = !rare && hi > P.near_lo[0];
     const bool okT = DO_T && actT && vok && hi < P.near_lo[1];
     const bool okP = actP && vok && hi < P.near_lo[2];
     if (!__any_sync(0xffffffffu, okT || okP)) return;
     const bool doT = DO_T && __any_sync(0xffffffffu, okT);       // warp-uniform
+    cnt += (okT || okP) ? 1.0 : 0.0;
 
     const double y = rsqrt_fast(nv2);                            // lanes with a bad |v|^2 carry NaN; their terms are selected away
     const double nv = nv2 * y;
@@ -624,23 +344,31 @@ __device__ __forceinline__ void n0_poly_node(const N0Params& P, const double4* _
     const double c2 = fma((dot * dot) * (y * y), g.rl2x2, -1.0); // cos 2phi_uv
     const double s2sq = fma(-c2, c2, 1.0);                       // sin^2 2phi_uv
 
-    const int i = max(min((int)nv, P.n_ell - 2), 0);
+    const int i = max(min((int)nv, P.n_int - 1), 0);
     const double t = nv - (double)i;
-    const double t2 = t * t;
     const double* row = reinterpret_cast<const double*>(ptab) + i;
-    const double E2 = horner3<0>(row, t, t2), vE = horner3<2>(row, t, t2);
-    double B2 = horner3<1>(row, t, t2);
-    const double vB = HAS_UB ? horner3<3>(row, t, t2) : 0.0;
-    if (!FULL) { if (!(P.terms & LBG_EB)) B2 = 1.0; }
+    double E2 = horner3<0>(row, t);
+    const double vE = horner3<2>(row, t);
+    double B2 = horner3<1>(row, t);
+    const double vB = horner3<3>(row, t);
+    double en = 0.0;
+    if (EXPN) {
+        en = exp((nv * (nv + 1.0)) * P.a);
+        E2 = fma(P.nP, en, E2);
+        B2 = fma(P.nP, en, B2);
+    }
+    if (!(P.terms & (LBG_EB | LBG_BB))) B2 = 1.0;
     const double uEd = u.uE * dLu;
     const double p2 = E2 * B2;
     double rE2, rB2;
     if (doT) {
-        double T2 = horner3<4>(row, t, t2);
-        const double X2 = horner3<5>(row, t, t2), vT = horner3<6>(row, t, t2), vX = horner3<7>(row, t, t2);
+        double T2 = horner3<4>(row, t);
+        if (EXPN) T2 = fma(P.nT, en, T2);
+        const double X2 = horner3<5>(row, t), vT = horner3<6>(row, t), vX = horner3<7>(row, t);
         const double E1T2 = u.E1 * T2, xx = u.X1 * X2;
         double den = fma(u.T1 * E2, E1T2, -(xx * xx));
-        if (!FULL) { if (!(P.terms & LBG_TE)) den = 1.0;  if (!(P.terms & LBG_TT)) T2 = 1.0; }
+        if (!(P.terms & LBG_TE)) den = 1.0;
+        if (!(P.terms & LBG_TT)) T2 = 1.0;
         const double p1 = T2 * den;
         const double r = rcp_fast(p1 * p2);                      // one reciprocal for the four filter denominators
         const double r34 = r * p1, r12 = r * p2;
@@ -660,59 +388,43 @@ __device__ __forceinline__ void n0_poly_node(const N0Params& P, const double4* _
     }
     const double fe = fma(vE, dLv, uEd) * c2;
     const double ee = (fe * fe) * (u.rE1h * rE2);
-    const double fb = HAS_UB ? fma(-vB, dLv, uEd) : uEd;
+    const double fb = fma(-vB, dLv, uEd);
     const double eb = ((fb * fb) * s2sq) * (u.rE1 * rB2);
     aEE = fma(cw.y, okP ? ee : 0.0, aEE);
     aEB = fma(cw.y, okP ? eb : 0.0, aEB);
+    if (P.terms & LBG_BB) {                                      // cmb/Nkk.py:148-154
+        const double fbb = fma(vB, dLv, u.uB * dLu) * c2;
+        const double bb = (fbb * fbb) * (u.rB1h * rB2);
+        aBB = fma(cw.y, okP ? bb : 0.0, aBB);
+    }
 }
 
-#ifndef LBG_ROWS3_UNROLL
-#define LBG_ROWS3_UNROLL 2
-#endif
-template <bool DO_T, bool HAS_UB, bool FULL>
+template <bool DO_T, bool EXPN>
 __device__ __forceinline__ void n0_rows3_loop(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
-                                              bool actT, bool actP, bool& any_rare, double& aTT, double& aTE, double& aEE, double& aEB) {
+                                              bool actT, bool actP, bool& any_rare, double& cnt,
+                                              double& aTT, double& aTE, double& aEE, double& aEB, double& aBB) {
+    const double2* cw = c_cw[P.lane];
     int j = 0;
-#if LBG_ROWS3_UNROLL >= 3
-    for (; j + 2 < P.n_phi; j += 3) {
-        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], any_rare, aTT, aTE, aEE, aEB);
-        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j + 1], any_rare, aTT, aTE, aEE, aEB);
-        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j + 2], any_rare, aTT, aTE, aEE, aEB);
-    }
-#endif
-#if LBG_ROWS3_UNROLL >= 2
     for (; j + 1 < P.n_phi; j += 2) {      // two independent nodes per trip: ILP for the FP64 pipe
-        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], any_rare, aTT, aTE, aEE, aEB);
-        n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j + 1], any_rare, aTT, aTE, aEE, aEB);
+        n0_poly_node<DO_T, EXPN>(P, ptab, g, u, actT, actP, cw[j], any_rare, cnt, aTT, aTE, aEE, aEB, aBB);
+        n0_poly_node<DO_T, EXPN>(P, ptab, g, u, actT, actP, cw[j + 1], any_rare, cnt, aTT, aTE, aEE, aEB, aBB);
     }
-#endif
-    for (; j < P.n_phi; ++j) n0_poly_node<DO_T, HAS_UB, FULL>(P, ptab, g, u, actT, actP, c_cw[j], any_rare, aTT, aTE, aEE, aEB);
+    for (; j < P.n_phi; ++j) n0_poly_node<DO_T, EXPN>(P, ptab, g, u, actT, actP, cw[j], any_rare, cnt, aTT, aTE, aEE, aEB, aBB);
 }
 
-#ifndef LBG_ROWS3_MINB
-#define LBG_ROWS3_MINB 5
-#endif
-template <bool HAS_UB, bool FULL>
-__global__ void __launch_bounds__(128, LBG_ROWS3_MINB)
+template <bool EXPN>
+__global__ void __launch_bounds__(128, 4)
 n0_rows3_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const double4* __restrict__ ptab,
-                const double* __restrict__ soa, double* __restrict__ partial /*[5][n_L][n_rb]*/) {
-    __shared__ double red[5][4];
+                const double* __restrict__ soa, const double* __restrict__ phi /*[6][n_phi]*/, double* __restrict__ partial) {
+    __shared__ double red[6][4];
     __shared__ int s_anyT;
-    const int r = blockIdx.x * 128 + threadIdx.x;
-    const int iL = blockIdx.y, n_rb = gridDim.x;
+    const int iL = blockIdx.x / P.n_rb, rb = blockIdx.x - iL * P.n_rb;
+    const int r = rb * 128 + threadIdx.x;
     const double L = Ls[iL];
     if (threadIdx.x == 0) s_anyT = 0;
-    int fl = 0;
-    double l = 1.0, wl = 0.0;
-    UVals u = {};
-    if (r < P.n_l1) {
-        const double4* up = reinterpret_cast<const double4*>(utab + r);
-        const double4 q0 = ld4(up), q1 = ld4(up + 1), q2 = ld4(up + 2), q3 = ld4(up + 3);
-        fl = (int)q3.y;
-        l = q0.x; wl = q0.y;
-        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
-        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
-    }
+    const RowCtx rc = load_row(P, utab, r);
+    const int fl = rc.fl;
+    const double l = rc.l;
     const bool act = (fl & 5) && !(fl & 16);
     const bool actT = act && (fl & 1), actP = act && (fl & 4);
     __syncthreads();
@@ -720,44 +432,33 @@ n0_rows3_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
     __syncthreads();
     RowGeom g;
     g.L2 = L * L; g.l2 = l * l; g.rl2x2 = 2.0 / g.l2; g.lL = l * L; g.m2lL = -2.0 * g.lL; g.l2pL2 = g.l2 + g.L2;
-    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
+    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0, cnt = 0.0;
     bool any_rare = false;
-    if (s_anyT) n0_rows3_loop<true, HAS_UB, FULL>(P, ptab, g, u, actT, actP, any_rare, aTT, aTE, aEE, aEB);
-    else        n0_rows3_loop<false, HAS_UB, FULL>(P, ptab, g, u, actT, actP, any_rare, aTT, aTE, aEE, aEB);
+    if (s_anyT) n0_rows3_loop<true, EXPN>(P, ptab, g, rc.u, actT, actP, any_rare, cnt, aTT, aTE, aEE, aEB, aBB);
+    else        n0_rows3_loop<false, EXPN>(P, ptab, g, rc.u, actT, actP, any_rare, cnt, aTT, aTE, aEE, aEB, aBB);
     // second pass: nodes within 4e-6 of a cut in |v|^2, evaluated exactly as the reference rounds them
     if (act && any_rare) {
         const bool fold = P.fold != 0;
-        for (int j = 0; j < P.n_phi; ++j) {
-            const double nv2 = fma(g.m2lL, c_cw[j].x, g.l2pL2);
+        const int n = P.n_phi;
+        const double2* cw = c_cw[P.lane];
+        for (int j = 0; j < n; ++j) {
+            const double nv2 = fma(g.m2lL, cw[j].x, g.l2pL2);
             const unsigned hi = (unsigned)__double2hiint(nv2);
-            if ((hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] || (hi - P.near_lo[2]) <= P.near_span[2])
-                n0_node<true>(P, reinterpret_cast<const ClRow*>(soa), L, l, c_phi[j], c_phi[P.n_phi + j], u, fl & 1, fl & 4, c_cw[j].y, fold,
-                              c_phi[3 * P.n_phi + j], c_phi[4 * P.n_phi + j], c_phi[5 * P.n_phi + j], aTT, aTE, aEE, aEB, aBB);
+            if ((hi - P.near_lo[0]) <= P.near_span[0] || (hi - P.near_lo[1]) <= P.near_span[1] ||
+                (hi - P.near_lo[2]) <= P.near_span[2] || (hi - P.near_lo[3]) <= P.near_span[3])
+                cnt += n0_node<true>(P, reinterpret_cast<const ClRow*>(soa), L, l, __ldg(phi + j), __ldg(phi + n + j), rc.u, fl & 1, fl & 4,
+                                     cw[j].y, fold, __ldg(phi + 3 * n + j), __ldg(phi + 4 * n + j), __ldg(phi + 5 * n + j),
+                                     aTT, aTE, aEE, aEB, aBB) ? 1.0 : 0.0;
         }
     }
-    if (!FULL) {
-        if (!(P.terms & LBG_TT)) aTT = 0.0;
-        if (!(P.terms & LBG_TE)) aTE = 0.0;
-        if (!(P.terms & LBG_EE)) aEE = 0.0;
-        if (!(P.terms & LBG_EB)) aEB = 0.0;
-    }
-    double acc[5] = {aTT * wl, aTE * wl, aEE * wl, aEB * wl, aBB * wl};
-#pragma unroll
-    for (int t = 0; t < 5; ++t) {
-        double v = acc[t];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) == 0) red[t][threadIdx.x >> 5] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < 5) {
-        const int t = threadIdx.x;
-        const double v = (red[t][0] + red[t][1]) + (red[t][2] + red[t][3]);
-        partial[((size_t)t * P.n_L + iL) * n_rb + blockIdx.x] = v;
-    }
+    if (!(P.terms & LBG_TT)) aTT = 0.0;
+    if (!(P.terms & LBG_TE)) aTE = 0.0;
+    if (!(P.terms & LBG_EE)) aEE = 0.0;
+    if (!(P.terms & LBG_EB)) aEB = 0.0;
+    store_partials(P, red, iL, rb, rc.wl, aTT, aTE, aEE, aEB, aBB, cnt, partial);
 }
 
-// ---- "rows5": rows3 tables and arithmetic, masks turned into phi-index ranges -------------------------------------------
+// ---- fast integrand kernel: masks turned into phi-index ranges (path 5) ---------------------------------------------------------
 // On the folded grid cos phi_j decreases with j, so |v|^2 = l^2 + L^2 - 2 l L cos phi_j (and its high word `hi`, the value
 // every mask test of rows3 looks at) is non-decreasing in j: each mask is a RANGE of j.  A thread finds its range ends once
 // per row by bisection on `hi` (six searches of ~7 steps, 2 instructions per node amortised):
@@ -769,11 +470,11 @@ n0_rows3_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
 // non-FP64 instruction removed counts): no per-node window arithmetic / votes / branches (about 25 of 99 instructions
 // per warp-node), fully masked nodes are never visited, and the branch-free bodies let the scheduler overlap the table
 // loads of two nodes.  The selected values are bit-identical to rows3 for every node it evaluates.
-__device__ __forceinline__ int first_j_hi_ge(const RowGeom& g, int n_phi, unsigned x) {   // first j with hi(j) >= x (n_phi if none)
+__device__ __forceinline__ int first_j_hi_ge(const RowGeom& g, const double2* cw, int n_phi, unsigned x) {   // first j with hi(j) >= x (n_phi if none)
     int lo = 0, hi = n_phi;
     while (lo < hi) {
         const int mid = (lo + hi) >> 1;
-        const unsigned h = (unsigned)__double2hiint(fma(g.m2lL, c_cw[mid].x, g.l2pL2));
+        const unsigned h = (unsigned)__double2hiint(fma(g.m2lL, cw[mid].x, g.l2pL2));
         if (h >= x) hi = mid; else lo = mid + 1;
     }
     return lo;
@@ -787,7 +488,7 @@ __device__ __forceinline__ NodePre n0_prep5(const N0Params& P, const RowGeom& g,
     const double nv2 = fma(g.m2lL, c, g.l2pL2);                  // |v|^2; lanes outside their own range may carry junk: selected away
     q.y = rsqrt_fast(nv2);
     const double nv = nv2 * q.y;
-    q.i = max(min((int)nv, P.n_ell - 2), 0);
+    q.i = max(min((int)nv, P.n_int - 1), 0);
     q.t = nv - (double)q.i;
     return q;
 }
@@ -795,23 +496,23 @@ __device__ __forceinline__ NodePre n0_prep5(const N0Params& P, const RowGeom& g,
 template <bool DO_T, bool HAS_UB, bool FULL>
 __device__ __forceinline__ void n0_node5(const N0Params& P, const double4* __restrict__ ptab, const RowGeom& g, const UVals& u,
                                          bool okT, bool okP, const double2 cw, const NodePre pre,
-                                         double& aTT, double& aTE, double& aEE, double& aEB) {
+                                         double& aTT, double& aTE, double& aEE, double& aEB, double& aBB) {
     const double y = pre.y, t = pre.t;
     const double* row = reinterpret_cast<const double*>(ptab) + pre.i;
     const double dLu = g.lL * cw.x, dLv = g.L2 - dLu;            // L.u, L.v
     const double dot = dLu - g.l2;                               // u.v
     const double c2 = fma((dot * dot) * (y * y), g.rl2x2, -1.0); // cos 2phi_uv = 2 (u.v)^2 / (|u|^2 |v|^2) - 1
     const double s2sq = fma(-c2, c2, 1.0);                       // sin^2 2phi_uv
-    const double E2 = horner3<0>(row, t, 0.0), vE = horner3<2>(row, t, 0.0);
-    double B2 = horner3<1>(row, t, 0.0);
-    const double vB = HAS_UB ? horner3<3>(row, t, 0.0) : 0.0;
-    if (!FULL) { if (!(P.terms & LBG_EB)) B2 = 1.0; }
+    const double E2 = horner3<0>(row, t), vE = horner3<2>(row, t);
+    double B2 = horner3<1>(row, t);
+    const double vB = HAS_UB ? horner3<3>(row, t) : 0.0;
+    if (!FULL) { if (!(P.terms & (LBG_EB | LBG_BB))) B2 = 1.0; }
     const double uEd = u.uE * dLu;
     const double p2 = E2 * B2;
     double rE2, rB2;
     if (DO_T) {
-        double T2 = horner3<4>(row, t, 0.0);
-        const double X2 = horner3<5>(row, t, 0.0), vT = horner3<6>(row, t, 0.0), vX = horner3<7>(row, t, 0.0);
+        double T2 = horner3<4>(row, t);
+        const double X2 = horner3<5>(row, t), vT = horner3<6>(row, t), vX = horner3<7>(row, t);
         const double E1T2 = u.E1 * T2, xx = u.X1 * X2;
         double den = fma(u.T1 * E2, E1T2, -(xx * xx));
         if (!FULL) { if (!(P.terms & LBG_TE)) den = 1.0;  if (!(P.terms & LBG_TT)) T2 = 1.0; }
@@ -838,73 +539,72 @@ __device__ __forceinline__ void n0_node5(const N0Params& P, const double4* __res
     const double eb = ((fb * fb) * s2sq) * (u.rE1 * rB2);
     aEE = fma(cw.y, okP ? ee : 0.0, aEE);
     aEB = fma(cw.y, okP ? eb : 0.0, aEB);
+    if (!FULL && HAS_UB) {
+        if (P.terms & LBG_BB) {                                  // cmb/Nkk.py:148-154 (zero when the unlensed BB table is)
+            const double fbb = fma(vB, dLv, u.uB * dLu) * c2;
+            const double bb = (fbb * fbb) * (u.rB1h * rB2);
+            aBB = fma(cw.y, okP ? bb : 0.0, aBB);
+        }
+    }
 }
 
-#ifndef LBG_ROWS5_MINB
-#define LBG_ROWS5_MINB 4
-#endif
-#ifndef LBG_ROWS5_UNROLL
-#define LBG_ROWS5_UNROLL 2
-#endif
 template <bool HAS_UB, bool FULL>
-__global__ void __launch_bounds__(128, LBG_ROWS5_MINB)
+__global__ void __launch_bounds__(128, 4)
 n0_rows5_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restrict__ utab, const double4* __restrict__ ptab,
-                const double* __restrict__ soa, double* __restrict__ partial /*[5][n_L][n_rb]*/) {
-    __shared__ double red[5][4];
-    const int r = blockIdx.x * 128 + threadIdx.x;
-    const int iL = blockIdx.y, n_rb = gridDim.x;
+                const double* __restrict__ soa, const double* __restrict__ phi /*[6][n_phi]*/, double* __restrict__ partial) {
+    __shared__ double red[6][4];
+    const int iL = blockIdx.x / P.n_rb, rb = blockIdx.x - iL * P.n_rb;
+    const int r = rb * 128 + threadIdx.x;
     const double L = Ls[iL];
-    int fl = 0;
-    double l = 1.0, wl = 0.0;
-    UVals u = {};
-    if (r < P.n_l1) {
-        const double4* up = reinterpret_cast<const double4*>(utab + r);
-        const double4 q0 = ld4(up), q1 = ld4(up + 1), q2 = ld4(up + 2), q3 = ld4(up + 3);
-        fl = (int)q3.y;
-        l = q0.x; wl = q0.y;
-        u.uT = q0.z; u.uX = q0.w; u.uE = q1.x; u.uB = q1.y; u.T1 = q1.z; u.E1 = q1.w;
-        u.X1 = q2.x; u.rT1h = q2.y; u.rE1h = q2.z; u.rE1 = q2.w; u.rB1h = q3.x;
-    }
+    const RowCtx rc = load_row(P, utab, r);
+    const int fl = rc.fl;
+    const double l = rc.l;
+    const UVals& u = rc.u;
     const bool act = (fl & 5) && !(fl & 16);
     const bool actT = act && (fl & 1), actP = act && (fl & 4);
     RowGeom g;
     g.L2 = L * L; g.l2 = l * l; g.rl2x2 = 2.0 / g.l2; g.lL = l * L; g.m2lL = -2.0 * g.lL; g.l2pL2 = g.l2 + g.L2;
     const int n = P.n_phi;
+    const double2* cw = c_cw[P.lane];
     // range ends of this row (see the header); inactive lanes get empty ranges that do not widen the warp's walk
     int j0s = n, j0e = n, jT = 0, jTe = 0, jP = 0, jPe = 0;
     if (act) {
-        j0s = first_j_hi_ge(g, n, P.near_lo[0]);
-        j0e = first_j_hi_ge(g, n, P.near_lo[0] + P.near_span[0] + 1u);
-        jT = first_j_hi_ge(g, n, P.near_lo[1]);
-        jTe = first_j_hi_ge(g, n, P.near_lo[1] + P.near_span[1] + 1u);
-        jP = first_j_hi_ge(g, n, P.near_lo[2]);
-        jPe = first_j_hi_ge(g, n, P.near_lo[2] + P.near_span[2] + 1u);
+        j0s = first_j_hi_ge(g, cw, n, P.near_lo[0]);
+        j0e = first_j_hi_ge(g, cw, n, P.near_lo[0] + P.near_span[0] + 1u);
+        jT = first_j_hi_ge(g, cw, n, P.near_lo[1]);
+        jTe = first_j_hi_ge(g, cw, n, P.near_lo[1] + P.near_span[1] + 1u);
+        jP = first_j_hi_ge(g, cw, n, P.near_lo[2]);
+        jPe = first_j_hi_ge(g, cw, n, P.near_lo[2] + P.near_span[2] + 1u);
     }
     const bool any_rare = act && (j0e > j0s || jTe > jT || jPe > jP);
     const int endT = actT ? jT : 0, endP = actP ? jP : 0;       // first j at which the T / P estimators stop (|v| side)
     const int w0 = __reduce_min_sync(0xffffffffu, j0e);
     const int wT = __reduce_max_sync(0xffffffffu, endT), wP = __reduce_max_sync(0xffffffffu, endP);
     double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
+    // unmasked nodes of this row on the fast path: the P range [j0e, endP) without the lmax_T window (T nodes are P nodes too: lmax_T <= lmax_P)
+    int cnt_i = max(endP - j0e, 0) - max(min(jTe, endP) - max(jT, j0e), 0);
+    if (cnt_i < 0) cnt_i = 0;
 #define LBG_OKT(j) ((j) >= j0e && (j) < endT)
 #define LBG_OKP(j) ((j) >= j0e && (j) < endP && !((j) >= jT && (j) < jTe))
     // pairs (j, j+1) from w0 on: 7-slot body while j < wT, then 3-slot body while j < wP.  A pair's second node may lie past a
-    // range end (or past n_phi): its predicates are false there, and c_cw holds LBG_MAX_PHI_CONST finite entries.
+    // range end (or past n_phi): its predicates are false there, and c_cw holds finite entries up to n_phi + 3.
     int j = w0;
-    NodePre p0 = n0_prep5(P, g, c_cw[j].x), p1 = n0_prep5(P, g, c_cw[j + 1].x);
+    NodePre p0 = n0_prep5(P, g, cw[j].x), p1 = n0_prep5(P, g, cw[j + 1].x);
     for (; j < wT; j += 2) {
-        const NodePre n0 = n0_prep5(P, g, c_cw[j + 2].x), n1 = n0_prep5(P, g, c_cw[j + 3].x);
-        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j), LBG_OKP(j), c_cw[j], p0, aTT, aTE, aEE, aEB);
-        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j + 1), LBG_OKP(j + 1), c_cw[j + 1], p1, aTT, aTE, aEE, aEB);
+        const NodePre n0 = n0_prep5(P, g, cw[j + 2].x), n1 = n0_prep5(P, g, cw[j + 3].x);
+        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j), LBG_OKP(j), cw[j], p0, aTT, aTE, aEE, aEB, aBB);
+        n0_node5<true, HAS_UB, FULL>(P, ptab, g, u, LBG_OKT(j + 1), LBG_OKP(j + 1), cw[j + 1], p1, aTT, aTE, aEE, aEB, aBB);
         p0 = n0; p1 = n1;
     }
     for (; j < wP; j += 2) {
-        const NodePre n0 = n0_prep5(P, g, c_cw[j + 2].x), n1 = n0_prep5(P, g, c_cw[j + 3].x);
-        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j), c_cw[j], p0, aTT, aTE, aEE, aEB);
-        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j + 1), c_cw[j + 1], p1, aTT, aTE, aEE, aEB);
+        const NodePre n0 = n0_prep5(P, g, cw[j + 2].x), n1 = n0_prep5(P, g, cw[j + 3].x);
+        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j), cw[j], p0, aTT, aTE, aEE, aEB, aBB);
+        n0_node5<false, HAS_UB, FULL>(P, ptab, g, u, false, LBG_OKP(j + 1), cw[j + 1], p1, aTT, aTE, aEE, aEB, aBB);
         p0 = n0; p1 = n1;
     }
 #undef LBG_OKT
 #undef LBG_OKP
+    double cnt = (double)cnt_i;
     if (any_rare) {                                              // bit-faithful second pass over the window nodes only
         const bool fold = P.fold != 0;
         for (int k = 0; k < 3; ++k) {
@@ -913,8 +613,9 @@ n0_rows5_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
                 if (k == 2 && jj >= jT && jj < jTe) continue;    // lmax_T == lmax_P: the windows coincide, visit once
                 if (k == 1 && jj >= j0s && jj < j0e) continue;
                 if (k == 2 && jj >= j0s && jj < j0e) continue;
-                n0_node<true>(P, reinterpret_cast<const ClRow*>(soa), L, l, c_phi[jj], c_phi[n + jj], u, fl & 1, fl & 4, c_cw[jj].y, fold,
-                              c_phi[3 * n + jj], c_phi[4 * n + jj], c_phi[5 * n + jj], aTT, aTE, aEE, aEB, aBB);
+                cnt += n0_node<true>(P, reinterpret_cast<const ClRow*>(soa), L, l, __ldg(phi + jj), __ldg(phi + n + jj), u, fl & 1, fl & 4,
+                                     cw[jj].y, fold, __ldg(phi + 3 * n + jj), __ldg(phi + 4 * n + jj), __ldg(phi + 5 * n + jj),
+                                     aTT, aTE, aEE, aEB, aBB) ? 1.0 : 0.0;
             }
         }
     }
@@ -924,39 +625,26 @@ n0_rows5_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
         if (!(P.terms & LBG_EE)) aEE = 0.0;
         if (!(P.terms & LBG_EB)) aEB = 0.0;
     }
-    double acc[5] = {aTT * wl, aTE * wl, aEE * wl, aEB * wl, aBB * wl};
-#pragma unroll
-    for (int t = 0; t < 5; ++t) {
-        double v = acc[t];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) == 0) red[t][threadIdx.x >> 5] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < 5) {
-        const int t = threadIdx.x;
-        const double v = (red[t][0] + red[t][1]) + (red[t][2] + red[t][3]);
-        partial[((size_t)t * P.n_L + iL) * n_rb + blockIdx.x] = v;
-    }
+    store_partials(P, red, iL, rb, rc.wl, aTT, aTE, aEE, aEB, aBB, cnt, partial);
 }
 
 // Special rows, always on the full (unfolded) phi grid:
 //  * rows sitting on the lmax_T / lmax_P cuts, where the reference's mask `|u| > lmax` (cmb/Nkk.py:17,20) depends on the
-//    rounding of |u| = sqrt((l cos)^2 + (l sin)^2) at each phi node;
-//  * rows the caller wants evaluated with its own u-side spline values at |u|_j (rows below the first non-zero C_l,
-//    where the reference's filter 1/C^tot is pure noise and its result inherits the rounding of scipy's spline).
-// su: [n_special][n_phi][8] splines at |u|_j (uTT,uTE,uEE,uBB,lTT,lTE,lEE,lBB); sm: [n_special][n_phi] |u|_j.
+//    rounding of |u| = sqrt((l cos)^2 + (l sin)^2) at each phi node; rows on the last knot of a table that ends in range likewise;
+//  * rows below the first non-zero C_l, where the reference's filter 1/C^tot is pure noise and its result inherits the rounding of
+//    scipy's spline: their u-side values come from splev_exact() (a host restatement of that routine) or from the caller.
+// su: [n_special][n_phi][8] splines at |u|_j (uTT,uTE,uEE,uBB,lTT,lTE,lEE,lBB); snu: [n_special][n_phi] |u|_j.
 __global__ void __launch_bounds__(128)
 n0_special_kernel(N0Params P, int n_special, int n_phi_full, const int* __restrict__ srow, const double* __restrict__ Ls,
                   const double* __restrict__ phi /*[3][n_phi_full]*/, const URow* __restrict__ utab,
                   const double* __restrict__ su, const double* __restrict__ snu, const ClRow* __restrict__ rows,
-                  double* __restrict__ partial /*[5][n_L*n_phi_full]*/) {
+                  double* __restrict__ partial /*[6][n_L*n_phi_full]*/) {
     const int npairs = P.n_L * n_phi_full;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= npairs) return;
     const int iL = p / n_phi_full, j = p - iL * n_phi_full;
     const double L = Ls[iL], c = phi[j], s = phi[n_phi_full + j];
-    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0;
+    double aTT = 0.0, aTE = 0.0, aEE = 0.0, aEB = 0.0, aBB = 0.0, cnt = 0.0;
     for (int k = 0; k < n_special; ++k) {
         const URow& ur = utab[srow[k]];
         const double* v = su + ((size_t)k * n_phi_full + j) * 8;
@@ -967,7 +655,7 @@ n0_special_kernel(N0Params P, int n_special, int n_phi_full, const int* __restri
         u.T1 = v[4] + P.nT * en; u.X1 = v[5]; u.E1 = v[6] + P.nP * en;
         const double B1 = v[7] + P.nP * en;
         u.rT1h = 0.5 / u.T1; u.rE1h = 0.5 / u.E1; u.rE1 = 1.0 / u.E1; u.rB1h = 0.5 / B1;
-        n0_node(P, rows, L, ur.l, c, s, u, !(nu > P.lmax_T), !(nu > P.lmax_P), ur.wl, false, 0.0, 0.0, 1.0, aTT, aTE, aEE, aEB, aBB);
+        cnt += n0_node(P, rows, L, ur.l, c, s, u, !(nu > P.lmax_T), !(nu > P.lmax_P), ur.wl, false, 0.0, 0.0, 1.0, aTT, aTE, aEE, aEB, aBB) ? 1.0 : 0.0;
     }
     const double wphi = phi[2 * n_phi_full + j];
     const size_t stride = (size_t)npairs;
@@ -976,9 +664,10 @@ n0_special_kernel(N0Params P, int n_special, int n_phi_full, const int* __restri
     partial[2 * stride + p] = aEE * wphi;
     partial[3 * stride + p] = aEB * wphi;
     partial[4 * stride + p] = aBB * wphi;
+    partial[5 * stride + p] = cnt;
 }
 
-// Library-side u values for special rows without caller-supplied ones: the eight splines at |u|_j.
+// Library-side u values for the special rows on a cut: the eight splines at |u|_j.
 __global__ void n0_special_u_kernel(int n_ell, int n, const double* __restrict__ nu, const ClRow* __restrict__ rows,
                                     double* __restrict__ out /*[n][8]*/) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -998,36 +687,32 @@ __global__ void n0_special_u_kernel(int n_ell, int n, const double* __restrict__
     for (int k = 0; k < 8; ++k) out[(size_t)t * 8 + k] = v[k];
 }
 
-// One block per L: fixed-order reduction of the partial sums, then cmb/Nkk.py:169-172.
+// One block per L: fixed-order sum of the row-block partials (+ the special rows), then cmb/Nkk.py:169-172.
+// out[7][n_L]: N0, the TT, TE, EE, EB, BB integrals, and the number of unmasked integrand nodes of this L.
 __global__ void __launch_bounds__(128)
-n0_reduce_kernel(N0Params P, const double* __restrict__ Ls, const double* __restrict__ partial,
-                 const double* __restrict__ spartial, int n_phi_full,
-                 double* __restrict__ out /*[6][n_L]: N0, TT, TE, EE, EB, BB integrals*/) {
-    __shared__ double sm[5][128];
-    const int iL = blockIdx.x, npairs = P.n_L * P.n_phi;
-    const size_t stride = (size_t)P.n_chunk * npairs;
-    const int n = P.n_chunk * P.n_phi;
-    double acc[5] = {0, 0, 0, 0, 0};
-    for (int e = threadIdx.x; e < n; e += 128) {
-        int ch = e / P.n_phi, j = e - ch * P.n_phi;
-        size_t o = (size_t)ch * npairs + (size_t)iL * P.n_phi + j;
+n0_rows_reduce_kernel(N0Params P, const double* __restrict__ Ls, const double* __restrict__ partial,
+                      const double* __restrict__ spartial, int n_phi_full, double* __restrict__ out) {
+    __shared__ double sm[6][128];
+    const int iL = blockIdx.x;
+    double acc[6] = {0, 0, 0, 0, 0, 0};
+    for (int b = threadIdx.x; b < P.n_rb; b += 128) {
 #pragma unroll
-        for (int t = 0; t < 5; ++t) acc[t] += partial[t * stride + o];
+        for (int t = 0; t < 6; ++t) acc[t] += partial[((size_t)t * P.n_L + iL) * P.n_rb + b];
     }
     if (spartial) {
         const size_t sstride = (size_t)P.n_L * n_phi_full;
         for (int j = threadIdx.x; j < n_phi_full; j += 128) {
 #pragma unroll
-            for (int t = 0; t < 5; ++t) acc[t] += spartial[t * sstride + (size_t)iL * n_phi_full + j];
+            for (int t = 0; t < 6; ++t) acc[t] += spartial[t * sstride + (size_t)iL * n_phi_full + j];
         }
     }
 #pragma unroll
-    for (int t = 0; t < 5; ++t) sm[t][threadIdx.x] = acc[t];
+    for (int t = 0; t < 6; ++t) sm[t][threadIdx.x] = acc[t];
     __syncthreads();
     for (int h = 64; h > 0; h >>= 1) {
         if (threadIdx.x < h) {
 #pragma unroll
-            for (int t = 0; t < 5; ++t) sm[t][threadIdx.x] += sm[t][threadIdx.x + h];
+            for (int t = 0; t < 6; ++t) sm[t][threadIdx.x] += sm[t][threadIdx.x + h];
         }
         __syncthreads();
     }
@@ -1039,96 +724,212 @@ n0_reduce_kernel(N0Params P, const double* __restrict__ Ls, const double* __rest
         r = 1.0 / r;
         const double pre = L * (L + 1.0) / 2.0;
         out[iL] = r * (pre * pre);
-        for (int t = 0; t < 5; ++t) out[(size_t)(t + 1) * P.n_L + iL] = sm[t][0];
+        for (int t = 0; t < 6; ++t) out[(size_t)(t + 1) * P.n_L + iL] = sm[t][0];
     }
 }
+
+// scipy's interp1d(kind='cubic') at one point, in its own operation order (ctx.cu).  On rows below the first non-zero C_l the
+// reference's 1/C^tot is pure detector noise and inherits the last-bit rounding of that routine (DESIGN.md "parity notes"): those few
+// values (2 rows x 201 nodes x 8 spectra) are computed on the host with the same recurrences from the same LAPACK-order coefficients.
+double scipy_bspline_eval(const double* t, const double* c, int n, double x);
 }  // namespace lbg
 
 using namespace lbg;
 
-extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_mask,
+namespace {
+// Everything of an N0 call that depends on the quadrature grids and cuts only: built once, kept on the context (host copies for the
+// comparison, device copies for the kernels) and reused while the caller passes the same grids (a forecast loop always does).
+struct N0Key {
+    int n_l1 = 0, n_phi = 0, fold = 0, n_exact = 0, n_ell = 0;
+    double lmax_T = 0, lmax_P = 0, lmin_v = 0, exact_below = -1;
+    std::vector<double> l1, w_l1, cphi, sphi, wphi;
+    std::vector<int> exact_rows;
+    bool same(int nl1, const double* a, const double* b, int nphi, const double* c, const double* s, const double* w, double lt, double lp,
+              double lv, int f, int ne, const int* er, int nell) const {
+        return nl1 == n_l1 && nphi == n_phi && f == fold && ne == n_exact && nell == n_ell && lt == lmax_T && lp == lmax_P && lv == lmin_v &&
+               !memcmp(a, l1.data(), (size_t)nl1 * 8) && !memcmp(b, w_l1.data(), (size_t)nl1 * 8) && !memcmp(c, cphi.data(), (size_t)nphi * 8) &&
+               !memcmp(s, sphi.data(), (size_t)nphi * 8) && !memcmp(w, wphi.data(), (size_t)nphi * 8) &&
+               (ne == 0 || !memcmp(er, exact_rows.data(), (size_t)ne * 4));
+    }
+};
+}  // namespace
+
+struct lbg_n0_plan {
+    N0Key key;
+    bool valid = false;
+    int n_phe = 0, n_special = 0, n_lib_exact = 0;   // folded node count; special rows; how many of them get library splev values
+    long long active_rows = 0;
+    bool cos_decreasing = false;
+    std::vector<int> srow;
+    std::vector<double> snu;                          // [n_special][n_phi] |u|_j in the reference's rounding
+    std::vector<double> cw;                           // (cos, w) pairs of the main kernel's grid, zero-padded by 4
+    double l1_max = 0.0;
+};
+
+// which context's (cos phi, w) block sits in lane `l` of c_cw on device `d` (c_cw is per device, contexts come and go)
+static std::mutex g_cw_mu;
+static lbg_ctx* g_cw_owner[64][LBG_MAX_LANES];
+
+static void n0_plan_free(lbg_ctx* c) {
+    delete c->n0_plan;
+    c->n0_plan = nullptr;
+    std::lock_guard<std::mutex> g(g_cw_mu);
+    for (auto& dev : g_cw_owner) for (auto& o : dev) if (o == c) o = nullptr;
+}
+
+// ---- begin: validate, (re)build the plan, stage the inputs, enqueue every kernel and the result copy; returns without waiting ----
+static int n0_begin_locked(lbg_ctx* c, int n_L, const double* L, unsigned terms_mask,
                            double thetab_arcmin, double deltaT_uK_arcmin, double Tcmb_K, int iterative,
                            int n_l1, const double* l1, const double* w_l1,
                            int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
                            double lmax_T, double lmax_P, double lmin_v, int fold_phi,
-                           int n_exact, const int* exact_rows, const double* exact_u,
-                           double* out_nkk, double* out_terms, long long* nodes_executed) {
-    LBG_REQUIRE(c && L && l1 && w_l1 && cos_phi && sin_phi && w_phi && out_nkk, "lbg_n0_ho02: NULL argument");
+                           int n_exact, const int* exact_rows, const double* exact_u, double exact_below) {
+    LBG_REQUIRE(c && L && l1 && w_l1 && cos_phi && sin_phi && w_phi, "lbg_n0_ho02: NULL argument");
     if (c->n_ell <= 0) { set_error("lbg_n0_ho02: call lbg_upload_cl_tables first"); return LBG_ESTATE; }
+    if (c->n0_pending) { set_error("lbg_n0_ho02: a call begun with lbg_n0_ho02_begin is still pending on this context"); return LBG_ESTATE; }
     LBG_REQUIRE(n_L >= 0 && n_l1 > 0 && n_phi > 0, "lbg_n0_ho02: bad sizes n_L=%d n_l1=%d n_phi=%d", n_L, n_l1, n_phi);
     LBG_REQUIRE((terms_mask & ~(LBG_TT | LBG_TE | LBG_EE | LBG_EB | LBG_BB)) == 0 && terms_mask != 0,
                 "lbg_n0_ho02: unsupported terms mask 0x%x", terms_mask);
     LBG_REQUIRE(Tcmb_K > 0 && lmax_T <= lmax_P, "lbg_n0_ho02: need Tcmb > 0 and lmax_T <= lmax_P");
+    LBG_REQUIRE(lmin_v > 0.0 && lmin_v < lmax_T, "lbg_n0_ho02: need 0 < lmin_v < lmax_T (the integrand is singular at v = 0)");
     LBG_REQUIRE(n_exact >= 0 && (n_exact == 0 || (exact_rows && exact_u)), "lbg_n0_ho02: exact rows given without values");
-    if (n_L == 0) { if (nodes_executed) *nodes_executed = 0; return LBG_OK; }
-    std::lock_guard<std::mutex> g(c->mu);
+    LBG_REQUIRE(fold_phi >= 0 && fold_phi <= 2, "lbg_n0_ho02: fold_phi must be 0 (full grid), 1 (mirror pairs) or 2 (mirror pairs, generic kernel)");
+    LBG_REQUIRE(c->lane >= 0 && c->lane < LBG_MAX_LANES, "lbg_n0_ho02: context lane %d has no phi-table block (lanes 0..%d)", c->lane, LBG_MAX_LANES - 1);
+    c->n0_n_L = n_L;
+    if (n_L == 0) { c->n0_pending = true; return LBG_OK; }
     LBG_CUDA(cudaSetDevice(c->device));
+    if (!c->n0_plan) c->n0_plan = new lbg_n0_plan();
+    lbg_n0_plan& pl = *c->n0_plan;
+    cudaStream_t st = c->stream;
 
-    // ---- phi nodes of the main kernel (optionally folded onto one node per mirror pair) -------------------
-    std::vector<double> ph;   // [6][n_phe]: cos, sin, w (pair sum), mirror cos, mirror sin, w_j / (w_j + w_m)
-    int n_phe = 0;
-    if (fold_phi) {
-        n_phe = (n_phi + 1) / 2;
-        ph.assign(6 * (size_t)n_phe, 0.0);
-        for (int j = 0, m = n_phi - 1; j <= m; ++j, --m) {
-            bool ok = fabs(cos_phi[j] - cos_phi[m]) < 1e-9 && fabs(sin_phi[j] + sin_phi[m]) < 1e-9;
-            LBG_REQUIRE(ok, "lbg_n0_ho02: fold_phi requested but nodes %d and %d are not mirror images", j, m);
-            const double w = (m != j) ? w_phi[j] + w_phi[m] : w_phi[j];
-            ph[j] = cos_phi[j]; ph[n_phe + j] = sin_phi[j]; ph[2 * (size_t)n_phe + j] = w;
-            ph[3 * (size_t)n_phe + j] = cos_phi[m]; ph[4 * (size_t)n_phe + j] = sin_phi[m];
-            ph[5 * (size_t)n_phe + j] = (m != j && w != 0.0) ? w_phi[j] / w : 1.0;
+    // ---- plan: grids, row flags, special rows, |u|_j of the special rows -------------------------------------------------
+    const bool fold = fold_phi != 0;
+    bool plan_fresh = false;
+    if (!pl.valid || !pl.key.same(n_l1, l1, w_l1, n_phi, cos_phi, sin_phi, w_phi, lmax_T, lmax_P, lmin_v, fold ? 1 : 0, n_exact, exact_rows, c->n_ell)
+        || pl.key.exact_below != exact_below) {
+        pl.valid = false;
+        plan_fresh = true;
+        std::vector<double> ph;   // [6][n_phe]: cos, sin, w (pair sum), mirror cos, mirror sin, w_j / (w_j + w_m)
+        int n_phe = 0;
+        if (fold) {
+            n_phe = (n_phi + 1) / 2;
+            ph.assign(6 * (size_t)n_phe, 0.0);
+            for (int j = 0, m = n_phi - 1; j <= m; ++j, --m) {
+                bool ok = fabs(cos_phi[j] - cos_phi[m]) < 1e-9 && fabs(sin_phi[j] + sin_phi[m]) < 1e-9;
+                LBG_REQUIRE(ok, "lbg_n0_ho02: fold_phi requested but nodes %d and %d are not mirror images", j, m);
+                const double w = (m != j) ? w_phi[j] + w_phi[m] : w_phi[j];
+                ph[j] = cos_phi[j]; ph[n_phe + j] = sin_phi[j]; ph[2 * (size_t)n_phe + j] = w;
+                ph[3 * (size_t)n_phe + j] = cos_phi[m]; ph[4 * (size_t)n_phe + j] = sin_phi[m];
+                ph[5 * (size_t)n_phe + j] = (m != j && w != 0.0) ? w_phi[j] / w : 1.0;
+            }
+        } else {
+            n_phe = n_phi;
+            ph.assign(6 * (size_t)n_phe, 0.0);
+            memcpy(&ph[0], cos_phi, (size_t)n_phi * 8);
+            memcpy(&ph[n_phe], sin_phi, (size_t)n_phi * 8);
+            memcpy(&ph[2 * (size_t)n_phe], w_phi, (size_t)n_phi * 8);
+            for (int j = 0; j < n_phe; ++j) ph[5 * (size_t)n_phe + j] = 1.0;
         }
-    } else {
-        n_phe = n_phi;
-        ph.assign(6 * (size_t)n_phe, 0.0);
-        memcpy(&ph[0], cos_phi, (size_t)n_phi * 8);
-        memcpy(&ph[n_phe], sin_phi, (size_t)n_phi * 8);
-        memcpy(&ph[2 * (size_t)n_phe], w_phi, (size_t)n_phi * 8);
-    }
-    std::vector<double> phf(3 * (size_t)n_phi);  // full grid for the special rows
-    memcpy(&phf[0], cos_phi, (size_t)n_phi * 8);
-    memcpy(&phf[n_phi], sin_phi, (size_t)n_phi * 8);
-    memcpy(&phf[2 * (size_t)n_phi], w_phi, (size_t)n_phi * 8);
+        LBG_REQUIRE(n_phe + 4 <= LBG_MAX_PHI, "lbg_n0_ho02: %d phi nodes after folding, at most %d fit the constant-memory table", n_phe, LBG_MAX_PHI - 4);
+        std::vector<double> phf(3 * (size_t)n_phi);  // full grid for the special rows
+        memcpy(&phf[0], cos_phi, (size_t)n_phi * 8);
+        memcpy(&phf[n_phi], sin_phi, (size_t)n_phi * 8);
+        memcpy(&phf[2 * (size_t)n_phi], w_phi, (size_t)n_phi * 8);
+        pl.cos_decreasing = true;
+        for (int j = 1; j < n_phe; ++j) pl.cos_decreasing = pl.cos_decreasing && ph[j] < ph[j - 1];
+        pl.cw.assign(2 * (size_t)(n_phe + 4), 0.0);
+        for (int j = 0; j < n_phe; ++j) { pl.cw[2 * j] = ph[j]; pl.cw[2 * j + 1] = ph[2 * (size_t)n_phe + j]; }
 
-    // ---- row flags; special rows = rows on a cut of prep_lmaxmask + rows the caller supplies exact u values for
-    std::vector<int> rowflag(n_l1, 0);
-    std::vector<int> srow;                       // special rows, caller's first (same order as exact_u)
-    for (int k = 0; k < n_exact; ++k) {
-        LBG_REQUIRE(exact_rows[k] >= 0 && exact_rows[k] < n_l1, "lbg_n0_ho02: exact row %d out of range", exact_rows[k]);
-        srow.push_back(exact_rows[k]);
-    }
-    long long active_rows = 0;
-    for (int r = 0; r < n_l1; ++r) {
-        double l = l1[r];
-        LBG_REQUIRE(l > 0.0, "lbg_n0_ho02: l1 nodes must be positive");
-        int f = 0;
-        bool onT = fabs(l - lmax_T) <= 1e-12 * lmax_T, onP = fabs(l - lmax_P) <= 1e-12 * lmax_P;
-        if (l < lmax_T || onT) f |= 1;
-        if (l < lmax_P || onP) f |= 4;
-        // a row sitting on the LAST KNOT of a table that ends inside the integration range: the reference's interp1d returns the
-        // knot value or its fill value 0 per phi node, depending on whether |u|_j = sqrt((l cos)^2 + (l sin)^2) rounds to the knot
-        // or one ulp above it (prep_camb.py:88-89) -- the same per-node rounding as the lmax cuts, so the same treatment
-        const double l_end = (double)(c->n_ell - 1);
-        const bool onEnd = f != 0 && fabs(l - l_end) <= 1e-12 * l_end;
-        if (onT || onP || onEnd) {
-            bool have = false;
-            for (int q : srow) have = have || q == r;
-            if (!have) srow.push_back(r);
+        // row flags; special rows = caller's exact rows, rows below `exact_below` (library splev values), rows on a cut of prep_lmaxmask
+        std::vector<int> rowflag(n_l1, 0);
+        pl.srow.clear();
+        for (int k = 0; k < n_exact; ++k) {
+            LBG_REQUIRE(exact_rows[k] >= 0 && exact_rows[k] < n_l1, "lbg_n0_ho02: exact row %d out of range", exact_rows[k]);
+            pl.srow.push_back(exact_rows[k]);
         }
-        rowflag[r] = f;
-        if (f) ++active_rows;
-    }
-    for (int q : srow) rowflag[q] |= 16;
-    const int n_special = (int)srow.size();
-    // |u|_j exactly as cmb/Nkk.py:66-67,79 for every (special row, phi node)
-    std::vector<double> snu((size_t)n_special * n_phi);
-    for (int k = 0; k < n_special; ++k)
-        for (int j = 0; j < n_phi; ++j) {
-            volatile double ux = l1[srow[k]] * cos_phi[j], uy = l1[srow[k]] * sin_phi[j];
-            volatile double a2 = ux * ux, b2 = uy * uy;
-            volatile double s2 = a2 + b2;
-            snu[(size_t)k * n_phi + j] = sqrt(s2);
+        auto have = [&](int r) { for (int q : pl.srow) if (q == r) return true; return false; };
+        pl.n_lib_exact = 0;
+        for (int r = 0; r < n_l1; ++r)
+            if (l1[r] < exact_below && !have(r)) { pl.srow.push_back(r); ++pl.n_lib_exact; }
+        pl.active_rows = 0;
+        pl.l1_max = 0.0;
+        for (int r = 0; r < n_l1; ++r) {
+            double l = l1[r];
+            LBG_REQUIRE(l > 0.0, "lbg_n0_ho02: l1 nodes must be positive");
+            pl.l1_max = std::max(pl.l1_max, l);
+            int f = 0;
+            bool onT = fabs(l - lmax_T) <= 1e-12 * lmax_T, onP = fabs(l - lmax_P) <= 1e-12 * lmax_P;
+            if (l < lmax_T || onT) f |= 1;
+            if (l < lmax_P || onP) f |= 4;
+            // a row sitting on the LAST KNOT of a table that ends inside the integration range: the reference's interp1d returns the
+            // knot value or its fill value 0 per phi node, depending on whether |u|_j = sqrt((l cos)^2 + (l sin)^2) rounds to the knot
+            // or one ulp above it (prep_camb.py:88-89) -- the same per-node rounding as the lmax cuts, so the same treatment
+            const double l_end = (double)(c->n_ell - 1);
+            const bool onEnd = f != 0 && fabs(l - l_end) <= 1e-12 * l_end;
+            if ((onT || onP || onEnd) && !have(r)) pl.srow.push_back(r);
+            rowflag[r] = f;
+            if (f) ++pl.active_rows;
         }
+        for (int q : pl.srow) rowflag[q] |= 16;
+        pl.n_special = (int)pl.srow.size();
+        // |u|_j exactly as cmb/Nkk.py:66-67,79 for every (special row, phi node)
+        pl.snu.assign((size_t)pl.n_special * n_phi, 0.0);
+        for (int k = 0; k < pl.n_special; ++k)
+            for (int j = 0; j < n_phi; ++j) {
+                volatile double ux = l1[pl.srow[k]] * cos_phi[j], uy = l1[pl.srow[k]] * sin_phi[j];
+                volatile double a2 = ux * ux, b2 = uy * uy;
+                volatile double s2 = a2 + b2;
+                pl.snu[(size_t)k * n_phi + j] = sqrt(s2);
+            }
+        pl.n_phe = n_phe;
+        // device copies of the plan: one staged block [l1 | w_l1 | ph | phf | snu | rowflag | srow]
+        const size_t nd = 2 * (size_t)n_l1 + ph.size() + phf.size() + pl.snu.size();
+        const size_t bytes = nd * 8 + ((size_t)n_l1 + pl.n_special) * 4;
+        LBG_CUDA(cudaStreamSynchronize(st));       // the staging block may still feed an earlier copy
+        if (c->n0_plan_dev.reserve(bytes + 64) || c->pin_n0.reserve(bytes + 64)) return LBG_ENOMEM;
+        double* hd = c->pin_n0.as<double>();
+        size_t o = 0;
+        memcpy(hd + o, l1, (size_t)n_l1 * 8); o += n_l1;
+        memcpy(hd + o, w_l1, (size_t)n_l1 * 8); o += n_l1;
+        memcpy(hd + o, ph.data(), ph.size() * 8); o += ph.size();
+        memcpy(hd + o, phf.data(), phf.size() * 8); o += phf.size();
+        if (!pl.snu.empty()) memcpy(hd + o, pl.snu.data(), pl.snu.size() * 8);
+        o += pl.snu.size();
+        int* hi = reinterpret_cast<int*>(hd + o);
+        memcpy(hi, rowflag.data(), (size_t)n_l1 * 4);
+        if (pl.n_special) memcpy(hi + n_l1, pl.srow.data(), (size_t)pl.n_special * 4);
+        LBG_CUDA(cudaMemcpyAsync(c->n0_plan_dev.p, hd, bytes, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaStreamSynchronize(st));       // pin_n0 is reused for the per-call block below
+        N0Key& k = pl.key;
+        k.n_l1 = n_l1; k.n_phi = n_phi; k.fold = fold ? 1 : 0; k.n_exact = n_exact; k.n_ell = c->n_ell;
+        k.lmax_T = lmax_T; k.lmax_P = lmax_P; k.lmin_v = lmin_v; k.exact_below = exact_below;
+        k.l1.assign(l1, l1 + n_l1); k.w_l1.assign(w_l1, w_l1 + n_l1);
+        k.cphi.assign(cos_phi, cos_phi + n_phi); k.sphi.assign(sin_phi, sin_phi + n_phi); k.wphi.assign(w_phi, w_phi + n_phi);
+        k.exact_rows.assign(exact_rows, exact_rows + n_exact);
+        c->cw_lane_valid = false;
+        pl.valid = true;
+    }
+    const int n_phe = pl.n_phe, n_special = pl.n_special;
+    const double* d_l1 = c->n0_plan_dev.as<double>();
+    const double* d_wl1 = d_l1 + n_l1;
+    const double* d_ph = d_wl1 + n_l1;
+    const double* d_phf = d_ph + 6 * (size_t)n_phe;
+    const double* d_snu = d_phf + 3 * (size_t)n_phi;
+    const int* d_rowflag = reinterpret_cast<const int*>(d_snu + (size_t)n_special * n_phi);
+    const int* d_srow = d_rowflag + n_l1;
+    bool cw_mine;
+    {
+        std::lock_guard<std::mutex> g(g_cw_mu);
+        lbg_ctx*& owner = g_cw_owner[c->device & 63][c->lane];
+        cw_mine = owner == c;
+        owner = c;
+    }
+    if (!c->cw_lane_valid || !cw_mine) {
+        LBG_CUDA(cudaMemcpyToSymbolAsync(c_cw, pl.cw.data(), pl.cw.size() * 8, (size_t)c->lane * LBG_MAX_PHI * sizeof(double2),
+                                         cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaStreamSynchronize(st));
+        c->cw_lane_valid = true;
+    }
 
     // ---- noise constants, cmb/DetectorNoise.py:13-26 ------------------------------------------------------
     const double arcmin2rad = M_PI / (60. * 180.);
@@ -1140,51 +941,47 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     N0Params P;
     P.soa_stride = c->cl_soa_stride;
     P.n_L = n_L; P.n_phi = n_phe; P.n_l1 = n_l1; P.n_ell = c->n_ell; P.terms = terms_mask;
+    P.n_rb = (n_l1 + 127) / 128;
+    P.lane = c->lane;
     P.nT = (dT / Tcmb_K) * (dT / Tcmb_K);
     P.nP = (dP / Tcmb_K) * (dP / Tcmb_K);
     P.a = tb * tb / (8. * log(2.));
     P.lmax_T = lmax_T; P.lmax_P = lmax_P; P.lmin_v = lmin_v;
     P.ebfac = iterative ? 2.5 : 1.0;                              // cmb/Nkk.py:141-143
-    P.fold = fold_phi ? 1 : 0;
+    P.fold = fold ? 1 : 0;
+    // every |v| an unmasked node can have lies below vmax: the polynomial table covers [0, vmax]
+    double Lmax = 0.0;
+    for (int i = 0; i < n_L; ++i) { LBG_REQUIRE(L[i] == L[i], "lbg_n0_ho02: L[%d] is NaN", i); Lmax = std::max(Lmax, fabs(L[i])); }
+    const double vmax = std::min(lmax_P, Lmax + pl.l1_max);
+    LBG_REQUIRE(vmax + 3.0 < (double)LBG_PAIR_STRIDE, "lbg_n0_ho02: |v| reaches %.0f; the per-call spline table holds %d knot intervals "
+                "(lower lmax_P or L)", vmax, LBG_PAIR_STRIDE - 3);
+    const bool short_table = (double)(c->n_ell - 1) < vmax;     // the table ends inside the reachable |v| range
+    P.n_int = short_table ? (int)vmax + 2 : std::min(c->n_ell - 1, LBG_PAIR_STRIDE);
     {
-        const double thr[3] = {lmin_v, lmax_T, lmax_P};
-        for (int k = 0; k < 3; ++k) {
+        const double thr[4] = {lmin_v, lmax_T, lmax_P, (double)(c->n_ell - 1)};
+        for (int k = 0; k < 4; ++k) {
             double lo = thr[k] * thr[k] * (1.0 - 4e-6), hi = thr[k] * thr[k] * (1.0 + 4e-6);
             unsigned long long blo, bhi;
             memcpy(&blo, &lo, 8); memcpy(&bhi, &hi, 8);
             P.near_lo[k] = (unsigned)(blo >> 32);
             P.near_span[k] = (unsigned)(bhi >> 32) - P.near_lo[k];
         }
+        if (!short_table) { P.near_lo[3] = 0xffffffffu; P.near_span[3] = 0u; }    // (hi - lo) <= span never holds for a finite |v|^2
     }
     const long long npairs = (long long)n_L * n_phe, npairs_full = (long long)n_L * n_phi;
     LBG_REQUIRE(npairs_full < (1LL << 30), "lbg_n0_ho02: n_L * n_phi too large");
-    const int bx = (int)((npairs + 127) / 128);
-    int n_chunk = (c->sm_count * 32 + bx - 1) / bx;
-    n_chunk = std::max(1, std::min(n_chunk, std::max(1, n_l1 / 128)));
-    P.rows_per_chunk = (n_l1 + n_chunk - 1) / n_chunk;
-    n_chunk = (n_l1 + P.rows_per_chunk - 1) / P.rows_per_chunk;
-    P.n_chunk = n_chunk;
+    LBG_REQUIRE((long long)n_L * P.n_rb < (1LL << 31), "lbg_n0_ho02: n_L * row blocks exceeds the grid limit");
 
-    // kernel variant: 0 = thread per (L, phi) marching over |u| rows, 1 = thread per |u| row looping over phi ("rows")
-    int variant = 5;
-    if (const char* e = getenv("LBG_N0_VARIANT")) variant = atoi(e);
-    if (n_phe > LBG_MAX_PHI_CONST || n_L > 65535) variant = 0;
-    // rows2 needs: only TT/TE/EE/EB requested, every |v| up to lmax_P inside the table, cuts ordered lmin_v < lmax_T <= lmax_P
-    if (variant >= 2 && ((terms_mask & LBG_BB) || lmax_P > (double)(c->n_ell - 2) || c->n_ell + 2 > LBG_PAIR_STRIDE || !(lmin_v > 0.0 && lmin_v < lmax_T))) variant = 1;
-    // rows5 walks index ranges: needs cos phi_j strictly decreasing (the folded grid) and disjoint, ordered cut windows
-    bool rows5 = variant == 5;
-    if (rows5) {
-        variant = 3;
-        for (int j = 1; j < n_phe; ++j) rows5 = rows5 && ph[j] < ph[j - 1];
-        rows5 = rows5 && n_phe + 4 <= LBG_MAX_PHI_CONST && fold_phi && P.near_lo[0] + P.near_span[0] < P.near_lo[1] && P.near_lo[1] <= P.near_lo[2];
-    }
+    // ---- which integrand kernel ---------------------------------------------------------------------------------------------
+    // folded-noise bound of the per-interval Chebyshev cubic (see the table's header)
+    const double beta = P.a * (2.0 * vmax + 1.0);
+    const double bound = (beta * beta * beta * beta + 12.0 * P.a * beta * beta + 12.0 * P.a * P.a) / 3072.0;
+    const bool expn = bound > 2e-12;
+    const bool rows5 = fold_phi == 1 && pl.cos_decreasing && !short_table && !expn &&
+                       P.near_lo[0] + P.near_span[0] < P.near_lo[1] && P.near_lo[1] <= P.near_lo[2];
+    c->n0_path = rows5 ? 5 : 3;
     ChebFit fit;
-    if (variant == 3) {
-        // rows3 folds the noise into the table: relative error bound of the per-interval Chebyshev cubic (see the kernel's header)
-        const double beta = P.a * (2.0 * lmax_P + 1.0);
-        const double bound = (beta * beta * beta * beta + 12.0 * P.a * beta * beta + 12.0 * P.a * P.a) / 3072.0;
-        if (bound > 2e-12) variant = 2;
-        // monomial <- samples matrix of the four Chebyshev nodes on [0, 1] (Gauss-Jordan in long double)
+    {   // monomial <- samples matrix of the four Chebyshev nodes on [0, 1] (Gauss-Jordan in long double)
         long double V[4][8];
         for (int q = 0; q < 4; ++q) {
             const long double tq = 0.5L + 0.5L * cosl((2 * q + 1) * M_PIl / 8.0L);
@@ -1204,111 +1001,165 @@ extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_
         }
         for (int q = 0; q < 4; ++q) for (int k = 0; k < 4; ++k) fit.m[q][k] = (double)V[q][4 + k];
     }
-    const int n_rb = (n_l1 + 127) / 128;
-    const size_t su_bytes = (size_t)n_special * n_phi * 8 * 8, snu_bytes = (size_t)n_special * n_phi * 8;
-    if (c->n0_L.reserve((size_t)n_L * 8) || c->s0.reserve((size_t)n_l1 * 8) || c->s1.reserve((size_t)n_l1 * 8) ||
-        c->n0_rowflag.reserve((size_t)n_l1 * 4) || c->n0_G.reserve((size_t)c->n_ell * 8 + 64) || c->n0_phi.reserve((ph.size() + phf.size()) * 8) ||
-        c->n0_utab.reserve((size_t)n_l1 * sizeof(URow)) ||
-        c->n0_partial.reserve((size_t)5 * (std::max((long long)n_chunk * npairs, (long long)n_L * n_rb) + npairs_full) * 8) || c->n0_out.reserve((size_t)6 * n_L * 8) ||
-        (variant == 3 && c->cl_poly.reserve((size_t)LBG_PAIR_STRIDE * 8 * 32)) || c->s2.reserve(su_bytes + 64) || c->s3.reserve(snu_bytes + 64) || c->s4.reserve((size_t)n_special * 4 + 64))
-        return LBG_ENOMEM;
-    cudaStream_t st = c->stream;
-    double* d_ph = c->n0_phi.as<double>();
-    double* d_phf = d_ph + ph.size();
-    double* d_part = c->n0_partial.as<double>();
-    double* d_spart = d_part + (size_t)5 * std::max((long long)n_chunk * npairs, (long long)n_L * n_rb);
-    LBG_CUDA(cudaMemcpyAsync(c->n0_L.p, L, (size_t)n_L * 8, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(c->s0.p, l1, (size_t)n_l1 * 8, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(c->s1.p, w_l1, (size_t)n_l1 * 8, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(c->n0_rowflag.p, rowflag.data(), (size_t)n_l1 * 4, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(d_ph, ph.data(), ph.size() * 8, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(d_phf, phf.data(), phf.size() * 8, cudaMemcpyHostToDevice, st));
-    if (n_special) {
-        LBG_CUDA(cudaMemcpyAsync(c->s3.p, snu.data(), snu_bytes, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaMemcpyAsync(c->s4.p, srow.data(), (size_t)n_special * 4, cudaMemcpyHostToDevice, st));
-        if (n_exact)
-            LBG_CUDA(cudaMemcpyAsync(c->s2.p, exact_u, (size_t)n_exact * n_phi * 64, cudaMemcpyHostToDevice, st));
-    }
 
-    if (variant >= 1) LBG_CUDA(cudaMemcpyToSymbolAsync(c_phi, ph.data(), ph.size() * 8, 0, cudaMemcpyHostToDevice, st));
-    KernelTimer t(c);
-    n0_uside_kernel<<<(n_l1 + 127) / 128, 128, 0, st>>>(P, c->s0.as<double>(), c->s1.as<double>(), c->n0_rowflag.as<int>(),
-                                                         c->cl_rows.as<ClRow>(), c->n0_utab.as<URow>());
-    t.launched();
-    if (n_special > n_exact) {   // library-evaluated splines at |u|_j for the rows the caller gave no values for
-        int cnt = (n_special - n_exact) * n_phi;
-        n0_special_u_kernel<<<(cnt + 127) / 128, 128, 0, st>>>(c->n_ell, cnt, c->s3.as<double>() + (size_t)n_exact * n_phi,
-                                                               c->cl_rows.as<ClRow>(), c->s2.as<double>() + (size_t)n_exact * n_phi * 8);
-        t.launched();
-    }
-    if (variant == 3) {
-        std::vector<double> cw(2 * (size_t)n_phe);
-        for (int j = 0; j < n_phe; ++j) { cw[2 * j] = ph[j]; cw[2 * j + 1] = ph[2 * (size_t)n_phe + j]; }
-        LBG_CUDA(cudaMemcpyToSymbolAsync(c_cw, cw.data(), cw.size() * 8, 0, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaStreamSynchronize(st));      // cw is a local
-        const int n_int = c->n_ell - 1;
-        n0_poly_table_kernel<<<(n_int + 127) / 128, 128, 0, st>>>(P, fit, n_int, c->cl_soa.as<double>(), c->cl_poly.as<double4>());
-        t.launched();
-        cudaEventRecord(c->ev2, st);
-        const bool full = terms_mask == (LBG_TT | LBG_TE | LBG_EE | LBG_EB);
-        const dim3 grid(n_rb, n_L);
-#define LBG_R3(UB, FULL) n0_rows3_kernel<UB, FULL><<<grid, 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), \
-                             c->cl_poly.as<double4>(), c->cl_soa.as<double>(), d_part)
-#define LBG_R5(UB, FULL) n0_rows5_kernel<UB, FULL><<<grid, 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), \
-                             c->cl_poly.as<double4>(), c->cl_soa.as<double>(), d_part)
-        if (rows5) {
-            if (c->ub_zero) { if (full) LBG_R5(false, true); else LBG_R5(false, false); }
-            else            { if (full) LBG_R5(true, true);  else LBG_R5(true, false); }
-        } else {
-            if (c->ub_zero) { if (full) LBG_R3(false, true); else LBG_R3(false, false); }
-            else            { if (full) LBG_R3(true, true);  else LBG_R3(true, false); }
+    // ---- per-call staging block: [L | u values of the special rows] in pinned memory, one copy -----------------------------------
+    const size_t su_count = (size_t)n_special * n_phi * 8;
+    const size_t part_main = (size_t)6 * n_L * P.n_rb, part_special = (size_t)6 * npairs_full;
+    if (c->n0_L.reserve((size_t)n_L * 8 + su_count * 8 + 64) || c->pin_n0.reserve((size_t)n_L * 8 + su_count * 8 + 64) ||
+        c->n0_utab.reserve((size_t)n_l1 * sizeof(URow)) || c->n0_partial.reserve((part_main + part_special) * 8) ||
+        c->n0_out.reserve((size_t)7 * n_L * 8) || c->pin_n0_out.reserve((size_t)7 * n_L * 8) ||
+        c->cl_poly.reserve((size_t)LBG_PAIR_STRIDE * 8 * 32))
+        return LBG_ENOMEM;
+    double* hL = c->pin_n0.as<double>();
+    memcpy(hL, L, (size_t)n_L * 8);
+    double* hsu = hL + n_L;
+    if (n_exact) memcpy(hsu, exact_u, (size_t)n_exact * n_phi * 64);
+    if (pl.n_lib_exact) {
+        // u-side values of the rows below `exact_below` by the reference's own spline routine (deboor_cubic), cached per table upload
+        const size_t cnt = (size_t)pl.n_lib_exact * n_phi * 8;
+        if (plan_fresh || c->n0_exact_gen != c->cl_gen || c->n0_exact_vals.size() != cnt) {
+            if (int rc = ensure_scipy_bspline(c)) return rc;
+            c->n0_exact_vals.assign(cnt, 0.0);
+            const int nk = c->n_ell;
+            const double xmax = (double)(nk - 1);
+            for (int k = 0; k < pl.n_lib_exact; ++k)
+                for (int j = 0; j < n_phi; ++j) {
+                    const double x = pl.snu[(size_t)(n_exact + k) * n_phi + j];
+                    for (int s8 = 0; s8 < 8; ++s8) {
+                        double v = 0.0;                                   // bounds_error=False, fill_value=0.0
+                        if (x >= 0.0 && x <= xmax) v = scipy_bspline_eval(c->cl_bspl_t.data(), c->cl_bspl_c.data() + (size_t)s8 * nk, nk, x);
+                        c->n0_exact_vals[((size_t)k * n_phi + j) * 8 + s8] = v;
+                    }
+                }
+            c->n0_exact_gen = c->cl_gen;
         }
+        memcpy(hsu + (size_t)n_exact * n_phi * 8, c->n0_exact_vals.data(), cnt * 8);
+    }
+    const int n_given = n_exact + pl.n_lib_exact;                // special rows whose u values arrive from the host
+    double* d_L = c->n0_L.as<double>();
+    double* d_su = d_L + n_L;
+    LBG_CUDA(cudaMemcpyAsync(d_L, hL, ((size_t)n_L + (size_t)n_given * n_phi * 8) * 8, cudaMemcpyHostToDevice, st));
+    double* d_part = c->n0_partial.as<double>();
+    double* d_spart = d_part + part_main;
+
+    c->last_launches = 0;
+    cudaEventRecord(c->ev0, st);
+    n0_uside_kernel<<<(n_l1 + 127) / 128, 128, 0, st>>>(P, d_l1, d_wl1, d_rowflag, c->cl_rows.as<ClRow>(), c->n0_utab.as<URow>());
+    ++c->last_launches;
+    if (n_special > n_given) {   // device-evaluated splines at |u|_j for the rows on a cut
+        int cnt = (n_special - n_given) * n_phi;
+        n0_special_u_kernel<<<(cnt + 127) / 128, 128, 0, st>>>(c->n_ell, cnt, d_snu + (size_t)n_given * n_phi,
+                                                               c->cl_rows.as<ClRow>(), d_su + (size_t)n_given * n_phi * 8);
+        ++c->last_launches;
+    }
+    n0_poly_table_kernel<<<(P.n_int + 127) / 128, 128, 0, st>>>(P, fit, expn ? 0 : 1, c->cl_soa.as<double>(), c->cl_poly.as<double4>());
+    ++c->last_launches;
+    cudaEventRecord(c->ev2, st);
+    const unsigned grid = (unsigned)((long long)n_L * P.n_rb);
+    const bool full = terms_mask == (LBG_TT | LBG_TE | LBG_EE | LBG_EB);
+#define LBG_R5(UB, FULL) n0_rows5_kernel<UB, FULL><<<grid, 128, 0, st>>>(P, d_L, c->n0_utab.as<URow>(), c->cl_poly.as<double4>(), \
+                             c->cl_soa.as<double>(), d_ph, d_part)
+#define LBG_R3(EXPN) n0_rows3_kernel<EXPN><<<grid, 128, 0, st>>>(P, d_L, c->n0_utab.as<URow>(), c->cl_poly.as<double4>(), \
+                             c->cl_soa.as<double>(), d_ph, d_part)
+    if (rows5) {
+        if (c->ub_zero) { if (full) LBG_R5(false, true); else LBG_R5(false, false); }
+        else            { if (full) LBG_R5(true, true);  else LBG_R5(true, false); }
+    } else {
+        if (expn) LBG_R3(true); else LBG_R3(false);
+    }
 #undef LBG_R5
 #undef LBG_R3
-    } else if (variant == 2) {
-        // overlapping-pair copy of the spline coefficients, built from the spectrum-major table (only this variant reads it)
-        if (c->cl_pairs.reserve((size_t)8 * LBG_PAIR_STRIDE * 16)) return LBG_ENOMEM;
-        LBG_CUDA(cudaMemsetAsync(c->cl_pairs.p, 0, (size_t)8 * LBG_PAIR_STRIDE * 16, st));
-        n0_pairs_kernel<<<dim3((c->n_ell + 2 + 255) / 256, 8), 256, 0, st>>>(c->n_ell + 2, c->cl_soa_stride, c->cl_soa.as<double>(), c->cl_pairs.as<double>());
-        t.launched();
-        const double xmax = P.a * 2.0 * (double)c->n_ell;                 // largest Taylor argument of the noise factor
-        const size_t smem = ((size_t)4 * n_phe + 5 * 4) * 8;
-        n0_noise_knots_kernel<<<(c->n_ell + 255) / 256, 256, 0, st>>>(c->n_ell, P.a, c->n0_G.as<double>());
-        t.launched();
-        if (xmax < 0.03)
-            n0_rows2_kernel<false><<<dim3(n_rb, n_L), 128, smem, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_pairs.as<double>(), c->cl_soa.as<double>(), c->n0_G.as<double>(), d_part);
-        else
-            n0_rows2_kernel<true><<<dim3(n_rb, n_L), 128, smem, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_pairs.as<double>(), c->cl_soa.as<double>(), c->n0_G.as<double>(), d_part);
-    } else if (variant == 1) {
-        n0_rows_kernel<<<dim3(n_rb, n_L), 128, 0, st>>>(P, c->n0_L.as<double>(), c->n0_utab.as<URow>(), c->cl_soa.as<ClRow>(), d_part);
-    } else {
-        n0_kernel<<<dim3(bx, n_chunk), 128, 0, st>>>(P, c->n0_L.as<double>(), d_ph, c->n0_utab.as<URow>(),
-                                                     c->cl_rows.as<ClRow>(), d_part);
-    }
-    t.launched();
+    ++c->last_launches;
     cudaEventRecord(c->ev3, st);
     if (n_special) {
-        n0_special_kernel<<<(int)((npairs_full + 127) / 128), 128, 0, st>>>(P, n_special, n_phi, c->s4.as<int>(), c->n0_L.as<double>(), d_phf,
-                                                                            c->n0_utab.as<URow>(), c->s2.as<double>(), c->s3.as<double>(),
-                                                                            c->cl_rows.as<ClRow>(), d_spart);
-        t.launched();
+        n0_special_kernel<<<(int)((npairs_full + 127) / 128), 128, 0, st>>>(P, n_special, n_phi, d_srow, d_L, d_phf, c->n0_utab.as<URow>(),
+                                                                            d_su, d_snu, c->cl_rows.as<ClRow>(), d_spart);
+        ++c->last_launches;
     }
-    if (variant >= 1)
-        n0_rows_reduce_kernel<<<n_L, 128, 0, st>>>(P, n_rb, c->n0_L.as<double>(), d_part, n_special ? d_spart : nullptr, n_phi, c->n0_out.as<double>());
-    else
-        n0_reduce_kernel<<<n_L, 128, 0, st>>>(P, c->n0_L.as<double>(), d_part, n_special ? d_spart : nullptr, n_phi, c->n0_out.as<double>());
-    t.launched();
-    std::vector<double> host((size_t)6 * n_L);
-    // Wait for the kernels here, not inside the copy: a device-to-host copy into pageable memory issued while the stream is busy
-    // blocks in the driver for the whole kernel time and (measured, scripts/overlap_timeline.py) stalls the pageable copies of
-    // every other context of the process with it, which would serialise lane-0 calls behind this 25 ms launch.
-    LBG_CUDA(cudaStreamSynchronize(st));
-    LBG_CUDA(cudaMemcpyAsync(host.data(), c->n0_out.p, host.size() * 8, cudaMemcpyDeviceToHost, st));
-    int rc = t.finish();
-    if (rc) return rc;
-    { float ms = 0.f; c->last_main_ms = (variant == 3 && cudaEventElapsedTime(&ms, c->ev2, c->ev3) == cudaSuccess) ? ms : c->last_ms; }
-    memcpy(out_nkk, host.data(), (size_t)n_L * 8);
-    if (out_terms) memcpy(out_terms, host.data() + n_L, (size_t)5 * n_L * 8);
-    if (nodes_executed) *nodes_executed = npairs * (active_rows - n_special) + npairs_full * n_special;
+    n0_rows_reduce_kernel<<<n_L, 128, 0, st>>>(P, d_L, d_part, n_special ? d_spart : nullptr, n_phi, c->n0_out.as<double>());
+    ++c->last_launches;
+    cudaEventRecord(c->ev1, st);
+    LBG_CUDA(cudaMemcpyAsync(c->pin_n0_out.p, c->n0_out.p, (size_t)7 * n_L * 8, cudaMemcpyDeviceToHost, st));
+    LBG_CUDA(cudaGetLastError());
+    c->n0_nodes_walked = npairs * (pl.active_rows - n_special) + npairs_full * n_special;
+    c->n0_pending = true;
     return LBG_OK;
 }
+
+static int n0_end_locked(lbg_ctx* c, int n_L, double* out_nkk, double* out_terms, long long* nodes_executed, long long* nodes_unmasked) {
+    if (!c->n0_pending) { set_error("lbg_n0_ho02_end: no pending call on this context"); return LBG_ESTATE; }
+    c->n0_pending = false;
+    if (n_L != c->n0_n_L) {                         // the pending call is dropped; wait for it so that its buffers can be reused
+        cudaSetDevice(c->device);
+        cudaStreamSynchronize(c->stream);
+        set_error("lbg_n0_ho02_end: n_L=%d but the pending call has %d multipoles (call dropped)", n_L, c->n0_n_L);
+        return LBG_EINVAL;
+    }
+    if (n_L == 0) { if (nodes_executed) *nodes_executed = 0; if (nodes_unmasked) *nodes_unmasked = 0; return LBG_OK; }
+    LBG_REQUIRE(out_nkk, "lbg_n0_ho02_end: out_nkk is NULL");
+    LBG_CUDA(cudaSetDevice(c->device));
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("kernel execution failed: %s", cudaGetErrorString(e)); return LBG_ECUDA; }
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) { c->last_ms = ms; c->total_ms += ms; c->total_launches += c->last_launches; }
+    c->last_main_ms = cudaEventElapsedTime(&ms, c->ev2, c->ev3) == cudaSuccess ? ms : c->last_ms;
+    const double* host = c->pin_n0_out.as<double>();
+    memcpy(out_nkk, host, (size_t)n_L * 8);
+    if (out_terms) memcpy(out_terms, host + n_L, (size_t)5 * n_L * 8);
+    if (nodes_executed) *nodes_executed = c->n0_nodes_walked;
+    if (nodes_unmasked) {
+        double s = 0.0;
+        for (int i = 0; i < n_L; ++i) s += host[(size_t)6 * n_L + i];
+        *nodes_unmasked = (long long)(s + 0.5);
+    }
+    return LBG_OK;
+}
+
+extern "C" int lbg_n0_ho02(lbg_ctx* c, int n_L, const double* L, unsigned terms_mask,
+                           double thetab_arcmin, double deltaT_uK_arcmin, double Tcmb_K, int iterative,
+                           int n_l1, const double* l1, const double* w_l1,
+                           int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
+                           double lmax_T, double lmax_P, double lmin_v, int fold_phi,
+                           int n_exact, const int* exact_rows, const double* exact_u,
+                           double* out_nkk, double* out_terms, long long* nodes_executed) {
+    LBG_REQUIRE(c && out_nkk, "lbg_n0_ho02: NULL argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    int rc = n0_begin_locked(c, n_L, L, terms_mask, thetab_arcmin, deltaT_uK_arcmin, Tcmb_K, iterative, n_l1, l1, w_l1, n_phi, cos_phi, sin_phi,
+                             w_phi, lmax_T, lmax_P, lmin_v, fold_phi, n_exact, exact_rows, exact_u, c->n0_exact_below);
+    if (rc) return rc;
+    return n0_end_locked(c, n_L, out_nkk, out_terms, nodes_executed, nullptr);
+}
+
+extern "C" int lbg_n0_ho02_begin(lbg_ctx* c, int n_L, const double* L, unsigned terms_mask,
+                                 double thetab_arcmin, double deltaT_uK_arcmin, double Tcmb_K, int iterative,
+                                 int n_l1, const double* l1, const double* w_l1,
+                                 int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
+                                 double lmax_T, double lmax_P, double lmin_v, int fold_phi,
+                                 int n_exact, const int* exact_rows, const double* exact_u) {
+    LBG_REQUIRE(c, "lbg_n0_ho02_begin: ctx is NULL");
+    std::lock_guard<std::mutex> g(c->mu);
+    return n0_begin_locked(c, n_L, L, terms_mask, thetab_arcmin, deltaT_uK_arcmin, Tcmb_K, iterative, n_l1, l1, w_l1, n_phi, cos_phi, sin_phi,
+                           w_phi, lmax_T, lmax_P, lmin_v, fold_phi, n_exact, exact_rows, exact_u, c->n0_exact_below);
+}
+
+extern "C" int lbg_n0_ho02_end(lbg_ctx* c, int n_L, double* out_nkk, double* out_terms, long long* nodes_executed, long long* nodes_unmasked) {
+    LBG_REQUIRE(c, "lbg_n0_ho02_end: ctx is NULL");
+    std::lock_guard<std::mutex> g(c->mu);
+    return n0_end_locked(c, n_L, out_nkk, out_terms, nodes_executed, nodes_unmasked);
+}
+
+extern "C" int lbg_n0_set_exact_below(lbg_ctx* c, double l_below) {
+    LBG_REQUIRE(c, "lbg_n0_set_exact_below: ctx is NULL");
+    std::lock_guard<std::mutex> g(c->mu);
+    c->n0_exact_below = l_below;
+    return LBG_OK;
+}
+
+extern "C" int lbg_n0_last_path(lbg_ctx* c, int* path) {
+    LBG_REQUIRE(c && path, "lbg_n0_last_path: NULL argument");
+    *path = c->n0_path;
+    return LBG_OK;
+}
+
+void lbg_n0_release(lbg_ctx* c) { n0_plan_free(c); }

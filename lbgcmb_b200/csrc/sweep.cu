@@ -96,29 +96,27 @@ extern "C" int lbg_forecast_grid(lbg_ctx* c, int n_ell, const double* ell, const
     LBG_REQUIRE(fsky > 0 && fid_sig8 > 0, "lbg_forecast_grid: fsky and fid_sig8 must be positive");
     std::lock_guard<std::mutex> g(c->mu);
     LBG_CUDA(cudaSetDevice(c->device));
-    const size_t ne = (size_t)n_ell * 8, ng = (size_t)n_cfg * ne, nn = (size_t)n_noise * ne, no = (size_t)n_noise * n_cfg * 64;
+    // every input travels in ONE pinned staging block: [ell | nmodes | ckk | cgg | ckg | (xcgg | xckg) | nkk | cfg]
     const int n_arr = xcgg ? 4 : 2;
-    if (c->s0.reserve(3 * ne) || c->s1.reserve(n_arr * ng) || c->s2.reserve((size_t)n_cfg * 64) || c->s3.reserve(nn) || c->s4.reserve(no)) return LBG_ENOMEM;
+    const size_t ne = (size_t)n_ell, ng = (size_t)n_cfg * ne, nn = (size_t)n_noise * ne, no = (size_t)n_noise * n_cfg * 8;
+    const size_t n_in = 3 * ne + n_arr * ng + nn + (size_t)n_cfg * 8;
+    if (c->s0.reserve(n_in * 8) || c->pin_in.reserve(n_in * 8) || c->s4.reserve(no * 8) || c->pin_out.reserve(no * 8)) return LBG_ENOMEM;
     cudaStream_t st = c->stream;
-    double* d0 = c->s0.as<double>();
-    double* d1 = c->s1.as<double>();
-    LBG_CUDA(cudaMemcpyAsync(d0, ell, ne, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(d0 + n_ell, nmodes, ne, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(d0 + 2 * (size_t)n_ell, ckk, ne, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(d1, cgg, ng, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(d1 + (size_t)n_cfg * n_ell, ckg, ng, cudaMemcpyHostToDevice, st));
-    if (xcgg) {
-        LBG_CUDA(cudaMemcpyAsync(d1 + 2 * (size_t)n_cfg * n_ell, xcgg, ng, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaMemcpyAsync(d1 + 3 * (size_t)n_cfg * n_ell, xckg, ng, cudaMemcpyHostToDevice, st));
-    }
-    LBG_CUDA(cudaMemcpyAsync(c->s2.p, cfg, (size_t)n_cfg * 64, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(c->s3.p, nkk, nn, cudaMemcpyHostToDevice, st));
+    double* h = c->pin_in.as<double>();
+    size_t o = 0;
+    auto put = [&](const double* src, size_t n) { size_t at = o; memcpy(h + o, src, n * 8); o += n; return at; };
+    const size_t o_ell = put(ell, ne), o_nm = put(nmodes, ne), o_kk = put(ckk, ne), o_gg = put(cgg, ng), o_kg = put(ckg, ng);
+    const size_t o_xgg = xcgg ? put(xcgg, ng) : 0, o_xkg = xcgg ? put(xckg, ng) : 0;
+    const size_t o_nkk = put(nkk, nn), o_cfg = put(cfg, (size_t)n_cfg * 8);
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, h, o * 8, cudaMemcpyHostToDevice, st));
+    const double* d = c->s0.as<double>();
     KernelTimer t(c);
     forecast_grid_kernel<<<dim3(n_cfg, n_noise), RED_T, 0, st>>>(
-        n_ell, n_cfg, d0, d0 + n_ell, d0 + 2 * (size_t)n_ell, d1, d1 + (size_t)n_cfg * n_ell,
-        xcgg ? d1 + 2 * (size_t)n_cfg * n_ell : nullptr, xcgg ? d1 + 3 * (size_t)n_cfg * n_ell : nullptr,
-        c->s2.as<GridCfg>(), c->s3.as<double>(), fsky, fid_sig8, c->s4.as<double>());
+        n_ell, n_cfg, d + o_ell, d + o_nm, d + o_kk, d + o_gg, d + o_kg, xcgg ? d + o_xgg : nullptr, xcgg ? d + o_xkg : nullptr,
+        reinterpret_cast<const GridCfg*>(d + o_cfg), d + o_nkk, fsky, fid_sig8, c->s4.as<double>());
     t.launched();
-    LBG_CUDA(cudaMemcpyAsync(out, c->s4.p, no, cudaMemcpyDeviceToHost, st));
-    return t.finish();
+    LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, c->s4.p, no * 8, cudaMemcpyDeviceToHost, st));
+    const int rc = t.finish();
+    if (rc == LBG_OK) memcpy(out, c->pin_out.p, no * 8);
+    return rc;
 }

@@ -58,6 +58,74 @@ def allgather_cyclic(local, n):
     return out
 
 
+_xbuf = {}
+last_exchange_ms = None
+
+
+def exchange(sums, curves, n):
+    """The exchange step of a sharded forecast in one round trip: `sums` (any shape) is all-reduced (SUM) and `curves`
+    [n_curves, n_mine] (this rank's cyclic shard of n units, shard_indices) is all-gathered back into [n_curves, n].
+
+    On NCCL both payloads travel in ONE pinned host block -> one device tensor, the two collectives run on slices of it, and one
+    copy brings [reduced sums | gathered curves] back (two copies, two collectives, one synchronisation); the device time of the
+    two collectives (CUDA events on torch's stream) is returned as the third value (None off-GPU).  gloo / no process group:
+    CPU tensors / identity."""
+    global last_exchange_ms
+    d = _dist()
+    sums = np.ascontiguousarray(sums, dtype=np.float64)
+    curves = np.atleast_2d(np.ascontiguousarray(curves, dtype=np.float64))
+    if d is None or d.get_world_size() == 1:
+        last_exchange_ms = None
+        return sums.copy(), curves.copy(), None
+    import torch
+    world = d.get_world_size()
+    width = (n + world - 1) // world
+    nc, ns = curves.shape[0], sums.size
+    nccl = d.get_backend() == 'nccl'
+    key = (ns, nc, width, world, nccl)
+    buf = _xbuf.get(key)
+    if buf is None:
+        n_in, n_out = ns + nc * width, ns + world * nc * width
+        if nccl:
+            dev = torch.device('cuda', torch.cuda.current_device())
+            buf = (torch.empty(n_in, dtype=torch.float64).pin_memory(), torch.empty(n_out, dtype=torch.float64).pin_memory(),
+                   torch.empty(n_in, dtype=torch.float64, device=dev), torch.empty(n_out, dtype=torch.float64, device=dev),
+                   torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        else:
+            buf = (torch.empty(n_in, dtype=torch.float64), torch.empty(n_out, dtype=torch.float64), None, None, None, None)
+        _xbuf.clear()
+        _xbuf[key] = buf
+    h_in, h_out, d_in, d_out, e0, e1 = buf
+    hin = h_in.numpy()
+    hin[:ns] = sums.ravel()
+    pad = hin[ns:].reshape(nc, width)
+    pad[:, :curves.shape[1]] = curves
+    pad[:, curves.shape[1]:] = 0.0
+    if nccl:
+        d_in.copy_(h_in, non_blocking=True)
+        e0.record()
+        d_out[:ns].copy_(d_in[:ns])
+        d.all_reduce(d_out[:ns], op=d.ReduceOp.SUM)
+        d.all_gather_into_tensor(d_out[ns:], d_in[ns:])
+        e1.record()
+        h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        ms = e0.elapsed_time(e1)
+    else:
+        h_out[:ns] = h_in[:ns]
+        d.all_reduce(h_out[:ns], op=d.ReduceOp.SUM)
+        d.all_gather_into_tensor(h_out[ns:], h_in[ns:].clone())
+        ms = None
+    hout = h_out.numpy()
+    parts = hout[ns:].reshape(world, nc, width)
+    out = np.empty((nc, n))
+    for r in range(world):
+        m = len(range(r, n, world))
+        out[:, r::world] = parts[r, :, :m]
+    last_exchange_ms = ms
+    return hout[:ns].reshape(sums.shape).copy(), out, ms
+
+
 def allreduce_sum(*arrays):
     """Sum float64 numpy arrays over all ranks in one collective (packed); identity without a process group."""
     d = _dist()

@@ -259,6 +259,12 @@ class Cosmology(object):
         self._slots[key] = slot
         return out
 
+    def table_slot(self, zs, nonlinear=True, sig8=None):
+        """Device table slot (lbg_pk_select_slot index) holding row r = P(k, zs[r]), built if it is not parked already: what
+        lbg_forecast_spectra takes per z grid."""
+        self.build_rows(zs, nonlinear=nonlinear, sig8=sig8)
+        return self._cur_slot
+
     def _select_slot(self, ctx, slot):
         import ctypes as C
         n = C.c_int(0)

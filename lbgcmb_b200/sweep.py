@@ -21,19 +21,64 @@ from lbgcmb_b200.pmh import engine_of
 OUT_FIELDS = ('snr', 'F_s8s8', 'F_s8b1', 'F_b1s8', 'F_b1b1', 'bias_s8', 'bias_b1')
 
 
-def limber_grid(Pk_interps, Llls, samples, zmin=0.01, zmax=10.0):
-    """C_gg[n, n_l], C_kg[n, n_l], N_gg[n] for samples = [{'pz', 'bz', 'nbar'}, ...] on a common z range: what
-    Cgg.Cgg(..., zeff=False), Ckg.Ckg(..., zeff=False) and Cgg.Ngg return per sample, from two batched launches."""
+def _grid_dz(zs):
+    """The spacing sliced_pz.py:22-24 divides by: the 6-decimal rounded step of the (asserted uniform) grid."""
+    steps = set(np.around(np.ediff1d(zs), 6))
+    assert len(steps) == 1
+    return float(list(steps)[0])
+
+
+def forecast_spectra(Pk_interps, Llls, samples, zmin=0.01, zmax=10.0, want_ckk=True):
+    """(C_kk[n_l] or None, C_gg[n, n_l], C_kg[n, n_l], N_gg[n]) for samples = [{'pz', 'bz', 'nbar'}, ...] on a common z range:
+    what lensing.Ckk, Cgg.Cgg(..., zeff=False), Ckg.Ckg(..., zeff=False) and Cgg.Ngg return per sample -- the body of
+    interloper.get_allCls (interloper.py:23-40) for a batch, in ONE library call (lbg_forecast_spectra).  The host evaluates each
+    callable once per grid (the C_gg nodes, the C_kg nodes, and the dz = 0.001 normalisation grid shared by sliced_pz.py:6-9 and
+    pz2nbar.py:6-17); the p(z) renormalisation, the prefactors, the quadrature weights and the sums over z run on the device."""
+    from lbgcmb_b200.Cgg import _cgg_nodes, _each
+    from lbgcmb_b200.Ckg import _ckg_nodes
+    from lbgcmb_b200.lensing import _ckk_nodes
+    from lbgcmb_b200.params import get_params
+    from lbgcmb_b200.pz2nbar import nbar_convert
+    par = get_params()
     engine, nonlinear = engine_of(Pk_interps, 'nlinear')
-    Ld = np.asarray(Llls, dtype=np.float64)
-    zs, chis, w = cgg_nodes(zmin, zmax)
-    wg = np.stack([cgg_weights(zs, chis, w, zmin, zmax, s['pz'], s['bz']) for s in samples])
-    cgg = engine.limber(Ld, zs, chis, wg, nonlinear=nonlinear)
-    zs, chis, w = ckg_nodes(zmin, zmax)
-    wk = np.stack([ckg_weights(zs, chis, w, zmin, zmax, s['pz'], s['bz']) for s in samples])
-    ckg = engine.limber(Ld, zs, chis, wk, nonlinear=nonlinear)
-    ngg = np.array([Ngg(Ld[:1], zmin, zmax, s['pz'], s['nbar'])[0] for s in samples])
-    return cgg, ckg, ngg
+    Ld = _ffi.f64(Llls)
+    zg, chig, wg, hcg = _cgg_nodes(float(zmin), float(zmax))
+    zk, chik, wk, wkap = _ckg_nodes(float(zmin), float(zmax))
+    n_s = len(samples)
+    fine = np.arange(zmin, zmax, 0.001)
+    pgg, bgg, pkg, bkg = np.empty((n_s, zg.size)), np.empty((n_s, zg.size)), np.empty((n_s, zk.size)), np.empty((n_s, zk.size))
+    norm, ngg = np.empty(n_s), np.empty(n_s)
+    for i, smp in enumerate(samples):
+        pz, bz = smp['pz'], smp['bz']
+        norm[i] = np.trapezoid(pz(fine), fine)                  # sliced_pz.py:6-9 == pz2nbar.pz_slice (same grid, same rule)
+        pgg[i], pkg[i] = pz(zg), pz(zk)
+        bgg[i], bkg[i] = _each(bz, zg), _each(bz, zk)
+        ngg[i] = 1. / (nbar_convert(smp['nbar'], unit='str') * norm[i]) if smp.get('nbar') is not None else np.nan   # Cgg.py:85-95
+    slot_g = engine.table_slot(zg, nonlinear=nonlinear)
+    slot_k = engine.table_slot(zk, nonlinear=nonlinear)
+    if want_ckk:
+        zc, chic, wc = _ckk_nodes(float(par['zscatter']))
+        slot_c = engine.table_slot(zc, nonlinear=nonlinear)
+    else:
+        chic = wc = np.zeros(0)
+        slot_c = 0
+    ctx = engine._ctx()
+    cgg, ckg = np.empty((n_s, Ld.size)), np.empty((n_s, Ld.size))
+    ckk = np.empty(Ld.size) if want_ckk else None
+    dp = _ffi._dp
+    _ffi.check(_ffi.lib().lbg_forecast_spectra(
+        ctx.handle, Ld.size, dp(Ld), float(zmin), float(zmax), float(par['h_100']),
+        zg.size, dp(zg), dp(chig), dp(hcg), dp(wg), _grid_dz(zg), int(slot_g),
+        zk.size, dp(zk), dp(chik), dp(wkap), dp(wk), _grid_dz(zk), int(slot_k),
+        chic.size, dp(_ffi.f64(chic)), dp(_ffi.f64(wc)), int(slot_c),
+        n_s, dp(pgg), dp(bgg), dp(pkg), dp(bkg), dp(norm), dp(cgg), dp(ckg), dp(ckk) if want_ckk else None))
+    return ckk, cgg, ckg, ngg
+
+
+def limber_grid(Pk_interps, Llls, samples, zmin=0.01, zmax=10.0):
+    """C_gg[n, n_l], C_kg[n, n_l], N_gg[n] for samples = [{'pz', 'bz', 'nbar'}, ...] on a common z range (forecast_spectra
+    without C_kk)."""
+    return forecast_spectra(Pk_interps, Llls, samples, zmin, zmax, want_ckk=False)[1:]
 
 
 def forecast_grid(Llls, nmodes, ckk, cgg, ckg, ngg, nkk, fsky, fid_sig8, fid_b1, LllMax, snr_lmax=None,
@@ -79,24 +124,27 @@ def survey_sweep(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noi
     Ld = np.asarray(Llls, dtype=np.float64)
     n0_async = n0_fn is None
     if spectra_fn is None:
-        from lbgcmb_b200.lensing import Ckk
-
         def spectra_fn(smp):
-            return (Ckk(Pk_interps, Ld),) + limber_grid(Pk_interps, Ld, smp, zmin, zmax)
+            return forecast_spectra(Pk_interps, Ld, smp, zmin, zmax)
     if grid_fn is None:
         grid_fn = forecast_grid
     lo, hi = _dist.shard_slice(len(noise_configs))
-    futs = None
-    if n0_async:                                 # this rank's N0 curves run on the second context while the spectra are built
+    mine = list(noise_configs[lo:hi])
+    call = None
+    if n0_async and mine:                        # this rank's first N0 curve runs on the second context while the spectra are built
         from lbgcmb_b200.Nkk import n0_terms_async
-        futs = [n0_terms_async(lensCl_interps, nolensCl_interps, Llls, terms, cfg[0], cfg[1], cfg[2], reuse_tables=True)
-                for cfg in noise_configs[lo:hi]]
+        call = n0_terms_async(lensCl_interps, nolensCl_interps, Llls, terms, mine[0][0], mine[0][1], mine[0][2])
     ckk, cgg, ckg, ngg = spectra_fn(samples)
     xc = spectra_fn(xsamples)[1:] if xsamples is not None else (None, None, None)
-    if futs is not None:
-        nkk = np.array([f.result()[0] for f in futs]).reshape(hi - lo, Ld.size)
+    if n0_async:
+        rows = []
+        for i in range(len(mine)):               # one call in flight per context: collect curve i, start curve i + 1
+            rows.append(call.result()[0])
+            if i + 1 < len(mine):
+                call = n0_terms_async(lensCl_interps, nolensCl_interps, Llls, terms, mine[i + 1][0], mine[i + 1][1], mine[i + 1][2])
+        nkk = np.array(rows).reshape(hi - lo, Ld.size)
     else:
-        nkk = np.array([n0_fn(cfg) for cfg in noise_configs[lo:hi]]).reshape(hi - lo, Ld.size)
+        nkk = np.array([n0_fn(cfg) for cfg in mine]).reshape(hi - lo, Ld.size)
     if hi > lo:
         out = grid_fn(Ld, nmodes, ckk, cgg, ckg, ngg, nkk, fsky, fid_sig8, [s['fid_b1'] for s in samples],
                       [s['LllMax'] for s in samples], xcgg=xc[0], xckg=xc[1], xngg=xc[2])
@@ -109,64 +157,84 @@ def survey_sweep(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noi
 
 def sharded_forecast(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noise_config, sample, fsky, fid_sig8=0.819,
                      xsample=None, zmin=0.01, zmax=10.0, terms=('TT', 'TE', 'EE', 'EB'), n0_fn=None, spectra_fn=None, grid_fn=None,
-                     timing=None):
-    """ONE forecast (one experiment, one galaxy sample) with the multipole grid sharded over the ranks -- the layout north_star
-    names: every rank evaluates N0, C_kk, C_gg, C_kg and the per-multipole covariance / Fisher terms on its own multipoles
-    (dist.shard_indices: L[rank::world], because the N0 cost per L falls with L; N0 per L and Limber per l are independent), and
-    the only exchange inside the path is ONE all-reduce of the partial sums (S/N^2, the 2 x 2 Fisher matrix of (sigma8, b1), the
-    bias vector, N_gg): 10 doubles over NCCL.  The curves are then gathered (one all_gather) so that every rank returns the full
-    arrays, as snr.py / interloper.py produce them.  On a GPU the N0 curve runs on the library's second context
-    (Nkk.n0_terms_async) while the spectra are built.
+                     timing=None, overlap=True):
+    """ONE forecast (one experiment; one galaxy sample or a list of them) with the multipole grid sharded over the ranks -- the
+    layout north_star names: every rank evaluates N0, C_kk, C_gg, C_kg and the per-multipole covariance / Fisher terms on its own
+    multipoles (dist.shard_indices: L[rank::world], because the N0 cost per L falls with L; N0 per L and Limber per l are
+    independent), and the only exchange inside the path is ONE all-reduce of the partial sums (per sample: S/N^2, the 2 x 2 Fisher
+    matrix of (sigma8, b1), the bias vector, N_gg) over NCCL.  The curves are then gathered (one all_gather) so that every rank
+    returns the full arrays, as snr.py / interloper.py produce them.  On a GPU the N0 curve is started first on the library's second
+    context (Nkk.n0_terms_async: enqueued, not waited for) and the spectra are built while it runs; `overlap=False` makes the
+    calls strictly one after another (per-stage device timing).
 
-    noise_config = (thetab, DeltaT, iterative); sample = {'pz', 'bz', 'nbar', 'fid_b1', 'LllMax'}; xsample: the interloper-
-    contaminated twin (bias vector).  Returns {'snr', 'Fisher', 'interim', 'dtheta', 'nkk', 'ckk', 'cgg', 'ckg', 'ngg'}.
+    noise_config = (thetab, DeltaT, iterative); sample = {'pz', 'bz', 'nbar', 'fid_b1', 'LllMax'} or a list of such; xsample: the
+    interloper-contaminated twin(s) (bias vector).  Returns {'snr', 'Fisher', 'interim', 'dtheta', 'ngg', 'nkk', 'ckk', 'cgg',
+    'ckg'}; with a list of samples every per-sample entry gains a leading sample axis.
     `n0_fn`, `spectra_fn`, `grid_fn` replace the device calls in the CPU (gloo) test of the sharding logic; `timing`, a dict,
-    receives this rank's wall seconds per phase."""
+    receives this rank's wall seconds per phase and the device ms of the exchange."""
     import time
     t0 = time.perf_counter()
+    single = isinstance(sample, dict)
+    samples = [sample] if single else list(sample)
+    xsamples = None if xsample is None else ([xsample] if isinstance(xsample, dict) else list(xsample))
+    n_b = len(samples)
+    if xsamples is not None and len(xsamples) != n_b:
+        raise ValueError('xsample must pair up with sample')
     Ld = np.asarray(Llls, dtype=np.float64)
     nm = np.asarray(nmodes, dtype=np.float64)
     mine = _dist.shard_indices(Ld.size)
     Lr = Ld[mine]
     have = mine.size > 0
     if spectra_fn is None:
-        from lbgcmb_b200.lensing import Ckk
-
         def spectra_fn(Ls, smp):
-            return (Ckk(Pk_interps, Ls),) + limber_grid(Pk_interps, Ls, smp, zmin, zmax)
+            return forecast_spectra(Pk_interps, Ls, smp, zmin, zmax)
     if grid_fn is None:
         grid_fn = forecast_grid
-    smp = [sample] if xsample is None else [sample, xsample]
+    smp = samples if xsamples is None else samples + xsamples
     if have:
         if n0_fn is None:
-            from lbgcmb_b200.Nkk import n0_terms_async
-            fut = n0_terms_async(lensCl_interps, nolensCl_interps, np.asarray(Llls)[mine], terms, noise_config[0], noise_config[1],
-                                 noise_config[2])
+            from lbgcmb_b200.Nkk import n0_begin
+            call = n0_begin(lensCl_interps, nolensCl_interps, np.asarray(Llls)[mine], terms, noise_config[0], noise_config[1],
+                            noise_config[2], lane=1 if overlap else 0)
+            if not overlap:
+                call.result()
             ckk, cgg, ckg, ngg = spectra_fn(Lr, smp)
             t1 = time.perf_counter()
-            nkk = fut.result()[0]
+            nkk = call.result()[0]
         else:
             nkk = np.asarray(n0_fn(np.asarray(Llls)[mine]), dtype=np.float64)
             ckk, cgg, ckg, ngg = spectra_fn(Lr, smp)
             t1 = time.perf_counter()
         t2 = time.perf_counter()
-        x = {} if xsample is None else {'xcgg': cgg[1:2], 'xckg': ckg[1:2], 'xngg': ngg[1:2]}
-        part = grid_fn(Lr, nm[mine], ckk, cgg[:1], ckg[:1], ngg[:1], nkk[None, :], fsky, fid_sig8, [sample['fid_b1']],
-                       [sample['LllMax']], **x)[0, 0]
-        sums = np.concatenate([[part[0] ** 2.], part[1:7], ngg[:1], [1.0]])     # S/N adds in quadrature over the shards
-        curves = np.stack([nkk, ckk, cgg[0], ckg[0]])
+        x = {} if xsamples is None else {'xcgg': cgg[n_b:], 'xckg': ckg[n_b:], 'xngg': ngg[n_b:]}
+        part = grid_fn(Lr, nm[mine], ckk, cgg[:n_b], ckg[:n_b], ngg[:n_b], nkk[None, :], fsky, fid_sig8,
+                       [s_['fid_b1'] for s_ in samples], [s_['LllMax'] for s_ in samples], **x)[0]         # [n_b, 8]
+        sums = np.empty((n_b, 9))
+        sums[:, 0] = part[:, 0] ** 2.                                 # S/N adds in quadrature over the shards
+        sums[:, 1:7] = part[:, 1:7]
+        sums[:, 7] = ngg[:n_b]
+        sums[:, 8] = 1.0
+        curves = np.concatenate([nkk[None, :], ckk[None, :], cgg[:n_b], ckg[:n_b]])
     else:                                                             # more ranks than multipoles
         t1 = t2 = time.perf_counter()
-        sums = np.zeros(9)
-        curves = np.zeros((4, 0))
+        sums = np.zeros((n_b, 9))
+        curves = np.zeros((2 + 2 * n_b, 0))
     t3 = time.perf_counter()
-    sums = _dist.allreduce_sum(sums)[0]                               # THE exchange step of the path
-    curves = _dist.allgather_cyclic(curves, Ld.size)
+    sums, curves, xms = _dist.exchange(sums, curves, Ld.size)         # THE exchange step of the path: one all-reduce, one all-gather
     t4 = time.perf_counter()
-    F = sums[1:5].reshape(2, 2)
-    interim = sums[5:7]
+    F = sums[:, 1:5].reshape(n_b, 2, 2)
+    interim = sums[:, 5:7]
+    dtheta = np.zeros((n_b, 2))
+    if xsamples is not None:
+        for i in range(n_b):
+            if np.linalg.det(F[i]) != 0:
+                dtheta[i] = np.linalg.solve(F[i], interim[i])
     if timing is not None:
-        timing.update(spectra_s=t1 - t0, n0_wait_s=t2 - t1, grid_s=t3 - t2, collectives_s=t4 - t3, n_L_mine=int(mine.size))
-    return {'snr': float(np.sqrt(sums[0])), 'Fisher': F, 'interim': interim,
-            'dtheta': np.linalg.solve(F, interim) if xsample is not None and np.linalg.det(F) != 0 else np.zeros(2),
-            'ngg': sums[7] / sums[8], 'nkk': curves[0], 'ckk': curves[1], 'cgg': curves[2], 'ckg': curves[3]}
+        timing.update(spectra_s=t1 - t0, n0_wait_s=t2 - t1, grid_s=t3 - t2, collectives_s=t4 - t3, exchange_device_ms=xms,
+                      n_L_mine=int(mine.size))
+    res = {'snr': np.sqrt(sums[:, 0]), 'Fisher': F, 'interim': interim, 'dtheta': dtheta, 'ngg': sums[:, 7] / sums[:, 8],
+           'nkk': curves[0], 'ckk': curves[1], 'cgg': curves[2:2 + n_b], 'ckg': curves[2 + n_b:2 + 2 * n_b]}
+    if single:
+        res = {k: (v if k in ('nkk', 'ckk') else v[0]) for k, v in res.items()}
+        res['snr'] = float(res['snr'])
+    return res

@@ -12,24 +12,37 @@ import sys
 import tempfile
 
 REF = os.environ.get('LBGCMB_REFERENCE', '/root/reference')
+# the reference's path modules byte-compiled by oracle/stage_ref.py (what travels to the GPU box instead of /root/reference)
+STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_ref', 'refpy')
 _done = False
 
 
 def available():
+    """The full reference tree (build container)."""
     return os.path.isfile(os.path.join(REF, 'cmb', 'Nkk.py'))
+
+
+def staged_available():
+    """The byte-compiled path modules (cmb/Nkk, Cgg, Ckg, cmb/lensing and their imports): enough for the CPU baseline arm."""
+    return os.path.isfile(os.path.join(STAGED, 'cmb', 'Nkk.pyc'))
+
+
+def root():
+    return REF if available() else (STAGED if staged_available() else None)
 
 
 def setup():
     global _done
     if _done:
         return
-    if not available():
-        raise RuntimeError('reference tree not present at %s' % REF)
+    if root() is None:
+        raise RuntimeError('reference tree not present at %s (and nothing staged under %s)' % (REF, STAGED))
     import numpy as np
     import scipy.integrate
     from . import simps121, romberg121
     here = os.path.dirname(os.path.abspath(__file__))
-    sys.path[:0] = [os.path.join(here, 'shim'), REF, os.path.join(REF, 'cmb'), os.path.join(REF, 'modi')]
+    base = root()
+    sys.path[:0] = [os.path.join(here, 'shim'), base, os.path.join(base, 'cmb'), os.path.join(base, 'modi')]
     import matplotlib  # noqa: F401  (the shim registers matplotlib.pyplot and pylab)
     # python-2 / old-numpy isms used by the reference (SURVEY.md N6)
     for name, typ in (('int', int), ('float', float)):

@@ -1,6 +1,6 @@
 """One small call of every kernel family, for compute-sanitizer (memcheck / racecheck):
   compute-sanitizer --tool memcheck python scripts/sanitize_case.py
-Sizes are tiny (the sanitizer slows kernels 10-100x) but walk the same code paths as the bench: N0 rows5 + special rows + second pass,
+Sizes are tiny (the sanitizer slows kernels 10-100x) but walk the same code paths as the bench: N0 rows5 / rows3 + special rows + second pass,
 the modi N0, the Limber kernel in both batch templates with out-of-range nodes, halofit table slots, S/N, covariance, Fisher, the
 design grid, mqw / cadence Fisher, E-H and growth tables."""
 import os
@@ -19,10 +19,9 @@ li, ni = cl_interps_from_tables(*bench.make_inputs())
 Ls = np.array([50, 2999, 3001, 5000])
 nkk, terms = Nkk.n0_terms(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True)
 nkk2 = Nkk.n0_terms_async(li, ni, Ls[:2], ['TT', 'EB'], 7.0, 30.0, False).result()[0]
-for v in ('1', '2', '3'):
-    os.environ['LBG_N0_VARIANT'] = v
-    assert np.allclose(Nkk.n0_terms(li, ni, Ls[:2], ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True)[0], nkk[:2], rtol=1e-11)
-del os.environ['LBG_N0_VARIANT']
+for fold in (2, False):        # the generic per-node-mask kernel on the folded and on the full phi grid
+    assert np.allclose(Nkk.n0_terms(li, ni, Ls[:2], ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True, fold_phi=fold)[0], nkk[:2], rtol=1e-11)
+Nkk.n0_terms(li, ni, Ls[:2], ['TT', 'BB'], 9.0, 30.0, False)      # analytic-noise variant (wide beam) + BB estimator
 kk, pp, bands = bench.forecast_inputs()
 Pk = pmh.get_PkInterps(pmh.PkTable(kk, pp))
 Lf = np.array([50., 300., 1500., 4000.])

@@ -114,10 +114,11 @@ def test_edge_cases(ctx, cl_tables):
     assert many[0] == one[0] == many[1] == many[3]
 
 
-def test_full_grid_B_properties(ctx, cl_tables, monkeypatch):
+def test_full_grid_B_properties(ctx, cl_tables):
     """BASELINE.json configs[1] at full size (every integer L in [50, 5000]): size-independent properties.
     * every L of the run equals the same L evaluated in a small call (the value of an L never depends on its neighbours);
-    * the range-walking kernel (rows5, default) and the per-node-mask kernel (rows3) agree to the last bits on all 4951 L;
+    * the range-walking kernel (rows5, default) and the per-node-mask kernel (rows3, fold_phi=2) agree to the last bits on all 4951 L
+      and count the same unmasked nodes;
     * N0 is smooth in L: no isolated outliers (a dropped or doubled node shows up as a spike at the 1e-3 level);
     * three spot values against the live numpy oracle."""
     from lbgcmb_b200 import Nkk
@@ -130,9 +131,9 @@ def test_full_grid_B_properties(ctx, cl_tables, monkeypatch):
     pick = np.array([50, 51, 999, 1000, 2999, 3000, 3001, 4999, 5000])
     small, _ = Nkk.n0_terms(li, ni, pick, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True)
     assert np.array_equal(full[pick - 50], small)
-    monkeypatch.setenv('LBG_N0_VARIANT', '3')
-    v3, t3 = Nkk.n0_terms(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True)
-    monkeypatch.delenv('LBG_N0_VARIANT')
+    assert Nkk.last_stats['path'] == 5
+    v3, t3 = Nkk.n0_terms(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, True, fold_phi=2)      # generic kernel, same folded grid
+    assert Nkk.last_stats['path'] == 3
     assert np.max(np.abs(full / v3 - 1)) < 5e-15
     for t in ('TT', 'TE', 'EE', 'EB'):
         assert np.max(np.abs(tf[t] / t3[t] - 1)) < 5e-15
@@ -168,19 +169,56 @@ def test_async_lane_matches_sync_and_overlaps_limber(ctx, cl_tables):
     assert np.array_equal(Nkk.Nkk_async(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 7.0, False).result(), want)
 
 
-def test_kernel_variants_agree(ctx, cl_tables, monkeypatch):
-    """The earlier integrand kernels stay selectable (LBG_N0_VARIANT: 0 node-per-thread, 1 rows, 2 rows + pair table built on the
-    device, 3 rows3) and agree with the default rows5 kernel to 1e-12."""
+def test_kernel_paths_and_unmasked_node_count(ctx, cl_tables):
+    """Which integrand kernel runs is decided by the inputs and reported (no environment switch): the range-walking kernel (5) for
+    the folded reference grid, the generic one (3) for an unfolded grid, on request, for a table that ends in range and for a beam
+    beyond the folded-noise bound.  The kernels count the nodes that pass a mask: equal to a direct count of the reference's masks
+    (cmb/Nkk.py:13-26) on the same grid, for both kernels and for folded / unfolded grids."""
     from lbgcmb_b200 import Nkk
     ell, lens, nolens = cl_tables
     li, ni = _interps(ell, lens, nolens)
     Ls = np.array([50, 333, 2999, 3001, 5000])
     want = Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False)[0]
-    for v in ('0', '1', '2', '3'):
-        monkeypatch.setenv('LBG_N0_VARIANT', v)
-        got = Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False)[0]
-        assert np.max(np.abs(got / want - 1)) < 1e-12, v
-    monkeypatch.delenv('LBG_N0_VARIANT')
+    assert Nkk.last_stats['path'] == 5
+    n5 = Nkk.last_stats['nodes_unmasked']
+    got = Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False, fold_phi=2)[0]
+    assert Nkk.last_stats['path'] == 3 and Nkk.last_stats['nodes_unmasked'] == n5
+    assert np.max(np.abs(got / want - 1)) < 1e-12
+    got = Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False, fold_phi=False)[0]
+    assert Nkk.last_stats['path'] == 3
+    n_full = Nkk.last_stats['nodes_unmasked']
+    assert np.max(np.abs(got / want - 1)) < 1e-11
+    # direct count of the reference's masks on the full grid (P family: |u| <= 5000 always holds; 2 <= |v| <= 5000)
+    l1, _, pphi, _ = Nkk.root_grids()
+    cnt = 0
+    for L in Ls:
+        ux, uy = l1[:, None] * np.cos(pphi)[None, :], l1[:, None] * np.sin(pphi)[None, :]
+        nv = ((L - ux) ** 2. + uy ** 2.) ** 0.5
+        nu = (ux ** 2. + uy ** 2.) ** 0.5
+        cnt += int(np.count_nonzero((nv >= 2) & (nv <= 5000) & (nu <= 5000)))
+    assert n_full == cnt
+    # a folded node stands for two nodes (one on the axis): 2 n5 - (nodes at phi = 0, pi) - (special rows counted on the full grid) ~ n_full
+    assert abs(2 * n5 - n_full) < 0.02 * n_full
+    Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 9.0, 30.0, False)
+    assert Nkk.last_stats['path'] == 3          # beam beyond the folded-noise bound: exp() per node
+
+
+def test_concurrent_lanes_with_different_grids(ctx, cl_tables):
+    """Two N0 calls in flight on the two contexts of one GPU with DIFFERENT phi grids and kernels (lane 1: folded, range-walking;
+    lane 0: unfolded, generic): each lane has its own block of the constant-memory phi table, so neither disturbs the other."""
+    from lbgcmb_b200 import Nkk
+    ell, lens, nolens = cl_tables
+    li, ni = _interps(ell, lens, nolens)
+    Ls = np.arange(50, 850)
+    a0 = Nkk.n0_terms(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False)[0]
+    b0 = Nkk.n0_terms(li, ni, Ls[:60], ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False, fold_phi=False)[0]
+    ca = Nkk.n0_begin(li, ni, Ls, ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False, lane=1)
+    cb = Nkk.n0_begin(li, ni, Ls[:60], ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False, fold_phi=False, lane=0)
+    with pytest.raises(Exception):
+        Nkk.n0_begin(li, ni, Ls[:3], ('TT',), 1.4, 7.0, False, lane=0)          # one call in flight per context
+    assert np.array_equal(cb.result()[0], b0)
+    assert np.array_equal(ca.result()[0], a0)
+    assert np.array_equal(Nkk.n0_terms(li, ni, Ls[:3], ('TT', 'TE', 'EE', 'EB'), 1.4, 7.0, False)[0], a0[:3])   # the context is usable again
 
 
 def test_flat_spectrum_tt_closed_form(ctx):
@@ -211,7 +249,8 @@ def test_flat_spectrum_tt_closed_form(ctx):
 
 def test_short_and_long_tables(ctx, cl_tables):
     """Tables that end inside the integration range (the reference's interp1d returns 0 beyond its last knot, so C^tot is pure
-    noise there: prep_camb.py:88-89) and tables longer than the fast kernels' compile-time stride (fall-back kernel)."""
+    noise there: prep_camb.py:88-89; generic kernel with the zero-extended table) and tables longer than the per-call table's
+    compile-time stride (only the intervals |v| can reach are tabulated: still the range-walking kernel)."""
     from oracle import n0 as on0
     from lbgcmb_b200 import Nkk
     from lbgcmb_b200.synthetic import cmb_cl_tables
@@ -223,19 +262,22 @@ def test_short_and_long_tables(ctx, cl_tables):
     li, ni = _interps(ell[:n], lens[:, :n], nolens[:, :n])
     got = Nkk.Nkk(li, ni, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 7.0, iterative=False, pickleit=False)
     assert np.max(np.abs(got / ref - 1)) < RTOL
+    assert Nkk.last_stats['path'] == 3
     ell2, lens2, nolens2 = cmb_cl_tables(n_ell=17001)          # > 16382 knots
     assert np.array_equal(lens2[:, :ell.size], lens)           # same spectra, longer tables
     li2, ni2 = _interps(ell2, lens2, nolens2)
     li0, ni0 = _interps(ell, lens, nolens)
     Ls = np.array([50, 2000, 5000])
     a = Nkk.Nkk(li2, ni2, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, iterative=True, pickleit=False)
+    assert Nkk.last_stats['path'] == 5
     b = Nkk.Nkk(li0, ni0, Ls, ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, iterative=True, pickleit=False)
     assert np.max(np.abs(a / b - 1)) < RTOL                    # the far end of a not-a-knot spline does not reach l <= 10000
 
 
 def test_unusual_L_and_wide_beam_against_oracle(ctx, cl_tables):
     """L outside the usual grid (below the first l1 node, non-integer, beyond lmax_P where only part of the |v| annulus survives)
-    and the widest beam / highest noise of the BASELINE sweep (the noise factor reaches e^19 at l = 5000)."""
+    and the widest beam / highest noise of the BASELINE sweep (the noise factor reaches e^19 at l = 5000); a 10 arcmin beam leaves
+    the folded-noise bound and runs the analytic-noise variant of the generic kernel."""
     from oracle import n0 as on0
     from lbgcmb_b200 import Nkk
     ell, lens, nolens = cl_tables
@@ -243,7 +285,7 @@ def test_unusual_L_and_wide_beam_against_oracle(ctx, cl_tables):
     ol, on = on0.cl_interps(ell, lens), on0.cl_interps(ell, nolens)
     terms = ('TT', 'TE', 'EE', 'EB')
     for Ls, thetab, DeltaT, it in ((np.array([2, 7.5, 6000, 9990]), 1.4, 7.0, False), (np.array([50, 1234, 5000]), 7.0, 30.0, False),
-                                   (np.array([3000, 3001]), 1.0, 1.0, True)):
+                                   (np.array([3000, 3001]), 1.0, 1.0, True), (np.array([50, 2500]), 10.0, 30.0, False)):
         ref = on0.nkk_root(ol, on, Ls, terms, thetab, DeltaT, it)
         got = Nkk.n0_terms(li, ni, Ls, terms, thetab, DeltaT, it)[0]
         assert np.all(np.isfinite(got)) and np.all(got > 0)
