@@ -162,7 +162,7 @@ class OracleForecast(object):
     """CPU legs only: the numpy restatements (oracle/limber.py, oracle/halofit.py, oracle/fisher.py) behind the call surface
     forecast_stage() uses.  P(k,z) rows are cached per redshift, the way the reference's camb interpolator is built once.
     `reference=True`: C_gg / C_kg / C_kk / N_gg come from the UNMODIFIED reference modules (Cgg.py, Ckg.py, cmb/lensing.py through
-    oracle/refload.py: /root/reference in the build container, the byte-compiled copy under oracle/_ref/refpy on the GPU box)."""
+    oracle/refload.py: /root/reference in the build container, the byte-compiled copy under oracle/_ref/refpy.zip on the GPU box)."""
 
     def __init__(self, k, p, reference=False):
         from oracle import limber as ol, fisher as ofi, halofit as oh, modi_lensing as om
@@ -239,7 +239,7 @@ def _ref_worker(args):
 
 
 def run_reference(a, rank, world):
-    """CPU arm on all host cores.  With the reference staged (oracle/_ref/refpy, or /root/reference in the build container) N0 is the
+    """CPU arm on all host cores.  With the reference staged (oracle/_ref/refpy.zip, or /root/reference in the build container) N0 is the
     UNMODIFIED cmb/Nkk.py and the spectra are the UNMODIFIED Cgg.py / Ckg.py / cmb/lensing.py (`kind: reference`); the covariance /
     Fisher / S/N sums (negligible time) are the numpy restatement of the interloper.py script body, which is not importable as a
     function.  Otherwise the numpy port (`kind: port`).  One step = N0 for `nper` L values spread over the grid, one per worker

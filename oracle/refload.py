@@ -13,7 +13,7 @@ import tempfile
 
 REF = os.environ.get('LBGCMB_REFERENCE', '/root/reference')
 # the reference's path modules byte-compiled by oracle/stage_ref.py (what travels to the GPU box instead of /root/reference)
-STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_ref', 'refpy')
+STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_ref', 'refpy.zip')
 _done = False
 
 
@@ -24,7 +24,7 @@ def available():
 
 def staged_available():
     """The byte-compiled path modules (cmb/Nkk, Cgg, Ckg, cmb/lensing and their imports): enough for the CPU baseline arm."""
-    return os.path.isfile(os.path.join(STAGED, 'cmb', 'Nkk.pyc'))
+    return os.path.isfile(STAGED)
 
 
 def root():
