@@ -139,6 +139,26 @@ int lbg_halofit_sigma2(lbg_ctx* ctx, int n_R, const double* R, double* out_sigma
  * {D^2, k_nl, n_eff, curvature, Omega_m(z), Omega_L(z), use_halofit (0 -> linear row, modi/cosmology.py:171), unused}. */
 int lbg_pk_build_table(lbg_ctx* ctx, int n_rows, const double* halo_z, double fnu, double om0, double w, int takahashi,
                        double* out_pnl /*[n_rows][n_k] or NULL: table stays on the device*/);
+/* modi/halofit.py:70-98 (`_get_spec`'s two quintic InterpolatedUnivariateSpline fits, the inverse evaluation at ln sigma^2 = 0 and the
+ * two derivatives) on the host in FITPACK's own operation order -- coefficients, values and derivatives are bit-identical to scipy's
+ * (tests/test_fitpack_cpu.py), which matters because the curvature is the second derivative of an interpolating spline on a 0.0092
+ * grid (rounding of the fit x 1e4).  lnr increasing, lnsig = ln sigma^2 on it (decreasing).  out = (k_nl = 1 / R_nl [the reference's `rknl`], n_eff, curvature); host-only.
+ * *status: 0 ok, 1 = the derivative point ln(1 / rknl) lies outside the fitted range (scipy raises there: the reference's `except` branch, :79-96).
+ * rknl_in > 0: skip the inverse fit and differentiate at ln(1 / rknl_in) (the refit inside that branch). */
+int lbg_halofit_spec_host(int n, const double* lnr, const double* lnsig, double rknl_in, double* out /*[3]*/, int* status);
+/* Number of k nodes of the linear table installed on the context (0: none). */
+int lbg_pk_table_nk(lbg_ctx* ctx, int* n_k);
+/* The same for a whole z grid on the device, and the P(k,z) rows built from it (modi/cosmology.py:171-179 per node) without a host
+ * round trip: zin[n_rows][4] = {D(z)^2, Omega_m(z), Omega_L(z), use_halofit}; lnr[n_R] / R[n_R] = the reference's fitting grid
+ * np.linspace(ln 0.1, ln 10, 500) and its exp (modi/halofit.py:36-37).  sigma_0^2(R) is summed once per linear table, R_nl(z) comes
+ * from one inverse fit at z = 0 evaluated at -ln D^2 (the interpolant commutes with the shift; 1e-14), and (n_eff, C) from a
+ * per-redshift fit of ln(D^2 sigma_0^2) in FITPACK order, one device thread per redshift on a factorisation shared by all.
+ * out_spec (may be NULL): [n_rows][4] = {k_nl = 1 / R_nl, n_eff, curvature, flag}; flag 1 = R_nl outside the tabulated decade: that row needs the
+ * reference's exception path (lbg_halofit_spec_host on a re-sampled grid + lbg_pk_build_table).  *n_flagged = number of such rows.
+ * build != 0 and no flagged row: the table (row r = P(k, z_r)) is built into the current slot, like lbg_pk_build_table. */
+int lbg_pk_build_table_hf(lbg_ctx* ctx, int n_rows, const double* zin, int n_R, const double* lnr, const double* R,
+                          double fnu, double om0, double w, int takahashi, int build, double* out_spec, int* n_flagged,
+                          double* out_pnl /*[n_rows][n_k] or NULL*/);
 /* The context holds up to 4 P(k,z) tables; one is current (the one lbg_pk_build_table fills and lbg_limber / lbg_pk_eval read).
  * Makes table `slot` (0..3) current and returns its row count in *out_rows (0: nothing built in it yet).  Pointer swaps only.
  * Every table is dropped when a new linear table or k grid is installed (lbg_upload_pk_linear, lbg_eh_linear_table,

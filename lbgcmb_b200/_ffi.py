@@ -11,8 +11,25 @@ LIB_PATH = os.environ.get('LBGCMB_LIB') or os.path.join(_HERE, 'liblbgcmb.so')  
 _lib = None
 _lock = threading.Lock()
 _ctxs = {}
-# device index -> id() of the python object whose linear P(k) table currently sits on that context (None: nobody's)
+# device index -> (token, digest) of the python object whose linear P(k) table currently sits on that context (None: nobody's).
+# The token comes from `new_owner_token()` (never reused, unlike id()); the digest covers the table's bytes, so a table edited in
+# place is uploaded again.
 table_owner = {}
+_owner_tokens = __import__('itertools').count(1)
+
+
+def new_owner_token():
+    return next(_owner_tokens)
+
+
+def table_digest(*arrays):
+    import hashlib
+    h = hashlib.blake2b(digest_size=16)
+    for a in arrays:
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        h.update(str(a.shape).encode())
+        h.update(a.tobytes())
+    return h.digest()
 
 c_double_p = C.POINTER(C.c_double)
 c_ll_p = C.POINTER(C.c_longlong)
@@ -66,6 +83,9 @@ def _declare(L):
         'lbg_upload_pk_linear': [vp, i, c_double_p, c_double_p, c_double_p],
         'lbg_halofit_sigma2': [vp, i, c_double_p, c_double_p],
         'lbg_pk_build_table': [vp, i, c_double_p, d, d, d, i, c_double_p],
+        'lbg_halofit_spec_host': [i, c_double_p, c_double_p, d, c_double_p, c_int_p],
+        'lbg_pk_table_nk': [vp, c_int_p],
+        'lbg_pk_build_table_hf': [vp, i, c_double_p, i, c_double_p, c_double_p, d, d, d, i, i, c_double_p, c_int_p, c_double_p],
         'lbg_pk_upload_rows': [vp, i, c_double_p, i, c_double_p],
         'lbg_pk_eval': [vp, i, i, c_double_p, i, c_double_p],
         'lbg_eh_transfer': [vp, d, d, d, i, d, d, d, i, c_double_p, c_double_p, c_double_p, c_double_p],

@@ -77,6 +77,7 @@ struct __align__(64) ClRow {
 }  // namespace lbg
 
 struct lbg_n0_plan;               // n0.cu: grid-dependent part of an N0 call, kept between calls
+struct lbg_hf_state;              // halofit.cu: HALOFIT fitting grid / sigma_0^2 state
 
 struct lbg_ctx {
     int          device = 0;
@@ -119,6 +120,8 @@ struct lbg_ctx {
     lbg::PinBuf  pin_in, pin_out;    // pinned staging for the short, copy-dominated calls (lbg_limber)
     // P(k) / Limber state (see limber.cu)
     int          n_k = 0;
+    unsigned long long pk_gen = 0;   // bumped whenever a new linear table / k grid is installed
+    lbg_hf_state* hf = nullptr;
     lbg::DevBuf  pk_lnk, pk_plin, pk_rdk;
     int          pnl_nz = 0;         // rows of the CURRENT P(k,z) table (pk_pnl); 0 = none built
     lbg::DevBuf  pk_pnl;
@@ -128,7 +131,7 @@ struct lbg_ctx {
     int          pk_cur = 0;
     int          store_nz[PK_SLOTS] = {0, 0, 0, 0};
     lbg::DevBuf  pk_store[PK_SLOTS];
-    void drop_pk_tables() { pnl_nz = 0; for (int i = 0; i < PK_SLOTS; ++i) store_nz[i] = 0; }
+    void drop_pk_tables() { pnl_nz = 0; for (int i = 0; i < PK_SLOTS; ++i) store_nz[i] = 0; ++pk_gen; }
 };
 
 namespace lbg {

@@ -1,0 +1,218 @@
+// halofit.cu -- HALOFIT spectral parameters (k_nl, n_eff, curvature) for every redshift of a z grid on the device, and the
+// P(k, z) rows built from them without a host round trip.  Replaces modi/halofit.py:70-98 (`_get_spec`: two quintic
+// InterpolatedUnivariateSpline fits per redshift + an inverse evaluation + two derivatives) as modi/cosmology.py:171-179 applies
+// it at every z node.
+//
+//   sigma_0^2(R_i), 500 nodes            sigma2_kernel (limber.cu), once per linear table
+//   R_nl(z): ln sigma^2(R, z) = 0        ln sigma^2(R, z) = ln D(z)^2 + ln sigma_0^2(R), and an interpolating spline commutes with a
+//                                        shift of its abscissae, so ONE inverse fit at z = 0 (host, FITPACK order, fitpack.cuh)
+//                                        evaluated at -ln D^2 gives ln R_nl(z) (1e-14 against the reference's per-z inverse fits)
+//   n_eff, C at ln(1/R_nl)               first / second derivative of the quintic spline through ln(D^2 sigma_0^2(R_i)): fitted PER
+//                                        REDSHIFT in FITPACK's own operation order -- the second derivative amplifies the fit's
+//                                        rounding by ~1e4, so only the same statements give the same C (fitpack.cuh).  The rotations
+//                                        depend on the ln R grid alone: factored once on the host, applied by one device thread per z.
+//   P(k, z) rows                         pnl_kernel (limber.cu)
+// Redshifts whose R_nl leaves the tabulated decade (the reference's `except` branch) are flagged and left to the caller.
+#include "common.cuh"
+#include "pk_kernels.cuh"
+#include "fitpack.cuh"
+#include <cmath>
+#include <algorithm>
+
+namespace lbg {
+#define HF_MAX_R 512
+// One thread per redshift: y_i = ln(D^2 sigma_0^2(R_i)), FITPACK right-hand-side rotations + back-substitution, derivatives at x_nl.
+__global__ void __launch_bounds__(64)
+halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const double* __restrict__ tknots, const int* __restrict__ lint,
+                    const double* __restrict__ rot, const double* __restrict__ band, const double* __restrict__ in /*[n][8]: D2, rknl, x_nl, omz, ovz, use, -, -*/,
+                    HaloZ* __restrict__ rows) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_rows) return;
+    const double* q = in + (size_t)r * 8;
+    HaloZ h;
+    h.D2 = q[0]; h.rknl = 1.0; h.neff = 0.0; h.ncur = 0.0; h.omz = q[3]; h.ovz = q[4]; h.use_halofit = q[5]; h.pad = 0.0;
+    if (q[5] != 0.0) {
+        double y[HF_MAX_R], z[HF_MAX_R];
+        for (int i = 0; i < m; ++i) y[i] = log(q[0] * s0[i]);
+        fitpack::fit_apply(m, lint, rot, band, y, z, y);          // coefficients overwrite y (fpback reads z only)
+        double d[6];
+        const bool ok = fitpack::spalde(tknots, m + 6, y, q[2], d);
+        h.rknl = q[1];
+        h.neff = ok ? -d[1] - 3.0 : nan("");
+        h.ncur = ok ? -d[2] : nan("");
+    }
+    rows[r] = h;
+}
+}  // namespace lbg
+
+using namespace lbg;
+
+namespace {
+struct HfGrid {                     // per process: the ln R grid the reference fits on, factored once (host) 
+    std::mutex mu;
+    std::vector<double> lnr;
+    fitpack::FitFactor F;
+};
+HfGrid g_hf;
+}
+
+struct lbg_hf_state {               // per context: device copies of the factor, sigma_0^2 on the grid for the current linear table
+    std::vector<double> lnr, s0, lns0_rev, lnr_rev, inv_t, inv_c;
+    unsigned long long pk_gen = ~0ull;
+    lbg::DevBuf dev;                // [s0 m | t m+6 | rot 12 m | band 6 m | lint m (int)]
+    bool dev_ok = false;
+};
+
+void lbg_hf_release(lbg_ctx* c) { if (c->hf) { c->hf->dev.release(); delete c->hf; c->hf = nullptr; } }
+
+// modi/halofit.py:70-98 on the host, FITPACK order: lnr increasing, lnsig = ln sigma^2 on it.  out = (rknl = k_nl = 1 / R_nl, neff, ncur).
+// *status: 0 ok; 1 = the derivative point ln(1 / rknl) lies outside the fitted range (scipy raises there: the reference's except branch).
+// rknl_in > 0: the inverse fit is skipped and that R_nl is used (the refit of the except branch, :82-96).
+extern "C" int lbg_halofit_spec_host(int n, const double* lnr, const double* lnsig, double rknl_in, double* out, int* status) {
+    LBG_REQUIRE(lnr && lnsig && out && status && n >= 7 && n <= 100000, "lbg_halofit_spec_host: bad argument");
+    fitpack::FitFactor inv, fwd;
+    std::vector<double> c(n);
+    double rknl = rknl_in;
+    if (!(rknl_in > 0.0)) {
+        std::vector<double> xr(n), yr(n);
+        for (int i = 0; i < n; ++i) { xr[i] = lnsig[n - 1 - i]; yr[i] = lnr[n - 1 - i]; }
+        LBG_REQUIRE(inv.build(n, xr.data()), "lbg_halofit_spec_host: ln sigma^2 must be strictly decreasing in R (scipy: x must be strictly increasing)");
+        inv.solve(yr.data(), c.data());
+        rknl = 1.0 / exp(fitpack::splev(inv.t.data(), inv.n, c.data(), 0.0));
+    }
+    LBG_REQUIRE(fwd.build(n, lnr), "lbg_halofit_spec_host: ln R must be strictly increasing");
+    fwd.solve(lnsig, c.data());
+    double d[6];
+    out[0] = rknl;
+    if (!fitpack::spalde(fwd.t.data(), fwd.n, c.data(), log(1.0 / rknl), d)) { *status = 1; out[1] = out[2] = nan(""); return LBG_OK; }
+    out[1] = -d[1] - 3.0;
+    out[2] = -d[2];
+    *status = 0;
+    return LBG_OK;
+}
+
+// Device-side table build for one z grid.  zin[n_rows][4] = {D(z)^2, Omega_m(z), Omega_L(z), use_halofit (0 -> linear row)};
+// lnr / R: the reference's fitting grid (np.linspace(ln 0.1, ln 10, 500) and its exp, modi/halofit.py:36-37) as the caller's numpy
+// computed them.  out_spec (may be NULL): [n_rows][4] = {k_nl = 1 / R_nl (the reference's `rknl`), n_eff, curvature, flag}; flag 1 = R_nl outside the tabulated
+// decade (the caller evaluates that row by the reference's exception path and passes it through lbg_pk_build_table).
+// *n_flagged receives the number of flagged rows; the table is built (and made current) only when it is 0 or build = 0 was asked.
+extern "C" int lbg_pk_build_table_hf(lbg_ctx* c, int n_rows, const double* zin, int n_R, const double* lnr, const double* R,
+                                     double fnu, double om0, double w, int takahashi, int build, double* out_spec, int* n_flagged,
+                                     double* out_pnl) {
+    LBG_REQUIRE(c && zin && lnr && R && n_flagged && n_rows > 0, "lbg_pk_build_table_hf: bad argument");
+    LBG_REQUIRE(n_R >= 7 && n_R <= HF_MAX_R, "lbg_pk_build_table_hf: n_R=%d outside [7, %d]", n_R, HF_MAX_R);
+    std::lock_guard<std::mutex> g(c->mu);
+    if (c->n_k <= 0) { set_error("lbg_pk_build_table_hf: call lbg_upload_pk_linear first"); return LBG_ESTATE; }
+    LBG_CUDA(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    if (!c->hf) c->hf = new lbg_hf_state();
+    lbg_hf_state& H = *c->hf;
+    const int m = n_R;
+    int launches = 0;
+    KernelTimer t(c);
+    // ---- the grid's factorisation (per process) and its device copy (per context) ----
+    const bool grid_same = (int)H.lnr.size() == m && !memcmp(H.lnr.data(), lnr, (size_t)m * 8);
+    if (!grid_same || !H.dev_ok) {
+        std::lock_guard<std::mutex> gg(g_hf.mu);
+        if ((int)g_hf.lnr.size() != m || memcmp(g_hf.lnr.data(), lnr, (size_t)m * 8)) {
+            LBG_REQUIRE(g_hf.F.build(m, lnr), "lbg_pk_build_table_hf: ln R grid must be strictly increasing");
+            g_hf.lnr.assign(lnr, lnr + m);
+        }
+        const size_t nd = (size_t)m + (m + 6) + 12 * (size_t)m + 6 * (size_t)m;
+        if (H.dev.reserve(nd * 8 + (size_t)m * 4 + 64)) return LBG_ENOMEM;
+        double* d = H.dev.as<double>();
+        LBG_CUDA(cudaMemcpyAsync(d + m, g_hf.F.t.data(), (size_t)(m + 6) * 8, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaMemcpyAsync(d + m + (m + 6), g_hf.F.rot.data(), (size_t)12 * m * 8, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaMemcpyAsync(d + m + (m + 6) + 12 * (size_t)m, g_hf.F.a.data(), (size_t)6 * m * 8, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaMemcpyAsync(d + nd, g_hf.F.lint.data(), (size_t)m * 4, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaStreamSynchronize(st));
+        H.lnr.assign(lnr, lnr + m);
+        H.dev_ok = true;
+        H.pk_gen = ~0ull;
+    }
+    double* d = H.dev.as<double>();
+    double* d_s0 = d;
+    const double* d_t = d + m;
+    const double* d_rot = d_t + (m + 6);
+    const double* d_band = d_rot + 12 * (size_t)m;
+    const int* d_lint = reinterpret_cast<const int*>(d_band + 6 * (size_t)m);
+    // ---- sigma_0^2 on the grid + the z = 0 inverse fit: once per linear table ----
+    if (H.pk_gen != c->pk_gen) {
+        if (c->s0.reserve((size_t)m * 8)) return LBG_ENOMEM;
+        LBG_CUDA(cudaMemcpyAsync(c->s0.p, R, (size_t)m * 8, cudaMemcpyHostToDevice, st));
+        const double* kd = c->pk_lnk.as<double>();
+        sigma2_kernel<<<m, 256, 0, st>>>(c->n_k, kd, kd + 2 * (size_t)c->n_k, c->s0.as<double>(), d_s0);
+        ++launches;
+        H.s0.resize(m);
+        LBG_CUDA(cudaMemcpyAsync(H.s0.data(), d_s0, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+        LBG_CUDA(cudaStreamSynchronize(st));
+        H.lns0_rev.resize(m); H.lnr_rev.resize(m);
+        bool mono = true;
+        for (int i = 0; i < m; ++i) { H.lns0_rev[i] = log(H.s0[m - 1 - i]); H.lnr_rev[i] = lnr[m - 1 - i]; }
+        for (int i = 1; i < m; ++i) mono = mono && H.lns0_rev[i] > H.lns0_rev[i - 1];
+        LBG_REQUIRE(mono, "lbg_pk_build_table_hf: sigma^2(R) of this table is not strictly decreasing on the grid");
+        fitpack::FitFactor inv;
+        inv.build(m, H.lns0_rev.data());
+        H.inv_t = inv.t;
+        H.inv_c.resize(m);
+        inv.solve(H.lnr_rev.data(), H.inv_c.data());
+        H.pk_gen = c->pk_gen;
+    }
+    // ---- per row: R_nl from the inverse fit (host, n splev), flags ----
+    const size_t in_bytes = (size_t)n_rows * 64;
+    if (c->pin_in.reserve(in_bytes) || c->s1.reserve(in_bytes) || c->s5.reserve((size_t)n_rows * sizeof(HaloZ)) ||
+        c->pin_out.reserve((size_t)n_rows * sizeof(HaloZ)))
+        return LBG_ENOMEM;
+    double* hin = c->pin_in.as<double>();
+    const double lo = H.lns0_rev[0], hi = H.lns0_rev[m - 1];
+    int flagged = 0;
+    std::vector<unsigned char> flag(n_rows, 0);
+    for (int r = 0; r < n_rows; ++r) {
+        const double D2 = zin[4 * r], use = zin[4 * r + 3];
+        double rknl = 1.0, x = 0.0;
+        if (use != 0.0) {
+            const double tt = -log(D2);
+            const double lnR = fitpack::splev(H.inv_t.data(), m + 6, H.inv_c.data(), tt);
+            rknl = 1.0 / exp(lnR);
+            x = log(1.0 / rknl);
+            if (!(tt > lo && tt < hi && lnR > lnr[0] && lnR < lnr[m - 1])) { flag[r] = 1; ++flagged; }
+        }
+        double* q = hin + 8 * (size_t)r;
+        q[0] = D2; q[1] = rknl; q[2] = x; q[3] = zin[4 * r + 1]; q[4] = zin[4 * r + 2]; q[5] = flag[r] ? 0.0 : use; q[6] = q[7] = 0.0;
+    }
+    *n_flagged = flagged;
+    LBG_CUDA(cudaMemcpyAsync(c->s1.p, hin, in_bytes, cudaMemcpyHostToDevice, st));
+    halofit_spec_kernel<<<(n_rows + 63) / 64, 64, 0, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, c->s1.as<double>(), c->s5.as<HaloZ>());
+    ++launches;
+    const bool do_build = build && flagged == 0;
+    const int n_k = c->n_k;
+    if (do_build) {
+        if (c->pk_pnl.reserve((size_t)n_rows * n_k * 8)) return LBG_ENOMEM;
+        HaloConst hc{fnu, om0, w, takahashi};
+        const double* kd = c->pk_lnk.as<double>();
+        pnl_kernel<<<dim3((n_k + 127) / 128, n_rows), 128, 0, st>>>(n_rows, n_k, kd, kd + n_k, c->s5.as<HaloZ>(), hc, c->pk_pnl.as<double>());
+        ++launches;
+        if (out_pnl) LBG_CUDA(cudaMemcpyAsync(out_pnl, c->pk_pnl.p, (size_t)n_rows * n_k * 8, cudaMemcpyDeviceToHost, st));
+    }
+    if (out_spec) LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, c->s5.p, (size_t)n_rows * sizeof(HaloZ), cudaMemcpyDeviceToHost, st));
+    t.launched(launches);
+    const int rc = t.finish();
+    if (rc) return rc;
+    if (out_spec) {
+        const HaloZ* hz = c->pin_out.as<HaloZ>();
+        for (int r = 0; r < n_rows; ++r) {
+            out_spec[4 * r] = hz[r].rknl; out_spec[4 * r + 1] = hz[r].neff; out_spec[4 * r + 2] = hz[r].ncur; out_spec[4 * r + 3] = flag[r];
+        }
+    }
+    if (do_build) c->pnl_nz = n_rows;
+    return LBG_OK;
+}
+
+// Number of k nodes of the linear table installed on the context (0: none): callers size their host buffers for
+// lbg_pk_build_table / lbg_pk_build_table_hf output with it.
+extern "C" int lbg_pk_table_nk(lbg_ctx* c, int* n_k) {
+    LBG_REQUIRE(c && n_k, "lbg_pk_table_nk: NULL argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    *n_k = c->n_k;
+    return LBG_OK;
+}

@@ -1,0 +1,90 @@
+// pk_kernels.cuh -- the two matter-power kernels shared by limber.cu (explicit-row table builds) and halofit.cu (device-side spectral
+// parameters): sigma^2(R) integrals (modi/halofit.py:36-44) and the Takahashi / Smith formula on every table node (:139-212).
+#pragma once
+#include "common.cuh"
+#include <cmath>
+
+namespace lbg {
+
+// sigma0^2(R) = sum_i w_i Delta0^2(k_i) exp(-(k_i R)^2): one block per R.  w = scipy-1.2.1 simps weights in ln k.
+static __global__ void __launch_bounds__(256)
+sigma2_kernel(int n_k, const double* __restrict__ k, const double* __restrict__ d2w /*Delta0^2 * w*/,
+              const double* __restrict__ R, double* __restrict__ out) {
+    __shared__ double sm[256];
+    const double r = R[blockIdx.x];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n_k; i += 256) {
+        const double kr = k[i] * r;
+        acc += d2w[i] * exp(-(kr * kr));
+    }
+    sm[threadIdx.x] = acc;
+    __syncthreads();
+    for (int h = 128; h > 0; h >>= 1) {
+        if (threadIdx.x < h) sm[threadIdx.x] += sm[threadIdx.x + h];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[blockIdx.x] = sm[0];
+}
+
+struct HaloZ {           // per-redshift HALOFIT inputs (modi/halofit.py:139-199)
+    double D2;           // growth^2 applied to the z=0 table (modi/cosmology.py:160,175)
+    double rknl, neff, ncur, omz, ovz;
+    double use_halofit;  // 0 -> linear row (z > 4, modi/cosmology.py:171-172)
+    double pad;
+};
+
+struct HaloConst { double fnu, om0, w; int takahashi; };
+
+// One thread per (z, k) table node: P_nl(k, z) [(Mpc/h)^3] from Delta_lin^2 = P0 k^3 D^2 / (2 pi^2).
+static __global__ void pnl_kernel(int n_z, int n_k, const double* __restrict__ k, const double* __restrict__ p0,
+                           const HaloZ* __restrict__ hz, HaloConst hc, double* __restrict__ out) {
+    const int ik = blockIdx.x * blockDim.x + threadIdx.x;
+    const int iz = blockIdx.y;
+    if (ik >= n_k) return;
+    const HaloZ h = hz[iz];
+    const double kk = k[ik];
+    const double twopi2 = 2.0 * 3.14159265358979323846 * 3.14159265358979323846;
+    const double plin_dim = p0[ik] * (kk * kk * kk) / twopi2 * h.D2;     // modi/cosmology.py:174-175
+    double res = plin_dim;
+    if (h.use_halofit != 0.0 && kk > 0.005) {                             // modi/halofit.py:139
+        const double neff = h.neff, rncur = h.ncur, w = hc.w, fnu = hc.fnu;
+        const double n2 = neff * neff, n3 = n2 * neff, n4 = n2 * n2;
+        double a, b, c, gam, alpha, beta, xmu, xnu;
+        if (hc.takahashi) {                                               // modi/halofit.py:152-166
+            a = pow(10.0, 1.5222 + 2.8553 * neff + 2.3706 * n2 + 0.9903 * n3 + 0.2250 * n4 - 0.6038 * rncur + 0.1749 * h.ovz * (1 + w));
+            b = pow(10.0, -0.5642 + 0.5864 * neff + 0.5716 * n2 - 1.5474 * rncur + 0.2279 * h.ovz * (1 + w));
+            c = pow(10.0, 0.3698 + 2.0404 * neff + 0.8161 * n2 + 0.5869 * rncur);
+            gam = 0.1971 - 0.0843 * neff + 0.8460 * rncur;
+            alpha = fabs(6.0835 + 1.3373 * neff - 0.1959 * n2 - 5.5274 * rncur);
+            beta = 2.0379 - 0.7354 * neff + 0.3157 * n2 + 1.2490 * n3 + 0.3980 * n4 - 0.1682 * rncur + fnu * (1.081 + 0.395 * n2);
+            xmu = 0.0;
+            xnu = pow(10.0, 5.2105 + 3.6902 * neff);
+        } else {                                                          // modi/halofit.py:168-180 (Smith+03)
+            a = pow(10.0, 1.4861 + 1.8369 * neff + 1.6762 * n2 + 0.7940 * n3 + 0.1670 * n4 - 0.6206 * rncur);
+            b = pow(10.0, 0.9463 + 0.9466 * neff + 0.3084 * n2 - 0.94 * rncur);
+            c = pow(10.0, -0.2807 + 0.6669 * neff + 0.3214 * n2 - 0.0793 * rncur);
+            gam = 0.8649 + 0.2989 * neff + 0.1631 * rncur;
+            alpha = fabs(1.3884 + 0.3700 * neff - 0.1452 * n2);
+            beta = 0.8291 + 0.9854 * neff + 0.3401 * n2;
+            xmu = pow(10.0, -3.5442 + 0.1908 * neff);
+            xnu = pow(10.0, 0.9589 + 1.2857 * neff);
+        }
+        double f1 = 1.0, f2 = 1.0, f3 = 1.0;
+        if (fabs(1 - h.omz) > 0.01) {                                     // modi/halofit.py:183-199
+            const double f1a = pow(h.omz, -0.0732), f2a = pow(h.omz, -0.1423), f3a = pow(h.omz, 0.0725);
+            const double f1b = pow(h.omz, -0.0307), f2b = pow(h.omz, -0.0585), f3b = pow(h.omz, 0.0743);
+            const double frac = h.ovz / (1 - h.omz);
+            if (hc.takahashi) { f1 = f1b; f2 = f2b; f3 = f3b; }
+            else { f1 = frac * f1b + (1 - frac) * f1a; f2 = frac * f2b + (1 - frac) * f2a; f3 = frac * f3b + (1 - frac) * f3a; }
+        }
+        const double y = kk / h.rknl;                                     // modi/halofit.py:201-212
+        double ph = a * pow(y, f1 * 3) / (1 + b * pow(y, f2) + pow(f3 * c * y, 3 - gam));
+        ph = ph / (1 + xmu / y + xnu / (y * y)) * (1 + fnu * (0.977 - 18.015 * (hc.om0 - 0.3)));
+        const double plinaa = plin_dim * (1 + fnu * 47.48 * kk * kk / (1 + 1.5 * kk * kk));
+        const double pq = plin_dim * pow(1 + plinaa, beta) / (1 + plinaa * alpha) * exp(-y / 4.0 - y * y / 8.0);
+        res = pq + ph;
+    }
+    out[(size_t)iz * n_k + ik] = res * twopi2 / (kk * kk * kk);           // modi/cosmology.py:179
+}
+
+}  // namespace lbg

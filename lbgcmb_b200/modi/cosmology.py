@@ -16,6 +16,9 @@ from lbgcmb_b200.quadrature import simps_weights_x, romberg
 
 _owner = _ffi.table_owner
 _PK_SLOTS = 4                            # lbg_ctx::PK_SLOTS
+# the grid modi/halofit.py:36-37 fits ln sigma^2 on, and its exp, as numpy computes them
+_HF_LNR = _ffi.f64(np.linspace(np.log(0.1), np.log(10.0), 500))
+_HF_R = _ffi.f64(np.exp(_HF_LNR))
 
 
 LOGA_NODES = np.linspace(-20., 0, 1000)            # modi/cosmology.py:98-101
@@ -62,10 +65,11 @@ class Cosmology(object):
             y = growth_tables([M], [L], device=device)[0] if isinstance(Dplus_table, str) else np.asarray(Dplus_table, dtype=np.float64)
             self.Dplus = interpolate(np.exp(LOGA_NODES), y)
         self.device = device
+        self._token = _ffi.new_owner_token()      # identifies this object's table on a context (id() is reused by CPython)
+        self._wlnk = None
         self._sig0 = None
         self._spec_cache = {}
-        self._spl0 = None
-        self._rows_cache = {}
+        self._bg_cache = {}              # per z grid: D(z)^2, Omega_m(z), Omega_L(z) -- the background, independent of the P(k) table
         self._rows_key = None
         self._slots = {}                 # z-grid key -> device table slot (lbg_pk_select_slot); insertion order = LRU order
         self._cur_slot = 0
@@ -132,21 +136,25 @@ class Cosmology(object):
     # ---- P(k, z) (device) ---------------------------------------------------------------------------------------
     def _ctx(self):
         ctx = _ffi.context(self.device)
-        if _owner.get(ctx.device) != id(self):
-            k, p = _ffi.f64(self.klin), _ffi.f64(self.plin)
-            w = _ffi.f64(simps_weights_x(np.log(k)))
-            _ffi.check(_ffi.lib().lbg_upload_pk_linear(ctx.handle, k.size, _ffi._dp(k), _ffi._dp(p), _ffi._dp(w)))
-            _owner[ctx.device] = id(self)
+        k, p = _ffi.f64(self.klin), _ffi.f64(self.plin)
+        owner = (self._token, _ffi.table_digest(k, p))           # the digest catches tables edited in place
+        if _owner.get(ctx.device) != owner:
+            if self._wlnk is None or self._wlnk.size != k.size:
+                self._wlnk = _ffi.f64(simps_weights_x(np.log(k)))
+            _ffi.check(_ffi.lib().lbg_upload_pk_linear(ctx.handle, k.size, _ffi._dp(k), _ffi._dp(p), _ffi._dp(self._wlnk)))
+            _owner[ctx.device] = owner
             self._rows_key = None
             self._slots = {}             # the upload dropped every P(k,z) table of the context
+            self._sig0 = None
+            self._spec_cache = {}
         return ctx
 
     def invalidate_device(self):
         """Forget what this object has on the GPU: the next call uploads the linear table and rebuilds the P(k,z) rows."""
-        if _owner.get(_ffi.context(self.device).device) == id(self):
-            _owner[_ffi.context(self.device).device] = None
+        dev = _ffi.context(self.device).device
+        if (_owner.get(dev) or (None,))[0] == self._token:
+            _owner[dev] = None
         self._rows_key = None
-        self._rows_cache = {}
         self._slots = {}
 
     def _sigma2_z0(self, R):
@@ -157,31 +165,38 @@ class Cosmology(object):
         return out
 
     def halofit_spec(self, z, sig8=None):
-        """(k_nl, n_eff, curvature) at redshift z: modi/halofit.py:7-100 applied to Delta^2_lin(k) D(z)^2 (the per-z
-        route: its own pair of quintic fits, exactly as the reference does for every call)."""
+        """(k_nl, n_eff, curvature) at redshift z: modi/halofit.py:7-100 applied to Delta^2_lin(k) D(z)^2 (its own pair of quintic
+        fits on the host, exactly as the reference does for every call; FITPACK order, csrc/fitpack.cuh)."""
         sig8 = self.sig8 if sig8 is None else sig8
+        self._ctx()
         key = (float(z), float(sig8))
         if key not in self._spec_cache:
             D2 = float(self.Dgrow(z=z)) ** 2.
-            if sig8 < 1.0 and sig8 > 0.6 and self._sig0 is None:
-                lnr = np.linspace(np.log(0.1), np.log(10.0), 500)
-                self._sig0 = (lnr, self._sigma2_z0(np.exp(lnr)))
             if sig8 < 1.0 and sig8 > 0.6:
-                lnr, s0 = self._sig0
-                spec = _hf.spec_from_lnsig(lnr, np.log(D2 * s0), lambda R: D2 * self._sigma2_z0(R))
+                if self._sig0 is None:
+                    self._sig0 = self._sigma2_z0(_HF_R)
+                spec = _hf.spec_from_lnsig(_HF_LNR, np.log(D2 * self._sig0), lambda R: D2 * self._sigma2_z0(R))
             else:
                 spec = _hf._get_spec_from(lambda R: D2 * self._sigma2_z0(R), sig8)
             self._spec_cache[key] = spec
         return self._spec_cache[key]
 
-    def halofit_specs(self, zs, D2, sig8=None):
-        """halofit_spec for many redshifts at once -> [n, 3].
+    def _device_specs(self, ctx, zin, build):
+        """lbg_pk_build_table_hf on rows zin[n, 4] = (D^2, Omega_m(z), Omega_L(z), use_halofit): (spec[n, 4], n_flagged)."""
+        import ctypes as C
+        spec = np.empty((zin.shape[0], 4))
+        nflag = C.c_int(0)
+        fnu = self.cosmo.Onu0 / self.cosmo.Om0
+        _ffi.check(_ffi.lib().lbg_pk_build_table_hf(ctx.handle, zin.shape[0], _ffi._dp(zin), _HF_LNR.size, _ffi._dp(_HF_LNR), _ffi._dp(_HF_R),
+                                                    float(fnu), float(self.cosmo.Om0), -1.0, 1, int(build), _ffi._dp(spec), C.byref(nflag), None))
+        return spec, nflag.value
 
-        ln sigma^2(R, z) = ln D(z)^2 + ln sigma_0^2(R), and the interpolating quintic splines of modi/halofit.py:70-76 commute
-        with a constant shift of the ordinate (inverse spline: of the abscissa), so ONE pair of fits at z = 0 serves every z:
-        R_nl(z) = r_of_sig0(-ln D^2), derivatives of sig_of_r0 at ln R_nl.  Same arithmetic as the reference up to the
-        rounding of the shift (measured < 1e-12 on k_nl, n_eff, C against the per-z fits); redshifts whose R_nl leaves the
-        tabulated decade fall back to the per-z route, which reproduces the reference's exception path."""
+    def halofit_specs(self, zs, D2, sig8=None):
+        """halofit_spec for many redshifts at once -> [n, 3] = (k_nl, n_eff, curvature), on the device (csrc/halofit.cu): R_nl(z) from
+        one inverse fit at z = 0 evaluated at -ln D^2 (ln sigma^2(R, z) = ln D^2 + ln sigma_0^2(R); 1e-14 against per-z inverse fits),
+        n_eff and the curvature from a per-redshift quintic fit in FITPACK order (one device thread per redshift).  Redshifts whose
+        R_nl leaves the tabulated decade, and unusual sigma_8, take the per-z host route, which reproduces the reference's other
+        branches."""
         sig8 = self.sig8 if sig8 is None else sig8
         zs, D2 = np.asarray(zs, dtype=np.float64), np.asarray(D2, dtype=np.float64)
         out = np.empty((zs.size, 3))
@@ -189,23 +204,14 @@ class Cosmology(object):
             for i, z in enumerate(zs):
                 out[i] = self.halofit_spec(z, sig8)
             return out
-        if self._sig0 is None:
-            lnr = np.linspace(np.log(0.1), np.log(10.0), 500)
-            self._sig0 = (lnr, self._sigma2_z0(np.exp(lnr)))
-        if self._spl0 is None:
-            lnr, s0 = self._sig0
-            lns0 = np.log(s0)
-            fwd = interpolate(lnr, lns0, k=5)
-            self._spl0 = (interpolate(lns0[::-1], lnr[::-1], k=5), fwd.derivative(1), fwd.derivative(2), lns0.min(), lns0.max())
-        inv0, d1, d2, lo, hi = self._spl0
-        t = -np.log(D2)
-        lnR = inv0(t)
-        ok = (t > lo) & (t < hi) & (lnR > self._sig0[0][0]) & (lnR < self._sig0[0][-1])
-        out[:, 0] = 1.0 / np.exp(lnR)
-        x = np.log(1.0 / out[:, 0])
-        out[:, 1] = -d1(x) - 3.0
-        out[:, 2] = -d2(x)
-        for i in np.nonzero(~ok)[0]:
+        ctx = self._ctx()
+        zin = np.zeros((zs.size, 4))
+        zin[:, 0] = D2
+        zin[:, 3] = 1.0
+        spec, _ = self._device_specs(ctx, _ffi.f64(zin), build=False)
+        out[:, 0] = spec[:, 0]
+        out[:, 1:3] = spec[:, 1:3]
+        for i in np.nonzero(spec[:, 3] != 0.0)[0]:
             out[i] = self.halofit_spec(zs[i], sig8)
         return out
 
@@ -234,27 +240,50 @@ class Cosmology(object):
                 old = next(k for k, v in self._slots.items() if v in pool)   # least recently used
                 slot = self._slots.pop(old)
         self._select_slot(ctx, slot)
-        rows = self._rows_cache.get(key)        # per z grid: D^2, k_nl, n_eff, C, Omega_m(z), Omega_L(z) (dropped by invalidate_device)
-        if rows is None:
-            rows = np.zeros((zs.size, 8))
+        bg = self._bg_cache.get(key)            # per z grid: D^2, Omega_m(z), Omega_L(z), use_halofit (the background: kept across table rebuilds)
+        if bg is None:
+            bg = np.zeros((zs.size, 4))
             aa = self.ztoa(zs)
-            rows[:, 0] = (self.Dplus(aa) / self.Dplus(1.)) ** 2.                 # Dgrow(z)^2, modi/cosmology.py:113-117
-            rows[:, 1] = 1.0
+            bg[:, 0] = (self.Dplus(aa) / self.Dplus(1.)) ** 2.                   # Dgrow(z)^2, modi/cosmology.py:113-117
             if nonlinear:
                 hf = ~(zs > zmax_halofit)                                         # modi/cosmology.py:171
-                if np.any(hf):
-                    zz = self.atoz(aa[hf])
-                    rows[hf, 1:4] = self.halofit_specs(zs[hf], rows[hf, 0], sig8)
-                    rows[hf, 4] = self.cosmo.Om(zz)
-                    rows[hf, 5] = self.cosmo.Ode(zz)
-                    rows[hf, 6] = 1.0
-            if len(self._rows_cache) >= 16:
-                self._rows_cache.clear()
-            self._rows_cache[key] = rows
+                zz = self.atoz(aa[hf])
+                bg[hf, 1] = self.cosmo.Om(zz)
+                bg[hf, 2] = self.cosmo.Ode(zz)
+                bg[hf, 3] = 1.0
+            bg = _ffi.f64(bg)
+            if len(self._bg_cache) >= 16:
+                self._bg_cache.clear()
+            self._bg_cache[key] = bg
+        import ctypes as C
+        nk = C.c_int(0)
+        _ffi.check(_ffi.lib().lbg_pk_table_nk(ctx.handle, C.byref(nk)))
+        if nk.value != len(self.klin):
+            raise RuntimeError('the context holds a %d-node k grid, this object has %d' % (nk.value, len(self.klin)))
         out = np.empty((zs.size, len(self.klin))) if want_host else None
         fnu = self.cosmo.Onu0 / self.cosmo.Om0
-        _ffi.check(_ffi.lib().lbg_pk_build_table(ctx.handle, zs.size, _ffi._dp(_ffi.f64(rows)), float(fnu), float(self.cosmo.Om0),
-                                                 -1.0, 1, _ffi._dp(out) if want_host else None))
+        std_sig8 = (self.sig8 if sig8 is None else sig8)
+        std_sig8 = std_sig8 < 1.0 and std_sig8 > 0.6
+        done = False
+        if std_sig8 or not np.any(bg[:, 3]):
+            # spectral parameters and rows on the device in one call (no host round trip); flagged rows -> explicit route below
+            nflag = C.c_int(0)
+            _ffi.check(_ffi.lib().lbg_pk_build_table_hf(ctx.handle, zs.size, _ffi._dp(bg), _HF_LNR.size, _ffi._dp(_HF_LNR), _ffi._dp(_HF_R),
+                                                        float(fnu), float(self.cosmo.Om0), -1.0, 1, 1, None, C.byref(nflag),
+                                                        _ffi._dp(out) if want_host else None))
+            done = nflag.value == 0
+        if not done:
+            rows = np.zeros((zs.size, 8))
+            rows[:, 0] = bg[:, 0]
+            rows[:, 1] = 1.0
+            hf = bg[:, 3] != 0.0
+            if np.any(hf):
+                rows[hf, 1:4] = self.halofit_specs(zs[hf], rows[hf, 0], sig8)
+                rows[hf, 4] = bg[hf, 1]
+                rows[hf, 5] = bg[hf, 2]
+                rows[hf, 6] = 1.0
+            _ffi.check(_ffi.lib().lbg_pk_build_table(ctx.handle, zs.size, _ffi._dp(_ffi.f64(rows)), float(fnu), float(self.cosmo.Om0),
+                                                     -1.0, 1, _ffi._dp(out) if want_host else None))
         self._rows_key = key
         self._slots[key] = slot
         return out

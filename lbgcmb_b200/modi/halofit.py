@@ -1,11 +1,14 @@
 """HALOFIT; mirrors reference modi/halofit.py:7-214 (`_get_spec`, `halofit`), itself a copy of hmf's.
 
-Device work (csrc/limber.cu): the sigma^2(R) Simpson integrals over the k table (`sigma2_kernel`, halofit.py:36-44)
+Device work (csrc/pk_kernels.cuh): the sigma^2(R) Simpson integrals over the k table (`sigma2_kernel`, halofit.py:36-44)
 and the Smith/Takahashi formula on every table node (`pnl_kernel`, halofit.py:139-212).  The quintic-spline glue
-(k_nl, n_eff, curvature; halofit.py:70-98) runs on the host with the same scipy `InterpolatedUnivariateSpline(k=5)`
-the reference calls -- an analytic shortcut would miss 1e-10 (SURVEY.md "hard parts")."""
+(k_nl, n_eff, curvature; halofit.py:70-98) is the library's restatement of the FITPACK routines behind the reference's
+`InterpolatedUnivariateSpline(k=5)` (csrc/fitpack.cuh: same statements, same order, bit-identical coefficients and
+derivatives) -- an analytic shortcut, or any other correct spline code, misses 1e-10 on the curvature (SURVEY.md "hard
+parts").  For whole z grids the same fits run on the device (csrc/halofit.cu, lbg_pk_build_table_hf)."""
+import ctypes as _C
+
 import numpy as np
-from scipy.interpolate import InterpolatedUnivariateSpline as _spline
 
 from lbgcmb_b200 import _ffi
 from lbgcmb_b200.quadrature import simps_weights_x
@@ -20,7 +23,7 @@ class _DeviceTable(object):
         p0 = _ffi.f64(delta_k) * (2. * np.pi ** 2) / self.k ** 3
         w = _ffi.f64(simps_weights_x(np.log(self.k)))
         _ffi.check(_ffi.lib().lbg_upload_pk_linear(self.ctx.handle, self.k.size, _ffi._dp(self.k), _ffi._dp(p0), _ffi._dp(w)))
-        _ffi.table_owner[self.ctx.device] = id(self)
+        _ffi.table_owner[self.ctx.device] = (_ffi.new_owner_token(), None)      # a one-off table: nobody else's
 
     def sigma2(self, R):
         R = _ffi.f64(np.atleast_1d(R))
@@ -29,26 +32,33 @@ class _DeviceTable(object):
         return out
 
 
+def _spec_host(lnr, lnsig, rknl=0.0):
+    """(R_nl, n_eff, curvature), status: the two quintic fits of modi/halofit.py:70-78 in FITPACK order (lbg_halofit_spec_host)."""
+    lnr, lnsig = _ffi.f64(lnr), _ffi.f64(lnsig)
+    out = np.empty(3)
+    status = _C.c_int(0)
+    _ffi.check(_ffi.lib().lbg_halofit_spec_host(lnr.size, _ffi._dp(lnr), _ffi._dp(lnsig), float(rknl), _ffi._dp(out), _C.byref(status)))
+    return out, status.value
+
+
 def spec_from_lnsig(lnr, lnsig, sigma2_of_R=None):
     """k_nl, n_eff, curvature from samples of ln sigma^2(ln R); modi/halofit.py:70-98."""
-    r_of_sig = _spline(lnsig[::-1], lnr[::-1], k=5)
-    rknl = 1.0 / np.exp(r_of_sig(0.0))
-    sig_of_r = _spline(lnr, lnsig, k=5)
-    try:
-        dev1, dev2 = sig_of_r.derivatives(np.log(1.0 / rknl))[1:3]
-    except Exception as e:
+    out, status = _spec_host(lnr, lnsig)
+    rknl = out[0]
+    if status:                                                     # the reference's `except` branch (:79-96)
         if sigma2_of_R is None:
-            raise
-        print("WARNING: ", e)
+            raise ValueError('derivative point ln(1 / R_nl) outside the fitted range')
+        print("WARNING: ", 'derivative point ln(1 / R_nl) = %g outside the fitted range' % np.log(1.0 / rknl))
         lnr = np.linspace(np.log(0.2 / rknl), np.log(5 / rknl), 100)
         lnsig = np.log(sigma2_of_R(np.exp(lnr)))
         keep = np.logical_not(np.isinf(lnsig))
         lnr, lnsig = lnr[keep], lnsig[keep]
         if len(lnr) < 2:
             raise Exception("Lots of things went wrong in halofit")
-        sig_of_r = _spline(lnr, lnsig, k=5)
-        dev1, dev2 = sig_of_r.derivatives(np.log(1.0 / rknl))[1:3]
-    return rknl, -dev1 - 3.0, -dev2
+        out, status = _spec_host(lnr, lnsig, rknl=rknl)
+        if status:
+            raise Exception("Lots of things went wrong in halofit")
+    return rknl, out[1], out[2]
 
 
 def _get_spec_from(sigma2_of_R, sigma_8):

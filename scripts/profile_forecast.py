@@ -1,44 +1,58 @@
-"""cProfile of the host side of bench.py's forecast stage (run on the GPU box): python scripts/profile_forecast.py"""
-import cProfile
+"""Host-side phase breakdown of one forecast step at a given shard size (what bounds the strong scaling of bench.py --gpus N):
+  python scripts/profile_forecast.py [stride]      stride = 8 -> the 619-multipole shard one rank of an 8-GPU run evaluates
+Wall-clock microseconds per phase, median of 20 steps, N0 overlapped on the second context as in the bench."""
+import json
 import os
-import pstats
 import sys
 import time
+
 import numpy as np
+
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench
-from lbgcmb_b200 import interloper, pmh, snr, _ffi
+from lbgcmb_b200 import Nkk, _ffi, pmh, sweep
+from lbgcmb_b200.prep_camb import cl_interps_from_tables
 
+stride = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+li, ni = cl_interps_from_tables(*bench.make_inputs())
 kk, pp, bands = bench.forecast_inputs()
-Ls = np.arange(50, 5001).astype(np.float64)
-nkk = 1e-8 * np.ones_like(Ls)
-
-
+samples, xsamples = bench.band_samples(bands)
+smp = samples + xsamples
 T = pmh.PkTable(kk, pp)
 Pk = pmh.get_PkInterps(T)
+Ls = np.arange(50, 5001)[::stride]
+Lf = Ls.astype(np.float64)
+ctx1 = _ffi.context(None, 1)
+rec = {}
 
 
-def run():
+def tick(name, t0):
+    rec.setdefault(name, []).append((time.perf_counter() - t0) * 1e6)
+
+
+for rep in range(25):
     T.engine.invalidate_device()
-    return bench.forecast_stage((interloper, snr), Pk, bands, Ls, np.ones_like(Ls), nkk)
-
-
-for _ in range(2):
-    t = time.perf_counter(); run(); print('stage s', time.perf_counter() - t)
-ctx = _ffi.context()
-ctx.kernel_totals(reset=True)
-pr = cProfile.Profile(); pr.enable(); run(); pr.disable()
-print('kernel totals', ctx.kernel_totals())
-pstats.Stats(pr).sort_stats('tottime').print_stats(28)
-
-# host side of N0
-from lbgcmb_b200 import Nkk
-from lbgcmb_b200.prep_camb import cl_interps_from_tables
-ell, lens, nolens = bench.make_inputs()
-li, ni = cl_interps_from_tables(ell, lens, nolens)
-Li = np.arange(50, 5001)
-for _ in range(2):
-    Nkk.n0_terms(li, ni, Li, bench.TERMS, 1.4, 1.0, True)
-pr = cProfile.Profile(); pr.enable(); Nkk.n0_terms(li, ni, Li, bench.TERMS, 1.4, 1.0, True); pr.disable()
-print('n0 kernel ms', Nkk.last_stats)
-pstats.Stats(pr).sort_stats('cumulative').print_stats(20)
+    t_all = time.perf_counter()
+    t0 = time.perf_counter(); Nkk.upload_cls(ctx1, li, ni); tick('upload_cls (stack + compare)', t0)
+    t0 = time.perf_counter(); call = Nkk.n0_begin(li, ni, Ls, bench.TERMS, 1.4, 1.0, True, lane=1); tick('n0_begin (incl. upload_cls again)', t0)
+    t0 = time.perf_counter()
+    fine = np.arange(0.01, 10.0, 0.001)
+    for s in smp:
+        np.trapezoid(s['pz'](fine), fine)
+    tick('callables on the fine grid (8 samples)', t0)
+    eng = T.engine
+    from lbgcmb_b200.Cgg import _cgg_nodes
+    from lbgcmb_b200.Ckg import _ckg_nodes
+    from lbgcmb_b200.lensing import _ckk_nodes
+    t0 = time.perf_counter(); eng._ctx(); tick('linear table upload', t0)
+    for name, zs in (('gg', _cgg_nodes(0.01, 10.0)[0]), ('kg', _ckg_nodes(0.01, 10.0)[0]), ('kk', _ckk_nodes(1100.)[0])):
+        t0 = time.perf_counter(); eng.table_slot(zs); tick('P(k,z) table %s (specs + rows on the device)' % name, t0)
+    t0 = time.perf_counter(); ckk, cgg, ckg, ngg = sweep.forecast_spectra(Pk, Lf, smp); tick('forecast_spectra (tables parked; callables + 1 library call)', t0)
+    t0 = time.perf_counter(); nkk = call.result()[0]; tick('n0 wait', t0)
+    t0 = time.perf_counter()
+    sweep.forecast_grid(Lf, np.ones_like(Lf), ckk, cgg[:4], ckg[:4], ngg[:4], nkk[None, :], 0.4, 0.819, [s['fid_b1'] for s in samples],
+                        [s['LllMax'] for s in samples], xcgg=cgg[4:], xckg=ckg[4:], xngg=ngg[4:])
+    tick('forecast_grid', t0)
+    tick('TOTAL', t_all)
+out = {k: float(np.median(v[5:])) for k, v in rec.items()}
+print(json.dumps({'n_L': int(Ls.size), 'stride': stride, 'median_us': out}, indent=1))

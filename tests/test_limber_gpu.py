@@ -30,6 +30,67 @@ def test_halofit_golden(ctx, golden_dir):
         assert np.max(np.abs(got / g['delta_nl_smith'][i] - 1)) < RTOL, z
 
 
+def test_halofit_specs_per_redshift_golden(ctx, golden_dir):
+    """Cosmology.halofit_specs (device: one inverse fit at z = 0 + a per-redshift FITPACK-order forward fit, csrc/halofit.cu) against
+    the UNMODIFIED reference's `_get_spec` at every golden redshift: k_nl, n_eff AND the curvature to 1e-10 (the curvature is the
+    second derivative of an interpolating quintic spline: only the reference's own operation order gets there).  The table built
+    from them in the same call equals the explicit-row route."""
+    from lbgcmb_b200.modi.cosmology import Cosmology
+    from lbgcmb_b200.synthetic import PARAMS
+    g = _g(golden_dir, 'halofit.npz')
+    eng = Cosmology(M=PARAMS['om_m'], H0=100., B=PARAMS['om_b'], sig8=float(g['sig8']), klin=g['k'], plin=g['plin'])
+    got = eng.halofit_specs(g['zs'], g['D'] ** 2.)
+    assert got.shape == (g['zs'].size, 3)
+    rel = np.abs(got / g['spec'] - 1)
+    assert np.max(rel) < RTOL, rel
+    one = np.array([eng.halofit_spec(z) for z in g['zs']])            # per-z host route (both fits per redshift, as the reference)
+    assert np.max(np.abs(one / g['spec'] - 1)) < RTOL
+    # rows built on the device in the same call == rows from explicitly passed parameters
+    zs = np.array([0.0, 0.7, 2.5, 4.0, 6.0])
+    a = eng.build_rows(zs, want_host=True)
+    D2 = np.array([float(eng.Dgrow(z=z)) ** 2. for z in zs])
+    rows = np.zeros((zs.size, 8))
+    rows[:, 0] = D2
+    rows[:, 1] = 1.0
+    hf = zs <= 4.0
+    rows[hf, 1:4] = eng.halofit_specs(zs[hf], D2[hf])
+    rows[hf, 4], rows[hf, 5], rows[hf, 6] = eng.cosmo.Om(zs[hf]), eng.cosmo.Ode(zs[hf]), 1.0
+    from lbgcmb_b200 import _ffi
+    b = np.empty_like(a)
+    _ffi.check(_ffi.lib().lbg_pk_build_table(eng._ctx().handle, zs.size, _ffi._dp(_ffi.f64(rows)), 0.0, eng.cosmo.Om0, -1.0, 1, _ffi._dp(b)))
+    eng.invalidate_device()
+    assert np.max(np.abs(a / b - 1)) < 1e-13
+
+
+def test_two_tables_in_a_row_do_not_share_device_state(ctx, golden_dir):
+    """Two Cosmology / PkTable objects built one after the other in a helper (CPython hands the second the id() of the first):
+    ownership of the device table is by a never-reused token + a digest of the table, so each object's spectra are its own; a
+    table edited in place is uploaded again."""
+    from lbgcmb_b200 import pmh
+    g = _g(golden_dir, 'limber_root.npz')
+    L = np.array([100., 1000.])
+
+    def ckk_of(scale, n_k=None):
+        from lbgcmb_b200.lensing import Ckk
+        k, p = g['k'], g['plin'] * scale
+        if n_k:
+            k, p = k[::2][:n_k], p[::2][:n_k]
+        return Ckk(pmh.get_PkInterps(pmh.PkTable(k, p)), L)
+    a = ckk_of(1.0)
+    b = ckk_of(1.21)                       # same k grid, different P: linear part scales by 1.21, the non-linear part by more
+    assert np.all(b > 1.2 * a)
+    c = ckk_of(1.0)
+    assert np.array_equal(c, a)
+    d = ckk_of(1.0, n_k=900)               # another k grid length right after: no stale table, no buffer mismatch
+    assert np.all(np.isfinite(d)) and np.max(np.abs(d / a - 1)) < 0.05
+    T = pmh.PkTable(g['k'], g['plin'].copy())
+    from lbgcmb_b200.lensing import Ckk
+    Pk = pmh.get_PkInterps(T)
+    a1 = Ckk(Pk, L)
+    T.engine.plin *= 1.21                  # edited in place
+    assert np.array_equal(Ckk(Pk, L), b) and np.array_equal(a1, a)
+
+
 def test_sigma2_power_law_closed_form(ctx):
     """sigma^2(R) for Delta^2 = k^n on a wide grid: 0.5 Gamma(n/2) R^-n (SURVEY.md 8(c) closed forms)."""
     from math import gamma
