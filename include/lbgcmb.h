@@ -148,17 +148,22 @@ int lbg_pk_build_table(lbg_ctx* ctx, int n_rows, const double* halo_z, double fn
 int lbg_halofit_spec_host(int n, const double* lnr, const double* lnsig, double rknl_in, double* out /*[3]*/, int* status);
 /* Number of k nodes of the linear table installed on the context (0: none). */
 int lbg_pk_table_nk(lbg_ctx* ctx, int* n_k);
-/* The same for a whole z grid on the device, and the P(k,z) rows built from it (modi/cosmology.py:171-179 per node) without a host
- * round trip: zin[n_rows][4] = {D(z)^2, Omega_m(z), Omega_L(z), use_halofit}; lnr[n_R] / R[n_R] = the reference's fitting grid
- * np.linspace(ln 0.1, ln 10, 500) and its exp (modi/halofit.py:36-37).  sigma_0^2(R) is summed once per linear table, R_nl(z) comes
- * from one inverse fit at z = 0 evaluated at -ln D^2 (the interpolant commutes with the shift; 1e-14), and (n_eff, C) from a
- * per-redshift fit of ln(D^2 sigma_0^2) in FITPACK order, one device thread per redshift on a factorisation shared by all.
- * out_spec (may be NULL): [n_rows][4] = {k_nl = 1 / R_nl, n_eff, curvature, flag}; flag 1 = R_nl outside the tabulated decade: that row needs the
- * reference's exception path (lbg_halofit_spec_host on a re-sampled grid + lbg_pk_build_table).  *n_flagged = number of such rows.
- * build != 0 and no flagged row: the table (row r = P(k, z_r)) is built into the current slot, like lbg_pk_build_table. */
-int lbg_pk_build_table_hf(lbg_ctx* ctx, int n_rows, const double* zin, int n_R, const double* lnr, const double* R,
-                          double fnu, double om0, double w, int takahashi, int build, double* out_spec, int* n_flagged,
-                          double* out_pnl /*[n_rows][n_k] or NULL*/);
+/* The same for whole z grids on the device, and the P(k,z) tables built from it (modi/cosmology.py:171-179 per node) without a host
+ * round trip, for several z grids in one call: table i has n_rows[i] rows and is written to table slot slots[i] (lbg_pk_select_slot
+ * numbering, -1 = the current slot); zin = the rows of all tables one after another, zin[row][4] = {D(z)^2, Omega_m(z), Omega_L(z),
+ * use_halofit}; lnr[n_R] / R[n_R] = the reference's fitting grid np.linspace(ln 0.1, ln 10, 500) and its exp (modi/halofit.py:36-37).
+ * sigma_0^2(R) is summed once per linear table in the reference's own order (scipy-1.2.1 simps panels + numpy's pairwise np.sum),
+ * R_nl(z) comes from one inverse fit at z = 0 evaluated at -ln D^2 (the interpolant commutes with the shift; 1e-14), and (n_eff, C)
+ * from a per-redshift fit of ln(D^2 sigma_0^2) in FITPACK order, one device thread per redshift on a factorisation shared by all.
+ * out_spec (may be NULL): [rows][4] = {k_nl = 1 / R_nl, n_eff, curvature, flag}; flag 1 = R_nl outside the tabulated decade: that row
+ * needs the reference's exception path (lbg_halofit_spec_host on a re-sampled grid + lbg_pk_build_table).  *n_flagged = number of
+ * such rows.  build != 0 and no flagged row: the tables are built (row r = P(k, z_r)).  out_pnl: n_tables == 1 only. */
+int lbg_pk_build_tables_hf(lbg_ctx* ctx, int n_tables, const int* n_rows, const int* slots, const double* zin,
+                           int n_R, const double* lnr, const double* R, double fnu, double om0, double w, int takahashi, int build,
+                           double* out_spec, int* n_flagged, double* out_pnl /*[n_rows][n_k] or NULL*/);
+/* lbg_upload_pk_linear with the caller's own ln k values (numpy's np.log(k); NULL = this libm's): the sigma^2(R) sums of
+ * lbg_pk_build_tables_hf then use exactly the reference's panel widths. */
+int lbg_upload_pk_linear2(lbg_ctx* ctx, int n_k, const double* k, const double* plin_z0, const double* w_lnk, const double* lnk);
 /* The context holds up to 4 P(k,z) tables; one is current (the one lbg_pk_build_table fills and lbg_limber / lbg_pk_eval read).
  * Makes table `slot` (0..3) current and returns its row count in *out_rows (0: nothing built in it yet).  Pointer swaps only.
  * Every table is dropped when a new linear table or k grid is installed (lbg_upload_pk_linear, lbg_eh_linear_table,

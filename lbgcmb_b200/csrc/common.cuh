@@ -123,6 +123,9 @@ struct lbg_ctx {
     unsigned long long pk_gen = 0;   // bumped whenever a new linear table / k grid is installed
     lbg_hf_state* hf = nullptr;
     lbg::DevBuf  pk_lnk, pk_plin, pk_rdk;
+    lbg::DevBuf  pk_simps;           // numpy-order Simpson data of the ln k grid: [Delta0^2 n_k | SimpsPanel x (npan0 + npan1)]
+    int          pk_npan0 = 0, pk_npan1 = 0;
+    double       pk_first_dx = 0.0, pk_last_dx = 0.0;
     int          pnl_nz = 0;         // rows of the CURRENT P(k,z) table (pk_pnl); 0 = none built
     lbg::DevBuf  pk_pnl;
     // parked P(k,z) tables (lbg_pk_select_slot): a forecast alternates between a few z grids (C_gg, C_kg, C_kk nodes) and

@@ -177,6 +177,7 @@ extern "C" int lbg_eh_linear_table(lbg_ctx* c, double omega_matter, double omega
     if (rc) return rc;
     if ((rc = upload_rdk(c, n_k, k))) return rc;
     c->n_k = n_k;
+    c->pk_npan0 = c->pk_npan1 = 0;           // no numpy-order Simpson data for a device-built table: sigma^2 by the weight-vector kernel
     c->drop_pk_tables();
     return LBG_OK;
 }

@@ -22,21 +22,97 @@
 namespace lbg {
 #define HF_MAX_R 512
 // One thread per redshift: y_i = ln(D^2 sigma_0^2(R_i)), FITPACK right-hand-side rotations + back-substitution, derivatives at x_nl.
-__global__ void __launch_bounds__(64)
-halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const double* __restrict__ tknots, const int* __restrict__ lint,
+// The statements are fitpack::fit_apply's, arranged for a single thread's latency: the six rows a data point rotates into, and the five
+// coefficients a back-substitution row reads, live in a register window that slides with the knot interval (the rows leaving it are
+// final); only z (500 doubles) goes through local memory, and of the coefficients only the six the derivative needs are kept.
+__global__ void __launch_bounds__(32)
+halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const double* __restrict__ tk, const int* __restrict__ lint,
                     const double* __restrict__ rot, const double* __restrict__ band, const double* __restrict__ in /*[n][8]: D2, rknl, x_nl, omz, ovz, use, -, -*/,
                     HaloZ* __restrict__ rows) {
+    using namespace fitpack;
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_rows) return;
     const double* q = in + (size_t)r * 8;
     HaloZ h;
     h.D2 = q[0]; h.rknl = 1.0; h.neff = 0.0; h.ncur = 0.0; h.omz = q[3]; h.ovz = q[4]; h.use_halofit = q[5]; h.pad = 0.0;
     if (q[5] != 0.0) {
-        double y[HF_MAX_R], z[HF_MAX_R];
-        for (int i = 0; i < m; ++i) y[i] = log(q[0] * s0[i]);
-        fitpack::fit_apply(m, lint, rot, band, y, z, y);          // coefficients overwrite y (fpback reads z only)
-        double d[6];
-        const bool ok = fitpack::spalde(tknots, m + 6, y, q[2], d);
+        const double D2 = q[0], x = q[2];
+        const int n = m + K1, nk1 = m;
+        double z[HF_MAX_R];
+        // ---- right-hand side through the rotations (fpcurf) ----
+        double w0 = 0, w1 = 0, w2 = 0, w3 = 0, w4 = 0, w5 = 0;       // z[base .. base + 5]
+        int base = __ldg(lint) - K1;
+        for (int it = 0; it < m; ++it) {
+            const int l = __ldg(lint + it);
+            while (base < l - K1) { z[base] = w0; w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; w5 = 0.0; ++base; }
+            double yi = log(D2 * __ldg(s0 + it));
+            const double2* rp = reinterpret_cast<const double2*>(rot) + (size_t)it * K1;
+#define LBG_ROT(W, I) { const double2 cs = __ldg(rp + I); if (!(cs.x > 1.5)) { const double s1 = yi, s2 = W; \
+                        W = add(mul(cs.x, s2), mul(cs.y, s1)); yi = sub(mul(cs.x, s1), mul(cs.y, s2)); } }
+            LBG_ROT(w0, 0) LBG_ROT(w1, 1) LBG_ROT(w2, 2) LBG_ROT(w3, 3) LBG_ROT(w4, 4) LBG_ROT(w5, 5)
+#undef LBG_ROT
+        }
+        z[base] = w0; z[base + 1] = w1; z[base + 2] = w2; z[base + 3] = w3; z[base + 4] = w4; z[base + 5] = w5;
+        // ---- interval of the derivative point (spalde) ----
+        bool ok = !(x < tk[K1 - 1] || x > tk[nk1]);
+        int l = K1;
+        while (!(x < tk[l]) && l != nk1) ++l;
+        ok = ok && tk[l - 1] < tk[l];
+        const int lk = l - K1;                                        // coefficients c[lk .. lk + 5] (0-based) are needed
+        // ---- back-substitution (fpback), window c[i+1 .. i+5] ----
+        double c1 = 0, c2 = 0, c3 = 0, c4 = 0, c5 = 0, keep[K1] = {0, 0, 0, 0, 0, 0};
+        for (int i = nk1 - 1; i >= 0; --i) {                          // 0-based row
+            const double* ar = band + (size_t)i * K1;
+            double store = z[i];
+            const int avail = nk1 - 1 - i;                            // coefficients above this row that exist (i1 of fpback = min(5, avail))
+            if (avail >= 1) store = sub(store, mul(c1, __ldg(ar + 1)));
+            if (avail >= 2) store = sub(store, mul(c2, __ldg(ar + 2)));
+            if (avail >= 3) store = sub(store, mul(c3, __ldg(ar + 3)));
+            if (avail >= 4) store = sub(store, mul(c4, __ldg(ar + 4)));
+            if (avail >= 5) store = sub(store, mul(c5, __ldg(ar + 5)));
+            const double ci = dvd(store, __ldg(ar));
+            c5 = c4; c4 = c3; c3 = c2; c2 = c1; c1 = ci;
+            const int rel = i - lk;
+            if (rel >= 0 && rel < K1) {
+#pragma unroll
+                for (int e = 0; e < K1; ++e) if (e == rel) keep[e] = ci;
+            }
+        }
+        // ---- derivatives at x (fpader on the six kept coefficients: spalde with the interval found above) ----
+        double d[K1] = {0, 0, 0, 0, 0, 0};
+        if (ok) {
+            double hh[K1 + 1];
+            for (int i = 1; i <= K1; ++i) hh[i] = keep[i - 1];
+            int kj = K1;
+            double fac = 1.0;
+            for (int j = 1; j <= K1; ++j) {
+                int ki = kj;
+                if (j != 1) {
+                    int i = K1;
+                    for (int jj = j; jj <= K1; ++jj) {
+                        const int li = i + lk, lj = li + kj;
+                        hh[i] = dvd(sub(hh[i], hh[i - 1]), sub(tk[lj - 1], tk[li - 1]));
+                        --i;
+                    }
+                }
+                double dd[K1 + 1];
+                for (int i = j; i <= K1; ++i) dd[i] = hh[i];
+                if (j != K1) {
+                    for (int jj = j + 1; jj <= K1; ++jj) {
+                        --ki;
+                        int i = K1;
+                        for (int j2 = jj; j2 <= K1; ++j2) {
+                            const int li = i + lk, lj = li + ki;
+                            dd[i] = dvd(add(mul(sub(x, tk[li - 1]), dd[i]), mul(sub(tk[lj - 1], x), dd[i - 1])), sub(tk[lj - 1], tk[li - 1]));
+                            --i;
+                        }
+                    }
+                }
+                d[j - 1] = mul(dd[K1], fac);
+                fac = mul(fac, (double)(K1 - j));
+                --kj;
+            }
+        }
         h.rknl = q[1];
         h.neff = ok ? -d[1] - 3.0 : nan("");
         h.ncur = ok ? -d[2] : nan("");
@@ -91,18 +167,29 @@ extern "C" int lbg_halofit_spec_host(int n, const double* lnr, const double* lns
     return LBG_OK;
 }
 
-// Device-side table build for one z grid.  zin[n_rows][4] = {D(z)^2, Omega_m(z), Omega_L(z), use_halofit (0 -> linear row)};
+// Device-side build of the P(k,z) tables of several z grids in one call.  Table i has n_rows[i] rows and goes to table slot
+// slots[i] (lbg_pk_select_slot numbering; -1 = the current slot); zin = the tables' rows one after another,
+// zin[row][4] = {D(z)^2, Omega_m(z), Omega_L(z), use_halofit (0 -> linear row)};
 // lnr / R: the reference's fitting grid (np.linspace(ln 0.1, ln 10, 500) and its exp, modi/halofit.py:36-37) as the caller's numpy
-// computed them.  out_spec (may be NULL): [n_rows][4] = {k_nl = 1 / R_nl (the reference's `rknl`), n_eff, curvature, flag}; flag 1 = R_nl outside the tabulated
-// decade (the caller evaluates that row by the reference's exception path and passes it through lbg_pk_build_table).
-// *n_flagged receives the number of flagged rows; the table is built (and made current) only when it is 0 or build = 0 was asked.
-extern "C" int lbg_pk_build_table_hf(lbg_ctx* c, int n_rows, const double* zin, int n_R, const double* lnr, const double* R,
-                                     double fnu, double om0, double w, int takahashi, int build, double* out_spec, int* n_flagged,
-                                     double* out_pnl) {
-    LBG_REQUIRE(c && zin && lnr && R && n_flagged && n_rows > 0, "lbg_pk_build_table_hf: bad argument");
-    LBG_REQUIRE(n_R >= 7 && n_R <= HF_MAX_R, "lbg_pk_build_table_hf: n_R=%d outside [7, %d]", n_R, HF_MAX_R);
+// computed them.  out_spec (may be NULL): [total rows][4] = {k_nl = 1 / R_nl (the reference's `rknl`), n_eff, curvature, flag}; flag 1 =
+// R_nl outside the tabulated decade (the caller evaluates that row by the reference's exception path and passes it through
+// lbg_pk_build_table).  *n_flagged receives the number of flagged rows; the tables are built only when it is 0 and build != 0.
+// out_pnl (may be NULL, n_tables == 1 only): the rows of the table.
+extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_rows_each, const int* slots, const double* zin,
+                                      int n_R, const double* lnr, const double* R, double fnu, double om0, double w, int takahashi,
+                                      int build, double* out_spec, int* n_flagged, double* out_pnl) {
+    LBG_REQUIRE(c && n_rows_each && slots && zin && lnr && R && n_flagged && n_tables > 0 && n_tables <= lbg_ctx::PK_SLOTS,
+                "lbg_pk_build_tables_hf: bad argument");
+    LBG_REQUIRE(n_R >= 7 && n_R <= HF_MAX_R, "lbg_pk_build_tables_hf: n_R=%d outside [7, %d]", n_R, HF_MAX_R);
+    LBG_REQUIRE(out_pnl == nullptr || n_tables == 1, "lbg_pk_build_tables_hf: out_pnl needs n_tables == 1");
+    int n_rows = 0;
+    for (int i = 0; i < n_tables; ++i) {
+        LBG_REQUIRE(n_rows_each[i] > 0 && slots[i] >= -1 && slots[i] < lbg_ctx::PK_SLOTS, "lbg_pk_build_tables_hf: table %d: bad size / slot", i);
+        for (int j = 0; j < i; ++j) LBG_REQUIRE(slots[i] != slots[j], "lbg_pk_build_tables_hf: slot %d given twice", slots[i]);
+        n_rows += n_rows_each[i];
+    }
     std::lock_guard<std::mutex> g(c->mu);
-    if (c->n_k <= 0) { set_error("lbg_pk_build_table_hf: call lbg_upload_pk_linear first"); return LBG_ESTATE; }
+    if (c->n_k <= 0) { set_error("lbg_pk_build_tables_hf: call lbg_upload_pk_linear first"); return LBG_ESTATE; }
     LBG_CUDA(cudaSetDevice(c->device));
     cudaStream_t st = c->stream;
     if (!c->hf) c->hf = new lbg_hf_state();
@@ -112,13 +199,13 @@ extern "C" int lbg_pk_build_table_hf(lbg_ctx* c, int n_rows, const double* zin, 
     KernelTimer t(c);
     // ---- the grid's factorisation (per process) and its device copy (per context) ----
     const bool grid_same = (int)H.lnr.size() == m && !memcmp(H.lnr.data(), lnr, (size_t)m * 8);
+    const size_t nd = (size_t)m + (m + 6) + 12 * (size_t)m + 6 * (size_t)m;
     if (!grid_same || !H.dev_ok) {
         std::lock_guard<std::mutex> gg(g_hf.mu);
         if ((int)g_hf.lnr.size() != m || memcmp(g_hf.lnr.data(), lnr, (size_t)m * 8)) {
-            LBG_REQUIRE(g_hf.F.build(m, lnr), "lbg_pk_build_table_hf: ln R grid must be strictly increasing");
+            LBG_REQUIRE(g_hf.F.build(m, lnr), "lbg_pk_build_tables_hf: ln R grid must be strictly increasing");
             g_hf.lnr.assign(lnr, lnr + m);
         }
-        const size_t nd = (size_t)m + (m + 6) + 12 * (size_t)m + 6 * (size_t)m;
         if (H.dev.reserve(nd * 8 + (size_t)m * 4 + 64)) return LBG_ENOMEM;
         double* d = H.dev.as<double>();
         LBG_CUDA(cudaMemcpyAsync(d + m, g_hf.F.t.data(), (size_t)(m + 6) * 8, cudaMemcpyHostToDevice, st));
@@ -135,22 +222,29 @@ extern "C" int lbg_pk_build_table_hf(lbg_ctx* c, int n_rows, const double* zin, 
     const double* d_t = d + m;
     const double* d_rot = d_t + (m + 6);
     const double* d_band = d_rot + 12 * (size_t)m;
-    const int* d_lint = reinterpret_cast<const int*>(d_band + 6 * (size_t)m);
+    const int* d_lint = reinterpret_cast<const int*>(d + nd);
     // ---- sigma_0^2 on the grid + the z = 0 inverse fit: once per linear table ----
     if (H.pk_gen != c->pk_gen) {
-        if (c->s0.reserve((size_t)m * 8)) return LBG_ENOMEM;
+        if (c->s0.reserve((size_t)m * 8) || c->pin_out.reserve((size_t)m * 8)) return LBG_ENOMEM;
         LBG_CUDA(cudaMemcpyAsync(c->s0.p, R, (size_t)m * 8, cudaMemcpyHostToDevice, st));
         const double* kd = c->pk_lnk.as<double>();
-        sigma2_kernel<<<m, 256, 0, st>>>(c->n_k, kd, kd + 2 * (size_t)c->n_k, c->s0.as<double>(), d_s0);
+        const size_t smem = ((size_t)c->n_k + c->pk_npan0 + c->pk_npan1) * 8;
+        if (c->pk_npan0 > 0 && smem <= 48 * 1024) {              // the reference's own summation order (pk_kernels.cuh)
+            const double* sp = c->pk_simps.as<double>();
+            sigma2_np_kernel<<<m, 256, smem, st>>>(c->n_k, kd, sp, reinterpret_cast<const SimpsPanel*>(sp + c->n_k), c->pk_npan0, c->pk_npan1,
+                                                   c->pk_first_dx, c->pk_last_dx, c->s0.as<double>(), d_s0);
+        } else {
+            sigma2_kernel<<<m, 256, 0, st>>>(c->n_k, kd, kd + 2 * (size_t)c->n_k, c->s0.as<double>(), d_s0);
+        }
         ++launches;
-        H.s0.resize(m);
-        LBG_CUDA(cudaMemcpyAsync(H.s0.data(), d_s0, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+        LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, d_s0, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
         LBG_CUDA(cudaStreamSynchronize(st));
+        H.s0.assign(c->pin_out.as<double>(), c->pin_out.as<double>() + m);
         H.lns0_rev.resize(m); H.lnr_rev.resize(m);
         bool mono = true;
         for (int i = 0; i < m; ++i) { H.lns0_rev[i] = log(H.s0[m - 1 - i]); H.lnr_rev[i] = lnr[m - 1 - i]; }
         for (int i = 1; i < m; ++i) mono = mono && H.lns0_rev[i] > H.lns0_rev[i - 1];
-        LBG_REQUIRE(mono, "lbg_pk_build_table_hf: sigma^2(R) of this table is not strictly decreasing on the grid");
+        LBG_REQUIRE(mono, "lbg_pk_build_tables_hf: sigma^2(R) of this table is not strictly decreasing on the grid");
         fitpack::FitFactor inv;
         inv.build(m, H.lns0_rev.data());
         H.inv_t = inv.t;
@@ -158,7 +252,7 @@ extern "C" int lbg_pk_build_table_hf(lbg_ctx* c, int n_rows, const double* zin, 
         inv.solve(H.lnr_rev.data(), H.inv_c.data());
         H.pk_gen = c->pk_gen;
     }
-    // ---- per row: R_nl from the inverse fit (host, n splev), flags ----
+    // ---- per row: R_nl from the inverse fit (host, one splev each), flags ----
     const size_t in_bytes = (size_t)n_rows * 64;
     if (c->pin_in.reserve(in_bytes) || c->s1.reserve(in_bytes) || c->s5.reserve((size_t)n_rows * sizeof(HaloZ)) ||
         c->pin_out.reserve((size_t)n_rows * sizeof(HaloZ)))
@@ -182,17 +276,24 @@ extern "C" int lbg_pk_build_table_hf(lbg_ctx* c, int n_rows, const double* zin, 
     }
     *n_flagged = flagged;
     LBG_CUDA(cudaMemcpyAsync(c->s1.p, hin, in_bytes, cudaMemcpyHostToDevice, st));
-    halofit_spec_kernel<<<(n_rows + 63) / 64, 64, 0, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, c->s1.as<double>(), c->s5.as<HaloZ>());
+    halofit_spec_kernel<<<(n_rows + 31) / 32, 32, 0, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, c->s1.as<double>(), c->s5.as<HaloZ>());
     ++launches;
     const bool do_build = build && flagged == 0;
     const int n_k = c->n_k;
     if (do_build) {
-        if (c->pk_pnl.reserve((size_t)n_rows * n_k * 8)) return LBG_ENOMEM;
         HaloConst hc{fnu, om0, w, takahashi};
         const double* kd = c->pk_lnk.as<double>();
-        pnl_kernel<<<dim3((n_k + 127) / 128, n_rows), 128, 0, st>>>(n_rows, n_k, kd, kd + n_k, c->s5.as<HaloZ>(), hc, c->pk_pnl.as<double>());
-        ++launches;
-        if (out_pnl) LBG_CUDA(cudaMemcpyAsync(out_pnl, c->pk_pnl.p, (size_t)n_rows * n_k * 8, cudaMemcpyDeviceToHost, st));
+        int row0 = 0;
+        for (int i = 0; i < n_tables; ++i) {
+            const int nr = n_rows_each[i];
+            const bool cur = slots[i] < 0 || slots[i] == c->pk_cur;
+            DevBuf& buf = cur ? c->pk_pnl : c->pk_store[slots[i]];
+            if (buf.reserve((size_t)nr * n_k * 8)) return LBG_ENOMEM;
+            pnl_kernel<<<dim3((n_k + 127) / 128, nr), 128, 0, st>>>(nr, n_k, kd, kd + n_k, c->s5.as<HaloZ>() + row0, hc, buf.as<double>());
+            ++launches;
+            if (out_pnl) LBG_CUDA(cudaMemcpyAsync(out_pnl, buf.p, (size_t)nr * n_k * 8, cudaMemcpyDeviceToHost, st));
+            row0 += nr;
+        }
     }
     if (out_spec) LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, c->s5.p, (size_t)n_rows * sizeof(HaloZ), cudaMemcpyDeviceToHost, st));
     t.launched(launches);
@@ -204,7 +305,10 @@ extern "C" int lbg_pk_build_table_hf(lbg_ctx* c, int n_rows, const double* zin, 
             out_spec[4 * r] = hz[r].rknl; out_spec[4 * r + 1] = hz[r].neff; out_spec[4 * r + 2] = hz[r].ncur; out_spec[4 * r + 3] = flag[r];
         }
     }
-    if (do_build) c->pnl_nz = n_rows;
+    if (do_build)
+        for (int i = 0; i < n_tables; ++i) {
+            if (slots[i] < 0 || slots[i] == c->pk_cur) c->pnl_nz = n_rows_each[i]; else c->store_nz[slots[i]] = n_rows_each[i];
+        }
     return LBG_OK;
 }
 

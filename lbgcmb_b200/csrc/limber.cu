@@ -224,7 +224,9 @@ int lbg::upload_rdk(lbg_ctx* c, int n_k, const double* k) {
     return LBG_OK;
 }
 
-extern "C" int lbg_upload_pk_linear(lbg_ctx* c, int n_k, const double* k, const double* plin_z0, const double* w_lnk) {
+// lnk (may be NULL: log(k) of this libm): the ln k values the caller's numpy computed, so that the numpy-order sigma^2 sums
+// (sigma2_np_kernel) see the reference's own panel widths.
+extern "C" int lbg_upload_pk_linear2(lbg_ctx* c, int n_k, const double* k, const double* plin_z0, const double* w_lnk, const double* lnk) {
     LBG_REQUIRE(c && k && plin_z0 && w_lnk, "lbg_upload_pk_linear: NULL argument");
     LBG_REQUIRE(n_k >= 4 && n_k <= 6000, "lbg_upload_pk_linear: n_k=%d outside [4, 6000] (k grid is staged in shared memory)", n_k);
     for (int i = 1; i < n_k; ++i) LBG_REQUIRE(k[i] > k[i - 1] && k[0] > 0, "lbg_upload_pk_linear: k must be positive and increasing");
@@ -237,13 +239,37 @@ extern "C" int lbg_upload_pk_linear(lbg_ctx* c, int n_k, const double* k, const 
         buf[n_k + i] = plin_z0[i];
         buf[2 * (size_t)n_k + i] = plin_z0[i] * (k[i] * k[i] * k[i]) / twopi2 * w_lnk[i];   // Delta0^2 * simps weight
     }
-    if (c->pk_lnk.reserve(buf.size() * 8)) return LBG_ENOMEM;
+    // numpy-order Simpson data (oracle/simps121.py `_composite` with x given): per-panel constants of both panel sets
+    std::vector<double> x(n_k), h(n_k - 1);
+    for (int i = 0; i < n_k; ++i) x[i] = lnk ? lnk[i] : log(k[i]);
+    for (int i = 0; i + 1 < n_k; ++i) { volatile double d = x[i + 1] - x[i]; h[i] = d; }
+    const bool odd = n_k % 2 == 1;
+    const int npan0 = odd ? (n_k - 1) / 2 : (n_k - 2) / 2, npan1 = odd ? 0 : (n_k - 2) / 2;
+    std::vector<double> sp((size_t)n_k + 5 * (size_t)(npan0 + npan1));
+    for (int i = 0; i < n_k; ++i) sp[i] = plin_z0[i] * (k[i] * k[i] * k[i]) / twopi2;       // Delta0^2
+    for (int p = 0; p < npan0 + npan1; ++p) {
+        const int i = p < npan0 ? 2 * p : 2 * (p - npan0) + 1;
+        volatile double h0 = h[i], h1 = h[i + 1];
+        volatile double hsum = h0 + h1, hprod = h0 * h1, q = h0 / h1;
+        volatile double inv = 1.0 / q;
+        volatile double c0 = 2 - inv, c2 = 2 - q, s6 = hsum / 6.0;
+        double* o = &sp[(size_t)n_k + 5 * (size_t)p];
+        o[0] = c0; o[1] = hsum; o[2] = hprod; o[3] = c2; o[4] = s6;
+    }
+    if (c->pk_lnk.reserve(buf.size() * 8) || c->pk_simps.reserve(sp.size() * 8)) return LBG_ENOMEM;
     LBG_CUDA(cudaMemcpyAsync(c->pk_lnk.p, buf.data(), buf.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    LBG_CUDA(cudaMemcpyAsync(c->pk_simps.p, sp.data(), sp.size() * 8, cudaMemcpyHostToDevice, c->stream));
     LBG_CUDA(cudaStreamSynchronize(c->stream));
+    c->pk_npan0 = npan0; c->pk_npan1 = npan1;
+    c->pk_first_dx = h[0]; c->pk_last_dx = h[n_k - 2];
     if (int rc = upload_rdk(c, n_k, k)) return rc;
     c->n_k = n_k;
     c->drop_pk_tables();
     return LBG_OK;
+}
+
+extern "C" int lbg_upload_pk_linear(lbg_ctx* c, int n_k, const double* k, const double* plin_z0, const double* w_lnk) {
+    return lbg_upload_pk_linear2(c, n_k, k, plin_z0, w_lnk, nullptr);
 }
 
 extern "C" int lbg_halofit_sigma2(lbg_ctx* c, int n_R, const double* R, double* out_sigma2) {
@@ -391,6 +417,7 @@ extern "C" int lbg_pk_upload_rows(lbg_ctx* c, int n_k, const double* k, int n_ro
     LBG_CUDA(cudaStreamSynchronize(c->stream));
     if (int rc = upload_rdk(c, n_k, k)) return rc;
     c->n_k = n_k;
+    c->pk_npan0 = c->pk_npan1 = 0;
     c->drop_pk_tables();
     c->pnl_nz = n_rows;
     return LBG_OK;

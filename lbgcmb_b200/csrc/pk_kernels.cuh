@@ -26,6 +26,69 @@ sigma2_kernel(int n_k, const double* __restrict__ k, const double* __restrict__ 
     if (threadIdx.x == 0) out[blockIdx.x] = sm[0];
 }
 
+// The same integral summed EXACTLY as the reference sums it (modi/halofit.py:41-42: scipy-1.2.1 `simps(y, ln k)` = numpy products per
+// three-point panel + np.sum, whose pairwise order is reproduced below).  Needed where ln sigma^2(R) feeds HALOFIT's curvature: the
+// second derivative of the interpolating spline multiplies the ~1e-16 difference between two summation orders by ~1e4 / C.
+// Block per R: threads fill y_i = Delta0^2 exp(-(k_i R)^2) and the panel terms in shared memory, thread 0 adds them in numpy's order.
+struct SimpsPanel { double c0, hsum, hprod, c2, s6; };   // 2 - 1/(h0/h1), h0 + h1, h0 h1, 2 - h0/h1, (h0 + h1)/6 of one panel
+
+__device__ inline double np_pairwise_sum(const double* a, int n) {       // numpy's pairwise_sum for contiguous float64
+    if (n < 8) {
+        double res = 0.0;
+        for (int i = 0; i < n; ++i) res = __dadd_rn(res, a[i]);
+        return res;
+    }
+    if (n <= 128) {
+        double r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = a[j];
+        int i = 8;
+        for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) r[j] = __dadd_rn(r[j], a[i + j]);
+        }
+        double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])), __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+        for (; i < n; ++i) res = __dadd_rn(res, a[i]);
+        return res;
+    }
+    int n2 = n / 2;
+    n2 -= n2 % 8;
+    return __dadd_rn(np_pairwise_sum(a, n2), np_pairwise_sum(a + n2, n - n2));
+}
+
+static __global__ void __launch_bounds__(256)
+sigma2_np_kernel(int n, const double* __restrict__ k, const double* __restrict__ delta0, const SimpsPanel* __restrict__ pan,
+                 int npan0, int npan1, double first_dx, double last_dx, const double* __restrict__ R, double* __restrict__ out) {
+    extern __shared__ double sh[];
+    double* y = sh;                       // [n]
+    double* tmp = sh + n;                 // [npan0 + npan1]
+    const double r = R[blockIdx.x];
+    for (int i = threadIdx.x; i < n; i += 256) {
+        const double kr = __dmul_rn(k[i], r);
+        y[i] = __dmul_rn(delta0[i], exp(-__dmul_rn(kr, kr)));
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < npan0 + npan1; p += 256) {
+        const int i = p < npan0 ? 2 * p : 2 * (p - npan0) + 1;            // first sample of the panel
+        const SimpsPanel P = pan[p];
+        const double a = __dmul_rn(y[i], P.c0);
+        const double b = __ddiv_rn(__dmul_rn(__dmul_rn(y[i + 1], P.hsum), P.hsum), P.hprod);
+        const double c = __dmul_rn(y[i + 2], P.c2);
+        tmp[p] = __dmul_rn(P.s6, __dadd_rn(__dadd_rn(a, b), c));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double res = np_pairwise_sum(tmp, npan0);
+        if (npan1 > 0) {                  // even number of samples: scipy-1.2.1 even='avg'
+            double val = __dmul_rn(__dmul_rn(0.5, last_dx), __dadd_rn(y[n - 1], y[n - 2]));
+            val = __dadd_rn(val, __dmul_rn(__dmul_rn(0.5, first_dx), __dadd_rn(y[1], y[0])));
+            res = __dadd_rn(res, np_pairwise_sum(tmp + npan0, npan1));
+            res = __dadd_rn(__ddiv_rn(res, 2.0), __ddiv_rn(val, 2.0));
+        }
+        out[blockIdx.x] = res;
+    }
+}
+
 struct HaloZ {           // per-redshift HALOFIT inputs (modi/halofit.py:139-199)
     double D2;           // growth^2 applied to the z=0 table (modi/cosmology.py:160,175)
     double rknl, neff, ncur, omz, ovz;

@@ -139,9 +139,11 @@ class Cosmology(object):
         k, p = _ffi.f64(self.klin), _ffi.f64(self.plin)
         owner = (self._token, _ffi.table_digest(k, p))           # the digest catches tables edited in place
         if _owner.get(ctx.device) != owner:
-            if self._wlnk is None or self._wlnk.size != k.size:
-                self._wlnk = _ffi.f64(simps_weights_x(np.log(k)))
-            _ffi.check(_ffi.lib().lbg_upload_pk_linear(ctx.handle, k.size, _ffi._dp(k), _ffi._dp(p), _ffi._dp(self._wlnk)))
+            if self._wlnk is None or self._wlnk[0].size != k.size or not np.array_equal(self._wlnk[2], k):
+                lnk = _ffi.f64(np.log(k))
+                self._wlnk = (_ffi.f64(simps_weights_x(lnk)), lnk, k.copy())
+            _ffi.check(_ffi.lib().lbg_upload_pk_linear2(ctx.handle, k.size, _ffi._dp(k), _ffi._dp(p), _ffi._dp(self._wlnk[0]),
+                                                        _ffi._dp(self._wlnk[1])))
             _owner[ctx.device] = owner
             self._rows_key = None
             self._slots = {}             # the upload dropped every P(k,z) table of the context
@@ -181,14 +183,20 @@ class Cosmology(object):
             self._spec_cache[key] = spec
         return self._spec_cache[key]
 
-    def _device_specs(self, ctx, zin, build):
-        """lbg_pk_build_table_hf on rows zin[n, 4] = (D^2, Omega_m(z), Omega_L(z), use_halofit): (spec[n, 4], n_flagged)."""
+    def _device_tables(self, ctx, zins, slots, build, want_spec=False, out=None):
+        """lbg_pk_build_tables_hf on one or more z grids: zins = [rows[n_i, 4] = (D^2, Omega_m(z), Omega_L(z), use_halofit)], slots =
+        their table slots (-1: the current one).  Returns (spec[sum n_i, 4] or None, n_flagged)."""
         import ctypes as C
-        spec = np.empty((zin.shape[0], 4))
+        n_each = np.ascontiguousarray([z.shape[0] for z in zins], dtype=np.int32)
+        sl = np.ascontiguousarray(slots, dtype=np.int32)
+        zin = _ffi.f64(np.concatenate(zins)) if len(zins) > 1 else _ffi.f64(zins[0])
+        spec = np.empty((zin.shape[0], 4)) if want_spec else None
         nflag = C.c_int(0)
         fnu = self.cosmo.Onu0 / self.cosmo.Om0
-        _ffi.check(_ffi.lib().lbg_pk_build_table_hf(ctx.handle, zin.shape[0], _ffi._dp(zin), _HF_LNR.size, _ffi._dp(_HF_LNR), _ffi._dp(_HF_R),
-                                                    float(fnu), float(self.cosmo.Om0), -1.0, 1, int(build), _ffi._dp(spec), C.byref(nflag), None))
+        _ffi.check(_ffi.lib().lbg_pk_build_tables_hf(ctx.handle, len(zins), n_each.ctypes.data_as(_ffi.c_int_p), sl.ctypes.data_as(_ffi.c_int_p),
+                                                     _ffi._dp(zin), _HF_LNR.size, _ffi._dp(_HF_LNR), _ffi._dp(_HF_R), float(fnu),
+                                                     float(self.cosmo.Om0), -1.0, 1, int(build), _ffi._dp(spec) if want_spec else None,
+                                                     C.byref(nflag), _ffi._dp(out) if out is not None else None))
         return spec, nflag.value
 
     def halofit_specs(self, zs, D2, sig8=None):
@@ -208,7 +216,7 @@ class Cosmology(object):
         zin = np.zeros((zs.size, 4))
         zin[:, 0] = D2
         zin[:, 3] = 1.0
-        spec, _ = self._device_specs(ctx, _ffi.f64(zin), build=False)
+        spec, _ = self._device_tables(ctx, [_ffi.f64(zin)], [-1], build=False, want_spec=True)
         out[:, 0] = spec[:, 0]
         out[:, 1:3] = spec[:, 1:3]
         for i in np.nonzero(spec[:, 3] != 0.0)[0]:
@@ -240,21 +248,7 @@ class Cosmology(object):
                 old = next(k for k, v in self._slots.items() if v in pool)   # least recently used
                 slot = self._slots.pop(old)
         self._select_slot(ctx, slot)
-        bg = self._bg_cache.get(key)            # per z grid: D^2, Omega_m(z), Omega_L(z), use_halofit (the background: kept across table rebuilds)
-        if bg is None:
-            bg = np.zeros((zs.size, 4))
-            aa = self.ztoa(zs)
-            bg[:, 0] = (self.Dplus(aa) / self.Dplus(1.)) ** 2.                   # Dgrow(z)^2, modi/cosmology.py:113-117
-            if nonlinear:
-                hf = ~(zs > zmax_halofit)                                         # modi/cosmology.py:171
-                zz = self.atoz(aa[hf])
-                bg[hf, 1] = self.cosmo.Om(zz)
-                bg[hf, 2] = self.cosmo.Ode(zz)
-                bg[hf, 3] = 1.0
-            bg = _ffi.f64(bg)
-            if len(self._bg_cache) >= 16:
-                self._bg_cache.clear()
-            self._bg_cache[key] = bg
+        bg = self._background(key, zs, nonlinear, zmax_halofit)
         import ctypes as C
         nk = C.c_int(0)
         _ffi.check(_ffi.lib().lbg_pk_table_nk(ctx.handle, C.byref(nk)))
@@ -267,11 +261,8 @@ class Cosmology(object):
         done = False
         if std_sig8 or not np.any(bg[:, 3]):
             # spectral parameters and rows on the device in one call (no host round trip); flagged rows -> explicit route below
-            nflag = C.c_int(0)
-            _ffi.check(_ffi.lib().lbg_pk_build_table_hf(ctx.handle, zs.size, _ffi._dp(bg), _HF_LNR.size, _ffi._dp(_HF_LNR), _ffi._dp(_HF_R),
-                                                        float(fnu), float(self.cosmo.Om0), -1.0, 1, 1, None, C.byref(nflag),
-                                                        _ffi._dp(out) if want_host else None))
-            done = nflag.value == 0
+            _, nflag = self._device_tables(ctx, [bg], [-1], build=True, out=out)
+            done = nflag == 0
         if not done:
             rows = np.zeros((zs.size, 8))
             rows[:, 0] = bg[:, 0]
@@ -287,6 +278,62 @@ class Cosmology(object):
         self._rows_key = key
         self._slots[key] = slot
         return out
+
+    def build_tables(self, grids, nonlinear=True, sig8=None, zmax_halofit=4.0):
+        """Table slots for several z grids at once, every missing table built by ONE library call (lbg_pk_build_tables_hf: one
+        sigma^2 pass, one spectral-parameter launch for all rows, one row launch per table).  Falls back to table_slot per grid for
+        unusual sigma_8 or when a redshift needs the reference's exception path."""
+        grids = [np.atleast_1d(np.asarray(z, dtype=np.float64)) for z in grids]
+        keys = [(z.tobytes(), bool(nonlinear), sig8, zmax_halofit) for z in grids]
+        s8 = self.sig8 if sig8 is None else sig8
+        if len(grids) > _PK_SLOTS - 1 or not (s8 < 1.0 and s8 > 0.6):
+            return [self.table_slot(z, nonlinear=nonlinear, sig8=sig8) for z in grids]
+        ctx = self._ctx()
+        for key in keys:                                   # refresh the recency of the tables that are already parked
+            if key in self._slots:
+                self._slots[key] = self._slots.pop(key)
+        missing = [i for i, key in enumerate(keys) if key not in self._slots]
+        if missing:
+            pool = range(_PK_SLOTS - 1)
+            zins, slots = [], []
+            for i in missing:
+                used = set(self._slots.values())
+                free = [q for q in pool if q not in used]
+                if free:
+                    slot = free[0]
+                else:
+                    old = next(k for k, v in self._slots.items() if v in pool and k not in keys)   # least recently used, not of this batch
+                    slot = self._slots.pop(old)
+                self._slots[keys[i]] = slot
+                zins.append(self._background(keys[i], grids[i], nonlinear, zmax_halofit))
+                slots.append(slot)
+            _, nflag = self._device_tables(ctx, zins, slots, build=True)
+            if self._cur_slot in slots:
+                self._rows_key = keys[missing[slots.index(self._cur_slot)]]
+            if nflag:
+                for i in missing:
+                    del self._slots[keys[i]]
+                return [self.table_slot(z, nonlinear=nonlinear, sig8=sig8) for z in grids]
+        return [self._slots[key] for key in keys]
+
+    def _background(self, key, zs, nonlinear, zmax_halofit):
+        """Per z grid: D^2, Omega_m(z), Omega_L(z), use_halofit -- the background, kept across table rebuilds."""
+        bg = self._bg_cache.get(key)
+        if bg is None:
+            bg = np.zeros((zs.size, 4))
+            aa = self.ztoa(zs)
+            bg[:, 0] = (self.Dplus(aa) / self.Dplus(1.)) ** 2.                   # Dgrow(z)^2, modi/cosmology.py:113-117
+            if nonlinear:
+                hf = ~(zs > zmax_halofit)                                         # modi/cosmology.py:171
+                zz = self.atoz(aa[hf])
+                bg[hf, 1] = self.cosmo.Om(zz)
+                bg[hf, 2] = self.cosmo.Ode(zz)
+                bg[hf, 3] = 1.0
+            bg = _ffi.f64(bg)
+            if len(self._bg_cache) >= 16:
+                self._bg_cache.clear()
+            self._bg_cache[key] = bg
+        return bg
 
     def table_slot(self, zs, nonlinear=True, sig8=None):
         """Device table slot (lbg_pk_select_slot index) holding row r = P(k, zs[r]), built if it is not parked already: what

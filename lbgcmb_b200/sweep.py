@@ -54,13 +54,12 @@ def forecast_spectra(Pk_interps, Llls, samples, zmin=0.01, zmax=10.0, want_ckk=T
         pgg[i], pkg[i] = pz(zg), pz(zk)
         bgg[i], bkg[i] = _each(bz, zg), _each(bz, zk)
         ngg[i] = 1. / (nbar_convert(smp['nbar'], unit='str') * norm[i]) if smp.get('nbar') is not None else np.nan   # Cgg.py:85-95
-    slot_g = engine.table_slot(zg, nonlinear=nonlinear)
-    slot_k = engine.table_slot(zk, nonlinear=nonlinear)
     if want_ckk:
         zc, chic, wc = _ckk_nodes(float(par['zscatter']))
-        slot_c = engine.table_slot(zc, nonlinear=nonlinear)
+        slot_g, slot_k, slot_c = engine.build_tables([zg, zk, zc], nonlinear=nonlinear)
     else:
         chic = wc = np.zeros(0)
+        slot_g, slot_k = engine.build_tables([zg, zk], nonlinear=nonlinear)
         slot_c = 0
     ctx = engine._ctx()
     cgg, ckg = np.empty((n_s, Ld.size)), np.empty((n_s, Ld.size))

@@ -45,8 +45,7 @@ for rep in range(25):
     from lbgcmb_b200.Ckg import _ckg_nodes
     from lbgcmb_b200.lensing import _ckk_nodes
     t0 = time.perf_counter(); eng._ctx(); tick('linear table upload', t0)
-    for name, zs in (('gg', _cgg_nodes(0.01, 10.0)[0]), ('kg', _ckg_nodes(0.01, 10.0)[0]), ('kk', _ckk_nodes(1100.)[0])):
-        t0 = time.perf_counter(); eng.table_slot(zs); tick('P(k,z) table %s (specs + rows on the device)' % name, t0)
+    t0 = time.perf_counter(); eng.build_tables([_cgg_nodes(0.01, 10.0)[0], _ckg_nodes(0.01, 10.0)[0], _ckk_nodes(1100.)[0]]); tick('P(k,z) tables gg + kg + kk (one call: specs + rows on the device)', t0)
     t0 = time.perf_counter(); ckk, cgg, ckg, ngg = sweep.forecast_spectra(Pk, Lf, smp); tick('forecast_spectra (tables parked; callables + 1 library call)', t0)
     t0 = time.perf_counter(); nkk = call.result()[0]; tick('n0 wait', t0)
     t0 = time.perf_counter()
