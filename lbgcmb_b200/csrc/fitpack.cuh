@@ -59,11 +59,16 @@ LBG_HD void fpbspl(const double* t, double x, int l, double* h /*[K1]*/) {
     }
 }
 
-// splev at one point: interval search as splev.f, value = sum_j c(l-k1+j) h(j)
+// splev at one point: value = sum_j c(l-k1+j) h(j).  The interval is the one splev.f's linear walk stops at (the first l >= k1 with
+// x < t(l+1), or nk1), found by bisection: same l, 9 steps instead of ~250.
 LBG_HD double splev(const double* t, int n, const double* c, double x) {
     const int nk1 = n - K1;
-    int l = K1;
-    while (!(x < t[l]) && l != nk1) ++l;                    // t(l+1) is t[l] 0-based
+    int l = nk1;
+    if (x < t[nk1 - 1]) {
+        int lo = K1, hi = nk1 - 1;                          // invariant: the answer lies in [lo, hi], x < t[hi]
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (x < t[mid]) hi = mid; else lo = mid + 1; }
+        l = lo;
+    }
     double h[K1];
     fpbspl(t, x, l, h);
     double sp = 0.0;

@@ -27,16 +27,29 @@ namespace lbg {
 // final); only z (500 doubles) goes through local memory, and of the coefficients only the six the derivative needs are kept.
 __global__ void __launch_bounds__(32)
 halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const double* __restrict__ tk, const int* __restrict__ lint,
-                    const double* __restrict__ rot, const double* __restrict__ band, const double* __restrict__ in /*[n][8]: D2, rknl, x_nl, omz, ovz, use, -, -*/,
-                    HaloZ* __restrict__ rows) {
+                    const double* __restrict__ rot, const double* __restrict__ band, const double* __restrict__ inv_t, const double* __restrict__ inv_c,
+                    double lo, double hi, double lnr0, double lnr1, const double* __restrict__ in /*[n][4]: D2, omz, ovz, use*/,
+                    HaloZ* __restrict__ rows, int* __restrict__ n_flagged) {
     using namespace fitpack;
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_rows) return;
-    const double* q = in + (size_t)r * 8;
+    const double* q = in + (size_t)r * 4;
     HaloZ h;
-    h.D2 = q[0]; h.rknl = 1.0; h.neff = 0.0; h.ncur = 0.0; h.omz = q[3]; h.ovz = q[4]; h.use_halofit = q[5]; h.pad = 0.0;
-    if (q[5] != 0.0) {
-        const double D2 = q[0], x = q[2];
+    h.D2 = q[0]; h.rknl = 1.0; h.neff = 0.0; h.ncur = 0.0; h.omz = q[1]; h.ovz = q[2]; h.use_halofit = q[3]; h.pad = 0.0;
+    double rknl = 1.0, x = 0.0;
+    if (q[3] != 0.0) {
+        // R_nl from the z = 0 inverse fit at -ln D^2 (modi/halofit.py:71-72 with the abscissae shifted by ln D^2)
+        const double tt = -log(q[0]);
+        const double lnR = splev(inv_t, m + K1, inv_c, tt);
+        rknl = 1.0 / exp(lnR);
+        x = log(1.0 / rknl);
+        if (!(tt > lo && tt < hi && lnR > lnr0 && lnR < lnr1)) {       // outside the tabulated decade: the caller's exception path
+            h.use_halofit = 0.0; h.pad = 1.0; h.rknl = rknl;
+            atomicAdd(n_flagged, 1);
+        }
+    }
+    if (h.use_halofit != 0.0) {
+        const double D2 = q[0];
         const int n = m + K1, nk1 = m;
         double z[HF_MAX_R];
         // ---- right-hand side through the rotations (fpcurf) ----
@@ -113,7 +126,7 @@ halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const doub
                 --kj;
             }
         }
-        h.rknl = q[1];
+        h.rknl = rknl;
         h.neff = ok ? -d[1] - 3.0 : nan("");
         h.ncur = ok ? -d[2] : nan("");
     }
@@ -199,14 +212,14 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
     KernelTimer t(c);
     // ---- the grid's factorisation (per process) and its device copy (per context) ----
     const bool grid_same = (int)H.lnr.size() == m && !memcmp(H.lnr.data(), lnr, (size_t)m * 8);
-    const size_t nd = (size_t)m + (m + 6) + 12 * (size_t)m + 6 * (size_t)m;
+    const size_t nd = (size_t)m + (m + 6) + 12 * (size_t)m + 6 * (size_t)m;    // then lint (m ints, padded to m doubles), then the inverse fit (2 m + 6)
     if (!grid_same || !H.dev_ok) {
         std::lock_guard<std::mutex> gg(g_hf.mu);
         if ((int)g_hf.lnr.size() != m || memcmp(g_hf.lnr.data(), lnr, (size_t)m * 8)) {
             LBG_REQUIRE(g_hf.F.build(m, lnr), "lbg_pk_build_tables_hf: ln R grid must be strictly increasing");
             g_hf.lnr.assign(lnr, lnr + m);
         }
-        if (H.dev.reserve(nd * 8 + (size_t)m * 4 + 64)) return LBG_ENOMEM;
+        if (H.dev.reserve((nd + m + 2 * (size_t)m + 6) * 8 + 64)) return LBG_ENOMEM;
         double* d = H.dev.as<double>();
         LBG_CUDA(cudaMemcpyAsync(d + m, g_hf.F.t.data(), (size_t)(m + 6) * 8, cudaMemcpyHostToDevice, st));
         LBG_CUDA(cudaMemcpyAsync(d + m + (m + 6), g_hf.F.rot.data(), (size_t)12 * m * 8, cudaMemcpyHostToDevice, st));
@@ -223,6 +236,7 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
     const double* d_rot = d_t + (m + 6);
     const double* d_band = d_rot + 12 * (size_t)m;
     const int* d_lint = reinterpret_cast<const int*>(d + nd);
+    double* d_inv = d + nd + m;
     // ---- sigma_0^2 on the grid + the z = 0 inverse fit: once per linear table ----
     if (H.pk_gen != c->pk_gen) {
         if (c->s0.reserve((size_t)m * 8) || c->pin_out.reserve((size_t)m * 8)) return LBG_ENOMEM;
@@ -250,34 +264,31 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
         H.inv_t = inv.t;
         H.inv_c.resize(m);
         inv.solve(H.lnr_rev.data(), H.inv_c.data());
+        LBG_CUDA(cudaMemcpyAsync(d_inv, H.inv_t.data(), (size_t)(m + 6) * 8, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaMemcpyAsync(d_inv + (m + 6), H.inv_c.data(), (size_t)m * 8, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaStreamSynchronize(st));
         H.pk_gen = c->pk_gen;
     }
-    // ---- per row: R_nl from the inverse fit (host, one splev each), flags ----
-    const size_t in_bytes = (size_t)n_rows * 64;
-    if (c->pin_in.reserve(in_bytes) || c->s1.reserve(in_bytes) || c->s5.reserve((size_t)n_rows * sizeof(HaloZ)) ||
-        c->pin_out.reserve((size_t)n_rows * sizeof(HaloZ)))
+    // ---- per row on the device: R_nl from the inverse fit, flags, the per-redshift forward fit ----
+    const size_t in_bytes = (size_t)n_rows * 32;
+    if (c->pin_in.reserve(in_bytes + 64) || c->s1.reserve(in_bytes + 64) || c->s5.reserve((size_t)n_rows * sizeof(HaloZ)) ||
+        c->pin_out.reserve((size_t)n_rows * sizeof(HaloZ) + 64))
         return LBG_ENOMEM;
-    double* hin = c->pin_in.as<double>();
-    const double lo = H.lns0_rev[0], hi = H.lns0_rev[m - 1];
-    int flagged = 0;
-    std::vector<unsigned char> flag(n_rows, 0);
-    for (int r = 0; r < n_rows; ++r) {
-        const double D2 = zin[4 * r], use = zin[4 * r + 3];
-        double rknl = 1.0, x = 0.0;
-        if (use != 0.0) {
-            const double tt = -log(D2);
-            const double lnR = fitpack::splev(H.inv_t.data(), m + 6, H.inv_c.data(), tt);
-            rknl = 1.0 / exp(lnR);
-            x = log(1.0 / rknl);
-            if (!(tt > lo && tt < hi && lnR > lnr[0] && lnR < lnr[m - 1])) { flag[r] = 1; ++flagged; }
-        }
-        double* q = hin + 8 * (size_t)r;
-        q[0] = D2; q[1] = rknl; q[2] = x; q[3] = zin[4 * r + 1]; q[4] = zin[4 * r + 2]; q[5] = flag[r] ? 0.0 : use; q[6] = q[7] = 0.0;
-    }
-    *n_flagged = flagged;
-    LBG_CUDA(cudaMemcpyAsync(c->s1.p, hin, in_bytes, cudaMemcpyHostToDevice, st));
-    halofit_spec_kernel<<<(n_rows + 31) / 32, 32, 0, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, c->s1.as<double>(), c->s5.as<HaloZ>());
+    memcpy(c->pin_in.p, zin, in_bytes);
+    LBG_CUDA(cudaMemcpyAsync(c->s1.p, c->pin_in.p, in_bytes, cudaMemcpyHostToDevice, st));
+    int* d_flag = reinterpret_cast<int*>(c->s1.as<unsigned char>() + in_bytes);
+    LBG_CUDA(cudaMemsetAsync(d_flag, 0, 4, st));
+    halofit_spec_kernel<<<(n_rows + 31) / 32, 32, 0, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, d_inv, d_inv + (m + 6),
+                                                           H.lns0_rev[0], H.lns0_rev[m - 1], lnr[0], lnr[m - 1], c->s1.as<double>(),
+                                                           c->s5.as<HaloZ>(), d_flag);
     ++launches;
+    int flagged = 0;
+    if (build) {                                   // the decision to build needs the count: one small synchronous copy
+        int* hflag = reinterpret_cast<int*>(c->pin_out.as<unsigned char>() + (size_t)n_rows * sizeof(HaloZ));
+        LBG_CUDA(cudaMemcpyAsync(hflag, d_flag, 4, cudaMemcpyDeviceToHost, st));
+        LBG_CUDA(cudaStreamSynchronize(st));
+        flagged = *hflag;
+    }
     const bool do_build = build && flagged == 0;
     const int n_k = c->n_k;
     if (do_build) {
@@ -301,10 +312,13 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
     if (rc) return rc;
     if (out_spec) {
         const HaloZ* hz = c->pin_out.as<HaloZ>();
+        flagged = 0;
         for (int r = 0; r < n_rows; ++r) {
-            out_spec[4 * r] = hz[r].rknl; out_spec[4 * r + 1] = hz[r].neff; out_spec[4 * r + 2] = hz[r].ncur; out_spec[4 * r + 3] = flag[r];
+            out_spec[4 * r] = hz[r].rknl; out_spec[4 * r + 1] = hz[r].neff; out_spec[4 * r + 2] = hz[r].ncur; out_spec[4 * r + 3] = hz[r].pad;
+            flagged += hz[r].pad != 0.0;
         }
     }
+    *n_flagged = flagged;
     if (do_build)
         for (int i = 0; i < n_tables; ++i) {
             if (slots[i] < 0 || slots[i] == c->pk_cur) c->pnl_nz = n_rows_each[i]; else c->store_nz[slots[i]] = n_rows_each[i];

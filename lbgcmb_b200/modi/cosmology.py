@@ -308,8 +308,7 @@ class Cosmology(object):
                 zins.append(self._background(keys[i], grids[i], nonlinear, zmax_halofit))
                 slots.append(slot)
             _, nflag = self._device_tables(ctx, zins, slots, build=True)
-            if self._cur_slot in slots:
-                self._rows_key = keys[missing[slots.index(self._cur_slot)]]
+            self._rows_key = None                          # whichever slot is current may just have been rewritten: select before use
             if nflag:
                 for i in missing:
                     del self._slots[keys[i]]
