@@ -21,23 +21,40 @@
 
 namespace lbg {
 #define HF_MAX_R 512
-// One thread per redshift: y_i = ln(D^2 sigma_0^2(R_i)), FITPACK right-hand-side rotations + back-substitution, derivatives at x_nl.
-// The statements are fitpack::fit_apply's, arranged for a single thread's latency: the six rows a data point rotates into, and the five
+#define HF_WARPS 8
+// One WARP per redshift, eight redshifts per block.  The factorisation (rotations 48 KB, band 24 KB, knots, intervals, sigma_0^2) is
+// staged in shared memory once per block: the fit is one long dependent chain per redshift, so what matters is the latency of every
+// operand it touches (one thread per redshift reading the rotations through L2: 650 us for 4000 redshifts; from shared memory with the
+// six pairs of a data point fetched ahead of the chain: 360 us).  The warp's lanes take the logarithms y_i = ln(D^2 sigma_0^2(R_i)) in
+// parallel; lane 0 then runs fitpack::fit_apply's statements in their order: the six rows a data point rotates into, and the five
 // coefficients a back-substitution row reads, live in a register window that slides with the knot interval (the rows leaving it are
-// final); only z (500 doubles) goes through local memory, and of the coefficients only the six the derivative needs are kept.
-__global__ void __launch_bounds__(32)
-halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const double* __restrict__ tk, const int* __restrict__ lint,
-                    const double* __restrict__ rot, const double* __restrict__ band, const double* __restrict__ inv_t, const double* __restrict__ inv_c,
+// final); of the coefficients only the six the derivative needs are kept.
+__global__ void __launch_bounds__(32 * HF_WARPS)
+halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const double* __restrict__ tk_g, const int* __restrict__ lint_g,
+                    const double* __restrict__ rot_g, const double* __restrict__ band_g, const double* __restrict__ inv_t, const double* __restrict__ inv_c,
                     double lo, double hi, double lnr0, double lnr1, const double* __restrict__ in /*[n][4]: D2, omz, ovz, use*/,
                     HaloZ* __restrict__ rows, int* __restrict__ n_flagged) {
     using namespace fitpack;
-    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    extern __shared__ double hsm[];
+    double* rot = hsm;                               // [m][K1][2]
+    double* band = rot + 12 * (size_t)m;             // [m][K1]
+    double* tk = band + 6 * (size_t)m;               // [m + K1]
+    double* s0s = tk + (m + K1);                     // [m]
+    double* yz = s0s + m;                            // [HF_WARPS][m]: y, then z in place
+    int* lint = reinterpret_cast<int*>(yz + (size_t)HF_WARPS * m);   // [m]
+    for (int i = threadIdx.x; i < 12 * m; i += blockDim.x) rot[i] = rot_g[i];
+    for (int i = threadIdx.x; i < 6 * m; i += blockDim.x) band[i] = band_g[i];
+    for (int i = threadIdx.x; i < m + K1; i += blockDim.x) tk[i] = tk_g[i];
+    for (int i = threadIdx.x; i < m; i += blockDim.x) { s0s[i] = s0[i]; lint[i] = lint_g[i]; }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int r = blockIdx.x * HF_WARPS + warp;
     if (r >= n_rows) return;
     const double* q = in + (size_t)r * 4;
     HaloZ h;
     h.D2 = q[0]; h.rknl = 1.0; h.neff = 0.0; h.ncur = 0.0; h.omz = q[1]; h.ovz = q[2]; h.use_halofit = q[3]; h.pad = 0.0;
     double rknl = 1.0, x = 0.0;
-    if (q[3] != 0.0) {
+    if (q[3] != 0.0) {                               // warp-uniform
         // R_nl from the z = 0 inverse fit at -ln D^2 (modi/halofit.py:71-72 with the abscissae shifted by ln D^2)
         const double tt = -log(q[0]);
         const double lnR = splev(inv_t, m + K1, inv_c, tt);
@@ -45,24 +62,29 @@ halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const doub
         x = log(1.0 / rknl);
         if (!(tt > lo && tt < hi && lnR > lnr0 && lnR < lnr1)) {       // outside the tabulated decade: the caller's exception path
             h.use_halofit = 0.0; h.pad = 1.0; h.rknl = rknl;
-            atomicAdd(n_flagged, 1);
+            if (lane == 0) atomicAdd(n_flagged, 1);
         }
     }
     if (h.use_halofit != 0.0) {
+        double* y = yz + (size_t)warp * m;
         const double D2 = q[0];
-        const int n = m + K1, nk1 = m;
-        double z[HF_MAX_R];
+        for (int i = lane; i < m; i += 32) y[i] = log(D2 * s0s[i]);
+        __syncwarp();
+      if (lane == 0) {
+        const int nk1 = m;
+        double* z = y;                               // z[base] is written after y[base] was consumed (base <= it)
         // ---- right-hand side through the rotations (fpcurf) ----
         double w0 = 0, w1 = 0, w2 = 0, w3 = 0, w4 = 0, w5 = 0;       // z[base .. base + 5]
-        int base = __ldg(lint) - K1;
+        int base = lint[0] - K1;
         for (int it = 0; it < m; ++it) {
-            const int l = __ldg(lint + it);
-            while (base < l - K1) { z[base] = w0; w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; w5 = 0.0; ++base; }
-            double yi = log(D2 * __ldg(s0 + it));
+            const int l = lint[it];
+            double yi = y[it];
             const double2* rp = reinterpret_cast<const double2*>(rot) + (size_t)it * K1;
-#define LBG_ROT(W, I) { const double2 cs = __ldg(rp + I); if (!(cs.x > 1.5)) { const double s1 = yi, s2 = W; \
-                        W = add(mul(cs.x, s2), mul(cs.y, s1)); yi = sub(mul(cs.x, s1), mul(cs.y, s2)); } }
-            LBG_ROT(w0, 0) LBG_ROT(w1, 1) LBG_ROT(w2, 2) LBG_ROT(w3, 3) LBG_ROT(w4, 4) LBG_ROT(w5, 5)
+            const double2 r0 = rp[0], r1 = rp[1], r2 = rp[2], r3 = rp[3], r4 = rp[4], r5 = rp[5];   // fetched ahead of the chain
+            while (base < l - K1) { z[base] = w0; w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; w5 = 0.0; ++base; }
+#define LBG_ROT(W, CS) { if (!(CS.x > 1.5)) { const double s1 = yi, s2 = W; \
+                        W = add(mul(CS.x, s2), mul(CS.y, s1)); yi = sub(mul(CS.x, s1), mul(CS.y, s2)); } }
+            LBG_ROT(w0, r0) LBG_ROT(w1, r1) LBG_ROT(w2, r2) LBG_ROT(w3, r3) LBG_ROT(w4, r4) LBG_ROT(w5, r5)
 #undef LBG_ROT
         }
         z[base] = w0; z[base + 1] = w1; z[base + 2] = w2; z[base + 3] = w3; z[base + 4] = w4; z[base + 5] = w5;
@@ -76,14 +98,15 @@ halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const doub
         double c1 = 0, c2 = 0, c3 = 0, c4 = 0, c5 = 0, keep[K1] = {0, 0, 0, 0, 0, 0};
         for (int i = nk1 - 1; i >= 0; --i) {                          // 0-based row
             const double* ar = band + (size_t)i * K1;
+            const double a0 = ar[0], a1 = ar[1], a2 = ar[2], a3 = ar[3], a4 = ar[4], a5 = ar[5];
             double store = z[i];
             const int avail = nk1 - 1 - i;                            // coefficients above this row that exist (i1 of fpback = min(5, avail))
-            if (avail >= 1) store = sub(store, mul(c1, __ldg(ar + 1)));
-            if (avail >= 2) store = sub(store, mul(c2, __ldg(ar + 2)));
-            if (avail >= 3) store = sub(store, mul(c3, __ldg(ar + 3)));
-            if (avail >= 4) store = sub(store, mul(c4, __ldg(ar + 4)));
-            if (avail >= 5) store = sub(store, mul(c5, __ldg(ar + 5)));
-            const double ci = dvd(store, __ldg(ar));
+            if (avail >= 1) store = sub(store, mul(c1, a1));
+            if (avail >= 2) store = sub(store, mul(c2, a2));
+            if (avail >= 3) store = sub(store, mul(c3, a3));
+            if (avail >= 4) store = sub(store, mul(c4, a4));
+            if (avail >= 5) store = sub(store, mul(c5, a5));
+            const double ci = dvd(store, a0);
             c5 = c4; c4 = c3; c3 = c2; c2 = c1; c1 = ci;
             const int rel = i - lk;
             if (rel >= 0 && rel < K1) {
@@ -129,8 +152,9 @@ halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const doub
         h.rknl = rknl;
         h.neff = ok ? -d[1] - 3.0 : nan("");
         h.ncur = ok ? -d[2] : nan("");
+      }
     }
-    rows[r] = h;
+    if (lane == 0) rows[r] = h;
 }
 }  // namespace lbg
 
@@ -278,7 +302,14 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
     LBG_CUDA(cudaMemcpyAsync(c->s1.p, c->pin_in.p, in_bytes, cudaMemcpyHostToDevice, st));
     int* d_flag = reinterpret_cast<int*>(c->s1.as<unsigned char>() + in_bytes);
     LBG_CUDA(cudaMemsetAsync(d_flag, 0, 4, st));
-    halofit_spec_kernel<<<(n_rows + 31) / 32, 32, 0, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, d_inv, d_inv + (m + 6),
+    const size_t hsmem = (12 * (size_t)m + 6 * (size_t)m + (m + 6) + m + (size_t)HF_WARPS * m) * 8 + (size_t)m * 4;
+    static bool attr_set = false;                  // the attribute is per function, not per device context
+    if (!attr_set) {
+        LBG_CUDA(cudaFuncSetAttribute(halofit_spec_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)((28 * (size_t)HF_MAX_R + 6) * 8 + HF_MAX_R * 4)));
+        attr_set = true;
+    }
+    halofit_spec_kernel<<<(n_rows + HF_WARPS - 1) / HF_WARPS, 32 * HF_WARPS, hsmem, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, d_inv, d_inv + (m + 6),
                                                            H.lns0_rev[0], H.lns0_rev[m - 1], lnr[0], lnr[m - 1], c->s1.as<double>(),
                                                            c->s5.as<HaloZ>(), d_flag);
     ++launches;
