@@ -225,6 +225,15 @@ int lbg_forecast_spectra(lbg_ctx* ctx, int n_ell, const double* ell, double zmin
 /* snr.py:21-25 `snr`: sqrt( sum_{l <= lmax} nmodes (C_l / sqrt(Var_l))^2 ). */
 int lbg_snr(lbg_ctx* ctx, int n_ell, const double* ell, const double* cl, const double* var, const double* nmodes,
             double lmax, double* out_snr);
+/* lbg_snr for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same arguments, same kernel and same
+ * result as lbg_snr, but the device staging of the four vectors and of the result lives in a fixed file-scope device array instead of
+ * the context's grow-only scratch: the call performs no cudaMalloc / cudaFree / allocating library call.  Limit: n_ell <= 16384
+ * (LBG_EINVAL beyond, with a message); the array (512 KiB + 256 B) is held by every GPU that loads the library until the process
+ * exits.  All calls on a device share it and it keeps the previous call's contents (the result slot is cleared per call): calls that
+ * overlap on one GPU would race, so the library serialises them with a process-wide lock. */
+int lbg_snr_noalloc(lbg_ctx* ctx, int n_ell, const double* ell, const double* cl, const double* var, const double* nmodes,
+                    double lmax, double* out_snr);
 /* interloper.py:42-63 `get_ClsCov` for any set of fields: tot[l][a][b] = (C + N)^{ab}(l) (n_f x n_f, symmetric);
  * spectrum i is the field pair (spec_a[i], spec_b[i]);
  * cov[l][i][j] = (T^{ac} T^{bd} + T^{ad} T^{bc}) / (2 l + 1) / fsky  with (a,b) = pair i and (c,d) = pair j. */

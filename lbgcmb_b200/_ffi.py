@@ -102,6 +102,7 @@ def _declare(L):
                         c_int_p, c_double_p, c_double_p, c_double_p],
         'lbg_eval_spline_ext': [vp, i, d, c_double_p, i, c_double_p, c_double_p],
         'lbg_snr': [vp, i, c_double_p, c_double_p, c_double_p, c_double_p, d, c_double_p],
+        'lbg_snr_noalloc': [vp, i, c_double_p, c_double_p, c_double_p, c_double_p, d, c_double_p],
         'lbg_gaussian_cov': [vp, i, c_double_p, i, c_double_p, i, c_int_p, c_int_p, d, c_double_p],
         'lbg_fisher_accum': [vp, i, i, i, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p],
         'lbg_field_fisher': [vp, i, i, i, c_int_p, c_int_p, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p],

@@ -565,3 +565,51 @@ extern "C" int lbg_cadence_fisher(lbg_ctx* c, int n_ell, int n_bin, const double
                                   const double* mode_weight, double fsky, double* out_F, double* out_Fsl, double* out_S) {
     return mqw_fisher_impl(c, n_ell, n_bin, cgg, 1, bins, mode_weight, fsky, out_F, out_Fsl, out_S, true);
 }
+
+// ---- lbg_snr without any allocation ---------------------------------------------------------------------------------------------
+// Some callers cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  lbg_snr stages
+// its four input vectors and its result in the context's grow-only scratch buffer (cudaMalloc on first use / growth); this variant
+// runs the SAME kernel with that scratch in a file-scope device array of fixed size instead: it calls no cudaMalloc, cudaFree or any
+// allocating routine.  Every GPU that loads the library holds the array (LBG_SNR_NOALLOC_MAX x 4 doubles + one line = 512 KiB + 256 B)
+// until the process exits.  Every call on a device shares the array, and it keeps the last call's contents: the result slot is
+// cleared before each launch, and calls that overlap on one GPU (two contexts / lanes of a device, or two threads) race -- they
+// are serialised here by a process-wide mutex, callers outside this library's knowledge must not overlap them themselves.
+#define LBG_SNR_NOALLOC_MAX 16384
+static __device__ __align__(256) double g_snr_scratch[4 * LBG_SNR_NOALLOC_MAX + 32];   // [ell | cl | var | nmodes | result (own 256 B line)]
+
+namespace {
+std::mutex g_snr_noalloc_mu;
+double* g_snr_scratch_ptr[64];          // device address of g_snr_scratch per device (in host code the array's NAME is only a stand-in)
+}
+
+extern "C" int lbg_snr_noalloc(lbg_ctx* c, int n_ell, const double* ell, const double* cl, const double* var, const double* nmodes,
+                               double lmax, double* out_snr) {
+    LBG_REQUIRE(c && out_snr && n_ell >= 0, "lbg_snr_noalloc: bad argument");
+    LBG_REQUIRE(n_ell == 0 || (ell && cl && var && nmodes), "lbg_snr_noalloc: NULL array");
+    LBG_REQUIRE(n_ell <= LBG_SNR_NOALLOC_MAX, "lbg_snr_noalloc: n_ell=%d exceeds the fixed scratch of %d multipoles (use lbg_snr, which allocates)",
+                n_ell, LBG_SNR_NOALLOC_MAX);
+    LBG_REQUIRE(c->device >= 0 && c->device < 64, "lbg_snr_noalloc: device %d outside the 64 devices this entry point keeps an address for", c->device);
+    if (n_ell == 0) { *out_snr = 0.0; return LBG_OK; }
+    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::mutex> gs(g_snr_noalloc_mu);          // the array is shared by every context of the device
+    LBG_CUDA(cudaSetDevice(c->device));
+    double*& d = g_snr_scratch_ptr[c->device];
+    if (!d) {                                                  // set-up, once per device, with that device current
+        double* p = nullptr;
+        LBG_CUDA(cudaGetSymbolAddress((void**)&p, g_snr_scratch));
+        d = p;
+    }
+    const size_t nb = (size_t)n_ell * 8, N = LBG_SNR_NOALLOC_MAX;
+    double* d_out = d + 4 * N;
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaMemcpyAsync(d, ell, nb, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d + N, cl, nb, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d + 2 * N, var, nb, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d + 3 * N, nmodes, nb, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemsetAsync(d_out, 0, 8, st));                // the slot keeps the previous call's result otherwise
+    KernelTimer t(c);
+    snr_kernel<<<1, RED_T, 0, st>>>(n_ell, d, d + N, d + 2 * N, d + 3 * N, lmax, d_out);
+    t.launched();
+    LBG_CUDA(cudaMemcpyAsync(out_snr, d_out, 8, cudaMemcpyDeviceToHost, st));
+    return t.finish();
+}
