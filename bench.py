@@ -525,7 +525,7 @@ def main():
                          'kernel': 'n0_rows5_kernel', 'kernel_ms': main_ms, 'kernel_share_of_step': share},
             'clocks': clocks, 'wall_s_timed_region': t_region,
         }
-        if not a.no_cpu_baseline:
+        if not a.no_cpu_baseline and world == 1:                   # rank 0 at N = 1 only: the other ranks would idle in the final barrier
             sample = np.array([50, 162, 520, 1677, 3660, 5000][:max(a.cpu_sample, 1)])     # SURVEY.md 8(d) subset
             sample = sample[(sample >= a.lmin) & (sample <= a.lmax)]
             reference = reference_staged()
