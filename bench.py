@@ -12,7 +12,8 @@ NCCL all-reduce of the partial S/N^2 / Fisher / bias sums and one all-gather of 
 north_star names; "scaling": "strong" (total work fixed).
 
   value      whole-job L-modes/s over the DEVICE time of the step: every kernel of the step (CUDA events on the library's stream,
-             calls made one after another) + the collectives (CUDA events on torch's stream); max over ranks
+             calls made one after another; max over ranks) + the collectives (CUDA events on torch's stream; min over ranks: the
+             rank that arrives last measures the exchange without the wait for its peers)
   e2e        the same metric through the public call with HOST inputs (tables, callables) and host results: table comparison /
              upload, callable evaluation, H2D, kernels (N0 started first on the library's second context and overlapped with the
              Limber stage), D2H, collectives -- wall clock between barriers, max over ranks
@@ -434,13 +435,17 @@ def main():
     assert np.all(res['nkk'] > 0) and np.all(np.isfinite(rows_of(res)))
     assert np.max(np.abs(rows_of(res) / rows_of(res_seq) - 1)) < 1e-13, 'overlapped step changed the results'
 
-    dev_ms = acc['kernel_ms'] + acc['xchg_ms']
-    t = torch.tensor([dev_ms, seq_s, ovl_s, acc['n0_ms'], acc['main_ms'], acc['xchg_ms']], dtype=torch.float64, device='cuda')
+    # device time of the step = max over ranks of the summed kernel times + the exchange.  The exchange is timed with CUDA events on
+    # every rank; a rank that arrives early also waits for its peers inside the collective, so the time of the exchange itself is the
+    # MIN over ranks (the last rank to arrive sees no wait).  The skew is host time, which e2e (wall clock) contains.
+    t = torch.tensor([acc['kernel_ms'], seq_s, ovl_s, acc['n0_ms'], acc['main_ms'], -acc['xchg_ms']], dtype=torch.float64, device='cuda')
     counts = torch.tensor([float(nodes_step), float(unmasked_step), float(acc['launches'])], dtype=torch.float64, device='cuda')
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(counts, op=dist.ReduceOp.SUM)
-    dev_ms, seq_s, ovl_s, n0_ms, main_ms_sum, xchg_ms = (float(x) for x in t)
+    kern_ms, seq_s, ovl_s, n0_ms, main_ms_sum, xchg_ms = (float(x) for x in t)
+    xchg_ms = -xchg_ms
+    dev_ms = kern_ms + xchg_ms
     nodes_all, unmasked_all, launches_all = (float(x) for x in counts)
     # per-rank phase breakdown of the last overlapped step (wall ms on that rank)
     mine = {k_: (v * 1e3 if k_.endswith('_s') else v) for k_, v in phases[-1].items()}
@@ -475,7 +480,7 @@ def main():
         fpn = prof.get('flop_per_unmasked_node') if prof else None
         ach = unmasked_all * fpn / (main_ms * 1e-3) * 1e-12 / world if fpn else None
         n_band = len(bands)
-        fc_ms = (dev_ms - n0_ms - xchg_ms) / a.steps
+        fc_ms = (kern_ms - n0_ms) / a.steps
         # bytes counted from the arrays handed to / returned by the C ABI per step on one rank (pinned staging blocks)
         nLr = int(np.ceil(Ls.size / world))
         nz = (1000, 999, 2000)                                   # Cgg, Ckg, Ckk z nodes (interloper.py:148-149, cmb/lensing.py:27)

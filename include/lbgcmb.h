@@ -157,10 +157,17 @@ int lbg_pk_table_nk(lbg_ctx* ctx, int* n_k);
  * from a per-redshift fit of ln(D^2 sigma_0^2) in FITPACK order, one device thread per redshift on a factorisation shared by all.
  * out_spec (may be NULL): [rows][4] = {k_nl = 1 / R_nl, n_eff, curvature, flag}; flag 1 = R_nl outside the tabulated decade: that row
  * needs the reference's exception path (lbg_halofit_spec_host on a re-sampled grid + lbg_pk_build_table).  *n_flagged = number of
- * such rows.  build != 0 and no flagged row: the tables are built (row r = P(k, z_r)).  out_pnl: n_tables == 1 only. */
+ * such rows.  build = 0: parameters only; 1: the tables are built when no row is flagged (row r = P(k, z_r)) and waited for;
+ * 2: the build is enqueued and the call returns at once (*n_flagged = -1, no host outputs): the caller does its host work (evaluating
+ * p(z), b(z)) meanwhile, later calls on the context are ordered behind the build, and lbg_pk_build_wait() reports the flagged count
+ * (> 0: flagged rows were built as linear rows; rebuild through the explicit route before using results).  out_pnl: n_tables == 1. */
 int lbg_pk_build_tables_hf(lbg_ctx* ctx, int n_tables, const int* n_rows, const int* slots, const double* zin,
                            int n_R, const double* lnr, const double* R, double fnu, double om0, double w, int takahashi, int build,
                            double* out_spec, int* n_flagged, double* out_pnl /*[n_rows][n_k] or NULL*/);
+int lbg_pk_build_wait(lbg_ctx* ctx, int* n_flagged);
+/* Enqueues (without waiting) the sigma_0^2(R) sums of the linear table just installed; lbg_pk_build_tables_hf picks them up.  Optional:
+ * lets the caller overlap host work with the sums. */
+int lbg_pk_prepare_hf(lbg_ctx* ctx, int n_R, const double* lnr, const double* R);
 /* lbg_upload_pk_linear with the caller's own ln k values (numpy's np.log(k); NULL = this libm's): the sigma^2(R) sums of
  * lbg_pk_build_tables_hf then use exactly the reference's panel widths. */
 int lbg_upload_pk_linear2(lbg_ctx* ctx, int n_k, const double* k, const double* plin_z0, const double* w_lnk, const double* lnk);

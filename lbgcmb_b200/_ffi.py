@@ -86,6 +86,8 @@ def _declare(L):
         'lbg_halofit_spec_host': [i, c_double_p, c_double_p, d, c_double_p, c_int_p],
         'lbg_pk_table_nk': [vp, c_int_p],
         'lbg_pk_build_tables_hf': [vp, i, c_int_p, c_int_p, c_double_p, i, c_double_p, c_double_p, d, d, d, i, i, c_double_p, c_int_p, c_double_p],
+        'lbg_pk_build_wait': [vp, c_int_p],
+        'lbg_pk_prepare_hf': [vp, i, c_double_p, c_double_p],
         'lbg_upload_pk_linear2': [vp, i, c_double_p, c_double_p, c_double_p, c_double_p],
         'lbg_pk_upload_rows': [vp, i, c_double_p, i, c_double_p],
         'lbg_pk_eval': [vp, i, i, c_double_p, i, c_double_p],

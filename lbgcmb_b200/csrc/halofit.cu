@@ -170,13 +170,50 @@ HfGrid g_hf;
 }
 
 struct lbg_hf_state {               // per context: device copies of the factor, sigma_0^2 on the grid for the current linear table
-    std::vector<double> lnr, s0, lns0_rev, lnr_rev, inv_t, inv_c;
-    unsigned long long pk_gen = ~0ull;
-    lbg::DevBuf dev;                // [s0 m | t m+6 | rot 12 m | band 6 m | lint m (int)]
-    bool dev_ok = false;
+    std::vector<double> lnr, R, lns0_rev, lnr_rev, inv;
+    unsigned long long pk_gen = ~0ull;      // linear table the inverse fit belongs to
+    unsigned long long s0_gen = ~0ull;      // linear table whose sigma_0^2 sums were enqueued last
+    lbg::DevBuf dev;                // [s0 m | t m+6 | rot 12 m | band 6 m | lint m (int, padded) | inverse fit: t m+6, c m]
+    lbg::DevBuf Rdev, zin, rows;    // R grid; build inputs (+ flag counter); HaloZ rows
+    lbg::PinBuf pin, pin_in;        // sigma_0^2 read-back (+ flag count); build inputs (own buffers: the build may still be reading
+                                    // them when the next call on the context fills the shared staging blocks)
+    cudaEvent_t ev_s0a = nullptr, ev_s0 = nullptr, ev_b0 = nullptr, ev_b1 = nullptr;
+    bool dev_ok = false, pending = false;
+    int pending_launches = 0;
+    int init() {
+        for (cudaEvent_t* e : {&ev_s0a, &ev_s0, &ev_b0, &ev_b1}) LBG_CUDA(cudaEventCreate(e));
+        LBG_CUDA(cudaEventRecord(ev_s0a, 0)); LBG_CUDA(cudaEventRecord(ev_s0, 0));
+        return LBG_OK;
+    }
+    void release() {
+        dev.release(); Rdev.release(); zin.release(); rows.release(); pin.release(); pin_in.release();
+        for (cudaEvent_t e : {ev_s0a, ev_s0, ev_b0, ev_b1}) if (e) cudaEventDestroy(e);
+    }
 };
 
-void lbg_hf_release(lbg_ctx* c) { if (c->hf) { c->hf->dev.release(); delete c->hf; c->hf = nullptr; } }
+// Waits for the pending build, adds its device time (sigma^2 interval + build interval) and launches to the context's totals.
+static int hf_wait_locked(lbg_ctx* c, lbg_hf_state& H, int* n_flagged) {
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    H.pending = false;
+    if (e != cudaSuccess) { lbg::set_error("kernel execution failed: %s", cudaGetErrorString(e)); return LBG_ECUDA; }
+    float ms0 = 0.f, ms1 = 0.f;
+    cudaEventElapsedTime(&ms0, H.ev_s0a, H.ev_s0);
+    cudaEventElapsedTime(&ms1, H.ev_b0, H.ev_b1);
+    if (!(ms0 >= 0.f)) ms0 = 0.f;
+    if (getenv("LBG_DEBUG_HF")) fprintf(stderr, "hf_wait: sigma2 interval %.3f ms, build interval %.3f ms\n", ms0, ms1);
+    c->last_ms = (double)ms0 + ms1;
+    c->last_launches = H.pending_launches;
+    c->total_ms += c->last_ms;
+    c->total_launches += H.pending_launches;
+    H.pending_launches = 0;
+    cudaEventRecord(H.ev_s0a, c->stream);          // a later wait without new sums adds nothing
+    cudaEventRecord(H.ev_s0, c->stream);
+    *n_flagged = *reinterpret_cast<int*>(H.pin.as<double>() + H.lnr.size());
+    return LBG_OK;
+}
+
+void lbg_hf_release(lbg_ctx* c) { if (c->hf) { c->hf->release(); delete c->hf; c->hf = nullptr; } }
 
 // modi/halofit.py:70-98 on the host, FITPACK order: lnr increasing, lnsig = ln sigma^2 on it.  out = (rknl = k_nl = 1 / R_nl, neff, ncur).
 // *status: 0 ok; 1 = the derivative point ln(1 / rknl) lies outside the fitted range (scipy raises there: the reference's except branch).
@@ -204,13 +241,113 @@ extern "C" int lbg_halofit_spec_host(int n, const double* lnr, const double* lns
     return LBG_OK;
 }
 
+// ---- device-side build of the P(k,z) tables -------------------------------------------------------------------------------------
+// Pieces (all under the context lock, on the context's stream):
+//   hf_ensure_grid     factorisation of the ln R grid on the device (once per grid)
+//   hf_enqueue_sigma2  sigma_0^2(R_i) of the current linear table -> pinned host memory, NOT waited for (lbg_pk_prepare_hf: a caller
+//                      issues it right after the table upload and does host work meanwhile)
+//   hf_finish_sigma2   waits for it, fits the z = 0 inverse spline on the host (50 us; a single device thread would take 10x longer:
+//                      3000 dependent Givens rotations with a division and a square root each), uploads it
+//   then one spectral-parameter launch for all rows of all tables and one row launch per table.
+static int hf_ensure_grid(lbg_ctx* c, lbg_hf_state& H, int m, const double* lnr, const char* who) {
+    cudaStream_t st = c->stream;
+    const bool grid_same = (int)H.lnr.size() == m && !memcmp(H.lnr.data(), lnr, (size_t)m * 8);
+    if (grid_same && H.dev_ok) return LBG_OK;
+    std::lock_guard<std::mutex> gg(g_hf.mu);
+    if ((int)g_hf.lnr.size() != m || memcmp(g_hf.lnr.data(), lnr, (size_t)m * 8)) {
+        LBG_REQUIRE(g_hf.F.build(m, lnr), "%s: ln R grid must be strictly increasing", who);
+        g_hf.lnr.assign(lnr, lnr + m);
+    }
+    const size_t nd = (size_t)m + (m + 6) + 12 * (size_t)m + 6 * (size_t)m;    // then lint (m ints, padded to m doubles), then the inverse fit (2 m + 6)
+    if (H.dev.reserve((nd + m + 2 * (size_t)m + 6) * 8 + 64) || H.pin.reserve(((size_t)m + 8) * 8)) return LBG_ENOMEM;
+    double* d = H.dev.as<double>();
+    LBG_CUDA(cudaMemcpyAsync(d + m, g_hf.F.t.data(), (size_t)(m + 6) * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d + m + (m + 6), g_hf.F.rot.data(), (size_t)12 * m * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d + m + (m + 6) + 12 * (size_t)m, g_hf.F.a.data(), (size_t)6 * m * 8, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaMemcpyAsync(d + nd, g_hf.F.lint.data(), (size_t)m * 4, cudaMemcpyHostToDevice, st));
+    LBG_CUDA(cudaStreamSynchronize(st));
+    H.lnr.assign(lnr, lnr + m);
+    H.dev_ok = true;
+    H.pk_gen = ~0ull;
+    H.s0_gen = ~0ull;
+    return LBG_OK;
+}
+
+static int hf_enqueue_sigma2(lbg_ctx* c, lbg_hf_state& H, int m, const double* R, int* launches) {
+    if (H.s0_gen == c->pk_gen) return LBG_OK;                 // already in flight / done for this linear table
+    cudaStream_t st = c->stream;
+    if (H.Rdev.reserve((size_t)m * 8)) return LBG_ENOMEM;
+    if (H.R.size() != (size_t)m || memcmp(H.R.data(), R, (size_t)m * 8)) {
+        H.R.assign(R, R + m);
+        LBG_CUDA(cudaMemcpyAsync(H.Rdev.p, H.R.data(), (size_t)m * 8, cudaMemcpyHostToDevice, st));
+    }
+    double* d_s0 = H.dev.as<double>();
+    const double* kd = c->pk_lnk.as<double>();
+    const size_t smem = ((size_t)c->n_k + c->pk_npan0 + c->pk_npan1) * 8;
+    if (c->pk_npan0 > 0 && smem <= 48 * 1024) {              // the reference's own summation order (pk_kernels.cuh)
+        const double* sp = c->pk_simps.as<double>();
+        sigma2_np_kernel<<<m, 256, smem, st>>>(c->n_k, kd, sp, reinterpret_cast<const SimpsPanel*>(sp + c->n_k), c->pk_npan0, c->pk_npan1,
+                                               c->pk_first_dx, c->pk_last_dx, H.Rdev.as<double>(), d_s0);
+    } else {
+        sigma2_kernel<<<m, 256, 0, st>>>(c->n_k, kd, kd + 2 * (size_t)c->n_k, H.Rdev.as<double>(), d_s0);
+    }
+    ++*launches;
+    LBG_CUDA(cudaMemcpyAsync(H.pin.p, d_s0, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+    LBG_CUDA(cudaEventRecord(H.ev_s0, st));
+    H.s0_gen = c->pk_gen;
+    return LBG_OK;
+}
+
+static int hf_finish_sigma2(lbg_ctx* c, lbg_hf_state& H, int m, const double* lnr, const char* who) {
+    if (H.pk_gen == c->pk_gen) return LBG_OK;
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaEventSynchronize(H.ev_s0));
+    const double* s0 = H.pin.as<double>();
+    H.lns0_rev.resize(m); H.lnr_rev.resize(m);
+    bool mono = true;
+    for (int i = 0; i < m; ++i) { H.lns0_rev[i] = log(s0[m - 1 - i]); H.lnr_rev[i] = lnr[m - 1 - i]; }
+    for (int i = 1; i < m; ++i) mono = mono && H.lns0_rev[i] > H.lns0_rev[i - 1];
+    LBG_REQUIRE(mono, "%s: sigma^2(R) of this table is not strictly decreasing on the grid", who);
+    fitpack::FitFactor inv;
+    inv.build(m, H.lns0_rev.data());
+    H.inv.resize(2 * (size_t)m + 6);
+    memcpy(H.inv.data(), inv.t.data(), (size_t)(m + 6) * 8);
+    inv.solve(H.lnr_rev.data(), H.inv.data() + (m + 6));
+    const size_t nd = (size_t)m + (m + 6) + 12 * (size_t)m + 6 * (size_t)m;
+    LBG_CUDA(cudaMemcpyAsync(H.dev.as<double>() + nd + m, H.inv.data(), H.inv.size() * 8, cudaMemcpyHostToDevice, st));   // pageable: staged before return
+    H.pk_gen = c->pk_gen;
+    return LBG_OK;
+}
+
+// sigma_0^2 on the HALOFIT grid for the linear table just installed, enqueued and not waited for: lbg_pk_build_tables_hf picks the
+// result up.  Optional (the build issues it itself when it was not): it lets the caller overlap its own host work with the sums.
+extern "C" int lbg_pk_prepare_hf(lbg_ctx* c, int n_R, const double* lnr, const double* R) {
+    LBG_REQUIRE(c && lnr && R, "lbg_pk_prepare_hf: NULL argument");
+    LBG_REQUIRE(n_R >= 7 && n_R <= HF_MAX_R, "lbg_pk_prepare_hf: n_R=%d outside [7, %d]", n_R, HF_MAX_R);
+    std::lock_guard<std::mutex> g(c->mu);
+    if (c->n_k <= 0) { set_error("lbg_pk_prepare_hf: call lbg_upload_pk_linear first"); return LBG_ESTATE; }
+    LBG_CUDA(cudaSetDevice(c->device));
+    if (!c->hf) { c->hf = new lbg_hf_state(); if (int rc = c->hf->init()) return rc; }
+    lbg_hf_state& H = *c->hf;
+    if (int rc = hf_ensure_grid(c, H, n_R, lnr, "lbg_pk_prepare_hf")) return rc;
+    int launches = 0;
+    if (H.s0_gen != c->pk_gen) LBG_CUDA(cudaEventRecord(H.ev_s0a, c->stream));
+    if (int rc = hf_enqueue_sigma2(c, H, n_R, R, &launches)) return rc;
+    H.pending_launches += launches;
+    return LBG_OK;
+}
+
 // Device-side build of the P(k,z) tables of several z grids in one call.  Table i has n_rows[i] rows and goes to table slot
 // slots[i] (lbg_pk_select_slot numbering; -1 = the current slot); zin = the tables' rows one after another,
 // zin[row][4] = {D(z)^2, Omega_m(z), Omega_L(z), use_halofit (0 -> linear row)};
 // lnr / R: the reference's fitting grid (np.linspace(ln 0.1, ln 10, 500) and its exp, modi/halofit.py:36-37) as the caller's numpy
 // computed them.  out_spec (may be NULL): [total rows][4] = {k_nl = 1 / R_nl (the reference's `rknl`), n_eff, curvature, flag}; flag 1 =
 // R_nl outside the tabulated decade (the caller evaluates that row by the reference's exception path and passes it through
-// lbg_pk_build_table).  *n_flagged receives the number of flagged rows; the tables are built only when it is 0 and build != 0.
+// lbg_pk_build_table).  *n_flagged receives the number of flagged rows.
+// build: 0 = spectral parameters only; 1 = build the tables when no row is flagged, wait for them; 2 = enqueue the table build and
+// RETURN WITHOUT WAITING (*n_flagged = -1): the caller does host work meanwhile, any later call on this context is ordered behind
+// the build, and lbg_pk_build_wait() reports the flagged count afterwards (> 0: the tables hold linear rows where HALOFIT rows were
+// flagged and must be rebuilt through the explicit route before their results are used).  out_spec / out_pnl need build != 2.
 // out_pnl (may be NULL, n_tables == 1 only): the rows of the table.
 extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_rows_each, const int* slots, const double* zin,
                                       int n_R, const double* lnr, const double* R, double fnu, double om0, double w, int takahashi,
@@ -219,6 +356,7 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
                 "lbg_pk_build_tables_hf: bad argument");
     LBG_REQUIRE(n_R >= 7 && n_R <= HF_MAX_R, "lbg_pk_build_tables_hf: n_R=%d outside [7, %d]", n_R, HF_MAX_R);
     LBG_REQUIRE(out_pnl == nullptr || n_tables == 1, "lbg_pk_build_tables_hf: out_pnl needs n_tables == 1");
+    LBG_REQUIRE(build >= 0 && build <= 2 && (build != 2 || (!out_spec && !out_pnl)), "lbg_pk_build_tables_hf: build must be 0, 1 or 2 (2: no host outputs)");
     int n_rows = 0;
     for (int i = 0; i < n_tables; ++i) {
         LBG_REQUIRE(n_rows_each[i] > 0 && slots[i] >= -1 && slots[i] < lbg_ctx::PK_SLOTS, "lbg_pk_build_tables_hf: table %d: bad size / slot", i);
@@ -229,78 +367,32 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
     if (c->n_k <= 0) { set_error("lbg_pk_build_tables_hf: call lbg_upload_pk_linear first"); return LBG_ESTATE; }
     LBG_CUDA(cudaSetDevice(c->device));
     cudaStream_t st = c->stream;
-    if (!c->hf) c->hf = new lbg_hf_state();
+    if (!c->hf) { c->hf = new lbg_hf_state(); if (int rc = c->hf->init()) return rc; }
     lbg_hf_state& H = *c->hf;
+    if (H.pending) { set_error("lbg_pk_build_tables_hf: an asynchronous build is pending: call lbg_pk_build_wait first"); return LBG_ESTATE; }
     const int m = n_R;
     int launches = 0;
-    KernelTimer t(c);
-    // ---- the grid's factorisation (per process) and its device copy (per context) ----
-    const bool grid_same = (int)H.lnr.size() == m && !memcmp(H.lnr.data(), lnr, (size_t)m * 8);
-    const size_t nd = (size_t)m + (m + 6) + 12 * (size_t)m + 6 * (size_t)m;    // then lint (m ints, padded to m doubles), then the inverse fit (2 m + 6)
-    if (!grid_same || !H.dev_ok) {
-        std::lock_guard<std::mutex> gg(g_hf.mu);
-        if ((int)g_hf.lnr.size() != m || memcmp(g_hf.lnr.data(), lnr, (size_t)m * 8)) {
-            LBG_REQUIRE(g_hf.F.build(m, lnr), "lbg_pk_build_tables_hf: ln R grid must be strictly increasing");
-            g_hf.lnr.assign(lnr, lnr + m);
-        }
-        if (H.dev.reserve((nd + m + 2 * (size_t)m + 6) * 8 + 64)) return LBG_ENOMEM;
-        double* d = H.dev.as<double>();
-        LBG_CUDA(cudaMemcpyAsync(d + m, g_hf.F.t.data(), (size_t)(m + 6) * 8, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaMemcpyAsync(d + m + (m + 6), g_hf.F.rot.data(), (size_t)12 * m * 8, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaMemcpyAsync(d + m + (m + 6) + 12 * (size_t)m, g_hf.F.a.data(), (size_t)6 * m * 8, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaMemcpyAsync(d + nd, g_hf.F.lint.data(), (size_t)m * 4, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaStreamSynchronize(st));
-        H.lnr.assign(lnr, lnr + m);
-        H.dev_ok = true;
-        H.pk_gen = ~0ull;
-    }
+    if (int rc = hf_ensure_grid(c, H, m, lnr, "lbg_pk_build_tables_hf")) return rc;
+    if (H.s0_gen != c->pk_gen) LBG_CUDA(cudaEventRecord(H.ev_s0a, st));
+    if (int rc = hf_enqueue_sigma2(c, H, m, R, &launches)) return rc;
+    if (int rc = hf_finish_sigma2(c, H, m, lnr, "lbg_pk_build_tables_hf")) return rc;
+    const size_t nd = (size_t)m + (m + 6) + 12 * (size_t)m + 6 * (size_t)m;
     double* d = H.dev.as<double>();
-    double* d_s0 = d;
+    const double* d_s0 = d;
     const double* d_t = d + m;
     const double* d_rot = d_t + (m + 6);
     const double* d_band = d_rot + 12 * (size_t)m;
     const int* d_lint = reinterpret_cast<const int*>(d + nd);
-    double* d_inv = d + nd + m;
-    // ---- sigma_0^2 on the grid + the z = 0 inverse fit: once per linear table ----
-    if (H.pk_gen != c->pk_gen) {
-        if (c->s0.reserve((size_t)m * 8) || c->pin_out.reserve((size_t)m * 8)) return LBG_ENOMEM;
-        LBG_CUDA(cudaMemcpyAsync(c->s0.p, R, (size_t)m * 8, cudaMemcpyHostToDevice, st));
-        const double* kd = c->pk_lnk.as<double>();
-        const size_t smem = ((size_t)c->n_k + c->pk_npan0 + c->pk_npan1) * 8;
-        if (c->pk_npan0 > 0 && smem <= 48 * 1024) {              // the reference's own summation order (pk_kernels.cuh)
-            const double* sp = c->pk_simps.as<double>();
-            sigma2_np_kernel<<<m, 256, smem, st>>>(c->n_k, kd, sp, reinterpret_cast<const SimpsPanel*>(sp + c->n_k), c->pk_npan0, c->pk_npan1,
-                                                   c->pk_first_dx, c->pk_last_dx, c->s0.as<double>(), d_s0);
-        } else {
-            sigma2_kernel<<<m, 256, 0, st>>>(c->n_k, kd, kd + 2 * (size_t)c->n_k, c->s0.as<double>(), d_s0);
-        }
-        ++launches;
-        LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, d_s0, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
-        LBG_CUDA(cudaStreamSynchronize(st));
-        H.s0.assign(c->pin_out.as<double>(), c->pin_out.as<double>() + m);
-        H.lns0_rev.resize(m); H.lnr_rev.resize(m);
-        bool mono = true;
-        for (int i = 0; i < m; ++i) { H.lns0_rev[i] = log(H.s0[m - 1 - i]); H.lnr_rev[i] = lnr[m - 1 - i]; }
-        for (int i = 1; i < m; ++i) mono = mono && H.lns0_rev[i] > H.lns0_rev[i - 1];
-        LBG_REQUIRE(mono, "lbg_pk_build_tables_hf: sigma^2(R) of this table is not strictly decreasing on the grid");
-        fitpack::FitFactor inv;
-        inv.build(m, H.lns0_rev.data());
-        H.inv_t = inv.t;
-        H.inv_c.resize(m);
-        inv.solve(H.lnr_rev.data(), H.inv_c.data());
-        LBG_CUDA(cudaMemcpyAsync(d_inv, H.inv_t.data(), (size_t)(m + 6) * 8, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaMemcpyAsync(d_inv + (m + 6), H.inv_c.data(), (size_t)m * 8, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaStreamSynchronize(st));
-        H.pk_gen = c->pk_gen;
-    }
+    const double* d_inv = d + nd + m;
     // ---- per row on the device: R_nl from the inverse fit, flags, the per-redshift forward fit ----
     const size_t in_bytes = (size_t)n_rows * 32;
-    if (c->pin_in.reserve(in_bytes + 64) || c->s1.reserve(in_bytes + 64) || c->s5.reserve((size_t)n_rows * sizeof(HaloZ)) ||
-        c->pin_out.reserve((size_t)n_rows * sizeof(HaloZ) + 64))
+    if (H.pin_in.reserve(in_bytes + 64) || H.zin.reserve(in_bytes + 64) || H.rows.reserve((size_t)n_rows * sizeof(HaloZ)) ||
+        (out_spec && c->pin_out.reserve((size_t)n_rows * sizeof(HaloZ) + 64)))
         return LBG_ENOMEM;
-    memcpy(c->pin_in.p, zin, in_bytes);
-    LBG_CUDA(cudaMemcpyAsync(c->s1.p, c->pin_in.p, in_bytes, cudaMemcpyHostToDevice, st));
-    int* d_flag = reinterpret_cast<int*>(c->s1.as<unsigned char>() + in_bytes);
+    memcpy(H.pin_in.p, zin, in_bytes);
+    LBG_CUDA(cudaEventRecord(H.ev_b0, st));
+    LBG_CUDA(cudaMemcpyAsync(H.zin.p, H.pin_in.p, in_bytes, cudaMemcpyHostToDevice, st));
+    int* d_flag = reinterpret_cast<int*>(H.zin.as<unsigned char>() + in_bytes);
     LBG_CUDA(cudaMemsetAsync(d_flag, 0, 4, st));
     const size_t hsmem = (12 * (size_t)m + 6 * (size_t)m + (m + 6) + m + (size_t)HF_WARPS * m) * 8 + (size_t)m * 4;
     static bool attr_set = false;                  // the attribute is per function, not per device context
@@ -310,17 +402,17 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
         attr_set = true;
     }
     halofit_spec_kernel<<<(n_rows + HF_WARPS - 1) / HF_WARPS, 32 * HF_WARPS, hsmem, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, d_inv, d_inv + (m + 6),
-                                                           H.lns0_rev[0], H.lns0_rev[m - 1], lnr[0], lnr[m - 1], c->s1.as<double>(),
-                                                           c->s5.as<HaloZ>(), d_flag);
+                                                           H.lns0_rev[0], H.lns0_rev[m - 1], lnr[0], lnr[m - 1], H.zin.as<double>(),
+                                                           H.rows.as<HaloZ>(), d_flag);
     ++launches;
+    int* hflag = reinterpret_cast<int*>(H.pin.as<double>() + m);
+    LBG_CUDA(cudaMemcpyAsync(hflag, d_flag, 4, cudaMemcpyDeviceToHost, st));
     int flagged = 0;
-    if (build) {                                   // the decision to build needs the count: one small synchronous copy
-        int* hflag = reinterpret_cast<int*>(c->pin_out.as<unsigned char>() + (size_t)n_rows * sizeof(HaloZ));
-        LBG_CUDA(cudaMemcpyAsync(hflag, d_flag, 4, cudaMemcpyDeviceToHost, st));
+    if (build == 1) {                              // the decision to build needs the count
         LBG_CUDA(cudaStreamSynchronize(st));
         flagged = *hflag;
     }
-    const bool do_build = build && flagged == 0;
+    const bool do_build = build == 2 || (build == 1 && flagged == 0);
     const int n_k = c->n_k;
     if (do_build) {
         HaloConst hc{fnu, om0, w, takahashi};
@@ -331,30 +423,42 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
             const bool cur = slots[i] < 0 || slots[i] == c->pk_cur;
             DevBuf& buf = cur ? c->pk_pnl : c->pk_store[slots[i]];
             if (buf.reserve((size_t)nr * n_k * 8)) return LBG_ENOMEM;
-            pnl_kernel<<<dim3((n_k + 127) / 128, nr), 128, 0, st>>>(nr, n_k, kd, kd + n_k, c->s5.as<HaloZ>() + row0, hc, buf.as<double>());
+            pnl_kernel<<<dim3((n_k + 127) / 128, nr), 128, 0, st>>>(nr, n_k, kd, kd + n_k, H.rows.as<HaloZ>() + row0, hc, buf.as<double>());
             ++launches;
             if (out_pnl) LBG_CUDA(cudaMemcpyAsync(out_pnl, buf.p, (size_t)nr * n_k * 8, cudaMemcpyDeviceToHost, st));
             row0 += nr;
         }
-    }
-    if (out_spec) LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, c->s5.p, (size_t)n_rows * sizeof(HaloZ), cudaMemcpyDeviceToHost, st));
-    t.launched(launches);
-    const int rc = t.finish();
-    if (rc) return rc;
-    if (out_spec) {
-        const HaloZ* hz = c->pin_out.as<HaloZ>();
-        flagged = 0;
-        for (int r = 0; r < n_rows; ++r) {
-            out_spec[4 * r] = hz[r].rknl; out_spec[4 * r + 1] = hz[r].neff; out_spec[4 * r + 2] = hz[r].ncur; out_spec[4 * r + 3] = hz[r].pad;
-            flagged += hz[r].pad != 0.0;
-        }
-    }
-    *n_flagged = flagged;
-    if (do_build)
         for (int i = 0; i < n_tables; ++i) {
             if (slots[i] < 0 || slots[i] == c->pk_cur) c->pnl_nz = n_rows_each[i]; else c->store_nz[slots[i]] = n_rows_each[i];
         }
+    }
+    if (out_spec) LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, H.rows.p, (size_t)n_rows * sizeof(HaloZ), cudaMemcpyDeviceToHost, st));
+    LBG_CUDA(cudaEventRecord(H.ev_b1, st));
+    LBG_CUDA(cudaGetLastError());
+    H.pending_launches += launches;
+    H.pending = true;
+    if (build == 2) { *n_flagged = -1; return LBG_OK; }
+    int rc = hf_wait_locked(c, H, &flagged);
+    if (rc) return rc;
+    if (out_spec) {
+        const HaloZ* hz = c->pin_out.as<HaloZ>();
+        for (int r = 0; r < n_rows; ++r) {
+            out_spec[4 * r] = hz[r].rknl; out_spec[4 * r + 1] = hz[r].neff; out_spec[4 * r + 2] = hz[r].ncur; out_spec[4 * r + 3] = hz[r].pad;
+        }
+    }
+    *n_flagged = flagged;
     return LBG_OK;
+}
+
+// Waits for the build lbg_pk_build_tables_hf(build = 2) enqueued; *n_flagged = rows whose R_nl left the tabulated decade (0: the tables
+// are good).  Without a pending build: *n_flagged = 0.
+extern "C" int lbg_pk_build_wait(lbg_ctx* c, int* n_flagged) {
+    LBG_REQUIRE(c && n_flagged, "lbg_pk_build_wait: NULL argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    *n_flagged = 0;
+    if (!c->hf || !c->hf->pending) return LBG_OK;
+    LBG_CUDA(cudaSetDevice(c->device));
+    return hf_wait_locked(c, *c->hf, n_flagged);
 }
 
 // Number of k nodes of the linear table installed on the context (0: none): callers size their host buffers for

@@ -69,6 +69,7 @@ class Cosmology(object):
         self._wlnk = None
         self._sig0 = None
         self._spec_cache = {}
+        self._async_keys = None
         self._bg_cache = {}              # per z grid: D(z)^2, Omega_m(z), Omega_L(z) -- the background, independent of the P(k) table
         self._rows_key = None
         self._slots = {}                 # z-grid key -> device table slot (lbg_pk_select_slot); insertion order = LRU order
@@ -144,6 +145,9 @@ class Cosmology(object):
                 self._wlnk = (_ffi.f64(simps_weights_x(lnk)), lnk, k.copy())
             _ffi.check(_ffi.lib().lbg_upload_pk_linear2(ctx.handle, k.size, _ffi._dp(k), _ffi._dp(p), _ffi._dp(self._wlnk[0]),
                                                         _ffi._dp(self._wlnk[1])))
+            s8 = self.sig8
+            if s8 < 1.0 and s8 > 0.6:        # the HALOFIT sigma^2 sums start now, unwaited: build_tables picks them up
+                _ffi.check(_ffi.lib().lbg_pk_prepare_hf(ctx.handle, _HF_LNR.size, _ffi._dp(_HF_LNR), _ffi._dp(_HF_R)))
             _owner[ctx.device] = owner
             self._rows_key = None
             self._slots = {}             # the upload dropped every P(k,z) table of the context
@@ -153,6 +157,7 @@ class Cosmology(object):
 
     def invalidate_device(self):
         """Forget what this object has on the GPU: the next call uploads the linear table and rebuilds the P(k,z) rows."""
+        self.finish_tables()
         dev = _ffi.context(self.device).device
         if (_owner.get(dev) or (None,))[0] == self._token:
             _owner[dev] = None
@@ -183,6 +188,22 @@ class Cosmology(object):
             self._spec_cache[key] = spec
         return self._spec_cache[key]
 
+    def finish_tables(self):
+        """Wait for a build started with build_tables(..., wait=False).  True: the tables are good; False: some redshift needs the
+        reference's exception path -- the tables were dropped, call build_tables(grids) (blocking) and redo what used them."""
+        import ctypes as C
+        if not self._async_keys:
+            return True
+        keys, self._async_keys = self._async_keys, None
+        n = C.c_int(0)
+        _ffi.check(_ffi.lib().lbg_pk_build_wait(_ffi.context(self.device).handle, C.byref(n)))
+        if n.value:
+            for key in keys:
+                self._slots.pop(key, None)
+            self._rows_key = None
+            return False
+        return True
+
     def _device_tables(self, ctx, zins, slots, build, want_spec=False, out=None):
         """lbg_pk_build_tables_hf on one or more z grids: zins = [rows[n_i, 4] = (D^2, Omega_m(z), Omega_L(z), use_halofit)], slots =
         their table slots (-1: the current one).  Returns (spec[sum n_i, 4] or None, n_flagged)."""
@@ -212,6 +233,7 @@ class Cosmology(object):
             for i, z in enumerate(zs):
                 out[i] = self.halofit_spec(z, sig8)
             return out
+        self.finish_tables()
         ctx = self._ctx()
         zin = np.zeros((zs.size, 4))
         zin[:, 0] = D2
@@ -227,6 +249,7 @@ class Cosmology(object):
         """Device-resident table with row r = P(k, zs[r]): pkanlin (HALOFIT for z <= 4, else linear) or pkalin."""
         zs = np.atleast_1d(np.asarray(zs, dtype=np.float64))
         key = (zs.tobytes(), bool(nonlinear), sig8, zmax_halofit)
+        self.finish_tables()
         ctx = self._ctx()
         if self._rows_key == key and not want_host:
             return None
@@ -279,10 +302,12 @@ class Cosmology(object):
         self._slots[key] = slot
         return out
 
-    def build_tables(self, grids, nonlinear=True, sig8=None, zmax_halofit=4.0):
+    def build_tables(self, grids, nonlinear=True, sig8=None, zmax_halofit=4.0, wait=True):
         """Table slots for several z grids at once, every missing table built by ONE library call (lbg_pk_build_tables_hf: one
         sigma^2 pass, one spectral-parameter launch for all rows, one row launch per table).  Falls back to table_slot per grid for
-        unusual sigma_8 or when a redshift needs the reference's exception path."""
+        unusual sigma_8 or when a redshift needs the reference's exception path.  wait=False: the build is enqueued and not waited
+        for (the caller evaluates its p(z), b(z) callables meanwhile; any library call made afterwards is ordered behind it) and
+        finish_tables() must be called before results that used the tables are trusted."""
         grids = [np.atleast_1d(np.asarray(z, dtype=np.float64)) for z in grids]
         keys = [(z.tobytes(), bool(nonlinear), sig8, zmax_halofit) for z in grids]
         s8 = self.sig8 if sig8 is None else sig8
@@ -307,8 +332,12 @@ class Cosmology(object):
                 self._slots[keys[i]] = slot
                 zins.append(self._background(keys[i], grids[i], nonlinear, zmax_halofit))
                 slots.append(slot)
-            _, nflag = self._device_tables(ctx, zins, slots, build=True)
+            self.finish_tables()
+            _, nflag = self._device_tables(ctx, zins, slots, build=(1 if wait else 2))
             self._rows_key = None                          # whichever slot is current may just have been rewritten: select before use
+            if not wait:
+                self._async_keys = [keys[i] for i in missing]
+                nflag = 0
             if nflag:
                 for i in missing:
                     del self._slots[keys[i]]

@@ -21,11 +21,34 @@ from lbgcmb_b200.pmh import engine_of
 OUT_FIELDS = ('snr', 'F_s8s8', 'F_s8b1', 'F_b1s8', 'F_b1b1', 'bias_s8', 'bias_b1')
 
 
+_FINE = {}
+
+
+def _fine_grid(zmin, zmax):
+    """np.arange(zmin, zmax, 0.001): the normalisation grid of sliced_pz.py:6 / pz2nbar.py:8, kept per range."""
+    g = _FINE.get((zmin, zmax))
+    if g is None:
+        if len(_FINE) > 16:
+            _FINE.clear()
+        g = _FINE[(zmin, zmax)] = np.arange(zmin, zmax, 0.001)
+        g.setflags(write=False)
+    return g
+
+
+_DZ = {}
+
+
 def _grid_dz(zs):
     """The spacing sliced_pz.py:22-24 divides by: the 6-decimal rounded step of the (asserted uniform) grid."""
-    steps = set(np.around(np.ediff1d(zs), 6))
-    assert len(steps) == 1
-    return float(list(steps)[0])
+    key = (zs.size, float(zs[0]), float(zs[-1]))
+    dz = _DZ.get(key)
+    if dz is None:
+        steps = set(np.around(np.ediff1d(zs), 6))
+        assert len(steps) == 1
+        if len(_DZ) > 16:
+            _DZ.clear()
+        dz = _DZ[key] = float(list(steps)[0])
+    return dz
 
 
 def forecast_spectra(Pk_interps, Llls, samples, zmin=0.01, zmax=10.0, want_ckk=True):
@@ -45,32 +68,43 @@ def forecast_spectra(Pk_interps, Llls, samples, zmin=0.01, zmax=10.0, want_ckk=T
     zg, chig, wg, hcg = _cgg_nodes(float(zmin), float(zmax))
     zk, chik, wk, wkap = _ckg_nodes(float(zmin), float(zmax))
     n_s = len(samples)
-    fine = np.arange(zmin, zmax, 0.001)
+    grids = [zg, zk]
+    if want_ckk:
+        zc, chic, wc = _ckk_nodes(float(par['zscatter']))
+        grids.append(zc)
+    else:
+        chic = wc = np.zeros(0)
+    # Order of the host work (the GPU builds the P(k,z) tables meanwhile): the linear table goes up and its sigma^2 sums start;
+    # the callables are evaluated on the two Limber grids; the table build is enqueued; the callables are evaluated on the
+    # normalisation grid (the larger half of the host work); then the one library call of the stage.
+    ctx = engine._ctx()
     pgg, bgg, pkg, bkg = np.empty((n_s, zg.size)), np.empty((n_s, zg.size)), np.empty((n_s, zk.size)), np.empty((n_s, zk.size))
     norm, ngg = np.empty(n_s), np.empty(n_s)
     for i, smp in enumerate(samples):
         pz, bz = smp['pz'], smp['bz']
-        norm[i] = np.trapezoid(pz(fine), fine)                  # sliced_pz.py:6-9 == pz2nbar.pz_slice (same grid, same rule)
         pgg[i], pkg[i] = pz(zg), pz(zk)
         bgg[i], bkg[i] = _each(bz, zg), _each(bz, zk)
+    slots = engine.build_tables(grids, nonlinear=nonlinear, wait=False)
+    fine = _fine_grid(float(zmin), float(zmax))
+    for i, smp in enumerate(samples):
+        norm[i] = np.trapezoid(smp['pz'](fine), fine)           # sliced_pz.py:6-9 == pz2nbar.pz_slice (same grid, same rule)
         ngg[i] = 1. / (nbar_convert(smp['nbar'], unit='str') * norm[i]) if smp.get('nbar') is not None else np.nan   # Cgg.py:85-95
-    if want_ckk:
-        zc, chic, wc = _ckk_nodes(float(par['zscatter']))
-        slot_g, slot_k, slot_c = engine.build_tables([zg, zk, zc], nonlinear=nonlinear)
-    else:
-        chic = wc = np.zeros(0)
-        slot_g, slot_k = engine.build_tables([zg, zk], nonlinear=nonlinear)
-        slot_c = 0
-    ctx = engine._ctx()
     cgg, ckg = np.empty((n_s, Ld.size)), np.empty((n_s, Ld.size))
     ckk = np.empty(Ld.size) if want_ckk else None
     dp = _ffi._dp
-    _ffi.check(_ffi.lib().lbg_forecast_spectra(
-        ctx.handle, Ld.size, dp(Ld), float(zmin), float(zmax), float(par['h_100']),
-        zg.size, dp(zg), dp(chig), dp(hcg), dp(wg), _grid_dz(zg), int(slot_g),
-        zk.size, dp(zk), dp(chik), dp(wkap), dp(wk), _grid_dz(zk), int(slot_k),
-        chic.size, dp(_ffi.f64(chic)), dp(_ffi.f64(wc)), int(slot_c),
-        n_s, dp(pgg), dp(bgg), dp(pkg), dp(bkg), dp(norm), dp(cgg), dp(ckg), dp(ckk) if want_ckk else None))
+    chic, wc = _ffi.f64(chic), _ffi.f64(wc)
+    for attempt in (0, 1):
+        slot_g, slot_k = slots[0], slots[1]
+        slot_c = slots[2] if want_ckk else 0
+        _ffi.check(_ffi.lib().lbg_forecast_spectra(
+            ctx.handle, Ld.size, dp(Ld), float(zmin), float(zmax), float(par['h_100']),
+            zg.size, dp(zg), dp(chig), dp(hcg), dp(wg), _grid_dz(zg), int(slot_g),
+            zk.size, dp(zk), dp(chik), dp(wkap), dp(wk), _grid_dz(zk), int(slot_k),
+            chic.size, dp(chic), dp(wc), int(slot_c),
+            n_s, dp(pgg), dp(bgg), dp(pkg), dp(bkg), dp(norm), dp(cgg), dp(ckg), dp(ckk) if want_ckk else None))
+        if engine.finish_tables():
+            break
+        slots = engine.build_tables(grids, nonlinear=nonlinear)     # a redshift took the reference's exception path: explicit rows, again
     return ckk, cgg, ckg, ngg
 
 

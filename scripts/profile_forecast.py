@@ -35,18 +35,7 @@ for rep in range(25):
     t_all = time.perf_counter()
     t0 = time.perf_counter(); Nkk.upload_cls(ctx1, li, ni); tick('upload_cls (stack + compare)', t0)
     t0 = time.perf_counter(); call = Nkk.n0_begin(li, ni, Ls, bench.TERMS, 1.4, 1.0, True, lane=1); tick('n0_begin (incl. upload_cls again)', t0)
-    t0 = time.perf_counter()
-    fine = np.arange(0.01, 10.0, 0.001)
-    for s in smp:
-        np.trapezoid(s['pz'](fine), fine)
-    tick('callables on the fine grid (8 samples)', t0)
-    eng = T.engine
-    from lbgcmb_b200.Cgg import _cgg_nodes
-    from lbgcmb_b200.Ckg import _ckg_nodes
-    from lbgcmb_b200.lensing import _ckk_nodes
-    t0 = time.perf_counter(); eng._ctx(); tick('linear table upload', t0)
-    t0 = time.perf_counter(); eng.build_tables([_cgg_nodes(0.01, 10.0)[0], _ckg_nodes(0.01, 10.0)[0], _ckk_nodes(1100.)[0]]); tick('P(k,z) tables gg + kg + kk (one call: specs + rows on the device)', t0)
-    t0 = time.perf_counter(); ckk, cgg, ckg, ngg = sweep.forecast_spectra(Pk, Lf, smp); tick('forecast_spectra (tables parked; callables + 1 library call)', t0)
+    t0 = time.perf_counter(); ckk, cgg, ckg, ngg = sweep.forecast_spectra(Pk, Lf, smp); tick('forecast_spectra (upload, callables, tables built meanwhile, 1 library call)', t0)
     t0 = time.perf_counter(); nkk = call.result()[0]; tick('n0 wait', t0)
     t0 = time.perf_counter()
     sweep.forecast_grid(Lf, np.ones_like(Lf), ckk, cgg[:4], ckg[:4], ngg[:4], nkk[None, :], 0.4, 0.819, [s['fid_b1'] for s in samples],
