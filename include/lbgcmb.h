@@ -109,6 +109,22 @@ int lbg_n0_ho02_begin(lbg_ctx* ctx, int n_L, const double* L, unsigned terms_mas
                       int n_exact, const int* exact_rows, const double* exact_u);
 int lbg_n0_ho02_end(lbg_ctx* ctx, int n_L, double* out_nkk /*[n_L]*/, double* out_terms /*[5][n_L] or NULL*/,
                     long long* nodes_executed /*or NULL*/, long long* nodes_unmasked /*or NULL*/);
+/* Several noise levels of ONE beam in one pass (survey-design sweeps, BASELINE configs[4]; the reference loops Nkk over experiments,
+ * snr.py:108-124): estimators TT,TE,EE,EB, folded phi grid.  For levels that share the beam C^tot = S + n_level G(l), so the lensed
+ * splines and the noise shape are read once per node for all levels (n0_rows5m_kernel, groups of <= 3 levels): about half the
+ * device time per level of lbg_n0_ho02.  deltaT_uK_arcmin[n_lev], iterative[n_lev] (may be NULL: all 0).  out_nkk[n_lev][n_L],
+ * out_terms[n_lev][5][n_L] (may be NULL).  A level's result does not depend on which other levels travel with it; it agrees with
+ * lbg_n0_ho02 to ~1e-13 (the noise enters after the Horner sums instead of inside the coefficients).  Inputs the range-walking kernel
+ * cannot serve (see lbg_n0_ho02) return LBG_EINVAL: call lbg_n0_ho02 per level.  lbg_n0_last_path() reports 6. */
+int lbg_n0_ho02_levels(lbg_ctx* ctx, int n_L, const double* L, double thetab_arcmin, int n_lev, const double* deltaT_uK_arcmin,
+                       const int* iterative, double Tcmb_K, int n_l1, const double* l1, const double* w_l1,
+                       int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
+                       double lmax_T, double lmax_P, double lmin_v, double* out_nkk, double* out_terms);
+int lbg_n0_ho02_levels_begin(lbg_ctx* ctx, int n_L, const double* L, double thetab_arcmin, int n_lev, const double* deltaT_uK_arcmin,
+                             const int* iterative, double Tcmb_K, int n_l1, const double* l1, const double* w_l1,
+                             int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
+                             double lmax_T, double lmax_P, double lmin_v);
+int lbg_n0_ho02_levels_end(lbg_ctx* ctx, int n_lev, int n_L, double* out_nkk, double* out_terms);
 int lbg_n0_set_exact_below(lbg_ctx* ctx, double l_below);   /* 0 disables the scipy-order rows */
 int lbg_n0_last_path(lbg_ctx* ctx, int* path);
 /* Host-only (no GPU): scipy `interp1d(arange(n_knots), y, kind='cubic', bounds_error=False, fill_value=0.0)(x)`, bit for bit

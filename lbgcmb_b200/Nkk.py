@@ -153,6 +153,55 @@ def n0_begin(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'
     return N0Call(ctx, Ld.size, (Ld, ell, w_ell, cphi, sphi, w_phi, exact_rows, exact_u))
 
 
+class N0LevelsCall(object):
+    """lbg_n0_ho02_levels_begin issued: `result()` waits and returns (N0[n_lev, n_L], {term: integral[n_lev, n_L]})."""
+
+    def __init__(self, ctx, n_lev, n_L, keep):
+        self.ctx, self.n_lev, self.n_L, self._keep, self._res = ctx, n_lev, n_L, keep, None
+
+    def result(self):
+        if self._res is None:
+            import ctypes as C
+            out = np.empty((self.n_lev, self.n_L))
+            out_terms = np.empty((self.n_lev, 5, self.n_L))
+            _ffi.check(_ffi.lib().lbg_n0_ho02_levels_end(self.ctx.handle, self.n_lev, self.n_L, _ffi._dp(out), _ffi._dp(out_terms)))
+            path = C.c_int(0)
+            _ffi.check(_ffi.lib().lbg_n0_last_path(self.ctx.handle, C.byref(path)))
+            ms, launches = self.ctx.last_kernel_ms()
+            last_stats.update(kernel_ms=ms, launches=launches, n_L=self.n_L, n_lev=self.n_lev, main_kernel_ms=self.ctx.last_main_kernel_ms(),
+                              path=path.value)
+            self._keep = None
+            self._res = (out, {t: out_terms[:, i] for i, t in enumerate(('TT', 'TE', 'EE', 'EB', 'BB'))})
+        return self._res
+
+
+def n0_levels_begin(lensCl_interps, nolensCl_interps, Ls, thetab, DeltaTs, iteratives=None, device=None, Tcmb=None, lane=0,
+                    lmax_T=3000., lmax_P=5000., lmin_v=2.):
+    """Start N0 (TT, TE, EE, EB) for several noise levels DeltaTs[n_lev] of ONE beam `thetab` in one pass of the integrand
+    (lbg_n0_ho02_levels: the levels share every table read of a node); `iteratives[n_lev]` as Nkk's `iterative` per level.
+    The reference evaluates one experiment at a time (snr.py:108-124 loops cmb/Nkk.py:31 over bolometers)."""
+    ctx = _ffi.context(device, lane)
+    upload_cls(ctx, lensCl_interps, nolensCl_interps)
+    ell, w_ell, pphi, w_phi, cphi, sphi = _default_grids()
+    Ld = _ffi.f64(Ls)
+    dts = _ffi.f64(np.atleast_1d(DeltaTs))
+    its = np.zeros(dts.size, dtype=np.int32) if iteratives is None else np.ascontiguousarray(np.atleast_1d(iteratives), dtype=np.int32)
+    if its.size != dts.size:
+        raise ValueError('DeltaTs and iteratives differ in length')
+    if Tcmb is None:
+        Tcmb = get_params()['Tcmb']
+    _ffi.check(_ffi.lib().lbg_n0_ho02_levels_begin(ctx.handle, Ld.size, _ffi._dp(Ld), float(thetab), dts.size, _ffi._dp(dts),
+                                                   its.ctypes.data_as(_ffi.c_int_p), float(Tcmb), ell.size, _ffi._dp(ell), _ffi._dp(w_ell),
+                                                   pphi.size, _ffi._dp(cphi), _ffi._dp(sphi), _ffi._dp(w_phi),
+                                                   float(lmax_T), float(lmax_P), float(lmin_v)))
+    return N0LevelsCall(ctx, dts.size, Ld.size, (Ld, dts, its))
+
+
+def n0_levels(*args, **kw):
+    """(N0[n_lev, n_L], {term: integral[n_lev, n_L]}) -- arguments of n0_levels_begin."""
+    return n0_levels_begin(*args, **kw).result()
+
+
 def n0_terms(*args, **kw):
     """(N0[len(Ls)], {term: integral[len(Ls)]}) -- the combined noise plus the per-estimator integrals (arguments of n0_begin)."""
     return n0_begin(*args, **kw).result()

@@ -117,6 +117,11 @@ def _declare(L):
         'lbg_n0_ho02_begin': [vp, i, c_double_p, u, d, d, d, i, i, c_double_p, c_double_p, i, c_double_p, c_double_p,
                               c_double_p, d, d, d, i, i, c_int_p, c_double_p],
         'lbg_n0_ho02_end': [vp, i, c_double_p, c_double_p, c_ll_p, c_ll_p],
+        'lbg_n0_ho02_levels': [vp, i, c_double_p, d, i, c_double_p, c_int_p, d, i, c_double_p, c_double_p, i, c_double_p, c_double_p,
+                               c_double_p, d, d, d, c_double_p, c_double_p],
+        'lbg_n0_ho02_levels_begin': [vp, i, c_double_p, d, i, c_double_p, c_int_p, d, i, c_double_p, c_double_p, i, c_double_p, c_double_p,
+                                     c_double_p, d, d, d],
+        'lbg_n0_ho02_levels_end': [vp, i, i, c_double_p, c_double_p],
         'lbg_n0_set_exact_below': [vp, d],
         'lbg_n0_last_path': [vp, c_int_p],
         'lbg_scipy_cubic_eval_host': [i, c_double_p, i, c_double_p, c_double_p],

@@ -108,8 +108,8 @@ struct lbg_ctx {
     lbg::PinBuf  pin_n0, pin_n0_out;
     lbg_n0_plan* n0_plan = nullptr;
     bool         n0_pending = false; // lbg_n0_ho02_begin issued, lbg_n0_ho02_end not yet
-    int          n0_n_L = 0;
-    int          n0_path = 0;        // integrand kernel of the last call: 5 = range-walking (rows5), 3 = generic per-node masks (rows3)
+    int          n0_n_L = 0, n0_n_lev = 0;
+    int          n0_path = 0;        // integrand kernel of the last call: 5 = range-walking (rows5), 3 = generic per-node masks (rows3), 6 = multi-level (rows5m)
     long long    n0_nodes_walked = 0;
     double       n0_exact_below = 2.0;   // l1 rows below this get their u-side splines from the scipy-order host routine
     std::vector<double> n0_exact_vals;

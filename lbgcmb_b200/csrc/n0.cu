@@ -250,6 +250,9 @@ __global__ void n0_poly_table_kernel(N0Params P, ChebFit F, int fold_noise, cons
         a[k].z = (c0 - 2.0 * c1 + c2) * 0.5;
         a[k].w = ((c3 - c0) + 3.0 * (c1 - c2)) * (1.0 / 6.0);
     }
+    // fold_noise: 0 = no noise in the table (the generic kernel calls exp() per node), 1 = noise folded into the three C^tot slots,
+    // 2 = C^tot slots hold the lensed splines alone and slot 8 holds the noise SHAPE exp(a l (l + 1)) (multi-level kernel:
+    // C^tot = S + n_level G, so every level of one beam shares these loads)
     double n[4] = {0.0, 0.0, 0.0, 0.0};
     if (fold_noise) {
         const double fi = (double)i;
@@ -267,9 +270,11 @@ __global__ void n0_poly_table_kernel(N0Params P, ChebFit F, int fold_noise, cons
     double* o = reinterpret_cast<double*>(out) + i;
 #define LBG_PUT(slot, v) o[(4 * (slot)) * LBG_PAIR_STRIDE] = (v).x; o[(4 * (slot) + 1) * LBG_PAIR_STRIDE] = (v).y; \
                          o[(4 * (slot) + 2) * LBG_PAIR_STRIDE] = (v).z; o[(4 * (slot) + 3) * LBG_PAIR_STRIDE] = (v).w
-    const double4 e2 = make_double4(fma(P.nP, n[0], a[6].x), fma(P.nP, n[1], a[6].y), fma(P.nP, n[2], a[6].z), fma(P.nP, n[3], a[6].w));
-    const double4 b2 = make_double4(fma(P.nP, n[0], a[7].x), fma(P.nP, n[1], a[7].y), fma(P.nP, n[2], a[7].z), fma(P.nP, n[3], a[7].w));
-    const double4 t2 = make_double4(fma(P.nT, n[0], a[4].x), fma(P.nT, n[1], a[4].y), fma(P.nT, n[2], a[4].z), fma(P.nT, n[3], a[4].w));
+    const double nPf = fold_noise == 2 ? 0.0 : P.nP, nTf = fold_noise == 2 ? 0.0 : P.nT;
+    const double4 e2 = make_double4(fma(nPf, n[0], a[6].x), fma(nPf, n[1], a[6].y), fma(nPf, n[2], a[6].z), fma(nPf, n[3], a[6].w));
+    const double4 b2 = make_double4(fma(nPf, n[0], a[7].x), fma(nPf, n[1], a[7].y), fma(nPf, n[2], a[7].z), fma(nPf, n[3], a[7].w));
+    const double4 t2 = make_double4(fma(nTf, n[0], a[4].x), fma(nTf, n[1], a[4].y), fma(nTf, n[2], a[4].z), fma(nTf, n[3], a[4].w));
+    if (fold_noise == 2) { const double4 g4 = make_double4(n[0], n[1], n[2], n[3]); LBG_PUT(8, g4); }
     LBG_PUT(0, e2); LBG_PUT(1, b2); LBG_PUT(2, a[2]); LBG_PUT(3, a[3]);
     LBG_PUT(4, t2); LBG_PUT(5, a[5]); LBG_PUT(6, a[0]); LBG_PUT(7, a[1]);
 #undef LBG_PUT
@@ -628,6 +633,173 @@ n0_rows5_kernel(N0Params P, const double* __restrict__ Ls, const URow* __restric
     store_partials(P, red, iL, rb, rc.wl, aTT, aTE, aEE, aEB, aBB, cnt, partial);
 }
 
+
+// ---- several noise levels of ONE beam per node (survey-design sweeps: BASELINE configs[4], snr.py:108-124 loops Nkk over experiments) ------
+// For levels that share the beam, C^tot_X(l) = S_X(l) + n_X^level G(l) with S the lensed spline and G(l) = exp(a l (l + 1)) the noise
+// shape: the table holds S_TT, S_EE, S_BB and G once (n0_poly_table_kernel, fold_noise = 2) and a node serves NLEV levels with 8 slot
+// reads (32 loads) + 3 FMAs per level instead of 7 slot reads per level -- the single-level kernel is bound by exactly those loads (L1
+// data pipe 79 % against FP64 53 %, profiles/r2a_n0_rows5_ncu_full_summary.txt).  Geometry, masks (they do not depend on the noise), the
+// four unlensed spectra and every level-independent product (L.u, L.v, cos 2phi, the f_alpha) are computed once per node.
+// A level's arithmetic does not depend on NLEV or on its position in the group: its result is the same in any grouping.  It differs
+// from n0_rows5_kernel's in the last bits only (noise added after the Horner sums instead of inside the coefficients).
+struct LevelNoise { double nT, nP; };
+#define LBG_MAX_NLEV 3
+struct LevelParams { LevelNoise lv[LBG_MAX_NLEV]; };
+
+template <int NLEV>
+struct LevU { double T1[NLEV], E1[NLEV], rT1h[NLEV], rE1h[NLEV], rE1[NLEV]; };
+
+template <int NLEV, bool DO_T, bool HAS_UB>
+__device__ __forceinline__ void n0_node5m(const double4* __restrict__ ptab, const RowGeom& g, const UVals& u, const LevU<NLEV>& lu,
+                                          const LevelParams& LP, bool okT, bool okP, const double2 cw, const NodePre pre,
+                                          double (&aTT)[NLEV], double (&aTE)[NLEV], double (&aEE)[NLEV], double (&aEB)[NLEV]) {
+    const double y = pre.y, t = pre.t;
+    const double* row = reinterpret_cast<const double*>(ptab) + pre.i;
+    const double dLu = g.lL * cw.x, dLv = g.L2 - dLu;
+    const double dot = dLu - g.l2;
+    const double c2 = fma((dot * dot) * (y * y), g.rl2x2, -1.0);
+    const double s2sq = fma(-c2, c2, 1.0);
+    const double SE = horner3<0>(row, t), vE = horner3<2>(row, t), SB = horner3<1>(row, t), G = horner3<8>(row, t);
+    const double vB = HAS_UB ? horner3<3>(row, t) : 0.0;
+    const double uEd = u.uE * dLu;
+    const double fe = fma(vE, dLv, uEd) * c2;
+    const double fe2 = fe * fe;
+    const double fb = HAS_UB ? fma(-vB, dLv, uEd) : uEd;
+    const double fb2s = (fb * fb) * s2sq;
+    double ST = 0.0, X2 = 0.0, fa2 = 0.0, fa_uv = 0.0, fa_vu = 0.0, xx = 0.0;
+    if (DO_T) {
+        ST = horner3<4>(row, t); X2 = horner3<5>(row, t);
+        const double vT = horner3<6>(row, t), vX = horner3<7>(row, t);
+        xx = u.X1 * X2;
+        const double fa = fma(vT, dLv, u.uT * dLu);
+        fa2 = fa * fa;
+        const double uXd = u.uX * dLu, vXd = vX * dLv;
+        fa_uv = fma(uXd, c2, vXd); fa_vu = fma(vXd, c2, uXd);
+    }
+    const double wT = okT ? cw.y : 0.0, wP = okP ? cw.y : 0.0;     // a masked node adds +0 (its terms may be NaN: select BEFORE the product)
+#pragma unroll
+    for (int v = 0; v < NLEV; ++v) {
+        const double E2 = fma(LP.lv[v].nP, G, SE), B2 = fma(LP.lv[v].nP, G, SB);
+        const double p2 = E2 * B2;
+        double rE2, rB2;
+        if (DO_T) {
+            const double T2 = fma(LP.lv[v].nT, G, ST);
+            const double E1T2 = lu.E1[v] * T2;
+            const double den = fma(lu.T1[v] * E2, E1T2, -(xx * xx));
+            const double p1 = T2 * den;
+            const double r = rcp_fast(p1 * p2);
+            const double r34 = r * p1, r12 = r * p2;
+            rE2 = r34 * B2; rB2 = r34 * E2;
+            const double rT2 = r12 * den, rdn = r12 * T2;
+            const double tt = fa2 * (lu.rT1h[v] * rT2);
+            const double num = fma(E1T2, fa_uv, -(xx * fa_vu));
+            const double te = (fa_uv * num) * rdn;
+            aTT[v] = fma(wT, okT ? tt : 0.0, aTT[v]);
+            aTE[v] = fma(wT, okT ? te : 0.0, aTE[v]);
+        } else {
+            const double r = rcp_fast(p2);
+            rE2 = r * B2; rB2 = r * E2;
+        }
+        const double ee = fe2 * (lu.rE1h[v] * rE2);
+        const double eb = fb2s * (lu.rE1[v] * rB2);
+        aEE[v] = fma(wP, okP ? ee : 0.0, aEE[v]);
+        aEB[v] = fma(wP, okP ? eb : 0.0, aEB[v]);
+    }
+}
+
+template <int NLEV, bool HAS_UB>
+__global__ void __launch_bounds__(128, 3)
+n0_rows5m_kernel(N0Params P, LevelParams LP, const double* __restrict__ Ls, const URow* __restrict__ utab /*[NLEV][n_l1]*/,
+                 const double4* __restrict__ ptab, const double* __restrict__ soa, const double* __restrict__ phi /*[6][n_phi]*/,
+                 double* __restrict__ partial /*[NLEV][6][n_L][n_rb]*/) {
+    __shared__ double red[6][4];
+    const int iL = blockIdx.x / P.n_rb, rb = blockIdx.x - iL * P.n_rb;
+    const int r = rb * 128 + threadIdx.x;
+    const double L = Ls[iL];
+    const RowCtx rc = load_row(P, utab, r);                      // level 0's row: everything level-independent comes from it
+    const int fl = rc.fl;
+    const double l = rc.l;
+    const UVals& u = rc.u;
+    LevU<NLEV> lu;
+#pragma unroll
+    for (int v = 0; v < NLEV; ++v) {
+        lu.T1[v] = lu.E1[v] = 1.0; lu.rT1h[v] = lu.rE1h[v] = lu.rE1[v] = 0.0;
+        if (r < P.n_l1) {
+            const URow* ur = utab + (size_t)v * P.n_l1 + r;
+            lu.T1[v] = ur->T1; lu.E1[v] = ur->E1; lu.rT1h[v] = ur->rT1h; lu.rE1h[v] = ur->rE1h; lu.rE1[v] = ur->rE1;
+        }
+    }
+    const bool act = (fl & 5) && !(fl & 16);
+    const bool actT = act && (fl & 1), actP = act && (fl & 4);
+    RowGeom g;
+    g.L2 = L * L; g.l2 = l * l; g.rl2x2 = 2.0 / g.l2; g.lL = l * L; g.m2lL = -2.0 * g.lL; g.l2pL2 = g.l2 + g.L2;
+    const int n = P.n_phi;
+    const double2* cw = c_cw[P.lane];
+    int j0s = n, j0e = n, jT = 0, jTe = 0, jP = 0, jPe = 0;
+    if (act) {
+        j0s = first_j_hi_ge(g, cw, n, P.near_lo[0]);
+        j0e = first_j_hi_ge(g, cw, n, P.near_lo[0] + P.near_span[0] + 1u);
+        jT = first_j_hi_ge(g, cw, n, P.near_lo[1]);
+        jTe = first_j_hi_ge(g, cw, n, P.near_lo[1] + P.near_span[1] + 1u);
+        jP = first_j_hi_ge(g, cw, n, P.near_lo[2]);
+        jPe = first_j_hi_ge(g, cw, n, P.near_lo[2] + P.near_span[2] + 1u);
+    }
+    const bool any_rare = act && (j0e > j0s || jTe > jT || jPe > jP);
+    const int endT = actT ? jT : 0, endP = actP ? jP : 0;
+    const int w0 = __reduce_min_sync(0xffffffffu, j0e);
+    const int wT = __reduce_max_sync(0xffffffffu, endT), wP = __reduce_max_sync(0xffffffffu, endP);
+    double aTT[NLEV], aTE[NLEV], aEE[NLEV], aEB[NLEV], aBB[NLEV];
+#pragma unroll
+    for (int v = 0; v < NLEV; ++v) aTT[v] = aTE[v] = aEE[v] = aEB[v] = aBB[v] = 0.0;
+    int cnt_i = max(endP - j0e, 0) - max(min(jTe, endP) - max(jT, j0e), 0);
+    if (cnt_i < 0) cnt_i = 0;
+#define LBG_OKT(j) ((j) >= j0e && (j) < endT)
+#define LBG_OKP(j) ((j) >= j0e && (j) < endP && !((j) >= jT && (j) < jTe))
+    int j = w0;
+    NodePre p0 = n0_prep5(P, g, cw[j].x);
+    for (; j < wT; ++j) {                                        // one node per trip: the NLEV levels are the independent work
+        const NodePre nx = n0_prep5(P, g, cw[j + 1].x);
+        n0_node5m<NLEV, true, HAS_UB>(ptab, g, u, lu, LP, LBG_OKT(j), LBG_OKP(j), cw[j], p0, aTT, aTE, aEE, aEB);
+        p0 = nx;
+    }
+    for (; j < wP; ++j) {
+        const NodePre nx = n0_prep5(P, g, cw[j + 1].x);
+        n0_node5m<NLEV, false, HAS_UB>(ptab, g, u, lu, LP, false, LBG_OKP(j), cw[j], p0, aTT, aTE, aEE, aEB);
+        p0 = nx;
+    }
+#undef LBG_OKT
+#undef LBG_OKP
+    double cnt = (double)cnt_i;
+    if (any_rare) {                                              // bit-faithful second pass over the window nodes, level by level
+        const bool fold = P.fold != 0;
+        for (int k = 0; k < 3; ++k) {
+            const int a = k == 0 ? j0s : (k == 1 ? jT : jP), b = k == 0 ? j0e : (k == 1 ? jTe : jPe);
+            for (int jj = a; jj < b; ++jj) {
+                if (k == 2 && jj >= jT && jj < jTe) continue;
+                if (k == 1 && jj >= j0s && jj < j0e) continue;
+                if (k == 2 && jj >= j0s && jj < j0e) continue;
+#pragma unroll
+                for (int v = 0; v < NLEV; ++v) {
+                    N0Params Pv = P;
+                    Pv.nT = LP.lv[v].nT; Pv.nP = LP.lv[v].nP;
+                    UVals uv = u;
+                    uv.T1 = lu.T1[v]; uv.E1 = lu.E1[v]; uv.rT1h = lu.rT1h[v]; uv.rE1h = lu.rE1h[v]; uv.rE1 = lu.rE1[v];
+                    const bool hit = n0_node<true>(Pv, reinterpret_cast<const ClRow*>(soa), L, l, __ldg(phi + jj), __ldg(phi + n + jj), uv, fl & 1, fl & 4,
+                                                   cw[jj].y, fold, __ldg(phi + 3 * n + jj), __ldg(phi + 4 * n + jj), __ldg(phi + 5 * n + jj),
+                                                   aTT[v], aTE[v], aEE[v], aEB[v], aBB[v]);
+                    if (v == 0) cnt += hit ? 1.0 : 0.0;
+                }
+            }
+        }
+    }
+    const size_t lev_stride = (size_t)6 * P.n_L * P.n_rb;
+#pragma unroll
+    for (int v = 0; v < NLEV; ++v) {
+        if (v) __syncthreads();                                   // `red` is reused
+        store_partials(P, red, iL, rb, rc.wl, aTT[v], aTE[v], aEE[v], aEB[v], aBB[v], cnt, partial + v * lev_stride);
+    }
+}
+
 // Special rows, always on the full (unfolded) phi grid:
 //  * rows sitting on the lmax_T / lmax_P cuts, where the reference's mask `|u| > lmax` (cmb/Nkk.py:17,20) depends on the
 //    rounding of |u| = sqrt((l cos)^2 + (l sin)^2) at each phi node; rows on the last knot of a table that ends in range likewise;
@@ -783,7 +955,9 @@ static int n0_begin_locked(lbg_ctx* c, int n_L, const double* L, unsigned terms_
                            int n_l1, const double* l1, const double* w_l1,
                            int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
                            double lmax_T, double lmax_P, double lmin_v, int fold_phi,
-                           int n_exact, const int* exact_rows, const double* exact_u, double exact_below) {
+                           int n_exact, const int* exact_rows, const double* exact_u, double exact_below,
+                           int n_lev = 0, const double* deltaT_lev = nullptr, const int* iterative_lev = nullptr) {
+    // n_lev > 0: several noise levels of this beam in one pass (lbg_n0_ho02_levels); deltaT_uK_arcmin / iterative are then ignored
     LBG_REQUIRE(c && L && l1 && w_l1 && cos_phi && sin_phi && w_phi, "lbg_n0_ho02: NULL argument");
     if (c->n_ell <= 0) { set_error("lbg_n0_ho02: call lbg_upload_cl_tables first"); return LBG_ESTATE; }
     if (c->n0_pending) { set_error("lbg_n0_ho02: a call begun with lbg_n0_ho02_begin is still pending on this context"); return LBG_ESTATE; }
@@ -796,6 +970,8 @@ static int n0_begin_locked(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     LBG_REQUIRE(fold_phi >= 0 && fold_phi <= 2, "lbg_n0_ho02: fold_phi must be 0 (full grid), 1 (mirror pairs) or 2 (mirror pairs, generic kernel)");
     LBG_REQUIRE(c->lane >= 0 && c->lane < LBG_MAX_LANES, "lbg_n0_ho02: context lane %d has no phi-table block (lanes 0..%d)", c->lane, LBG_MAX_LANES - 1);
     c->n0_n_L = n_L;
+    c->n0_n_lev = n_lev;
+    if (n_lev > 0) deltaT_uK_arcmin = deltaT_lev[0];
     if (n_L == 0) { c->n0_pending = true; return LBG_OK; }
     LBG_CUDA(cudaSetDevice(c->device));
     if (!c->n0_plan) c->n0_plan = new lbg_n0_plan();
@@ -1005,10 +1181,11 @@ static int n0_begin_locked(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     // ---- per-call staging block: [L | u values of the special rows] in pinned memory, one copy -----------------------------------
     const size_t su_count = (size_t)n_special * n_phi * 8;
     const size_t part_main = (size_t)6 * n_L * P.n_rb, part_special = (size_t)6 * npairs_full;
+    const size_t nlv = (size_t)std::max(1, n_lev);
     if (c->n0_L.reserve((size_t)n_L * 8 + su_count * 8 + 64) || c->pin_n0.reserve((size_t)n_L * 8 + su_count * 8 + 64) ||
-        c->n0_utab.reserve((size_t)n_l1 * sizeof(URow)) || c->n0_partial.reserve((part_main + part_special) * 8) ||
-        c->n0_out.reserve((size_t)7 * n_L * 8) || c->pin_n0_out.reserve((size_t)7 * n_L * 8) ||
-        c->cl_poly.reserve((size_t)LBG_PAIR_STRIDE * 8 * 32))
+        c->n0_utab.reserve(nlv * n_l1 * sizeof(URow)) || c->n0_partial.reserve(nlv * (part_main + part_special) * 8) ||
+        c->n0_out.reserve(nlv * 7 * n_L * 8) || c->pin_n0_out.reserve(nlv * 7 * n_L * 8) ||
+        c->cl_poly.reserve((size_t)LBG_PAIR_STRIDE * 8 * 36))
         return LBG_ENOMEM;
     double* hL = c->pin_n0.as<double>();
     memcpy(hL, L, (size_t)n_L * 8);
@@ -1041,6 +1218,70 @@ static int n0_begin_locked(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     LBG_CUDA(cudaMemcpyAsync(d_L, hL, ((size_t)n_L + (size_t)n_given * n_phi * 8) * 8, cudaMemcpyHostToDevice, st));
     double* d_part = c->n0_partial.as<double>();
     double* d_spart = d_part + part_main;
+
+    if (n_lev > 0) {
+        // ---- several noise levels of one beam: per-level u rows / special rows / reductions, the integrand in groups of <= 3 levels ----
+        LBG_REQUIRE(rows5 && terms_mask == (LBG_TT | LBG_TE | LBG_EE | LBG_EB),
+                    "lbg_n0_ho02_levels: needs the four estimators TT,TE,EE,EB, a folded phi grid with decreasing cos, tables that cover every "
+                    "reachable |v| and a beam inside the folded-noise bound (use lbg_n0_ho02 per level otherwise)");
+        c->n0_path = 6;
+        c->last_launches = 0;
+        cudaEventRecord(c->ev0, st);
+        if (n_special > n_given) {
+            int cnt = (n_special - n_given) * n_phi;
+            n0_special_u_kernel<<<(cnt + 127) / 128, 128, 0, st>>>(c->n_ell, cnt, d_snu + (size_t)n_given * n_phi,
+                                                                   c->cl_rows.as<ClRow>(), d_su + (size_t)n_given * n_phi * 8);
+            ++c->last_launches;
+        }
+        n0_poly_table_kernel<<<(P.n_int + 127) / 128, 128, 0, st>>>(P, fit, 2, c->cl_soa.as<double>(), c->cl_poly.as<double4>());
+        ++c->last_launches;
+        std::vector<N0Params> PL(n_lev, P);
+        for (int v = 0; v < n_lev; ++v) {
+            double dTv = deltaT_lev[v] * pow(10., -6.);
+            dTv *= arcmin2rad;
+            const double dPv = sqrt(2.) * dTv;
+            PL[v].nT = (dTv / Tcmb_K) * (dTv / Tcmb_K);
+            PL[v].nP = (dPv / Tcmb_K) * (dPv / Tcmb_K);
+            PL[v].ebfac = (iterative_lev && iterative_lev[v]) ? 2.5 : 1.0;
+            n0_uside_kernel<<<(n_l1 + 127) / 128, 128, 0, st>>>(PL[v], d_l1, d_wl1, d_rowflag, c->cl_rows.as<ClRow>(),
+                                                                 c->n0_utab.as<URow>() + (size_t)v * n_l1);
+            ++c->last_launches;
+        }
+        cudaEventRecord(c->ev2, st);
+        const unsigned grid = (unsigned)((long long)n_L * P.n_rb);
+        for (int v0 = 0; v0 < n_lev; v0 += LBG_MAX_NLEV) {
+            const int nl = std::min(LBG_MAX_NLEV, n_lev - v0);
+            LevelParams LP;
+            for (int q = 0; q < LBG_MAX_NLEV; ++q) { const N0Params& S = PL[v0 + std::min(q, nl - 1)]; LP.lv[q].nT = S.nT; LP.lv[q].nP = S.nP; }
+            const URow* ut = c->n0_utab.as<URow>() + (size_t)v0 * n_l1;
+            double* part = d_part + (size_t)v0 * part_main;
+#define LBG_R5M(NL, UB) n0_rows5m_kernel<NL, UB><<<grid, 128, 0, st>>>(P, LP, d_L, ut, c->cl_poly.as<double4>(), c->cl_soa.as<double>(), d_ph, part)
+            if (c->ub_zero) { if (nl == 3) LBG_R5M(3, false); else if (nl == 2) LBG_R5M(2, false); else LBG_R5M(1, false); }
+            else            { if (nl == 3) LBG_R5M(3, true);  else if (nl == 2) LBG_R5M(2, true);  else LBG_R5M(1, true); }
+#undef LBG_R5M
+            ++c->last_launches;
+        }
+        cudaEventRecord(c->ev3, st);
+        double* d_spart_all = d_part + (size_t)n_lev * part_main;
+        for (int v = 0; v < n_lev; ++v) {
+            double* sp = d_spart_all + (size_t)v * part_special;
+            if (n_special) {
+                n0_special_kernel<<<(int)((npairs_full + 127) / 128), 128, 0, st>>>(PL[v], n_special, n_phi, d_srow, d_L, d_phf,
+                                                                                    c->n0_utab.as<URow>() + (size_t)v * n_l1, d_su, d_snu,
+                                                                                    c->cl_rows.as<ClRow>(), sp);
+                ++c->last_launches;
+            }
+            n0_rows_reduce_kernel<<<n_L, 128, 0, st>>>(PL[v], d_L, d_part + (size_t)v * part_main, n_special ? sp : nullptr, n_phi,
+                                                       c->n0_out.as<double>() + (size_t)v * 7 * n_L);
+            ++c->last_launches;
+        }
+        cudaEventRecord(c->ev1, st);
+        LBG_CUDA(cudaMemcpyAsync(c->pin_n0_out.p, c->n0_out.p, (size_t)n_lev * 7 * n_L * 8, cudaMemcpyDeviceToHost, st));
+        LBG_CUDA(cudaGetLastError());
+        c->n0_nodes_walked = npairs * (pl.active_rows - n_special) + npairs_full * n_special;
+        c->n0_pending = true;
+        return LBG_OK;
+    }
 
     c->last_launches = 0;
     cudaEventRecord(c->ev0, st);
@@ -1086,13 +1327,14 @@ static int n0_begin_locked(lbg_ctx* c, int n_L, const double* L, unsigned terms_
     return LBG_OK;
 }
 
-static int n0_end_locked(lbg_ctx* c, int n_L, double* out_nkk, double* out_terms, long long* nodes_executed, long long* nodes_unmasked) {
+static int n0_end_locked(lbg_ctx* c, int n_L, double* out_nkk, double* out_terms, long long* nodes_executed, long long* nodes_unmasked,
+                         int n_lev = 0) {
     if (!c->n0_pending) { set_error("lbg_n0_ho02_end: no pending call on this context"); return LBG_ESTATE; }
     c->n0_pending = false;
-    if (n_L != c->n0_n_L) {                         // the pending call is dropped; wait for it so that its buffers can be reused
+    if (n_L != c->n0_n_L || n_lev != c->n0_n_lev) {   // the pending call is dropped; wait for it so that its buffers can be reused
         cudaSetDevice(c->device);
         cudaStreamSynchronize(c->stream);
-        set_error("lbg_n0_ho02_end: n_L=%d but the pending call has %d multipoles (call dropped)", n_L, c->n0_n_L);
+        set_error("lbg_n0_ho02_end: n_L=%d, n_lev=%d but the pending call has %d multipoles, %d levels (call dropped)", n_L, n_lev, c->n0_n_L, c->n0_n_lev);
         return LBG_EINVAL;
     }
     if (n_L == 0) { if (nodes_executed) *nodes_executed = 0; if (nodes_unmasked) *nodes_unmasked = 0; return LBG_OK; }
@@ -1105,8 +1347,11 @@ static int n0_end_locked(lbg_ctx* c, int n_L, double* out_nkk, double* out_terms
     if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) { c->last_ms = ms; c->total_ms += ms; c->total_launches += c->last_launches; }
     c->last_main_ms = cudaEventElapsedTime(&ms, c->ev2, c->ev3) == cudaSuccess ? ms : c->last_ms;
     const double* host = c->pin_n0_out.as<double>();
-    memcpy(out_nkk, host, (size_t)n_L * 8);
-    if (out_terms) memcpy(out_terms, host + n_L, (size_t)5 * n_L * 8);
+    for (int v = 0; v < std::max(1, n_lev); ++v) {      // per level: [N0 | 5 estimator integrals | unmasked count], each n_L long
+        const double* hv = host + (size_t)v * 7 * n_L;
+        memcpy(out_nkk + (size_t)v * n_L, hv, (size_t)n_L * 8);
+        if (out_terms) memcpy(out_terms + (size_t)v * 5 * n_L, hv + n_L, (size_t)5 * n_L * 8);
+    }
     if (nodes_executed) *nodes_executed = c->n0_nodes_walked;
     if (nodes_unmasked) {
         double s = 0.0;
@@ -1163,3 +1408,39 @@ extern "C" int lbg_n0_last_path(lbg_ctx* c, int* path) {
 }
 
 void lbg_n0_release(lbg_ctx* c) { n0_plan_free(c); }
+
+// ---- several noise levels of one beam in one pass (BASELINE configs[4]: beam x noise sweeps; snr.py:108-124 loops Nkk over experiments) ----
+static int check_levels(int n_lev, const double* deltaT, const char* who) {
+    LBG_REQUIRE(n_lev >= 1 && n_lev <= 4096 && deltaT, "%s: need 1 <= n_lev <= 4096 and the noise levels", who);
+    for (int v = 0; v < n_lev; ++v) LBG_REQUIRE(deltaT[v] >= 0.0 && deltaT[v] == deltaT[v], "%s: deltaT[%d] is negative or NaN", who, v);
+    return LBG_OK;
+}
+
+extern "C" int lbg_n0_ho02_levels_begin(lbg_ctx* c, int n_L, const double* L, double thetab_arcmin, int n_lev, const double* deltaT_uK_arcmin,
+                                        const int* iterative, double Tcmb_K,
+                                        int n_l1, const double* l1, const double* w_l1,
+                                        int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
+                                        double lmax_T, double lmax_P, double lmin_v) {
+    LBG_REQUIRE(c, "lbg_n0_ho02_levels_begin: ctx is NULL");
+    if (int rc = check_levels(n_lev, deltaT_uK_arcmin, "lbg_n0_ho02_levels")) return rc;
+    std::lock_guard<std::mutex> g(c->mu);
+    return n0_begin_locked(c, n_L, L, LBG_TT | LBG_TE | LBG_EE | LBG_EB, thetab_arcmin, 0.0, Tcmb_K, 0, n_l1, l1, w_l1, n_phi, cos_phi, sin_phi,
+                           w_phi, lmax_T, lmax_P, lmin_v, 1, 0, nullptr, nullptr, c->n0_exact_below, n_lev, deltaT_uK_arcmin, iterative);
+}
+
+extern "C" int lbg_n0_ho02_levels_end(lbg_ctx* c, int n_lev, int n_L, double* out_nkk, double* out_terms) {
+    LBG_REQUIRE(c && n_lev >= 1, "lbg_n0_ho02_levels_end: bad argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    return n0_end_locked(c, n_L, out_nkk, out_terms, nullptr, nullptr, n_lev);
+}
+
+extern "C" int lbg_n0_ho02_levels(lbg_ctx* c, int n_L, const double* L, double thetab_arcmin, int n_lev, const double* deltaT_uK_arcmin,
+                                  const int* iterative, double Tcmb_K,
+                                  int n_l1, const double* l1, const double* w_l1,
+                                  int n_phi, const double* cos_phi, const double* sin_phi, const double* w_phi,
+                                  double lmax_T, double lmax_P, double lmin_v, double* out_nkk, double* out_terms) {
+    int rc = lbg_n0_ho02_levels_begin(c, n_L, L, thetab_arcmin, n_lev, deltaT_uK_arcmin, iterative, Tcmb_K, n_l1, l1, w_l1, n_phi, cos_phi, sin_phi,
+                                      w_phi, lmax_T, lmax_P, lmin_v);
+    if (rc) return rc;
+    return lbg_n0_ho02_levels_end(c, n_lev, n_L, out_nkk, out_terms);
+}

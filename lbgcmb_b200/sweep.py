@@ -163,19 +163,44 @@ def survey_sweep(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes, noi
         grid_fn = forecast_grid
     lo, hi = _dist.shard_slice(len(noise_configs))
     mine = list(noise_configs[lo:hi])
-    call = None
-    if n0_async and mine:                        # this rank's first N0 curve runs on the second context while the spectra are built
-        from lbgcmb_b200.Nkk import n0_terms_async
-        call = n0_terms_async(lensCl_interps, nolensCl_interps, Llls, terms, mine[0][0], mine[0][1], mine[0][2])
+    groups = []
+    if n0_async and mine:
+        # this rank's noise levels grouped by beam: levels of one beam share every table read of the N0 integrand
+        # (Nkk.n0_levels, csrc/n0.cu n0_rows5m_kernel); one call per beam, on the second context while the spectra are built
+        from lbgcmb_b200.Nkk import n0_levels_begin
+        by_beam = {}
+        for i, cfg in enumerate(mine):
+            by_beam.setdefault(float(cfg[0]), []).append(i)
+        groups = list(by_beam.items())
+
+        class _PerLevel(object):            # a beam the multi-level kernel cannot serve (beyond its folded-noise bound): level by level
+            def __init__(self, beam, idx):
+                self.beam, self.idx = beam, idx
+
+            def result(self):
+                from lbgcmb_b200.Nkk import n0_terms
+                return (np.array([n0_terms(lensCl_interps, nolensCl_interps, Llls, terms, self.beam, mine[i][1], mine[i][2], lane=1)[0]
+                                  for i in self.idx]),)
+
+        def start(gi):
+            beam, idx = groups[gi]
+            try:
+                return n0_levels_begin(lensCl_interps, nolensCl_interps, Llls, beam, [mine[i][1] for i in idx],
+                                       [int(bool(mine[i][2])) for i in idx], lane=1)
+            except ValueError:
+                return _PerLevel(beam, idx)
+        if tuple(terms) != ('TT', 'TE', 'EE', 'EB'):
+            raise ValueError('survey_sweep evaluates the four estimators TT, TE, EE, EB')
+        call = start(0)
     ckk, cgg, ckg, ngg = spectra_fn(samples)
     xc = spectra_fn(xsamples)[1:] if xsamples is not None else (None, None, None)
     if n0_async:
-        rows = []
-        for i in range(len(mine)):               # one call in flight per context: collect curve i, start curve i + 1
-            rows.append(call.result()[0])
-            if i + 1 < len(mine):
-                call = n0_terms_async(lensCl_interps, nolensCl_interps, Llls, terms, mine[i + 1][0], mine[i + 1][1], mine[i + 1][2])
-        nkk = np.array(rows).reshape(hi - lo, Ld.size)
+        nkk = np.empty((hi - lo, Ld.size))
+        for gi in range(len(groups)):              # one call in flight per context: collect group gi, start group gi + 1
+            res = call.result()[0]
+            nkk[groups[gi][1]] = res
+            if gi + 1 < len(groups):
+                call = start(gi + 1)
     else:
         nkk = np.array([n0_fn(cfg) for cfg in mine]).reshape(hi - lo, Ld.size)
     if hi > lo:
