@@ -4,7 +4,8 @@
   python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 scripts/sweep_bench.py ...
 
 64 n(z) configurations = 4 bands x 4 widths {0.15, 0.24, 0.35, 0.5} x 4 nbar scalings {0.25, 0.5, 1, 2}.
-Noise levels: the first --n-noise of the 7 x 30 (beam, DeltaT) grid in a fixed seed-0 permutation, iterative-EB for DeltaT <= 3.
+Noise levels: the first --n-noise of the 7 x 30 (beam, DeltaT) grid in a fixed seed-0 permutation (--full: all 210, beam-major), iterative-EB
+for DeltaT <= 3.  Levels of one beam go through the multi-level N0 kernel (Nkk.n0_levels).
 Prints one JSON line on rank 0 (wall-clock of the whole sweep, max over ranks through the final gather)."""
 import argparse
 import json
@@ -21,6 +22,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--n-noise', type=int, default=16)
     ap.add_argument('--grid', default='B', choices=['A', 'B'])
+    ap.add_argument('--full', action='store_true', help='the stated size of configs[4]: all 7 x 30 = 210 (beam, noise) levels, beam-major')
     a = ap.parse_args()
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (('RANK', '0'), ('WORLD_SIZE', '1'), ('LOCAL_RANK', '0')))
     import torch
@@ -48,25 +50,27 @@ def main():
                 xsamples.append({'pz': pzz, 'bz': linz_bz, 'nbar': 1.06 * f * nbar})
     noise = [(tb, dT, dT <= 3.0) for tb in range(1, 8) for dT in range(1, 31)]
     perm = np.random.default_rng(0).permutation(len(noise))
-    noise = [noise[i] for i in perm[:a.n_noise]]
-    ctx = _ffi.context(local)
+    noise = sorted(noise) if a.full else [noise[i] for i in perm[:a.n_noise]]      # beam-major: a rank's block holds whole beams
+    ctx, ctx1 = _ffi.context(local), _ffi.context(local, 1)
     sweep.survey_sweep(li, ni, Pk, Ls[:8], nmodes[:8], noise[:world], samples[:2], bench.FSKY, xsamples=xsamples[:2])     # warm-up
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     ctx.kernel_totals(reset=True)
+    ctx1.kernel_totals(reset=True)
     t0 = time.perf_counter()
     res = sweep.survey_sweep(li, ni, Pk, Ls, nmodes, noise, samples, bench.FSKY, xsamples=xsamples)
     if world > 1:
         dist.barrier()
     dt = time.perf_counter() - t0
     kms, launches = ctx.kernel_totals()
+    kms1, launches1 = ctx1.kernel_totals()
     assert np.all(np.isfinite(res['out'])) and np.all(res['out'][:, :, 0] > 0)
     if rank == 0:
         n_design = len(noise) * len(samples)
         print(json.dumps({'workload': 'survey sweep: %d noise levels x %d n(z) configurations on %d multipoles' % (len(noise), len(samples), Ls.size),
                           'n_gpus': world, 'wall_s': dt, 'designs_per_s': n_design / dt, 'n0_L_modes_per_s': len(noise) * Ls.size / dt,
-                          'rank0_kernel_ms': kms, 'rank0_launches': launches,
+                          'rank0_kernel_ms': kms + kms1, 'rank0_n0_kernel_ms': kms1, 'rank0_launches': launches + launches1,
                           'best_snr_design': [int(x) for x in np.unravel_index(np.argmax(res['out'][:, :, 0]), res['out'].shape[:2])],
                           'snr_range': [float(res['out'][:, :, 0].min()), float(res['out'][:, :, 0].max())]}), flush=True)
     if world > 1:
