@@ -280,6 +280,14 @@ int lbg_fisher_accum(lbg_ctx* ctx, int n_ell, int n_spec, int n_par, const doubl
  * kappa + 6 tracers x 20 bins = 121 fields, 241 spectra).  out_per_ell ([n_ell][n_par][n_par], unweighted) may be NULL. */
 int lbg_field_fisher(lbg_ctx* ctx, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
                      int n_par, const double* dC, const double* mode_weight, double* out_F, double* out_per_ell /*or NULL*/);
+/* lbg_field_fisher with amplitude-type parameters described instead of tabulated: parameters 0..n_dense-1 have explicit rows
+ * dC[n_dense][n_spec][n_ell]; parameter n_dense + a is an amplitude A_a with d C_s / d A_a = amp[a][s] * sig[s][l] (sig[n_spec][n_ell] = the
+ * signal spectra C without noise; e.g. a bias amplitude: amp = 1 on its kappa-g spectra, 2 on its auto spectra, 0 elsewhere -- the
+ * analytic dp_DL('b1') of interloper.py:65-74).  Their rows are formed on the device: a tomographic forecast with 2 cosmological + 6 bias
+ * parameters uploads 38 MB instead of 86 MB and the host never builds the 57 MB of copied spectra.  n_dense + n_amp <= 8. */
+int lbg_field_fisher_amp(lbg_ctx* ctx, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
+                         int n_dense, const double* dC, int n_amp, const double* amp, const double* sig,
+                         const double* mode_weight, double* out_F, double* out_per_ell /*or NULL*/);
 /* mqw/py/mqw.py:63-104 `Fisher` (clustering-redshift N_p(z_i) Fisher): bins[n_bin][8] = {bp, bs, Np, Ns, wp, ws, wps, -}
  * per redshift shell (mqw.py:24-41); cgg[n_ell] shared by all shells (cgg_per_bin = 0, as mqw.py:48) or
  * cgg[n_bin][n_ell] (cgg_per_bin = 1, as cadence/cadence.py:97); mode_weight[l] = 2l+1 (0 beyond an l cut).

@@ -108,6 +108,8 @@ def _declare(L):
         'lbg_gaussian_cov': [vp, i, c_double_p, i, c_double_p, i, c_int_p, c_int_p, d, c_double_p],
         'lbg_fisher_accum': [vp, i, i, i, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p],
         'lbg_field_fisher': [vp, i, i, i, c_int_p, c_int_p, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p],
+        'lbg_field_fisher_amp': [vp, i, i, i, c_int_p, c_int_p, c_double_p, i, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p,
+                                 c_double_p],
         'lbg_mqw_fisher': [vp, i, i, c_double_p, i, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_cadence_fisher': [vp, i, i, c_double_p, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_forecast_grid': [vp, i, c_double_p, c_double_p, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p,

@@ -427,14 +427,30 @@ field_fisher_kernel(int n_ell, int nf, int n_spec, int np, int n_heavy, const in
     }
 }
 
-extern "C" int lbg_field_fisher(lbg_ctx* c, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
-                                int n_par, const double* dC, const double* mode_weight, double* out_F, double* out_per_ell) {
+// dC rows of amplitude-type parameters built on the device: dC[n_dense + a][s][l] = amp[a][s] * sig[s][l]
+__global__ void ff_expand_amp_kernel(int n_amp, int n_spec, int n_ell, const double* __restrict__ amp, const double* __restrict__ sig,
+                                     double* __restrict__ out) {
+    const size_t nt = (size_t)n_spec * n_ell;
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nt) return;
+    const int sp = (int)(t / n_ell);
+    const double v = sig[t];
+    for (int a = 0; a < n_amp; ++a) out[(size_t)a * nt + t] = amp[(size_t)a * n_spec + sp] * v;
+}
+
+// n_par = n_dense + n_amp parameters: the first n_dense with explicit derivative rows dC[n_dense][n_spec][n_ell], the others amplitude
+// parameters described by amp[n_amp][n_spec] (d C_s / d A_a = amp[a][s] * sig_s) and the signal spectra sig[n_spec][n_ell].
+static int field_fisher_impl(lbg_ctx* c, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
+                             int n_dense, const double* dC, int n_amp, const double* amp, const double* sig,
+                             const double* mode_weight, double* out_F, double* out_per_ell) {
+    const int n_par = n_dense + n_amp;
     LBG_REQUIRE(c && out_F, "lbg_field_fisher: NULL argument");
     LBG_REQUIRE(n_ell >= 0 && n_f >= 1 && n_f <= 160, "lbg_field_fisher: n_f=%d outside [1, 160]", n_f);
     LBG_REQUIRE(n_spec >= 1 && n_spec <= n_f * (n_f + 1) / 2, "lbg_field_fisher: n_spec=%d outside [1, n_f (n_f + 1) / 2]", n_spec);
     LBG_REQUIRE(n_par >= 1 && n_par <= MAX_PAR, "lbg_field_fisher: n_par=%d outside [1, %d]", n_par, MAX_PAR);
     LBG_REQUIRE(spec_a && spec_b, "lbg_field_fisher: NULL spectrum list");
-    LBG_REQUIRE(n_ell == 0 || (tot && dC && mode_weight), "lbg_field_fisher: NULL array");
+    LBG_REQUIRE(n_dense >= 0 && n_amp >= 0, "lbg_field_fisher: negative parameter count");
+    LBG_REQUIRE(n_ell == 0 || (tot && mode_weight && (n_dense == 0 || dC) && (n_amp == 0 || (amp && sig))), "lbg_field_fisher: NULL array");
     // CSC pattern of the symmetric matrices the spectra list fills; every field needs its auto spectrum (else C_l is singular)
     std::vector<int> cnt(n_f + 1, 0), seen((size_t)n_f * n_f, 0);
     for (int s = 0; s < n_spec; ++s) {
@@ -485,7 +501,8 @@ extern "C" int lbg_field_fisher(lbg_ctx* c, int n_ell, int n_f, int n_spec, cons
     const int gx = n_ell < sms ? n_ell : sms;     // one CTA per SM: 512 threads x 128 registers fill the register file
     const int nq = n_par * n_par;
     const size_t nt = (size_t)n_spec * n_ell, nd = nt * n_par;
-    if (c->s0.reserve(nt * 8) || c->s1.reserve(nd * 8) || c->s2.reserve(pat.size() * 4) || c->s3.reserve((size_t)n_ell * 8) ||
+    if (c->s0.reserve(nt * 8) || c->s1.reserve((nd + (n_amp ? nt : 0)) * 8) || c->s2.reserve(pat.size() * 4) ||
+        c->s3.reserve(((size_t)n_ell + (size_t)n_amp * n_spec) * 8) ||
         c->s4.reserve((size_t)n_ell * nq * 8) || c->s5.reserve((size_t)nq * 8)) return LBG_ENOMEM;
     cudaStream_t st = c->stream;
     typedef void (*ff_kernel_t)(int, int, int, int, int, const int*, const int*, const int*, const int*, const int*, const int*, const double*,
@@ -496,11 +513,20 @@ extern "C" int lbg_field_fisher(lbg_ctx* c, int n_ell, int n_f, int n_spec, cons
     const ff_kernel_t kern = kerns[dv_sm ? 1 : 0][ncg - 1];
     LBG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     LBG_CUDA(cudaMemcpyAsync(c->s0.p, tot, nt * 8, cudaMemcpyHostToDevice, st));
-    LBG_CUDA(cudaMemcpyAsync(c->s1.p, dC, nd * 8, cudaMemcpyHostToDevice, st));
+    if (n_dense) LBG_CUDA(cudaMemcpyAsync(c->s1.p, dC, nt * n_dense * 8, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s2.p, pat.data(), pat.size() * 4, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s3.p, mode_weight, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
+    if (n_amp) {
+        LBG_CUDA(cudaMemcpyAsync(c->s1.as<double>() + nd, sig, nt * 8, cudaMemcpyHostToDevice, st));
+        LBG_CUDA(cudaMemcpyAsync(c->s3.as<double>() + n_ell, amp, (size_t)n_amp * n_spec * 8, cudaMemcpyHostToDevice, st));
+    }
     const int* d_pat = c->s2.as<int>();
     KernelTimer t(c);
+    if (n_amp) {
+        ff_expand_amp_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(n_amp, n_spec, n_ell, c->s3.as<double>() + n_ell, c->s1.as<double>() + nd,
+                                                                           c->s1.as<double>() + nt * n_dense);
+        t.launched();
+    }
     kern<<<gx, FF_T, smem, st>>>(n_ell, n_f, n_spec, n_par, n_heavy, d_pat, d_pat + n_spec, d_pat + 2 * n_spec,
                                  d_pat + 2 * n_spec + 2 * n_f + 1, d_pat + 2 * n_spec + 2 * n_f + 1 + nnz, d_pat + 2 * n_spec + n_f + 1,
                                  c->s0.as<double>(), c->s1.as<double>(), c->s4.as<double>());
@@ -510,6 +536,17 @@ extern "C" int lbg_field_fisher(lbg_ctx* c, int n_ell, int n_f, int n_spec, cons
     LBG_CUDA(cudaMemcpyAsync(out_F, c->s5.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, st));
     if (out_per_ell) LBG_CUDA(cudaMemcpyAsync(out_per_ell, c->s4.p, (size_t)n_ell * nq * 8, cudaMemcpyDeviceToHost, st));
     return t.finish();
+}
+
+extern "C" int lbg_field_fisher(lbg_ctx* c, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
+                                int n_par, const double* dC, const double* mode_weight, double* out_F, double* out_per_ell) {
+    return field_fisher_impl(c, n_ell, n_f, n_spec, spec_a, spec_b, tot, n_par, dC, 0, nullptr, nullptr, mode_weight, out_F, out_per_ell);
+}
+
+extern "C" int lbg_field_fisher_amp(lbg_ctx* c, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
+                                    int n_dense, const double* dC, int n_amp, const double* amp, const double* sig,
+                                    const double* mode_weight, double* out_F, double* out_per_ell) {
+    return field_fisher_impl(c, n_ell, n_f, n_spec, spec_a, spec_b, tot, n_dense, dC, n_amp, amp, sig, mode_weight, out_F, out_per_ell);
 }
 
 static int mqw_fisher_impl(lbg_ctx* c, int n_ell, int n_bin, const double* cgg, int cgg_per_bin, const double* bins,

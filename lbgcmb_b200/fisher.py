@@ -66,6 +66,29 @@ def field_fisher(n_f, spectra, tot, dC, mode_weight, per_ell=False, device=None)
     return (F, Q) if per_ell else F
 
 
+def field_fisher_amp(n_f, spectra, tot, dC, amp, sig, mode_weight, device=None):
+    """field_fisher with amplitude parameters described, not tabulated (lbg_field_fisher_amp): dC [n_dense, n_spec, n_ell] for the
+    parameters with explicit derivatives, then one parameter per row of amp [n_amp, n_spec] with d C_s / d A = amp[a, s] * sig[s]
+    (sig [n_spec, n_ell]: the signal spectra).  Parameter order of F: dense ones first."""
+    ctx = _ffi.context(device)
+    tot, sig, amp, w = _ffi.f64(tot), _ffi.f64(sig), _ffi.f64(np.atleast_2d(amp)), _ffi.f64(mode_weight)
+    n_spec, n_ell = tot.shape
+    dC = _ffi.f64(dC) if dC is not None and np.size(dC) else np.zeros((0, n_spec, n_ell))
+    if dC.ndim != 3 or dC.shape[1:] != (n_spec, n_ell) or sig.shape != tot.shape or amp.shape[1] != n_spec or w.shape != (n_ell,) \
+            or len(spectra) != n_spec:
+        raise ValueError('spectra / tot / dC / amp / sig / mode_weight shapes disagree')
+    n_par = dC.shape[0] + amp.shape[0]
+    sa = np.ascontiguousarray([s_[0] for s_ in spectra], dtype=np.int32)
+    sb = np.ascontiguousarray([s_[1] for s_ in spectra], dtype=np.int32)
+    F = np.empty((n_par, n_par))
+    _ffi.check(_ffi.lib().lbg_field_fisher_amp(ctx.handle, n_ell, int(n_f), n_spec, sa.ctypes.data_as(_ffi.c_int_p),
+                                               sb.ctypes.data_as(_ffi.c_int_p), _ffi._dp(tot), dC.shape[0], _ffi._dp(dC), amp.shape[0],
+                                               _ffi._dp(amp), _ffi._dp(sig), _ffi._dp(w), _ffi._dp(F), None))
+    if not np.all(np.isfinite(F)):
+        raise np.linalg.LinAlgError('lbg_field_fisher: C_l is singular (zero pivot) or holds non-finite entries at some multipole')
+    return F
+
+
 def mqw_fisher(cgg, bins, mode_weight, fsky, device=None):
     """(F [n_bin, n_bin], F_ii Schur-Limber [n_bin], S(l)) of mqw/py/mqw.py:63-104; bins[n_bin, 7] = bp,bs,Np,Ns,wp,ws,wps."""
     ctx = _ffi.context(device)

@@ -137,24 +137,28 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
     ngg = np.concatenate([np.broadcast_to(1. / np.asarray(t['nbar'], dtype=np.float64), (n,)) for t, n in zip(tracers, nb)])
     spectra = [(0, 0)] + [(0, i) for i in range(1, nf)] + [(i, i) for i in range(1, nf)]
     tot = np.concatenate([(ckk + nkk)[None], ckg, cgg + ngg[:, None]])
-    dC = np.empty((len(names), len(spectra), ell.size))
+    n_c = len(cosmo_params)
+    dC = np.empty((n_c, len(spectra), ell.size))            # explicit rows for the cosmological parameters only
     for j, p in enumerate(cosmo_params):
         up, dn = spec[1 + 2 * j], spec[2 + 2 * j]
         for sl, x, y in ((slice(0, 1), up[0], dn[0]), (slice(1, nf), up[1], dn[1]), (slice(nf, 2 * nf - 1), up[2], dn[2])):
             np.subtract(x, y, out=dC[j, sl].reshape(np.shape(x)))
             dC[j, sl] /= 2. * steps[p]
+    # bias amplitudes: d C_kg / d A = C_kg, d C_gg / d A = 2 C_gg on the tracer's own bins (the analytic dp_DL('b1') of
+    # interloper.py:65-74): described by a (tracer x spectrum) factor matrix, their rows are formed on the device
+    amp = np.zeros((len(tracers), len(spectra)))
     o = 0
     for t, n in enumerate(nb):
-        j = len(cosmo_params) + t
-        dC[j] = 0.0
-        dC[j, 1 + o:1 + o + n] = ckg[o:o + n]
-        dC[j, nf + o:nf + o + n] = 2. * cgg[o:o + n]
+        amp[t, 1 + o:1 + o + n] = 1.0
+        amp[t, nf + o:nf + o + n] = 2.0
         o += n
+    sig = np.concatenate([ckk[None], ckg, cgg])
     w = nmodes * (2. * ell + 1.) * fsky
     if accum is None:
-        F = fisher.field_fisher(nf, spectra, tot, dC, w, device=device)
+        F = fisher.field_fisher_amp(nf, spectra, tot, dC, amp, sig, w, device=device)
     else:
-        F = accum(nf, spectra, tot, dC, w)
+        full = np.concatenate([dC, amp[:, :, None] * sig[None]])
+        F = accum(nf, spectra, tot, full, w)
     if sharded:
         F, = dist.allreduce_sum(F)
     cov = np.linalg.inv(F)

@@ -50,7 +50,7 @@ def main():
     nkk = np.zeros(Ls.size)
     nkk[idx] = Nkk.Nkk(li, ni, Ls[idx], ['TT', 'TE', 'EE', 'EB'], 1.4, 1.0, iterative=True, pickleit=False)
     small = [dict(t, edges=t['edges'][:3], nbar=t['nbar'][:2]) for t in tracers[:2]]
-    tm.tomographic_fisher(small, Lf[:64], np.ones(64), bench.FSKY, nkk[:64] + 1e-7, cosmo_params=('sig8',))      # warm-up
+    tm.tomographic_fisher(small, Lf[:64], np.ones(64), bench.FSKY, nkk[:64] + 1e-7, cosmo_params=('sig8',), sharded=world > 1)      # warm-up (incl. the first NCCL all-reduce)
     ctx.kernel_totals(reset=True)
     t0 = time.perf_counter()
     r = tm.tomographic_fisher(tracers, Lf, np.ones_like(Lf), bench.FSKY, nkk, cosmo_params=('sig8', 'mnu'), sharded=world > 1)

@@ -84,3 +84,25 @@ def test_field_fisher_errors(ctx):
     with pytest.raises(np.linalg.LinAlgError):
         field_fisher(2, [(0, 0), (0, 1), (1, 1)], np.array([[1., 1.], [1., 1.], [1., 1.]]), np.ones((1, 3, 2)), np.ones(2))   # singular C_l
     assert np.array_equal(field_fisher(1, [(0, 0)], np.ones((1, 0)), np.ones((2, 1, 0)), np.ones(0)), np.zeros((2, 2)))
+
+
+def test_amplitude_parameters_described_instead_of_tabulated(ctx):
+    """lbg_field_fisher_amp: rows of amplitude parameters formed on the device from (factor matrix, signal spectra) == the same rows
+    handed over explicitly (bit for bit: the product amp * sig is the same double either way), also with no dense parameter at all."""
+    from lbgcmb_b200.fisher import field_fisher, field_fisher_amp
+    rng = np.random.default_rng(7)
+    spectra, tot, dC, w = _random_case(rng, 25, 37, 2, True)
+    n_spec = len(spectra)
+    sig = tot * rng.uniform(0.3, 0.9, tot.shape)
+    amp = np.zeros((3, n_spec))
+    amp[0, 1:9] = 1.0; amp[0, 25:33] = 2.0
+    amp[1, 9:17] = 1.0; amp[1, 33:41] = 2.0
+    amp[2, 17:25] = 0.7; amp[2, 41:49] = 1.4
+    full = np.concatenate([dC, amp[:, :, None] * sig[None]])
+    want = field_fisher(25, spectra, tot, full, w)
+    got = field_fisher_amp(25, spectra, tot, dC, amp, sig, w)
+    assert got.shape == (5, 5) and np.array_equal(got, want)
+    only = field_fisher_amp(25, spectra, tot, None, amp, sig, w)
+    assert np.array_equal(only, want[2:, 2:])
+    with pytest.raises(ValueError):
+        field_fisher_amp(25, spectra, tot, dC, amp[:, :-1], sig, w)
