@@ -288,6 +288,26 @@ int lbg_field_fisher(lbg_ctx* ctx, int n_ell, int n_f, int n_spec, const int* sp
 int lbg_field_fisher_amp(lbg_ctx* ctx, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
                          int n_dense, const double* dC, int n_amp, const double* amp, const double* sig,
                          const double* mode_weight, double* out_F, double* out_per_ell /*or NULL*/);
+/* Spectra kept on the device between calls, for forecasts whose Fisher inputs are differences of Limber sums (the host loop of
+ * interloper.py:223-253 taken over configs[3]'s 241 spectra x 5 cosmologies): a context holds up to 20 spectra sets, each a
+ * [set_rows][n_ell] matrix.
+ *   lbg_limber_keep       lbg_limber whose batch row b stays on the device as row dest_row[b] of set `set` (dest_row[b] < 0: dropped); the
+ *                         first call that names a set with a new shape zeroes it, later calls fill further rows.
+ *   lbg_spectra_set_fill  a set filled without a Limber sum (noise): row r = row_const[r] at every multipole, then rows curve_row[i]
+ *                         replaced by curves[i][n_ell] (n_curves may be 0).
+ *   lbg_spectra_set_get   rows [row0, row0 + n_rows) of a set copied to the host.
+ *   lbg_field_fisher_sets lbg_field_fisher_amp with tot = fid + noise (set_noise < 0: none), explicit derivative rows
+ *                         dC_j = (plus_j - minus_j) / two_h[j] (j < n_diff; the roundings of numpy's subtract-then-divide) and sig = fid, all
+ *                         formed on the device from the named sets (each n_spec rows x n_ell).  n_diff + n_amp <= 8.
+ * No counterpart in the reference (its spectra live in numpy arrays); the results equal the host-array entry points bit for bit. */
+int lbg_limber_keep(lbg_ctx* ctx, int n_batch, int n_ell, const double* ell, int n_z, const double* chi, const double* weight,
+                    const int* prow, int oob, int set, int set_rows, const int* dest_row /*[n_batch]*/);
+int lbg_spectra_set_fill(lbg_ctx* ctx, int set, int set_rows, int n_ell, const double* row_const /*[set_rows]*/, int n_curves,
+                         const int* curve_row, const double* curves /*[n_curves][n_ell]*/);
+int lbg_spectra_set_get(lbg_ctx* ctx, int set, int row0, int n_rows, int n_ell, double* out /*[n_rows][n_ell]*/);
+int lbg_field_fisher_sets(lbg_ctx* ctx, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, int set_fid, int set_noise,
+                          int n_diff, const int* set_plus, const int* set_minus, const double* two_h, int n_amp, const double* amp,
+                          const double* mode_weight, double* out_F, double* out_per_ell /*or NULL*/);
 /* mqw/py/mqw.py:63-104 `Fisher` (clustering-redshift N_p(z_i) Fisher): bins[n_bin][8] = {bp, bs, Np, Ns, wp, ws, wps, -}
  * per redshift shell (mqw.py:24-41); cgg[n_ell] shared by all shells (cgg_per_bin = 0, as mqw.py:48) or
  * cgg[n_bin][n_ell] (cgg_per_bin = 1, as cadence/cadence.py:97); mode_weight[l] = 2l+1 (0 beyond an l cut).

@@ -110,6 +110,11 @@ def _declare(L):
         'lbg_field_fisher': [vp, i, i, i, c_int_p, c_int_p, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p],
         'lbg_field_fisher_amp': [vp, i, i, i, c_int_p, c_int_p, c_double_p, i, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p,
                                  c_double_p],
+        'lbg_limber_keep': [vp, i, i, c_double_p, i, c_double_p, c_double_p, c_int_p, i, i, i, c_int_p],
+        'lbg_spectra_set_fill': [vp, i, i, i, c_double_p, i, c_int_p, c_double_p],
+        'lbg_spectra_set_get': [vp, i, i, i, i, c_double_p],
+        'lbg_field_fisher_sets': [vp, i, i, i, c_int_p, c_int_p, i, i, i, c_int_p, c_int_p, c_double_p, i, c_double_p, c_double_p, c_double_p,
+                                  c_double_p],
         'lbg_mqw_fisher': [vp, i, i, c_double_p, i, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_cadence_fisher': [vp, i, i, c_double_p, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_forecast_grid': [vp, i, c_double_p, c_double_p, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p,

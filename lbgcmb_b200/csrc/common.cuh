@@ -135,6 +135,10 @@ struct lbg_ctx {
     int          store_nz[PK_SLOTS] = {0, 0, 0, 0};
     lbg::DevBuf  pk_store[PK_SLOTS];
     void drop_pk_tables() { pnl_nz = 0; for (int i = 0; i < PK_SLOTS; ++i) store_nz[i] = 0; ++pk_gen; }
+    // spectra kept on the device between calls (lbg_limber_keep -> lbg_field_fisher_sets): set s is a [set_rows][set_n_ell] matrix
+    static const int SPEC_SETS = 20;
+    lbg::DevBuf  spec_set[SPEC_SETS];
+    int          set_rows[SPEC_SETS] = {0}, set_n_ell[SPEC_SETS] = {0};
 };
 
 namespace lbg {

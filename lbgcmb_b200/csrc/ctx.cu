@@ -244,6 +244,7 @@ extern "C" int lbg_ctx_destroy(lbg_ctx* c) {
                       &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->pk_lnk, &c->pk_plin, &c->pk_pnl, &c->pk_rdk})
         b->release();
     for (DevBuf& b : c->pk_store) b.release();
+    for (DevBuf& b : c->spec_set) b.release();
     c->pin_in.release(); c->pin_out.release(); c->pin_n0.release(); c->pin_n0_out.release();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->stream);

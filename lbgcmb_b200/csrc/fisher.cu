@@ -440,9 +440,24 @@ __global__ void ff_expand_amp_kernel(int n_amp, int n_spec, int n_ell, const dou
 
 // n_par = n_dense + n_amp parameters: the first n_dense with explicit derivative rows dC[n_dense][n_spec][n_ell], the others amplitude
 // parameters described by amp[n_amp][n_spec] (d C_s / d A_a = amp[a][s] * sig_s) and the signal spectra sig[n_spec][n_ell].
+// Inputs taken from spectra sets kept on the device (lbg_limber_keep / lbg_spectra_set_fill) instead of host arrays:
+//   tot = fid + noise,   dC_j = (plus_j - minus_j) / two_h_j  (central difference, the same two roundings as numpy's subtract and divide),
+//   sig = fid
+struct FFSets { int fid, noise, n_diff; int plus[MAX_PAR], minus[MAX_PAR]; double two_h[MAX_PAR]; };
+struct FFAsm { const double* fid; const double* noise; const double* plus[MAX_PAR]; const double* minus[MAX_PAR]; double two_h[MAX_PAR]; int n_diff; };
+
+__global__ void ff_assemble_kernel(size_t nt, FFAsm a, double* __restrict__ tot, double* __restrict__ dC) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nt) return;
+    const double f = a.fid[t];
+    tot[t] = a.noise ? __dadd_rn(f, a.noise[t]) : f;
+    for (int j = 0; j < a.n_diff; ++j) dC[(size_t)j * nt + t] = __ddiv_rn(__dsub_rn(a.plus[j][t], a.minus[j][t]), a.two_h[j]);
+}
+
 static int field_fisher_impl(lbg_ctx* c, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, const double* tot,
                              int n_dense, const double* dC, int n_amp, const double* amp, const double* sig,
-                             const double* mode_weight, double* out_F, double* out_per_ell) {
+                             const double* mode_weight, double* out_F, double* out_per_ell, const FFSets* sets = nullptr) {
+    if (sets) n_dense = sets->n_diff;
     const int n_par = n_dense + n_amp;
     LBG_REQUIRE(c && out_F, "lbg_field_fisher: NULL argument");
     LBG_REQUIRE(n_ell >= 0 && n_f >= 1 && n_f <= 160, "lbg_field_fisher: n_f=%d outside [1, 160]", n_f);
@@ -450,7 +465,8 @@ static int field_fisher_impl(lbg_ctx* c, int n_ell, int n_f, int n_spec, const i
     LBG_REQUIRE(n_par >= 1 && n_par <= MAX_PAR, "lbg_field_fisher: n_par=%d outside [1, %d]", n_par, MAX_PAR);
     LBG_REQUIRE(spec_a && spec_b, "lbg_field_fisher: NULL spectrum list");
     LBG_REQUIRE(n_dense >= 0 && n_amp >= 0, "lbg_field_fisher: negative parameter count");
-    LBG_REQUIRE(n_ell == 0 || (tot && mode_weight && (n_dense == 0 || dC) && (n_amp == 0 || (amp && sig))), "lbg_field_fisher: NULL array");
+    LBG_REQUIRE(n_ell == 0 || sets || (tot && (n_dense == 0 || dC) && (n_amp == 0 || sig)), "lbg_field_fisher: NULL array");
+    LBG_REQUIRE(n_ell == 0 || (mode_weight && (n_amp == 0 || amp)), "lbg_field_fisher: NULL array");
     // CSC pattern of the symmetric matrices the spectra list fills; every field needs its auto spectrum (else C_l is singular)
     std::vector<int> cnt(n_f + 1, 0), seen((size_t)n_f * n_f, 0);
     for (int s = 0; s < n_spec; ++s) {
@@ -512,19 +528,43 @@ static int field_fisher_impl(lbg_ctx* c, int n_ell, int n_f, int n_spec, const i
         {field_fisher_kernel<true, 1>, field_fisher_kernel<true, 2>, field_fisher_kernel<true, 3>, field_fisher_kernel<true, 4>, field_fisher_kernel<true, 5>}};
     const ff_kernel_t kern = kerns[dv_sm ? 1 : 0][ncg - 1];
     LBG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    LBG_CUDA(cudaMemcpyAsync(c->s0.p, tot, nt * 8, cudaMemcpyHostToDevice, st));
-    if (n_dense) LBG_CUDA(cudaMemcpyAsync(c->s1.p, dC, nt * n_dense * 8, cudaMemcpyHostToDevice, st));
+    FFAsm fa{};
+    if (sets) {
+        auto set_ptr = [&](int s, const double** out) -> int {
+            LBG_REQUIRE(s >= 0 && s < lbg_ctx::SPEC_SETS, "lbg_field_fisher_sets: set %d outside [0, %d)", s, lbg_ctx::SPEC_SETS);
+            if (c->set_rows[s] != n_spec || c->set_n_ell[s] != n_ell) {
+                set_error("lbg_field_fisher_sets: set %d holds %d rows x %d multipoles, the call names %d spectra x %d multipoles", s,
+                          c->set_rows[s], c->set_n_ell[s], n_spec, n_ell);
+                return LBG_ESTATE;
+            }
+            *out = c->spec_set[s].as<double>();
+            return LBG_OK;
+        };
+        if (int rc = set_ptr(sets->fid, &fa.fid)) return rc;
+        if (sets->noise >= 0) { if (int rc = set_ptr(sets->noise, &fa.noise)) return rc; }
+        fa.n_diff = sets->n_diff;
+        for (int j = 0; j < sets->n_diff; ++j) {
+            if (int rc = set_ptr(sets->plus[j], &fa.plus[j])) return rc;
+            if (int rc = set_ptr(sets->minus[j], &fa.minus[j])) return rc;
+            fa.two_h[j] = sets->two_h[j];
+        }
+    } else {
+        LBG_CUDA(cudaMemcpyAsync(c->s0.p, tot, nt * 8, cudaMemcpyHostToDevice, st));
+        if (n_dense) LBG_CUDA(cudaMemcpyAsync(c->s1.p, dC, nt * n_dense * 8, cudaMemcpyHostToDevice, st));
+        if (n_amp) LBG_CUDA(cudaMemcpyAsync(c->s1.as<double>() + nd, sig, nt * 8, cudaMemcpyHostToDevice, st));
+    }
     LBG_CUDA(cudaMemcpyAsync(c->s2.p, pat.data(), pat.size() * 4, cudaMemcpyHostToDevice, st));
     LBG_CUDA(cudaMemcpyAsync(c->s3.p, mode_weight, (size_t)n_ell * 8, cudaMemcpyHostToDevice, st));
-    if (n_amp) {
-        LBG_CUDA(cudaMemcpyAsync(c->s1.as<double>() + nd, sig, nt * 8, cudaMemcpyHostToDevice, st));
-        LBG_CUDA(cudaMemcpyAsync(c->s3.as<double>() + n_ell, amp, (size_t)n_amp * n_spec * 8, cudaMemcpyHostToDevice, st));
-    }
+    if (n_amp) LBG_CUDA(cudaMemcpyAsync(c->s3.as<double>() + n_ell, amp, (size_t)n_amp * n_spec * 8, cudaMemcpyHostToDevice, st));
     const int* d_pat = c->s2.as<int>();
     KernelTimer t(c);
+    if (sets) {
+        ff_assemble_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(nt, fa, c->s0.as<double>(), c->s1.as<double>());
+        t.launched();
+    }
     if (n_amp) {
-        ff_expand_amp_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(n_amp, n_spec, n_ell, c->s3.as<double>() + n_ell, c->s1.as<double>() + nd,
-                                                                           c->s1.as<double>() + nt * n_dense);
+        ff_expand_amp_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(n_amp, n_spec, n_ell, c->s3.as<double>() + n_ell,
+                                                                           sets ? fa.fid : c->s1.as<double>() + nd, c->s1.as<double>() + nt * n_dense);
         t.launched();
     }
     kern<<<gx, FF_T, smem, st>>>(n_ell, n_f, n_spec, n_par, n_heavy, d_pat, d_pat + n_spec, d_pat + 2 * n_spec,
@@ -547,6 +587,20 @@ extern "C" int lbg_field_fisher_amp(lbg_ctx* c, int n_ell, int n_f, int n_spec, 
                                     int n_dense, const double* dC, int n_amp, const double* amp, const double* sig,
                                     const double* mode_weight, double* out_F, double* out_per_ell) {
     return field_fisher_impl(c, n_ell, n_f, n_spec, spec_a, spec_b, tot, n_dense, dC, n_amp, amp, sig, mode_weight, out_F, out_per_ell);
+}
+
+extern "C" int lbg_field_fisher_sets(lbg_ctx* c, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, int set_fid,
+                                     int set_noise, int n_diff, const int* set_plus, const int* set_minus, const double* two_h,
+                                     int n_amp, const double* amp, const double* mode_weight, double* out_F, double* out_per_ell) {
+    LBG_REQUIRE(n_diff >= 0 && n_diff <= MAX_PAR, "lbg_field_fisher_sets: n_diff=%d outside [0, %d]", n_diff, MAX_PAR);
+    LBG_REQUIRE(n_diff == 0 || (set_plus && set_minus && two_h), "lbg_field_fisher_sets: NULL argument");
+    FFSets fs{};
+    fs.fid = set_fid; fs.noise = set_noise; fs.n_diff = n_diff;
+    for (int j = 0; j < n_diff; ++j) {
+        LBG_REQUIRE(two_h[j] != 0.0, "lbg_field_fisher_sets: zero step for difference %d", j);
+        fs.plus[j] = set_plus[j]; fs.minus[j] = set_minus[j]; fs.two_h[j] = two_h[j];
+    }
+    return field_fisher_impl(c, n_ell, n_f, n_spec, spec_a, spec_b, nullptr, n_diff, nullptr, n_amp, amp, nullptr, mode_weight, out_F, out_per_ell, &fs);
 }
 
 static int mqw_fisher_impl(lbg_ctx* c, int n_ell, int n_bin, const double* cgg, int cgg_per_bin, const double* bins,

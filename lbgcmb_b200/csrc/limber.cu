@@ -322,11 +322,25 @@ extern "C" int lbg_pk_select_slot(lbg_ctx* c, int slot, int* out_rows) {
     return LBG_OK;
 }
 
-extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell, int n_z, const double* chi,
-                          const double* weight /*[n_batch][n_z]*/, const int* prow /*[n_z]*/, int oob,
-                          double* out_cl /*[n_batch][n_ell]*/) {
-    LBG_REQUIRE(c && ell && chi && weight && prow && out_cl, "lbg_limber: NULL argument");
+// rows of a finished Limber batch moved into a kept spectra set: set row dest[b] <- batch row b (dest[b] < 0: dropped)
+__global__ void keep_rows_kernel(int n_batch, int n_ell, const int* __restrict__ dest, const double* __restrict__ src, double* __restrict__ set) {
+    const size_t n = (size_t)n_batch * n_ell, t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const int b = (int)(t / n_ell), d = dest[b];
+    if (d >= 0) set[(size_t)d * n_ell + (t - (size_t)b * n_ell)] = src[t];
+}
+
+// out_cl != NULL: the spectra go back to the host (lbg_limber).  set >= 0: they stay on the device in spectra set `set`, a
+// [set_rows][n_ell] matrix, batch row b in set row dest_row[b] (lbg_limber_keep); rows of the set no batch entry names keep their contents.
+static int limber_impl(lbg_ctx* c, int n_batch, int n_ell, const double* ell, int n_z, const double* chi, const double* weight,
+                       const int* prow, int oob, double* out_cl, int set, int set_rows, const int* dest_row) {
+    LBG_REQUIRE(c && ell && chi && weight && prow && (out_cl || set >= 0), "lbg_limber: NULL argument");
     LBG_REQUIRE(n_batch > 0 && n_ell >= 0 && n_z > 0, "lbg_limber: bad sizes");
+    if (set >= 0) {
+        LBG_REQUIRE(set < lbg_ctx::SPEC_SETS, "lbg_limber_keep: set %d outside [0, %d)", set, lbg_ctx::SPEC_SETS);
+        LBG_REQUIRE(dest_row && set_rows > 0, "lbg_limber_keep: no destination rows");
+        for (int b = 0; b < n_batch; ++b) LBG_REQUIRE(dest_row[b] < set_rows, "lbg_limber_keep: dest_row[%d]=%d outside the %d-row set", b, dest_row[b], set_rows);
+    }
     std::lock_guard<std::mutex> g(c->mu);     // the table state is read under the lock: another thread may be swapping slots
     if (c->pnl_nz <= 0) { set_error("lbg_limber: call lbg_pk_build_table first"); return LBG_ESTATE; }
     for (int i = 0; i < n_z; ++i) LBG_REQUIRE(prow[i] >= 0 && prow[i] < c->pnl_nz, "lbg_limber: prow[%d]=%d outside the %d-row table", i, prow[i], c->pnl_nz);
@@ -378,10 +392,88 @@ extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell,
         limber_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, n_split, part, c->s4.as<double>());
         t.launched();
     }
-    LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, c->s4.p, bo, cudaMemcpyDeviceToHost, st));
+    if (set >= 0) {
+        // a set keeps its shape until a call names another one: the first call of a new shape starts from zeros
+        if (c->set_rows[set] != set_rows || c->set_n_ell[set] != n_ell) {
+            if (c->spec_set[set].reserve((size_t)set_rows * n_ell * 8)) return LBG_ENOMEM;
+            LBG_CUDA(cudaMemsetAsync(c->spec_set[set].p, 0, (size_t)set_rows * n_ell * 8, st));
+            c->set_rows[set] = set_rows; c->set_n_ell[set] = n_ell;
+        }
+        if (c->s3.reserve((size_t)n_batch * 4)) return LBG_ENOMEM;
+        int* hd = reinterpret_cast<int*>(c->pin_out.p);          // pin_out holds >= n_batch * n_ell * 8 bytes and is otherwise unused here
+        memcpy(hd, dest_row, (size_t)n_batch * 4);
+        LBG_CUDA(cudaMemcpyAsync(c->s3.p, hd, (size_t)n_batch * 4, cudaMemcpyHostToDevice, st));
+        const size_t n = (size_t)n_batch * n_ell;
+        keep_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n_batch, n_ell, c->s3.as<int>(), c->s4.as<double>(), c->spec_set[set].as<double>());
+        t.launched();
+    }
+    if (out_cl) LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, c->s4.p, bo, cudaMemcpyDeviceToHost, st));
     const int rc = t.finish();
-    if (rc == LBG_OK) memcpy(out_cl, c->pin_out.p, bo);
+    if (rc == LBG_OK && out_cl) memcpy(out_cl, c->pin_out.p, bo);
     return rc;
+}
+
+extern "C" int lbg_limber(lbg_ctx* c, int n_batch, int n_ell, const double* ell, int n_z, const double* chi,
+                          const double* weight /*[n_batch][n_z]*/, const int* prow /*[n_z]*/, int oob,
+                          double* out_cl /*[n_batch][n_ell]*/) {
+    LBG_REQUIRE(out_cl, "lbg_limber: NULL argument");
+    return limber_impl(c, n_batch, n_ell, ell, n_z, chi, weight, prow, oob, out_cl, -1, 0, nullptr);
+}
+
+extern "C" int lbg_limber_keep(lbg_ctx* c, int n_batch, int n_ell, const double* ell, int n_z, const double* chi,
+                               const double* weight, const int* prow, int oob, int set, int set_rows, const int* dest_row) {
+    LBG_REQUIRE(set >= 0, "lbg_limber_keep: set %d outside [0, %d)", set, lbg_ctx::SPEC_SETS);
+    return limber_impl(c, n_batch, n_ell, ell, n_z, chi, weight, prow, oob, nullptr, set, set_rows, dest_row);
+}
+
+// Rows of a kept set filled without a Limber sum (noise): row r = row_const[r] at every multipole, then rows curve_row[i] replaced
+// by the caller's curves[i][n_ell].
+__global__ void set_fill_kernel(int n_rows, int n_ell, const double* __restrict__ row_const, double* __restrict__ set) {
+    const size_t n = (size_t)n_rows * n_ell, t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) set[t] = row_const[t / n_ell];
+}
+
+extern "C" int lbg_spectra_set_fill(lbg_ctx* c, int set, int set_rows, int n_ell, const double* row_const, int n_curves,
+                                    const int* curve_row, const double* curves) {
+    LBG_REQUIRE(c && row_const && (n_curves == 0 || (curve_row && curves)), "lbg_spectra_set_fill: NULL argument");
+    LBG_REQUIRE(set >= 0 && set < lbg_ctx::SPEC_SETS, "lbg_spectra_set_fill: set %d outside [0, %d)", set, lbg_ctx::SPEC_SETS);
+    LBG_REQUIRE(set_rows > 0 && n_ell >= 0 && n_curves >= 0, "lbg_spectra_set_fill: bad sizes");
+    for (int i = 0; i < n_curves; ++i) LBG_REQUIRE(curve_row[i] >= 0 && curve_row[i] < set_rows, "lbg_spectra_set_fill: curve_row[%d]=%d outside the %d-row set", i, curve_row[i], set_rows);
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    c->set_rows[set] = set_rows; c->set_n_ell[set] = n_ell;
+    if (n_ell == 0) return LBG_OK;
+    const size_t bc = ((size_t)set_rows * 8 + 255) & ~(size_t)255, total = bc + (size_t)n_curves * n_ell * 8;
+    if (c->spec_set[set].reserve((size_t)set_rows * n_ell * 8) || c->s0.reserve(total) || c->pin_in.reserve(total)) return LBG_ENOMEM;
+    unsigned char* hin = c->pin_in.as<unsigned char>();
+    memcpy(hin, row_const, (size_t)set_rows * 8);
+    if (n_curves) memcpy(hin + bc, curves, (size_t)n_curves * n_ell * 8);
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, hin, total, cudaMemcpyHostToDevice, st));
+    KernelTimer t(c);
+    const size_t n = (size_t)set_rows * n_ell;
+    set_fill_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(set_rows, n_ell, c->s0.as<double>(), c->spec_set[set].as<double>());
+    t.launched();
+    for (int i = 0; i < n_curves; ++i)
+        LBG_CUDA(cudaMemcpyAsync(c->spec_set[set].as<double>() + (size_t)curve_row[i] * n_ell, c->s0.as<unsigned char>() + bc + (size_t)i * n_ell * 8,
+                                 (size_t)n_ell * 8, cudaMemcpyDeviceToDevice, st));
+    return t.finish();
+}
+
+extern "C" int lbg_spectra_set_get(lbg_ctx* c, int set, int row0, int n_rows, int n_ell, double* out) {
+    LBG_REQUIRE(c && out, "lbg_spectra_set_get: NULL argument");
+    LBG_REQUIRE(set >= 0 && set < lbg_ctx::SPEC_SETS, "lbg_spectra_set_get: set %d outside [0, %d)", set, lbg_ctx::SPEC_SETS);
+    std::lock_guard<std::mutex> g(c->mu);
+    if (c->set_rows[set] <= 0 || c->set_n_ell[set] != n_ell) { set_error("lbg_spectra_set_get: set %d holds %d rows of %d multipoles, asked for %d multipoles", set, c->set_rows[set], c->set_n_ell[set], n_ell); return LBG_ESTATE; }
+    LBG_REQUIRE(row0 >= 0 && n_rows >= 0 && row0 + n_rows <= c->set_rows[set], "lbg_spectra_set_get: rows [%d, %d) outside the %d-row set", row0, row0 + n_rows, c->set_rows[set]);
+    if (n_rows == 0 || n_ell == 0) return LBG_OK;
+    LBG_CUDA(cudaSetDevice(c->device));
+    const size_t b = (size_t)n_rows * n_ell * 8;
+    if (c->pin_out.reserve(b)) return LBG_ENOMEM;
+    LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, c->spec_set[set].as<double>() + (size_t)row0 * n_ell, b, cudaMemcpyDeviceToHost, c->stream));
+    LBG_CUDA(cudaStreamSynchronize(c->stream));
+    memcpy(out, c->pin_out.p, b);
+    return LBG_OK;
 }
 
 extern "C" int lbg_pk_eval(lbg_ctx* c, int row, int n, const double* x, int oob, double* out) {

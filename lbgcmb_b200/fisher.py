@@ -89,6 +89,52 @@ def field_fisher_amp(n_f, spectra, tot, dC, amp, sig, mode_weight, device=None):
     return F
 
 
+def spectra_set_fill(set_index, row_const, n_ell, curves=None, device=None):
+    """Spectra set `set_index` on the device <- rows constant over the multipoles (row_const [n_rows]), rows named by `curves`
+    ({row: [n_ell] array}) then replaced (lbg_spectra_set_fill): the noise matrix of a forecast without building it on the host."""
+    ctx = _ffi.context(device)
+    rc = _ffi.f64(row_const)
+    curves = curves or {}
+    rows = np.ascontiguousarray(sorted(curves), dtype=np.int32)
+    cv = _ffi.f64(np.array([curves[r] for r in rows], dtype=np.float64).reshape(rows.size, int(n_ell)))
+    _ffi.check(_ffi.lib().lbg_spectra_set_fill(ctx.handle, int(set_index), rc.size, int(n_ell), _ffi._dp(rc), rows.size,
+                                               rows.ctypes.data_as(_ffi.c_int_p), _ffi._dp(cv)))
+
+
+def spectra_set_get(set_index, row0, n_rows, n_ell, device=None):
+    """Rows [row0, row0 + n_rows) of a kept spectra set (lbg_spectra_set_get)."""
+    ctx = _ffi.context(device)
+    out = np.empty((int(n_rows), int(n_ell)))
+    _ffi.check(_ffi.lib().lbg_spectra_set_get(ctx.handle, int(set_index), int(row0), int(n_rows), int(n_ell), _ffi._dp(out)))
+    return out
+
+
+def field_fisher_sets(n_f, spectra, n_ell, set_fid, set_noise, diffs, amp, mode_weight, device=None):
+    """field_fisher_amp whose spectra never left the device (lbg_field_fisher_sets): tot = set_fid + set_noise (None: no noise),
+    explicit derivatives (set_plus - set_minus) / two_h for each (set_plus, set_minus, two_h) of `diffs`, sig = set_fid; the sets were
+    filled by Cosmology.limber(..., keep=...) / spectra_set_fill."""
+    ctx = _ffi.context(device)
+    n_spec = len(spectra)
+    amp = _ffi.f64(np.atleast_2d(amp)) if amp is not None and np.size(amp) else np.zeros((0, n_spec))
+    w = _ffi.f64(mode_weight)
+    if amp.shape[1] != n_spec or w.shape != (int(n_ell),):
+        raise ValueError('spectra / amp / mode_weight shapes disagree')
+    sa = np.ascontiguousarray([s_[0] for s_ in spectra], dtype=np.int32)
+    sb = np.ascontiguousarray([s_[1] for s_ in spectra], dtype=np.int32)
+    plus = np.ascontiguousarray([d_[0] for d_ in diffs], dtype=np.int32)
+    minus = np.ascontiguousarray([d_[1] for d_ in diffs], dtype=np.int32)
+    two_h = _ffi.f64([d_[2] for d_ in diffs])
+    n_par = len(diffs) + amp.shape[0]
+    F = np.empty((n_par, n_par))
+    _ffi.check(_ffi.lib().lbg_field_fisher_sets(ctx.handle, int(n_ell), int(n_f), n_spec, sa.ctypes.data_as(_ffi.c_int_p),
+                                                sb.ctypes.data_as(_ffi.c_int_p), int(set_fid), -1 if set_noise is None else int(set_noise),
+                                                len(diffs), plus.ctypes.data_as(_ffi.c_int_p), minus.ctypes.data_as(_ffi.c_int_p),
+                                                _ffi._dp(two_h), amp.shape[0], _ffi._dp(amp), _ffi._dp(w), _ffi._dp(F), None))
+    if not np.all(np.isfinite(F)):
+        raise np.linalg.LinAlgError('lbg_field_fisher: C_l is singular (zero pivot) or holds non-finite entries at some multipole')
+    return F
+
+
 def mqw_fisher(cgg, bins, mode_weight, fsky, device=None):
     """(F [n_bin, n_bin], F_ii Schur-Limber [n_bin], S(l)) of mqw/py/mqw.py:63-104; bins[n_bin, 7] = bp,bs,Np,Ns,wp,ws,wps."""
     ctx = _ffi.context(device)

@@ -383,8 +383,10 @@ class Cosmology(object):
         z, a = self._za(z, a)
         return self.klin, self.build_rows([z], nonlinear=True, sig8=sig8, want_host=True)[0]
 
-    def limber(self, ells, zs, chis, weights, nonlinear=True, oob=0, sig8=None):
-        """C_l[b] = sum_z weights[b, z] P(k=(l+1/2)/chi_z, z) on the device (csrc/limber.cu limber_kernel)."""
+    def limber(self, ells, zs, chis, weights, nonlinear=True, oob=0, sig8=None, keep=None):
+        """C_l[b] = sum_z weights[b, z] P(k=(l+1/2)/chi_z, z) on the device (csrc/limber.cu limber_kernel).
+        keep = (set, set_rows, dest_rows): the spectra stay on the device, batch row b as row dest_rows[b] of spectra set `set`
+        (lbg_limber_keep, for fisher.field_fisher_sets); returns None."""
         zs = np.atleast_1d(np.asarray(zs, dtype=np.float64))
         self.build_rows(zs, nonlinear=nonlinear, sig8=sig8)
         ctx = self._ctx()
@@ -393,6 +395,14 @@ class Cosmology(object):
         prow = np.arange(zs.size, dtype=np.int32)
         if chis.size != zs.size or w.shape[1] != zs.size:
             raise ValueError('zs, chis and weights disagree in length')
+        if keep is not None:
+            dest = np.ascontiguousarray(keep[2], dtype=np.int32)
+            if dest.shape != (w.shape[0],):
+                raise ValueError('keep: one destination row per batch entry')
+            _ffi.check(_ffi.lib().lbg_limber_keep(ctx.handle, w.shape[0], ells.size, _ffi._dp(ells), zs.size, _ffi._dp(chis), _ffi._dp(w),
+                                                  prow.ctypes.data_as(_ffi.c_int_p), int(oob), int(keep[0]), int(keep[1]),
+                                                  dest.ctypes.data_as(_ffi.c_int_p)))
+            return None
         out = np.empty((w.shape[0], ells.size))
         _ffi.check(_ffi.lib().lbg_limber(ctx.handle, w.shape[0], ells.size, _ffi._dp(ells), zs.size, _ffi._dp(chis), _ffi._dp(w),
                                          prow.ctypes.data_as(_ffi.c_int_p), int(oob), _ffi._dp(out)))

@@ -128,10 +128,13 @@ class LensingX:
         ggwts2 = self.kerg * kerg2 / self.chis ** 2.
         return self._project_table(kp, self.chis, ggwts2 * self._tw, oob=1)
 
-    def _project_z(self, ikpz, zs, chis, weights, oob):
+    def _project_z(self, ikpz, zs, chis, weights, oob, keep=None):
         if isinstance(ikpz, PkZ):
             w = weights * ikpz.amplitude(zs)
-            return ikpz.cosmo.limber(self.l, zs, chis, w[None, :], nonlinear=ikpz.nonlinear, oob=oob, sig8=ikpz.sig8)[0]
+            out = ikpz.cosmo.limber(self.l, zs, chis, w[None, :], nonlinear=ikpz.nonlinear, oob=oob, sig8=ikpz.sig8, keep=keep)
+            return None if keep is not None else out[0]
+        if keep is not None:
+            raise ValueError('keep= needs a PkZ table (device P(k, z))')
         tabs = [ikpz(z=z) for z in zs]                     # a foreign callable is the caller's input: sampled on the host
         k = np.asarray(tabs[0][0], dtype=np.float64)
         for t in tabs:
@@ -145,6 +148,8 @@ class LensingX:
         wts = self.ggwts if auto else self.kgwts
         return self._project_z(ikpz, self.zs, self.chis, wts * self._tw, oob=1)
 
-    def cl_kkz(self, ikpz):
-        ''' Assuming interpolating function for Pk(z) across the redshift bin '''
-        return self._project_z(ikpz, self.kkzs, self.kkchis, self.kkwts * self._kktw, oob=0)
+    def cl_kkz(self, ikpz, keep=None):
+        ''' Assuming interpolating function for Pk(z) across the redshift bin.  keep = (set, set_rows, row): left on the device '''
+        if keep is not None:
+            keep = (keep[0], keep[1], [keep[2]])
+        return self._project_z(ikpz, self.kkzs, self.kkchis, self.kkwts * self._kktw, oob=0, keep=keep)

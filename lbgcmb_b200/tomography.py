@@ -54,13 +54,15 @@ def make_cosmology(theta, Dplus_table='device', k=None, device=None):
     return Background(M=M, B=theta['B'], sig8=theta['sig8'], klin=k, plin=plin, device=device, Dplus_table=Dplus_table)
 
 
-def field_spectra(cosmo, ell, tracers, nodes_per_bin=10, nonlinear=True, kk=True, geometry=None):
-    """C_kk [n_ell] (None without `kk`), C_kg [n_field, n_ell], C_gg [n_field, n_ell] for every redshift bin of every tracer; one batched
-    Limber launch per tracer (2 n_bin entries sharing each P(k, z) lookup).  tracers: dicts with 'edges' [n_bin + 1] (contiguous bins),
+def field_spectra(cosmo, ell, tracers, nodes_per_bin=10, nonlinear=True, kk=True, geometry=None, keep_set=None):
+    """C_kk [n_ell] (None without `kk`), C_kg [n_field, n_ell], C_gg [n_field, n_ell] for every redshift bin of every tracer; ONE batched
+    Limber launch for all tracers (block-diagonal weights over the tracers' concatenated z grids).  tracers: dicts with 'edges' [n_bin + 1] (contiguous bins),
     'dndz' and 'bz' callables.  Bin i integrates over its own `nodes_per_bin` + 1 nodes of the tracer's z grid (edge nodes belong to both
     neighbours), normalised over the bin as modi/lensing.py:78-87.  `geometry`: a dict the caller keeps between calls with the SAME
     ell, tracers and nodes_per_bin; the distances and weight vectors (host `quad`s, modi/cosmology.py:134-150) depend on (M, L) only and
-    are then computed once per background instead of once per cosmology."""
+    are then computed once per background instead of once per cosmology.
+    keep_set = s: nothing comes back to the host; spectra set s on the device holds [kk | kg rows | gg rows] (2 n_field + 1 rows,
+    the spectrum order tomographic_fisher uses) for fisher.field_fisher_sets, and the return value is None."""
     ell = np.asarray(ell, dtype=np.float64)
     key = (cosmo.M, cosmo.L, cosmo.H0)
     geo = None if geometry is None else geometry.get(key)
@@ -84,21 +86,41 @@ def field_spectra(cosmo, ell, tracers, nodes_per_bin=10, nonlinear=True, kk=True
                 w[i, s] = kcmb[s] * kg_i / chis[s] ** 2. * b[s] * tw              # kgwts, :90
                 w[nb + i, s] = kg_i ** 2. / chis[s] ** 2. * b[s] ** 2. * tw       # ggwts, :89
             per_tracer.append((nb, zs, chis, w))
-        geo = (lx, per_tracer)
+        # ONE batched Limber call for all tracers: their z nodes one after another, the weights block-diagonal (a batch block of 8
+        # entries holds bins of one tracer -- 2 n_bin is a multiple of 8 for the 20-bin case -- and the kernel skips the z nodes none of
+        # a block's entries weights, so the zeros cost nothing); one P(k, z) table build per cosmology instead of one per tracer
+        nz_all = sum(zs.size for _, zs, _, _ in per_tracer)
+        nb_all = sum(nb for nb, _, _, _ in per_tracer)
+        z_all = np.concatenate([zs for _, zs, _, _ in per_tracer])
+        chi_all = np.concatenate([chis for _, _, chis, _ in per_tracer])
+        w_all = np.zeros((2 * nb_all, nz_all))
+        rows_kg, rows_gg, r0, c0 = [], [], 0, 0
+        for nb, zs, chis, w in per_tracer:
+            w_all[r0:r0 + 2 * nb, c0:c0 + zs.size] = w
+            rows_kg.append(np.arange(r0, r0 + nb))
+            rows_gg.append(np.arange(r0 + nb, r0 + 2 * nb))
+            r0 += 2 * nb
+            c0 += zs.size
+        geo = (lx, (z_all, chi_all, w_all, np.concatenate(rows_kg), np.concatenate(rows_gg)))
         if geometry is not None:
             geometry[key] = geo
-    lx, per_tracer = geo
+    lx, (z_all, chi_all, w_all, rows_kg, rows_gg) = geo
+    if keep_set is not None:
+        n_fld = rows_kg.size
+        dest = np.empty(2 * n_fld, dtype=np.int32)
+        dest[rows_kg] = 1 + np.arange(n_fld)
+        dest[rows_gg] = 1 + n_fld + np.arange(n_fld)
+        lx.cl_kkz(PkZ(cosmo, nonlinear=nonlinear), keep=(keep_set, 2 * n_fld + 1, 0))
+        cosmo.limber(ell, z_all, chi_all, w_all, nonlinear=nonlinear, oob=1, keep=(keep_set, 2 * n_fld + 1, dest))
+        return None
     ckk = lx.cl_kkz(PkZ(cosmo, nonlinear=nonlinear)) if kk else None
-    kg, gg = [], []
-    for nb, zs, chis, w in per_tracer:
-        out = cosmo.limber(ell, zs, chis, w, nonlinear=nonlinear, oob=1)
-        kg.append(out[:nb])
-        gg.append(out[nb:])
-    return ckk, np.concatenate(kg), np.concatenate(gg)
+    out = cosmo.limber(ell, z_all, chi_all, w_all, nonlinear=nonlinear, oob=1)
+    return ckk, out[rows_kg], out[rows_gg]
+
 
 
 def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=('sig8', 'mnu'), steps=None, nodes_per_bin=10,
-                       nonlinear=True, k=None, device=None, sharded=False, spectra_fn=None, accum=None):
+                       nonlinear=True, k=None, device=None, sharded=False, spectra_fn=None, accum=None, return_spectra=True, host_arrays=False):
     """Fisher matrix over `cosmo_params` + one bias amplitude per tracer (b(z) -> A_t b(z), fiducial A_t = 1) from kappa and every
     galaxy bin: fields (kappa, g_1 .. g_n), spectra kk, kappa g_i, g_i g_i (bins of one tracer are disjoint; cross-tracer overlaps
     are neglected), noise N_kk = `nkk` [n_ell] and 1 / nbar_i on the galaxy autos (tracers[t]['nbar']: per bin, sr^-1).
@@ -107,7 +129,9 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
     (C_kg / A, 2 C_gg / A).  n_par <= 8.  sharded=True: this rank takes ell[rank::world] and the matrices are all-reduced.
     Returns dict: params, F, cov (= F^-1), sigma (marginalised 1-sigma), spectra (fiducial kk, kg, gg on this rank's multipoles).
     `spectra_fn(theta, ell) -> (ckk, ckg, cgg)` and `accum` (signature of fisher.field_fisher) replace the device calls in the CPU
-    (gloo) tests of the sharding logic; the product path leaves both None."""
+    (gloo) tests of the sharding logic; the product path leaves both None and then keeps every spectrum on the device (spectra sets:
+    Cosmology.limber(keep=...), fisher.field_fisher_sets); host_arrays=True selects the host-array route of the same device kernels
+    (spectra copied back, sums and differences in numpy, fisher.field_fisher_amp), kept for the parity test between the two.  return_spectra=False skips the read-back of the fiducial spectra."""
     fid = dict(FIDUCIAL, **(fid or {}))
     steps = dict(STEPS, **(steps or {}))
     ell, nmodes, nkk = (np.asarray(a, dtype=np.float64) for a in (ell, nmodes, nkk))
@@ -123,27 +147,11 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
     thetas = [fid]
     for p in cosmo_params:
         thetas += [dict(fid, **{p: fid[p] + steps[p]}), dict(fid, **{p: fid[p] - steps[p]})]
-    if spectra_fn is None:
-        growth = growth_tables([t['M'] for t in thetas], device=device)       # the whole stencil in one launch
-        spec, geometry = [], {}
-        for theta, y in zip(thetas, growth):
-            c = make_cosmology(theta, Dplus_table=y, k=k, device=device)
-            spec.append(field_spectra(c, ell, tracers, nodes_per_bin, nonlinear, geometry=geometry))
-    else:
-        spec = [spectra_fn(theta, ell) for theta in thetas]
-    ckk, ckg, cgg = spec[0]
     nb = [len(t['edges']) - 1 for t in tracers]
     nf = 1 + sum(nb)
     ngg = np.concatenate([np.broadcast_to(1. / np.asarray(t['nbar'], dtype=np.float64), (n,)) for t, n in zip(tracers, nb)])
     spectra = [(0, 0)] + [(0, i) for i in range(1, nf)] + [(i, i) for i in range(1, nf)]
-    tot = np.concatenate([(ckk + nkk)[None], ckg, cgg + ngg[:, None]])
     n_c = len(cosmo_params)
-    dC = np.empty((n_c, len(spectra), ell.size))            # explicit rows for the cosmological parameters only
-    for j, p in enumerate(cosmo_params):
-        up, dn = spec[1 + 2 * j], spec[2 + 2 * j]
-        for sl, x, y in ((slice(0, 1), up[0], dn[0]), (slice(1, nf), up[1], dn[1]), (slice(nf, 2 * nf - 1), up[2], dn[2])):
-            np.subtract(x, y, out=dC[j, sl].reshape(np.shape(x)))
-            dC[j, sl] /= 2. * steps[p]
     # bias amplitudes: d C_kg / d A = C_kg, d C_gg / d A = 2 C_gg on the tracer's own bins (the analytic dp_DL('b1') of
     # interloper.py:65-74): described by a (tracer x spectrum) factor matrix, their rows are formed on the device
     amp = np.zeros((len(tracers), len(spectra)))
@@ -152,13 +160,47 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
         amp[t, 1 + o:1 + o + n] = 1.0
         amp[t, nf + o:nf + o + n] = 2.0
         o += n
-    sig = np.concatenate([ckk[None], ckg, cgg])
     w = nmodes * (2. * ell + 1.) * fsky
-    if accum is None:
-        F = fisher.field_fisher_amp(nf, spectra, tot, dC, amp, sig, w, device=device)
+    if spectra_fn is None and accum is None and not host_arrays:
+        # product path: every spectrum stays on the device.  Cosmology i of the stencil fills spectra set i; the noise is set
+        # len(thetas); sums, differences and amplitude rows are formed there (lbg_field_fisher_sets)
+        growth = growth_tables([t['M'] for t in thetas], device=device)       # the whole stencil in one launch
+        geometry = {}
+        for i, (theta, y) in enumerate(zip(thetas, growth)):
+            c = make_cosmology(theta, Dplus_table=y, k=k, device=device)
+            field_spectra(c, ell, tracers, nodes_per_bin, nonlinear, geometry=geometry, keep_set=i)
+        noise_set = len(thetas)
+        fisher.spectra_set_fill(noise_set, np.concatenate([np.zeros(nf), ngg]), ell.size, curves={0: nkk}, device=device)
+        diffs = [(1 + 2 * j, 2 + 2 * j, 2. * steps[p]) for j, p in enumerate(cosmo_params)]
+        F = fisher.field_fisher_sets(nf, spectra, ell.size, 0, noise_set, diffs, amp, w, device=device)
+        if return_spectra:
+            fidu = fisher.spectra_set_get(0, 0, 2 * nf - 1, ell.size, device=device)
+            ckk, ckg, cgg = fidu[0], fidu[1:nf], fidu[nf:]
+        else:
+            ckk = ckg = cgg = None
     else:
-        full = np.concatenate([dC, amp[:, :, None] * sig[None]])
-        F = accum(nf, spectra, tot, full, w)
+        if spectra_fn is None:
+            growth = growth_tables([t['M'] for t in thetas], device=device)
+            spec, geometry = [], {}
+            for theta, y in zip(thetas, growth):
+                c = make_cosmology(theta, Dplus_table=y, k=k, device=device)
+                spec.append(field_spectra(c, ell, tracers, nodes_per_bin, nonlinear, geometry=geometry))
+        else:
+            spec = [spectra_fn(theta, ell) for theta in thetas]
+        ckk, ckg, cgg = spec[0]
+        tot = np.concatenate([(ckk + nkk)[None], ckg, cgg + ngg[:, None]])
+        dC = np.empty((n_c, len(spectra), ell.size))            # explicit rows for the cosmological parameters only
+        for j, p in enumerate(cosmo_params):
+            up, dn = spec[1 + 2 * j], spec[2 + 2 * j]
+            for sl, x, y in ((slice(0, 1), up[0], dn[0]), (slice(1, nf), up[1], dn[1]), (slice(nf, 2 * nf - 1), up[2], dn[2])):
+                np.subtract(x, y, out=dC[j, sl].reshape(np.shape(x)))
+                dC[j, sl] /= 2. * steps[p]
+        sig = np.concatenate([ckk[None], ckg, cgg])
+        if accum is None:
+            F = fisher.field_fisher_amp(nf, spectra, tot, dC, amp, sig, w, device=device)
+        else:
+            full = np.concatenate([dC, amp[:, :, None] * sig[None]])
+            F = accum(nf, spectra, tot, full, w)
     if sharded:
         F, = dist.allreduce_sum(F)
     cov = np.linalg.inv(F)

@@ -91,3 +91,58 @@ def test_geometry_cache_is_per_background(ctx):
     for x, y, z in zip(a[1:], a2[1:], a3[1:]):
         assert np.array_equal(x, y) and np.array_equal(x, z)
     assert np.array_equal(a[0], a2[0])
+
+
+def test_device_resident_route_equals_host_array_route(ctx):
+    """Spectra kept on the device (lbg_limber_keep -> lbg_field_fisher_sets) against the same kernels fed through host arrays
+    (lbg_limber -> numpy sums and differences -> lbg_field_fisher_amp): the same doubles, so F and the fiducial spectra agree bit for bit."""
+    from lbgcmb_b200 import tomography as tm
+    nm = np.linspace(1., 2., ELL.size)
+    nkk = 2e-8 * (1. + ELL / 1000.)
+    kw = dict(cosmo_params=('sig8', 'mnu'))
+    dev = tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, **kw)
+    host = tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, host_arrays=True, **kw)
+    assert np.array_equal(dev['F'], host['F'])
+    for key in ('kk', 'kg', 'gg'):
+        assert np.array_equal(dev['spectra'][key], host['spectra'][key])
+    lean = tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, return_spectra=False, **kw)
+    assert np.array_equal(lean['F'], dev['F']) and lean['spectra']['kg'] is None
+
+
+def test_spectra_sets_entry_points(ctx):
+    """lbg_spectra_set_fill / _get round trip, lbg_field_fisher_sets == lbg_field_fisher_amp on the same numbers, and the state errors."""
+    from lbgcmb_b200 import fisher
+    rng = np.random.default_rng(5)
+    nf, n_ell = 4, 23
+    spectra = [(0, 0)] + [(0, i) for i in range(1, nf)] + [(i, i) for i in range(1, nf)]
+    ns = len(spectra)
+    fid = np.abs(rng.normal(1., 0.1, (ns, n_ell))) * np.array([1.] + [0.2] * (nf - 1) + [1.] * (nf - 1))[:, None]
+    up, dn = fid * rng.uniform(1.0, 1.1, fid.shape), fid * rng.uniform(0.9, 1.0, fid.shape)
+    noise_c = np.concatenate([np.zeros(nf), rng.uniform(0.1, 0.3, nf - 1)])
+    nkk = rng.uniform(0.1, 0.2, n_ell)
+    for s, m in ((3, fid), (4, up), (5, dn)):                                   # a set filled row by row from curves
+        fisher.spectra_set_fill(s, np.zeros(ns), n_ell, curves={r: m[r] for r in range(ns)})
+        assert np.array_equal(fisher.spectra_set_get(s, 0, ns, n_ell), m)
+    fisher.spectra_set_fill(6, noise_c, n_ell, curves={0: nkk})
+    noise = np.repeat(noise_c[:, None], n_ell, axis=1)
+    noise[0] = nkk
+    assert np.array_equal(fisher.spectra_set_get(6, 0, ns, n_ell), noise)
+    assert np.array_equal(fisher.spectra_set_get(6, 2, 3, n_ell), noise[2:5])
+    amp = np.zeros((1, ns))
+    amp[0, 1:nf], amp[0, nf:] = 1., 2.
+    w = rng.uniform(1., 5., n_ell)
+    h = 0.01
+    got = fisher.field_fisher_sets(nf, spectra, n_ell, 3, 6, [(4, 5, 2. * h)], amp, w)
+    dC = ((up - dn) / (2. * h))[None]
+    want = fisher.field_fisher_amp(nf, spectra, fid + noise, dC, amp, fid, w)
+    assert np.array_equal(got, want)
+    none = fisher.field_fisher_sets(nf, spectra, n_ell, 3, None, [(4, 5, 2. * h)], amp, w)
+    assert np.array_equal(none, fisher.field_fisher_amp(nf, spectra, fid, dC, amp, fid, w))
+    with pytest.raises(Exception, match='holds'):                               # a set of another shape
+        fisher.field_fisher_sets(nf, spectra, n_ell - 1, 3, 6, [(4, 5, 2. * h)], amp, w[:-1])
+    with pytest.raises(ValueError):
+        fisher.field_fisher_sets(nf, spectra, n_ell, 3, 25, [(4, 5, 2. * h)], amp, w)
+    with pytest.raises(ValueError):
+        fisher.field_fisher_sets(nf, spectra, n_ell, 3, 6, [(4, 5, 0.0)], amp, w)
+    with pytest.raises(ValueError):
+        fisher.spectra_set_get(6, ns - 1, 2, n_ell)
