@@ -70,18 +70,22 @@ def _default_grids():
     return _DEFAULT_GRIDS
 
 
-def upload_cls(ctx, lensCl_interps, nolensCl_interps, reuse=False):
-    """C_l tables -> the context.  The library compares them, value for value, with the tables it already holds and keeps its
-    splines when nothing changed (a sweep over beam / noise calls N0 many times on the same spectra), so every call hands the
-    tables over; `reuse` is accepted for compatibility and changes nothing."""
+def _cl_tables(lensCl_interps, nolensCl_interps):
+    """(n, lensed [4, n], unlensed [4, n]): the callables sampled on the integer multipoles 0..n-1 the library splines."""
     lens = [table_of(lensCl_interps[x]) for x in _ORDER]
     n = min(t.size for t in lens)
     nolens = []
     for x in _ORDER:
         nolens.append(table_of(nolensCl_interps[x], n_default=n))
     n = min(n, min(t.size for t in nolens))
-    lt = _ffi.f64(np.stack([t[:n] for t in lens]))
-    ut = _ffi.f64(np.stack([t[:n] for t in nolens]))
+    return n, _ffi.f64(np.stack([t[:n] for t in lens])), _ffi.f64(np.stack([t[:n] for t in nolens]))
+
+
+def upload_cls(ctx, lensCl_interps, nolensCl_interps, reuse=False):
+    """C_l tables -> the context.  The library compares them, value for value, with the tables it already holds and keeps its
+    splines when nothing changed (a sweep over beam / noise calls N0 many times on the same spectra), so every call hands the
+    tables over; `reuse` is accepted for compatibility and changes nothing."""
+    n, lt, ut = _cl_tables(lensCl_interps, nolensCl_interps)
     _ffi.check(_ffi.lib().lbg_upload_cl_tables(ctx.handle, n, _ffi._dp(lt), _ffi._dp(ut)))
     return n
 
@@ -231,27 +235,37 @@ def Nkk_async(lensCl_interps, nolensCl_interps, Ls, terms=['TT', 'TE', 'EE', 'EB
     return _Mapped(n0_begin(lensCl_interps, nolensCl_interps, Ls, terms, thetab, DeltaT, iterative, lane=1), lambda r: r[0])
 
 
-def _cache_path(Ls, terms, thetab, DeltaT, iterative):
+def _cache_path(Ls, terms, thetab, DeltaT, iterative, lensCl_interps=None, nolensCl_interps=None):
+    """The reference's file name (cmb/Nkk.py:36-41) + a digest of what that name leaves out: the C_l tables (hence the cosmology) and
+    the exact L grid.  Under the reference's key a file written for other spectra is silently served; here it is simply another file."""
     root = os.environ['LBGCMB']
     fpath = root + '/pickle/Nkk_thetab_%.2lf_DeltaT_%.2lf_' % (thetab, DeltaT) + 'Nlls_%d_Lmin_%d_Lmax_%d_' % (len(Ls), Ls[0], Ls[-1])
-    fpath += '_'.join(terms) + '_iterative_%d.p' % int(iterative == True)  # noqa: E712 (reference spelling)
-    return fpath
+    fpath += '_'.join(terms) + '_iterative_%d' % int(iterative == True)  # noqa: E712 (reference spelling)
+    if lensCl_interps is not None:
+        import hashlib
+        h = hashlib.sha256()
+        _, lt, ut = _cl_tables(lensCl_interps, nolensCl_interps)
+        for a in (lt, ut, _ffi.f64(np.asarray(Ls, dtype=np.float64)), np.array([thetab, DeltaT], dtype=np.float64)):
+            h.update(a.tobytes())
+        fpath += '_cl_%s' % h.hexdigest()[:16]
+    return fpath + '.p'
 
 
 def Nkk(lensCl_interps, nolensCl_interps, Ls, terms=['TT', 'TE', 'EE', 'EB'], thetab=1., DeltaT=1., iterative=False,
         pickleit=True):
     """Ckk noise curve for the flat-sky limit (Hu & Okamoto 2002); drop-in for cmb/Nkk.py:31.
 
-    The pickle cache of cmb/Nkk.py:36-46,174-182 is honoured only when $LBGCMB is set."""
+    The pickle cache of cmb/Nkk.py:36-46,174-182 is honoured only when $LBGCMB is set; its file name carries a
+    digest of the C_l tables and the L grid, which the reference's key ignores."""
     have_root = 'LBGCMB' in os.environ
     if have_root:
         try:
-            return load(open(_cache_path(Ls, terms, thetab, DeltaT, iterative), 'rb'))
+            return load(open(_cache_path(Ls, terms, thetab, DeltaT, iterative, lensCl_interps, nolensCl_interps), 'rb'))
         except Exception:
             pass
     result, _ = n0_terms(lensCl_interps, nolensCl_interps, Ls, terms, thetab, DeltaT, iterative)
     if pickleit and have_root:
-        fpath = _cache_path(Ls, terms, thetab, DeltaT, iterative)
+        fpath = _cache_path(Ls, terms, thetab, DeltaT, iterative, lensCl_interps, nolensCl_interps)
         os.makedirs(os.path.dirname(fpath), exist_ok=True)
         dump(result, open(fpath, 'wb'))
     return result

@@ -201,7 +201,6 @@ static int hf_wait_locked(lbg_ctx* c, lbg_hf_state& H, int* n_flagged) {
     cudaEventElapsedTime(&ms0, H.ev_s0a, H.ev_s0);
     cudaEventElapsedTime(&ms1, H.ev_b0, H.ev_b1);
     if (!(ms0 >= 0.f)) ms0 = 0.f;
-    if (getenv("LBG_DEBUG_HF")) fprintf(stderr, "hf_wait: sigma2 interval %.3f ms, build interval %.3f ms\n", ms0, ms1);
     c->last_ms = (double)ms0 + ms1;
     c->last_launches = H.pending_launches;
     c->total_ms += c->last_ms;

@@ -22,28 +22,42 @@ def bz_callmodel(z, mlim):
     return bz_fitmodel(z, A, B)
 
 
-class drop_bz():
+_MISSING = -98.9          # entries at or below -99 mark (z, m) cells without a measurement
+
+
+def _bias_table(path):
+    """(row labels, column labels, body) of a labelled table file: first row / column hold the labels, the corner is unused;
+    cells marked missing come back masked."""
+    raw = np.loadtxt(path)
+    body = np.where(raw[1:, 1:] < _MISSING, np.nan, raw[1:, 1:])
+    return raw[1:, 0], raw[0, 1:], ma.masked_invalid(body)
+
+
+class drop_bz(object):
+    """Measured dropout bias b(z, m_lim) with asymmetric errors from the table pair <type>.dat / <type>_err.dat
+    (dropouts/bz/py/get_bz.py:34-111 reads the same files): attributes zs, ms (the tabulated redshifts and magnitude limits), bs
+    [n_z, n_m] (masked where not measured), el / eu (lower / upper errors: the two column halves of the error file) and the table
+    limits zlo, zhi, mlo, mhi."""
+
     def __init__(self, type='harikane4'):
-        root = os.environ['LBGCMB'] + '/dropouts/bz/dat/'
-        har = np.loadtxt(root + '%s.dat' % type)
-        hare = np.loadtxt(root + '%s_err.dat' % type)
-        zs = har[:, 0][1:]
-        mags = har[0, :][1:]
-        har[har < -98.9] = np.nan
-        hare[hare < -98.9] = np.nan
-        har = ma.masked_invalid(har)[1:, 1:]
-        hare = ma.masked_invalid(hare)[1:, 1:]
-        cut = len(mags)
-        self.zs, self.ms, self.bs = zs, mags, har
-        self.el, self.eu = hare[:, :cut], hare[:, cut:]
+        stem = os.path.join(os.environ['LBGCMB'], 'dropouts', 'bz', 'dat', type)
+        self.zs, self.ms, self.bs = _bias_table(stem + '.dat')
+        _, _, err = _bias_table(stem + '_err.dat')
+        n_m = self.ms.size
+        self.el, self.eu = err[:, :n_m], err[:, n_m:]
         self.zlo, self.zhi = self.zs.min(), self.zs.max()
         self.mlo, self.mhi = self.ms.min(), self.ms.max()
 
+    def _nearest(self, nodes, x):
+        d = np.abs(nodes - x)
+        return d == d.min()                  # boolean selector: ties select both neighbours, as the reference's lookup does
+
     def get_bzm(self, z, m, printit=False):
-        if (z >= self.zlo) & (z <= self.zhi) & (m >= self.mlo) & (m <= self.mhi):
-            zindex = np.abs(self.zs - z) == np.abs(self.zs - z).min()
-            mindex = np.abs(self.ms - m) == np.abs(self.ms - m).min()
-            if printit:
-                print(self.bs[zindex, mindex], self.el[zindex, mindex], self.eu[zindex, mindex])
-            return self.bs[zindex, mindex], self.el[zindex, mindex], self.eu[zindex, mindex]
-        raise UserWarning('\n\nHarikane bias not available at z=%.2lf' % z)
+        """(b, lower error, upper error) at the tabulated node nearest to (z, m); UserWarning outside the table."""
+        if not (self.zlo <= z <= self.zhi and self.mlo <= m <= self.mhi):
+            raise UserWarning('\n\nHarikane bias not available at z=%.2lf' % z)
+        iz, im = self._nearest(self.zs, z), self._nearest(self.ms, m)
+        out = self.bs[iz, im], self.el[iz, im], self.eu[iz, im]
+        if printit:
+            print(*out)
+        return out

@@ -206,3 +206,44 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
     cov = np.linalg.inv(F)
     return {'params': names, 'F': F, 'cov': cov, 'sigma': np.sqrt(np.diag(cov)), 'fiducial': fid,
             'spectra': {'kk': ckk, 'kg': ckg, 'gg': cgg, 'ngg': ngg}, 'fields': nf, 'n_cosmologies': len(thetas)}
+
+
+# ---- f sigma8(z) as a derived quantity ---------------------------------------------------------------------------------------
+# BASELINE configs[3] lists "b(z) / f sigma8 / sum m_nu".  Angular kappa-g / g-g spectra in the Limber approximation carry no
+# redshift-space-distortion term, so f sigma8 is not a parameter these observables constrain on their own; what the forecast can state
+# is the error on f(z) sigma8(z) INSIDE the model (flat LCDM + the parameters varied), propagated from the Fisher covariance.
+def growth_rate(cosmo, z):
+    """f = d ln D / d ln a.  The growth table is D ~ y = E(a) int_0^a da' / (a' E)^3 (modi/cosmology.py:92-111), whose logarithmic
+    derivative is closed-form given y: f = d ln E / d ln a + 1 / (a^2 E^2 y)."""
+    a = 1. / (1. + np.asarray(z, dtype=np.float64))
+    M, L = cosmo.M, cosmo.L
+    K = 1. - M - L
+    E2 = M * a ** -3. + K * a ** -2. + L
+    dlnE = (-3. * M * a ** -3. - 2. * K * a ** -2.) / (2. * E2)
+    return dlnE + 1. / (a ** 2. * E2 * cosmo.Dplus(a))
+
+
+def fsigma8(cosmo, z):
+    """f(z) sigma8 D(z) / D(0)."""
+    return growth_rate(cosmo, z) * cosmo.sig8 * cosmo.Dgrow(z=np.asarray(z, dtype=np.float64))
+
+
+def fsigma8_forecast(result, zs, steps=None, device=None, growth='device'):
+    """1-sigma errors on f sigma8 at redshifts `zs` from a tomographic_fisher result: J cov J^T with J = d (f sigma8)(z) / d theta by
+    central differences over the cosmological parameters of the result (bias amplitudes do not enter; of the FIDUCIAL keys only sig8 and
+    M move the scale-independent growth modelled here -- sum m_nu changes the transfer-function shape only).  The
+    stencil's growth tables come from one lbg_growth_table launch (growth='host': the reference's Romberg route, CPU tests)."""
+    zs = np.atleast_1d(np.asarray(zs, dtype=np.float64))
+    steps = dict(STEPS, **(steps or {}))
+    fid = result['fiducial']
+    cosmo_params = [p for p in result['params'] if p in FIDUCIAL]
+    thetas = [fid]
+    for p in cosmo_params:
+        thetas += [dict(fid, **{p: fid[p] + steps[p]}), dict(fid, **{p: fid[p] - steps[p]})]
+    tabs = growth_tables([t['M'] for t in thetas], device=device) if growth == 'device' else [None] * len(thetas)
+    vals = [fsigma8(Background(M=t['M'], B=t['B'], sig8=t['sig8'], Dplus_table=y, device=device), zs) for t, y in zip(thetas, tabs)]
+    J = np.zeros((zs.size, len(result['params'])))
+    for j, p in enumerate(cosmo_params):
+        J[:, result['params'].index(p)] = (vals[1 + 2 * j] - vals[2 + 2 * j]) / (2. * steps[p])
+    cov = J @ result['cov'] @ J.T
+    return {'z': zs, 'fsigma8': vals[0], 'sigma': np.sqrt(np.diag(cov)), 'cov': cov, 'jacobian': J}

@@ -5,6 +5,7 @@ import os
 import sys
 
 import numpy as np
+import numpy.ma as ma
 import pytest
 
 pytestmark = pytest.mark.reference
@@ -42,6 +43,10 @@ def test_dropout_providers(ref):
     assert peakz(get_pz('u')) == 2.99           # gen_pz.py itself imports modules that are not in the tree; :37-43 restated
     a, b = drop_bz(), rbz.drop_bz()
     assert np.array_equal(a.zs, b.zs) and np.array_equal(a.ms, b.ms) and np.array_equal(a.bs.filled(-1), b.bs.filled(-1))
+    assert np.array_equal(a.el.filled(-1), b.el.filled(-1)) and np.array_equal(a.eu.filled(-1), b.eu.filled(-1))
+    for z, m in ((a.zs[0], a.ms[0]), (a.zs[1] + 0.01, a.ms[-1] - 0.01), (0.5 * (a.zlo + a.zhi), 0.5 * (a.mlo + a.mhi))):
+        for x, y in zip(a.get_bzm(z, m), b.get_bzm(z, m)):
+            assert x.shape == y.shape and np.array_equal(ma.filled(x, -1), ma.filled(y, -1))
     with pytest.raises(UserWarning):
         a.get_bzm(9.0, 25.0)
 

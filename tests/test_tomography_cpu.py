@@ -19,6 +19,25 @@ def test_background_distance_equals_quad():
     assert abs(tm.omega_hdm(0.06, 0.69) - 0.06 / 93.14 / 0.69 ** 2) < 1e-18
 
 
+def test_growth_rate_closed_form_and_fsigma8_propagation():
+    """f = d ln D / d ln a from the growth table's closed form against the numerical derivative of the same table (1e-6) and the
+    Omega_m(a)^0.55 approximation (1 % in LCDM); with sigma8 the only cosmological parameter, f sigma8 is proportional to it and the
+    propagated relative error equals sigma(sigma8) / sigma8."""
+    from lbgcmb_b200 import tomography as tm
+    c = tm.Background(M=0.292, B=0.0468, sig8=0.819)                   # host Romberg growth table (no device)
+    z = np.array([0.1, 0.5, 1., 2., 4.])
+    a = 1. / (1. + z)
+    f = tm.growth_rate(c, z)
+    h = 1e-4
+    num = (np.log(c.Dplus(a * np.exp(h))) - np.log(c.Dplus(a * np.exp(-h)))) / (2. * h)
+    assert np.max(np.abs(num / f - 1)) < 1e-6
+    assert np.max(np.abs(f / c.OmegaMa(z=z) ** 0.55 - 1)) < 1e-2
+    assert np.allclose(tm.fsigma8(c, z), f * 0.819 * c.Dgrow(z=z), rtol=1e-15)
+    result = {'params': ['sig8', 'b_x'], 'fiducial': dict(tm.FIDUCIAL), 'cov': np.array([[4e-6, 1e-7], [1e-7, 9e-6]])}
+    r = tm.fsigma8_forecast(result, z, growth='host')
+    assert np.max(np.abs(r['sigma'] / r['fsigma8'] - 2e-3 / 0.819)) < 1e-12 and np.all(r['jacobian'][:, 1] == 0.0)
+
+
 # ---- sharding logic of tomographic_fisher over gloo (world sizes 2 and 3); the device calls are replaced by numpy stand-ins ----------
 import os
 import sys

@@ -146,3 +146,21 @@ def test_spectra_sets_entry_points(ctx):
         fisher.field_fisher_sets(nf, spectra, n_ell, 3, 6, [(4, 5, 0.0)], amp, w)
     with pytest.raises(ValueError):
         fisher.spectra_set_get(6, ns - 1, 2, n_ell)
+
+
+def test_fsigma8_derived_errors(ctx):
+    """f sigma8(z) errors propagated from the (sig8, M) block of the forecast: positive, finite, and with device growth tables equal to
+    the host-table route; sigma8-only forecasts give sigma(f sigma8) / f sigma8 = sigma(sig8) / sig8."""
+    from lbgcmb_b200 import tomography as tm
+    nm = np.ones_like(ELL)
+    nkk = 2e-8 * np.ones_like(ELL)
+    zs = np.array([0.5, 1.0, 2.0, 3.0])
+    r = tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, cosmo_params=('sig8', 'M'))
+    d = tm.fsigma8_forecast(r, zs)
+    assert d['sigma'].shape == (4,) and np.all(d['sigma'] > 0) and np.all(np.isfinite(d['sigma']))
+    assert np.all(d['jacobian'][:, 2:] == 0.0) and np.all(d['jacobian'][:, 0] > 0)
+    h = tm.fsigma8_forecast(r, zs[:2], growth='host')
+    assert np.max(np.abs(h['fsigma8'] / d['fsigma8'][:2] - 1)) < 1e-9 and np.max(np.abs(h['sigma'] / d['sigma'][:2] - 1)) < 1e-6
+    r1 = tm.tomographic_fisher(_tracers(), ELL, nm, 0.4, nkk, cosmo_params=('sig8',))
+    d1 = tm.fsigma8_forecast(r1, zs)
+    assert np.max(np.abs(d1['sigma'] / d1['fsigma8'] - r1['sigma'][0] / tm.FIDUCIAL['sig8'])) < 1e-10
