@@ -21,15 +21,19 @@
 
 namespace lbg {
 #define HF_MAX_R 512
-#define HF_WARPS 8
-// One WARP per redshift, eight redshifts per block.  The factorisation (rotations 48 KB, band 24 KB, knots, intervals, sigma_0^2) is
-// staged in shared memory once per block: the fit is one long dependent chain per redshift, so what matters is the latency of every
-// operand it touches (one thread per redshift reading the rotations through L2: 650 us for 4000 redshifts; from shared memory with the
-// six pairs of a data point fetched ahead of the chain: 360 us).  The warp's lanes take the logarithms y_i = ln(D^2 sigma_0^2(R_i)) in
-// parallel; lane 0 then runs fitpack::fit_apply's statements in their order: the six rows a data point rotates into, and the five
-// coefficients a back-substitution row reads, live in a register window that slides with the knot interval (the rows leaving it are
-// final); of the coefficients only the six the derivative needs are kept.
-__global__ void __launch_bounds__(32 * HF_WARPS)
+#define HF_T 32          // redshifts per block: one per lane of warp 0
+#define HF_THREADS 256   // the other warps help with staging and the logarithms
+// One LANE per redshift, 32 redshifts per block, one block per SM.  The fit is one long dependent chain per redshift (3000 plane
+// rotations of the right-hand side, then 500 back-substitution rows with a division each): its time is the latency of the chain, so
+// every chain of the call has to be in flight at once.  The control flow of fitpack::fit_apply depends on the abscissae only -- the
+// same for every redshift -- so 32 redshifts run in lock step on the lanes of ONE warp at the price of one (a warp per redshift, eight
+// per block, needed four waves of blocks for the 4000 redshifts of a forecast: 360 us; this layout needs one).  The factorisation
+// (rotations 48 KB, band 24 KB, knots, intervals, sigma_0^2) is staged in shared memory once per block and read by broadcast; the
+// right-hand sides live there node-major, y[i][lane] (conflict-free), 4 KB per redshift.  All threads take the logarithms
+// y_i = ln(D^2 sigma_0^2(R_i)); warp 0 then runs fit_apply's statements in their order: the six rows a data point rotates into, and
+// the five coefficients a back-substitution row reads, live in a register window that slides with the knot interval (the rows leaving
+// it are final); of the coefficients only the six the derivative needs are kept.
+__global__ void __launch_bounds__(HF_THREADS)
 halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const double* __restrict__ tk_g, const int* __restrict__ lint_g,
                     const double* __restrict__ rot_g, const double* __restrict__ band_g, const double* __restrict__ inv_t, const double* __restrict__ inv_c,
                     double lo, double hi, double lnr0, double lnr1, const double* __restrict__ in /*[n][4]: D2, omz, ovz, use*/,
@@ -40,54 +44,96 @@ halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const doub
     double* band = rot + 12 * (size_t)m;             // [m][K1]
     double* tk = band + 6 * (size_t)m;               // [m + K1]
     double* s0s = tk + (m + K1);                     // [m]
-    double* yz = s0s + m;                            // [HF_WARPS][m]: y, then z in place
-    int* lint = reinterpret_cast<int*>(yz + (size_t)HF_WARPS * m);   // [m]
-    for (int i = threadIdx.x; i < 12 * m; i += blockDim.x) rot[i] = rot_g[i];
+    double* rinv = s0s + m;                          // [m]: RN(1 / band[i][0]) for the divisions of the back-substitution
+    double* yz = rinv + m;                           // [m][HF_T]: y, then z in place
+    int* lint = reinterpret_cast<int*>(yz + (size_t)HF_T * m);   // [m]
+    __shared__ double sD2[HF_T];
+    __shared__ int suse[HF_T];
+    __shared__ int sreg[2];
+    for (int i = threadIdx.x; i < 12 * m; i += blockDim.x) { const double v = rot_g[i]; rot[i] = (!(i & 1) && v > 1.5) ? 1.0 : v; }   // skipped rotation -> identity
     for (int i = threadIdx.x; i < 6 * m; i += blockDim.x) band[i] = band_g[i];
+    for (int i = threadIdx.x; i < m; i += blockDim.x) rinv[i] = __drcp_rn(band_g[(size_t)i * K1]);
     for (int i = threadIdx.x; i < m + K1; i += blockDim.x) tk[i] = tk_g[i];
     for (int i = threadIdx.x; i < m; i += blockDim.x) { s0s[i] = s0[i]; lint[i] = lint_g[i]; }
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int r = blockIdx.x * HF_WARPS + warp;
-    if (r >= n_rows) return;
-    const double* q = in + (size_t)r * 4;
+    const int lane = threadIdx.x;                    // meaningful for warp 0 only
+    const int r = blockIdx.x * HF_T + lane;
+    const bool mine = threadIdx.x < HF_T && r < n_rows;
     HaloZ h;
-    h.D2 = q[0]; h.rknl = 1.0; h.neff = 0.0; h.ncur = 0.0; h.omz = q[1]; h.ovz = q[2]; h.use_halofit = q[3]; h.pad = 0.0;
     double rknl = 1.0, x = 0.0;
-    if (q[3] != 0.0) {                               // warp-uniform
-        // R_nl from the z = 0 inverse fit at -ln D^2 (modi/halofit.py:71-72 with the abscissae shifted by ln D^2)
-        const double tt = -log(q[0]);
-        const double lnR = splev(inv_t, m + K1, inv_c, tt);
-        rknl = 1.0 / exp(lnR);
-        x = log(1.0 / rknl);
-        if (!(tt > lo && tt < hi && lnR > lnr0 && lnR < lnr1)) {       // outside the tabulated decade: the caller's exception path
-            h.use_halofit = 0.0; h.pad = 1.0; h.rknl = rknl;
-            if (lane == 0) atomicAdd(n_flagged, 1);
+    if (threadIdx.x < HF_T) { sD2[lane] = 1.0; suse[lane] = 0; }
+    if (mine) {
+        const double* q = in + (size_t)r * 4;
+        h.D2 = q[0]; h.rknl = 1.0; h.neff = 0.0; h.ncur = 0.0; h.omz = q[1]; h.ovz = q[2]; h.use_halofit = q[3]; h.pad = 0.0;
+        if (q[3] != 0.0) {
+            // R_nl from the z = 0 inverse fit at -ln D^2 (modi/halofit.py:71-72 with the abscissae shifted by ln D^2)
+            const double tt = -log(q[0]);
+            const double lnR = splev(inv_t, m + K1, inv_c, tt);
+            rknl = 1.0 / exp(lnR);
+            x = log(1.0 / rknl);
+            if (!(tt > lo && tt < hi && lnR > lnr0 && lnR < lnr1)) {       // outside the tabulated decade: the caller's exception path
+                h.use_halofit = 0.0; h.pad = 1.0; h.rknl = rknl;
+                atomicAdd(n_flagged, 1);
+            }
         }
+        sD2[lane] = q[0];
+        suse[lane] = h.use_halofit != 0.0;
     }
-    if (h.use_halofit != 0.0) {
-        double* y = yz + (size_t)warp * m;
-        const double D2 = q[0];
-        for (int i = lane; i < m; i += 32) y[i] = log(D2 * s0s[i]);
-        __syncwarp();
-      if (lane == 0) {
+    __syncthreads();
+    if (threadIdx.x == HF_T) {                       // [sreg[0], sreg[1]): the data points that move the row window by exactly one
+        int lo = 1;
+        while (lo < m && lint[lo] != lint[lo - 1] + 1) ++lo;
+        int hi = lo;
+        while (hi < m && lint[hi] == lint[hi - 1] + 1) ++hi;
+        sreg[0] = lo; sreg[1] = hi;
+    }
+    for (int e = threadIdx.x; e < m * HF_T; e += blockDim.x) {              // y[i][t] = ln(D2_t sigma_0^2(R_i)), every thread of the block
+        const int t = e & (HF_T - 1), i = e / HF_T;
+        if (suse[t]) yz[e] = log(sD2[t] * s0s[i]);
+    }
+    __syncthreads();
+    if (threadIdx.x >= HF_T) return;
+    if (mine && h.use_halofit != 0.0) {
+        double* y = yz + lane;                       // element i at y[i * HF_T]
+      {
         const int nk1 = m;
-        double* z = y;                               // z[base] is written after y[base] was consumed (base <= it)
+        double* z = y;                               // z[base] is written after y[base] was consumed (base <= it); same stride
         // ---- right-hand side through the rotations (fpcurf) ----
+        // The operands of the NEXT data point (its right-hand side and six rotation pairs) are fetched before the chain of the current
+        // one starts: issue is in order, so a load placed after the chain would wait for it and add its latency to every point.
+        // Between points sreg[0] and sreg[1] every point moves the six-row window by exactly one row (interior of the knot vector):
+        // those go six at a time with the window registers renamed instead of shifted.  Rotations fpcurf skips (zero pivot) were staged
+        // as (cos, sin) = (1, 0), which leaves both operands as they are.
         double w0 = 0, w1 = 0, w2 = 0, w3 = 0, w4 = 0, w5 = 0;       // z[base .. base + 5]
         int base = lint[0] - K1;
-        for (int it = 0; it < m; ++it) {
-            const int l = lint[it];
-            double yi = y[it];
-            const double2* rp = reinterpret_cast<const double2*>(rot) + (size_t)it * K1;
-            const double2 r0 = rp[0], r1 = rp[1], r2 = rp[2], r3 = rp[3], r4 = rp[4], r5 = rp[5];   // fetched ahead of the chain
-            while (base < l - K1) { z[base] = w0; w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; w5 = 0.0; ++base; }
-#define LBG_ROT(W, CS) { if (!(CS.x > 1.5)) { const double s1 = yi, s2 = W; \
-                        W = add(mul(CS.x, s2), mul(CS.y, s1)); yi = sub(mul(CS.x, s1), mul(CS.y, s2)); } }
-            LBG_ROT(w0, r0) LBG_ROT(w1, r1) LBG_ROT(w2, r2) LBG_ROT(w3, r3) LBG_ROT(w4, r4) LBG_ROT(w5, r5)
-#undef LBG_ROT
+        const double2* rp = reinterpret_cast<const double2*>(rot);
+        double yn = y[0], yi;
+        double2 n0 = rp[0], n1 = rp[1], n2 = rp[2], n3 = rp[3], n4 = rp[4], n5 = rp[5];
+        double2 r0, r1, r2, r3, r4, r5;
+#define LBG_ROT(W, CS) { const double s1 = yi, s2 = W; W = add(mul(CS.x, s2), mul(CS.y, s1)); yi = sub(mul(CS.x, s1), mul(CS.y, s2)); }
+#define LBG_TAKE(NEXT) { yi = yn; r0 = n0; r1 = n1; r2 = n2; r3 = n3; r4 = n4; r5 = n5; \
+                         if ((NEXT) < m) { const double2* q2 = rp + (size_t)(NEXT) * K1; yn = y[(size_t)(NEXT) * HF_T]; \
+                                           n0 = q2[0]; n1 = q2[1]; n2 = q2[2]; n3 = q2[3]; n4 = q2[4]; n5 = q2[5]; } }
+#define LBG_GENERIC(IT) { const int l = lint[IT]; LBG_TAKE((IT) + 1) \
+                          while (base < l - K1) { z[(size_t)base * HF_T] = w0; w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; w5 = 0.0; ++base; } \
+                          LBG_ROT(w0, r0) LBG_ROT(w1, r1) LBG_ROT(w2, r2) LBG_ROT(w3, r3) LBG_ROT(w4, r4) LBG_ROT(w5, r5) }
+#define LBG_STEP(A, B, C, D, E, F, NEXT) { LBG_TAKE(NEXT) z[(size_t)base * HF_T] = A; A = 0.0; ++base; \
+                          LBG_ROT(B, r0) LBG_ROT(C, r1) LBG_ROT(D, r2) LBG_ROT(E, r3) LBG_ROT(F, r4) LBG_ROT(A, r5) }
+        int it = 0;
+        const int reg_lo = sreg[0], reg_hi = sreg[1];
+        for (; it < reg_lo; ++it) LBG_GENERIC(it)
+#pragma unroll 1
+        for (; it + 6 <= reg_hi; it += 6) {
+            LBG_STEP(w0, w1, w2, w3, w4, w5, it + 1) LBG_STEP(w1, w2, w3, w4, w5, w0, it + 2) LBG_STEP(w2, w3, w4, w5, w0, w1, it + 3)
+            LBG_STEP(w3, w4, w5, w0, w1, w2, it + 4) LBG_STEP(w4, w5, w0, w1, w2, w3, it + 5) LBG_STEP(w5, w0, w1, w2, w3, w4, it + 6)
         }
-        z[base] = w0; z[base + 1] = w1; z[base + 2] = w2; z[base + 3] = w3; z[base + 4] = w4; z[base + 5] = w5;
+#pragma unroll 1
+        for (; it < m; ++it) LBG_GENERIC(it)
+#undef LBG_STEP
+#undef LBG_GENERIC
+#undef LBG_TAKE
+#undef LBG_ROT
+        z[(size_t)base * HF_T] = w0; z[(size_t)(base + 1) * HF_T] = w1; z[(size_t)(base + 2) * HF_T] = w2;
+        z[(size_t)(base + 3) * HF_T] = w3; z[(size_t)(base + 4) * HF_T] = w4; z[(size_t)(base + 5) * HF_T] = w5;
         // ---- interval of the derivative point (spalde) ----
         bool ok = !(x < tk[K1 - 1] || x > tk[nk1]);
         int l = K1;
@@ -95,25 +141,39 @@ halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const doub
         ok = ok && tk[l - 1] < tk[l];
         const int lk = l - K1;                                        // coefficients c[lk .. lk + 5] (0-based) are needed
         // ---- back-substitution (fpback), window c[i+1 .. i+5] ----
-        double c1 = 0, c2 = 0, c3 = 0, c4 = 0, c5 = 0, keep[K1] = {0, 0, 0, 0, 0, 0};
-        for (int i = nk1 - 1; i >= 0; --i) {                          // 0-based row
-            const double* ar = band + (size_t)i * K1;
-            const double a0 = ar[0], a1 = ar[1], a2 = ar[2], a3 = ar[3], a4 = ar[4], a5 = ar[5];
-            double store = z[i];
-            const int avail = nk1 - 1 - i;                            // coefficients above this row that exist (i1 of fpback = min(5, avail))
+        // store / a0 is taken as the correctly rounded quotient from the correctly rounded reciprocal y = RN(1 / a0) (Markstein: q0 = RN(store y),
+        // two exact-remainder corrections r = fma(-a0, q, store), q <- fma(r, y, q); the second starts from a faithful q and returns
+        // RN(store / a0), the result of the reference's division; tests/test_fitpack_cpu.py) -- 5 dependent operations instead of the ~15
+        // of the division sequence, which sits on the chain of every row.  Row i - 1 is fetched before row i's chain, as above; c_i
+        // overwrites z_i (read for the last time by its own row) and the six coefficients the derivative needs are read back afterwards.
+        double c1 = 0, c2 = 0, c3 = 0, c4 = 0, c5 = 0, keep[K1];
+        const double* ar = band + (size_t)(nk1 - 1) * K1;
+        double a1n = ar[1], a2n = ar[2], a3n = ar[3], a4n = ar[4], a5n = ar[5], a0n = ar[0], rvn = rinv[nk1 - 1], zn = z[(size_t)(nk1 - 1) * HF_T];
+        double a0, a1, a2, a3, a4, a5, rv, store;
+#define LBG_ROW(I) { a0 = a0n; a1 = a1n; a2 = a2n; a3 = a3n; a4 = a4n; a5 = a5n; rv = rvn; store = zn; \
+                     if ((I) > 0) { const double* an = band + (size_t)((I) - 1) * K1; a0n = an[0]; a1n = an[1]; a2n = an[2]; a3n = an[3]; \
+                                    a4n = an[4]; a5n = an[5]; rvn = rinv[(I) - 1]; zn = z[(size_t)((I) - 1) * HF_T]; } }
+#define LBG_QUOT(I) { double ci = __dmul_rn(store, rv); ci = __fma_rn(__fma_rn(-a0, ci, store), rv, ci); ci = __fma_rn(__fma_rn(-a0, ci, store), rv, ci); \
+                      z[(size_t)(I) * HF_T] = ci; c5 = c4; c4 = c3; c3 = c2; c2 = c1; c1 = ci; }
+        int i = nk1 - 1;
+        for (; i >= 0 && i > nk1 - 1 - (K1 - 1); --i) {               // the first rows have fewer than five coefficients above them
+            LBG_ROW(i)
+            const int avail = nk1 - 1 - i;                            // i1 of fpback = min(5, avail)
             if (avail >= 1) store = sub(store, mul(c1, a1));
             if (avail >= 2) store = sub(store, mul(c2, a2));
             if (avail >= 3) store = sub(store, mul(c3, a3));
             if (avail >= 4) store = sub(store, mul(c4, a4));
-            if (avail >= 5) store = sub(store, mul(c5, a5));
-            const double ci = dvd(store, a0);
-            c5 = c4; c4 = c3; c3 = c2; c2 = c1; c1 = ci;
-            const int rel = i - lk;
-            if (rel >= 0 && rel < K1) {
-#pragma unroll
-                for (int e = 0; e < K1; ++e) if (e == rel) keep[e] = ci;
-            }
+            LBG_QUOT(i)
         }
+#pragma unroll 2
+        for (; i >= 0; --i) {
+            LBG_ROW(i)
+            store = sub(sub(sub(sub(sub(store, mul(c1, a1)), mul(c2, a2)), mul(c3, a3)), mul(c4, a4)), mul(c5, a5));
+            LBG_QUOT(i)
+        }
+#undef LBG_QUOT
+#undef LBG_ROW
+        for (int e = 0; e < K1; ++e) keep[e] = z[(size_t)(lk + e) * HF_T];
         // ---- derivatives at x (fpader on the six kept coefficients: spalde with the interval found above) ----
         double d[K1] = {0, 0, 0, 0, 0, 0};
         if (ok) {
@@ -154,7 +214,7 @@ halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const doub
         h.ncur = ok ? -d[2] : nan("");
       }
     }
-    if (lane == 0) rows[r] = h;
+    if (mine) rows[r] = h;
 }
 }  // namespace lbg
 
@@ -393,14 +453,14 @@ extern "C" int lbg_pk_build_tables_hf(lbg_ctx* c, int n_tables, const int* n_row
     LBG_CUDA(cudaMemcpyAsync(H.zin.p, H.pin_in.p, in_bytes, cudaMemcpyHostToDevice, st));
     int* d_flag = reinterpret_cast<int*>(H.zin.as<unsigned char>() + in_bytes);
     LBG_CUDA(cudaMemsetAsync(d_flag, 0, 4, st));
-    const size_t hsmem = (12 * (size_t)m + 6 * (size_t)m + (m + 6) + m + (size_t)HF_WARPS * m) * 8 + (size_t)m * 4;
+    const size_t hsmem = (12 * (size_t)m + 6 * (size_t)m + (m + 6) + 2 * (size_t)m + (size_t)HF_T * m) * 8 + (size_t)m * 4;
     static bool attr_set = false;                  // the attribute is per function, not per device context
     if (!attr_set) {
         LBG_CUDA(cudaFuncSetAttribute(halofit_spec_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)((28 * (size_t)HF_MAX_R + 6) * 8 + HF_MAX_R * 4)));
+                                      (int)(((21 + HF_T) * (size_t)HF_MAX_R + 6) * 8 + HF_MAX_R * 4)));
         attr_set = true;
     }
-    halofit_spec_kernel<<<(n_rows + HF_WARPS - 1) / HF_WARPS, 32 * HF_WARPS, hsmem, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, d_inv, d_inv + (m + 6),
+    halofit_spec_kernel<<<(n_rows + HF_T - 1) / HF_T, HF_THREADS, hsmem, st>>>(n_rows, m, d_s0, d_t, d_lint, d_rot, d_band, d_inv, d_inv + (m + 6),
                                                            H.lns0_rev[0], H.lns0_rev[m - 1], lnr[0], lnr[m - 1], H.zin.as<double>(),
                                                            H.rows.as<HaloZ>(), d_flag);
     ++launches;

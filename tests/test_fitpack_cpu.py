@@ -44,3 +44,44 @@ def test_reference_spec_from_reference_sigma2(golden_dir):
         lnsig = np.array([np.log(simps(delta * np.exp(-(k * np.exp(r)) ** 2), lnk)) for r in lnr])
         got = np.array(spec_from_lnsig(lnr, lnsig))
         assert np.allclose(got, g['spec'][i], rtol=1e-14, atol=0), (i, got, g['spec'][i])
+
+
+def test_quotient_from_rounded_reciprocal_is_correctly_rounded():
+    """halofit_spec_kernel's back-substitution replaces store / a0 by q0 = RN(store y), q <- fma(fma(-a0, q, store), y, q) twice, with
+    y = RN(1 / a0) (csrc/halofit.cu): the claim is that this IS RN(store / a0), the reference's division.  Checked here with libm's fma
+    on random and adversarial operands (mantissas near all-ones / near a power of two / short: ties and exact quotients); the same
+    loop over 4e8 pairs in C found no mismatch either."""
+    import ctypes
+    import ctypes.util
+    libm = ctypes.CDLL(ctypes.util.find_library('m'))
+    libm.fma.restype = ctypes.c_double
+    libm.fma.argtypes = [ctypes.c_double] * 3
+    fma = libm.fma
+    rng = np.random.default_rng(11)
+    n = 60000
+
+    def mant(kind, size):
+        m = rng.integers(0, 1 << 52, size, dtype=np.uint64)
+        if kind == 1:
+            m = (np.uint64((1 << 52) - 1) - rng.integers(0, 256, size, dtype=np.uint64))
+        elif kind == 2:
+            m = rng.integers(0, 256, size, dtype=np.uint64)
+        elif kind == 3:
+            m = rng.integers(0, 1 << 20, size, dtype=np.uint64) << np.uint64(32)
+        return m
+
+    bad = 0
+    for ka in range(4):
+        for kb in range(4):
+            ea = rng.integers(-20, 20, n // 16).astype(np.uint64) + np.uint64(1023)
+            eb = rng.integers(-20, 20, n // 16).astype(np.uint64) + np.uint64(1023)
+            a = ((ea << np.uint64(52)) | mant(ka, n // 16)).view(np.float64) * rng.choice([-1., 1.], n // 16)
+            b = ((eb << np.uint64(52)) | mant(kb, n // 16)).view(np.float64)
+            y = 1.0 / b
+            want = a / b
+            for ai, bi, yi, wi in zip(a.tolist(), b.tolist(), y.tolist(), want.tolist()):
+                q = ai * yi
+                q = fma(fma(-bi, q, ai), yi, q)
+                q = fma(fma(-bi, q, ai), yi, q)
+                bad += q != wi
+    assert bad == 0
