@@ -98,44 +98,68 @@ struct HaloZ {           // per-redshift HALOFIT inputs (modi/halofit.py:139-199
 
 struct HaloConst { double fnu, om0, w; int takahashi; };
 
-// One thread per (z, k) table node: P_nl(k, z) [(Mpc/h)^3] from Delta_lin^2 = P0 k^3 D^2 / (2 pi^2).
+// One thread per (z, k) table node: P_nl(k, z) [(Mpc/h)^3] from Delta_lin^2 = P0 k^3 D^2 / (2 pi^2).  A block works on ONE redshift
+// (blockIdx.y), and ten of the fourteen pow() calls of the formula depend on the redshift only: the first warp takes them in one
+// call -- lane i its own (base, exponent) pair, no divergence -- and leaves them in shared memory; a node then costs four pow + one exp.
 static __global__ void pnl_kernel(int n_z, int n_k, const double* __restrict__ k, const double* __restrict__ p0,
                            const HaloZ* __restrict__ hz, HaloConst hc, double* __restrict__ out) {
     const int ik = blockIdx.x * blockDim.x + threadIdx.x;
     const int iz = blockIdx.y;
-    if (ik >= n_k) return;
+    __shared__ double pw[16];
     const HaloZ h = hz[iz];
+    const double neff = h.neff, rncur = h.ncur, w = hc.w, fnu = hc.fnu;
+    const double n2 = neff * neff, n3 = n2 * neff, n4 = n2 * n2;
+    const bool nl = h.use_halofit != 0.0;                                 // block-uniform
+    if (nl && threadIdx.x < 11) {
+        double base = 10.0, ex = 0.0;
+        if (hc.takahashi) {                                               // modi/halofit.py:152-166
+            switch (threadIdx.x) {
+                case 0: ex = 1.5222 + 2.8553 * neff + 2.3706 * n2 + 0.9903 * n3 + 0.2250 * n4 - 0.6038 * rncur + 0.1749 * h.ovz * (1 + w); break;
+                case 1: ex = -0.5642 + 0.5864 * neff + 0.5716 * n2 - 1.5474 * rncur + 0.2279 * h.ovz * (1 + w); break;
+                case 2: ex = 0.3698 + 2.0404 * neff + 0.8161 * n2 + 0.5869 * rncur; break;
+                case 3: ex = 5.2105 + 3.6902 * neff; break;
+                default: break;
+            }
+        } else {                                                          // modi/halofit.py:168-180 (Smith+03)
+            switch (threadIdx.x) {
+                case 0: ex = 1.4861 + 1.8369 * neff + 1.6762 * n2 + 0.7940 * n3 + 0.1670 * n4 - 0.6206 * rncur; break;
+                case 1: ex = 0.9463 + 0.9466 * neff + 0.3084 * n2 - 0.94 * rncur; break;
+                case 2: ex = -0.2807 + 0.6669 * neff + 0.3214 * n2 - 0.0793 * rncur; break;
+                case 3: ex = 0.9589 + 1.2857 * neff; break;
+                case 4: ex = -3.5442 + 0.1908 * neff; break;
+                default: break;
+            }
+        }
+        if (threadIdx.x >= 5) {                                           // modi/halofit.py:183-199: f1a f2a f3a f1b f2b f3b
+            const double fe[6] = {-0.0732, -0.1423, 0.0725, -0.0307, -0.0585, 0.0743};
+            base = h.omz;
+            ex = fe[threadIdx.x - 5];
+        }
+        pw[threadIdx.x] = pow(base, ex);                                  // the exponents were plain arithmetic: one pow for the warp
+    }
+    __syncthreads();
+    if (ik >= n_k) return;
     const double kk = k[ik];
     const double twopi2 = 2.0 * 3.14159265358979323846 * 3.14159265358979323846;
     const double plin_dim = p0[ik] * (kk * kk * kk) / twopi2 * h.D2;     // modi/cosmology.py:174-175
     double res = plin_dim;
-    if (h.use_halofit != 0.0 && kk > 0.005) {                             // modi/halofit.py:139
-        const double neff = h.neff, rncur = h.ncur, w = hc.w, fnu = hc.fnu;
-        const double n2 = neff * neff, n3 = n2 * neff, n4 = n2 * n2;
-        double a, b, c, gam, alpha, beta, xmu, xnu;
-        if (hc.takahashi) {                                               // modi/halofit.py:152-166
-            a = pow(10.0, 1.5222 + 2.8553 * neff + 2.3706 * n2 + 0.9903 * n3 + 0.2250 * n4 - 0.6038 * rncur + 0.1749 * h.ovz * (1 + w));
-            b = pow(10.0, -0.5642 + 0.5864 * neff + 0.5716 * n2 - 1.5474 * rncur + 0.2279 * h.ovz * (1 + w));
-            c = pow(10.0, 0.3698 + 2.0404 * neff + 0.8161 * n2 + 0.5869 * rncur);
+    if (nl && kk > 0.005) {                                               // modi/halofit.py:139
+        const double a = pw[0], b = pw[1], c = pw[2], xnu = pw[3];
+        double gam, alpha, beta, xmu;
+        if (hc.takahashi) {
             gam = 0.1971 - 0.0843 * neff + 0.8460 * rncur;
             alpha = fabs(6.0835 + 1.3373 * neff - 0.1959 * n2 - 5.5274 * rncur);
             beta = 2.0379 - 0.7354 * neff + 0.3157 * n2 + 1.2490 * n3 + 0.3980 * n4 - 0.1682 * rncur + fnu * (1.081 + 0.395 * n2);
             xmu = 0.0;
-            xnu = pow(10.0, 5.2105 + 3.6902 * neff);
-        } else {                                                          // modi/halofit.py:168-180 (Smith+03)
-            a = pow(10.0, 1.4861 + 1.8369 * neff + 1.6762 * n2 + 0.7940 * n3 + 0.1670 * n4 - 0.6206 * rncur);
-            b = pow(10.0, 0.9463 + 0.9466 * neff + 0.3084 * n2 - 0.94 * rncur);
-            c = pow(10.0, -0.2807 + 0.6669 * neff + 0.3214 * n2 - 0.0793 * rncur);
+        } else {
             gam = 0.8649 + 0.2989 * neff + 0.1631 * rncur;
             alpha = fabs(1.3884 + 0.3700 * neff - 0.1452 * n2);
             beta = 0.8291 + 0.9854 * neff + 0.3401 * n2;
-            xmu = pow(10.0, -3.5442 + 0.1908 * neff);
-            xnu = pow(10.0, 0.9589 + 1.2857 * neff);
+            xmu = pw[4];
         }
         double f1 = 1.0, f2 = 1.0, f3 = 1.0;
         if (fabs(1 - h.omz) > 0.01) {                                     // modi/halofit.py:183-199
-            const double f1a = pow(h.omz, -0.0732), f2a = pow(h.omz, -0.1423), f3a = pow(h.omz, 0.0725);
-            const double f1b = pow(h.omz, -0.0307), f2b = pow(h.omz, -0.0585), f3b = pow(h.omz, 0.0743);
+            const double f1a = pw[5], f2a = pw[6], f3a = pw[7], f1b = pw[8], f2b = pw[9], f3b = pw[10];
             const double frac = h.ovz / (1 - h.omz);
             if (hc.takahashi) { f1 = f1b; f2 = f2b; f3 = f3b; }
             else { f1 = frac * f1b + (1 - frac) * f1a; f2 = frac * f2b + (1 - frac) * f2a; f3 = frac * f3b + (1 - frac) * f3a; }

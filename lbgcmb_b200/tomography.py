@@ -46,12 +46,16 @@ def omega_hdm(mnu, h):
 
 def make_cosmology(theta, Dplus_table='device', k=None, device=None):
     """modi Cosmology for the parameter dict `theta` (keys of FIDUCIAL) with its linear table built on the device by the E-H fit,
-    sigma8-normalised (so sigma8 is a parameter in its own right and the other ones move the shape at fixed sigma8)."""
+    sigma8-normalised (so sigma8 is a parameter in its own right and the other ones move the shape at fixed sigma8).
+    sum m_nu enters through the z = 0 transfer-function shape (T_cb+nu) and HALOFIT's f_nu terms; the growth factor stays the
+    scale-independent LCDM one ("sum m_nu limitation")."""
     k = K_GRID if k is None else np.asarray(k, dtype=np.float64)
     M, h = theta['M'], theta['h']
     plin = eisenstein_hu.linear_power(k, M, theta['B'], 1. - M, h, theta['ns'], theta['sig8'], omega_hdm=omega_hdm(theta['mnu'], h),
                                       degen_hdm=1, device=device)
-    return Background(M=M, B=theta['B'], sig8=theta['sig8'], klin=k, plin=plin, device=device, Dplus_table=Dplus_table)
+    c = Background(M=M, B=theta['B'], sig8=theta['sig8'], klin=k, plin=plin, device=device, Dplus_table=Dplus_table)
+    c.cosmo.Onu0 = omega_hdm(theta['mnu'], h)        # f_nu = Onu0 / Om0 of HALOFIT's neutrino terms (modi/halofit.py:149,164,204-206)
+    return c
 
 
 def field_spectra(cosmo, ell, tracers, nodes_per_bin=10, nonlinear=True, kk=True, geometry=None, keep_set=None):

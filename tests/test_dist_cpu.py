@@ -34,7 +34,17 @@ def _worker(rank, world, port, q):
     F2, b2 = ld.fisher_accum_sharded(cov, dD, w, accum=_numpy_accum)
     lo, hi = ld.shard_slice(len(w))
     curve = ld.allgather_concat(w[lo:hi] * 2.0)
-    q.put((rank, F, b, F2, b2 is None, (lo, hi), curve))
+    # cyclic shards: the one-round-trip exchange and the gather that a sharded forecast enqueues before its N0 join
+    n = 11
+    mine = ld.shard_indices(n)
+    full = np.arange(3 * n, dtype=np.float64).reshape(3, n) + 0.5
+    sums, curves, ms = ld.exchange(np.array([1.0 + rank, 10.0]), full[:, mine], n)
+    g = ld.gather_begin(full[1:, mine] * 3.0, n)
+    early, gms = g.finish()
+    empty, _ = ld.gather_begin(np.zeros((2, 0)), 0).finish()
+    ok = (np.array_equal(sums, [3.0, 20.0]) and np.array_equal(curves, full) and ms is None and np.array_equal(early, full[1:] * 3.0)
+          and gms is None and g.finish()[0] is early and empty.shape == (2, 0))
+    q.put((rank, F, b, F2, b2 is None, (lo, hi), curve, ok))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -72,7 +82,8 @@ def test_fisher_allreduce_world2_gloo():
         assert p.exitcode == 0
     cov, dD, w, dl = _problem()
     Fr, br = _numpy_accum(cov, dD, w, dl)
-    for rank, F, b, F2, b2none, cut, curve in res:
+    for rank, F, b, F2, b2none, cut, curve, ok in res:
+        assert ok
         assert np.allclose(F, Fr, rtol=1e-13) and np.allclose(b, br, rtol=1e-12)
         assert np.allclose(F2, Fr, rtol=1e-13) and b2none
         assert np.array_equal(curve, w * 2.0)
