@@ -497,8 +497,7 @@ def main():
             'config': {'workload': WORKLOAD % (cfg[0], cfg[1], a.lmin, a.lmax), 'n_L': int(Ls.size), 'call': 'lbgcmb_b200.sweep.sharded_forecast',
                        'phi_fold': True, 'nodes_walked_per_step': nodes_all, 'nodes_unmasked_per_step': unmasked_all,
                        'multi_gpu': ('ONE forecast per step, multipole grid sharded L[r::N]; one NCCL all-reduce of %d partial sums + one all-gather of '
-                                     '%d curves inside the timed region (in the overlapped e2e steps the %d spectra curves are gathered while the N0 shard still runs and only '
-                                     'the sums and the N0 curve cross after the join)' % (9 * n_band, 2 + 2 * n_band, 1 + 2 * n_band)) if world > 1 else 'single GPU',
+                                     '%d curves inside the timed region' % (9 * n_band, 2 + 2 * n_band)) if world > 1 else 'single GPU',
                        'cl_tables': 'handed over every step; the library compares them with its resident copy and re-solves / re-uploads only on change',
                        'pk_tables': 'linear P(k) uploaded and every P(k,z) row (3 z grids) rebuilt every step',
                        'l2': 'flushed between timed iterations (256 MB memset); tables are re-read from HBM each step'},

@@ -127,77 +127,6 @@ def exchange(sums, curves, n):
     return hout[:ns].reshape(sums.shape).copy(), out, ms
 
 
-class _Gather(object):
-    """An all-gather of curves in flight (gather_begin): finish() waits for it and returns ([n_curves, n], device ms or None)."""
-
-    def __init__(self, out=None, ms=None, buf=None, shape=None):
-        self._out, self._ms, self._buf, self._shape = out, ms, buf, shape
-
-    def finish(self):
-        if self._out is None:
-            h_out, e0, e1, done = self._buf
-            nc, width, world, n = self._shape
-            done.synchronize()
-            self._ms = e0.elapsed_time(e1)
-            self._out = _uncycle(h_out.numpy().reshape(world, nc, width), nc, n, world)
-            self._buf = None
-        return self._out, self._ms
-
-
-def _uncycle(parts, nc, n, world):
-    out = np.empty((nc, n))
-    for r in range(world):
-        m = len(range(r, n, world))
-        out[:, r::world] = parts[r, :, :m]
-    return out
-
-
-_gbuf = {}
-
-
-def gather_begin(curves, n):
-    """All-gather of this rank's cyclic shard of curves [n_curves, n_mine] into [n_curves, n], ENQUEUED and not waited for (NCCL:
-    pinned block -> device -> all_gather_into_tensor -> pinned block, all asynchronous on torch's stream; gloo / no group: done at
-    once).  A sharded forecast gathers the spectra, which do not depend on N0, while its N0 shard is still running, so that only
-    the sums and the N0 curve are exchanged after the join.  One gather per shape may be in flight."""
-    d = _dist()
-    curves = np.atleast_2d(np.ascontiguousarray(curves, dtype=np.float64))
-    if d is None or d.get_world_size() == 1:
-        return _Gather(out=curves.copy())
-    import torch
-    world = d.get_world_size()
-    width = (n + world - 1) // world
-    nc = curves.shape[0]
-    nccl = d.get_backend() == 'nccl'
-    if not nccl:
-        pad = torch.zeros(nc, width, dtype=torch.float64)
-        pad[:, :curves.shape[1]] = torch.from_numpy(curves)
-        out = torch.empty(world * nc * width, dtype=torch.float64)
-        d.all_gather_into_tensor(out, pad.reshape(-1))
-        return _Gather(out=_uncycle(out.numpy().reshape(world, nc, width), nc, n, world))
-    key = (nc, width, world)
-    buf = _gbuf.get(key)
-    if buf is None:
-        dev = torch.device('cuda', torch.cuda.current_device())
-        buf = (torch.empty(nc * width, dtype=torch.float64).pin_memory(), torch.empty(world * nc * width, dtype=torch.float64).pin_memory(),
-               torch.empty(nc * width, dtype=torch.float64, device=dev), torch.empty(world * nc * width, dtype=torch.float64, device=dev),
-               torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event())
-        if len(_gbuf) >= 4:
-            _gbuf.clear()
-        _gbuf[key] = buf
-    h_in, h_out, d_in, d_out, e0, e1, done = buf
-    pad = h_in.numpy().reshape(nc, width)
-    pad[:, :curves.shape[1]] = curves
-    pad[:, curves.shape[1]:] = 0.0
-    d_in.copy_(h_in, non_blocking=True)
-    e0.record()
-    d.all_gather_into_tensor(d_out, d_in)
-    e1.record()
-    h_out.copy_(d_out, non_blocking=True)
-    done.record()
-    return _Gather(buf=(h_out, e0, e1, done), shape=(nc, width, world, n))
-
-
 def allreduce_sum(*arrays):
     """Sum float64 numpy arrays over all ranks in one collective (packed); identity without a process group."""
     d = _dist()

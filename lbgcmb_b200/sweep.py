@@ -249,10 +249,6 @@ def sharded_forecast(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes,
     if grid_fn is None:
         grid_fn = forecast_grid
     smp = samples if xsamples is None else samples + xsamples
-    # overlapped product path: the spectra curves do not depend on N0, so their all-gather is enqueued before the N0 join and only
-    # the sums (one all-reduce) and the N0 curve cross after it.  The same on every rank, also on one without multipoles.
-    two_phase = n0_fn is None and overlap
-    early = None
     if have:
         if n0_fn is None:
             from lbgcmb_b200.Nkk import n0_begin
@@ -261,8 +257,6 @@ def sharded_forecast(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes,
             if not overlap:
                 call.result()
             ckk, cgg, ckg, ngg = spectra_fn(Lr, smp)
-            if two_phase:
-                early = _dist.gather_begin(np.concatenate([ckk[None, :], cgg[:n_b], ckg[:n_b]]), Ld.size)
             t1 = time.perf_counter()
             nkk = call.result()[0]
         else:
@@ -278,20 +272,13 @@ def sharded_forecast(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes,
         sums[:, 1:7] = part[:, 1:7]
         sums[:, 7] = ngg[:n_b]
         sums[:, 8] = 1.0
-        curves = nkk[None, :] if two_phase else np.concatenate([nkk[None, :], ckk[None, :], cgg[:n_b], ckg[:n_b]])
+        curves = np.concatenate([nkk[None, :], ckk[None, :], cgg[:n_b], ckg[:n_b]])
     else:                                                             # more ranks than multipoles
-        if two_phase:
-            early = _dist.gather_begin(np.zeros((1 + 2 * n_b, 0)), Ld.size)
         t1 = t2 = time.perf_counter()
         sums = np.zeros((n_b, 9))
-        curves = np.zeros((1 if two_phase else 2 + 2 * n_b, 0))
+        curves = np.zeros((2 + 2 * n_b, 0))
     t3 = time.perf_counter()
     sums, curves, xms = _dist.exchange(sums, curves, Ld.size)         # THE exchange step of the path: one all-reduce, one all-gather
-    if two_phase:
-        spec_curves, gms = early.finish()
-        curves = np.concatenate([curves, spec_curves])
-        if xms is not None and gms is not None:
-            xms += gms
     t4 = time.perf_counter()
     F = sums[:, 1:5].reshape(n_b, 2, 2)
     interim = sums[:, 5:7]

@@ -34,16 +34,12 @@ def _worker(rank, world, port, q):
     F2, b2 = ld.fisher_accum_sharded(cov, dD, w, accum=_numpy_accum)
     lo, hi = ld.shard_slice(len(w))
     curve = ld.allgather_concat(w[lo:hi] * 2.0)
-    # cyclic shards: the one-round-trip exchange and the gather that a sharded forecast enqueues before its N0 join
+    # cyclic shards: the one-round-trip exchange of a sharded forecast
     n = 11
     mine = ld.shard_indices(n)
     full = np.arange(3 * n, dtype=np.float64).reshape(3, n) + 0.5
     sums, curves, ms = ld.exchange(np.array([1.0 + rank, 10.0]), full[:, mine], n)
-    g = ld.gather_begin(full[1:, mine] * 3.0, n)
-    early, gms = g.finish()
-    empty, _ = ld.gather_begin(np.zeros((2, 0)), 0).finish()
-    ok = (np.array_equal(sums, [3.0, 20.0]) and np.array_equal(curves, full) and ms is None and np.array_equal(early, full[1:] * 3.0)
-          and gms is None and g.finish()[0] is early and empty.shape == (2, 0))
+    ok = np.array_equal(sums, [3.0, 20.0]) and np.array_equal(curves, full) and ms is None
     q.put((rank, F, b, F2, b2 is None, (lo, hi), curve, ok))
     dist.barrier()
     dist.destroy_process_group()
