@@ -511,6 +511,9 @@ def main():
                     'how': 'K further steps after the device-timed ones: same host inputs in / host results out through sweep.sharded_forecast, N0 enqueued '
                            "first on the library's second context (lbg_n0_ho02_begin) and joined before the variances; wall clock, barrier on both sides of "
                            'every step, max over ranks; results asserted identical to the sequential steps',
+                    'host_forecast_ms_per_step': float(np.mean([(ph_['spectra_s'] + ph_['grid_s']) * 1e3 for ph_ in phases])),
+                    'host_forecast_note': 'rank 0, mean over the K overlapped steps: wall time of the spectra + sums part of the step (N0 enqueue, table '
+                                          'upload, p(z) / b(z) callables, lbg_forecast_spectra incl. its own kernels, lbg_forecast_grid)',
                     'sequential': {'value': units / seq_s, 'ms_per_step': seq_s / a.steps * 1e3,
                                    'how': 'the K device-timed steps, library calls strictly one after another'}},
             'gpu_launches': int(launches_all),
@@ -522,6 +525,7 @@ def main():
                          'executed_definition': 'FP64 flop the kernel executes per unmasked node (2 DFMA + DMUL + DADD thread instructions of the ncu capture / its '
                                                 'unmasked nodes) x unmasked nodes / kernel time',
                          'ncu_profile': {k_: prof.get(k_) for k_ in ('file', 'commit', 'source_sha', 'flop_per_unmasked_node', 'pipes', 'nodes_unmasked', 'kernel')} if prof else None,
+                         'source_commit': prof.get('commit') if prof else None,
                          'stale': (prof['stale'] if prof else True), 'source_sha_now': n0_source_hash(),
                          'traffic': prof.get('dram_bytes_per_launch') if prof else None,
                          'traffic_note': 'ncu dram__bytes_read.sum + dram__bytes_write.sum of the profiled launch: the spline tables once; algorithmic bytes per launch = 8 B x n_L output',

@@ -35,7 +35,7 @@ def prep_lmaxmask(nu, nv):
 
 
 def _simpson_weights(n, dx):
-    """Composite Simpson weights for an odd number of uniform samples (scipy simps, cmb/Nkk.py:166-167)."""
+    """Composite Simpson weights for an odd number of uniform samples (SciPy's simps, cmb/Nkk.py:166-167)."""
     if n % 2 == 0:
         raise ValueError('the reference N0 grids are odd-length (SURVEY.md N5)')
     w = np.zeros(n)
@@ -121,7 +121,7 @@ def n0_begin(lensCl_interps, nolensCl_interps, Ls, terms=('TT', 'TE', 'EE', 'EB'
 
     fold_phi: True = one node per mirror pair (phi, 2 pi - phi), False = every node, 2 = mirror pairs through the generic
     per-node-mask kernel (cross-check).  exact_u_below: l1 rows below it get their u-side spline values from the library's
-    scipy-order host routine (csrc/ctx.cu; DESIGN.md "parity notes"); exact_rows / exact_u let a caller supply its own."""
+    SciPy-order host routine (csrc/ctx.cu; DESIGN.md "parity notes"); exact_rows / exact_u let a caller supply its own."""
     for t in terms:
         if t == 'TB':
             raise KeyError('TB')   # the reference indexes nolensCl_interps['TB'], which get_Cls never builds
