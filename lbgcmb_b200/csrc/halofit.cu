@@ -98,40 +98,59 @@ halofit_spec_kernel(int n_rows, int m, const double* __restrict__ s0, const doub
         const int nk1 = m;
         double* z = y;                               // z[base] is written after y[base] was consumed (base <= it); same stride
         // ---- right-hand side through the rotations (fpcurf) ----
-        // The operands of the NEXT data point (its right-hand side and six rotation pairs) are fetched before the chain of the current
-        // one starts: issue is in order, so a load placed after the chain would wait for it and add its latency to every point.
-        // Between points sreg[0] and sreg[1] every point moves the six-row window by exactly one row (interior of the knot vector):
-        // those go six at a time with the window registers renamed instead of shifted.  Rotations fpcurf skips (zero pivot) were staged
-        // as (cos, sin) = (1, 0), which leaves both operands as they are.
-        double w0 = 0, w1 = 0, w2 = 0, w3 = 0, w4 = 0, w5 = 0;       // z[base .. base + 5]
+        // Data point p rotates its right-hand side into the six rows base_p .. base_p + 5, one after the other.  Between points sreg[0]
+        // and sreg[1] (interior of the knot vector) base_p = base_(p-1) + 1, and rotation (p, i) needs only (p, i - 1) [the right-hand
+        // side] and (p - 1, i + 1) [the row]: rotations 0,1 of point p, 2,3 of point p - 1 and 4,5 of point p - 2 are independent of
+        // each other.  They are issued together -- a three-stage software pipeline over the points -- so the dependent chain per point is
+        // two rotations deep instead of six; every operation is the one fpcurf does, only the interleaving differs.  Four rows are live
+        // at a time (q0..q3; the row that leaves is final and goes to z), operands of the next step are fetched before the chains of
+        // this one.  Rotations fpcurf skips (zero pivot) were staged as (cos, sin) = (1, 0), which leaves both operands as they are.
+        double w0 = 0, w1 = 0, w2 = 0, w3 = 0, w4 = 0, w5 = 0;       // z[base .. base + 5] of the point-by-point form
         int base = lint[0] - K1;
         const double2* rp = reinterpret_cast<const double2*>(rot);
-        double yn = y[0], yi;
-        double2 n0 = rp[0], n1 = rp[1], n2 = rp[2], n3 = rp[3], n4 = rp[4], n5 = rp[5];
-        double2 r0, r1, r2, r3, r4, r5;
-#define LBG_ROT(W, CS) { const double s1 = yi, s2 = W; W = add(mul(CS.x, s2), mul(CS.y, s1)); yi = sub(mul(CS.x, s1), mul(CS.y, s2)); }
-#define LBG_TAKE(NEXT) { yi = yn; r0 = n0; r1 = n1; r2 = n2; r3 = n3; r4 = n4; r5 = n5; \
-                         if ((NEXT) < m) { const double2* q2 = rp + (size_t)(NEXT) * K1; yn = y[(size_t)(NEXT) * HF_T]; \
-                                           n0 = q2[0]; n1 = q2[1]; n2 = q2[2]; n3 = q2[3]; n4 = q2[4]; n5 = q2[5]; } }
-#define LBG_GENERIC(IT) { const int l = lint[IT]; LBG_TAKE((IT) + 1) \
+#define LBG_ROT2(W, Y, CS) { const double s1 = Y, s2 = W; W = add(mul(CS.x, s2), mul(CS.y, s1)); Y = sub(mul(CS.x, s1), mul(CS.y, s2)); }
+#define LBG_GENERIC(IT) { const int l = lint[IT]; double yi = y[(size_t)(IT) * HF_T]; const double2* g2 = rp + (size_t)(IT) * K1; \
+                          const double2 r0 = g2[0], r1 = g2[1], r2 = g2[2], r3 = g2[3], r4 = g2[4], r5 = g2[5]; \
                           while (base < l - K1) { z[(size_t)base * HF_T] = w0; w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; w5 = 0.0; ++base; } \
-                          LBG_ROT(w0, r0) LBG_ROT(w1, r1) LBG_ROT(w2, r2) LBG_ROT(w3, r3) LBG_ROT(w4, r4) LBG_ROT(w5, r5) }
-#define LBG_STEP(A, B, C, D, E, F, NEXT) { LBG_TAKE(NEXT) z[(size_t)base * HF_T] = A; A = 0.0; ++base; \
-                          LBG_ROT(B, r0) LBG_ROT(C, r1) LBG_ROT(D, r2) LBG_ROT(E, r3) LBG_ROT(F, r4) LBG_ROT(A, r5) }
+                          LBG_ROT2(w0, yi, r0) LBG_ROT2(w1, yi, r1) LBG_ROT2(w2, yi, r2) LBG_ROT2(w3, yi, r3) LBG_ROT2(w4, yi, r4) LBG_ROT2(w5, yi, r5) }
+        // one pipeline step: stage A = rotations 0,1 of point P, stage B = 2,3 of point P - 1, stage C = 4,5 of point P - 2
+#define LBG_PIPE(P, DA, DB, DC) { \
+            const int pa = ::min((P) + 1, m - 1), pb = ::min((P), m - 1), pc = ::min(::max((P) - 1, 0), m - 1); \
+            const double2 ta0 = rp[(size_t)pa * K1], ta1 = rp[(size_t)pa * K1 + 1], tb2 = rp[(size_t)pb * K1 + 2], tb3 = rp[(size_t)pb * K1 + 3]; \
+            const double2 tc4 = rp[(size_t)pc * K1 + 4], tc5 = rp[(size_t)pc * K1 + 5]; \
+            const double ynx = y[(size_t)pa * HF_T]; \
+            q3 = nx3; nx3 = nx4; nx4 = 0.0; \
+            if (DA) LBG_ROT2(q0, yA, a0) if (DB) LBG_ROT2(q1, yB, b2) if (DC) LBG_ROT2(q2, yC, c4) \
+            if (DA) LBG_ROT2(q1, yA, a1) if (DB) LBG_ROT2(q2, yB, b3) if (DC) LBG_ROT2(q3, yC, c5) \
+            z[(size_t)bb * HF_T] = q0; ++bb; q0 = q1; q1 = q2; q2 = q3; \
+            yC = yB; yB = yA; yA = ynx; a0 = ta0; a1 = ta1; b2 = tb2; b3 = tb3; c4 = tc4; c5 = tc5; }
         int it = 0;
         const int reg_lo = sreg[0], reg_hi = sreg[1];
-        for (; it < reg_lo; ++it) LBG_GENERIC(it)
-#pragma unroll 1
-        for (; it + 6 <= reg_hi; it += 6) {
-            LBG_STEP(w0, w1, w2, w3, w4, w5, it + 1) LBG_STEP(w1, w2, w3, w4, w5, w0, it + 2) LBG_STEP(w2, w3, w4, w5, w0, w1, it + 3)
-            LBG_STEP(w3, w4, w5, w0, w1, w2, it + 4) LBG_STEP(w4, w5, w0, w1, w2, w3, it + 5) LBG_STEP(w5, w0, w1, w2, w3, w4, it + 6)
+        if (reg_hi - reg_lo >= 3) {
+            for (; it < reg_lo; ++it) LBG_GENERIC(it)
+            // point reg_lo moves the window by one row: row `base` is final; rows base + 1 .. base + 5 enter the pipeline
+            z[(size_t)base * HF_T] = w0;
+            double q0 = w1, q1 = w2, q2 = w3, q3 = 0.0, nx3 = w4, nx4 = w5;
+            int bb = base + 1;
+            double yA = y[(size_t)reg_lo * HF_T], yB = 0.0, yC = 0.0;
+            double2 a0 = rp[(size_t)reg_lo * K1], a1 = rp[(size_t)reg_lo * K1 + 1], b2 = a0, b3 = a0, c4 = a0, c5 = a0;
+            LBG_PIPE(reg_lo, 1, 0, 0)
+            LBG_PIPE(reg_lo + 1, 1, 1, 0)
+#pragma unroll 2
+            for (int p = reg_lo + 2; p < reg_hi; ++p) LBG_PIPE(p, 1, 1, 1)
+            LBG_PIPE(reg_hi, 0, 1, 1)
+            LBG_PIPE(reg_hi + 1, 0, 0, 1)
+            // back to the point-by-point form: the window of point reg_hi - 1 (its first three rows were written out above)
+            base = bb - 3;
+            w0 = z[(size_t)base * HF_T]; w1 = z[(size_t)(base + 1) * HF_T]; w2 = z[(size_t)(base + 2) * HF_T];
+            w3 = q0; w4 = q1; w5 = q2;
+            it = reg_hi;
         }
 #pragma unroll 1
         for (; it < m; ++it) LBG_GENERIC(it)
-#undef LBG_STEP
+#undef LBG_PIPE
 #undef LBG_GENERIC
-#undef LBG_TAKE
-#undef LBG_ROT
+#undef LBG_ROT2
         z[(size_t)base * HF_T] = w0; z[(size_t)(base + 1) * HF_T] = w1; z[(size_t)(base + 2) * HF_T] = w2;
         z[(size_t)(base + 3) * HF_T] = w3; z[(size_t)(base + 4) * HF_T] = w4; z[(size_t)(base + 5) * HF_T] = w5;
         // ---- interval of the derivative point (spalde) ----

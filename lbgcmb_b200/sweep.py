@@ -284,9 +284,9 @@ def sharded_forecast(lensCl_interps, nolensCl_interps, Pk_interps, Llls, nmodes,
     interim = sums[:, 5:7]
     dtheta = np.zeros((n_b, 2))
     if xsamples is not None:
-        for i in range(n_b):
-            if np.linalg.det(F[i]) != 0:
-                dtheta[i] = np.linalg.solve(F[i], interim[i])
+        ok = np.linalg.det(F) != 0                                    # stacked calls: LAPACK per matrix, as one call per sample gives
+        if ok.any():
+            dtheta[ok] = np.linalg.solve(F[ok], interim[ok][:, :, None])[:, :, 0]
     if timing is not None:
         timing.update(spectra_s=t1 - t0, n0_wait_s=t2 - t1, grid_s=t3 - t2, collectives_s=t4 - t3, exchange_device_ms=xms,
                       n_L_mine=int(mine.size))
