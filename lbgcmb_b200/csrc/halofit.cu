@@ -362,7 +362,7 @@ static int hf_enqueue_sigma2(lbg_ctx* c, lbg_hf_state& H, int m, const double* R
     double* d_s0 = H.dev.as<double>();
     const double* kd = c->pk_lnk.as<double>();
     const size_t smem = ((size_t)c->n_k + c->pk_npan0 + c->pk_npan1) * 8;
-    if (c->pk_npan0 > 0 && smem <= 48 * 1024) {              // the reference's own summation order (pk_kernels.cuh)
+    if (c->pk_npan0 > 0 && smem <= 45 * 1024 && c->pk_npan0 <= 2048 && c->pk_npan1 <= 2048) {   // the reference's own summation order (pk_kernels.cuh); <= 2 x 31 tree nodes
         const double* sp = c->pk_simps.as<double>();
         sigma2_np_kernel<<<m, 256, smem, st>>>(c->n_k, kd, sp, reinterpret_cast<const SimpsPanel*>(sp + c->n_k), c->pk_npan0, c->pk_npan1,
                                                c->pk_first_dx, c->pk_last_dx, H.Rdev.as<double>(), d_s0);

@@ -29,7 +29,7 @@ sigma2_kernel(int n_k, const double* __restrict__ k, const double* __restrict__ 
 // The same integral summed EXACTLY as the reference sums it (modi/halofit.py:41-42: scipy-1.2.1 `simps(y, ln k)` = numpy products per
 // three-point panel + np.sum, whose pairwise order is reproduced below).  Needed where ln sigma^2(R) feeds HALOFIT's curvature: the
 // second derivative of the interpolating spline multiplies the ~1e-16 difference between two summation orders by ~1e4 / C.
-// Block per R: threads fill y_i = Delta0^2 exp(-(k_i R)^2) and the panel terms in shared memory, thread 0 adds them in numpy's order.
+// Block per R: threads fill y_i = Delta0^2 exp(-(k_i R)^2) and the panel terms in shared memory and add them in numpy's order (below).
 struct SimpsPanel { double c0, hsum, hprod, c2, s6; };   // 2 - 1/(h0/h1), h0 + h1, h0 h1, 2 - h0/h1, (h0 + h1)/6 of one panel
 
 __device__ inline double np_pairwise_sum(const double* a, int n) {       // numpy's pairwise_sum for contiguous float64
@@ -56,13 +56,41 @@ __device__ inline double np_pairwise_sum(const double* a, int n) {       // nump
     return __dadd_rn(np_pairwise_sum(a, n2), np_pairwise_sum(a + n2, n - n2));
 }
 
-static __global__ void __launch_bounds__(256)
+// numpy's pairwise sum is a binary recursion over halves down to leaves of <= 128 elements.  The tree (pre-order: a parent before its
+// children) is laid out by one thread; the leaves are then independent sums that any thread can take, and the inner nodes are
+// combined child + child in reverse index order -- the additions numpy makes, in its order.
+struct PwNode { int off, n, left, right; };      // left < 0: leaf
+constexpr int PW_MAX_NODES = 96;                 // 2 trees of up to ~1000 panels: 2 x (2 x 16 - 1) nodes; bound checked on the host
+
+__device__ inline int pw_build(PwNode* nodes, int* cnt, int off, int n) {
+    const int me = (*cnt)++;
+    nodes[me].off = off; nodes[me].n = n; nodes[me].left = -1; nodes[me].right = -1;
+    if (n > 128) {
+        int n2 = n / 2;
+        n2 -= n2 % 8;
+        const int l = pw_build(nodes, cnt, off, n2);
+        const int r = pw_build(nodes, cnt, off + n2, n - n2);
+        nodes[me].left = l; nodes[me].right = r;
+    }
+    return me;
+}
+
+static __global__ void __launch_bounds__(256, 4)
 sigma2_np_kernel(int n, const double* __restrict__ k, const double* __restrict__ delta0, const SimpsPanel* __restrict__ pan,
                  int npan0, int npan1, double first_dx, double last_dx, const double* __restrict__ R, double* __restrict__ out) {
     extern __shared__ double sh[];
     double* y = sh;                       // [n]
     double* tmp = sh + n;                 // [npan0 + npan1]
+    __shared__ PwNode nodes[PW_MAX_NODES];
+    __shared__ double val[PW_MAX_NODES];
+    __shared__ int roots[3];              // root of the first tree, root of the second, node count
     const double r = R[blockIdx.x];
+    if (threadIdx.x == 255) {             // the summation trees, laid out while the other threads fill y
+        int cnt = 0;
+        roots[0] = pw_build(nodes, &cnt, 0, npan0);
+        roots[1] = npan1 > 0 ? pw_build(nodes, &cnt, npan0, npan1) : -1;
+        roots[2] = cnt;
+    }
     for (int i = threadIdx.x; i < n; i += 256) {
         const double kr = __dmul_rn(k[i], r);
         y[i] = __dmul_rn(delta0[i], exp(-__dmul_rn(kr, kr)));
@@ -77,13 +105,20 @@ sigma2_np_kernel(int n, const double* __restrict__ k, const double* __restrict__
         tmp[p] = __dmul_rn(P.s6, __dadd_rn(__dadd_rn(a, b), c));
     }
     __syncthreads();
+    const int cnt = roots[2];
+    // one leaf per warp-strided thread: leaves are <= 128 elements, 8 independent accumulators each
+    for (int q = threadIdx.x; q < cnt; q += 256)
+        if (nodes[q].left < 0) val[q] = np_pairwise_sum(tmp + nodes[q].off, nodes[q].n);
+    __syncthreads();
     if (threadIdx.x == 0) {
-        double res = np_pairwise_sum(tmp, npan0);
+        for (int q = cnt - 1; q >= 0; --q)
+            if (nodes[q].left >= 0) val[q] = __dadd_rn(val[nodes[q].left], val[nodes[q].right]);
+        double res = val[roots[0]];
         if (npan1 > 0) {                  // even number of samples: scipy-1.2.1 even='avg'
-            double val = __dmul_rn(__dmul_rn(0.5, last_dx), __dadd_rn(y[n - 1], y[n - 2]));
-            val = __dadd_rn(val, __dmul_rn(__dmul_rn(0.5, first_dx), __dadd_rn(y[1], y[0])));
-            res = __dadd_rn(res, np_pairwise_sum(tmp + npan0, npan1));
-            res = __dadd_rn(__ddiv_rn(res, 2.0), __ddiv_rn(val, 2.0));
+            double v2 = __dmul_rn(__dmul_rn(0.5, last_dx), __dadd_rn(y[n - 1], y[n - 2]));
+            v2 = __dadd_rn(v2, __dmul_rn(__dmul_rn(0.5, first_dx), __dadd_rn(y[1], y[0])));
+            res = __dadd_rn(res, val[roots[1]]);
+            res = __dadd_rn(__ddiv_rn(res, 2.0), __ddiv_rn(v2, 2.0));
         }
         out[blockIdx.x] = res;
     }
