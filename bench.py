@@ -381,6 +381,8 @@ def main():
         stage.update(kernel_ms=ms0 + ms1, launches=n0_ + n1_, n0_ms=Nkk.last_stats['kernel_ms'], main_ms=Nkk.last_stats['main_kernel_ms'],
                      nodes=Nkk.last_stats['nodes'], unmasked=Nkk.last_stats['nodes_unmasked'], path=Nkk.last_stats['path'],
                      n_L_mine=Nkk.last_stats['n_L'], xchg_ms=timing.get('exchange_device_ms') or 0.0)
+        if ldist.last_exchange_backend == 'p2p':
+            stage['launches'] += 1                   # the peer-memory exchange kernel (csrc/xchg.cu) is ours too
         return res
 
     def barrier():
@@ -447,6 +449,27 @@ def main():
     xchg_ms = -xchg_ms
     dev_ms = kern_ms + xchg_ms
     nodes_all, unmasked_all, launches_all = (float(x) for x in counts)
+    # the exchange alone on the last step's payload, both routes (device ms, median of 20; collective calls: every rank takes part)
+    xchg_how, xchg_cmp = 'none', None
+    if world > 1:
+        backend = ldist.last_exchange_backend
+        xs, xc = np.ones((len(bands), 9)), np.ones((2 + 2 * len(bands), len(range(rank, Ls.size, world))))
+        def xtime():
+            t_ = []
+            for _ in range(20):
+                barrier()
+                t_.append(ldist.exchange(xs, xc, Ls.size)[2])
+            return float(np.median(t_))
+        ms_used = xtime()
+        xchg_cmp = {'backend': backend, 'device_ms': ms_used, 'p2p_unavailable_because': ldist._p2p['why']}
+        if backend == 'p2p':
+            keep_ctx, ldist._p2p['ctx'] = ldist._p2p['ctx'], None
+            xchg_cmp['nccl_device_ms'] = xtime()
+            ldist._p2p['ctx'] = keep_ctx
+            xchg_how = ('over NVLink peer memory: ONE kernel per rank stores its block into every peer\'s window and waits for theirs (csrc/xchg.cu), sums '
+                        'added in rank order; the NCCL route (all_reduce + all_gather_into_tensor) of the same payload is timed beside it in `exchange`')
+        else:
+            xchg_how = 'one NCCL all_reduce + one all_gather_into_tensor'
     # per-rank phase breakdown of the last overlapped step (wall ms on that rank)
     mine = {k_: (v * 1e3 if k_.endswith('_s') else v) for k_, v in phases[-1].items()}
     mine.update(rank=rank, kernel_ms_seq=stage['kernel_ms'], n0_kernel_ms=stage['n0_ms'])
@@ -496,8 +519,8 @@ def main():
             'higher_is_better': True, 'scaling': 'strong' if world > 1 else 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
             'config': {'workload': WORKLOAD % (cfg[0], cfg[1], a.lmin, a.lmax), 'n_L': int(Ls.size), 'call': 'lbgcmb_b200.sweep.sharded_forecast',
                        'phi_fold': True, 'nodes_walked_per_step': nodes_all, 'nodes_unmasked_per_step': unmasked_all,
-                       'multi_gpu': ('ONE forecast per step, multipole grid sharded L[r::N]; one NCCL all-reduce of %d partial sums + one all-gather of '
-                                     '%d curves inside the timed region' % (9 * n_band, 2 + 2 * n_band)) if world > 1 else 'single GPU',
+                       'multi_gpu': ('ONE forecast per step, multipole grid sharded L[r::N]; the exchange inside the timed region -- all-reduce of %d partial '
+                                     'sums + all-gather of %d curves -- %s' % (9 * n_band, 2 + 2 * n_band, xchg_how)) if world > 1 else 'single GPU',
                        'cl_tables': 'handed over every step; the library compares them with its resident copy and re-solves / re-uploads only on change',
                        'pk_tables': 'linear P(k) uploaded and every P(k,z) row (3 z grids) rebuilt every step',
                        'l2': 'flushed between timed iterations (256 MB memset); tables are re-read from HBM each step'},
@@ -517,6 +540,7 @@ def main():
                     'sequential': {'value': units / seq_s, 'ms_per_step': seq_s / a.steps * 1e3,
                                    'how': 'the K device-timed steps, library calls strictly one after another'}},
             'gpu_launches': int(launches_all),
+            'exchange': xchg_cmp,
             'phases_per_rank_ms': per_rank,
             'roofline': {'bound': 'fp64', 'achieved': conv, 'peak': peak, 'unit': 'TFLOP/s', 'frac': conv / peak if peak else None,
                          'definition': 'SURVEY.md 8(d): 145 FP64 op per integrand node x nodes that pass a mask (counted by the kernel: %d per step) / kernel '

@@ -308,6 +308,24 @@ int lbg_spectra_set_get(lbg_ctx* ctx, int set, int row0, int n_rows, int n_ell, 
 int lbg_field_fisher_sets(lbg_ctx* ctx, int n_ell, int n_f, int n_spec, const int* spec_a, const int* spec_b, int set_fid, int set_noise,
                           int n_diff, const int* set_plus, const int* set_minus, const double* two_h, int n_amp, const double* amp,
                           const double* mode_weight, double* out_F, double* out_per_ell /*or NULL*/);
+/* ---- the exchange step of a forecast whose multipoles are sharded over the GPUs of one box, over NVLink peer memory.
+ * One process per GPU.  lbg_xchg_create allocates this rank's window (room for blocks of up to cap_doubles doubles from every rank,
+ * double-buffered) and returns its 64-byte CUDA IPC handle; the caller passes the handles of all ranks around (any transport:
+ * torch.distributed in lbgcmb_b200/dist.py) and hands them to lbg_xchg_open.  lbg_xchg_allgather is then a collective: every rank
+ * calls it the same number of times with the same n; block[n] of rank r arrives as out[r][n] on every rank -- one kernel per rank
+ * that stores the block into every peer's window and waits for the peers' blocks (release / acquire flags), no library collective.
+ * A rank that does not arrive within ~4 s of GPU clocks ends the call with LBG_ECUDA instead of hanging.  *out_ms: device time of
+ * the kernel (includes the wait for the slowest peer).  No counterpart in the reference (single process). */
+int lbg_xchg_create(lbg_ctx* ctx, int rank, int world, long long cap_doubles, unsigned char* out_handle /*[64]*/);
+int lbg_xchg_open(lbg_ctx* ctx, const unsigned char* handles /*[world][64], rank order*/);
+int lbg_xchg_allgather(lbg_ctx* ctx, long long n, const double* block /*[n]*/, double* out /*[world][n]*/, double* out_ms /*or NULL*/);
+/* The exchange step of a sharded forecast in one call (what lbgcmb_b200/dist.py `exchange` makes): sums[n_sums] are added over
+ * the ranks, in rank order (the all-reduce of the Fisher / S/N^2 / bias sums of interloper.py:223-253, snr.py:21-25 taken over
+ * multipole shards), and curves[n_curves][n_mine] -- this rank's cyclic shard, units rank, rank + world, ... of n -- come back whole
+ * as out_curves[n_curves][n]. */
+int lbg_xchg_sums_curves(lbg_ctx* ctx, int n_sums, const double* sums, int n_curves, long long n, const double* curves,
+                         double* out_sums, double* out_curves, double* out_ms /*or NULL*/);
+int lbg_xchg_destroy(lbg_ctx* ctx);
 /* mqw/py/mqw.py:63-104 `Fisher` (clustering-redshift N_p(z_i) Fisher): bins[n_bin][8] = {bp, bs, Np, Ns, wp, ws, wps, -}
  * per redshift shell (mqw.py:24-41); cgg[n_ell] shared by all shells (cgg_per_bin = 0, as mqw.py:48) or
  * cgg[n_bin][n_ell] (cgg_per_bin = 1, as cadence/cadence.py:97); mode_weight[l] = 2l+1 (0 beyond an l cut).

@@ -115,6 +115,11 @@ def _declare(L):
         'lbg_spectra_set_get': [vp, i, i, i, i, c_double_p],
         'lbg_field_fisher_sets': [vp, i, i, i, c_int_p, c_int_p, i, i, i, c_int_p, c_int_p, c_double_p, i, c_double_p, c_double_p, c_double_p,
                                   c_double_p],
+        'lbg_xchg_create': [vp, i, i, C.c_longlong, C.POINTER(C.c_ubyte)],
+        'lbg_xchg_open': [vp, C.POINTER(C.c_ubyte)],
+        'lbg_xchg_allgather': [vp, C.c_longlong, c_double_p, c_double_p, c_double_p],
+        'lbg_xchg_sums_curves': [vp, i, c_double_p, i, C.c_longlong, c_double_p, c_double_p, c_double_p, c_double_p],
+        'lbg_xchg_destroy': [vp],
         'lbg_mqw_fisher': [vp, i, i, c_double_p, i, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_cadence_fisher': [vp, i, i, c_double_p, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_forecast_grid': [vp, i, c_double_p, c_double_p, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p,

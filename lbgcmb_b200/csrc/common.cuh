@@ -78,6 +78,7 @@ struct __align__(64) ClRow {
 
 struct lbg_n0_plan;               // n0.cu: grid-dependent part of an N0 call, kept between calls
 struct lbg_hf_state;              // halofit.cu: HALOFIT fitting grid / sigma_0^2 state
+struct lbg_xchg_state;            // xchg.cu: peer-memory windows of the exchange step
 
 struct lbg_ctx {
     int          device = 0;
@@ -122,6 +123,7 @@ struct lbg_ctx {
     int          n_k = 0;
     unsigned long long pk_gen = 0;   // bumped whenever a new linear table / k grid is installed
     lbg_hf_state* hf = nullptr;
+    lbg_xchg_state* xchg = nullptr;
     lbg::DevBuf  pk_lnk, pk_plin, pk_rdk;
     lbg::DevBuf  pk_simps;           // numpy-order Simpson data of the ln k grid: [Delta0^2 n_k | SimpsPanel x (npan0 + npan1)]
     int          pk_npan0 = 0, pk_npan1 = 0;

@@ -233,6 +233,7 @@ extern "C" int lbg_ctx_create_lane(int device, int lane, lbg_ctx** out) {
 
 void lbg_n0_release(lbg_ctx* c);   // n0.cu
 void lbg_hf_release(lbg_ctx* c);   // halofit.cu
+void lbg_xchg_release(lbg_ctx* c); // xchg.cu
 
 extern "C" int lbg_ctx_destroy(lbg_ctx* c) {
     if (!c) return LBG_OK;
@@ -240,6 +241,7 @@ extern "C" int lbg_ctx_destroy(lbg_ctx* c) {
     cudaStreamSynchronize(c->stream);
     lbg_n0_release(c);
     lbg_hf_release(c);
+    lbg_xchg_release(c);
     for (DevBuf* b : {&c->cl_rows, &c->cl_soa, &c->cl_poly, &c->n0_L, &c->n0_utab, &c->n0_partial, &c->n0_out, &c->n0_plan_dev,
                       &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->pk_lnk, &c->pk_plin, &c->pk_pnl, &c->pk_rdk})
         b->release();

@@ -60,28 +60,90 @@ def allgather_cyclic(local, n):
 
 _xbuf = {}
 last_exchange_ms = None
+last_exchange_backend = None        # 'p2p' (peer-memory kernel, csrc/xchg.cu), 'nccl', 'gloo' or None (single rank)
+_P2P_CAP = 1 << 16                  # doubles per rank and exchange (512 KB); larger payloads take the NCCL route
+_p2p = {'tried': False, 'ctx': None, 'why': None}
+
+
+def _p2p_context():
+    """The library context whose peer-memory windows serve `exchange` on NCCL process groups, or None (then `_p2p['why']` says why).
+    Set up once per process, collectively: every rank creates its window (lbg_xchg_create), the 64-byte IPC handles go round with
+    all_gather_object, every rank opens its peers' windows (lbg_xchg_open); the route is used only if every rank succeeded.
+    LBGCMB_XCHG=nccl keeps the exchange on NCCL."""
+    if _p2p['tried']:
+        return _p2p['ctx']
+    _p2p['tried'] = True
+    import ctypes as C
+    import os
+    d = _dist()
+    if os.environ.get('LBGCMB_XCHG', 'p2p').lower() == 'nccl':
+        _p2p['why'] = 'LBGCMB_XCHG=nccl'
+        return None
+    from lbgcmb_b200 import _ffi
+    rank, world = d.get_rank(), d.get_world_size()
+    ctx, handle, why = None, (C.c_ubyte * 64)(), None
+    try:
+        ctx = _ffi.context()
+        rc = _ffi.lib().lbg_xchg_create(ctx.handle, rank, world, _P2P_CAP, handle)
+        if rc != 0:
+            why = _ffi.lib().lbg_last_error().decode('utf-8', 'replace')
+    except Exception as e:                                  # noqa: BLE001 (any failure here means "use NCCL", the reason is kept)
+        why = repr(e)
+    got = [None] * world
+    d.all_gather_object(got, (why, bytes(handle)))
+    if any(g[0] for g in got):
+        _p2p['why'] = next(g[0] for g in got if g[0])
+    else:
+        blob = (C.c_ubyte * (64 * world)).from_buffer_copy(b''.join(g[1] for g in got))
+        rc = _ffi.lib().lbg_xchg_open(ctx.handle, blob)
+        why = None if rc == 0 else _ffi.lib().lbg_last_error().decode('utf-8', 'replace')
+        got = [None] * world
+        d.all_gather_object(got, why)
+        if any(got):
+            _p2p['why'] = next(g for g in got if g)
+        else:
+            _p2p['ctx'] = ctx
+    if _p2p['ctx'] is None and ctx is not None:
+        _ffi.lib().lbg_xchg_destroy(ctx.handle)
+    return _p2p['ctx']
 
 
 def exchange(sums, curves, n):
     """The exchange step of a sharded forecast in one round trip: `sums` (any shape) is all-reduced (SUM) and `curves`
     [n_curves, n_mine] (this rank's cyclic shard of n units, shard_indices) is all-gathered back into [n_curves, n].
 
-    On NCCL both payloads travel in ONE pinned host block -> one device tensor, the two collectives run on slices of it, and one
-    copy brings [reduced sums | gathered curves] back (two copies, two collectives, one synchronisation); the device time of the
-    two collectives (CUDA events on torch's stream) is returned as the third value (None off-GPU).  gloo / no process group:
-    CPU tensors / identity."""
-    global last_exchange_ms
+    On GPUs (NCCL process group) the exchange runs over NVLink peer memory when the windows could be set up (_p2p_context): ONE
+    kernel per rank stores [sums | curves] into every peer's window and waits for the peers' blocks (csrc/xchg.cu); the sums are then
+    added on the host in rank order -- the all-reduce, with a summation order that does not depend on the collective library.
+    Otherwise (LBGCMB_XCHG=nccl, set-up failed, payload beyond the window) both payloads travel in ONE pinned host block -> one device
+    tensor, an NCCL all_reduce and an all_gather_into_tensor run on slices of it, and one copy brings the result back.  The device
+    time of the exchange is returned as the third value (None off-GPU).  gloo / no process group: CPU tensors / identity."""
+    global last_exchange_ms, last_exchange_backend
     d = _dist()
     sums = np.ascontiguousarray(sums, dtype=np.float64)
     curves = np.atleast_2d(np.ascontiguousarray(curves, dtype=np.float64))
     if d is None or d.get_world_size() == 1:
         last_exchange_ms = None
+        last_exchange_backend = None
         return sums.copy(), curves.copy(), None
     import torch
     world = d.get_world_size()
     width = (n + world - 1) // world
     nc, ns = curves.shape[0], sums.size
     nccl = d.get_backend() == 'nccl'
+    if nccl and ns + nc * width <= _P2P_CAP:
+        ctx = _p2p_context()
+        if ctx is not None:
+            import ctypes as C
+            from lbgcmb_b200 import _ffi
+            if curves.shape[1] != len(range(d.get_rank(), n, world)):
+                raise ValueError('curves must hold this rank\'s cyclic shard: %d of %d units' % (len(range(d.get_rank(), n, world)), n))
+            red, out, ms = np.empty(ns), np.empty((nc, n)), C.c_double(0.0)
+            flat = np.ascontiguousarray(curves)
+            _ffi.check(_ffi.lib().lbg_xchg_sums_curves(ctx.handle, ns, _ffi._dp(sums.ravel()), nc, n, _ffi._dp(flat), _ffi._dp(red),
+                                                       _ffi._dp(out), C.byref(ms)))
+            last_exchange_ms, last_exchange_backend = ms.value, 'p2p'
+            return red.reshape(sums.shape), out, ms.value
     key = (ns, nc, width, world, nccl)
     buf = _xbuf.get(key)
     if buf is None:
@@ -123,7 +185,7 @@ def exchange(sums, curves, n):
     for r in range(world):
         m = len(range(r, n, world))
         out[:, r::world] = parts[r, :, :m]
-    last_exchange_ms = ms
+    last_exchange_ms, last_exchange_backend = ms, ('nccl' if nccl else 'gloo')
     return hout[:ns].reshape(sums.shape).copy(), out, ms
 
 
