@@ -78,7 +78,18 @@ def _cl_tables(lensCl_interps, nolensCl_interps):
     for x in _ORDER:
         nolens.append(table_of(nolensCl_interps[x], n_default=n))
     n = min(n, min(t.size for t in nolens))
-    return n, _ffi.f64(np.stack([t[:n] for t in lens])), _ffi.f64(np.stack([t[:n] for t in nolens]))
+    return n, _rows_as_matrix(lens, n), _rows_as_matrix(nolens, n)
+
+
+def _rows_as_matrix(tabs, n):
+    """[4, n] float64 C-contiguous matrix of the four tables: the array they are rows of when they already lie that way in memory
+    (prep_camb.cl_interps_from_tables builds them from one [4, n] array), a stacked copy otherwise."""
+    b = tabs[0].base
+    if (isinstance(b, np.ndarray) and b.ndim == 2 and b.shape == (4, n) and b.dtype == np.float64 and b.flags.c_contiguous
+            and all(t.base is b and t.shape == (n,) and t.strides == (8,)
+                    and t.__array_interface__['data'][0] == b.__array_interface__['data'][0] + i * b.strides[0] for i, t in enumerate(tabs))):
+        return b
+    return _ffi.f64(np.stack([t[:n] for t in tabs]))
 
 
 def upload_cls(ctx, lensCl_interps, nolensCl_interps, reuse=False):

@@ -25,3 +25,24 @@ def test_cache_key_follows_the_spectra(tmp_path, monkeypatch):
     Ls2[3] += 1                                                            # same length, ends: the reference's name cannot tell
     assert Nkk._cache_path(Ls2, *args[1:]) == Nkk._cache_path(*args)
     assert Nkk._cache_path(Ls2, *args[1:], li, ni) != a
+
+
+def test_tables_handed_over_without_a_copy_when_they_already_form_a_matrix():
+    """Nkk._cl_tables: four tables that are the rows of one C-contiguous [4, n] array (prep_camb.cl_interps_from_tables) are passed
+    as that array; any other layout (separate arrays, permuted rows, a longer unlensed table) is stacked -- same values either way."""
+    from lbgcmb_b200 import Nkk
+    from lbgcmb_b200.prep_camb import ClInterp, cl_interps_from_tables
+    from lbgcmb_b200.synthetic import cmb_cl_tables
+    ell, lens, nolens = cmb_cl_tables(2000)
+    order = ('TT', 'EE', 'BB', 'TE')
+    li, ni = cl_interps_from_tables(ell, lens, nolens)
+    n, lt, ut = Nkk._cl_tables(li, ni)
+    assert n == 2000 and np.shares_memory(lt, lens) and np.array_equal(lt, lens) and np.array_equal(ut, nolens)
+    sep = {x: ClInterp(ell, lens[i].copy()) for i, x in enumerate(order)}
+    perm = {x: ClInterp(ell, lens[(i + 1) % 4]) for i, x in enumerate(order)}
+    for tabs, want in ((sep, lens), (perm, lens[[1, 2, 3, 0]])):
+        _, got, _ = Nkk._cl_tables(tabs, ni)
+        assert not np.shares_memory(got, lens) and np.array_equal(got, want) and got.flags.c_contiguous
+    short = {x: ClInterp(ell[:1500], lens[i, :1500]) for i, x in enumerate(order)}      # lensed table shorter than the unlensed one
+    n2, lt2, ut2 = Nkk._cl_tables(short, ni)
+    assert n2 == 1500 and np.array_equal(lt2, lens[:, :1500]) and np.array_equal(ut2, nolens[:, :1500]) and ut2.flags.c_contiguous
