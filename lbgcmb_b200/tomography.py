@@ -124,7 +124,7 @@ def field_spectra(cosmo, ell, tracers, nodes_per_bin=10, nonlinear=True, kk=True
 
 
 def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=('sig8', 'mnu'), steps=None, nodes_per_bin=10,
-                       nonlinear=True, k=None, device=None, sharded=False, spectra_fn=None, accum=None, return_spectra=True, host_arrays=False):
+                       nonlinear=True, k=None, device=None, sharded=False, spectra_fn=None, accum=None, return_spectra=True, host_arrays=False, geometry=None):
     """Fisher matrix over `cosmo_params` + one bias amplitude per tracer (b(z) -> A_t b(z), fiducial A_t = 1) from kappa and every
     galaxy bin: fields (kappa, g_1 .. g_n), spectra kk, kappa g_i, g_i g_i (bins of one tracer are disjoint; cross-tracer overlaps
     are neglected), noise N_kk = `nkk` [n_ell] and 1 / nbar_i on the galaxy autos (tracers[t]['nbar']: per bin, sr^-1).
@@ -135,7 +135,9 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
     `spectra_fn(theta, ell) -> (ckk, ckg, cgg)` and `accum` (signature of fisher.field_fisher) replace the device calls in the CPU
     (gloo) tests of the sharding logic; the product path leaves both None and then keeps every spectrum on the device (spectra sets:
     Cosmology.limber(keep=...), fisher.field_fisher_sets); host_arrays=True selects the host-array route of the same device kernels
-    (spectra copied back, sums and differences in numpy, fisher.field_fisher_amp), kept for the parity test between the two.  return_spectra=False skips the read-back of the fiducial spectra."""
+    (spectra copied back, sums and differences in numpy, fisher.field_fisher_amp), kept for the parity test between the two.
+    `geometry`: a dict the caller keeps between calls with the SAME ell, tracers and nodes_per_bin (a loop over noise curves or sky
+    fractions): distances and Limber weight vectors are then built once per background instead of once per call.  return_spectra=False skips the read-back of the fiducial spectra."""
     fid = dict(FIDUCIAL, **(fid or {}))
     steps = dict(STEPS, **(steps or {}))
     ell, nmodes, nkk = (np.asarray(a, dtype=np.float64) for a in (ell, nmodes, nkk))
@@ -169,7 +171,7 @@ def tomographic_fisher(tracers, ell, nmodes, fsky, nkk, fid=None, cosmo_params=(
         # product path: every spectrum stays on the device.  Cosmology i of the stencil fills spectra set i; the noise is set
         # len(thetas); sums, differences and amplitude rows are formed there (lbg_field_fisher_sets)
         growth = growth_tables([t['M'] for t in thetas], device=device)       # the whole stencil in one launch
-        geometry = {}
+        geometry = {} if geometry is None else geometry
         for i, (theta, y) in enumerate(zip(thetas, growth)):
             c = make_cosmology(theta, Dplus_table=y, k=k, device=device)
             field_spectra(c, ell, tracers, nodes_per_bin, nonlinear, geometry=geometry, keep_set=i)
