@@ -248,6 +248,14 @@ int lbg_forecast_spectra(lbg_ctx* ctx, int n_ell, const double* ell, double zmin
 /* snr.py:21-25 `snr`: sqrt( sum_{l <= lmax} nmodes (C_l / sqrt(Var_l))^2 ). */
 int lbg_snr(lbg_ctx* ctx, int n_ell, const double* ell, const double* cl, const double* var, const double* nmodes,
             double lmax, double* out_snr);
+/* The experiment x delensing x dilution sweep of snr.py:107-133 as ONE call: for experiment e (N_kk row e, fsky[e]), delensing curve r
+ * (rho[r][l]; a row of zeros = no delensing) and shot noise ngg[d] (= Ngg of the diluted density, Cgg.py:85-95),
+ *   out[e][r][d] = snr(L, C_kg, var, nmodes, lmax)   with   var = (((1 - rho^2) C_kk + N_kk)(C_gg + N_gg) + C_kg^2) / ((2L + 1) fsky)
+ * (Ckg.py:61-87 incl. the rho branch :69-71, snr.py:21-25).  Bit-identical to var_Ckg + snr called per design.  The caller divides
+ * by sqrt(fsky) where the reference driver does (snr.py:125). */
+int lbg_snr_grid(lbg_ctx* ctx, int n_ell, const double* ell, const double* nmodes, const double* ckk, const double* cgg, const double* ckg,
+                 int n_exp, const double* nkk /*[n_exp][n_ell]*/, const double* fsky /*[n_exp]*/, int n_rho, const double* rho /*[n_rho][n_ell]*/,
+                 int n_dil, const double* ngg /*[n_dil]*/, double lmax, double* out /*[n_exp][n_rho][n_dil]*/);
 /* lbg_snr for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
  * cudaMalloc).  No counterpart in the reference.  Same arguments, same kernel and same
  * result as lbg_snr, but the device staging of the four vectors and of the result lives in a fixed file-scope device array instead of

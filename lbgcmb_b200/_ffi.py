@@ -120,6 +120,8 @@ def _declare(L):
         'lbg_xchg_allgather': [vp, C.c_longlong, c_double_p, c_double_p, c_double_p],
         'lbg_xchg_sums_curves': [vp, i, c_double_p, i, C.c_longlong, c_double_p, c_double_p, c_double_p, c_double_p],
         'lbg_xchg_destroy': [vp],
+        'lbg_snr_grid': [vp, i, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, i, c_double_p, c_double_p, i, c_double_p, i, c_double_p, d,
+                         c_double_p],
         'lbg_mqw_fisher': [vp, i, i, c_double_p, i, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_cadence_fisher': [vp, i, i, c_double_p, c_double_p, c_double_p, d, c_double_p, c_double_p, c_double_p],
         'lbg_forecast_grid': [vp, i, c_double_p, c_double_p, c_double_p, i, c_double_p, c_double_p, c_double_p, c_double_p,

@@ -7,6 +7,7 @@
 // The work is tiny at reference sizes (<= 4951 multipoles, matrices <= 20 x 20): these kernels are latency bound and
 // no roofline fraction is claimed for them.
 #include "common.cuh"
+#include <cstring>
 #include "fisher_dev.cuh"
 #include <cmath>
 
@@ -26,6 +27,36 @@ snr_kernel(int n, const double* __restrict__ ell, const double* __restrict__ cl,
     }
     block_sum<1>(acc, sm);
     if (threadIdx.x == 0) out[0] = sqrt(acc[0]);
+}
+
+// The experiment x delensing x dilution sweep of snr.py:107-133 in one launch: CTA (d, r, e) evaluates, for every multipole,
+//   var = (((1 - rho_r^2) C_kk + N_kk^e) (C_gg + N_gg^d) + C_kg^2) / ((2 L + 1) fsky_e)            (Ckg.py:61-87 with rho, :69-71)
+// with numpy's roundings (one per operation, as the var_Ckg mirror produces it on the host), then the sum of snr_kernel above in
+// the same order: the value equals var_Ckg(...) followed by snr(...) for that design bit for bit.
+__global__ void __launch_bounds__(RED_T)
+snr_grid_kernel(int n, const double* __restrict__ ell, const double* __restrict__ nmodes, const double* __restrict__ ckk,
+                const double* __restrict__ cgg, const double* __restrict__ ckg, const double* __restrict__ nkk /*[n_exp][n]*/,
+                const double* __restrict__ fsky /*[n_exp]*/, const double* __restrict__ rho /*[n_rho][n]*/,
+                const double* __restrict__ ngg /*[n_dil]*/, double lmax, double* __restrict__ out /*[n_exp][n_rho][n_dil]*/) {
+    __shared__ double sm[RED_T];
+    const int d = blockIdx.x, r = blockIdx.y, e = blockIdx.z;
+    const double* nk = nkk + (size_t)e * n;
+    const double* rh = rho + (size_t)r * n;
+    const double fs = fsky[e], ng = ngg[d];
+    double acc[1] = {0.0};
+    for (int i = threadIdx.x; i < n; i += RED_T) {
+        const double L = ell[i];
+        if (L <= lmax) {
+            const double kk = __dmul_rn(__dsub_rn(1.0, __dmul_rn(rh[i], rh[i])), ckk[i]);
+            const double num = __dadd_rn(__dmul_rn(__dadd_rn(kk, nk[i]), __dadd_rn(cgg[i], ng)), __dmul_rn(ckg[i], ckg[i]));
+            const double den = __dmul_rn(__dadd_rn(__dmul_rn(2.0, L), 1.0), fs);
+            const double var = __ddiv_rn(num, den);
+            const double q = ckg[i] / sqrt(var);
+            acc[0] += nmodes[i] * (q * q);
+        }
+    }
+    block_sum<1>(acc, sm);
+    if (threadIdx.x == 0) out[((size_t)e * gridDim.y + r) * gridDim.x + d] = sqrt(acc[0]);
 }
 
 // interloper.py:42-63 for any set of fields: tot[l][a][b] = (C + N)^{ab}(l); spectrum i is the field pair (sa[i], sb[i]).
@@ -174,6 +205,39 @@ extern "C" int lbg_snr(lbg_ctx* c, int n_ell, const double* ell, const double* c
     t.launched();
     LBG_CUDA(cudaMemcpyAsync(out_snr, d + 4 * (size_t)n_ell, 8, cudaMemcpyDeviceToHost, st));
     return t.finish();
+}
+
+extern "C" int lbg_snr_grid(lbg_ctx* c, int n_ell, const double* ell, const double* nmodes, const double* ckk, const double* cgg,
+                            const double* ckg, int n_exp, const double* nkk, const double* fsky, int n_rho, const double* rho,
+                            int n_dil, const double* ngg, double lmax, double* out) {
+    LBG_REQUIRE(c && out, "lbg_snr_grid: NULL argument");
+    LBG_REQUIRE(n_ell >= 0 && n_exp >= 1 && n_exp <= 65535 && n_rho >= 1 && n_rho <= 65535 && n_dil >= 1,
+                "lbg_snr_grid: bad sizes n_ell=%d n_exp=%d n_rho=%d n_dil=%d", n_ell, n_exp, n_rho, n_dil);
+    LBG_REQUIRE(fsky && ngg && (n_ell == 0 || (ell && nmodes && ckk && cgg && ckg && nkk && rho)), "lbg_snr_grid: NULL argument");
+    for (int e = 0; e < n_exp; ++e) LBG_REQUIRE(fsky[e] > 0, "lbg_snr_grid: fsky[%d] must be positive", e);
+    const size_t no = (size_t)n_exp * n_rho * n_dil;
+    if (n_ell == 0) { for (size_t i = 0; i < no; ++i) out[i] = 0.0; return LBG_OK; }
+    std::lock_guard<std::mutex> g(c->mu);
+    LBG_CUDA(cudaSetDevice(c->device));
+    // one pinned staging block: [ell | nmodes | ckk | cgg | ckg | nkk | rho | fsky | ngg]
+    const size_t ne = (size_t)n_ell, n_in = 5 * ne + (size_t)n_exp * ne + (size_t)n_rho * ne + n_exp + n_dil;
+    if (c->s0.reserve(n_in * 8) || c->pin_in.reserve(n_in * 8) || c->s4.reserve(no * 8) || c->pin_out.reserve(no * 8)) return LBG_ENOMEM;
+    double* h = c->pin_in.as<double>();
+    size_t o = 0;
+    auto put = [&](const double* src, size_t n) { size_t at = o; memcpy(h + o, src, n * 8); o += n; return at; };
+    const size_t o_ell = put(ell, ne), o_nm = put(nmodes, ne), o_kk = put(ckk, ne), o_gg = put(cgg, ne), o_kg = put(ckg, ne);
+    const size_t o_nkk = put(nkk, (size_t)n_exp * ne), o_rho = put(rho, (size_t)n_rho * ne), o_fs = put(fsky, n_exp), o_ng = put(ngg, n_dil);
+    cudaStream_t st = c->stream;
+    LBG_CUDA(cudaMemcpyAsync(c->s0.p, h, o * 8, cudaMemcpyHostToDevice, st));
+    const double* d = c->s0.as<double>();
+    KernelTimer t(c);
+    snr_grid_kernel<<<dim3(n_dil, n_rho, n_exp), RED_T, 0, st>>>(n_ell, d + o_ell, d + o_nm, d + o_kk, d + o_gg, d + o_kg, d + o_nkk, d + o_fs,
+                                                                 d + o_rho, d + o_ng, lmax, c->s4.as<double>());
+    t.launched();
+    LBG_CUDA(cudaMemcpyAsync(c->pin_out.p, c->s4.p, no * 8, cudaMemcpyDeviceToHost, st));
+    const int rc = t.finish();
+    if (rc == LBG_OK) memcpy(out, c->pin_out.p, no * 8);
+    return rc;
 }
 
 extern "C" int lbg_gaussian_cov(lbg_ctx* c, int n_ell, const double* ell, int n_f, const double* tot, int n_spec,
